@@ -1,0 +1,227 @@
+/*
+ * b200_paged_attn.h — C ABI of the B200-native paged-attention decode path.
+ *
+ * This is the drop-in boundary.  Every entry point takes plain
+ * device pointers, sizes, element strides and a cudaStream_t passed as void*;
+ * no torch type crosses it.  The reference has no C ABI for this path: it
+ * registers torch-dispatcher ops (csrc/torch_bindings.cpp:45-69, :394-411,
+ * :423-426) whose C++ prototypes are csrc/ops.h:32-53 and csrc/cache.h:21-40.
+ * Each function below names the reference op it stands in for; the torch shim
+ * (vllm_metax_b200/csrc/torch_shim.cpp) turns the op's tensors into these
+ * arguments, exactly as the reference launchers turn them into kernel
+ * arguments (csrc/attention/paged_attention_v1.cu:43-125,
+ * csrc/cache_kernels.cu:407-488).
+ *
+ * Conventions
+ *   - all strides are in ELEMENTS of the tensor they belong to;
+ *   - every pointer is a device pointer unless stated otherwise;
+ *   - calls only enqueue work on `stream`; they never synchronise, never
+ *     allocate device memory and never read device memory on the host, so
+ *     they are CUDA-graph capturable;
+ *   - return value: B200_OK (0) or an error code; b200_last_error() gives
+ *     the message of the last failure on the calling thread.  The library
+ *     never calls exit()/abort().
+ */
+#ifndef B200_PAGED_ATTN_H_
+#define B200_PAGED_ATTN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_PAGED_ATTN_ABI_VERSION 1
+
+/* v2 partition size: template default of the reference launcher
+ * (csrc/attention/paged_attention_v2.cu:45) and of its callers
+ * (tests/kernels/attention/test_attention.py:30).  It fixes the layout of
+ * exp_sums / max_logits / tmp_out, so it is ABI. */
+#define B200_PARTITION_SIZE 512
+
+typedef enum b200_status {
+  B200_OK = 0,
+  B200_ERR_INVALID_ARGUMENT = 1, /* null pointer, negative size, bad enum     */
+  B200_ERR_UNSUPPORTED = 2,      /* head size / block size / dtype / sparse   */
+  B200_ERR_CUDA = 3,             /* a CUDA runtime call or launch failed      */
+  B200_ERR_WORKSPACE = 4         /* workspace missing or too small            */
+} b200_status_t;
+
+/* dtype of query / out / key / value (reference: float, half, bf16 —
+ * csrc/quantization/fp8/metax/quant_utils.cuh:29-39). */
+typedef enum b200_dtype {
+  B200_DTYPE_F32 = 0,
+  B200_DTYPE_F16 = 1,
+  B200_DTYPE_BF16 = 2,
+  B200_DTYPE_U8 = 3 /* only as the fp8 side of b200_convert_fp8 */
+} b200_dtype_t;
+
+/* kv_cache_dtype string of the ops ("auto" | "fp8" | "fp8_e4m3";
+ * csrc/cache_kernels.cu:581,595).  "fp8_e5m2" is listed by the reference enum
+ * (csrc/attention/dtype_fp8.cuh:9-13) but implemented nowhere: unsupported. */
+typedef enum b200_kv_dtype {
+  B200_KV_AUTO = 0,
+  B200_KV_FP8_E4M3 = 1
+} b200_kv_dtype_t;
+
+/* Which kernel family served the last attention call (for tests / bench). */
+typedef enum b200_attn_variant {
+  B200_VARIANT_AUTO = 0,    /* choose: stream-MMA when eligible, else generic */
+  B200_VARIANT_GENERIC = 1, /* FMA kernel, any supported shape                */
+  B200_VARIANT_STREAM_MMA = 2 /* TMA ring + mma.sync persistent kernel        */
+} b200_attn_variant_t;
+
+/*
+ * Arguments of paged_attention_v1 / paged_attention_v2.
+ *   reference ops : csrc/torch_bindings.cpp:45-55 (v1), :58-69 (v2)
+ *   reference C++ : csrc/ops.h:32-53
+ * Layouts (csrc/attention/attention_kernels.cuh:79-100):
+ *   out         [num_seqs, num_heads, head_size]              dtype, contiguous
+ *   query       [num_seqs, num_heads, head_size]              dtype, row stride q_stride
+ *   key_cache   [num_blocks, num_kv_heads, head_size/x, block_size, x]
+ *   value_cache [num_blocks, num_kv_heads, head_size, block_size]
+ *               x = 16 / sizeof(cache element); caches are addressed with
+ *               kv_block_stride / kv_head_stride taken from key_cache
+ *               (paged_attention_v1.cu:59-60), cache element = dtype (auto)
+ *               or one e4m3 byte (fp8)
+ *   block_tables[num_seqs, max_num_blocks_per_seq] int32
+ *   seq_lens    [num_seqs] int32
+ *   alibi_slopes[num_heads] float32 or NULL
+ *   k_scale, v_scale : one float32 each, ON THE DEVICE (read by the kernel)
+ * v2 only (caller-allocated scratch, P = ceil(max_seq_len / 512)):
+ *   exp_sums, max_logits [num_seqs, num_heads, P] float32
+ *   tmp_out              [num_seqs, num_heads, P, head_size] dtype
+ * workspace: v1 needs scratch for its split-KV partials (the reference op
+ *   has none because its v1 never splits).  Size it with
+ *   b200_paged_attention_workspace_bytes(); it may be reused across calls on
+ *   the same stream and needs no initialisation.  v2 needs none (NULL, 0).
+ */
+typedef struct b200_paged_attn_params {
+  void* out;
+  const void* query;
+  const void* key_cache;
+  const void* value_cache;
+  const int32_t* block_tables;
+  const int32_t* seq_lens;
+  const float* alibi_slopes; /* nullable */
+  const float* k_scale;
+  const float* v_scale;
+  float* exp_sums;   /* v2 */
+  float* max_logits; /* v2 */
+  void* tmp_out;     /* v2 */
+  void* workspace;   /* v1 */
+  uint64_t workspace_bytes;
+  int64_t q_stride;
+  int64_t kv_block_stride;
+  int64_t kv_head_stride;
+  int32_t num_seqs;
+  int32_t num_heads;
+  int32_t num_kv_heads;
+  int32_t head_size;
+  int32_t block_size;
+  int32_t max_seq_len;
+  int32_t max_num_blocks_per_seq;
+  int32_t dtype;    /* b200_dtype_t of query/out */
+  int32_t kv_dtype; /* b200_kv_dtype_t           */
+  float scale;
+  /* block-sparse arguments of the op signature; dense only
+   * (blocksparse_vert_stride <= 1), as in every reference test
+   * (tests/kernels/attention/test_attention.py:217-222). */
+  int32_t tp_rank;
+  int32_t blocksparse_local_blocks;
+  int32_t blocksparse_vert_stride;
+  int32_t blocksparse_block_size;
+  int32_t blocksparse_head_sliding_step;
+} b200_paged_attn_params_t;
+
+/* Replaces torch.ops._C.paged_attention_v1 (csrc/torch_bindings.cpp:45-55;
+ * csrc/attention/paged_attention_v1.cu:160-182). */
+int b200_paged_attention_v1(const b200_paged_attn_params_t* params, void* stream);
+
+/* Replaces torch.ops._C.paged_attention_v2 incl. its reduce kernel
+ * (csrc/torch_bindings.cpp:58-69; csrc/attention/paged_attention_v2.cu:167-192;
+ * csrc/attention/attention_kernels.cuh:556-658). */
+int b200_paged_attention_v2(const b200_paged_attn_params_t* params, void* stream);
+
+/* Bytes of workspace b200_paged_attention_v1 needs for these shapes (pointer
+ * fields of params are ignored).  Host-only, no CUDA call. */
+uint64_t b200_paged_attention_workspace_bytes(const b200_paged_attn_params_t* params);
+
+/*
+ * Arguments of reshape_and_cache / reshape_and_cache_flash.
+ *   reference ops : csrc/torch_bindings.cpp:394-400, :403-411
+ *   reference C++ : csrc/cache.h:21-40; csrc/cache_kernels.cu:407-433, :450-488
+ *   key, value  [num_tokens(+padding), num_heads, head_size] dtype,
+ *               token strides key_stride / value_stride, heads*dims contiguous
+ *   slot_mapping[num_tokens] int64; slot < 0 = padding, skipped
+ *               (csrc/cache_kernels.cu:217-220, :285-289)
+ * reshape_and_cache: contiguous v1/v2 layout, x = key_cache.size(4)
+ *               (index math from sizes, csrc/cache_kernels.cu:235-242).
+ * reshape_and_cache_flash: caches [num_blocks, block_size, num_heads, head_size]
+ *               addressed by block_stride / page_stride / head_stride
+ *               (= key_cache.stride(0/1/2)); NHD iff head_stride == head_size
+ *               (csrc/cache_kernels.cu:303), else per-head rows (HND).
+ */
+typedef struct b200_cache_write_params {
+  const void* key;
+  const void* value;
+  void* key_cache;
+  void* value_cache;
+  const int64_t* slot_mapping;
+  const float* k_scale; /* device; read only when kv_dtype != auto */
+  const float* v_scale;
+  int64_t key_stride;
+  int64_t value_stride;
+  int64_t block_stride; /* flash only */
+  int64_t page_stride;  /* flash only */
+  int64_t head_stride;  /* flash only */
+  int32_t num_tokens;   /* = slot_mapping.size(0) (csrc/cache_kernels.cu:417,469) */
+  int32_t num_heads;
+  int32_t head_size;
+  int32_t block_size;
+  int32_t x;        /* reshape_and_cache only */
+  int32_t dtype;    /* b200_dtype_t of key/value */
+  int32_t kv_dtype; /* b200_kv_dtype_t           */
+} b200_cache_write_params_t;
+
+/* Replaces torch.ops._C_cache_ops.reshape_and_cache. */
+int b200_reshape_and_cache(const b200_cache_write_params_t* params, void* stream);
+
+/* Replaces torch.ops._C_cache_ops.reshape_and_cache_flash. */
+int b200_reshape_and_cache_flash(const b200_cache_write_params_t* params, void* stream);
+
+/* Replaces torch.ops._C_cache_ops.convert_fp8 (csrc/torch_bindings.cpp:423-426;
+ * csrc/cache_kernels.cu:543-614).  Element-wise over num_elements
+ * (= size(0) * stride(0) of the op's tensors).  Exactly one of
+ * dst_dtype / src_dtype is B200_DTYPE_U8: src U8 = dequantise
+ * (float(e4m3) * scale -> dst dtype), dst U8 = quantise
+ * (e4m3_satfinite_rn(float(x) / scale)).  scale is a HOST float. */
+int b200_convert_fp8(void* dst, const void* src, int64_t num_elements, float scale,
+                     int32_t dst_dtype, int32_t src_dtype, int32_t kv_dtype, void* stream);
+
+/* "auto" -> B200_KV_AUTO, "fp8" | "fp8_e4m3" -> B200_KV_FP8_E4M3, anything
+ * else (incl. "fp8_e5m2") -> -1. */
+int b200_kv_dtype_from_string(const char* kv_cache_dtype);
+
+/* Message of the last error on this thread ("" if none). */
+const char* b200_last_error(void);
+
+/* ABI version of the loaded library (B200_PAGED_ATTN_ABI_VERSION). */
+int b200_abi_version(void);
+
+/* Test/bench hooks: force a kernel family (b200_attn_variant_t; AUTO
+ * restores dispatch) and read back which one the last attention call on this
+ * thread used.  Forcing STREAM_MMA on an ineligible shape fails with
+ * B200_ERR_UNSUPPORTED instead of falling back. */
+int b200_set_attention_variant(int variant);
+int b200_last_attention_variant(void);
+
+/* Number of kernel launches the library has enqueued from this process since
+ * load (bench.py reports it as gpu_launches). */
+uint64_t b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_PAGED_ATTN_H_ */

@@ -1,0 +1,252 @@
+"""ctypes binding of the C ABI in include/b200_paged_attn.h.
+
+Used by the bench harness and the parity tests to call the library without the torch
+dispatcher (raw device pointers, sizes, strides, a stream handle).  Struct layouts below must
+match the header field for field; tests/test_abi.py checks sizeof() and the exported symbols.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+LIB_PATH = Path(__file__).resolve().parent / "libb200_paged_attn.so"
+
+B200_OK = 0
+ERR_INVALID_ARGUMENT, ERR_UNSUPPORTED, ERR_CUDA, ERR_WORKSPACE = 1, 2, 3, 4
+DTYPE_F32, DTYPE_F16, DTYPE_BF16, DTYPE_U8 = 0, 1, 2, 3
+KV_AUTO, KV_FP8_E4M3 = 0, 1
+VARIANT_AUTO, VARIANT_GENERIC, VARIANT_STREAM_MMA = 0, 1, 2
+PARTITION_SIZE = 512
+
+# every symbol include/b200_paged_attn.h declares
+EXPORTED_SYMBOLS = (
+    "b200_paged_attention_v1",
+    "b200_paged_attention_v2",
+    "b200_paged_attention_workspace_bytes",
+    "b200_reshape_and_cache",
+    "b200_reshape_and_cache_flash",
+    "b200_convert_fp8",
+    "b200_kv_dtype_from_string",
+    "b200_last_error",
+    "b200_abi_version",
+    "b200_set_attention_variant",
+    "b200_last_attention_variant",
+    "b200_launch_count",
+)
+
+
+class PagedAttnParams(C.Structure):
+    _fields_ = [
+        ("out", C.c_void_p),
+        ("query", C.c_void_p),
+        ("key_cache", C.c_void_p),
+        ("value_cache", C.c_void_p),
+        ("block_tables", C.c_void_p),
+        ("seq_lens", C.c_void_p),
+        ("alibi_slopes", C.c_void_p),
+        ("k_scale", C.c_void_p),
+        ("v_scale", C.c_void_p),
+        ("exp_sums", C.c_void_p),
+        ("max_logits", C.c_void_p),
+        ("tmp_out", C.c_void_p),
+        ("workspace", C.c_void_p),
+        ("workspace_bytes", C.c_uint64),
+        ("q_stride", C.c_int64),
+        ("kv_block_stride", C.c_int64),
+        ("kv_head_stride", C.c_int64),
+        ("num_seqs", C.c_int32),
+        ("num_heads", C.c_int32),
+        ("num_kv_heads", C.c_int32),
+        ("head_size", C.c_int32),
+        ("block_size", C.c_int32),
+        ("max_seq_len", C.c_int32),
+        ("max_num_blocks_per_seq", C.c_int32),
+        ("dtype", C.c_int32),
+        ("kv_dtype", C.c_int32),
+        ("scale", C.c_float),
+        ("tp_rank", C.c_int32),
+        ("blocksparse_local_blocks", C.c_int32),
+        ("blocksparse_vert_stride", C.c_int32),
+        ("blocksparse_block_size", C.c_int32),
+        ("blocksparse_head_sliding_step", C.c_int32),
+    ]
+
+
+class CacheWriteParams(C.Structure):
+    _fields_ = [
+        ("key", C.c_void_p),
+        ("value", C.c_void_p),
+        ("key_cache", C.c_void_p),
+        ("value_cache", C.c_void_p),
+        ("slot_mapping", C.c_void_p),
+        ("k_scale", C.c_void_p),
+        ("v_scale", C.c_void_p),
+        ("key_stride", C.c_int64),
+        ("value_stride", C.c_int64),
+        ("block_stride", C.c_int64),
+        ("page_stride", C.c_int64),
+        ("head_stride", C.c_int64),
+        ("num_tokens", C.c_int32),
+        ("num_heads", C.c_int32),
+        ("head_size", C.c_int32),
+        ("block_size", C.c_int32),
+        ("x", C.c_int32),
+        ("dtype", C.c_int32),
+        ("kv_dtype", C.c_int32),
+    ]
+
+
+_lib = None
+
+
+class B200Error(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(msg)
+        self.code = code
+
+
+def load() -> C.CDLL:
+    """dlopen the C-ABI library; fail loudly (no fallback) if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise ImportError(
+            "%s is missing: the CUDA kernels are not built. Run `python -m vllm_metax_b200.build` "
+            "(there is no CPU fallback for this path)." % LIB_PATH
+        )
+    lib = C.CDLL(os.fspath(LIB_PATH), mode=C.RTLD_GLOBAL)
+    P = C.POINTER
+    lib.b200_paged_attention_v1.argtypes = [P(PagedAttnParams), C.c_void_p]
+    lib.b200_paged_attention_v1.restype = C.c_int
+    lib.b200_paged_attention_v2.argtypes = [P(PagedAttnParams), C.c_void_p]
+    lib.b200_paged_attention_v2.restype = C.c_int
+    lib.b200_paged_attention_workspace_bytes.argtypes = [P(PagedAttnParams)]
+    lib.b200_paged_attention_workspace_bytes.restype = C.c_uint64
+    lib.b200_reshape_and_cache.argtypes = [P(CacheWriteParams), C.c_void_p]
+    lib.b200_reshape_and_cache.restype = C.c_int
+    lib.b200_reshape_and_cache_flash.argtypes = [P(CacheWriteParams), C.c_void_p]
+    lib.b200_reshape_and_cache_flash.restype = C.c_int
+    lib.b200_convert_fp8.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_int32, C.c_int32, C.c_int32,
+                                     C.c_void_p]
+    lib.b200_convert_fp8.restype = C.c_int
+    lib.b200_kv_dtype_from_string.argtypes = [C.c_char_p]
+    lib.b200_kv_dtype_from_string.restype = C.c_int
+    lib.b200_last_error.argtypes = []
+    lib.b200_last_error.restype = C.c_char_p
+    lib.b200_abi_version.argtypes = []
+    lib.b200_abi_version.restype = C.c_int
+    lib.b200_set_attention_variant.argtypes = [C.c_int]
+    lib.b200_set_attention_variant.restype = C.c_int
+    lib.b200_last_attention_variant.argtypes = []
+    lib.b200_last_attention_variant.restype = C.c_int
+    lib.b200_launch_count.argtypes = []
+    lib.b200_launch_count.restype = C.c_uint64
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> None:
+    if rc != B200_OK:
+        raise B200Error(rc, load().b200_last_error().decode())
+
+
+def launch_count() -> int:
+    return int(load().b200_launch_count())
+
+
+def set_attention_variant(v: int) -> None:
+    check(load().b200_set_attention_variant(v))
+
+
+def last_attention_variant() -> int:
+    return int(load().b200_last_attention_variant())
+
+
+# ---- torch-tensor conveniences (pointers only; torch is plumbing here) ----------------------
+def _torch_dtype_code(t) -> int:
+    import torch
+
+    return {torch.float32: DTYPE_F32, torch.float16: DTYPE_F16, torch.bfloat16: DTYPE_BF16,
+            torch.uint8: DTYPE_U8, torch.float8_e4m3fn: DTYPE_U8}[t]
+
+
+def kv_dtype_code(s: str) -> int:
+    v = load().b200_kv_dtype_from_string(s.encode())
+    if v < 0:
+        raise B200Error(ERR_UNSUPPORTED, "Unsupported data type of kv cache: %s" % s)
+    return v
+
+
+def attn_params(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables, seq_lens, block_size,
+                max_seq_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale, exp_sums=None, max_logits=None,
+                tmp_out=None, workspace=None) -> PagedAttnParams:
+    p = PagedAttnParams()
+    p.out = out.data_ptr()
+    p.query = query.data_ptr()
+    p.key_cache = key_cache.data_ptr()
+    p.value_cache = value_cache.data_ptr()
+    p.block_tables = block_tables.data_ptr()
+    p.seq_lens = seq_lens.data_ptr()
+    p.alibi_slopes = alibi_slopes.data_ptr() if alibi_slopes is not None else None
+    p.k_scale = k_scale.data_ptr()
+    p.v_scale = v_scale.data_ptr()
+    if exp_sums is not None:
+        p.exp_sums, p.max_logits, p.tmp_out = exp_sums.data_ptr(), max_logits.data_ptr(), tmp_out.data_ptr()
+    if workspace is not None:
+        p.workspace, p.workspace_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+    p.q_stride = query.stride(0)
+    p.kv_block_stride = key_cache.stride(0)
+    p.kv_head_stride = key_cache.stride(1)
+    p.num_seqs, p.num_heads, p.head_size = query.shape
+    p.num_kv_heads = num_kv_heads
+    p.block_size = block_size
+    p.max_seq_len = max_seq_len
+    p.max_num_blocks_per_seq = block_tables.shape[1]
+    p.dtype = _torch_dtype_code(query.dtype)
+    p.kv_dtype = kv_dtype_code(kv_cache_dtype)
+    p.scale = scale
+    p.blocksparse_block_size = 64
+    return p
+
+
+def workspace_bytes(p: PagedAttnParams) -> int:
+    return int(load().b200_paged_attention_workspace_bytes(C.byref(p)))
+
+
+def paged_attention_v1(p: PagedAttnParams, stream: int) -> None:
+    check(load().b200_paged_attention_v1(C.byref(p), C.c_void_p(stream)))
+
+
+def paged_attention_v2(p: PagedAttnParams, stream: int) -> None:
+    check(load().b200_paged_attention_v2(C.byref(p), C.c_void_p(stream)))
+
+
+def cache_params(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale, v_scale,
+                 flash: bool) -> CacheWriteParams:
+    p = CacheWriteParams()
+    p.key, p.value = key.data_ptr(), value.data_ptr()
+    p.key_cache, p.value_cache = key_cache.data_ptr(), value_cache.data_ptr()
+    p.slot_mapping = slot_mapping.data_ptr()
+    p.k_scale, p.v_scale = k_scale.data_ptr(), v_scale.data_ptr()
+    p.key_stride, p.value_stride = key.stride(0), value.stride(0)
+    p.num_tokens = slot_mapping.shape[0]
+    p.num_heads, p.head_size = key.shape[1], key.shape[2]
+    p.dtype = _torch_dtype_code(key.dtype)
+    p.kv_dtype = kv_dtype_code(kv_cache_dtype)
+    if flash:
+        p.block_size = key_cache.shape[1]
+        p.block_stride, p.page_stride, p.head_stride = key_cache.stride(0), key_cache.stride(1), key_cache.stride(2)
+    else:
+        p.block_size = key_cache.shape[3]
+        p.x = key_cache.shape[4]
+    return p
+
+
+def reshape_and_cache(p: CacheWriteParams, stream: int) -> None:
+    check(load().b200_reshape_and_cache(C.byref(p), C.c_void_p(stream)))
+
+
+def reshape_and_cache_flash(p: CacheWriteParams, stream: int) -> None:
+    check(load().b200_reshape_and_cache_flash(C.byref(p), C.c_void_p(stream)))

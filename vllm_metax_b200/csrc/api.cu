@@ -1,0 +1,237 @@
+// C ABI of the paged-attention decode path: validation, kernel-family
+// dispatch, error plumbing.  See include/b200_paged_attn.h for the contract
+// and the reference entry points each function replaces
+// (csrc/attention/paged_attention_v1.cu:160-182, paged_attention_v2.cu:167-192).
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <atomic>
+
+#include "common.cuh"
+
+namespace b200 {
+
+namespace {
+thread_local char g_error[512] = "";
+thread_local int g_forced_variant = B200_VARIANT_AUTO;
+thread_local int g_last_variant = B200_VARIANT_AUTO;
+std::atomic<uint64_t> g_launches{0};
+}  // namespace
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: kernel launch failed: %s", what, cudaGetErrorString(e));
+    return B200_ERR_CUDA;
+  }
+  return B200_OK;
+}
+
+int device_sm_count() {
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    cudaGetLastError();
+    return 148;
+  }
+  int v = cache[dev].load(std::memory_order_relaxed);
+  if (v > 0) return v;
+  if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) {
+    cudaGetLastError();
+    v = 148;
+  }
+  cache[dev].store(v, std::memory_order_relaxed);
+  return v;
+}
+
+// Partition size the v1 op uses internally.  The generic kernel always cuts at
+// 512 tokens (its shared-memory logit buffer).  The streaming kernel cuts a
+// sequence only as far as needed to give every SM an equal number of work
+// items: the smallest partition count whose last wave is >= 95 % full.
+int v1_chunk_tokens(const b200_paged_attn_params_t& p, bool stream_variant) {
+  if (!stream_variant) return B200_PARTITION_SIZE;
+  const int nsm = device_sm_count();
+  const int L = max(32, (p.max_seq_len + 31) / 32 * 32);
+  const int64_t pairs = (int64_t)p.num_seqs * p.num_kv_heads;
+  int best_chunk = L;
+  double best_eff = 0.0;
+  for (int parts = 1; parts <= 4096; ++parts) {
+    int chunk = ((L + parts - 1) / parts + 31) / 32 * 32;
+    if (chunk < 128 && parts > 1) break;
+    const int P = (L + chunk - 1) / chunk;
+    const double items = (double)pairs * P;
+    const double waves = items / nsm;
+    const double eff = waves / (double)((int64_t)((items + nsm - 1) / nsm));
+    if (eff > best_eff + 1e-9) {
+      best_eff = eff;
+      best_chunk = chunk;
+    }
+    if (eff >= 0.95) break;
+  }
+  return best_chunk;
+}
+
+namespace {
+
+bool head_size_supported(int d) {
+  // csrc/attention/paged_attention_v1.cu:90-124
+  switch (d) {
+    case 32: case 64: case 80: case 96: case 112: case 120: case 128: case 192: case 256: return true;
+    default: return false;
+  }
+}
+
+int validate_attn(const b200_paged_attn_params_t* p, bool v2) {
+  B200_REQUIRE(p != nullptr, B200_ERR_INVALID_ARGUMENT, "params is NULL");
+  B200_REQUIRE(p->num_seqs >= 0 && p->num_heads > 0 && p->num_kv_heads > 0, B200_ERR_INVALID_ARGUMENT,
+               "bad sizes: seqs=%d heads=%d kv_heads=%d", p->num_seqs, p->num_heads, p->num_kv_heads);
+  B200_REQUIRE(p->num_heads % p->num_kv_heads == 0, B200_ERR_INVALID_ARGUMENT,
+               "num_heads %d is not a multiple of num_kv_heads %d", p->num_heads, p->num_kv_heads);
+  B200_REQUIRE(p->dtype == B200_DTYPE_F32 || p->dtype == B200_DTYPE_F16 || p->dtype == B200_DTYPE_BF16,
+               B200_ERR_UNSUPPORTED, "Unsupported data type: %d", p->dtype);
+  B200_REQUIRE(p->kv_dtype == B200_KV_AUTO || p->kv_dtype == B200_KV_FP8_E4M3, B200_ERR_UNSUPPORTED,
+               "Unsupported data type of kv cache: %d", p->kv_dtype);
+  B200_REQUIRE(head_size_supported(p->head_size), B200_ERR_UNSUPPORTED, "Unsupported head size: %d", p->head_size);
+  B200_REQUIRE(p->block_size == 8 || p->block_size == 16 || p->block_size == 32, B200_ERR_UNSUPPORTED,
+               "Unsupported block size: %d", p->block_size);
+  B200_REQUIRE(p->blocksparse_vert_stride <= 1, B200_ERR_UNSUPPORTED,
+               "block-sparse attention (blocksparse_vert_stride=%d) is not supported", p->blocksparse_vert_stride);
+  if (p->num_seqs == 0) return B200_OK;
+  B200_REQUIRE(p->out && p->query && p->key_cache && p->value_cache && p->block_tables && p->seq_lens,
+               B200_ERR_INVALID_ARGUMENT, "NULL tensor pointer");
+  B200_REQUIRE(p->max_seq_len >= 0 &&
+                   (int64_t)p->max_seq_len <= (int64_t)p->max_num_blocks_per_seq * p->block_size,
+               B200_ERR_INVALID_ARGUMENT, "max_seq_len %d exceeds block table capacity %d x %d", p->max_seq_len,
+               p->max_num_blocks_per_seq, p->block_size);
+  const int eb = p->kv_dtype == B200_KV_FP8_E4M3 ? 1 : dtype_bytes(p->dtype);
+  const int x = 16 / eb;
+  B200_REQUIRE(p->head_size % x == 0, B200_ERR_UNSUPPORTED, "head size %d is not a multiple of x=%d", p->head_size, x);
+  if (p->kv_dtype != B200_KV_AUTO)
+    B200_REQUIRE(p->k_scale && p->v_scale, B200_ERR_INVALID_ARGUMENT, "fp8 cache needs k_scale/v_scale");
+  B200_REQUIRE((p->kv_block_stride * eb) % 16 == 0 && (p->kv_head_stride * eb) % 16 == 0 &&
+                   reinterpret_cast<uintptr_t>(p->key_cache) % 16 == 0 &&
+                   reinterpret_cast<uintptr_t>(p->value_cache) % 16 == 0,
+               B200_ERR_UNSUPPORTED, "KV cache must be 16-byte aligned with 16-byte-multiple block/head strides");
+  if (v2)
+    B200_REQUIRE(p->exp_sums && p->max_logits && p->tmp_out, B200_ERR_INVALID_ARGUMENT,
+                 "paged_attention_v2 needs exp_sums / max_logits / tmp_out");
+  return B200_OK;
+}
+
+// returns B200_VARIANT_* to run, or a negative status on failure
+int pick_variant(const b200_paged_attn_params_t& p) {
+  const char* why = nullptr;
+  const bool ok = stream_variant_eligible(p, &why);
+  if (g_forced_variant == B200_VARIANT_STREAM_MMA) {
+    if (!ok) {
+      set_error("stream variant forced but not eligible: %s", why);
+      return -B200_ERR_UNSUPPORTED;
+    }
+    return B200_VARIANT_STREAM_MMA;
+  }
+  if (g_forced_variant == B200_VARIANT_GENERIC) return B200_VARIANT_GENERIC;
+  return ok ? B200_VARIANT_STREAM_MMA : B200_VARIANT_GENERIC;
+}
+
+uint64_t split_bytes(const b200_paged_attn_params_t& p, int chunk) {
+  const int64_t P = (p.max_seq_len + chunk - 1) / chunk;
+  if (P <= 1) return 0;
+  return (uint64_t)p.num_seqs * p.num_heads * P * (p.head_size + 2) * sizeof(float);
+}
+
+}  // namespace
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" uint64_t b200_paged_attention_workspace_bytes(const b200_paged_attn_params_t* p) {
+  if (p == nullptr || p->num_seqs <= 0 || p->num_heads <= 0 || p->num_kv_heads <= 0 || p->max_seq_len <= 0) return 0;
+  const uint64_t a = split_bytes(*p, v1_chunk_tokens(*p, false));
+  const uint64_t b = split_bytes(*p, v1_chunk_tokens(*p, true));
+  return a > b ? a : b;
+}
+
+extern "C" int b200_paged_attention_v1(const b200_paged_attn_params_t* p, void* stream) {
+  int rc = validate_attn(p, false);
+  if (rc != B200_OK) return rc;
+  if (p->num_seqs == 0 || p->max_seq_len == 0) return B200_OK;
+  const int variant = pick_variant(*p);
+  if (variant < 0) return -variant;
+  const bool stream_v = variant == B200_VARIANT_STREAM_MMA;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  SplitOut so;
+  so.chunk = v1_chunk_tokens(*p, stream_v);
+  so.num_partitions = (p->max_seq_len + so.chunk - 1) / so.chunk;
+  so.normalized = 0;
+  so.m = so.l = nullptr;
+  so.o = nullptr;
+  if (so.num_partitions > 1) {
+    const uint64_t need = split_bytes(*p, so.chunk);
+    B200_REQUIRE(p->workspace != nullptr && p->workspace_bytes >= need, B200_ERR_WORKSPACE,
+                 "paged_attention_v1 needs %llu bytes of workspace, got %llu", (unsigned long long)need,
+                 (unsigned long long)(p->workspace ? p->workspace_bytes : 0));
+    B200_REQUIRE(reinterpret_cast<uintptr_t>(p->workspace) % 16 == 0, B200_ERR_WORKSPACE,
+                 "workspace must be 16-byte aligned");
+    const int64_t n = (int64_t)p->num_seqs * p->num_heads * so.num_partitions;
+    so.o = p->workspace;
+    so.m = static_cast<float*>(p->workspace) + n * p->head_size;
+    so.l = so.m + n;
+  }
+  rc = stream_v ? launch_attention_stream(*p, so, s) : launch_attention_generic(*p, so, s);
+  if (rc != B200_OK) return rc;
+  g_last_variant = variant;
+  return launch_split_reduce(*p, so, s);
+}
+
+extern "C" int b200_paged_attention_v2(const b200_paged_attn_params_t* p, void* stream) {
+  int rc = validate_attn(p, true);
+  if (rc != B200_OK) return rc;
+  if (p->num_seqs == 0 || p->max_seq_len == 0) return B200_OK;
+  const int variant = pick_variant(*p);
+  if (variant < 0) return -variant;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // the caller sized exp_sums / max_logits / tmp_out for 512-token partitions
+  // (csrc/attention/paged_attention_v2.cu:45,82)
+  SplitOut so;
+  so.chunk = B200_PARTITION_SIZE;
+  so.num_partitions = (p->max_seq_len + so.chunk - 1) / so.chunk;
+  so.normalized = 1;
+  so.m = p->max_logits;
+  so.l = p->exp_sums;
+  so.o = p->tmp_out;
+  rc = variant == B200_VARIANT_STREAM_MMA ? launch_attention_stream(*p, so, s) : launch_attention_generic(*p, so, s);
+  if (rc != B200_OK) return rc;
+  g_last_variant = variant;
+  return launch_split_reduce(*p, so, s);
+}
+
+extern "C" int b200_kv_dtype_from_string(const char* s) {
+  if (s == nullptr) return -1;
+  if (strcmp(s, "auto") == 0) return B200_KV_AUTO;
+  if (strcmp(s, "fp8") == 0 || strcmp(s, "fp8_e4m3") == 0) return B200_KV_FP8_E4M3;
+  return -1;
+}
+
+extern "C" const char* b200_last_error(void) { return g_error; }
+extern "C" int b200_abi_version(void) { return B200_PAGED_ATTN_ABI_VERSION; }
+
+extern "C" int b200_set_attention_variant(int variant) {
+  if (variant != B200_VARIANT_AUTO && variant != B200_VARIANT_GENERIC && variant != B200_VARIANT_STREAM_MMA) {
+    set_error("unknown attention variant %d", variant);
+    return B200_ERR_INVALID_ARGUMENT;
+  }
+  g_forced_variant = variant;
+  return B200_OK;
+}
+extern "C" int b200_last_attention_variant(void) { return g_last_variant; }
+extern "C" uint64_t b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }

@@ -1,0 +1,377 @@
+// Thin torch-dispatcher shim: registers the reference's operator schemas and
+// forwards to the C ABI in include/b200_paged_attn.h.
+//
+// The schema strings are byte-identical to the reference's registrations
+// (csrc/torch_bindings.cpp:45-55, :58-69, :394-400, :403-411, :423-426), under
+// the same library names `_C` and `_C_cache_ops`, with CUDA-key
+// implementations only (the reference registers torch::kCUDA only: :55, :69,
+// :400, :410).  There is deliberately no CPU implementation: on a tensor that
+// is not on a CUDA device the dispatcher raises, exactly as with the reference.
+//
+// If another library already defined the schemas in this process (upstream
+// vllm._C, whose strings are identical), only the CUDA kernels are overridden.
+#include <ATen/cuda/CUDAContext.h>
+#include <Python.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <torch/library.h>
+#include <torch/types.h>
+
+#include <memory>
+#include <mutex>
+#include <optional>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/b200_paged_attn.h"
+
+namespace {
+
+int to_dtype(at::ScalarType t) {
+  switch (t) {
+    case at::kFloat: return B200_DTYPE_F32;
+    case at::kHalf: return B200_DTYPE_F16;
+    case at::kBFloat16: return B200_DTYPE_BF16;
+    case at::kByte: return B200_DTYPE_U8;
+    case at::kFloat8_e4m3fn: return B200_DTYPE_U8;
+    default: return -1;
+  }
+}
+
+int kv_dtype_or_throw(const std::string& s) {
+  const int kv = b200_kv_dtype_from_string(s.c_str());
+  // csrc/quantization/fp8/metax/quant_utils.cuh:37-41
+  TORCH_CHECK(kv >= 0, "Unsupported data type of kv cache: ", s);
+  return kv;
+}
+
+void check_status(int rc, const char* op) {
+  TORCH_CHECK(rc == B200_OK, op, ": ", b200_last_error());
+}
+
+bool is_cache_byte_type(at::ScalarType t) { return t == at::kByte || t == at::kFloat8_e4m3fn; }
+
+// v1 split-KV scratch: one growing buffer per (device, stream).  The op has no
+// workspace argument (csrc/torch_bindings.cpp:45-55), so the shim owns it;
+// work on one stream is ordered, so reuse across calls is safe.
+void* v1_workspace(uint64_t bytes, const at::Tensor& like, cudaStream_t stream) {
+  if (bytes == 0) return nullptr;
+  static std::mutex mu;
+  static std::unordered_map<uint64_t, at::Tensor> cache;
+  const uint64_t key = (static_cast<uint64_t>(like.get_device()) << 56) ^ reinterpret_cast<uint64_t>(stream);
+  std::lock_guard<std::mutex> lock(mu);
+  at::Tensor& t = cache[key];
+  if (!t.defined() || static_cast<uint64_t>(t.numel()) < bytes) {
+    const uint64_t want = bytes + bytes / 4;
+    t = at::empty({static_cast<int64_t>(want)}, like.options().dtype(at::kByte));
+  }
+  return t.data_ptr();
+}
+
+void fill_attn_params(b200_paged_attn_params_t& p, at::Tensor& out, const at::Tensor& query,
+                      const at::Tensor& key_cache, const at::Tensor& value_cache, int64_t num_kv_heads,
+                      double scale, const at::Tensor& block_tables, const at::Tensor& seq_lens,
+                      int64_t block_size, int64_t max_seq_len, const std::optional<at::Tensor>& alibi_slopes,
+                      const std::string& kv_cache_dtype, const at::Tensor& k_scale, const at::Tensor& v_scale,
+                      int64_t tp_rank, int64_t bs_local, int64_t bs_vert, int64_t bs_block, int64_t bs_slide) {
+  TORCH_CHECK(query.dim() == 3 && out.dim() == 3, "query/out must be [num_seqs, num_heads, head_size]");
+  TORCH_CHECK(out.scalar_type() == query.scalar_type(), "out and query dtypes differ");
+  TORCH_CHECK(out.is_contiguous(), "out must be contiguous");
+  TORCH_CHECK(query.stride(2) == 1 && query.stride(1) == query.size(2), "query heads must be contiguous");
+  TORCH_CHECK(key_cache.dim() == 5 && value_cache.dim() == 4,
+              "key_cache must be [nb, nkv, hs/x, bs, x] and value_cache [nb, nkv, hs, bs]");
+  TORCH_CHECK(block_tables.scalar_type() == at::kInt && block_tables.dim() == 2 && block_tables.stride(1) == 1,
+              "block_tables must be a 2-D int32 tensor with contiguous rows");
+  TORCH_CHECK(seq_lens.scalar_type() == at::kInt && seq_lens.is_contiguous(), "seq_lens must be contiguous int32");
+  TORCH_CHECK(k_scale.scalar_type() == at::kFloat && v_scale.scalar_type() == at::kFloat,
+              "k_scale / v_scale must be float32 tensors");
+  TORCH_CHECK(query.is_cuda() && key_cache.is_cuda() && value_cache.is_cuda() && block_tables.is_cuda() &&
+                  seq_lens.is_cuda() && k_scale.is_cuda() && v_scale.is_cuda(),
+              "all tensors must be on the CUDA device");
+  const int kv = kv_dtype_or_throw(kv_cache_dtype);
+  if (kv == B200_KV_AUTO) {
+    TORCH_CHECK(key_cache.scalar_type() == query.scalar_type() && value_cache.scalar_type() == query.scalar_type(),
+                "kv_cache_dtype 'auto' needs caches of the query dtype");
+  } else {
+    TORCH_CHECK(is_cache_byte_type(key_cache.scalar_type()) && is_cache_byte_type(value_cache.scalar_type()),
+                "fp8 kv cache must be stored as uint8");
+  }
+  TORCH_CHECK(value_cache.stride(0) == key_cache.stride(0) && value_cache.stride(1) == key_cache.stride(1),
+              "key_cache and value_cache must share block/head strides");
+  const int dt = to_dtype(query.scalar_type());
+  TORCH_CHECK(dt == B200_DTYPE_F32 || dt == B200_DTYPE_F16 || dt == B200_DTYPE_BF16, "Unsupported data type: ",
+              query.scalar_type());
+  memset(&p, 0, sizeof(p));
+  p.out = out.data_ptr();
+  p.query = query.data_ptr();
+  p.key_cache = key_cache.data_ptr();
+  p.value_cache = value_cache.data_ptr();
+  p.block_tables = block_tables.data_ptr<int32_t>();
+  p.seq_lens = seq_lens.data_ptr<int32_t>();
+  if (alibi_slopes.has_value() && alibi_slopes->defined()) {
+    TORCH_CHECK(alibi_slopes->scalar_type() == at::kFloat && alibi_slopes->is_contiguous() &&
+                    alibi_slopes->numel() == query.size(1) && alibi_slopes->is_cuda(),
+                "alibi_slopes must be a contiguous float32 CUDA tensor of num_heads entries");
+    p.alibi_slopes = alibi_slopes->data_ptr<float>();
+  }
+  p.k_scale = k_scale.data_ptr<float>();
+  p.v_scale = v_scale.data_ptr<float>();
+  p.q_stride = query.stride(0);
+  p.kv_block_stride = key_cache.stride(0);
+  p.kv_head_stride = key_cache.stride(1);
+  p.num_seqs = static_cast<int32_t>(query.size(0));
+  p.num_heads = static_cast<int32_t>(query.size(1));
+  p.num_kv_heads = static_cast<int32_t>(num_kv_heads);
+  p.head_size = static_cast<int32_t>(query.size(2));
+  p.block_size = static_cast<int32_t>(block_size);
+  p.max_seq_len = static_cast<int32_t>(max_seq_len);
+  p.max_num_blocks_per_seq = static_cast<int32_t>(block_tables.size(1));
+  p.dtype = dt;
+  p.kv_dtype = kv;
+  p.scale = static_cast<float>(scale);
+  p.tp_rank = static_cast<int32_t>(tp_rank);
+  p.blocksparse_local_blocks = static_cast<int32_t>(bs_local);
+  p.blocksparse_vert_stride = static_cast<int32_t>(bs_vert);
+  p.blocksparse_block_size = static_cast<int32_t>(bs_block);
+  p.blocksparse_head_sliding_step = static_cast<int32_t>(bs_slide);
+  TORCH_CHECK(value_cache.size(3) == block_size && value_cache.size(2) == query.size(2) &&
+                  value_cache.size(1) == num_kv_heads,
+              "value_cache shape does not match num_kv_heads / head_size / block_size");
+  TORCH_CHECK(block_tables.size(0) >= query.size(0) && seq_lens.numel() >= query.size(0),
+              "block_tables / seq_lens have fewer rows than query");
+}
+
+// csrc/ops.h:32-41
+void paged_attention_v1(at::Tensor& out, at::Tensor& query, at::Tensor& key_cache, at::Tensor& value_cache,
+                        int64_t num_kv_heads, double scale, at::Tensor& block_tables, at::Tensor& seq_lens,
+                        int64_t block_size, int64_t max_seq_len, const std::optional<at::Tensor>& alibi_slopes,
+                        const std::string& kv_cache_dtype, at::Tensor& k_scale, at::Tensor& v_scale,
+                        const int64_t tp_rank, const int64_t blocksparse_local_blocks,
+                        const int64_t blocksparse_vert_stride, const int64_t blocksparse_block_size,
+                        const int64_t blocksparse_head_sliding_step) {
+  b200_paged_attn_params_t p;
+  fill_attn_params(p, out, query, key_cache, value_cache, num_kv_heads, scale, block_tables, seq_lens, block_size,
+                   max_seq_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale, tp_rank, blocksparse_local_blocks,
+                   blocksparse_vert_stride, blocksparse_block_size, blocksparse_head_sliding_step);
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  p.workspace_bytes = b200_paged_attention_workspace_bytes(&p);
+  p.workspace = v1_workspace(p.workspace_bytes, query, stream);
+  check_status(b200_paged_attention_v1(&p, stream), "paged_attention_v1");
+}
+
+// csrc/ops.h:43-53
+void paged_attention_v2(at::Tensor& out, at::Tensor& exp_sums, at::Tensor& max_logits, at::Tensor& tmp_out,
+                        at::Tensor& query, at::Tensor& key_cache, at::Tensor& value_cache, int64_t num_kv_heads,
+                        double scale, at::Tensor& block_tables, at::Tensor& seq_lens, int64_t block_size,
+                        int64_t max_seq_len, const std::optional<at::Tensor>& alibi_slopes,
+                        const std::string& kv_cache_dtype, at::Tensor& k_scale, at::Tensor& v_scale,
+                        const int64_t tp_rank, const int64_t blocksparse_local_blocks,
+                        const int64_t blocksparse_vert_stride, const int64_t blocksparse_block_size,
+                        const int64_t blocksparse_head_sliding_step) {
+  b200_paged_attn_params_t p;
+  fill_attn_params(p, out, query, key_cache, value_cache, num_kv_heads, scale, block_tables, seq_lens, block_size,
+                   max_seq_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale, tp_rank, blocksparse_local_blocks,
+                   blocksparse_vert_stride, blocksparse_block_size, blocksparse_head_sliding_step);
+  const int64_t P = (max_seq_len + B200_PARTITION_SIZE - 1) / B200_PARTITION_SIZE;
+  const int64_t S = query.size(0), H = query.size(1), D = query.size(2);
+  TORCH_CHECK(exp_sums.scalar_type() == at::kFloat && max_logits.scalar_type() == at::kFloat &&
+                  exp_sums.is_contiguous() && max_logits.is_contiguous() && exp_sums.numel() >= S * H * P &&
+                  max_logits.numel() >= S * H * P,
+              "exp_sums / max_logits must be contiguous float32 [num_seqs, num_heads, max_num_partitions]");
+  TORCH_CHECK(tmp_out.scalar_type() == query.scalar_type() && tmp_out.is_contiguous() &&
+                  tmp_out.numel() >= S * H * P * D,
+              "tmp_out must be contiguous [num_seqs, num_heads, max_num_partitions, head_size] of the query dtype");
+  TORCH_CHECK(exp_sums.dim() == 3 && exp_sums.size(2) == P,
+              "exp_sums.size(2) must be ceil(max_seq_len / 512)");
+  p.exp_sums = exp_sums.data_ptr<float>();
+  p.max_logits = max_logits.data_ptr<float>();
+  p.tmp_out = tmp_out.data_ptr();
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  check_status(b200_paged_attention_v2(&p, stream), "paged_attention_v2");
+}
+
+void fill_cache_params(b200_cache_write_params_t& p, const at::Tensor& key, const at::Tensor& value,
+                       const at::Tensor& key_cache, const at::Tensor& value_cache, const at::Tensor& slot_mapping,
+                       const std::string& kv_cache_dtype, const at::Tensor& k_scale, const at::Tensor& v_scale) {
+  TORCH_CHECK(key.dim() == 3 && value.dim() == 3, "key/value must be [num_tokens, num_heads, head_size]");
+  TORCH_CHECK(key.scalar_type() == value.scalar_type(), "key and value dtypes differ");
+  TORCH_CHECK(key.stride(2) == 1 && key.stride(1) == key.size(2) && value.stride(2) == 1 &&
+                  value.stride(1) == value.size(2),
+              "key/value heads must be contiguous");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::kLong && slot_mapping.is_contiguous(),
+              "slot_mapping must be contiguous int64");
+  TORCH_CHECK(slot_mapping.size(0) <= key.size(0), "slot_mapping longer than key");
+  TORCH_CHECK(k_scale.scalar_type() == at::kFloat && v_scale.scalar_type() == at::kFloat,
+              "k_scale / v_scale must be float32 tensors");
+  TORCH_CHECK(key.is_cuda() && value.is_cuda() && key_cache.is_cuda() && value_cache.is_cuda() &&
+                  slot_mapping.is_cuda() && k_scale.is_cuda() && v_scale.is_cuda(),
+              "all tensors must be on the CUDA device");
+  const int kv = kv_dtype_or_throw(kv_cache_dtype);
+  if (kv == B200_KV_AUTO) {
+    TORCH_CHECK(key_cache.scalar_type() == key.scalar_type() && value_cache.scalar_type() == key.scalar_type(),
+                "kv_cache_dtype 'auto' needs caches of the key dtype");
+  } else {
+    TORCH_CHECK(is_cache_byte_type(key_cache.scalar_type()) && is_cache_byte_type(value_cache.scalar_type()),
+                "fp8 kv cache must be stored as uint8");
+  }
+  const int dt = to_dtype(key.scalar_type());
+  TORCH_CHECK(dt == B200_DTYPE_F32 || dt == B200_DTYPE_F16 || dt == B200_DTYPE_BF16,
+              "Unsupported input type of kv cache: ", key.scalar_type());
+  memset(&p, 0, sizeof(p));
+  p.key = key.data_ptr();
+  p.value = value.data_ptr();
+  p.key_cache = key_cache.data_ptr();
+  p.value_cache = value_cache.data_ptr();
+  p.slot_mapping = slot_mapping.data_ptr<int64_t>();
+  p.k_scale = k_scale.data_ptr<float>();
+  p.v_scale = v_scale.data_ptr<float>();
+  p.key_stride = key.stride(0);
+  p.value_stride = value.stride(0);
+  p.num_tokens = static_cast<int32_t>(slot_mapping.size(0));
+  p.num_heads = static_cast<int32_t>(key.size(1));
+  p.head_size = static_cast<int32_t>(key.size(2));
+  p.dtype = dt;
+  p.kv_dtype = kv;
+}
+
+// csrc/cache.h:21-26 ; csrc/cache_kernels.cu:407-433
+void reshape_and_cache(at::Tensor& key, at::Tensor& value, at::Tensor& key_cache, at::Tensor& value_cache,
+                       at::Tensor& slot_mapping, const std::string& kv_cache_dtype, at::Tensor& k_scale,
+                       at::Tensor& v_scale) {
+  b200_cache_write_params_t p;
+  fill_cache_params(p, key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale, v_scale);
+  TORCH_CHECK(key_cache.dim() == 5 && value_cache.dim() == 4,
+              "key_cache must be [nb, nh, hs/x, bs, x] and value_cache [nb, nh, hs, bs]");
+  // the reference computes destinations from sizes (csrc/cache_kernels.cu:235-242)
+  TORCH_CHECK(key_cache.is_contiguous() && value_cache.is_contiguous(), "reshape_and_cache needs contiguous caches");
+  p.block_size = static_cast<int32_t>(key_cache.size(3));
+  p.x = static_cast<int32_t>(key_cache.size(4));
+  TORCH_CHECK(key_cache.size(1) == key.size(1) && key_cache.size(2) * key_cache.size(4) == key.size(2) &&
+                  value_cache.size(1) == key.size(1) && value_cache.size(2) == key.size(2) &&
+                  value_cache.size(3) == key_cache.size(3),
+              "cache shapes do not match key/value");
+  const at::cuda::OptionalCUDAGuard guard(device_of(key));
+  check_status(b200_reshape_and_cache(&p, at::cuda::getCurrentCUDAStream()), "reshape_and_cache");
+}
+
+// csrc/cache.h:28-35 ; csrc/cache_kernels.cu:450-488
+void reshape_and_cache_flash(at::Tensor& key, at::Tensor& value, at::Tensor& key_cache, at::Tensor& value_cache,
+                             at::Tensor& slot_mapping, const std::string& kv_cache_dtype, at::Tensor& k_scale,
+                             at::Tensor& v_scale) {
+  b200_cache_write_params_t p;
+  fill_cache_params(p, key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale, v_scale);
+  TORCH_CHECK(key_cache.dim() == 4 && value_cache.dim() == 4, "caches must be [nb, bs, nh, hs]");
+  TORCH_CHECK(key_cache.stride(0) == value_cache.stride(0) && key_cache.stride(1) == value_cache.stride(1) &&
+                  key_cache.stride(2) == value_cache.stride(2) && key_cache.stride(3) == 1 &&
+                  value_cache.stride(3) == 1,
+              "key_cache and value_cache must share strides with contiguous head dims");
+  TORCH_CHECK(key.stride(0) == value.stride(0), "key and value token strides differ");  // cache_kernels.cu:479
+  p.block_size = static_cast<int32_t>(key_cache.size(1));
+  p.block_stride = key_cache.stride(0);
+  p.page_stride = key_cache.stride(1);
+  p.head_stride = key_cache.stride(2);
+  TORCH_CHECK(key_cache.size(2) == key.size(1) && key_cache.size(3) == key.size(2), "cache shapes do not match key");
+  const at::cuda::OptionalCUDAGuard guard(device_of(key));
+  check_status(b200_reshape_and_cache_flash(&p, at::cuda::getCurrentCUDAStream()), "reshape_and_cache_flash");
+}
+
+// csrc/cache.h:37-40 ; csrc/cache_kernels.cu:543-614
+void convert_fp8(at::Tensor& dst_cache, at::Tensor& src_cache, const double scale, const std::string& kv_cache_dtype) {
+  TORCH_CHECK(src_cache.device() == dst_cache.device(), "src and dst must be on the same device");
+  TORCH_CHECK(src_cache.is_cuda(), "src must be on a GPU");  // cache_kernels.cu:568-570
+  TORCH_CHECK(dst_cache.numel() == src_cache.numel(), "src and dst sizes differ");
+  TORCH_CHECK(dst_cache.is_contiguous() && src_cache.is_contiguous(), "convert_fp8 needs contiguous tensors");
+  // "auto" is accepted by the reference's string switch (cache_kernels.cu:581) but
+  // lands in an assert(false) conversion; only fp8 / fp8_e4m3 have defined results.
+  TORCH_CHECK(b200_kv_dtype_from_string(kv_cache_dtype.c_str()) == B200_KV_FP8_E4M3,
+              "Unsupported data type: ", kv_cache_dtype);
+  const at::cuda::OptionalCUDAGuard guard(device_of(src_cache));
+  check_status(b200_convert_fp8(dst_cache.data_ptr(), src_cache.data_ptr(), src_cache.numel(),
+                                static_cast<float>(scale), to_dtype(dst_cache.scalar_type()),
+                                to_dtype(src_cache.scalar_type()), B200_KV_FP8_E4M3,
+                                at::cuda::getCurrentCUDAStream()),
+               "convert_fp8");
+}
+
+const char* kSchemaV1 =
+    "paged_attention_v1("
+    "    Tensor! out, Tensor query, Tensor key_cache,"
+    "    Tensor value_cache, int num_kv_heads, float scale,"
+    "    Tensor block_tables, Tensor seq_lens, int block_size,"
+    "    int max_seq_len, Tensor? alibi_slopes,"
+    "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale,"
+    "    int tp_rank, int blocksparse_local_blocks,"
+    "    int blocksparse_vert_stride, int blocksparse_block_size,"
+    "    int blocksparse_head_sliding_step) -> ()";
+const char* kSchemaV2 =
+    "paged_attention_v2("
+    "    Tensor! out, Tensor! exp_sums, Tensor! max_logits,"
+    "    Tensor! tmp_out, Tensor query, Tensor key_cache,"
+    "    Tensor value_cache, int num_kv_heads, float scale,"
+    "    Tensor block_tables, Tensor seq_lens, int block_size,"
+    "    int max_seq_len, Tensor? alibi_slopes,"
+    "    str kv_cache_dtype, Tensor k_scale, Tensor v_scale,"
+    "    int tp_rank, int blocksparse_local_blocks,"
+    "    int blocksparse_vert_stride, int blocksparse_block_size,"
+    "    int blocksparse_head_sliding_step) -> ()";
+const char* kSchemaReshape =
+    "reshape_and_cache(Tensor key, Tensor value,"
+    "                  Tensor! key_cache, Tensor! value_cache,"
+    "                  Tensor slot_mapping,"
+    "                  str kv_cache_dtype,"
+    "                  Tensor k_scale, Tensor v_scale) -> ()";
+const char* kSchemaReshapeFlash =
+    "reshape_and_cache_flash(Tensor key, Tensor value,"
+    "                        Tensor! key_cache,"
+    "                        Tensor! value_cache,"
+    "                        Tensor slot_mapping,"
+    "                        str kv_cache_dtype,"
+    "                        Tensor k_scale, Tensor v_scale) -> ()";
+const char* kSchemaConvert =
+    "convert_fp8(Tensor! dst_cache, Tensor src_cache, float scale, "
+    "str kv_cache_dtype) -> ()";
+
+bool op_exists(const char* qualified) {
+  return c10::Dispatcher::singleton().findSchema({qualified, ""}).has_value();
+}
+
+template <typename F>
+void register_op(std::vector<std::unique_ptr<torch::Library>>& keep, const char* ns, const char* name,
+                 const char* schema, F* fn) {
+  const std::string qualified = std::string(ns) + "::" + name;
+  if (!op_exists(qualified.c_str())) {
+    auto frag = std::make_unique<torch::Library>(torch::Library::FRAGMENT, ns, std::nullopt, __FILE__, __LINE__);
+    frag->def(schema);
+    keep.push_back(std::move(frag));
+  }
+  auto impl = std::make_unique<torch::Library>(torch::Library::IMPL, ns, c10::DispatchKey::CUDA, __FILE__, __LINE__);
+  impl->impl(name, fn);
+  keep.push_back(std::move(impl));
+}
+
+void register_all() {
+  static std::once_flag once;
+  std::call_once(once, [] {
+    static std::vector<std::unique_ptr<torch::Library>> keep;
+    register_op(keep, "_C", "paged_attention_v1", kSchemaV1, &paged_attention_v1);
+    register_op(keep, "_C", "paged_attention_v2", kSchemaV2, &paged_attention_v2);
+    register_op(keep, "_C_cache_ops", "reshape_and_cache", kSchemaReshape, &reshape_and_cache);
+    register_op(keep, "_C_cache_ops", "reshape_and_cache_flash", kSchemaReshapeFlash, &reshape_and_cache_flash);
+    register_op(keep, "_C_cache_ops", "convert_fp8", kSchemaConvert, &convert_fp8);
+  });
+}
+
+struct StaticInit {
+  StaticInit() { register_all(); }
+} g_static_init;
+
+}  // namespace
+
+// `import vllm_metax_b200._C` only has to load the library (csrc/core/registration.h:22-27).
+PyMODINIT_FUNC PyInit__C(void) {
+  static struct PyModuleDef module = {PyModuleDef_HEAD_INIT, "_C", nullptr, 0, nullptr};
+  register_all();
+  return PyModule_Create(&module);
+}
