@@ -162,4 +162,6 @@ def test_cache_write_then_attend(ops):
     out = torch.empty_like(q, device="cuda")
     ops.paged_attention_v1(out, q.cuda(), kc_d, vc_d, Hkv, D ** -0.5, bt.cuda(), lens.cuda(), B, L, None, "fp8",
                            ks.cuda(), vs.cuda())
-    torch.testing.assert_close(out.cpu().float(), ref.float(), atol=2e-3, rtol=2e-2)
+    # N(0,1) data through e4m3: the oracle rounds every dequantised element to bf16, the kernel folds the
+    # scales; the reference tolerates 1e-2 for fp8 (tests/kernels/attention/test_attention.py:343-345)
+    torch.testing.assert_close(out.cpu().float(), ref.float(), atol=5e-3, rtol=2e-2)

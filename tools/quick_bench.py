@@ -42,8 +42,10 @@ def main():
     ap.add_argument("--v2", action="store_true")
     ap.add_argument("--iters", type=int, default=30)
     ap.add_argument("--variant", type=int, default=0)
+    ap.add_argument("--check", action="store_true", help="compare against the generic FMA kernel")
     a = ap.parse_args()
     q, kc, vc, bt, lens, scale = make(a.S, a.H, a.Hkv, a.D, a.B, a.L, a.fp8)
+    os.environ["B200_DEBUG_NUM_BLOCKS"] = str(kc.shape[0])
     out = torch.empty_like(q)
     one = torch.ones(1, dtype=torch.float32, device="cuda")
     kvd = "fp8" if a.fp8 else "auto"
@@ -56,6 +58,15 @@ def main():
         fn = lambda: ops.paged_attention_v2(out, es, ml, tmp, q, kc, vc, a.Hkv, scale, bt, lens, a.B, a.L, None, kvd, one, one)
     else:
         fn = lambda: ops.paged_attention_v1(out, q, kc, vc, a.Hkv, scale, bt, lens, a.B, a.L, None, kvd, one, one)
+    fn()
+    torch.cuda.synchronize()
+    if a.check:
+        res = out.clone()
+        _native.set_attention_variant(1)
+        fn()
+        torch.cuda.synchronize()
+        print("check vs generic: max abs diff %.3e (ref max %.3e)" % ((res.float() - out.float()).abs().max().item(), out.float().abs().max().item()))
+        _native.set_attention_variant(a.variant)
     for _ in range(5):
         fn()
     torch.cuda.synchronize()

@@ -61,7 +61,8 @@ def build_abi(verbose: bool = False) -> Path:
         obj = BUILD / (src[:-3] + ".o")
         objs.append(obj)
         if _newer(obj, [CSRC / src] + headers):
-            jobs.append([nvcc, *NVCC_FLAGS, "-c", str(CSRC / src), "-o", str(obj)])
+            extra = ["-DB200_DEBUG"] if os.environ.get("B200_DEBUG") else []
+            jobs.append([nvcc, *NVCC_FLAGS, *extra, "-c", str(CSRC / src), "-o", str(obj)])
     if jobs:
         if verbose:
             print("[build] nvcc x%d" % len(jobs), file=sys.stderr)

@@ -7,10 +7,11 @@
 //  * persistent grid, one CTA per SM; work item = (partition, seq, kv head);
 //    the CTA serves ALL query heads of the kv head, so every KV byte is read
 //    from HBM once (the reference re-reads it once per query head);
-//  * one producer warp walks the block table and streams the contiguous
-//    K chunk [D/x][B][x] and V chunk [D][B] of each (block, kv head) into a
-//    shared-memory ring with 1-D TMA bulk copies (cp.async.bulk) completing on
-//    mbarriers; the ring keeps ~100-190 KiB per SM in flight;
+//  * four producer warps (one issuing lane each, tiles dealt round-robin) walk
+//    the block table and stream the contiguous K chunk [D/x][B][x] and V chunk
+//    [D][B] of each (block, kv head) into a shared-memory ring with 1-D TMA
+//    bulk copies (cp.async.bulk) completing on mbarriers; the ring keeps
+//    128-192 KiB per SM in flight;
 //  * 8 consumer warps each take whole 32-token tiles out of the ring and run
 //    S^T = K.Q^T and O^T += V^T.P^T on mma.sync m16n8k16 with the roles
 //    swapped so that the 8-wide N dimension is the GQA group (M = tokens /
@@ -25,6 +26,8 @@
 //  * fp8: e4m3 bytes are expanded to f16 in registers (exact), the MMA runs in
 //    f16, k_scale is folded into the logit scale and v_scale into the output.
 #include <float.h>
+#include <stdio.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -34,7 +37,8 @@ namespace {
 constexpr int kD = 128;             // head size served by this kernel
 constexpr int kTileTokens = 32;     // tokens per ring stage
 constexpr int kConsumerWarps = 8;
-constexpr int kThreads = (kConsumerWarps + 1) * kWarpSize;
+constexpr int kProducerWarps = 4;
+constexpr int kThreads = (kConsumerWarps + kProducerWarps) * kWarpSize;
 constexpr int kMergeStride = kD + 4;  // fp32 words per (warp, head) row
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -55,6 +59,7 @@ struct StreamParams {
   int64_t kv_head_stride;   // bytes
   int S, H, Hkv, G, max_blocks, nstages, total_items;
   float scale;
+  int debug_num_blocks;  // B200_DEBUG builds only: bound for block-table entries (0 = unchecked)
 };
 
 // ---- PTX wrappers ------------------------------------------------------------
@@ -71,6 +76,31 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+#ifdef B200_DEBUG
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// debug build: a wait that gives up after ~2 s, reports who was waiting for what, and traps
+__device__ __noinline__ void mbar_wait_dbg(uint32_t bar, uint32_t parity, int tag, int a, int b) {
+  const long long t0 = clock64();
+  while (!mbar_try(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) {
+      printf("[b200 debug] mbarrier timeout: cta %d warp %d lane %d tag %d a %d b %d bar 0x%x parity %u\n",
+             (int)blockIdx.x, (int)(threadIdx.x >> 5), (int)(threadIdx.x & 31), tag, a, b, bar, parity);
+      __trap();
+    }
+  }
+}
+#define MBAR_WAIT(bar, parity, tag, a, b) mbar_wait_dbg(bar, parity, tag, a, b)
+#else
+#define MBAR_WAIT(bar, parity, tag, a, b) mbar_wait(bar, parity)
+#endif
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n"
@@ -197,45 +227,68 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
   }
   __syncthreads();
 
-  if (warp == kConsumerWarps) {
-    // ===================== producer warp =========================================
-    int stage = 0;
-    uint32_t phase = 0;
+  if (warp >= kConsumerWarps) {
+    // ===================== producer warps ========================================
+    // Producer warp pw owns the tiles gt == pw (mod kProducerWarps) of the CTA's tile stream; one
+    // lane walks the block table and issues the bulk copies (a single issuing thread costs ~1000
+    // cycles per tile, so four of them share the stream).
+    if (lane != 0) return;
+    const int pw = warp - kConsumerWarps;
+    uint32_t g_next = (uint32_t)pw;   // next tile of the stream this warp issues
+    int stage = pw;                   // g_next % nst (nst >= kProducerWarps)
+    uint32_t phase = 0;               // (g_next / nst) & 1
+    uint32_t tile_base = 0;
     for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
       Item it;
       if (!decode_item(p, item, it)) continue;
       const int nblk = (it.t1 - it.t0 + B - 1) / B;
+      const uint32_t ntiles = (uint32_t)((it.t1 - it.t0 + kTileTokens - 1) / kTileTokens);
       const int32_t* bt = p.bt + (int64_t)it.s * p.max_blocks + it.t0 / B;
       const uint8_t* kbase = p.kc + (int64_t)it.kvh * p.kv_head_stride;
       const uint8_t* vbase = p.vc + (int64_t)it.kvh * p.kv_head_stride;
-      int my_next = (lane < nblk) ? __ldg(bt + lane) : 0;
-      for (int bb = 0; bb < nblk; bb += 32) {
-        const int my = my_next;
-        if (bb + 32 < nblk) my_next = (bb + 32 + lane < nblk) ? __ldg(bt + bb + 32 + lane) : 0;
-        const int nb = min(32, nblk - bb);
-        for (int j = 0; j < nb; j += C::kBlocksPerTile) {
-          const int id0 = __shfl_sync(0xffffffffu, my, j);
-          const int id1 = __shfl_sync(0xffffffffu, my, (j + 1) & 31);
-          const int nvalid = min(C::kBlocksPerTile, nb - j);
-          if (lane == 0) {
-            mbar_wait(empty_u32 + 8u * stage, phase ^ 1u);
-            const uint32_t fb = full_u32 + 8u * stage;
-            mbar_expect_tx(fb, (uint32_t)(nvalid * 2 * C::kBlkBytes));
-            const uint32_t dst = ring_u32 + (uint32_t)stage * C::kStageBytes;
-            bulk_g2s(dst, kbase + (int64_t)id0 * p.kv_block_stride, C::kBlkBytes, fb);
-            bulk_g2s(dst + C::kVOffset, vbase + (int64_t)id0 * p.kv_block_stride, C::kBlkBytes, fb);
-            if (C::kBlocksPerTile == 2 && nvalid == 2) {
-              bulk_g2s(dst + C::kBlkBytes, kbase + (int64_t)id1 * p.kv_block_stride, C::kBlkBytes, fb);
-              bulk_g2s(dst + C::kVOffset + C::kBlkBytes, vbase + (int64_t)id1 * p.kv_block_stride,
-                       C::kBlkBytes, fb);
-            }
-          }
-          if (++stage == nst) {
-            stage = 0;
-            phase ^= 1u;
-          }
+      const uint32_t tile_end = tile_base + ntiles;
+      // block ids of the next tile are fetched one step ahead
+      int nid0 = 0, nid1 = 0;
+      if (g_next < tile_end) {
+        const int b0 = (int)(g_next - tile_base) * C::kBlocksPerTile;
+        nid0 = __ldg(bt + b0);
+        if (C::kBlocksPerTile == 2 && b0 + 1 < nblk) nid1 = __ldg(bt + b0 + 1);
+      }
+      while (g_next < tile_end) {
+        const int b0 = (int)(g_next - tile_base) * C::kBlocksPerTile;
+        const int id0 = nid0, id1 = nid1;
+        const int nvalid = min(C::kBlocksPerTile, nblk - b0);
+        const int bn = b0 + kProducerWarps * C::kBlocksPerTile;
+        if (bn < nblk) {
+          nid0 = __ldg(bt + bn);
+          if (C::kBlocksPerTile == 2 && bn + 1 < nblk) nid1 = __ldg(bt + bn + 1);
+        }
+#ifdef B200_DEBUG
+        if (p.debug_num_blocks > 0 && ((unsigned)id0 >= (unsigned)p.debug_num_blocks ||
+                                       (nvalid == 2 && (unsigned)id1 >= (unsigned)p.debug_num_blocks))) {
+          printf("[b200 debug] bad block id: cta %d item %d s %d part %d b0 %d id0 %d id1 %d nblk %d\n",
+                 (int)blockIdx.x, item, it.s, it.part, b0, id0, id1, nblk);
+          __trap();
+        }
+#endif
+        MBAR_WAIT(empty_u32 + 8u * stage, phase ^ 1u, 1, item, stage);
+        const uint32_t fb = full_u32 + 8u * stage;
+        mbar_expect_tx(fb, (uint32_t)(nvalid * 2 * C::kBlkBytes));
+        const uint32_t dst = ring_u32 + (uint32_t)stage * C::kStageBytes;
+        bulk_g2s(dst, kbase + (int64_t)id0 * p.kv_block_stride, C::kBlkBytes, fb);
+        bulk_g2s(dst + C::kVOffset, vbase + (int64_t)id0 * p.kv_block_stride, C::kBlkBytes, fb);
+        if (C::kBlocksPerTile == 2 && nvalid == 2) {
+          bulk_g2s(dst + C::kBlkBytes, kbase + (int64_t)id1 * p.kv_block_stride, C::kBlkBytes, fb);
+          bulk_g2s(dst + C::kVOffset + C::kBlkBytes, vbase + (int64_t)id1 * p.kv_block_stride, C::kBlkBytes, fb);
+        }
+        g_next += kProducerWarps;
+        stage += kProducerWarps;
+        if (stage >= nst) {
+          stage -= nst;
+          phase ^= 1u;
         }
       }
+      tile_base = tile_end;
     }
     return;
   }
@@ -344,11 +397,15 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
         for (int e = 0; e < 4; ++e) oacc[nt][i][e] = 0.f;
     }
 
-    for (int ti = warp; ti < ntiles; ti += kConsumerWarps) {
+    // Tile gt of the CTA's tile stream goes to warp gt % 8 and ring stage gt % nst; nst is a multiple
+    // of 8, so every use of a stage is consumed by the same warp, in order.  (A warp that skipped a
+    // phase of a stage could pass a parity wait one round early: mbarrier parity only tells odd from
+    // even.)
+    for (int ti = (int)((warp - tile_base) & (kConsumerWarps - 1)); ti < ntiles; ti += kConsumerWarps) {
       const uint32_t gt = tile_base + (uint32_t)ti;
       const uint32_t stage = gt % (uint32_t)nst;
       const uint32_t parity = (gt / (uint32_t)nst) & 1u;
-      mbar_wait(full_u32 + 8u * stage, parity);
+      MBAR_WAIT(full_u32 + 8u * stage, parity, 2, item, (int)gt);
       const uint32_t sb = ring_u32 + stage * C::kStageBytes;
       const int tok0 = it.t0 + ti * kTileTokens;   // first token of the tile
       const int nvalid = min(kTileTokens, it.t1 - tok0);
@@ -576,10 +633,13 @@ template <int B, bool FP8, int NT>
 int launch_stream_t(StreamParams& sp, cudaStream_t s) {
   using C = Cfg<B, FP8>;
   // deepest ring that fits (capped: beyond ~190 KiB in flight nothing is gained)
-  int nst = 2;
-  while (nst < 24 && stream_smem_bytes<B, FP8, NT>(nst + 1) <= kMaxSmem &&
-         (size_t)(nst + 1) * C::kStageBytes <= 192 * 1024)
-    ++nst;
+  // (a multiple of the consumer-warp count: see the tile -> warp mapping in the kernel)
+  int nst = kConsumerWarps;
+  while (stream_smem_bytes<B, FP8, NT>(nst + kConsumerWarps) <= kMaxSmem &&
+         (size_t)(nst + kConsumerWarps) * C::kStageBytes <= 192 * 1024)
+    nst += kConsumerWarps;
+  if (const char* e = getenv("B200_STREAM_NSTAGES"))
+    nst = max(kConsumerWarps, min(nst, atoi(e) / kConsumerWarps * kConsumerWarps));
   sp.nstages = nst;
   const size_t smem = stream_smem_bytes<B, FP8, NT>(nst);
   auto kern = paged_attention_stream_kernel<B, FP8, NT>;
@@ -640,6 +700,8 @@ int launch_attention_stream(const b200_paged_attn_params_t& p, const SplitOut& s
   sp.nstages = 0;
   sp.total_items = so.num_partitions * p.num_seqs * p.num_kv_heads;
   sp.scale = p.scale;
+  sp.debug_num_blocks = 0;
+  if (const char* e = getenv("B200_DEBUG_NUM_BLOCKS")) sp.debug_num_blocks = atoi(e);
   if (sp.total_items == 0) return B200_OK;
   const int nt = (sp.G + 7) / 8;
 #define GO(B_, FP8_)                                                     \
