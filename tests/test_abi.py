@@ -1,0 +1,172 @@
+"""C-ABI boundary checks that need no GPU: the library loads, exports every symbol the header declares,
+the ctypes mirrors match the C struct layouts, host-side validation returns the documented errors, the
+torch shim registers the reference's schemas, and there is no CPU fallback."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "b200_paged_attn.h")
+
+
+@pytest.fixture(scope="module")
+def native():
+    from vllm_metax_b200 import build
+
+    build.build_all()
+    from vllm_metax_b200 import _native
+
+    _native.load()
+    return _native
+
+
+def _declared_functions():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(b200_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_every_declared_symbol_is_exported(native):
+    names = _declared_functions()
+    assert sorted(native.EXPORTED_SYMBOLS) == names
+    lib = C.CDLL(os.fspath(native.LIB_PATH))
+    for n in names:
+        assert hasattr(lib, n), n
+    assert native.load().b200_abi_version() == 1
+
+
+def test_ctypes_structs_match_header_layout(native, tmp_path):
+    def fields(struct):
+        return [f[0] for f in struct._fields_]
+
+    prog = ['#include <stdio.h>', '#include <stddef.h>', '#include "b200_paged_attn.h"', "int main(void){"]
+    for cname, st in (("b200_paged_attn_params_t", native.PagedAttnParams),
+                      ("b200_cache_write_params_t", native.CacheWriteParams)):
+        prog.append('printf("%%zu\\n", sizeof(%s));' % cname)
+        for f in fields(st):
+            prog.append('printf("%%zu\\n", offsetof(%s, %s));' % (cname, f))
+    prog.append("return 0;}")
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(prog))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    vals = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    it = iter(vals)
+    for st in (native.PagedAttnParams, native.CacheWriteParams):
+        assert next(it) == C.sizeof(st)
+        for f in fields(st):
+            assert next(it) == getattr(st, f).offset, f
+
+
+def test_kv_dtype_strings(native):
+    lib = native.load()
+    assert lib.b200_kv_dtype_from_string(b"auto") == native.KV_AUTO
+    assert lib.b200_kv_dtype_from_string(b"fp8") == native.KV_FP8_E4M3
+    assert lib.b200_kv_dtype_from_string(b"fp8_e4m3") == native.KV_FP8_E4M3
+    assert lib.b200_kv_dtype_from_string(b"fp8_e5m2") == -1  # listed by the reference enum, implemented nowhere
+    assert lib.b200_kv_dtype_from_string(b"int8") == -1
+
+
+def _params(native, **kw):
+    p = native.PagedAttnParams()
+    p.num_seqs, p.num_heads, p.num_kv_heads, p.head_size, p.block_size = 4, 32, 8, 128, 16
+    p.max_seq_len, p.max_num_blocks_per_seq = 4096, 256
+    p.dtype, p.kv_dtype = native.DTYPE_BF16, native.KV_AUTO
+    p.kv_block_stride, p.kv_head_stride, p.q_stride = 8 * 128 * 16, 128 * 16, 32 * 128
+    for k, v in kw.items():
+        setattr(p, k, v)
+    return p
+
+
+@pytest.mark.parametrize("kw,code,msg", [
+    (dict(head_size=48), 2, "Unsupported head size: 48"),
+    (dict(block_size=64), 2, "Unsupported block size: 64"),
+    (dict(kv_dtype=7), 2, "Unsupported data type of kv cache"),
+    (dict(dtype=9), 2, "Unsupported data type"),
+    (dict(num_heads=30), 1, "not a multiple"),
+    (dict(blocksparse_vert_stride=8), 2, "block-sparse"),
+])
+def test_validation_errors_without_a_device(native, kw, code, msg):
+    """Argument errors are reported before any CUDA call (reference: TORCH_CHECK(false, "Unsupported head
+    size: ...") csrc/attention/paged_attention_v1.cu:121-123,155-157)."""
+    p = _params(native, **kw)
+    rc = native.load().b200_paged_attention_v1(C.byref(p), None)
+    assert rc == code
+    assert msg in native.load().b200_last_error().decode()
+
+
+def test_null_pointers_are_rejected(native):
+    p = _params(native)
+    assert native.load().b200_paged_attention_v1(C.byref(p), None) == native.ERR_INVALID_ARGUMENT
+    assert "NULL" in native.load().b200_last_error().decode()
+    cp = native.CacheWriteParams()
+    cp.num_tokens, cp.num_heads, cp.head_size, cp.block_size, cp.x = 4, 8, 128, 16, 8
+    assert native.load().b200_reshape_and_cache(C.byref(cp), None) == native.ERR_INVALID_ARGUMENT
+
+
+def test_empty_batches_are_noops(native):
+    p = _params(native, num_seqs=0)
+    assert native.load().b200_paged_attention_v1(C.byref(p), None) == 0
+    cp = native.CacheWriteParams()
+    cp.num_tokens, cp.num_heads, cp.head_size, cp.block_size, cp.x = 0, 8, 128, 16, 8
+    assert native.load().b200_reshape_and_cache(C.byref(cp), None) == 0
+    assert native.load().b200_reshape_and_cache_flash(C.byref(cp), None) == 0
+
+
+def test_workspace_sizing_is_host_only_and_monotone(native):
+    small = native.workspace_bytes(_params(native, max_seq_len=256, num_seqs=64))
+    big = native.workspace_bytes(_params(native, max_seq_len=131072, num_seqs=8))
+    assert small >= 0 and big > 0
+    # layout: (D + 2) floats per (seq, head, partition)
+    assert big % ((128 + 2) * 4) == 0
+
+
+def test_variant_hook(native):
+    native.set_attention_variant(native.VARIANT_GENERIC)
+    native.set_attention_variant(native.VARIANT_AUTO)
+    with pytest.raises(native.B200Error):
+        native.set_attention_variant(17)
+
+
+def test_torch_shim_registers_reference_schemas_and_has_no_cpu_fallback(native):
+    import vllm_metax_b200
+
+    vllm_metax_b200.import_kernels()
+    s = str(torch.ops._C.paged_attention_v1.default._schema)
+    assert s.startswith("_C::paged_attention_v1(Tensor($0! -> ) out, Tensor query, Tensor key_cache, Tensor value_cache, "
+                        "int num_kv_heads, float scale, Tensor block_tables, Tensor seq_lens, int block_size, "
+                        "int max_seq_len, Tensor? alibi_slopes, str kv_cache_dtype, Tensor k_scale, Tensor v_scale, "
+                        "int tp_rank, int blocksparse_local_blocks, int blocksparse_vert_stride, "
+                        "int blocksparse_block_size, int blocksparse_head_sliding_step) -> ()")
+    s2 = str(torch.ops._C.paged_attention_v2.default._schema)
+    assert "Tensor($0! -> ) out, Tensor($1! -> ) exp_sums, Tensor($2! -> ) max_logits, Tensor($3! -> ) tmp_out" in s2
+    for name in ("reshape_and_cache", "reshape_and_cache_flash"):
+        s3 = str(getattr(torch.ops._C_cache_ops, name).default._schema)
+        assert "Tensor key, Tensor value, Tensor($0! -> ) key_cache, Tensor($1! -> ) value_cache, Tensor slot_mapping, " \
+               "str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()" in s3
+    assert "convert_fp8(Tensor($0! -> ) dst_cache, Tensor src_cache, float scale, str kv_cache_dtype) -> ()" in str(
+        torch.ops._C_cache_ops.convert_fp8.default._schema)
+    # CPU tensors: the dispatcher must refuse (only the CUDA key is implemented, as in the reference)
+    q = torch.zeros(1, 8, 128, dtype=torch.bfloat16)
+    kc = torch.zeros(4, 2, 16, 16, 8, dtype=torch.bfloat16)
+    vc = torch.zeros(4, 2, 128, 16, dtype=torch.bfloat16)
+    one = torch.ones(1)
+    with pytest.raises((NotImplementedError, RuntimeError)):
+        torch.ops._C.paged_attention_v1(torch.empty_like(q), q, kc, vc, 2, 0.1, torch.zeros(1, 4, dtype=torch.int32),
+                                        torch.ones(1, dtype=torch.int32), 16, 16, None, "auto", one, one, 0, 0, 0, 64, 0)
+
+
+def test_product_code_never_touches_the_oracle():
+    """No import, dlopen or path of oracle/ anywhere in the product package (comments may mention the word)."""
+    pkg = os.path.join(ROOT, "vllm_metax_b200")
+    pat = re.compile(r"(^\s*(from|import)\s+oracle\b|liboracle|oracle/|oracle\.(torch_oracle|c_oracle|e4m3_np))", re.M)
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")) and f != "build.py":
+                txt = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert not pat.search(txt), os.path.join(dirpath, f)

@@ -29,7 +29,7 @@ def _scales(key, value):
 
 @pytest.mark.parametrize("head_size", [64, 80, 128, 256])
 @pytest.mark.parametrize("block_size", [8, 16, 32])
-@pytest.mark.parametrize("num_blocks", [1024, 10000])
+@pytest.mark.parametrize("num_blocks", [64, 1531])  # reference: 1024 / 10000
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32, torch.float16])
 @pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8"])
 def test_reshape_and_cache(ops, head_size, block_size, num_blocks, dtype, kv_cache_dtype):
@@ -59,7 +59,7 @@ def test_reshape_and_cache(ops, head_size, block_size, num_blocks, dtype, kv_cac
 
 @pytest.mark.parametrize("head_size", [64, 80, 128, 256])
 @pytest.mark.parametrize("block_size", [8, 16, 32])
-@pytest.mark.parametrize("num_blocks", [512, 5000])
+@pytest.mark.parametrize("num_blocks", [32, 777])  # reference: 512 / 5000
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8"])
 @pytest.mark.parametrize("layout", ["NHD", "HND"])

@@ -14,7 +14,7 @@ from oracle import torch_oracle as orc
 pytestmark = pytest.mark.gpu
 
 PARTITION_SIZE = 512
-NUM_BLOCKS = 4321  # as in the reference test
+NUM_BLOCKS = 613  # the reference uses 4321; the table entries stay random and non-unique
 ATOL_AUTO = 1e-3   # reference: tests/kernels/attention/test_attention.py:342
 ATOL_BAR = 2e-3    # BASELINE.json north_star
 
