@@ -220,17 +220,20 @@ def run_ours(args):
     clocks = sampler.summary(clock_note)
 
     # ---- end to end through the public op wrappers, host inputs ------------------------------------------
-    host = {k: w[k].cpu().pin_memory() for k in ("query", "key", "value", "slot_mapping", "block_tables", "seq_lens")}
+    from vllm_metax_b200.attention import PinnedDecodeInputs
+
+    names = ("query", "key", "value", "slot_mapping", "block_tables", "seq_lens")
+    staged = PinnedDecodeInputs({k: (tuple(w[k].shape), w[k].dtype) for k in names}, dev)  # one pinned buffer
+    for k in names:
+        staged.host(k).copy_(w[k].cpu())
     host_out = torch.empty(w["out"].shape, dtype=w["out"].dtype).pin_memory()
-    dbuf = {k: torch.empty_like(w[k]) for k in host}
-    h2d = sum(v.numel() * v.element_size() for v in host.values())
+    h2d = staged.nbytes
     d2h = host_out.numel() * host_out.element_size()
 
     def e2e_step():
-        for k in host:
-            dbuf[k].copy_(host[k], non_blocking=True)
-        cache_write(dbuf["key"], dbuf["value"], dbuf["slot_mapping"])
-        attention(dbuf["query"], dbuf["block_tables"], dbuf["seq_lens"], w["out"])
+        staged.upload()  # host -> device: this step's q, k, v, slot_mapping, block_tables, seq_lens
+        cache_write(staged.dev("key"), staged.dev("value"), staged.dev("slot_mapping"))
+        attention(staged.dev("query"), staged.dev("block_tables"), staged.dev("seq_lens"), w["out"])
         host_out.copy_(w["out"], non_blocking=True)
         torch.cuda.current_stream().synchronize()  # the caller reads the result
 

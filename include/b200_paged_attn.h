@@ -94,8 +94,10 @@ typedef enum b200_attn_variant {
  *   tmp_out              [num_seqs, num_heads, P, head_size] dtype
  * workspace: v1 needs scratch for its split-KV partials (the reference op
  *   has none because its v1 never splits).  Size it with
- *   b200_paged_attention_workspace_bytes(); it may be reused across calls on
- *   the same stream and needs no initialisation.  v2 needs none (NULL, 0).
+ *   b200_paged_attention_workspace_bytes().  It must be ZERO-FILLED ONCE before
+ *   its first use (it holds arrival counters that every completed launch
+ *   leaves at zero again) and may then be reused by calls on the same stream;
+ *   calls that may overlap need separate workspaces.  v2 needs none (NULL, 0).
  */
 typedef struct b200_paged_attn_params {
   void* out;

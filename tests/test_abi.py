@@ -122,8 +122,8 @@ def test_workspace_sizing_is_host_only_and_monotone(native):
     small = native.workspace_bytes(_params(native, max_seq_len=256, num_seqs=64))
     big = native.workspace_bytes(_params(native, max_seq_len=131072, num_seqs=8))
     assert small >= 0 and big > 0
-    # layout: (D + 2) floats per (seq, head, partition)
-    assert big % ((128 + 2) * 4) == 0
+    # layout: (D + 2) floats per (seq, head, partition) + one int per (seq, kv head)
+    assert (big - 8 * 8 * 4) % ((128 + 2) * 4) == 0
 
 
 def test_variant_hook(native):

@@ -232,7 +232,7 @@ def test_via_c_abi_matches_torch_op(ops):
     one = torch.ones(1, dtype=torch.float32, device="cuda")
     p = _native.attn_params(out, t["query"], t["key_cache"], t["value_cache"], 8, d["scale"], t["block_tables"],
                             t["seq_lens"], 16, d["max_seq_len"], None, "auto", one, one)
-    ws = torch.empty(max(16, _native.workspace_bytes(p)), dtype=torch.uint8, device="cuda")
+    ws = torch.zeros(max(16, _native.workspace_bytes(p)), dtype=torch.uint8, device="cuda")  # zero-filled once
     p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
     _native.paged_attention_v1(p, torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()

@@ -1,0 +1,2 @@
+"""Host-side callers of the decode hot path (the layer the reference's attention backends sit in)."""
+from .paged_attn import PagedAttention, PinnedDecodeInputs, shard_kv_heads  # noqa: F401

@@ -146,7 +146,9 @@ int pick_variant(const b200_paged_attn_params_t& p) {
 uint64_t split_bytes(const b200_paged_attn_params_t& p, int chunk) {
   const int64_t P = (p.max_seq_len + chunk - 1) / chunk;
   if (P <= 1) return 0;
-  return (uint64_t)p.num_seqs * p.num_heads * P * (p.head_size + 2) * sizeof(float);
+  // partial outputs, maxima, sums + one arrival counter per (seq, kv head)
+  return (uint64_t)p.num_seqs * p.num_heads * P * (p.head_size + 2) * sizeof(float) +
+         (uint64_t)p.num_seqs * p.num_kv_heads * sizeof(int);
 }
 
 }  // namespace
@@ -175,6 +177,7 @@ extern "C" int b200_paged_attention_v1(const b200_paged_attn_params_t* p, void* 
   so.normalized = 0;
   so.m = so.l = nullptr;
   so.o = nullptr;
+  so.counters = nullptr;
   if (so.num_partitions > 1) {
     const uint64_t need = split_bytes(*p, so.chunk);
     B200_REQUIRE(p->workspace != nullptr && p->workspace_bytes >= need, B200_ERR_WORKSPACE,
@@ -186,11 +189,13 @@ extern "C" int b200_paged_attention_v1(const b200_paged_attn_params_t* p, void* 
     so.o = p->workspace;
     so.m = static_cast<float*>(p->workspace) + n * p->head_size;
     so.l = so.m + n;
+    // the streaming kernel merges the partitions itself (arrival counters, zero on entry and exit)
+    if (stream_v) so.counters = reinterpret_cast<int*>(so.l + n);
   }
   rc = stream_v ? launch_attention_stream(*p, so, s) : launch_attention_generic(*p, so, s);
   if (rc != B200_OK) return rc;
   g_last_variant = variant;
-  return launch_split_reduce(*p, so, s);
+  return so.counters != nullptr ? B200_OK : launch_split_reduce(*p, so, s);
 }
 
 extern "C" int b200_paged_attention_v2(const b200_paged_attn_params_t* p, void* stream) {
@@ -209,6 +214,7 @@ extern "C" int b200_paged_attention_v2(const b200_paged_attn_params_t* p, void* 
   so.m = p->max_logits;
   so.l = p->exp_sums;
   so.o = p->tmp_out;
+  so.counters = nullptr;
   rc = variant == B200_VARIANT_STREAM_MMA ? launch_attention_stream(*p, so, s) : launch_attention_generic(*p, so, s);
   if (rc != B200_OK) return rc;
   g_last_variant = variant;

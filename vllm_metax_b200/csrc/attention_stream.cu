@@ -212,6 +212,7 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
   float* merge_m = merge_o + kConsumerWarps * NH * kMergeStride;
   float* merge_l = merge_m + kConsumerWarps * NH;
   uint64_t* bars = reinterpret_cast<uint64_t*>(merge_l + kConsumerWarps * NH);
+  int* merge_flag = reinterpret_cast<int*>(bars + 2 * nst);
   const uint32_t ring_u32 = smem_u32(ring);
   const uint32_t full_u32 = smem_u32(bars);
   const uint32_t empty_u32 = full_u32 + 8u * nst;
@@ -616,6 +617,39 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
         }
       }
     }
+    if (p.so.counters != nullptr && it.L > p.so.chunk) {
+      // ---- fused split-KV reduce: the CTA that delivers the last partition of (seq, kv head) merges them
+      // (same arithmetic as split_reduce_kernel / reference attention_kernels.cuh:594-657) --------------
+      __threadfence();       // this thread's partials are visible device-wide
+      consumer_bar_sync();   // ... and so are everyone's
+      if (tid == 0) {
+        const int nparts = (it.L + p.so.chunk - 1) / p.so.chunk;
+        int* cnt = p.so.counters + it.s * p.Hkv + it.kvh;
+        const int old = atomicAdd(cnt, 1);
+        const int last = old == nparts - 1;
+        if (last) *cnt = 0;  // leave the counters zeroed for the next launch
+        *merge_flag = last;
+      }
+      consumer_bar_sync();
+      if (*merge_flag) {
+        __threadfence();
+        const int nparts = (it.L + p.so.chunk - 1) / p.so.chunk;
+        const int d = tid & (kD - 1);
+        for (int h = tid >> 7; h < p.G; h += (kConsumerWarps * kWarpSize) >> 7) {
+          const int head = it.kvh * p.G + h;
+          const int64_t base = ((int64_t)it.s * p.H + head) * p.so.num_partitions;
+          float M = -INFINITY;
+          for (int j = 0; j < nparts; ++j) M = fmaxf(M, __ldcg(p.so.m + base + j));
+          float lsum = 0.f, o = 0.f;
+          for (int j = 0; j < nparts; ++j) {
+            const float wgt = __expf(__ldcg(p.so.m + base + j) - M);
+            lsum = fmaf(__ldcg(p.so.l + base + j), wgt, lsum);
+            o = fmaf(__ldcg(reinterpret_cast<const float*>(p.so.o) + (base + j) * kD + d), wgt, o);
+          }
+          p.out[((int64_t)it.s * p.H + head) * kD + d] = __float2bfloat16_rn(o * __fdividef(1.f, lsum + 1e-6f));
+        }
+      }
+    }
     consumer_bar_sync();  // merge buffers are free again
   }
 }
@@ -624,7 +658,7 @@ template <int B, bool FP8, int NT>
 size_t stream_smem_bytes(int nstages) {
   using C = Cfg<B, FP8>;
   return 128 + (size_t)nstages * C::kStageBytes +
-         (size_t)kConsumerWarps * 8 * NT * (kMergeStride + 2) * sizeof(float) + (size_t)nstages * 16;
+         (size_t)kConsumerWarps * 8 * NT * (kMergeStride + 2) * sizeof(float) + (size_t)nstages * 16 + 16;
 }
 
 constexpr size_t kMaxSmem = 227 * 1024;

@@ -53,7 +53,9 @@ __device__ __forceinline__ void store_one(void* dst_base, int64_t idx, T v, floa
 // (requires x % kElems == 0 and 16-byte aligned source rows).
 template <typename T, bool FP8, bool VECK>
 __global__ void reshape_and_cache_kernel(b200_cache_write_params_t p) {
+  // one CTA per (token, head): a decode step has few tokens, so the heads supply the parallelism
   const int64_t token = blockIdx.x;
+  const int h = blockIdx.y;
   const int64_t slot = p.slot_mapping[token];
   if (slot < 0) return;  // padding token (csrc/cache_kernels.cu:217-220)
   const int64_t blk = slot / p.block_size;
@@ -61,34 +63,28 @@ __global__ void reshape_and_cache_kernel(b200_cache_write_params_t p) {
   const int H = p.num_heads, D = p.head_size, B = p.block_size, x = p.x;
   const float ks = FP8 ? *p.k_scale : 0.f;
   const float vs = FP8 ? *p.v_scale : 0.f;
-  const T* ksrc = reinterpret_cast<const T*>(p.key) + token * p.key_stride;
-  const T* vsrc = reinterpret_cast<const T*>(p.value) + token * p.value_stride;
-  const int n = H * D;
+  const T* ksrc = reinterpret_cast<const T*>(p.key) + token * p.key_stride + (int64_t)h * D;
+  const T* vsrc = reinterpret_cast<const T*>(p.value) + token * p.value_stride + (int64_t)h * D;
   constexpr int N = VecOf<T>::kElems;
   constexpr int CB = FP8 ? 1 : (int)sizeof(T);  // cache element bytes
+  const int64_t kbase = (blk * H + h) * (int64_t)(D / x) * B * x + off * x;  // + (d/x)*B*x + d%x
+  const int64_t vbase = (blk * H + h) * (int64_t)D * B + off;               // + d*B
 
   if constexpr (VECK) {
     // one 16-byte source vector = N consecutive dims inside one x-unit
-    for (int v = threadIdx.x; v < n / N; v += blockDim.x) {
-      const int i = v * N;
-      const int h = i / D, d = i % D;
-      const int64_t dst = (((blk * H + h) * (D / x) + d / x) * B + off) * x + d % x;
-      Vec16 val = *reinterpret_cast<const Vec16*>(ksrc + i);
+    for (int v = threadIdx.x; v < D / N; v += blockDim.x) {
+      const int d = v * N;
+      const int64_t dst = kbase + (int64_t)(d / x) * B * x + d % x;
+      Vec16 val = *reinterpret_cast<const Vec16*>(ksrc + d);
       store_vec<T, FP8>(reinterpret_cast<uint8_t*>(p.key_cache) + dst * CB, val, ks);
     }
   } else {
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      const int h = i / D, d = i % D;
-      const int64_t dst = (((blk * H + h) * (D / x) + d / x) * B + off) * x + d % x;
-      store_one<T, FP8>(p.key_cache, dst, ksrc[i], ks);
-    }
+    for (int d = threadIdx.x; d < D; d += blockDim.x)
+      store_one<T, FP8>(p.key_cache, kbase + (int64_t)(d / x) * B * x + d % x, ksrc[d], ks);
   }
   // V: destination elements of one token are B apart -> scalar scatter.
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    const int h = i / D, d = i % D;
-    const int64_t dst = ((blk * H + h) * D + d) * B + off;
-    store_one<T, FP8>(p.value_cache, dst, vsrc[i], vs);
-  }
+  for (int d = threadIdx.x; d < D; d += blockDim.x)
+    store_one<T, FP8>(p.value_cache, vbase + (int64_t)d * B, vsrc[d], vs);
 }
 
 // ---- reshape_and_cache_flash -------------------------------------------------
@@ -160,10 +156,10 @@ int launch_reshape_and_cache(const b200_cache_write_params_t& p, cudaStream_t s)
   // vector path: x-units are whole vectors, source rows and the destination
   // units are vector aligned.
   const int cache_bytes = fp8 ? 1 : (int)sizeof(T);
-  const bool veck = (p.x % N == 0) && (p.head_size % p.x == 0) && (p.key_stride % N == 0) &&
+  const bool veck = (p.x % N == 0) && (p.head_size % p.x == 0) && (p.key_stride % N == 0) && (p.head_size % N == 0) &&
                     aligned(p.key, 16) && aligned(p.key_cache, (size_t)N * cache_bytes);
-  const int threads = veck ? max(32, min(512, (n / N + 31) / 32 * 32)) : max(32, min(512, n));
-  dim3 grid(p.num_tokens), block(threads);
+  const int threads = max(32, min(256, (p.head_size + 31) / 32 * 32));
+  dim3 grid(p.num_tokens, p.num_heads), block(threads);
   if (p.num_tokens == 0) return B200_OK;
 #define LAUNCH(FP8, VECK) reshape_and_cache_kernel<T, FP8, VECK><<<grid, block, 0, s>>>(p)
   if (fp8) {

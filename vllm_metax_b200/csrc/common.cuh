@@ -133,6 +133,10 @@ struct SplitOut {
   int num_partitions;  // P: partitions per (seq, head) in the layout
   int chunk;           // tokens per partition
   int normalized;      // 1: reference v2 format (o in query dtype)
+  // Optional [num_seqs * num_kv_heads] arrival counters (all zero on entry, left all zero on exit).
+  // When set, the streaming kernel merges the partitions of a sequence itself — the CTA that delivers
+  // the last partition of a (seq, kv head) does it — and no separate reduce launch is needed.
+  int* counters;
 };
 
 // ---- kernel-family entry points (defined in the .cu files) ------------------

@@ -63,7 +63,8 @@ void* v1_workspace(uint64_t bytes, const at::Tensor& like, cudaStream_t stream) 
   at::Tensor& t = cache[key];
   if (!t.defined() || static_cast<uint64_t>(t.numel()) < bytes) {
     const uint64_t want = bytes + bytes / 4;
-    t = at::empty({static_cast<int64_t>(want)}, like.options().dtype(at::kByte));
+    // zero-filled once: the arrival counters inside must start at zero; every launch leaves them at zero
+    t = at::zeros({static_cast<int64_t>(want)}, like.options().dtype(at::kByte));
   }
   return t.data_ptr();
 }
