@@ -95,9 +95,10 @@ typedef enum b200_attn_variant {
  * workspace: v1 needs scratch for its split-KV partials (the reference op
  *   has none because its v1 never splits).  Size it with
  *   b200_paged_attention_workspace_bytes().  It must be ZERO-FILLED ONCE before
- *   its first use (it holds arrival counters that every completed launch
- *   leaves at zero again) and may then be reused by calls on the same stream;
- *   calls that may overlap need separate workspaces.  v2 needs none (NULL, 0).
+ *   its first use (its first 1 MiB holds arrival counters that every completed
+ *   launch leaves at zero again, whatever the shapes) and may then be reused by
+ *   calls of any shape on the same stream; calls that may overlap need separate
+ *   workspaces.  v2 needs none (NULL, 0).
  */
 typedef struct b200_paged_attn_params {
   void* out;

@@ -256,3 +256,13 @@ def test_errors(ops):
         ops.paged_attention_v1(*bad)
     with pytest.raises(RuntimeError, match="block-sparse"):
         ops.paged_attention_v1(*args, 0, 16, 8, 64, 0)
+
+
+def test_v1_workspace_is_reusable_across_shapes(ops):
+    """The shim's v1 scratch is shared by calls of different shapes on a stream: the arrival counters of the
+    fused split-KV reduce must not land on a previous call's partials."""
+    shapes = [(7, 40, 40, 1571), (3, 8, 2, 4000), (9, 64, 8, 700), (2, 16, 16, 2600), (7, 40, 40, 1571)]
+    for i, (S, H, Hkv, L) in enumerate(shapes):
+        d = orc.make_decode_inputs(S, H, Hkv, 128, 16, max_seq_len=L, num_blocks=NUM_BLOCKS, seed=i, fixed_len=True)
+        out, _ = _run(ops, "v1", d)
+        _check(out, _oracle(d), ATOL_AUTO)

@@ -143,12 +143,17 @@ int pick_variant(const b200_paged_attn_params_t& p) {
   return ok ? B200_VARIANT_STREAM_MMA : B200_VARIANT_GENERIC;
 }
 
+// Workspace layout of the v1 op: [arrival counters: kCounterSlots ints][partial o | m | l].
+// The counter region sits at a FIXED place and size so that it stays all-zero between launches whatever
+// shapes share the workspace (a shape-dependent position would land on a previous call's partials).
+constexpr uint64_t kCounterSlots = 1u << 18;
+constexpr uint64_t kCounterBytes = kCounterSlots * sizeof(int);
+
 uint64_t split_bytes(const b200_paged_attn_params_t& p, int chunk) {
   const int64_t P = (p.max_seq_len + chunk - 1) / chunk;
   if (P <= 1) return 0;
-  // partial outputs, maxima, sums + one arrival counter per (seq, kv head)
-  return (uint64_t)p.num_seqs * p.num_heads * P * (p.head_size + 2) * sizeof(float) +
-         (uint64_t)p.num_seqs * p.num_kv_heads * sizeof(int);
+  // one arrival counter per (seq, kv head) + partial outputs, maxima, sums
+  return kCounterBytes + (uint64_t)p.num_seqs * p.num_heads * P * (p.head_size + 2) * sizeof(float);
 }
 
 }  // namespace
@@ -186,11 +191,14 @@ extern "C" int b200_paged_attention_v1(const b200_paged_attn_params_t* p, void* 
     B200_REQUIRE(reinterpret_cast<uintptr_t>(p->workspace) % 16 == 0, B200_ERR_WORKSPACE,
                  "workspace must be 16-byte aligned");
     const int64_t n = (int64_t)p->num_seqs * p->num_heads * so.num_partitions;
-    so.o = p->workspace;
-    so.m = static_cast<float*>(p->workspace) + n * p->head_size;
+    float* base = reinterpret_cast<float*>(static_cast<char*>(p->workspace) + kCounterBytes);
+    so.o = base;
+    so.m = base + n * p->head_size;
     so.l = so.m + n;
-    // the streaming kernel merges the partitions itself (arrival counters, zero on entry and exit)
-    if (stream_v) so.counters = reinterpret_cast<int*>(so.l + n);
+    // the streaming kernel merges the partitions itself (arrival counters, zero on entry and exit);
+    // beyond kCounterSlots (seq, kv head) pairs the separate reduce launch is used instead
+    if (stream_v && (uint64_t)p->num_seqs * p->num_kv_heads <= kCounterSlots)
+      so.counters = static_cast<int*>(p->workspace);
   }
   rc = stream_v ? launch_attention_stream(*p, so, s) : launch_attention_generic(*p, so, s);
   if (rc != B200_OK) return rc;
