@@ -266,3 +266,18 @@ def test_v1_workspace_is_reusable_across_shapes(ops):
         d = orc.make_decode_inputs(S, H, Hkv, 128, 16, max_seq_len=L, num_blocks=NUM_BLOCKS, seed=i, fixed_len=True)
         out, _ = _run(ops, "v1", d)
         _check(out, _oracle(d), ATOL_AUTO)
+
+
+@pytest.mark.parametrize("version", ["v1", "v2"])
+@pytest.mark.parametrize("H,Hkv,block_size,kv_cache_dtype",
+                         [(40, 40, 32, "auto"), (64, 8, 32, "auto"), (40, 40, 16, "auto"), (64, 8, 16, "fp8")])
+def test_streaming_kernel_is_deterministic(ops, version, H, Hkv, block_size, kv_cache_dtype):
+    """Regression: a ring stage was handed back to the TMA producer while the consumer's last ldmatrix reads
+    (bank-conflicted V rows at block_size 32, bf16) were still queued; 60 launches must be bit-identical."""
+    d = orc.make_decode_inputs(7, H, Hkv, 128, block_size, max_seq_len=1571, num_blocks=NUM_BLOCKS,
+                               kv_cache_dtype=kv_cache_dtype, seed=0)
+    first, _ = _run(ops, version, d)
+    _check(first, _oracle(d), ATOL_AUTO if kv_cache_dtype == "auto" else ATOL_BAR)
+    for _ in range(60):
+        again, _ = _run(ops, version, d)
+        assert torch.equal(again, first)

@@ -41,7 +41,8 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
 // one consumer warp per stage reads 16 B per lane (touches the data) and releases it.
 __global__ void __launch_bounds__(384, 1)
 gather_kernel(const uint8_t* __restrict__ src, const int32_t* __restrict__ table, int per_cta, int chunk,
-              int chunks_per_stage, int nst, int nprod, int ncons, unsigned long long* sink) {
+              int chunks_per_stage, int nst, int nprod, int ncons, int lanes_p, unsigned long long* sink,
+              unsigned int* bad, size_t base_off, int delay_ns) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int stage_bytes = chunk * chunks_per_stage;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)nst * stage_bytes);
@@ -58,15 +59,28 @@ gather_kernel(const uint8_t* __restrict__ src, const int32_t* __restrict__ table
   const int32_t* tb = table + (size_t)blockIdx.x * per_cta * chunks_per_stage;
   if (warp >= ncons) {
     const int pw = warp - ncons;
-    if (pw >= nprod || lane != 0) return;
+    if (pw >= nprod || lane >= lanes_p) return;
+    // lanes_p lanes share the chunks of a stage; lane 0 posts the expected byte count
+    int32_t nxt = -1;
+    if (pw < per_cta && lane < chunks_per_stage) nxt = __ldg(tb + pw * chunks_per_stage + lane);
     for (int t = pw; t < per_cta; t += nprod) {
       const int stage = t % nst;
       const uint32_t ph = (t / nst) & 1;
+      const int32_t cur = nxt;
+      if (t + nprod < per_cta && lane < chunks_per_stage) nxt = __ldg(tb + (t + nprod) * chunks_per_stage + lane);
       mbar_wait(empty + 8u * stage, ph ^ 1u);
-      mbar_expect_tx(full + 8u * stage, stage_bytes);
-      for (int c = 0; c < chunks_per_stage; ++c)
-        bulk_g2s(ring + stage * stage_bytes + c * chunk, src + (size_t)__ldg(tb + t * chunks_per_stage + c) * chunk,
-                 chunk, full + 8u * stage);
+      if (lane == 0) mbar_expect_tx(full + 8u * stage, stage_bytes);
+      if (lanes_p == 1) {
+        bulk_g2s(ring + stage * stage_bytes, src + (size_t)cur * chunk, chunk, full + 8u * stage);
+        for (int c = 1; c < chunks_per_stage; ++c)
+          bulk_g2s(ring + stage * stage_bytes + c * chunk, src + (size_t)__ldg(tb + t * chunks_per_stage + c) * chunk,
+                   chunk, full + 8u * stage);
+      } else {
+        for (int c = lane; c < chunks_per_stage; c += lanes_p)
+          bulk_g2s(ring + stage * stage_bytes + c * chunk,
+                   src + (size_t)(c == lane ? cur : __ldg(tb + t * chunks_per_stage + c)) * chunk, chunk,
+                   full + 8u * stage);
+      }
     }
     return;
   }
@@ -75,40 +89,68 @@ gather_kernel(const uint8_t* __restrict__ src, const int32_t* __restrict__ table
     const int stage = t % nst;
     const uint32_t ph = (t / nst) & 1;
     mbar_wait(full + 8u * stage, ph);
+    if (delay_ns > 0) __nanosleep(delay_ns);  // slow consumer: the ring stays full, producers block on `empty`
     const uint4 v = *reinterpret_cast<const uint4*>(smem + (size_t)stage * stage_bytes + lane * 16);
     acc += v.x ^ v.y ^ v.z ^ v.w;
+    if (bad != nullptr) {
+      // verify the data: every chunk of the stage, 16 B at 32 evenly spread offsets incl. the last 16 B
+      for (int c = 0; c < chunks_per_stage; ++c) {
+        const size_t so = (size_t)__ldg(tb + t * chunks_per_stage + c) * chunk;
+        const int off = lane == 31 ? chunk - 16 : lane * (chunk / 32);
+        const uint4 w = *reinterpret_cast<const uint4*>(smem + (size_t)stage * stage_bytes + c * chunk + off);
+        const unsigned e0 = (unsigned)((so + off + base_off) >> 2) * 2654435761u;
+        if (w.x != e0 || w.y != e0 + 2654435761u || w.z != e0 + 2u * 2654435761u || w.w != e0 + 3u * 2654435761u)
+          atomicAdd(bad + (lane == 31 ? 1 : 0), 1u);
+      }
+    }
     __syncwarp();
     if (lane == 0) mbar_arrive(empty + 8u * stage);
   }
   if (acc == 0x123456789abcdefULL) *sink = acc;
 }
 
+__global__ void fill_pattern(unsigned* p, size_t nwords) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nwords; i += (size_t)gridDim.x * blockDim.x)
+    p[i] = (unsigned)i * 2654435761u;
+}
+
 int main(int argc, char** argv) {
+  const bool verify = argc > 1 && argv[1][0] == 'v';
+  const size_t base_off = argc > 2 ? (size_t)atoi(argv[2]) : 0;  // misalign the chunk grid (bytes, multiple of 16)
+  const int delay_ns = argc > 3 ? atoi(argv[3]) : 0;
   const size_t total = (size_t)2 << 30;  // 2 GiB pool
   uint8_t* src;
   cudaMalloc(&src, total);
-  cudaMemset(src, 1, total);
+  fill_pattern<<<1184, 256>>>(reinterpret_cast<unsigned*>(src), total / 4);
+  unsigned int* bad;
+  cudaMalloc(&bad, 8);
+  cudaMemset(bad, 0, 8);
   unsigned long long* sink;
   cudaMalloc(&sink, 8);
   int nsm = 0;
   cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, 0);
   cudaFuncSetAttribute(gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   printf("SMs %d\n", nsm);
-  printf("%8s %6s %8s %6s %6s %6s %10s %10s\n", "chunk", "cps", "inflight", "nst", "nprod", "random", "us", "GB/s");
+  printf("%8s %6s %8s %6s %6s %6s %6s %6s %10s %10s\n", "chunk", "cps", "inflight", "nst", "nprod", "lanes", "ncons", "random", "us", "GB/s");
   const size_t read_bytes = (size_t)1 << 30;  // 1 GiB per launch
   std::mt19937 rng(0);
-  for (int random = 0; random <= 1; ++random)
+  struct PC { int nprod, lanes, ncons; };
+  const PC pcs[] = {{4, 1, 8}, {4, 2, 8}, {4, 4, 8}, {2, 4, 8}, {1, 4, 8}, {8, 1, 4}, {8, 4, 4}, {8, 2, 4}};
+  for (int random = 1; random >= 0; --random)
     for (int chunk : {2048, 4096, 8192, 16384})
       for (int cps : {1, 2, 4})
-        for (int inflight_kib : {64, 128, 192})
-          for (int nprod : {1, 4}) {
+        for (int inflight_kib : {32, 64, 96, 128, 192})
+          for (const PC& pc : pcs) {
+            const int nprod = pc.nprod, ncons = pc.ncons, lanes_p = pc.lanes;
+            if (lanes_p > cps) continue;
             const int stage_bytes = chunk * cps;
-            if (stage_bytes > 32768) continue;
-            const int ncons = 8;
-            // a stage must always be consumed by the same warp (mbarrier parity only tells odd from even)
-            const int nst = inflight_kib * 1024 / stage_bytes / ncons * ncons;
-            if (nst < ncons || nst * stage_bytes != inflight_kib * 1024) continue;
-            const size_t nchunks_pool = total / chunk;
+            if (stage_bytes > 16384) continue;
+            if (verify && (pc.nprod != 4 || pc.lanes != 1)) continue;
+            // a stage must always be served by the same producer / consumer warp (mbarrier parity only tells odd from even)
+            const int m = std::max(ncons, nprod);
+            const int nst = inflight_kib * 1024 / stage_bytes / m * m;
+            if (nst < m || nst * stage_bytes != inflight_kib * 1024) continue;
+            const size_t nchunks_pool = (total - base_off) / chunk - 1;
             const int per_cta = (int)(read_bytes / nsm / stage_bytes);
             const size_t nt = (size_t)nsm * per_cta * cps;
             std::vector<int32_t> tab(nchunks_pool);
@@ -126,7 +168,7 @@ int main(int argc, char** argv) {
             const int iters = 8;
             for (int it = 0; it < iters + 2; ++it) {
               cudaEventRecord(e0);
-              gather_kernel<<<nsm, 384, smem>>>(src, dtab, per_cta, chunk, cps, nst, nprod, ncons, sink);
+              gather_kernel<<<nsm, 384, smem>>>(src + base_off, dtab, per_cta, chunk, cps, nst, nprod, ncons, lanes_p, sink, verify ? bad : nullptr, base_off, delay_ns);
               cudaEventRecord(e1);
               cudaEventSynchronize(e1);
               float ms;
@@ -142,8 +184,14 @@ int main(int argc, char** argv) {
               return 1;
             }
             const double bytes = (double)nt * chunk;
-            printf("%8d %6d %7dK %6d %6d %6d %10.1f %10.0f   (best %.0f)\n", chunk, cps, inflight_kib, nst, nprod, random,
+            printf("%8d %6d %7dK %6d %6d %6d %6d %6d %10.1f %10.0f   (best %.0f)\n", chunk, cps, inflight_kib, nst, nprod, lanes_p, ncons, random,
                    sum / iters * 1e3, bytes / (sum / iters * 1e-3) / 1e9, bytes / (best * 1e-3) / 1e9);
+            if (verify) {
+              unsigned hb[2];
+              cudaMemcpy(hb, bad, 8, cudaMemcpyDeviceToHost);
+              printf("      verify: %u bad 16-byte samples in chunk bodies, %u in chunk tails (of %zu chunks x %d launches)\n", hb[0], hb[1], nt, iters + 2);
+              cudaMemset(bad, 0, 8);
+            }
             cudaFree(dtab);
           }
   return 0;

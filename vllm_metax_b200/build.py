@@ -62,6 +62,7 @@ def build_abi(verbose: bool = False) -> Path:
         objs.append(obj)
         if _newer(obj, [CSRC / src] + headers):
             extra = ["-DB200_DEBUG"] if os.environ.get("B200_DEBUG") else []
+            extra += os.environ.get("B200_EXTRA_NVCC_FLAGS", "").split()  # developer experiments
             jobs.append([nvcc, *NVCC_FLAGS, *extra, "-c", str(CSRC / src), "-o", str(obj)])
     if jobs:
         if verbose:

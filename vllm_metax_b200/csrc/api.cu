@@ -4,6 +4,7 @@
 // (csrc/attention/paged_attention_v1.cu:160-182, paged_attention_v2.cu:167-192).
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -52,33 +53,6 @@ int device_sm_count() {
   }
   cache[dev].store(v, std::memory_order_relaxed);
   return v;
-}
-
-// Partition size the v1 op uses internally.  The generic kernel always cuts at
-// 512 tokens (its shared-memory logit buffer).  The streaming kernel cuts a
-// sequence only as far as needed to give every SM an equal number of work
-// items: the smallest partition count whose last wave is >= 95 % full.
-int v1_chunk_tokens(const b200_paged_attn_params_t& p, bool stream_variant) {
-  if (!stream_variant) return B200_PARTITION_SIZE;
-  const int nsm = device_sm_count();
-  const int L = max(32, (p.max_seq_len + 31) / 32 * 32);
-  const int64_t pairs = (int64_t)p.num_seqs * p.num_kv_heads;
-  int best_chunk = L;
-  double best_eff = 0.0;
-  for (int parts = 1; parts <= 4096; ++parts) {
-    int chunk = ((L + parts - 1) / parts + 31) / 32 * 32;
-    if (chunk < 128 && parts > 1) break;
-    const int P = (L + chunk - 1) / chunk;
-    const double items = (double)pairs * P;
-    const double waves = items / nsm;
-    const double eff = waves / (double)((int64_t)((items + nsm - 1) / nsm));
-    if (eff > best_eff + 1e-9) {
-      best_eff = eff;
-      best_chunk = chunk;
-    }
-    if (eff >= 0.95) break;
-  }
-  return best_chunk;
 }
 
 namespace {
@@ -143,17 +117,13 @@ int pick_variant(const b200_paged_attn_params_t& p) {
   return ok ? B200_VARIANT_STREAM_MMA : B200_VARIANT_GENERIC;
 }
 
-// Workspace layout of the v1 op: [arrival counters: kCounterSlots ints][partial o | m | l].
-// The counter region sits at a FIXED place and size so that it stays all-zero between launches whatever
-// shapes share the workspace (a shape-dependent position would land on a previous call's partials).
-constexpr uint64_t kCounterSlots = 1u << 18;
-constexpr uint64_t kCounterBytes = kCounterSlots * sizeof(int);
-
-uint64_t split_bytes(const b200_paged_attn_params_t& p, int chunk) {
-  const int64_t P = (p.max_seq_len + chunk - 1) / chunk;
+// Workspace of the v1 op: [flat-schedule region of the streaming kernel: kFlatWorkspaceBytes, see common.cuh]
+// [generic kernel's split-KV partials: o | m | l per (seq, head, 512-token partition)].  The first region has a
+// fixed size and position, so its arrival counters stay all-zero between launches whatever shapes share it.
+uint64_t generic_split_bytes(const b200_paged_attn_params_t& p) {
+  const int64_t P = (p.max_seq_len + B200_PARTITION_SIZE - 1) / B200_PARTITION_SIZE;
   if (P <= 1) return 0;
-  // one arrival counter per (seq, kv head) + partial outputs, maxima, sums
-  return kCounterBytes + (uint64_t)p.num_seqs * p.num_heads * P * (p.head_size + 2) * sizeof(float);
+  return (uint64_t)p.num_seqs * p.num_heads * P * (p.head_size + 2) * sizeof(float);
 }
 
 }  // namespace
@@ -163,9 +133,7 @@ using namespace b200;
 
 extern "C" uint64_t b200_paged_attention_workspace_bytes(const b200_paged_attn_params_t* p) {
   if (p == nullptr || p->num_seqs <= 0 || p->num_heads <= 0 || p->num_kv_heads <= 0 || p->max_seq_len <= 0) return 0;
-  const uint64_t a = split_bytes(*p, v1_chunk_tokens(*p, false));
-  const uint64_t b = split_bytes(*p, v1_chunk_tokens(*p, true));
-  return a > b ? a : b;
+  return kFlatWorkspaceBytes + generic_split_bytes(*p);
 }
 
 extern "C" int b200_paged_attention_v1(const b200_paged_attn_params_t* p, void* stream) {
@@ -174,36 +142,40 @@ extern "C" int b200_paged_attention_v1(const b200_paged_attn_params_t* p, void* 
   if (p->num_seqs == 0 || p->max_seq_len == 0) return B200_OK;
   const int variant = pick_variant(*p);
   if (variant < 0) return -variant;
-  const bool stream_v = variant == B200_VARIANT_STREAM_MMA;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (variant == B200_VARIANT_STREAM_MMA) {
+    B200_REQUIRE(p->workspace != nullptr && p->workspace_bytes >= kFlatWorkspaceBytes, B200_ERR_WORKSPACE,
+                 "paged_attention_v1 needs %llu bytes of workspace, got %llu", (unsigned long long)kFlatWorkspaceBytes,
+                 (unsigned long long)(p->workspace ? p->workspace_bytes : 0));
+    B200_REQUIRE(reinterpret_cast<uintptr_t>(p->workspace) % 16 == 0, B200_ERR_WORKSPACE,
+                 "workspace must be 16-byte aligned");
+    rc = launch_attention_stream_flat(*p, p->workspace, s);  // one launch: split pairs are merged in the kernel
+    if (rc == B200_OK) g_last_variant = variant;
+    return rc;
+  }
   SplitOut so;
-  so.chunk = v1_chunk_tokens(*p, stream_v);
+  so.chunk = B200_PARTITION_SIZE;  // the generic kernel's shared-memory logit buffer
   so.num_partitions = (p->max_seq_len + so.chunk - 1) / so.chunk;
   so.normalized = 0;
   so.m = so.l = nullptr;
   so.o = nullptr;
-  so.counters = nullptr;
   if (so.num_partitions > 1) {
-    const uint64_t need = split_bytes(*p, so.chunk);
+    const uint64_t need = kFlatWorkspaceBytes + generic_split_bytes(*p);
     B200_REQUIRE(p->workspace != nullptr && p->workspace_bytes >= need, B200_ERR_WORKSPACE,
                  "paged_attention_v1 needs %llu bytes of workspace, got %llu", (unsigned long long)need,
                  (unsigned long long)(p->workspace ? p->workspace_bytes : 0));
     B200_REQUIRE(reinterpret_cast<uintptr_t>(p->workspace) % 16 == 0, B200_ERR_WORKSPACE,
                  "workspace must be 16-byte aligned");
     const int64_t n = (int64_t)p->num_seqs * p->num_heads * so.num_partitions;
-    float* base = reinterpret_cast<float*>(static_cast<char*>(p->workspace) + kCounterBytes);
+    float* base = reinterpret_cast<float*>(static_cast<char*>(p->workspace) + kFlatWorkspaceBytes);
     so.o = base;
     so.m = base + n * p->head_size;
     so.l = so.m + n;
-    // the streaming kernel merges the partitions itself (arrival counters, zero on entry and exit);
-    // beyond kCounterSlots (seq, kv head) pairs the separate reduce launch is used instead
-    if (stream_v && (uint64_t)p->num_seqs * p->num_kv_heads <= kCounterSlots)
-      so.counters = static_cast<int*>(p->workspace);
   }
-  rc = stream_v ? launch_attention_stream(*p, so, s) : launch_attention_generic(*p, so, s);
+  rc = launch_attention_generic(*p, so, s);
   if (rc != B200_OK) return rc;
   g_last_variant = variant;
-  return so.counters != nullptr ? B200_OK : launch_split_reduce(*p, so, s);
+  return launch_split_reduce(*p, so, s);
 }
 
 extern "C" int b200_paged_attention_v2(const b200_paged_attn_params_t* p, void* stream) {
@@ -222,7 +194,6 @@ extern "C" int b200_paged_attention_v2(const b200_paged_attn_params_t* p, void* 
   so.m = p->max_logits;
   so.l = p->exp_sums;
   so.o = p->tmp_out;
-  so.counters = nullptr;
   rc = variant == B200_VARIANT_STREAM_MMA ? launch_attention_stream(*p, so, s) : launch_attention_generic(*p, so, s);
   if (rc != B200_OK) return rc;
   g_last_variant = variant;

@@ -4,9 +4,17 @@
 // (reference: csrc/attention/attention_kernels.cuh:79-485).
 //
 // Design:
-//  * persistent grid, one CTA per SM; work item = (partition, seq, kv head);
-//    the CTA serves ALL query heads of the kv head, so every KV byte is read
-//    from HBM once (the reference re-reads it once per query head);
+//  * persistent grid, one CTA per SM; the CTA serves ALL query heads of a kv
+//    head, so every KV byte is read from HBM once (the reference re-reads it
+//    once per query head).  Two schedules:
+//      FLAT (paged_attention_v1): the 32-token tiles of all (seq, kv head)
+//        pairs form one flat sequence cut into equal contiguous ranges, one
+//        per CTA — perfect balance, <= 2 split pairs per CTA, and a pair that
+//        lies inside one CTA is finished with no global round trip; split
+//        pairs are merged by the CTA that delivers the last segment (arrival
+//        counters), so the op is a single launch;
+//      items (paged_attention_v2): work item = (512-token partition, seq, kv
+//        head), partials in the reference's exp_sums/max_logits/tmp_out format;
 //  * four producer warps (one issuing lane each, tiles dealt round-robin) walk
 //    the block table and stream the contiguous K chunk [D/x][B][x] and V chunk
 //    [D][B] of each (block, kv head) into a shared-memory ring with 1-D TMA
@@ -28,6 +36,7 @@
 #include <float.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 
@@ -53,7 +62,11 @@ struct StreamParams {
   const float* k_scale;
   const float* v_scale;
   __nv_bfloat16* out;
-  SplitOut so;
+  SplitOut so;              // item schedule only
+  float* ws_o;              // flat schedule: slots [cta][2][kFlatMaxGroup][kD] (unnormalised partial outputs)
+  float* ws_m;              //                      [cta][2][kFlatMaxGroup]     (max logit, log2 units)
+  float* ws_l;              //                      [cta][2][kFlatMaxGroup]     (sum exp)
+  int* counters;            //                      [S * Hkv] arrival counters, zero between launches
   int64_t q_stride;         // elements
   int64_t kv_block_stride;  // bytes
   int64_t kv_head_stride;   // bytes
@@ -172,22 +185,126 @@ __device__ __forceinline__ void consumer_bar_sync() {
   asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * kWarpSize) : "memory");
 }
 
-// ---- work items ----------------------------------------------------------------
-struct Item {
-  int s, kvh, part, t0, t1, L;
+// ---- work decomposition ----------------------------------------------------------
+// A segment is a run of whole tiles of one (seq, kv head) pair processed by one CTA.
+struct Seg {
+  int s, kvh, t0, t1, L, part;
+  bool starts, ends;   // flat: the segment contains the first / last tile of its pair
+  long long pb;        // flat: position of the pair's first tile in the flat tile sequence
+  int n;               // flat: tiles of the pair
 };
-__device__ __forceinline__ bool decode_item(const StreamParams& p, int item, Item& it) {
-  const int SH = p.S * p.Hkv;
-  it.part = item / SH;
-  const int r = item - it.part * SH;
-  it.s = r / p.Hkv;
-  it.kvh = r - it.s * p.Hkv;
-  it.L = __ldg(p.seq_lens + it.s);
-  it.t0 = it.part * p.so.chunk;
-  if (it.t0 >= it.L) return false;
-  it.t1 = min(it.t0 + p.so.chunk, it.L);
-  return true;
+// flat schedule of this CTA, computed once by warp 0 (shared memory)
+struct Sched {
+  long long f0, f1;    // this CTA's tile range
+  long long base0;     // flat position of the first tile of sequence s0
+  long long T;         // tiles in the batch
+  int s0;              // sequence holding tile f0
+  int neff;            // CTAs that own a non-empty range = min(gridDim.x, T)
+};
+__device__ __forceinline__ int tiles_of(int L) { return L > 0 ? (L + kTileTokens - 1) / kTileTokens : 0; }
+__device__ __forceinline__ long long warp_sum_ll(long long v) {
+#pragma unroll
+  for (int m = 16; m >= 1; m >>= 1) v += __shfl_xor_sync(0xffffffffu, v, m);
+  return v;
 }
+// CTA that owns flat tile x when T tiles are cut into n ranges [c*T/n, (c+1)*T/n)
+__device__ __forceinline__ int cta_of_tile(long long x, long long T, int n) {
+  return (int)(((x + 1) * n - 1) / T);
+}
+__device__ void compute_sched(const StreamParams& p, Sched* sc, int lane) {
+  long long tot = 0;
+  for (int i = lane; i < p.S; i += 32) tot += tiles_of(__ldg(p.seq_lens + i));
+  tot = warp_sum_ll(tot);
+  const long long T = tot * p.Hkv;
+  const int neff = (int)(T < (long long)gridDim.x ? T : (long long)gridDim.x);
+  long long f0 = 0, f1 = 0;
+  if ((int)blockIdx.x < neff) {
+    f0 = (long long)blockIdx.x * T / neff;
+    f1 = (long long)(blockIdx.x + 1) * T / neff;
+  }
+  if (lane == 0) {
+    sc->f0 = f0; sc->f1 = f1; sc->T = T; sc->neff = neff; sc->s0 = 0; sc->base0 = 0;
+  }
+  if (f0 >= f1) return;
+  long long running = 0;  // tiles per kv head before sequence `b`
+  for (int b = 0; b < p.S; b += 32) {
+    const int n = b + lane < p.S ? tiles_of(__ldg(p.seq_lens + b + lane)) : 0;
+    long long incl = n;
+#pragma unroll
+    for (int m = 1; m < 32; m <<= 1) {
+      const long long o = __shfl_up_sync(0xffffffffu, incl, m);
+      if (lane >= m) incl += o;
+    }
+    const long long lo = (running + incl - n) * p.Hkv, hi = (running + incl) * p.Hkv;
+    const bool hit = n > 0 && lo <= f0 && f0 < hi;
+    const unsigned ball = __ballot_sync(0xffffffffu, hit);
+    if (ball) {
+      if (hit) {
+        sc->s0 = b + lane;
+        sc->base0 = lo;
+      }
+      return;
+    }
+    running += __shfl_sync(0xffffffffu, incl, 31);
+  }
+}
+
+template <bool FLAT>
+struct WorkIter {
+  long long f, f1, base;
+  int s, n, L, item;
+  __device__ __forceinline__ void init(const StreamParams& p, const Sched* sc) {
+    if constexpr (FLAT) {
+      f = sc->f0; f1 = sc->f1; base = sc->base0; s = sc->s0;
+      L = 0; n = 0;
+      if (f < f1) {
+        L = __ldg(p.seq_lens + s);
+        n = tiles_of(L);
+      }
+    } else {
+      item = (int)blockIdx.x - (int)gridDim.x;
+    }
+  }
+  __device__ __forceinline__ bool next(const StreamParams& p, Seg& g) {
+    if constexpr (FLAT) {
+      if (f >= f1) return false;
+      while (f >= base + (long long)p.Hkv * n) {  // f < f1 <= T: a later sequence holds tile f
+        base += (long long)p.Hkv * n;
+        ++s;
+        L = __ldg(p.seq_lens + s);
+        n = tiles_of(L);
+      }
+      const long long r = f - base;
+      const int kvh = (int)(r / n);
+      const int tile0 = (int)(r - (long long)kvh * n);
+      const long long pb = base + (long long)kvh * n, pe = pb + n;
+      const long long se = pe < f1 ? pe : f1;
+      const int tile1 = tile0 + (int)(se - f);
+      g.s = s; g.kvh = kvh; g.L = L; g.part = 0;
+      g.t0 = tile0 * kTileTokens;
+      g.t1 = min(tile1 * kTileTokens, L);
+      g.starts = tile0 == 0; g.ends = se == pe; g.pb = pb; g.n = n;
+      f = se;
+      return true;
+    } else {
+      const int SH = p.S * p.Hkv;
+      for (;;) {
+        item += (int)gridDim.x;
+        if (item >= p.total_items) return false;
+        g.part = item / SH;
+        const int r = item - g.part * SH;
+        g.s = r / p.Hkv;
+        g.kvh = r - g.s * p.Hkv;
+        g.L = __ldg(p.seq_lens + g.s);
+        g.t0 = g.part * p.so.chunk;
+        if (g.t0 >= g.L) continue;
+        g.t1 = min(g.t0 + p.so.chunk, g.L);
+        g.starts = g.ends = false; g.pb = 0; g.n = 0;
+        return true;
+      }
+    }
+  }
+};
 
 template <int B, bool FP8>
 struct Cfg {
@@ -199,7 +316,7 @@ struct Cfg {
 };
 
 // ---- the kernel ------------------------------------------------------------------
-template <int B, bool FP8, int NT>
+template <int B, bool FP8, int NT, bool FLAT>
 __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(const StreamParams p) {
   using C = Cfg<B, FP8>;
   constexpr bool F16 = FP8;  // MMA operand type: f16 for fp8 caches, bf16 otherwise
@@ -212,7 +329,8 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
   float* merge_m = merge_o + kConsumerWarps * NH * kMergeStride;
   float* merge_l = merge_m + kConsumerWarps * NH;
   uint64_t* bars = reinterpret_cast<uint64_t*>(merge_l + kConsumerWarps * NH);
-  int* merge_flag = reinterpret_cast<int*>(bars + 2 * nst);
+  Sched* sched = reinterpret_cast<Sched*>(bars + 2 * nst);
+  int* merge_flag = reinterpret_cast<int*>(sched + 1);
   const uint32_t ring_u32 = smem_u32(ring);
   const uint32_t full_u32 = smem_u32(bars);
   const uint32_t empty_u32 = full_u32 + 8u * nst;
@@ -225,6 +343,9 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if constexpr (FLAT) {
+    if (warp == 0) compute_sched(p, sched, lane);
   }
   __syncthreads();
 
@@ -239,9 +360,12 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
     int stage = pw;                   // g_next % nst (nst >= kProducerWarps)
     uint32_t phase = 0;               // (g_next / nst) & 1
     uint32_t tile_base = 0;
-    for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-      Item it;
-      if (!decode_item(p, item, it)) continue;
+    WorkIter<FLAT> wi;
+    wi.init(p, sched);
+    Seg it;
+    int item = -1;  // segment ordinal (debug messages)
+    while (wi.next(p, it)) {
+      ++item;
       const int nblk = (it.t1 - it.t0 + B - 1) / B;
       const uint32_t ntiles = (uint32_t)((it.t1 - it.t0 + kTileTokens - 1) / kTileTokens);
       const int32_t* bt = p.bt + (int64_t)it.s * p.max_blocks + it.t0 / B;
@@ -321,10 +445,13 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
   const float ksc = FP8 ? __ldg(p.k_scale) : 1.f;
   const float vsc = FP8 ? __ldg(p.v_scale) : 1.f;
 
-  uint32_t tile_base = 0;  // tiles issued to the ring before this item
-  for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-    Item it;
-    if (!decode_item(p, item, it)) continue;
+  uint32_t tile_base = 0;  // tiles issued to the ring before this segment
+  WorkIter<FLAT> wi;
+  wi.init(p, sched);
+  Seg it;
+  int item = -1;
+  while (wi.next(p, it)) {
+    ++item;
     const int ntiles = (it.t1 - it.t0 + kTileTokens - 1) / kTileTokens;
 
     // ---- Q fragments (B operand: k = dims, n = heads) ------------------------------
@@ -552,7 +679,12 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
           }
         }
       }
-      // all lanes have consumed the stage: hand it back to the producer
+      // All lanes have consumed the stage: hand it back to the producer.  The fence is REQUIRED: ptxas
+      // issues the mbarrier arrive without waiting for the LDSMs still in flight (it even hoists it above the
+      // last HMMAs), and with bank-conflicted V fragments (B = 32 bf16: 64-byte rows, 4-way conflicts) the
+      // shared-memory queue is deep enough for the refill of the stage to land before those reads are
+      // performed (seen as run-to-run differences in output dims 112-127).  MEMBAR.CTA orders them.
+      __threadfence_block();
       __syncwarp();
       if (lane == 0) mbar_arrive(empty_u32 + 8u * stage);
     }
@@ -584,10 +716,11 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
       }
     }
     consumer_bar_sync();
-    {
+    const int d = tid & (kD - 1);
+    if constexpr (!FLAT) {
+      // ---- item schedule: one partition of (seq, kv head) --------------------------------------------
       const bool single = it.L <= p.so.chunk;
       const bool want_partials = p.so.o != nullptr && (!single || p.so.normalized);
-      const int d = tid & (kD - 1);
       for (int h = tid >> 7; h < NH; h += (kConsumerWarps * kWarpSize) >> 7) {
         if (h >= p.G) break;
         float M = -INFINITY;
@@ -616,37 +749,66 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
           }
         }
       }
-    }
-    if (p.so.counters != nullptr && it.L > p.so.chunk) {
-      // ---- fused split-KV reduce: the CTA that delivers the last partition of (seq, kv head) merges them
-      // (same arithmetic as split_reduce_kernel / reference attention_kernels.cuh:594-657) --------------
-      __threadfence();       // this thread's partials are visible device-wide
-      consumer_bar_sync();   // ... and so are everyone's
-      if (tid == 0) {
-        const int nparts = (it.L + p.so.chunk - 1) / p.so.chunk;
-        int* cnt = p.so.counters + it.s * p.Hkv + it.kvh;
-        const int old = atomicAdd(cnt, 1);
-        const int last = old == nparts - 1;
-        if (last) *cnt = 0;  // leave the counters zeroed for the next launch
-        *merge_flag = last;
-      }
-      consumer_bar_sync();
-      if (*merge_flag) {
-        __threadfence();
-        const int nparts = (it.L + p.so.chunk - 1) / p.so.chunk;
-        const int d = tid & (kD - 1);
-        for (int h = tid >> 7; h < p.G; h += (kConsumerWarps * kWarpSize) >> 7) {
-          const int head = it.kvh * p.G + h;
-          const int64_t base = ((int64_t)it.s * p.H + head) * p.so.num_partitions;
-          float M = -INFINITY;
-          for (int j = 0; j < nparts; ++j) M = fmaxf(M, __ldcg(p.so.m + base + j));
-          float lsum = 0.f, o = 0.f;
-          for (int j = 0; j < nparts; ++j) {
-            const float wgt = __expf(__ldcg(p.so.m + base + j) - M);
-            lsum = fmaf(__ldcg(p.so.l + base + j), wgt, lsum);
-            o = fmaf(__ldcg(reinterpret_cast<const float*>(p.so.o) + (base + j) * kD + d), wgt, o);
+    } else {
+      // ---- flat schedule: a whole pair is finished here; a split pair leaves a partial in this CTA's
+      // head / tail slot and the CTA that delivers the pair's last segment merges them (same arithmetic
+      // as the reference reduce, csrc/attention/attention_kernels.cuh:594-657) ----------------------------
+      const bool whole = it.starts && it.ends;
+      const int slot = ((int)blockIdx.x * 2 + (it.starts ? 1 : 0)) * kFlatMaxGroup;
+      for (int h = tid >> 7; h < NH; h += (kConsumerWarps * kWarpSize) >> 7) {
+        if (h >= p.G) break;
+        float M = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps; ++w) M = fmaxf(M, merge_m[w * NH + h]);
+        float lsum = 0.f, o = 0.f;
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps; ++w) {
+          const float wgt = exp2f(merge_m[w * NH + h] - M);
+          lsum = fmaf(merge_l[w * NH + h], wgt, lsum);
+          o = fmaf(merge_o[(w * NH + h) * kMergeStride + d], wgt, o);
+        }
+        o *= vsc;
+        if (whole) {
+          p.out[((int64_t)it.s * p.H + it.kvh * p.G + h) * kD + d] =
+              __float2bfloat16_rn(o * __fdividef(1.f, lsum + 1e-6f));
+        } else {
+          p.ws_o[(int64_t)(slot + h) * kD + d] = o;
+          if (d == 0) {
+            p.ws_m[slot + h] = M;  // log2 units
+            p.ws_l[slot + h] = lsum;
           }
-          p.out[((int64_t)it.s * p.H + head) * kD + d] = __float2bfloat16_rn(o * __fdividef(1.f, lsum + 1e-6f));
+        }
+      }
+      if (!whole) {
+        __threadfence();       // this thread's partials are visible device-wide
+        consumer_bar_sync();   // ... and so are everyone's
+        const int c0 = cta_of_tile(it.pb, sched->T, sched->neff);
+        const int c1 = cta_of_tile(it.pb + it.n - 1, sched->T, sched->neff);
+        if (tid == 0) {
+          int* cnt = p.counters + it.s * p.Hkv + it.kvh;
+          const int old = atomicAdd(cnt, 1);
+          const int last = old == c1 - c0;
+          if (last) *cnt = 0;  // leave the counters zeroed for the next launch
+          *merge_flag = last;
+        }
+        consumer_bar_sync();
+        if (*merge_flag) {
+          __threadfence();
+          for (int h = tid >> 7; h < p.G; h += (kConsumerWarps * kWarpSize) >> 7) {
+            // CTA c0 holds the segment that starts the pair (tail slot), the others their head slot
+            float M = -INFINITY;
+            for (int c = c0; c <= c1; ++c)
+              M = fmaxf(M, __ldcg(p.ws_m + (c * 2 + (c == c0 ? 1 : 0)) * kFlatMaxGroup + h));
+            float lsum = 0.f, o = 0.f;
+            for (int c = c0; c <= c1; ++c) {
+              const int sl = (c * 2 + (c == c0 ? 1 : 0)) * kFlatMaxGroup + h;
+              const float wgt = exp2f(__ldcg(p.ws_m + sl) - M);
+              lsum = fmaf(__ldcg(p.ws_l + sl), wgt, lsum);
+              o = fmaf(__ldcg(p.ws_o + (int64_t)sl * kD + d), wgt, o);
+            }
+            p.out[((int64_t)it.s * p.H + it.kvh * p.G + h) * kD + d] =
+                __float2bfloat16_rn(o * __fdividef(1.f, lsum + 1e-6f));
+          }
         }
       }
     }
@@ -658,12 +820,12 @@ template <int B, bool FP8, int NT>
 size_t stream_smem_bytes(int nstages) {
   using C = Cfg<B, FP8>;
   return 128 + (size_t)nstages * C::kStageBytes +
-         (size_t)kConsumerWarps * 8 * NT * (kMergeStride + 2) * sizeof(float) + (size_t)nstages * 16 + 16;
+         (size_t)kConsumerWarps * 8 * NT * (kMergeStride + 2) * sizeof(float) + (size_t)nstages * 16 + sizeof(Sched) + 16;
 }
 
 constexpr size_t kMaxSmem = 227 * 1024;
 
-template <int B, bool FP8, int NT>
+template <int B, bool FP8, int NT, bool FLAT>
 int launch_stream_t(StreamParams& sp, cudaStream_t s) {
   using C = Cfg<B, FP8>;
   // deepest ring that fits (capped: beyond ~190 KiB in flight nothing is gained)
@@ -676,7 +838,7 @@ int launch_stream_t(StreamParams& sp, cudaStream_t s) {
     nst = max(kConsumerWarps, min(nst, atoi(e) / kConsumerWarps * kConsumerWarps));
   sp.nstages = nst;
   const size_t smem = stream_smem_bytes<B, FP8, NT>(nst);
-  auto kern = paged_attention_stream_kernel<B, FP8, NT>;
+  auto kern = paged_attention_stream_kernel<B, FP8, NT, FLAT>;
   static thread_local int configured_device = -1;
   int dev = 0;
   cudaGetDevice(&dev);
@@ -688,7 +850,7 @@ int launch_stream_t(StreamParams& sp, cudaStream_t s) {
     }
     configured_device = dev;
   }
-  const int grid = min(device_sm_count(), sp.total_items);
+  const int grid = min(min(device_sm_count(), kFlatMaxCtas), sp.total_items);
   kern<<<grid, kThreads, smem, s>>>(sp);
   count_launch();
   return check_launch("paged_attention_stream");
@@ -703,7 +865,8 @@ bool stream_variant_eligible(const b200_paged_attn_params_t& p, const char** why
   if (p.dtype != B200_DTYPE_BF16) w = "query dtype is not bf16";
   else if (p.head_size != kD) w = "head_size is not 128";
   else if (p.block_size != 16 && p.block_size != 32) w = "block_size is not 16 or 32";
-  else if (G < 1 || G > 16) w = "GQA group size above 16";
+  else if (G < 1 || G > kFlatMaxGroup) w = "GQA group size above 16";
+  else if ((uint64_t)p.num_seqs * p.num_kv_heads > kFlatCounterSlots) w = "more (seq, kv head) pairs than arrival counters";
   else if ((p.kv_block_stride * eb) % 16 != 0 || (p.kv_head_stride * eb) % 16 != 0) w = "KV strides not 16-byte multiples";
   else if ((reinterpret_cast<uintptr_t>(p.key_cache) | reinterpret_cast<uintptr_t>(p.value_cache)) % 16 != 0) w = "KV cache not 16-byte aligned";
   else if (p.q_stride % 8 != 0 || reinterpret_cast<uintptr_t>(p.query) % 16 != 0) w = "query rows not 16-byte aligned";
@@ -711,38 +874,66 @@ bool stream_variant_eligible(const b200_paged_attn_params_t& p, const char** why
   return w == nullptr;
 }
 
-int launch_attention_stream(const b200_paged_attn_params_t& p, const SplitOut& so, cudaStream_t s) {
-  const char* why = nullptr;
-  B200_REQUIRE(stream_variant_eligible(p, &why), B200_ERR_UNSUPPORTED, "stream kernel not eligible: %s", why);
-  B200_REQUIRE(so.chunk > 0 && so.chunk % kTileTokens == 0, B200_ERR_INVALID_ARGUMENT,
-               "stream kernel: chunk %d is not a multiple of %d", so.chunk, kTileTokens);
-  const bool fp8 = p.kv_dtype == B200_KV_FP8_E4M3;
-  const int eb = fp8 ? 1 : 2;
+namespace {
+StreamParams fill_stream_params(const b200_paged_attn_params_t& p) {
+  const int eb = p.kv_dtype == B200_KV_FP8_E4M3 ? 1 : 2;
   StreamParams sp;
+  memset(&sp, 0, sizeof(sp));
   sp.q = static_cast<const __nv_bfloat16*>(p.query);
   sp.kc = static_cast<const uint8_t*>(p.key_cache);
   sp.vc = static_cast<const uint8_t*>(p.value_cache);
   sp.bt = p.block_tables; sp.seq_lens = p.seq_lens; sp.alibi = p.alibi_slopes;
   sp.k_scale = p.k_scale; sp.v_scale = p.v_scale;
   sp.out = static_cast<__nv_bfloat16*>(p.out);
-  sp.so = so;
   sp.q_stride = p.q_stride;
   sp.kv_block_stride = p.kv_block_stride * eb;
   sp.kv_head_stride = p.kv_head_stride * eb;
   sp.S = p.num_seqs; sp.H = p.num_heads; sp.Hkv = p.num_kv_heads; sp.G = p.num_heads / p.num_kv_heads;
   sp.max_blocks = p.max_num_blocks_per_seq;
-  sp.nstages = 0;
-  sp.total_items = so.num_partitions * p.num_seqs * p.num_kv_heads;
   sp.scale = p.scale;
-  sp.debug_num_blocks = 0;
   if (const char* e = getenv("B200_DEBUG_NUM_BLOCKS")) sp.debug_num_blocks = atoi(e);
-  if (sp.total_items == 0) return B200_OK;
+  return sp;
+}
+
+template <bool FLAT>
+int dispatch_stream(const b200_paged_attn_params_t& p, StreamParams& sp, cudaStream_t s) {
+  const bool fp8 = p.kv_dtype == B200_KV_FP8_E4M3;
   const int nt = (sp.G + 7) / 8;
-#define GO(B_, FP8_)                                                     \
-  (nt == 1 ? launch_stream_t<B_, FP8_, 1>(sp, s) : launch_stream_t<B_, FP8_, 2>(sp, s))
+#define GO(B_, FP8_) \
+  (nt == 1 ? launch_stream_t<B_, FP8_, 1, FLAT>(sp, s) : launch_stream_t<B_, FP8_, 2, FLAT>(sp, s))
   if (p.block_size == 16) return fp8 ? GO(16, true) : GO(16, false);
   return fp8 ? GO(32, true) : GO(32, false);
 #undef GO
+}
+}  // namespace
+
+int launch_attention_stream(const b200_paged_attn_params_t& p, const SplitOut& so, cudaStream_t s) {
+  const char* why = nullptr;
+  B200_REQUIRE(stream_variant_eligible(p, &why), B200_ERR_UNSUPPORTED, "stream kernel not eligible: %s", why);
+  B200_REQUIRE(so.chunk > 0 && so.chunk % kTileTokens == 0, B200_ERR_INVALID_ARGUMENT,
+               "stream kernel: chunk %d is not a multiple of %d", so.chunk, kTileTokens);
+  StreamParams sp = fill_stream_params(p);
+  sp.so = so;
+  sp.total_items = so.num_partitions * p.num_seqs * p.num_kv_heads;
+  if (sp.total_items == 0) return B200_OK;
+  return dispatch_stream<false>(p, sp, s);
+}
+
+int launch_attention_stream_flat(const b200_paged_attn_params_t& p, void* workspace, cudaStream_t s) {
+  const char* why = nullptr;
+  B200_REQUIRE(stream_variant_eligible(p, &why), B200_ERR_UNSUPPORTED, "stream kernel not eligible: %s", why);
+  B200_REQUIRE(workspace != nullptr, B200_ERR_WORKSPACE, "stream kernel: workspace missing");
+  StreamParams sp = fill_stream_params(p);
+  sp.counters = static_cast<int*>(workspace);
+  float* slots = reinterpret_cast<float*>(static_cast<char*>(workspace) + kFlatCounterBytes);
+  sp.ws_o = slots;
+  sp.ws_m = slots + (size_t)kFlatMaxCtas * 2 * kFlatMaxGroup * kD;
+  sp.ws_l = sp.ws_m + (size_t)kFlatMaxCtas * 2 * kFlatMaxGroup;
+  // upper bound of the tile count (the kernel derives the real one from seq_lens on the device)
+  const int64_t tiles = (int64_t)p.num_seqs * p.num_kv_heads * ((p.max_seq_len + kTileTokens - 1) / kTileTokens);
+  sp.total_items = (int)(tiles < (int64_t)kFlatMaxCtas ? tiles : (int64_t)kFlatMaxCtas);
+  if (sp.total_items == 0) return B200_OK;
+  return dispatch_stream<true>(p, sp, s);
 }
 
 }  // namespace b200

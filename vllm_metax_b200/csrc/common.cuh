@@ -133,17 +133,30 @@ struct SplitOut {
   int num_partitions;  // P: partitions per (seq, head) in the layout
   int chunk;           // tokens per partition
   int normalized;      // 1: reference v2 format (o in query dtype)
-  // Optional [num_seqs * num_kv_heads] arrival counters (all zero on entry, left all zero on exit).
-  // When set, the streaming kernel merges the partitions of a sequence itself — the CTA that delivers
-  // the last partition of a (seq, kv head) does it — and no separate reduce launch is needed.
-  int* counters;
 };
 
+// ---- flat (tile-balanced) schedule of the streaming kernel, used by paged_attention_v1 -----------------
+// The tiles (32 tokens of one (seq, kv head) pair) of the whole batch form one flat sequence that is cut
+// into equal contiguous ranges, one per CTA.  A pair that straddles a cut leaves one partial result per
+// CTA it touches in that CTA's "head" slot (segment that does not start the pair) or "tail" slot (segment
+// that starts the pair but does not finish it); the CTA that delivers the pair's last segment — found with
+// an arrival counter per pair — merges them.  Slots and counters live in the caller's workspace:
+//   [counters: kFlatCounterSlots ints, all zero between launches][slots: kFlatMaxCtas x 2 x kFlatMaxGroup x (D+2) f32]
+constexpr int kFlatMaxCtas = 256;
+constexpr int kFlatMaxGroup = 16;   // query heads per kv head served by the streaming kernel
+constexpr int kFlatHeadSize = 128;
+constexpr uint64_t kFlatCounterSlots = 1u << 18;
+constexpr uint64_t kFlatCounterBytes = kFlatCounterSlots * sizeof(int);
+constexpr uint64_t kFlatSlotBytes =
+    (uint64_t)kFlatMaxCtas * 2 * kFlatMaxGroup * (kFlatHeadSize + 2) * sizeof(float);
+constexpr uint64_t kFlatWorkspaceBytes = kFlatCounterBytes + kFlatSlotBytes;
+
 // ---- kernel-family entry points (defined in the .cu files) ------------------
-// max partitions the v1 path may use for these shapes / its chunk size
-int v1_chunk_tokens(const b200_paged_attn_params_t& p, bool stream_variant);
 int launch_attention_generic(const b200_paged_attn_params_t& p, const SplitOut& so, cudaStream_t s);
+// v2 format / fixed-size partitions: work item = (partition, seq, kv head)
 int launch_attention_stream(const b200_paged_attn_params_t& p, const SplitOut& so, cudaStream_t s);
+// v1: flat schedule; `workspace` holds kFlatWorkspaceBytes laid out as above
+int launch_attention_stream_flat(const b200_paged_attn_params_t& p, void* workspace, cudaStream_t s);
 bool stream_variant_eligible(const b200_paged_attn_params_t& p, const char** why);
 int launch_split_reduce(const b200_paged_attn_params_t& p, const SplitOut& so, cudaStream_t s);
 int device_sm_count();
