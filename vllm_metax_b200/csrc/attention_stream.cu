@@ -38,6 +38,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -46,8 +48,8 @@ namespace {
 constexpr int kD = 128;             // head size served by this kernel
 constexpr int kTileTokens = 32;     // tokens per ring stage
 constexpr int kConsumerWarps = 8;
-constexpr int kProducerWarps = 4;
-constexpr int kThreads = (kConsumerWarps + kProducerWarps) * kWarpSize;
+// producer warps: 4 (384 threads, up to 168 registers each) or 8 (512 threads, 128 registers: ptxas fits the
+// consumer loop into 128 without spills; setmaxnreg was tried and ptxas does not allocate past the launch bound)
 constexpr int kMergeStride = kD + 4;  // fp32 words per (warp, head) row
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -160,11 +162,12 @@ __device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], 
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
   }
 }
-// two e4m3 bytes -> f16x2 (exact)
-__device__ __forceinline__ uint32_t cvt_e4m3x2_f16x2(uint16_t v) {
-  uint32_t d;
-  asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(d) : "h"(v));
-  return d;
+// four e4m3 bytes -> two f16x2 (bytes 0,1 and bytes 2,3); the 16-bit halves are named in PTX so that ptxas
+// uses the .H1 operand selector instead of masking / shifting them out with LOP3
+__device__ __forceinline__ void cvt_e4m3x4_f16x2x2(uint32_t r, uint32_t& lo, uint32_t& hi) {
+  asm("{\n.reg .b16 l, h;\nmov.b32 {l, h}, %2;\ncvt.rn.f16x2.e4m3x2 %0, l;\ncvt.rn.f16x2.e4m3x2 %1, h;\n}"
+      : "=r"(lo), "=r"(hi)
+      : "r"(r));
 }
 template <bool F16>
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
@@ -316,9 +319,12 @@ struct Cfg {
 };
 
 // ---- the kernel ------------------------------------------------------------------
-template <int B, bool FP8, int NT, bool FLAT>
-__global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(const StreamParams p) {
+template <int B, bool FP8, int NT, bool FLAT, int NP>
+__global__ void __launch_bounds__((kConsumerWarps + NP) * kWarpSize, 1)
+paged_attention_stream_kernel(const StreamParams p) {
   using C = Cfg<B, FP8>;
+  constexpr int kProducerWarps = NP;
+  static_assert(NP == 4 || NP == 8, "whole warpgroups of producers");
   constexpr bool F16 = FP8;  // MMA operand type: f16 for fp8 caches, bf16 otherwise
   constexpr int NH = 8 * NT;  // padded heads per kv head
   extern __shared__ uint8_t smem_raw[];
@@ -446,6 +452,7 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
   const float vsc = FP8 ? __ldg(p.v_scale) : 1.f;
 
   uint32_t tile_base = 0;  // tiles issued to the ring before this segment
+  uint32_t stage = (uint32_t)warp, parity = 0;  // ring stage / phase of this warp's next tile
   WorkIter<FLAT> wi;
   wi.init(p, sched);
   Seg it;
@@ -530,10 +537,9 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
     // phase of a stage could pass a parity wait one round early: mbarrier parity only tells odd from
     // even.)
     for (int ti = (int)((warp - tile_base) & (kConsumerWarps - 1)); ti < ntiles; ti += kConsumerWarps) {
-      const uint32_t gt = tile_base + (uint32_t)ti;
-      const uint32_t stage = gt % (uint32_t)nst;
-      const uint32_t parity = (gt / (uint32_t)nst) & 1u;
-      MBAR_WAIT(full_u32 + 8u * stage, parity, 2, item, (int)gt);
+      // this warp's tiles are gt = warp, warp + 8, ... over the whole stream, so stage / parity advance
+      // incrementally (no division by the runtime ring depth)
+      MBAR_WAIT(full_u32 + 8u * stage, parity, 2, item, (int)(tile_base + (uint32_t)ti));
       const uint32_t sb = ring_u32 + stage * C::kStageBytes;
       const int tok0 = it.t0 + ti * kTileTokens;   // first token of the tile
       const int nvalid = min(kTileTokens, it.t1 - tok0);
@@ -564,10 +570,11 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
           for (int kk = 0; kk < 4; ++kk) {
             uint32_t r[4];
             ldmatrix_x4(r, kb + kk * 2 * B * 16);
-            uint32_t a0[4] = {cvt_e4m3x2_f16x2((uint16_t)(r[0] & 0xffffu)), cvt_e4m3x2_f16x2((uint16_t)(r[1] & 0xffffu)),
-                              cvt_e4m3x2_f16x2((uint16_t)(r[0] >> 16)), cvt_e4m3x2_f16x2((uint16_t)(r[1] >> 16))};
-            uint32_t a1[4] = {cvt_e4m3x2_f16x2((uint16_t)(r[2] & 0xffffu)), cvt_e4m3x2_f16x2((uint16_t)(r[3] & 0xffffu)),
-                              cvt_e4m3x2_f16x2((uint16_t)(r[2] >> 16)), cvt_e4m3x2_f16x2((uint16_t)(r[3] >> 16))};
+            uint32_t a0[4], a1[4];
+            cvt_e4m3x4_f16x2x2(r[0], a0[0], a0[2]);
+            cvt_e4m3x4_f16x2x2(r[1], a0[1], a0[3]);
+            cvt_e4m3x4_f16x2x2(r[2], a1[0], a1[2]);
+            cvt_e4m3x4_f16x2x2(r[3], a1[1], a1[3]);
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) {
               mma16816<F16>(sacc[j][nt], a0, qf[nt][2 * kk]);
@@ -634,51 +641,58 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
       }
 
       // ---- O^T += V^T . P^T : rows = head dims, cols = heads -------------------------------
-      uint32_t vmask[2][2];
-      if (partial) {
+      // Two copies of the loop (full tile / last, partial tile of a sequence): with a runtime predicate
+      // ptxas emits the 64 masking LOP3s as predicated instructions that occupy issue slots on every tile.
+      auto pv = [&](auto partial_tag) {
+        constexpr bool kPartial = decltype(partial_tag)::value;
+        uint32_t vmask[2][2];
+        if constexpr (kPartial) {
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const int tl = 16 * j + vtok_lo, th = 16 * j + vtok_hi;
+            vmask[j][0] = (tl < nvalid ? 0x0000ffffu : 0u) | (tl + 1 < nvalid ? 0xffff0000u : 0u);
+            vmask[j][1] = (th < nvalid ? 0x0000ffffu : 0u) | (th + 1 < nvalid ? 0xffff0000u : 0u);
+          }
+        }
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-          const int tl = 16 * j + vtok_lo, th = 16 * j + vtok_hi;
-          vmask[j][0] = (tl < nvalid ? 0x0000ffffu : 0u) | (tl + 1 < nvalid ? 0xffff0000u : 0u);
-          vmask[j][1] = (th < nvalid ? 0x0000ffffu : 0u) | (th + 1 < nvalid ? 0xffff0000u : 0u);
-        }
-      }
+          const uint32_t vb = sb + C::kVOffset + (B == 16 ? j * C::kBlkBytes : j * 16 * C::kElemBytes) + v_lane_off;
+          if constexpr (!FP8) {
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        const uint32_t vb = sb + C::kVOffset + (B == 16 ? j * C::kBlkBytes : j * 16 * C::kElemBytes) + v_lane_off;
-        if constexpr (!FP8) {
+            for (int i = 0; i < 8; ++i) {
+              uint32_t a[4];
+              ldmatrix_x4(a, vb + i * 16 * B * 2);
+              if constexpr (kPartial) {  // stale cache past seq_len may hold NaN/Inf: zero it
+                a[0] &= vmask[j][0]; a[1] &= vmask[j][0];
+                a[2] &= vmask[j][1]; a[3] &= vmask[j][1];
+              }
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            uint32_t a[4];
-            ldmatrix_x4(a, vb + i * 16 * B * 2);
-            if (partial) {  // stale cache past seq_len may hold NaN/Inf: zero it
-              a[0] &= vmask[j][0]; a[1] &= vmask[j][0];
-              a[2] &= vmask[j][1]; a[3] &= vmask[j][1];
+              for (int nt = 0; nt < NT; ++nt) mma16816<F16>(oacc[nt][i], a, pf[j][nt]);
             }
+          } else {
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt) mma16816<F16>(oacc[nt][i], a, pf[j][nt]);
-          }
-        } else {
+            for (int ii = 0; ii < 4; ++ii) {
+              uint32_t r[4];
+              ldmatrix_x4(r, vb + ii * 32 * B);
+              uint32_t a0[4], a1[4];
+              cvt_e4m3x4_f16x2x2(r[0], a0[0], a0[2]);
+              cvt_e4m3x4_f16x2x2(r[1], a0[1], a0[3]);
+              cvt_e4m3x4_f16x2x2(r[2], a1[0], a1[2]);
+              cvt_e4m3x4_f16x2x2(r[3], a1[1], a1[3]);
+              if constexpr (kPartial) {
+                a0[0] &= vmask[j][0]; a0[1] &= vmask[j][0]; a0[2] &= vmask[j][1]; a0[3] &= vmask[j][1];
+                a1[0] &= vmask[j][0]; a1[1] &= vmask[j][0]; a1[2] &= vmask[j][1]; a1[3] &= vmask[j][1];
+              }
 #pragma unroll
-          for (int ii = 0; ii < 4; ++ii) {
-            uint32_t r[4];
-            ldmatrix_x4(r, vb + ii * 32 * B);
-            uint32_t a0[4] = {cvt_e4m3x2_f16x2((uint16_t)(r[0] & 0xffffu)), cvt_e4m3x2_f16x2((uint16_t)(r[1] & 0xffffu)),
-                              cvt_e4m3x2_f16x2((uint16_t)(r[0] >> 16)), cvt_e4m3x2_f16x2((uint16_t)(r[1] >> 16))};
-            uint32_t a1[4] = {cvt_e4m3x2_f16x2((uint16_t)(r[2] & 0xffffu)), cvt_e4m3x2_f16x2((uint16_t)(r[3] & 0xffffu)),
-                              cvt_e4m3x2_f16x2((uint16_t)(r[2] >> 16)), cvt_e4m3x2_f16x2((uint16_t)(r[3] >> 16))};
-            if (partial) {
-              a0[0] &= vmask[j][0]; a0[1] &= vmask[j][0]; a0[2] &= vmask[j][1]; a0[3] &= vmask[j][1];
-              a1[0] &= vmask[j][0]; a1[1] &= vmask[j][0]; a1[2] &= vmask[j][1]; a1[3] &= vmask[j][1];
-            }
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt) {
-              mma16816<F16>(oacc[nt][2 * ii], a0, pf[j][nt]);
-              mma16816<F16>(oacc[nt][2 * ii + 1], a1, pf[j][nt]);
+              for (int nt = 0; nt < NT; ++nt) {
+                mma16816<F16>(oacc[nt][2 * ii], a0, pf[j][nt]);
+                mma16816<F16>(oacc[nt][2 * ii + 1], a1, pf[j][nt]);
+              }
             }
           }
         }
-      }
+      };
+      if (partial) pv(std::true_type{}); else pv(std::false_type{});
       // All lanes have consumed the stage: hand it back to the producer.  The fence is REQUIRED: ptxas
       // issues the mbarrier arrive without waiting for the LDSMs still in flight (it even hoists it above the
       // last HMMAs), and with bank-conflicted V fragments (B = 32 bf16: 64-byte rows, 4-way conflicts) the
@@ -687,6 +701,11 @@ __global__ void __launch_bounds__(kThreads, 1) paged_attention_stream_kernel(con
       __threadfence_block();
       __syncwarp();
       if (lane == 0) mbar_arrive(empty_u32 + 8u * stage);
+      stage += kConsumerWarps;
+      if (stage >= (uint32_t)nst) {
+        stage -= (uint32_t)nst;
+        parity ^= 1u;
+      }
     }
     tile_base += (uint32_t)ntiles;
 
@@ -825,20 +844,21 @@ size_t stream_smem_bytes(int nstages) {
 
 constexpr size_t kMaxSmem = 227 * 1024;
 
-template <int B, bool FP8, int NT, bool FLAT>
-int launch_stream_t(StreamParams& sp, cudaStream_t s) {
+template <int B, bool FP8, int NT, bool FLAT, int NP>
+int launch_stream_np(StreamParams& sp, cudaStream_t s) {
   using C = Cfg<B, FP8>;
-  // deepest ring that fits (capped: beyond ~190 KiB in flight nothing is gained)
-  // (a multiple of the consumer-warp count: see the tile -> warp mapping in the kernel)
+  // ring depth: a multiple of the consumer-warp count (see the tile -> warp mapping in the kernel), capped at
+  // 128 KiB in flight — the random-chunk gather does not get faster beyond that, and with 2 KiB chunks it gets
+  // slower (profiles/r1_gather_read_bench.log, r1_sweep.log: fp8 16 stages 5.67 TB/s vs 24 stages 5.23 TB/s)
   int nst = kConsumerWarps;
   while (stream_smem_bytes<B, FP8, NT>(nst + kConsumerWarps) <= kMaxSmem &&
-         (size_t)(nst + kConsumerWarps) * C::kStageBytes <= 192 * 1024)
+         (size_t)(nst + kConsumerWarps) * C::kStageBytes <= 128 * 1024)
     nst += kConsumerWarps;
   if (const char* e = getenv("B200_STREAM_NSTAGES"))
     nst = max(kConsumerWarps, min(nst, atoi(e) / kConsumerWarps * kConsumerWarps));
   sp.nstages = nst;
   const size_t smem = stream_smem_bytes<B, FP8, NT>(nst);
-  auto kern = paged_attention_stream_kernel<B, FP8, NT, FLAT>;
+  auto kern = paged_attention_stream_kernel<B, FP8, NT, FLAT, NP>;
   static thread_local int configured_device = -1;
   int dev = 0;
   cudaGetDevice(&dev);
@@ -851,9 +871,18 @@ int launch_stream_t(StreamParams& sp, cudaStream_t s) {
     configured_device = dev;
   }
   const int grid = min(min(device_sm_count(), kFlatMaxCtas), sp.total_items);
-  kern<<<grid, kThreads, smem, s>>>(sp);
+  kern<<<grid, (kConsumerWarps + NP) * kWarpSize, smem, s>>>(sp);
   count_launch();
   return check_launch("paged_attention_stream");
+}
+
+// Issuing warps: random 2 KiB chunks (fp8, block_size 16) need 8 issuing warps to reach the gather ceiling,
+// 4 KiB chunks are saturated by 4 (profiles/r1_gather_read_bench.log).
+template <int B, bool FP8, int NT, bool FLAT>
+int launch_stream_t(StreamParams& sp, cudaStream_t s) {
+  int np = (FP8 && B == 16) ? 8 : 4;
+  if (const char* e = getenv("B200_STREAM_NPROD")) np = atoi(e) >= 8 ? 8 : 4;
+  return np == 8 ? launch_stream_np<B, FP8, NT, FLAT, 8>(sp, s) : launch_stream_np<B, FP8, NT, FLAT, 4>(sp, s);
 }
 
 }  // namespace
