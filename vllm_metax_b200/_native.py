@@ -16,7 +16,7 @@ B200_OK = 0
 ERR_INVALID_ARGUMENT, ERR_UNSUPPORTED, ERR_CUDA, ERR_WORKSPACE = 1, 2, 3, 4
 DTYPE_F32, DTYPE_F16, DTYPE_BF16, DTYPE_U8 = 0, 1, 2, 3
 KV_AUTO, KV_FP8_E4M3 = 0, 1
-VARIANT_AUTO, VARIANT_GENERIC, VARIANT_STREAM_MMA = 0, 1, 2
+VARIANT_AUTO, VARIANT_GENERIC, VARIANT_STREAM_MMA, VARIANT_UMMA_FP8 = 0, 1, 2, 3
 PARTITION_SIZE = 512
 
 # every symbol include/b200_paged_attn.h declares

@@ -23,7 +23,7 @@ BUILD = ROOT / "build"
 LIB_ABI = PKG / "libb200_paged_attn.so"
 LIB_SHIM = PKG / "_C.so"
 
-CU_SOURCES = ["api.cu", "cache_kernels.cu", "attention_generic.cu", "attention_stream.cu"]
+CU_SOURCES = ["api.cu", "cache_kernels.cu", "attention_generic.cu", "attention_stream.cu", "attention_umma_fp8.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC",
@@ -53,7 +53,7 @@ def _run(cmd: list[str]) -> None:
 def build_abi(verbose: bool = False) -> Path:
     """nvcc -> libb200_paged_attn.so (sm_100a only)."""
     BUILD.mkdir(exist_ok=True)
-    headers = [CSRC / "common.cuh", ROOT / "include" / "b200_paged_attn.h"]
+    headers = [CSRC / "common.cuh", CSRC / "stream_common.cuh", ROOT / "include" / "b200_paged_attn.h"]
     nvcc = _nvcc()
     jobs = []
     objs = []

@@ -106,6 +106,15 @@ int validate_attn(const b200_paged_attn_params_t* p, bool v2) {
 int pick_variant(const b200_paged_attn_params_t& p) {
   const char* why = nullptr;
   const bool ok = stream_variant_eligible(p, &why);
+  const char* why_u = nullptr;
+  const bool ok_u = umma_fp8_variant_eligible(p, &why_u);
+  if (g_forced_variant == B200_VARIANT_UMMA_FP8) {
+    if (!ok_u) {
+      set_error("tcgen05 fp8 variant forced but not eligible: %s", why_u);
+      return -B200_ERR_UNSUPPORTED;
+    }
+    return B200_VARIANT_UMMA_FP8;
+  }
   if (g_forced_variant == B200_VARIANT_STREAM_MMA) {
     if (!ok) {
       set_error("stream variant forced but not eligible: %s", why);
@@ -114,6 +123,8 @@ int pick_variant(const b200_paged_attn_params_t& p) {
     return B200_VARIANT_STREAM_MMA;
   }
   if (g_forced_variant == B200_VARIANT_GENERIC) return B200_VARIANT_GENERIC;
+  static const bool no_umma = getenv("B200_DISABLE_UMMA") != nullptr;  // developer switch (A/B measurements)
+  if (ok_u && !no_umma) return B200_VARIANT_UMMA_FP8;
   return ok ? B200_VARIANT_STREAM_MMA : B200_VARIANT_GENERIC;
 }
 
@@ -143,13 +154,15 @@ extern "C" int b200_paged_attention_v1(const b200_paged_attn_params_t* p, void* 
   const int variant = pick_variant(*p);
   if (variant < 0) return -variant;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (variant == B200_VARIANT_STREAM_MMA) {
+  if (variant == B200_VARIANT_STREAM_MMA || variant == B200_VARIANT_UMMA_FP8) {
     B200_REQUIRE(p->workspace != nullptr && p->workspace_bytes >= kFlatWorkspaceBytes, B200_ERR_WORKSPACE,
                  "paged_attention_v1 needs %llu bytes of workspace, got %llu", (unsigned long long)kFlatWorkspaceBytes,
                  (unsigned long long)(p->workspace ? p->workspace_bytes : 0));
     B200_REQUIRE(reinterpret_cast<uintptr_t>(p->workspace) % 16 == 0, B200_ERR_WORKSPACE,
                  "workspace must be 16-byte aligned");
-    rc = launch_attention_stream_flat(*p, p->workspace, s);  // one launch: split pairs are merged in the kernel
+    // one launch: split pairs are merged in the kernel
+    rc = variant == B200_VARIANT_UMMA_FP8 ? launch_attention_umma_fp8_flat(*p, p->workspace, s)
+                                          : launch_attention_stream_flat(*p, p->workspace, s);
     if (rc == B200_OK) g_last_variant = variant;
     return rc;
   }
@@ -194,7 +207,9 @@ extern "C" int b200_paged_attention_v2(const b200_paged_attn_params_t* p, void* 
   so.m = p->max_logits;
   so.l = p->exp_sums;
   so.o = p->tmp_out;
-  rc = variant == B200_VARIANT_STREAM_MMA ? launch_attention_stream(*p, so, s) : launch_attention_generic(*p, so, s);
+  rc = variant == B200_VARIANT_UMMA_FP8     ? launch_attention_umma_fp8(*p, so, s)
+       : variant == B200_VARIANT_STREAM_MMA ? launch_attention_stream(*p, so, s)
+                                            : launch_attention_generic(*p, so, s);
   if (rc != B200_OK) return rc;
   g_last_variant = variant;
   return launch_split_reduce(*p, so, s);
@@ -211,7 +226,8 @@ extern "C" const char* b200_last_error(void) { return g_error; }
 extern "C" int b200_abi_version(void) { return B200_PAGED_ATTN_ABI_VERSION; }
 
 extern "C" int b200_set_attention_variant(int variant) {
-  if (variant != B200_VARIANT_AUTO && variant != B200_VARIANT_GENERIC && variant != B200_VARIANT_STREAM_MMA) {
+  if (variant != B200_VARIANT_AUTO && variant != B200_VARIANT_GENERIC && variant != B200_VARIANT_STREAM_MMA &&
+      variant != B200_VARIANT_UMMA_FP8) {
     set_error("unknown attention variant %d", variant);
     return B200_ERR_INVALID_ARGUMENT;
   }

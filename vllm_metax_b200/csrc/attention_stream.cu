@@ -33,297 +33,16 @@
 //    memory once per work item;
 //  * fp8: e4m3 bytes are expanded to f16 in registers (exact), the MMA runs in
 //    f16, k_scale is folded into the logit scale and v_scale into the output.
-#include <float.h>
-#include <stdio.h>
-#include <stdlib.h>
-#include <string.h>
-
-#include <type_traits>
-
-#include "common.cuh"
+#include "stream_common.cuh"
 
 namespace b200 {
 namespace {
-
-constexpr int kD = 128;             // head size served by this kernel
-constexpr int kTileTokens = 32;     // tokens per ring stage
-constexpr int kConsumerWarps = 8;
-// producer warps: 4 (384 threads, up to 168 registers each) or 8 (512 threads, 128 registers: ptxas fits the
-// consumer loop into 128 without spills; setmaxnreg was tried and ptxas does not allocate past the launch bound)
-constexpr int kMergeStride = kD + 4;  // fp32 words per (warp, head) row
-constexpr float kLog2e = 1.4426950408889634f;
-constexpr float kLn2 = 0.6931471805599453f;
-
-struct StreamParams {
-  const __nv_bfloat16* q;
-  const uint8_t* kc;
-  const uint8_t* vc;
-  const int32_t* bt;
-  const int32_t* seq_lens;
-  const float* alibi;
-  const float* k_scale;
-  const float* v_scale;
-  __nv_bfloat16* out;
-  SplitOut so;              // item schedule only
-  float* ws_o;              // flat schedule: slots [cta][2][kFlatMaxGroup][kD] (unnormalised partial outputs)
-  float* ws_m;              //                      [cta][2][kFlatMaxGroup]     (max logit, log2 units)
-  float* ws_l;              //                      [cta][2][kFlatMaxGroup]     (sum exp)
-  int* counters;            //                      [S * Hkv] arrival counters, zero between launches
-  int64_t q_stride;         // elements
-  int64_t kv_block_stride;  // bytes
-  int64_t kv_head_stride;   // bytes
-  int S, H, Hkv, G, max_blocks, nstages, total_items;
-  float scale;
-  int debug_num_blocks;  // B200_DEBUG builds only: bound for block-table entries (0 = unchecked)
-};
-
-// ---- PTX wrappers ------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-#ifdef B200_DEBUG
-__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-// debug build: a wait that gives up after ~2 s, reports who was waiting for what, and traps
-__device__ __noinline__ void mbar_wait_dbg(uint32_t bar, uint32_t parity, int tag, int a, int b) {
-  const long long t0 = clock64();
-  while (!mbar_try(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) {
-      printf("[b200 debug] mbarrier timeout: cta %d warp %d lane %d tag %d a %d b %d bar 0x%x parity %u\n",
-             (int)blockIdx.x, (int)(threadIdx.x >> 5), (int)(threadIdx.x & 31), tag, a, b, bar, parity);
-      __trap();
-    }
-  }
-}
-#define MBAR_WAIT(bar, parity, tag, a, b) mbar_wait_dbg(bar, parity, tag, a, b)
-#else
-#define MBAR_WAIT(bar, parity, tag, a, b) mbar_wait(bar, parity)
-#endif
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\n"
-      "bra WAIT_%=;\n"
-      "DONE_%=:\n"
-      "}\n" ::"r"(bar),
-      "r"(parity)
-      : "memory");
-}
-// 1-D TMA bulk copy global -> shared, completion counted on an mbarrier.
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile(
-      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-      "l"(src), "r"(bytes), "r"(bar)
-      : "memory");
-}
-__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
-               : "r"(addr));
-}
-__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
-  uint32_t d;
-  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
-  return d;
-}
-template <bool F16>
-__device__ __forceinline__ void mma16816(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
-  if constexpr (F16) {
-    asm volatile(
-        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
-        "{%0,%1,%2,%3};"
-        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
-  } else {
-    asm volatile(
-        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, "
-        "{%0,%1,%2,%3};"
-        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
-  }
-}
-// four e4m3 bytes -> two f16x2 (bytes 0,1 and bytes 2,3); the 16-bit halves are named in PTX so that ptxas
-// uses the .H1 operand selector instead of masking / shifting them out with LOP3
-__device__ __forceinline__ void cvt_e4m3x4_f16x2x2(uint32_t r, uint32_t& lo, uint32_t& hi) {
-  asm("{\n.reg .b16 l, h;\nmov.b32 {l, h}, %2;\ncvt.rn.f16x2.e4m3x2 %0, l;\ncvt.rn.f16x2.e4m3x2 %1, h;\n}"
-      : "=r"(lo), "=r"(hi)
-      : "r"(r));
-}
-template <bool F16>
-__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
-  uint32_t d;
-  if constexpr (F16) {
-    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
-  } else {
-    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
-  }
-  return d;
-}
-__device__ __forceinline__ float fast_exp2(float x) {  // ex2.approx: 2 ulp, exp2(-inf) = 0
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ void consumer_bar_sync() {
-  asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * kWarpSize) : "memory");
-}
-
-// ---- work decomposition ----------------------------------------------------------
-// A segment is a run of whole tiles of one (seq, kv head) pair processed by one CTA.
-struct Seg {
-  int s, kvh, t0, t1, L, part;
-  bool starts, ends;   // flat: the segment contains the first / last tile of its pair
-  long long pb;        // flat: position of the pair's first tile in the flat tile sequence
-  int n;               // flat: tiles of the pair
-};
-// flat schedule of this CTA, computed once by warp 0 (shared memory)
-struct Sched {
-  long long f0, f1;    // this CTA's tile range
-  long long base0;     // flat position of the first tile of sequence s0
-  long long T;         // tiles in the batch
-  int s0;              // sequence holding tile f0
-  int neff;            // CTAs that own a non-empty range = min(gridDim.x, T)
-};
-__device__ __forceinline__ int tiles_of(int L) { return L > 0 ? (L + kTileTokens - 1) / kTileTokens : 0; }
-__device__ __forceinline__ long long warp_sum_ll(long long v) {
-#pragma unroll
-  for (int m = 16; m >= 1; m >>= 1) v += __shfl_xor_sync(0xffffffffu, v, m);
-  return v;
-}
-// CTA that owns flat tile x when T tiles are cut into n ranges [c*T/n, (c+1)*T/n)
-__device__ __forceinline__ int cta_of_tile(long long x, long long T, int n) {
-  return (int)(((x + 1) * n - 1) / T);
-}
-__device__ void compute_sched(const StreamParams& p, Sched* sc, int lane) {
-  long long tot = 0;
-  for (int i = lane; i < p.S; i += 32) tot += tiles_of(__ldg(p.seq_lens + i));
-  tot = warp_sum_ll(tot);
-  const long long T = tot * p.Hkv;
-  const int neff = (int)(T < (long long)gridDim.x ? T : (long long)gridDim.x);
-  long long f0 = 0, f1 = 0;
-  if ((int)blockIdx.x < neff) {
-    f0 = (long long)blockIdx.x * T / neff;
-    f1 = (long long)(blockIdx.x + 1) * T / neff;
-  }
-  if (lane == 0) {
-    sc->f0 = f0; sc->f1 = f1; sc->T = T; sc->neff = neff; sc->s0 = 0; sc->base0 = 0;
-  }
-  if (f0 >= f1) return;
-  long long running = 0;  // tiles per kv head before sequence `b`
-  for (int b = 0; b < p.S; b += 32) {
-    const int n = b + lane < p.S ? tiles_of(__ldg(p.seq_lens + b + lane)) : 0;
-    long long incl = n;
-#pragma unroll
-    for (int m = 1; m < 32; m <<= 1) {
-      const long long o = __shfl_up_sync(0xffffffffu, incl, m);
-      if (lane >= m) incl += o;
-    }
-    const long long lo = (running + incl - n) * p.Hkv, hi = (running + incl) * p.Hkv;
-    const bool hit = n > 0 && lo <= f0 && f0 < hi;
-    const unsigned ball = __ballot_sync(0xffffffffu, hit);
-    if (ball) {
-      if (hit) {
-        sc->s0 = b + lane;
-        sc->base0 = lo;
-      }
-      return;
-    }
-    running += __shfl_sync(0xffffffffu, incl, 31);
-  }
-}
-
-template <bool FLAT>
-struct WorkIter {
-  long long f, f1, base;
-  int s, n, L, item;
-  __device__ __forceinline__ void init(const StreamParams& p, const Sched* sc) {
-    if constexpr (FLAT) {
-      f = sc->f0; f1 = sc->f1; base = sc->base0; s = sc->s0;
-      L = 0; n = 0;
-      if (f < f1) {
-        L = __ldg(p.seq_lens + s);
-        n = tiles_of(L);
-      }
-    } else {
-      item = (int)blockIdx.x - (int)gridDim.x;
-    }
-  }
-  __device__ __forceinline__ bool next(const StreamParams& p, Seg& g) {
-    if constexpr (FLAT) {
-      if (f >= f1) return false;
-      while (f >= base + (long long)p.Hkv * n) {  // f < f1 <= T: a later sequence holds tile f
-        base += (long long)p.Hkv * n;
-        ++s;
-        L = __ldg(p.seq_lens + s);
-        n = tiles_of(L);
-      }
-      const long long r = f - base;
-      const int kvh = (int)(r / n);
-      const int tile0 = (int)(r - (long long)kvh * n);
-      const long long pb = base + (long long)kvh * n, pe = pb + n;
-      const long long se = pe < f1 ? pe : f1;
-      const int tile1 = tile0 + (int)(se - f);
-      g.s = s; g.kvh = kvh; g.L = L; g.part = 0;
-      g.t0 = tile0 * kTileTokens;
-      g.t1 = min(tile1 * kTileTokens, L);
-      g.starts = tile0 == 0; g.ends = se == pe; g.pb = pb; g.n = n;
-      f = se;
-      return true;
-    } else {
-      const int SH = p.S * p.Hkv;
-      for (;;) {
-        item += (int)gridDim.x;
-        if (item >= p.total_items) return false;
-        g.part = item / SH;
-        const int r = item - g.part * SH;
-        g.s = r / p.Hkv;
-        g.kvh = r - g.s * p.Hkv;
-        g.L = __ldg(p.seq_lens + g.s);
-        g.t0 = g.part * p.so.chunk;
-        if (g.t0 >= g.L) continue;
-        g.t1 = min(g.t0 + p.so.chunk, g.L);
-        g.starts = g.ends = false; g.pb = 0; g.n = 0;
-        return true;
-      }
-    }
-  }
-};
-
-template <int B, bool FP8>
-struct Cfg {
-  static constexpr int kElemBytes = FP8 ? 1 : 2;
-  static constexpr int kBlkBytes = kD * B * kElemBytes;  // one K (or V) chunk of a block
-  static constexpr int kBlocksPerTile = kTileTokens / B;
-  static constexpr int kStageBytes = 2 * kBlocksPerTile * kBlkBytes;
-  static constexpr int kVOffset = kBlocksPerTile * kBlkBytes;  // V chunks follow the K chunks
-};
 
 // ---- the kernel ------------------------------------------------------------------
 template <int B, bool FP8, int NT, bool FLAT, int NP>
 __global__ void __launch_bounds__((kConsumerWarps + NP) * kWarpSize, 1)
 paged_attention_stream_kernel(const StreamParams p) {
   using C = Cfg<B, FP8>;
-  constexpr int kProducerWarps = NP;
   static_assert(NP == 4 || NP == 8, "whole warpgroups of producers");
   constexpr bool F16 = FP8;  // MMA operand type: f16 for fp8 caches, bf16 otherwise
   constexpr int NH = 8 * NT;  // padded heads per kv head
@@ -361,66 +80,7 @@ paged_attention_stream_kernel(const StreamParams p) {
     // lane walks the block table and issues the bulk copies (a single issuing thread costs ~1000
     // cycles per tile, so four of them share the stream).
     if (lane != 0) return;
-    const int pw = warp - kConsumerWarps;
-    uint32_t g_next = (uint32_t)pw;   // next tile of the stream this warp issues
-    int stage = pw;                   // g_next % nst (nst >= kProducerWarps)
-    uint32_t phase = 0;               // (g_next / nst) & 1
-    uint32_t tile_base = 0;
-    WorkIter<FLAT> wi;
-    wi.init(p, sched);
-    Seg it;
-    int item = -1;  // segment ordinal (debug messages)
-    while (wi.next(p, it)) {
-      ++item;
-      const int nblk = (it.t1 - it.t0 + B - 1) / B;
-      const uint32_t ntiles = (uint32_t)((it.t1 - it.t0 + kTileTokens - 1) / kTileTokens);
-      const int32_t* bt = p.bt + (int64_t)it.s * p.max_blocks + it.t0 / B;
-      const uint8_t* kbase = p.kc + (int64_t)it.kvh * p.kv_head_stride;
-      const uint8_t* vbase = p.vc + (int64_t)it.kvh * p.kv_head_stride;
-      const uint32_t tile_end = tile_base + ntiles;
-      // block ids of the next tile are fetched one step ahead
-      int nid0 = 0, nid1 = 0;
-      if (g_next < tile_end) {
-        const int b0 = (int)(g_next - tile_base) * C::kBlocksPerTile;
-        nid0 = __ldg(bt + b0);
-        if (C::kBlocksPerTile == 2 && b0 + 1 < nblk) nid1 = __ldg(bt + b0 + 1);
-      }
-      while (g_next < tile_end) {
-        const int b0 = (int)(g_next - tile_base) * C::kBlocksPerTile;
-        const int id0 = nid0, id1 = nid1;
-        const int nvalid = min(C::kBlocksPerTile, nblk - b0);
-        const int bn = b0 + kProducerWarps * C::kBlocksPerTile;
-        if (bn < nblk) {
-          nid0 = __ldg(bt + bn);
-          if (C::kBlocksPerTile == 2 && bn + 1 < nblk) nid1 = __ldg(bt + bn + 1);
-        }
-#ifdef B200_DEBUG
-        if (p.debug_num_blocks > 0 && ((unsigned)id0 >= (unsigned)p.debug_num_blocks ||
-                                       (nvalid == 2 && (unsigned)id1 >= (unsigned)p.debug_num_blocks))) {
-          printf("[b200 debug] bad block id: cta %d item %d s %d part %d b0 %d id0 %d id1 %d nblk %d\n",
-                 (int)blockIdx.x, item, it.s, it.part, b0, id0, id1, nblk);
-          __trap();
-        }
-#endif
-        MBAR_WAIT(empty_u32 + 8u * stage, phase ^ 1u, 1, item, stage);
-        const uint32_t fb = full_u32 + 8u * stage;
-        mbar_expect_tx(fb, (uint32_t)(nvalid * 2 * C::kBlkBytes));
-        const uint32_t dst = ring_u32 + (uint32_t)stage * C::kStageBytes;
-        bulk_g2s(dst, kbase + (int64_t)id0 * p.kv_block_stride, C::kBlkBytes, fb);
-        bulk_g2s(dst + C::kVOffset, vbase + (int64_t)id0 * p.kv_block_stride, C::kBlkBytes, fb);
-        if (C::kBlocksPerTile == 2 && nvalid == 2) {
-          bulk_g2s(dst + C::kBlkBytes, kbase + (int64_t)id1 * p.kv_block_stride, C::kBlkBytes, fb);
-          bulk_g2s(dst + C::kVOffset + C::kBlkBytes, vbase + (int64_t)id1 * p.kv_block_stride, C::kBlkBytes, fb);
-        }
-        g_next += kProducerWarps;
-        stage += kProducerWarps;
-        if (stage >= nst) {
-          stage -= nst;
-          phase ^= 1u;
-        }
-      }
-      tile_base = tile_end;
-    }
+    producer_loop<B, FP8, FLAT, NP>(p, sched, warp - kConsumerWarps, ring_u32, full_u32, empty_u32, nst);
     return;
   }
 
@@ -880,9 +540,13 @@ int launch_stream_np(StreamParams& sp, cudaStream_t s) {
 // 4 KiB chunks are saturated by 4 (profiles/r1_gather_read_bench.log).
 template <int B, bool FP8, int NT, bool FLAT>
 int launch_stream_t(StreamParams& sp, cudaStream_t s) {
-  int np = (FP8 && B == 16) ? 8 : 4;
-  if (const char* e = getenv("B200_STREAM_NPROD")) np = atoi(e) >= 8 ? 8 : 4;
-  return np == 8 ? launch_stream_np<B, FP8, NT, FLAT, 8>(sp, s) : launch_stream_np<B, FP8, NT, FLAT, 4>(sp, s);
+  // 8 producer warps leave 128 registers per thread: enough for one head tile (NT = 1), spills with two
+  if constexpr (FP8 && NT == 1) {
+    int np = B == 16 ? 8 : 4;
+    if (const char* e = getenv("B200_STREAM_NPROD")) np = atoi(e) >= 8 ? 8 : 4;
+    if (np == 8) return launch_stream_np<B, FP8, NT, FLAT, 8>(sp, s);
+  }
+  return launch_stream_np<B, FP8, NT, FLAT, 4>(sp, s);
 }
 
 }  // namespace
@@ -904,26 +568,6 @@ bool stream_variant_eligible(const b200_paged_attn_params_t& p, const char** why
 }
 
 namespace {
-StreamParams fill_stream_params(const b200_paged_attn_params_t& p) {
-  const int eb = p.kv_dtype == B200_KV_FP8_E4M3 ? 1 : 2;
-  StreamParams sp;
-  memset(&sp, 0, sizeof(sp));
-  sp.q = static_cast<const __nv_bfloat16*>(p.query);
-  sp.kc = static_cast<const uint8_t*>(p.key_cache);
-  sp.vc = static_cast<const uint8_t*>(p.value_cache);
-  sp.bt = p.block_tables; sp.seq_lens = p.seq_lens; sp.alibi = p.alibi_slopes;
-  sp.k_scale = p.k_scale; sp.v_scale = p.v_scale;
-  sp.out = static_cast<__nv_bfloat16*>(p.out);
-  sp.q_stride = p.q_stride;
-  sp.kv_block_stride = p.kv_block_stride * eb;
-  sp.kv_head_stride = p.kv_head_stride * eb;
-  sp.S = p.num_seqs; sp.H = p.num_heads; sp.Hkv = p.num_kv_heads; sp.G = p.num_heads / p.num_kv_heads;
-  sp.max_blocks = p.max_num_blocks_per_seq;
-  sp.scale = p.scale;
-  if (const char* e = getenv("B200_DEBUG_NUM_BLOCKS")) sp.debug_num_blocks = atoi(e);
-  return sp;
-}
-
 template <bool FLAT>
 int dispatch_stream(const b200_paged_attn_params_t& p, StreamParams& sp, cudaStream_t s) {
   const bool fp8 = p.kv_dtype == B200_KV_FP8_E4M3;
