@@ -67,7 +67,7 @@ typedef enum b200_kv_dtype {
 
 /* Which kernel family served the last attention call (for tests / bench). */
 typedef enum b200_attn_variant {
-  B200_VARIANT_AUTO = 0,      /* choose: tcgen05 fp8, else stream-MMA when eligible, else generic */
+  B200_VARIANT_AUTO = 0,      /* choose: stream-MMA when eligible, else generic (tcgen05 fp8: opt-in)  */
   B200_VARIANT_GENERIC = 1,   /* FMA kernel, any supported shape                */
   B200_VARIANT_STREAM_MMA = 2,/* TMA ring + mma.sync persistent kernel          */
   B200_VARIANT_UMMA_FP8 = 3   /* TMA ring + tcgen05.mma (fp8 cache, block 16, GQA group <= 8) */

@@ -80,7 +80,7 @@ def test_reference_grid(ops, version, num_heads, head_size, use_alibi, block_siz
 @pytest.mark.parametrize("G,Hkv", [(1, 32), (4, 8), (8, 8), (2, 4), (16, 2), (5, 2)])
 @pytest.mark.parametrize("block_size", [16, 32])
 def test_stream_variant_shapes(ops, version, kv_cache_dtype, G, Hkv, block_size):
-    """D=128 bf16 shapes served by the TMA + mma.sync streaming kernel (GQA 1..16)."""
+    """D=128 bf16 shapes served by the streaming kernels: TMA ring + mma.sync (GQA 1..16), TMA ring + tcgen05 (fp8)."""
     from vllm_metax_b200 import _native
 
     d = orc.make_decode_inputs(5, G * Hkv, Hkv, 128, block_size, max_seq_len=1300, num_blocks=2048,
@@ -88,6 +88,22 @@ def test_stream_variant_shapes(ops, version, kv_cache_dtype, G, Hkv, block_size)
     out, _ = _run(ops, version, d)
     assert _native.last_attention_variant() == _native.VARIANT_STREAM_MMA
     _check(out, _oracle(d), ATOL_AUTO if kv_cache_dtype == "auto" else ATOL_BAR)
+    if kv_cache_dtype == "fp8" and block_size == 16 and G <= 8:  # shapes the opt-in tcgen05 kernel serves too
+        out2, _ = _run_umma(ops, version, d)
+        _check(out2, _oracle(d), ATOL_BAR)
+
+
+def _run_umma(ops, version, d):
+    """Run with the tcgen05 fp8 kernel forced (it is opt-in: the mma.sync kernel is the default)."""
+    from vllm_metax_b200 import _native
+
+    _native.set_attention_variant(_native.VARIANT_UMMA_FP8)
+    try:
+        r = _run(ops, version, d)
+        assert _native.last_attention_variant() == _native.VARIANT_UMMA_FP8
+    finally:
+        _native.set_attention_variant(_native.VARIANT_AUTO)
+    return r
 
 
 @pytest.mark.parametrize("version", ["v1", "v2"])
@@ -281,3 +297,61 @@ def test_streaming_kernel_is_deterministic(ops, version, H, Hkv, block_size, kv_
     for _ in range(60):
         again, _ = _run(ops, version, d)
         assert torch.equal(again, first)
+
+
+# ---- tcgen05 fp8 kernel: cases aimed at its own machinery -------------------------------------------------
+@pytest.mark.parametrize("version", ["v1", "v2"])
+@pytest.mark.parametrize("G,Hkv", [(4, 8), (8, 1), (1, 4), (3, 2)])
+@pytest.mark.parametrize("k_scale,v_scale", [(1.0, 1.0), (0.037, 0.21), (2.5, 0.5)])
+def test_umma_fp8_scales_and_dynamic_range(ops, version, G, Hkv, k_scale, v_scale):
+    """Non-unit scales; k_scale 2.5 on full-range e4m3 keys gives logits spread over tens of units, so the classes
+    re-reference (rescale their TMEM accumulators) many times."""
+    from vllm_metax_b200 import _native
+
+    d = orc.make_decode_inputs(4, G * Hkv, Hkv, 128, 16, max_seq_len=2500, num_blocks=1024, kv_cache_dtype="fp8", seed=21)
+    g = torch.Generator().manual_seed(5)
+    d["key_cache"] = torch.randint(0, 0x7f, d["key_cache"].shape, generator=g, dtype=torch.uint8) | (
+        torch.randint(0, 2, d["key_cache"].shape, generator=g, dtype=torch.uint8) << 7)
+    d["key_cache"][(d["key_cache"] & 0x7f) > 0x50] &= 0xcf  # keep |k| <= 8: logits stay finite in every implementation
+    d["query"] = (torch.randn(d["query"].shape, generator=g) * 0.7).to(torch.bfloat16)
+    d["k_scale"], d["v_scale"] = k_scale, v_scale
+    out, _ = _run_umma(ops, version, d)
+    _check(out, _oracle(d), ATOL_BAR)
+
+
+@pytest.mark.parametrize("version", ["v1", "v2"])
+def test_umma_fp8_rising_logits_alibi(ops, version):
+    """ALiBi with large slopes makes the logits grow monotonically along the sequence: worst case for the lazy reference."""
+    from vllm_metax_b200 import _native
+
+    d = orc.make_decode_inputs(3, 16, 4, 128, 16, max_seq_len=1777, num_blocks=512, kv_cache_dtype="fp8", seed=8, use_alibi=True)
+    d["alibi_slopes"] = torch.linspace(0.01, 0.6, 16)
+    out, _ = _run_umma(ops, version, d)
+    _check(out, _oracle(d), ATOL_BAR)
+
+
+@pytest.mark.parametrize("version", ["v1", "v2"])
+def test_umma_fp8_stale_tail_nan_bytes(ops, version):
+    """e4m3 NaN bytes (0x7f / 0xff) past seq_len in the last block, and in the ring's second block slot, must not leak."""
+    from vllm_metax_b200 import _native
+
+    d = orc.make_decode_inputs(5, 32, 8, 128, 16, max_seq_len=333, num_blocks=256, kv_cache_dtype="fp8", seed=9, unique_blocks=True)
+    ref = _oracle(d)
+    kc, vc = d["key_cache"].clone(), d["value_cache"].clone()
+    for s in range(5):
+        L = int(d["seq_lens"][s])
+        blk = int(d["block_tables"][s, (L - 1) // 16])
+        off = L % 16
+        if off:
+            kc[blk, :, :, off:, :] = 0x7f
+            vc[blk, :, :, off:] = 0xff
+    out, _ = _run_umma(ops, version, dict(d, key_cache=kc, value_cache=vc))
+    _check(out, ref, ATOL_BAR)
+
+
+def test_umma_fp8_deterministic(ops):
+    d = orc.make_decode_inputs(64, 32, 8, 128, 16, max_seq_len=1500, num_blocks=8192, kv_cache_dtype="fp8", seed=4, unique_blocks=True)
+    a, _ = _run_umma(ops, "v1", d)
+    for _ in range(5):
+        b, _ = _run_umma(ops, "v1", d)
+        assert torch.equal(a, b)

@@ -64,7 +64,7 @@ constexpr int kVBytes = 4096;       // two V chunks
 // out_s [128 lanes][16], out_o [128 lanes][128]; cycles[0] = cycles for `reps` batches of 16 small + 2 big MMAs
 __global__ void __launch_bounds__(128, 1)
 probe(const uint8_t* q, const uint8_t* p, const uint8_t* k, const uint8_t* v, float* out_s, float* out_o,
-      long long* cycles, int reps, int sbo_a) {
+      long long* cycles, int reps, int sbo_a, float* out_s2) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sq = smem;
   uint8_t* sp = sq + kQBytes;
@@ -113,6 +113,16 @@ probe(const uint8_t* q, const uint8_t* p, const uint8_t* k, const uint8_t* v, fl
       tmem_ld16(tmem + lane_base + 128 + c, r);
       for (int i = 0; i < 16; ++i) out_o[(warp * 32 + lane) * 128 + c + i] = __uint_as_float(r[i]);
     }
+  }
+  {
+    // 16x256b.x2: 16 TMEM lanes x 16 columns spread over the 32 threads like an m16n8 accumulator fragment
+    uint32_t r[8];
+    const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
+    asm volatile("tcgen05.ld.sync.aligned.16x256b.x2.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(tmem + lane_base + 0));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    for (int i = 0; i < 8; ++i) out_s2[(warp * 32 + lane) * 8 + i] = __uint_as_float(r[i]);
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -189,6 +199,92 @@ __global__ void __launch_bounds__(128, 1) time_shape(long long* cycles, int reps
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
 }
 
+// ---- cost of the Q.K^T pattern: 8 MMAs (M64 N16 K32) per tile over 4 A operands (k-steps) and 2 B blocks ----
+//   MODE 0: block-major  (A changes on every MMA)          MODE 1: k-step-major (each A used twice in a row)
+//   MODE 2: k-step-major with collector::a::fill / lastuse MODE 3: two tiles batched, each A used 4x in a row (fill/use/lastuse)
+#define UMMA_F8_COLL(QUAL)                                                                                           \
+  asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f8f6f4" QUAL                \
+               " [%0], %1, %2, %3, p;\n}\n" ::"r"(d), "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory")
+__device__ __forceinline__ void umma_fill(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) { UMMA_F8_COLL(".collector::a::fill"); }
+__device__ __forceinline__ void umma_use(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) { UMMA_F8_COLL(".collector::a::use"); }
+__device__ __forceinline__ void umma_last(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) { UMMA_F8_COLL(".collector::a::lastuse"); }
+template <int MODE>
+__global__ void __launch_bounds__(128, 1) time_qk(long long* cycles, int reps) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 64 * 1024);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 2);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < 16 * 1024; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x38383838u;
+  if (tid == 0) {
+    mbar_init(smem_u32(bar), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *tmem_slot;
+  if (warp == 0) {
+    constexpr uint32_t idesc = (1u << 4) | ((uint32_t)(16 >> 3) << 17) | ((uint32_t)(64 >> 4) << 24);
+    const uint32_t qa = smem_u32(smem), ka = smem_u32(smem) + 8192;  // Q operand 8 KiB, then K blocks of 2 KiB
+    const long long t0 = clock64();
+    for (int it = 0; it < reps; ++it) {
+      const uint32_t kt = ka + (uint32_t)(it & 7) * 4096;  // a different ring stage every tile
+      if (elect_one()) {
+        if (MODE == 0) {
+          for (int j = 0; j < 2; ++j)
+            for (int kk = 0; kk < 4; ++kk)
+              umma_f8(tmem + 16 * j, make_desc(qa + kk * 2048, 1024, 128), make_desc(kt + j * 2048 + kk * 512, 256, 128), idesc, kk > 0);
+        } else if (MODE == 1) {
+          for (int kk = 0; kk < 4; ++kk)
+            for (int j = 0; j < 2; ++j)
+              umma_f8(tmem + 16 * j, make_desc(qa + kk * 2048, 1024, 128), make_desc(kt + j * 2048 + kk * 512, 256, 128), idesc, kk > 0);
+        } else if (MODE == 2) {
+          for (int kk = 0; kk < 4; ++kk) {
+            umma_fill(tmem, make_desc(qa + kk * 2048, 1024, 128), make_desc(kt + kk * 512, 256, 128), idesc, kk > 0);
+            umma_last(tmem + 16, make_desc(qa + kk * 2048, 1024, 128), make_desc(kt + 2048 + kk * 512, 256, 128), idesc, kk > 0);
+          }
+        } else {
+          // two tiles (4 blocks) per batch: counted as 2 tiles below
+          for (int kk = 0; kk < 4; ++kk) {
+            umma_fill(tmem, make_desc(qa + kk * 2048, 1024, 128), make_desc(kt + kk * 512, 256, 128), idesc, kk > 0);
+            umma_use(tmem + 16, make_desc(qa + kk * 2048, 1024, 128), make_desc(kt + 2048 + kk * 512, 256, 128), idesc, kk > 0);
+            umma_use(tmem + 32, make_desc(qa + kk * 2048, 1024, 128), make_desc(kt + 4096 + kk * 512, 256, 128), idesc, kk > 0);
+            umma_last(tmem + 48, make_desc(qa + kk * 2048, 1024, 128), make_desc(kt + 6144 + kk * 512, 256, 128), idesc, kk > 0);
+          }
+        }
+      }
+      __syncwarp();
+    }
+    const long long t1 = clock64();
+    if (elect_one()) umma_commit(smem_u32(bar));
+    mbar_wait(smem_u32(bar), 0);
+    const long long t2 = clock64();
+    if (tid == 0) {
+      cycles[0] = t1 - t0;
+      cycles[1] = t2 - t0;
+    }
+  }
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+}
+template <int MODE>
+void run_qk(long long* dc) {
+  const int reps = 2000;
+  cudaFuncSetAttribute(time_qk<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024 + 64);
+  time_qk<MODE><<<1, 128, 64 * 1024 + 64>>>(dc, reps);
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) { printf("time_qk<%d>: %s\n", MODE, cudaGetErrorString(e)); exit(1); }
+  long long cyc[2];
+  cudaMemcpy(cyc, dc, 16, cudaMemcpyDeviceToHost);
+  const int tiles = MODE == 3 ? 2 * reps : reps;
+  printf("Q.K^T pattern mode %d: issue %.1f cycles/tile, complete %.1f cycles/tile\n", MODE, (double)cyc[0] / tiles, (double)cyc[1] / tiles);
+}
+
 template <int M, int N, int CHAINED>
 void run_shape(long long* dc) {
   const int reps = 1000;
@@ -235,6 +331,8 @@ int main() {
   long long* dc;
   cudaMalloc(&dq, kQBytes); cudaMalloc(&dp, kPBytes); cudaMalloc(&dk, kKBytes); cudaMalloc(&dv, kVBytes);
   cudaMalloc(&ds, 128 * 16 * 4); cudaMalloc(&dout, 128 * 128 * 4); cudaMalloc(&dc, 16);
+  float* ds2;
+  cudaMalloc(&ds2, 128 * 8 * 4);
   cudaMemcpy(dq, sq.data(), kQBytes, cudaMemcpyHostToDevice);
   cudaMemcpy(dp, sp.data(), kPBytes, cudaMemcpyHostToDevice);
   cudaMemcpy(dk, sk.data(), kKBytes, cudaMemcpyHostToDevice);
@@ -245,7 +343,7 @@ int main() {
     cudaMemset(ds, 0xff, 128 * 16 * 4);
     cudaMemset(dout, 0xff, 128 * 128 * 4);
     const int reps = 2000;
-    probe<<<1, 128, smem>>>(dq, dp, dk, dv, ds, dout, dc, reps, sbo_a);
+    probe<<<1, 128, smem>>>(dq, dp, dk, dv, ds, dout, dc, reps, sbo_a, ds2);
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) {
       printf("sbo_a=%d: CUDA error %s\n", sbo_a, cudaGetErrorString(e));
@@ -272,11 +370,25 @@ int main() {
         max_o = fmax(max_o, fabs(ref - O[lane * 128 + d]));
       }
     }
+    {
+      // expected 16x256b.x2 layout: thread t of warp w, register 4j+2a+b = S[lane 32w + t/4 + 8a][col 8j + 2(t%4) + b]
+      std::vector<float> S2(128 * 8);
+      cudaMemcpy(S2.data(), ds2, S2.size() * 4, cudaMemcpyDeviceToHost);
+      int mism = 0;
+      for (int w = 0; w < 4; ++w)
+        for (int t = 0; t < 32; ++t)
+          for (int j = 0; j < 2; ++j)
+            for (int a = 0; a < 2; ++a)
+              for (int b = 0; b < 2; ++b)
+                if (S2[(w * 32 + t) * 8 + 4 * j + 2 * a + b] != S[(w * 32 + t / 4 + 8 * a) * 16 + 8 * j + 2 * (t % 4) + b]) ++mism;
+      printf("16x256b.x2 fragment layout mismatches: %d of 1024\n", mism);
+    }
     for (int l = 0; l < 128; ++l)
       if (l % 32 >= 16 && !isnan(S[l * 16])) ++bad_lane;  // lanes 16-31 of each quadrant must be untouched (0xff.. = NaN)
     printf("sbo_a=%3d: max|S-ref| %.3e  max|O-ref| %.3e  touched upper-half lanes %d  | %d x (16 small + 2 big MMA): issue %.1f cyc/batch, complete %.1f cyc/batch\n",
            sbo_a, max_s, max_o, bad_lane, reps, (double)cyc[0] / reps, (double)cyc[1] / reps);
   }
+  run_qk<0>(dc); run_qk<1>(dc); run_qk<2>(dc); run_qk<3>(dc);
   // ---- shape sweep ----
   printf("%5s %5s %8s %10s %12s\n", "M", "N", "chained", "issue/MMA", "complete/MMA");
   run_shape<64, 16, 0>(dc); run_shape<64, 16, 1>(dc);

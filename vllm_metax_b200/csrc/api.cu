@@ -123,8 +123,11 @@ int pick_variant(const b200_paged_attn_params_t& p) {
     return B200_VARIANT_STREAM_MMA;
   }
   if (g_forced_variant == B200_VARIANT_GENERIC) return B200_VARIANT_GENERIC;
-  static const bool no_umma = getenv("B200_DISABLE_UMMA") != nullptr;  // developer switch (A/B measurements)
-  if (ok_u && !no_umma) return B200_VARIANT_UMMA_FP8;
+  // The tcgen05 fp8 kernel is parity-green but its tensor pipe is the bottleneck (8 M64 N16 K32 MMAs per 32-token tile,
+  // 78 % tensor-active at 3.2 TB/s; profiles/README.md), so the mma.sync kernel (5.8 TB/s) stays the default for fp8.
+  // Opt in with B200_ENABLE_UMMA=1 or b200_set_attention_variant(B200_VARIANT_UMMA_FP8).
+  static const bool use_umma = getenv("B200_ENABLE_UMMA") != nullptr;
+  if (ok_u && use_umma) return B200_VARIANT_UMMA_FP8;
   return ok ? B200_VARIANT_STREAM_MMA : B200_VARIANT_GENERIC;
 }
 

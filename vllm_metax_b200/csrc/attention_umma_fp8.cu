@@ -16,14 +16,14 @@
 // (hi = rn_e4m3(x), lo = rn_e4m3((x - hi) * 16)), stacked along M: accumulator row h holds the hi product, row 8+h
 // the lo product, recombined in fp32.  Relative error <= 2^-9 per element (bf16 itself is 2^-9), K and V are exact.
 //
-// Warp roles (416 threads, one CTA per SM, persistent):
+// Warp roles (448 threads, one CTA per SM, persistent):
 //   warps 0-3   "class" warps.  M = 64 accumulators occupy TMEM lanes 32q..32q+15 (q = 0..3); the Q operand is
 //               replicated in all four 16-row groups, so every quadrant q sees the full S tile and class warp q owns
 //               the tiles gt == q (mod 4): softmax with its own running reference, P written to its own P buffer
 //               (rows of the other quadrants stay zero, so P.V adds nothing to their accumulator lanes).
-//   warp 4      MMA issuer (one elected lane): S = Q.K^T per block (8 x M64 N16 K32), O += P.V (M64 N128 K32), three
-//               tiles behind; tcgen05.commit hands ring stages back to the producers.
-//   warps 5-12  producers: block-table walk + 1-D TMA bulk copies into the ring (stream_common.cuh).
+//   warp 4      Q.K^T issuer (one elected lane): S = Q.K^T per block (8 x M64 N16 K32 per tile)
+//   warp 5      P.V issuer: O += P.V (M64 N128 K32 per tile); tcgen05.commit hands ring stages back to the producers
+//   warps 6-13  producers: block-table walk + 1-D TMA bulk copies into the ring (stream_common.cuh).
 // The four class partials of a (seq, kv head) segment are merged through shared memory at its end (exact: each class
 // keeps its true running max), then finished exactly like attention_stream.cu (flat arrival counters / v2 partials).
 #include "stream_common.cuh"
@@ -33,9 +33,10 @@ namespace {
 
 constexpr int kUB = 16;                // block size served
 constexpr int kClassWarps = 4;
-constexpr int kMmaWarp = kClassWarps;  // warp index of the MMA issuer
+constexpr int kQkWarp = kClassWarps;      // warp issuing S = Q.K^T
+constexpr int kPvWarp = kClassWarps + 1;  // warp issuing O += P.V
 constexpr int kUProducers = 8;
-constexpr int kUThreads = (kClassWarps + 1 + kUProducers) * kWarpSize;
+constexpr int kUThreads = (kClassWarps + 2 + kUProducers) * kWarpSize;
 using UC = Cfg<kUB, true>;             // ring stage: K chunk 0, K chunk 1, V chunk 0, V chunk 1 (2 KiB each)
 constexpr int kQBufBytes = 8 * 1024;   // A operand of Q.K^T: 8 chunks (16 dims) x 64 rows x 16 B
 constexpr int kPBufBytes = 2 * 1024;   // A operand of P.V  : 2 chunks (16 tokens) x 64 rows x 16 B
@@ -44,24 +45,19 @@ constexpr int kMergeRow = kD + 4;      // fp32 words per merged accumulator row
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kTmemO = 0;         // 2 x 128 columns: output accumulators, double-buffered by segment parity
 constexpr uint32_t kTmemS = 256;       // 4 x 32 columns: logits of one tile per class
-constexpr float kPShift = 3.f;         // p' = 2^(s - m_ref + 3): 8 at the reference
-constexpr float kTau = 5.f;            // re-reference when a logit exceeds m_ref by 2^5 (p' would pass 256; e4m3 max 448)
+constexpr float kPShift = 1.f;         // p' = 2^(s - m_ref + 1): 2 at the reference
+constexpr float kTau = 7.f;            // re-reference when a logit exceeds m_ref by 2^7 (p' would pass 256; e4m3 max 448)
 constexpr float kLoScale = 16.f;
 
 // barrier slots after full[nst] / empty[nst]
 enum : int { kBarSReady = 0, kBarPReady = 4, kBarPFree = 8, kBarQReady = 12, kBarOReady = 14, kBarOFree = 16,
-             kBarDrained = 18, kBarRescGo = 19, kBarRescDone = 23, kNumExtraBars = 27 };
+             kBarDrained = 18, kBarRescGo = 19, kBarRescDone = 23, kBarSFree = 27, kNumExtraBars = 31 };
 
 // ---- tcgen05 wrappers -------------------------------------------------------------------------------------
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
   return pred != 0;
-}
-__device__ __forceinline__ uint64_t umma_desc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
-  // no swizzle, K-major: start address, leading (K-direction) byte offset, stride (8-row group) byte offset, version 1
-  return (uint64_t)((addr >> 4) & 0x3fffu) | ((uint64_t)((lbo >> 4) & 0x3fffu) << 16) |
-         ((uint64_t)((sbo >> 4) & 0x3fffu) << 32) | ((uint64_t)1 << 46);
 }
 __host__ __device__ constexpr uint32_t umma_idesc_e4m3(int M, int N) {  // f32 accumulate, e4m3 x e4m3, both K-major
   return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
@@ -86,6 +82,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
         "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
         "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
         "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// 16 TMEM lanes x 32 columns in the m16n8 accumulator-fragment distribution:
+// thread t, register 4j + 2a + b = [lane t/4 + 8a][column 8j + 2(t%4) + b]   (verified by tools/umma_probe.cu)
+__device__ __forceinline__ void tmem_ld_frag16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.16x256b.x4.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr));
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
@@ -170,91 +176,56 @@ __device__ __forceinline__ USmem carve_smem(uint8_t* raw, int nst) {
   return m;
 }
 
-// ---- MMA issuer (whole warp converged, one elected lane issues) ------------------------------------------------
+// ---- MMA issuers (whole warp converged, one elected lane issues) ------------------------------------------------
+// Two issuing warps, because one warp's dependent chain of uniform-datapath instructions (~230 per tile when a
+// single warp did both jobs, ~1200 cycles) was the bottleneck of the whole kernel (profiles/r1_c3_umma_v0_*):
+//   Q.K^T warp: waits for a ring stage and for the class's S buffer, issues 4 MMAs per block, commits to s_ready;
+//   P.V warp  : waits for the class's P, issues one MMA, commits the ring stage back to the producers.
+// A P.V of tile t is only issued after class t&3 saw S(t), i.e. after Q.K^T(t) completed, so the commit that frees
+// the stage also covers the other warp's reads of its K chunks.
+// Descriptor low words are kept as "base + offset/16" sums: addresses stay below 256 KiB, so adding to the 14-bit
+// address field never carries into the LBO field.
+__device__ __forceinline__ uint64_t umma_desc_from(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; }
+
 template <bool FLAT>
-__device__ __forceinline__ void mma_warp(const StreamParams& p, const USmem& sm, int nst, uint32_t tmem) {
-  const uint32_t ring_u32 = smem_u32(sm.ring), qbuf_u32 = smem_u32(sm.qbuf), pbuf_u32 = smem_u32(sm.pbuf);
-  const uint32_t full_u32 = smem_u32(sm.bars), empty_u32 = full_u32 + 8u * nst, xb = empty_u32 + 8u * nst;
-  constexpr uint32_t idesc_s = umma_idesc_e4m3(64, 16), idesc_o = umma_idesc_e4m3(64, 128);
-  // pending P.V of the last tiles, one slot per class: stage in pend_stage, flags in pend_flags (8 bits per slot)
-  //   bit0 valid, bit1 accumulate, bit2 output buffer, bit3 last tile of its segment, bit4 wait for o_free first
-  uint32_t pend_stage = 0, pend_flags = 0;
-  uint32_t p_ready_par = 0;        // bit c: parity of the next p_ready[c] wait
-  uint32_t resc_par = 0;           // bit c: parity of the next resc_done[c] wait
-  uint32_t drained_par = 0;
-  uint32_t o_free_seen0 = 0, o_free_seen1 = 0;  // completions of o_free[b] consumed so far
-
-  auto do_pv = [&](uint32_t c) {
-    const uint32_t fl = (pend_flags >> (8 * c)) & 0xffu;
-    if (!(fl & 1u)) return;
-    pend_flags &= ~(0xffu << (8 * c));
-    const uint32_t st = (pend_stage >> (8 * c)) & 0xffu;
-    const uint32_t ob = (fl >> 2) & 1u;
-    MBAR_WAIT(xb + 8u * (kBarPReady + c), (p_ready_par >> c) & 1u, 10, (int)c, (int)st);
-    p_ready_par ^= 1u << c;
-    if (fl & 16u) {  // first P.V of a segment: the class warps must have drained this accumulator (two segments ago)
-      const uint32_t seen = ob ? o_free_seen1 : o_free_seen0;
-      MBAR_WAIT(xb + 8u * (kBarOFree + ob), seen & 1u, 11, (int)ob, 0);
-      if (ob) ++o_free_seen1; else ++o_free_seen0;
-    }
-    if (ld_volatile_smem(sm.resc_req + c)) {
-      // class c moved its reference: every MMA issued so far must finish, then it rescales its accumulator lanes
-      if (elect_one()) umma_commit(xb + 8u * kBarDrained);
-      MBAR_WAIT(xb + 8u * kBarDrained, drained_par, 12, (int)c, 0);
-      drained_par ^= 1u;
-      if (elect_one()) {
-        st_volatile_smem(sm.resc_req + c, 0);
-        mbar_arrive(xb + 8u * (kBarRescGo + c));
-      }
-      MBAR_WAIT(xb + 8u * (kBarRescDone + c), (resc_par >> c) & 1u, 13, (int)c, 0);
-      resc_par ^= 1u << c;
-    }
-    tc_fence_after();
-    if (elect_one()) {
-      umma_f8(tmem + kTmemO + 128u * ob, umma_desc(pbuf_u32 + c * kPBufBytes, kAChunkStride, 128),
-              umma_desc(ring_u32 + st * UC::kStageBytes + UC::kVOffset, UC::kBlkBytes, 128), idesc_o, (fl >> 1) & 1u);
-      umma_commit(empty_u32 + 8u * st);               // ring stage back to the producers
-      umma_commit(xb + 8u * (kBarPFree + c));          // P buffer of the class reusable
-      if (fl & 8u) umma_commit(xb + 8u * (kBarOReady + ob));
-    }
-    __syncwarp();
-  };
-
+__device__ __forceinline__ void qk_warp(const StreamParams& p, const USmem& sm, int nst, uint32_t tmem) {
+  const uint32_t full_u32 = smem_u32(sm.bars), xb = full_u32 + 16u * nst;
+  constexpr uint32_t idesc_s = umma_idesc_e4m3(64, 16);
+  constexpr uint32_t desc_hi = (128u >> 4) | (1u << 14);  // SBO 128 B, descriptor version 1
+  const uint32_t q_lo0 = ((smem_u32(sm.qbuf) >> 4) & 0x3fffu) | ((kAChunkStride >> 4) << 16);
+  const uint32_t k_lo0 = ((smem_u32(sm.ring) >> 4) & 0x3fffu) | ((256u >> 4) << 16);
   uint32_t gt = 0, stage = 0, full_par = 0, sidx = 0;
   WorkIter<FLAT> wi;
   wi.init(p, sm.sched);
   Seg it;
   while (wi.next(p, it)) {
     const int ntiles = (it.t1 - it.t0 + kTileTokens - 1) / kTileTokens;
-    const uint32_t qb = sidx & 1u, ob = sidx & 1u;
-    if (!mbar_test(xb + 8u * (kBarQReady + qb), (sidx >> 1) & 1u)) {
-      // The class warps write this segment's Q when they start the previous segment, i.e. after they finished the one
-      // before it — which needs that segment's last P.V, possibly still queued here behind the three-tile lag.
-      for (uint32_t k = 1; k <= 3; ++k) do_pv((gt + k) & 3u);
-      MBAR_WAIT(xb + 8u * (kBarQReady + qb), (sidx >> 1) & 1u, 14, (int)sidx, 0);
-    }
+    const int last_blocks = min(2, (it.t1 - (it.t0 + (ntiles - 1) * kTileTokens) + kUB - 1) / kUB);
+    const uint32_t q_lo = q_lo0 + (sidx & 1u) * (kQBufBytes >> 4);
+    MBAR_WAIT(xb + 8u * (kBarQReady + (sidx & 1u)), (sidx >> 1) & 1u, 14, (int)sidx, 0);
     for (int ti = 0; ti < ntiles; ++ti) {
       const uint32_t c = gt & 3u;
+      // the class has read S of its previous tile (first use passes: parity trick)
+      MBAR_WAIT(xb + 8u * (kBarSFree + c), ((gt >> 2) & 1u) ^ 1u, 16, (int)gt, (int)c);
       MBAR_WAIT(full_u32 + 8u * stage, full_par, 15, (int)gt, (int)stage);
       tc_fence_after();
-      const int nblk = min(2, (it.t1 - (it.t0 + ti * kTileTokens) + kUB - 1) / kUB);
+      const int nblk = ti == ntiles - 1 ? last_blocks : 2;
+      const uint32_t k_lo = k_lo0 + stage * (UC::kStageBytes >> 4);
+      const uint32_t d_s = tmem + kTmemS + 32u * c;
       if (elect_one()) {
-        const uint32_t kst = ring_u32 + stage * UC::kStageBytes;
-        for (int j = 0; j < nblk; ++j) {
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_f8(d_s, umma_desc_from(q_lo + kk * (2 * kAChunkStride >> 4), desc_hi),
+                  umma_desc_from(k_lo + kk * (512 >> 4), desc_hi), idesc_s, kk > 0);
+        if (nblk == 2) {
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)
-            umma_f8(tmem + kTmemS + 32u * c + 16u * j,
-                    umma_desc(qbuf_u32 + qb * kQBufBytes + kk * 2 * kAChunkStride, kAChunkStride, 128),
-                    umma_desc(kst + j * UC::kBlkBytes + kk * 512, 256, 128), idesc_s, kk > 0);
+            umma_f8(d_s + 16u, umma_desc_from(q_lo + kk * (2 * kAChunkStride >> 4), desc_hi),
+                    umma_desc_from(k_lo + (UC::kBlkBytes >> 4) + kk * (512 >> 4), desc_hi), idesc_s, kk > 0);
         }
         umma_commit(xb + 8u * (kBarSReady + c));
       }
       __syncwarp();
-      const uint32_t fl = 1u | (ti > 0 ? 2u : 0u) | (ob << 2) | (ti == ntiles - 1 ? 8u : 0u) |
-                          ((ti == 0 && sidx >= 2) ? 16u : 0u);
-      pend_stage = (pend_stage & ~(0xffu << (8 * c))) | (stage << (8 * c));
-      pend_flags = (pend_flags & ~(0xffu << (8 * c))) | (fl << (8 * c));
-      do_pv((gt + 1u) & 3u);  // tile gt - 3
       ++gt;
       if (++stage == (uint32_t)nst) {
         stage = 0;
@@ -263,7 +234,54 @@ __device__ __forceinline__ void mma_warp(const StreamParams& p, const USmem& sm,
     }
     ++sidx;
   }
-  for (uint32_t k = 1; k <= 3; ++k) do_pv((gt + k) & 3u);  // tiles gt-3, gt-2, gt-1
+}
+
+template <bool FLAT>
+__device__ __forceinline__ void pv_warp(const StreamParams& p, const USmem& sm, int nst, uint32_t tmem) {
+  const uint32_t full_u32 = smem_u32(sm.bars), empty_u32 = full_u32 + 8u * nst, xb = empty_u32 + 8u * nst;
+  constexpr uint32_t idesc_o = umma_idesc_e4m3(64, 128);
+  constexpr uint32_t desc_hi = (128u >> 4) | (1u << 14);
+  const uint32_t p_lo0 = ((smem_u32(sm.pbuf) >> 4) & 0x3fffu) | ((kAChunkStride >> 4) << 16);
+  const uint32_t v_lo0 = (((smem_u32(sm.ring) + UC::kVOffset) >> 4) & 0x3fffu) | ((UC::kBlkBytes >> 4) << 16);
+  uint32_t gt = 0, stage = 0, sidx = 0, drained_par = 0, resc_par = 0;
+  WorkIter<FLAT> wi;
+  wi.init(p, sm.sched);
+  Seg it;
+  while (wi.next(p, it)) {
+    const int ntiles = (it.t1 - it.t0 + kTileTokens - 1) / kTileTokens;
+    const uint32_t ob = sidx & 1u;
+    const uint32_t d_o = tmem + kTmemO + 128u * ob;
+    for (int ti = 0; ti < ntiles; ++ti) {
+      const uint32_t c = gt & 3u;
+      MBAR_WAIT(xb + 8u * (kBarPReady + c), (gt >> 2) & 1u, 10, (int)gt, (int)c);
+      if (ti == 0 && sidx >= 2)  // the class warps have drained this accumulator (two segments ago)
+        MBAR_WAIT(xb + 8u * (kBarOFree + ob), ((sidx >> 1) - 1u) & 1u, 11, (int)sidx, 0);
+      if (ld_volatile_smem(sm.resc_req + c)) {
+        // class c moved its reference: every P.V issued so far must finish, then it rescales its accumulator lanes
+        if (elect_one()) umma_commit(xb + 8u * kBarDrained);
+        MBAR_WAIT(xb + 8u * kBarDrained, drained_par, 12, (int)c, 0);
+        drained_par ^= 1u;
+        if (elect_one()) {
+          st_volatile_smem(sm.resc_req + c, 0);
+          mbar_arrive(xb + 8u * (kBarRescGo + c));
+        }
+        MBAR_WAIT(xb + 8u * (kBarRescDone + c), (resc_par >> c) & 1u, 13, (int)c, 0);
+        resc_par ^= 1u << c;
+      }
+      tc_fence_after();
+      if (elect_one()) {
+        umma_f8(d_o, umma_desc_from(p_lo0 + c * (kPBufBytes >> 4), desc_hi),
+                umma_desc_from(v_lo0 + stage * (UC::kStageBytes >> 4), desc_hi), idesc_o, ti > 0);
+        umma_commit(empty_u32 + 8u * stage);           // ring stage back to the producers
+        umma_commit(xb + 8u * (kBarPFree + c));         // P buffer of the class reusable
+        if (ti == ntiles - 1) umma_commit(xb + 8u * (kBarOReady + ob));
+      }
+      __syncwarp();
+      ++gt;
+      if (++stage == (uint32_t)nst) stage = 0;
+    }
+    ++sidx;
+  }
 }
 
 // ---- class (softmax) warps ---------------------------------------------------------------------------------------
@@ -272,16 +290,18 @@ __device__ __forceinline__ void class_warp(const StreamParams& p, const USmem& s
   const uint32_t ring_u32 = smem_u32(sm.ring), qbuf_u32 = smem_u32(sm.qbuf);
   const uint32_t pbuf_u32 = smem_u32(sm.pbuf) + (uint32_t)q * kPBufBytes;
   const uint32_t xb = smem_u32(sm.bars) + 16u * nst;
-  const int h = lane & 7, half = (lane >> 3) & 1;
-  const bool row_lane = lane < 16;       // lanes that own an accumulator row of this quadrant (hi: 0-7, lo: 8-15)
-  const bool active = row_lane && h < p.G;
+  // S is read with the 16x256b fragment shape: thread t gets, for head h = t / 4, the hi row (TMEM lane h) and the lo
+  // row (lane 8 + h) of the 8 tokens 8j + 2(t % 4) + {0, 1}, j = 0..3 — all 32 lanes work, no cross-lane exchange.
+  const int h = lane >> 2, c4 = lane & 3;
+  const bool row_lane = lane < 16;       // 32x32b accesses (O rows): lanes 0-7 hold hi rows, 8-15 lo rows
+  const bool active = h < p.G;
   const uint32_t lane_base = (uint32_t)(32 * q) << 16;
   const float ksc = __ldg(p.k_scale), vsc = __ldg(p.v_scale);
   const int tid = q * kWarpSize + lane;  // 0..127 over the class warps
   constexpr float kInvLo = 1.f / kLoScale;
 
   // Write the hi / lo e4m3 rows of this quadrant's copy of the Q operand for segment g into qbuf[buf]; returns the
-  // logit multiplier (log2 units, k_scale and the per-head power-of-two prescale folded in) of head lane & 7.
+  // logit multiplier (log2 units, k_scale and the per-head power-of-two prescale folded in) of head lane >> 2.
   auto prep_q = [&](const Seg& g, uint32_t buf) -> float {
     const int hh = lane >> 2, pp = lane & 3;  // head, 32-dim part
     const bool hv = hh < p.G;
@@ -327,7 +347,7 @@ __device__ __forceinline__ void class_warp(const StreamParams& p, const USmem& s
     __syncwarp();
     if (lane == 0) mbar_arrive(xb + 8u * (kBarQReady + buf));
     const float mine = p.scale * kLog2e * ksc / qs;
-    return __shfl_sync(0xffffffffu, mine, (lane & 7) * 4);
+    return mine;  // lanes 4hh..4hh+3 computed head hh = lane >> 2
   };
 
   uint32_t s_par = 0, pfree_par = 0, resc_go_par = 0, sidx = 0, tile_base = 0;
@@ -358,26 +378,28 @@ __device__ __forceinline__ void class_warp(const StreamParams& p, const USmem& s
       MBAR_WAIT(xb + 8u * (kBarSReady + q), s_par, 20, q, ti);
       s_par ^= 1u;
       tc_fence_after();
-      tmem_ld32(tmem + lane_base + kTmemS + 32u * q, r);
+      uint32_t sr[16];
+      tmem_ld_frag16(tmem + lane_base + kTmemS + 32u * q, sr);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(xb + 8u * (kBarSFree + q));  // S is in registers: the next Q.K^T of this class may land
       const int tok0 = it.t0 + ti * kTileTokens;
       const int nvalid = min(kTileTokens, it.t1 - tok0);
-      // lanes 0-7 hold the hi rows, lanes 8-15 the lo rows, 32 tokens each: swap halves so that lane (h, half)
-      // owns the 16 tokens of block `half` with s = hi + lo / 16
-      float sv[16];
+      float sv[8];
       float mx = -INFINITY;
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const uint32_t send = half ? r[i] : r[16 + i];
-        const float recv = __uint_as_float(__shfl_xor_sync(0xffffffffu, send, 8));
-        float v = half ? fmaf(__uint_as_float(r[16 + i]), kInvLo, recv) : fmaf(recv, kInvLo, __uint_as_float(r[i]));
-        const int tt = 16 * half + i;
-        v *= sc2;
-        if (use_alibi) v = fmaf(al2, (float)(tok0 + tt - it.L + 1), v);
-        if (tt >= nvalid) v = -INFINITY;
-        sv[i] = v;
-        mx = fmaxf(mx, v);
-      }
-      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          const int tt = 8 * j + 2 * c4 + b;  // token inside the tile
+          float v = fmaf(__uint_as_float(sr[4 * j + 2 + b]), kInvLo, __uint_as_float(sr[4 * j + b])) * sc2;
+          if (use_alibi) v = fmaf(al2, (float)(tok0 + tt - it.L + 1), v);
+          if (tt >= nvalid) v = -INFINITY;
+          sv[2 * j + b] = v;
+          mx = fmaxf(mx, v);
+        }
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
       m_true = fmaxf(m_true, mx);
       bool need = false;
       if (fresh) {
@@ -394,9 +416,9 @@ __device__ __forceinline__ void class_warp(const StreamParams& p, const USmem& s
         l *= f;
         m_ref = m_new;
       }
-      uint32_t hi4[4], lo4[4];
+      uint32_t hi4[2], lo4[2];
 #pragma unroll
-      for (int g4 = 0; g4 < 4; ++g4) {
+      for (int g4 = 0; g4 < 2; ++g4) {
         float pq[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -408,9 +430,15 @@ __device__ __forceinline__ void class_warp(const StreamParams& p, const USmem& s
       MBAR_WAIT(xb + 8u * (kBarPFree + q), pfree_par ^ 1u, 21, q, ti);  // P.V of this class's previous tile is done
       pfree_par ^= 1u;
       if (active) {
-        const uint32_t a = pbuf_u32 + (uint32_t)half * kAChunkStride + (uint32_t)(16 * q + h) * 16u;
-        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(hi4[0]), "r"(hi4[1]), "r"(hi4[2]), "r"(hi4[3]) : "memory");
-        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a + 128u), "r"(lo4[0]), "r"(lo4[1]), "r"(lo4[2]), "r"(lo4[3]) : "memory");
+        // token pair j (tokens 8j + 2c4, +1) sits in chunk j / 2 at byte 8 (j & 1) + 2 c4 of row 16q + h (hi) / + 8 (lo)
+        const uint32_t a = pbuf_u32 + (uint32_t)(16 * q + h) * 16u + 2u * (uint32_t)c4;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t aj = a + (uint32_t)(j >> 1) * kAChunkStride + 8u * (uint32_t)(j & 1);
+          const uint16_t hv = (uint16_t)(hi4[j >> 1] >> (16 * (j & 1))), lv = (uint16_t)(lo4[j >> 1] >> (16 * (j & 1)));
+          asm volatile("st.shared.u16 [%0], %1;" ::"r"(aj), "h"(hv) : "memory");
+          asm volatile("st.shared.u16 [%0], %1;" ::"r"(aj + 128u), "h"(lv) : "memory");
+        }
       }
       if (nvalid < kTileTokens) {
         // Last, partial tile of a sequence: V bytes past seq_len are stale cache (possibly NaN patterns) or, for a missing
@@ -443,12 +471,15 @@ __device__ __forceinline__ void class_warp(const StreamParams& p, const USmem& s
         MBAR_WAIT(xb + 8u * (kBarRescGo + q), resc_go_par, 22, q, ti);
         resc_go_par ^= 1u;
         tc_fence_after();
+        // accumulator rows are TMEM lanes 0-7 (hi) and 8-15 (lo) of head lane & 7, whose factor lives in thread 4 (lane & 7)
+        const float f_src = __shfl_sync(0xffffffffu, f, (lane & 7) * 4);
+        const float f_row = row_lane ? f_src : 1.f;
 #pragma unroll 1
         for (int ch = 0; ch < 4; ++ch) {
           const uint32_t ta = tmem + lane_base + kTmemO + 128u * ob + 32u * ch;
           tmem_ld32(ta, r);
 #pragma unroll
-          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * f);
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * f_row);
           tmem_st32(ta, r);
         }
         tc_fence_before();
@@ -461,7 +492,8 @@ __device__ __forceinline__ void class_warp(const StreamParams& p, const USmem& s
     tile_base += (uint32_t)ntiles;
 
     // ---- end of the segment: park this class's partial in shared memory ---------------------------------------
-    l += __shfl_xor_sync(0xffffffffu, l, 8);  // the two token halves
+    l += __shfl_xor_sync(0xffffffffu, l, 1);  // the four token quarters of a head
+    l += __shfl_xor_sync(0xffffffffu, l, 2);
     MBAR_WAIT(xb + 8u * (kBarOReady + ob), (sidx >> 1) & 1u, 23, q, (int)sidx);
     tc_fence_after();
 #pragma unroll 1
@@ -477,10 +509,10 @@ __device__ __forceinline__ void class_warp(const StreamParams& p, const USmem& s
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(xb + 8u * (kBarOFree + ob));
-    if (lane < 8) {
-      sm.merge_mref[q * 8 + lane] = fresh ? -INFINITY : m_ref;
-      sm.merge_mtrue[q * 8 + lane] = fresh ? -INFINITY : m_true;
-      sm.merge_l[q * 8 + lane] = fresh ? 0.f : l;
+    if (c4 == 0) {
+      sm.merge_mref[q * 8 + h] = fresh ? -INFINITY : m_ref;
+      sm.merge_mtrue[q * 8 + h] = fresh ? -INFINITY : m_true;
+      sm.merge_l[q * 8 + h] = fresh ? 0.f : l;
     }
     class_bar_sync();
     // ---- merge the four class partials (exact: every class kept its true running max) --------------------------
@@ -593,7 +625,7 @@ __global__ void __launch_bounds__(kUThreads, 1) paged_attention_umma_fp8_kernel(
   for (int i = tid; i < (2 * kQBufBytes + 4 * kPBufBytes) / 16; i += kUThreads)
     reinterpret_cast<uint4*>(sm.qbuf)[i] = make_uint4(0u, 0u, 0u, 0u);
   fence_async_smem();
-  if (warp == kMmaWarp) {
+  if (warp == kQkWarp) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(sm.tmem_slot)), "n"(kTmemCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -607,14 +639,16 @@ __global__ void __launch_bounds__(kUThreads, 1) paged_attention_umma_fp8_kernel(
 
   if (warp < kClassWarps) {
     class_warp<FLAT>(p, sm, nst, tmem, warp, lane);
-  } else if (warp == kMmaWarp) {
-    mma_warp<FLAT>(p, sm, nst, tmem);
+  } else if (warp == kQkWarp) {
+    qk_warp<FLAT>(p, sm, nst, tmem);
+  } else if (warp == kPvWarp) {
+    pv_warp<FLAT>(p, sm, nst, tmem);
   } else if (lane == 0) {
-    producer_loop<kUB, true, FLAT, kUProducers>(p, sm.sched, warp - kMmaWarp - 1, smem_u32(sm.ring), full_u32, empty_u32, nst);
+    producer_loop<kUB, true, FLAT, kUProducers>(p, sm.sched, warp - kPvWarp - 1, smem_u32(sm.ring), full_u32, empty_u32, nst);
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == kMmaWarp)
+  if (warp == kQkWarp)
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(kTmemCols) : "memory");
 }
 
