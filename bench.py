@@ -299,8 +299,8 @@ def run_ours(args):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the attention kernel, from the ncu --set full
-# capture committed under profiles/ (r1_c2_bf16_ncu_summary.md); null where no capture exists.
-TRAFFIC_BYTES = {"c2": 1074942000 + 5852416}
+# captures committed under profiles/ (r1_c2_bf16_ncu_summary.txt, r1_c3_fp8_ncu_summary.txt); null where no capture exists.
+TRAFFIC_BYTES = {"c2": 1075123000 + 4585728, "c3": 538070016 + 4122624}
 
 
 # ---- CPU arm --------------------------------------------------------------------------------------------

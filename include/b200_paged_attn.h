@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define B200_PAGED_ATTN_ABI_VERSION 1
+#define B200_PAGED_ATTN_ABI_VERSION 2
 
 /* v2 partition size: template default of the reference launcher
  * (csrc/attention/paged_attention_v2.cu:45) and of its callers
@@ -137,6 +137,13 @@ typedef struct b200_paged_attn_params {
   int32_t blocksparse_vert_stride;
   int32_t blocksparse_block_size;
   int32_t blocksparse_head_sliding_step;
+  /* ABI v2.  Optional log-sum-exp of the scaled logits per (head, seq), float32
+   * [num_heads, num_seqs] (the layout merge_attn_states reads: prefix_lse /
+   * suffix_lse [NUM_HEADS, NUM_TOKENS], csrc/attention/merge_attn_states.cu:43-44),
+   * natural-log units; NULL = not wanted (the reference ops have no such
+   * output).  A sequence of length 0 yields -inf.  Feeds b200_merge_attn_states
+   * (cascade / decode-context-parallel, vllm_metax/v1/attention/backends/flash_attn.py:794-872). */
+  float* out_lse;
 } b200_paged_attn_params_t;
 
 /* Replaces torch.ops._C.paged_attention_v1 (csrc/torch_bindings.cpp:45-55;
@@ -203,6 +210,115 @@ int b200_reshape_and_cache_flash(const b200_cache_write_params_t* params, void* 
  * (e4m3_satfinite_rn(float(x) / scale)).  scale is a HOST float. */
 int b200_convert_fp8(void* dst, const void* src, int64_t num_elements, float scale,
                      int32_t dst_dtype, int32_t src_dtype, int32_t kv_dtype, void* stream);
+
+/*
+ * Replaces torch.ops._C.merge_attn_states (csrc/torch_bindings.cpp:74-82;
+ * csrc/attention/merge_attn_states.cu:14-88, :129-168): section 2.2 of
+ * arXiv 2501.01005 — combine two partial attention results over disjoint key
+ * sets:  m = max(p_lse, s_lse), w_p = exp(p_lse - m), w_s = exp(s_lse - m),
+ * out = (prefix*w_p + suffix*w_s) / (w_p + w_s), out_lse = log(w_p + w_s) + m,
+ * with +inf lse treated as -inf (:45-46).  fp32 arithmetic.
+ *   output / prefix_output / suffix_output [num_tokens, num_heads, head_size]
+ *       dtype (f32/f16/bf16), heads*dims contiguous, token strides given in
+ *       elements (the reference assumes num_heads*head_size, :36-37)
+ *   prefix_lse / suffix_lse / output_lse [num_heads, num_tokens] float32,
+ *       output_lse nullable
+ *   head_size must be a multiple of 16 / sizeof(dtype) (:138-139) and the
+ *   tensors 16-byte aligned.
+ */
+typedef struct b200_merge_attn_states_params {
+  void* output;
+  float* output_lse; /* nullable */
+  const void* prefix_output;
+  const float* prefix_lse;
+  const void* suffix_output;
+  const float* suffix_lse;
+  int64_t output_stride; /* token strides, elements */
+  int64_t prefix_stride;
+  int64_t suffix_stride;
+  int32_t num_tokens;
+  int32_t num_heads;
+  int32_t head_size;
+  int32_t dtype; /* b200_dtype_t */
+} b200_merge_attn_states_params_t;
+
+int b200_merge_attn_states(const b200_merge_attn_states_params_t* params, void* stream);
+
+/*
+ * Replaces torch.ops._C_cache_ops.copy_blocks (csrc/torch_bindings.cpp:384-387;
+ * csrc/cache_kernels.cu:64-92, :113-163): for every layer and every
+ * (src, dst) pair copy block src onto block dst inside the same key cache and
+ * the same value cache.
+ *   key_caches / value_caches : HOST arrays of num_layers DEVICE pointers (the
+ *       reference stages them through a synchronous H2D copy, :139-145; here
+ *       they travel as kernel arguments — no copy, no sync, graph-capturable)
+ *   block_mapping : DEVICE int64 [num_pairs, 2]
+ *   block_bytes   : bytes of one block (= numel of cache[0] * element size, :148)
+ */
+int b200_copy_blocks(void* const* key_caches, void* const* value_caches, int32_t num_layers,
+                     const int64_t* block_mapping, int32_t num_pairs, int64_t block_bytes, void* stream);
+
+/* memcpy direction of b200_swap_blocks (csrc/cache_kernels.cu:22-34). */
+typedef enum b200_copy_kind {
+  B200_COPY_D2D = 0,
+  B200_COPY_D2H = 1,
+  B200_COPY_H2D = 2
+} b200_copy_kind_t;
+
+/*
+ * Replaces torch.ops._C_cache_ops.swap_blocks (csrc/torch_bindings.cpp:380-381;
+ * csrc/cache_kernels.cu:18-60): dst block mapping[i][1] <- src block mapping[i][0],
+ * block_bytes each (= element_size * stride(0), :46), enqueued on `stream`.
+ *   block_mapping : HOST int64 [num_pairs, 2] (:40)
+ * Runs of pairs that are consecutive in both src and dst go out as ONE copy
+ * (the reference issues one cudaMemcpyAsync per block, :52-59).
+ */
+int b200_swap_blocks(void* dst, const void* src, const int64_t* block_mapping, int64_t num_pairs,
+                     int64_t block_bytes, int32_t kind, void* stream);
+
+/*
+ * Arguments of gather_and_maybe_dequant_cache / cp_gather_cache: copy the
+ * cache entries of each sequence, in token order, into a packed destination.
+ *   reference ops : csrc/torch_bindings.cpp:431-442
+ *   reference C++ : csrc/cache_kernels.cu:618-773 (gather_and_maybe_dequant_cache),
+ *                   :775-839, :1075-1134 (cp_gather_cache)
+ *   src_cache   [num_blocks, block_size, entry_size] addressed by cache_block_stride /
+ *               cache_entry_stride (elements), entry contiguous
+ *   dst         [total_tokens, entry_size], row stride dst_entry_stride
+ *   block_table [batch, ...] int32, row stride block_table_stride
+ *   cu_seq_lens [batch + 1] int32; sequence b fills dst rows [cu[b], cu[b+1])
+ *   seq_starts  [batch] int32 or NULL: first token of each sequence inside its
+ *               block table.  token_granular_starts == 0: rounded DOWN to a block
+ *               boundary (gather_and_maybe_dequant_cache, :660-662);
+ *               != 0: used as is (cp_gather_cache, :806-811)
+ *   scale       device float, read only when kv_dtype != auto
+ *   src_dtype / dst_dtype: b200_dtype_t; auto: equal (any 1/2/4-byte element is
+ *               moved as bytes: pass U8/F16/F32 by width); fp8: src U8, dst f32/f16/bf16
+ *               = float(e4m3) * scale.
+ */
+typedef struct b200_gather_cache_params {
+  const void* src_cache;
+  void* dst;
+  const int32_t* block_table;
+  const int32_t* cu_seq_lens;
+  const int32_t* seq_starts; /* nullable */
+  const float* scale;        /* nullable when kv_dtype == auto */
+  int64_t block_table_stride;
+  int64_t cache_block_stride;
+  int64_t cache_entry_stride;
+  int64_t dst_entry_stride;
+  int32_t batch_size;
+  int32_t block_size;
+  int32_t entry_size;
+  int32_t src_dtype;
+  int32_t dst_dtype;
+  int32_t kv_dtype;
+  int32_t token_granular_starts;
+} b200_gather_cache_params_t;
+
+/* Replaces torch.ops._C_cache_ops.gather_and_maybe_dequant_cache and
+ * torch.ops._C_cache_ops.cp_gather_cache (see the struct). */
+int b200_gather_cache(const b200_gather_cache_params_t* params, void* stream);
 
 /* "auto" -> B200_KV_AUTO, "fp8" | "fp8_e4m3" -> B200_KV_FP8_E4M3, anything
  * else (incl. "fp8_e5m2") -> -1. */
