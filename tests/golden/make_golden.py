@@ -116,8 +116,107 @@ def make_cache():
         print("wrote", name)
 
 
+REF_MERGE_TEST = "/root/reference/tests/kernels/attention/test_merge_attn_states.py"
+
+
+def load_reference_merge():
+    """merge_attn_states_torch, cut out of the reference test file unmodified (test_merge_attn_states.py:16-47)."""
+    tree = ast.parse(open(REF_MERGE_TEST).read())
+    ns = {"torch": torch, "Optional": Optional}
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name == "merge_attn_states_torch":
+            exec(compile(ast.Module(body=[node], type_ignores=[]), REF_MERGE_TEST, "exec"), ns)
+    return ns["merge_attn_states_torch"]
+
+
+MERGE_CASES = [
+    # name, tokens, heads, head_size, dtype  (sizes from the reference grid, test_merge_attn_states.py:50-53, scaled down)
+    ("merge_bf16_h8_d128", 37, 8, 128, torch.bfloat16),
+    ("merge_f16_h4_d96", 29, 4, 96, torch.float16),
+    ("merge_f32_h4_d48", 21, 4, 48, torch.float32),
+]
+
+
+def make_merge(ref_fn):
+    for idx, (name, N, H, D, dtype) in enumerate(MERGE_CASES):
+        g = torch.Generator().manual_seed(300 + idx)
+        # inputs as the reference test draws them (:104-136): randn lse with ~10 % +inf on either side, never both
+        p_lse = torch.randn(H, N, generator=g)
+        s_lse = torch.randn(H, N, generator=g)
+        mp = torch.rand(H, N, generator=g) < 0.1
+        ms = torch.rand(H, N, generator=g) < 0.1
+        both = mp & ms
+        p_lse[mp & ~both] = float("inf")
+        s_lse[ms & ~both] = float("inf")
+        p_out = torch.randn(N, H, D, generator=g).to(dtype)
+        s_out = torch.randn(N, H, D, generator=g).to(dtype)
+        out0 = torch.zeros(N, H, D, dtype=dtype)
+        lse0 = torch.zeros(H, N)
+        ref_out, ref_lse = ref_fn(out0, p_out, p_lse.clone(), s_out, s_lse.clone(), lse0)  # the function mutates its lse args
+        fix = dict(prefix_output=p_out, prefix_lse=p_lse, suffix_output=s_out, suffix_lse=s_lse,
+                   ref_output=ref_out, ref_output_lse=ref_lse)
+        torch.save(fix, os.path.join(HERE, name + ".pt"))
+        print("wrote", name, ref_out.dtype, tuple(ref_out.shape))
+
+
+def make_movers():
+    """copy_blocks / gather goldens: the reference tests' own expectation loops, transcribed next to their lines."""
+    rnd = random.Random(5)
+    g = torch.Generator().manual_seed(17)
+    NB, B, H, D, layers, nmap = 24, 16, 2, 64, 3, 5
+    dtype = torch.bfloat16
+    x = 8
+    key_caches = [torch.randn(NB, H, D // x, B, x, generator=g).to(dtype) for _ in range(layers)]
+    value_caches = [torch.randn(NB, H, D, B, generator=g).to(dtype) for _ in range(layers)]
+    # tests/kernels/attention/test_cache.py:71-81: every source block is mapped to two destinations
+    src_blocks = rnd.sample(range(NB), nmap)
+    remaining = sorted(set(range(NB)) - set(src_blocks))
+    dst_blocks = rnd.sample(remaining, 2 * nmap)
+    mapping = []
+    for i in range(nmap):
+        mapping.append((src_blocks[i], dst_blocks[2 * i]))
+        mapping.append((src_blocks[i], dst_blocks[2 * i + 1]))
+    ref_k = [k.clone() for k in key_caches]
+    ref_v = [v.clone() for v in value_caches]
+    for src, dst in mapping:  # :106-111
+        for c in ref_k:
+            c[dst].copy_(c[src])
+        for c in ref_v:
+            c[dst].copy_(c[src])
+    torch.save(dict(key_caches=key_caches, value_caches=value_caches,
+                    block_mapping=torch.tensor(mapping, dtype=torch.int64).view(-1, 2), ref_key_caches=ref_k,
+                    ref_value_caches=ref_v), os.path.join(HERE, "movers_copy_blocks_bf16.pt"))
+    print("wrote movers_copy_blocks_bf16")
+
+    # gather (tests/kernels/attention/test_cache.py:720-777): MLA-shaped entries, float32, auto
+    NB, B, entry, batch, max_len = 20, 16, 576, 5, 100
+    src_cache = torch.randn(NB, B, entry, generator=g)
+    seq_len = torch.randint(0, max_len + 1, (batch,), generator=g)
+    seq_len[1] = 0  # the reference's loop skips empty sequences (:750-751)
+    cu = torch.zeros(batch + 1, dtype=torch.int32)
+    cu[1:] = seq_len.cumsum(0).to(torch.int32)
+    tot_blocks = (seq_len + B - 1) // B
+    block_table = torch.stack([torch.randperm(NB, generator=g) for _ in range(batch)]).to(torch.int32)
+    expected = []
+    for b in range(batch):  # :748-776
+        s_ = int(seq_len[b])
+        if s_ == 0:
+            continue
+        tot = int(tot_blocks[b])
+        blocks = block_table[b, :tot].tolist()
+        rows = [src_cache[blocks[i]] for i in range(tot - 1)]
+        remaining_tokens = s_ - (tot - 1) * B
+        rows.append(src_cache[blocks[-1], :remaining_tokens, :])
+        expected.append(torch.cat(rows, dim=0))
+    torch.save(dict(src_cache=src_cache, block_table=block_table, cu_seq_lens=cu, batch_size=batch,
+                    ref_dst=torch.cat(expected, dim=0)), os.path.join(HERE, "movers_gather_f32.pt"))
+    print("wrote movers_gather_f32")
+
+
 if __name__ == "__main__":
     if not os.path.exists(REF_TEST):
         sys.exit("the reference is not mounted at /root/reference: goldens can only be regenerated in the build container")
     make_attention(load_reference_oracle())
     make_cache()
+    make_merge(load_reference_merge())
+    make_movers()

@@ -37,7 +37,7 @@ def test_every_declared_symbol_is_exported(native):
     lib = C.CDLL(os.fspath(native.LIB_PATH))
     for n in names:
         assert hasattr(lib, n), n
-    assert native.load().b200_abi_version() == 1
+    assert native.load().b200_abi_version() == 2
 
 
 def test_ctypes_structs_match_header_layout(native, tmp_path):
@@ -46,7 +46,9 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
 
     prog = ['#include <stdio.h>', '#include <stddef.h>', '#include "b200_paged_attn.h"', "int main(void){"]
     for cname, st in (("b200_paged_attn_params_t", native.PagedAttnParams),
-                      ("b200_cache_write_params_t", native.CacheWriteParams)):
+                      ("b200_cache_write_params_t", native.CacheWriteParams),
+                      ("b200_merge_attn_states_params_t", native.MergeAttnStatesParams),
+                      ("b200_gather_cache_params_t", native.GatherCacheParams)):
         prog.append('printf("%%zu\\n", sizeof(%s));' % cname)
         for f in fields(st):
             prog.append('printf("%%zu\\n", offsetof(%s, %s));' % (cname, f))
@@ -57,7 +59,7 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     vals = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     it = iter(vals)
-    for st in (native.PagedAttnParams, native.CacheWriteParams):
+    for st in (native.PagedAttnParams, native.CacheWriteParams, native.MergeAttnStatesParams, native.GatherCacheParams):
         assert next(it) == C.sizeof(st)
         for f in fields(st):
             assert next(it) == getattr(st, f).offset, f
@@ -118,6 +120,37 @@ def test_empty_batches_are_noops(native):
     assert native.load().b200_reshape_and_cache_flash(C.byref(cp), None) == 0
 
 
+def test_new_entry_points_validate_on_the_host(native):
+    """merge_attn_states / cache movers: argument errors and empty calls need no device."""
+    lib = native.load()
+    mp = native.MergeAttnStatesParams()
+    mp.num_tokens, mp.num_heads, mp.head_size, mp.dtype = 0, 4, 128, native.DTYPE_BF16
+    assert lib.b200_merge_attn_states(C.byref(mp), None) == 0
+    mp.num_tokens = 8
+    assert lib.b200_merge_attn_states(C.byref(mp), None) == native.ERR_INVALID_ARGUMENT  # NULL tensors
+    mp.head_size, mp.dtype = 36, native.DTYPE_F16  # not a multiple of the 8-element pack
+    mp.output = mp.prefix_output = mp.suffix_output = mp.prefix_lse = mp.suffix_lse = 4096
+    assert lib.b200_merge_attn_states(C.byref(mp), None) == native.ERR_UNSUPPORTED
+    assert "pack_size" in lib.b200_last_error().decode()
+    mp.dtype = 7
+    assert lib.b200_merge_attn_states(C.byref(mp), None) == native.ERR_UNSUPPORTED
+    assert "Unsupported data type of O" in lib.b200_last_error().decode()
+    gp = native.GatherCacheParams()
+    gp.batch_size, gp.block_size, gp.entry_size = 0, 16, 576
+    assert lib.b200_gather_cache(C.byref(gp), None) == 0
+    gp.batch_size = 2
+    assert lib.b200_gather_cache(C.byref(gp), None) == native.ERR_INVALID_ARGUMENT
+    gp.src_cache = gp.dst = gp.block_table = gp.cu_seq_lens = 4096
+    gp.src_dtype, gp.dst_dtype, gp.kv_dtype = native.DTYPE_F32, native.DTYPE_F16, native.KV_AUTO
+    assert lib.b200_gather_cache(C.byref(gp), None) == native.ERR_UNSUPPORTED
+    assert "same dtype" in lib.b200_last_error().decode()
+    assert lib.b200_copy_blocks(None, None, 0, None, 0, 0, None) == 0
+    assert lib.b200_swap_blocks(None, None, None, 0, 4096, native.COPY_D2D, None) == 0
+    m = (C.c_int64 * 2)(0, 1)
+    assert lib.b200_swap_blocks(4096, 8192, m, 1, 64, 9, None) == native.ERR_INVALID_ARGUMENT
+    assert "Invalid device combination" in lib.b200_last_error().decode()
+
+
 def test_workspace_sizing_is_host_only_and_monotone(native):
     small = native.workspace_bytes(_params(native, max_seq_len=256, num_seqs=64))
     big = native.workspace_bytes(_params(native, max_seq_len=131072, num_seqs=8))
@@ -151,6 +184,19 @@ def test_torch_shim_registers_reference_schemas_and_has_no_cpu_fallback(native):
                "str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()" in s3
     assert "convert_fp8(Tensor($0! -> ) dst_cache, Tensor src_cache, float scale, str kv_cache_dtype) -> ()" in str(
         torch.ops._C_cache_ops.convert_fp8.default._schema)
+    assert str(torch.ops._C.merge_attn_states.default._schema) == (
+        "_C::merge_attn_states(Tensor($0! -> ) output, Tensor($1! -> )? output_lse, Tensor prefix_output, "
+        "Tensor prefix_lse, Tensor suffix_output, Tensor suffix_lse) -> ()")
+    assert str(torch.ops._C_cache_ops.swap_blocks.default._schema) == (
+        "_C_cache_ops::swap_blocks(Tensor src, Tensor($0! -> ) dst, Tensor block_mapping) -> ()")
+    assert str(torch.ops._C_cache_ops.copy_blocks.default._schema) == (
+        "_C_cache_ops::copy_blocks(Tensor(a!)[] key_caches, Tensor[](b!) value_caches, Tensor block_mapping) -> ()")
+    assert str(torch.ops._C_cache_ops.gather_and_maybe_dequant_cache.default._schema) == (
+        "_C_cache_ops::gather_and_maybe_dequant_cache(Tensor src_cache, Tensor($0! -> ) dst, Tensor block_table, "
+        "Tensor cu_seq_lens, int batch_size, str kv_cache_dtype, Tensor scale, Tensor? seq_starts) -> ()")
+    assert str(torch.ops._C_cache_ops.cp_gather_cache.default._schema) == (
+        "_C_cache_ops::cp_gather_cache(Tensor src_cache, Tensor($0! -> ) dst, Tensor block_table, Tensor cu_seq_lens, "
+        "int batch_size, Tensor? seq_starts) -> ()")
     # CPU tensors: the dispatcher must refuse (only the CUDA key is implemented, as in the reference)
     q = torch.zeros(1, 8, 128, dtype=torch.bfloat16)
     kc = torch.zeros(4, 2, 16, 16, 8, dtype=torch.bfloat16)

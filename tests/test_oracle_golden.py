@@ -55,3 +55,73 @@ def test_cache_writers_match_reference_loops(path, impl):
     mod.reshape_and_cache_flash(d["key"], d["value"], k.permute(0, 2, 1, 3), v.permute(0, 2, 1, 3),
                                 d["slot_mapping"], "auto", one, one)
     assert torch.equal(k, d["ref_hnd_k"]) and torch.equal(v, d["ref_hnd_v"])
+
+
+MERGE = sorted(glob.glob(os.path.join(GOLDEN, "merge_*.pt")))
+
+
+@pytest.mark.parametrize("path", MERGE, ids=[os.path.basename(p)[:-3] for p in MERGE])
+def test_merge_attn_states_oracle_matches_reference_torch(path):
+    """oracle.merge_attn_states against the output of the reference's merge_attn_states_torch
+    (tests/kernels/attention/test_merge_attn_states.py:16-47, executed by make_golden.py)."""
+    d = torch.load(path)
+    assert len(MERGE) >= 3
+    p_lse, s_lse = d["prefix_lse"].clone(), d["suffix_lse"].clone()
+    out, lse = orc.merge_attn_states(d["prefix_output"], p_lse, d["suffix_output"], s_lse)
+    assert torch.equal(p_lse, d["prefix_lse"]) and torch.equal(s_lse, d["suffix_lse"])  # inputs untouched
+    assert torch.equal(lse, d["ref_output_lse"])
+    # the reference function returns the fp32 result; the oracle rounds it once to the output dtype
+    assert torch.equal(out, d["ref_output"].to(out.dtype))
+    assert torch.isinf(d["prefix_lse"]).any() and torch.isinf(d["suffix_lse"]).any()  # the +inf path is exercised
+
+
+def test_copy_blocks_oracle_matches_reference_loop():
+    d = torch.load(os.path.join(GOLDEN, "movers_copy_blocks_bf16.pt"))
+    kcs = [k.clone() for k in d["key_caches"]]
+    vcs = [v.clone() for v in d["value_caches"]]
+    orc.copy_blocks(kcs, vcs, d["block_mapping"])
+    for a, b in zip(kcs + vcs, d["ref_key_caches"] + d["ref_value_caches"]):
+        assert torch.equal(a, b)
+
+
+def test_gather_cache_oracle_matches_reference_loop():
+    d = torch.load(os.path.join(GOLDEN, "movers_gather_f32.pt"))
+    for granular in (False, True):  # no seq_starts: both ops gather the same rows
+        out = orc.gather_cache(d["src_cache"], d["block_table"], d["cu_seq_lens"], d["batch_size"],
+                               token_granular_starts=granular)
+        assert torch.equal(out, d["ref_dst"])
+
+
+def test_gather_cache_oracle_seq_starts_semantics():
+    """seq_starts: block-granular for gather_and_maybe_dequant_cache (csrc/cache_kernels.cu:660-662),
+    token-granular for cp_gather_cache (:806-811)."""
+    B, NB, E = 4, 6, 3
+    src = torch.arange(NB * B * E, dtype=torch.float32).view(NB, B, E)
+    table = torch.tensor([[5, 2, 0, 1]], dtype=torch.int32)
+    cu = torch.tensor([0, 5], dtype=torch.int32)
+    starts = torch.tensor([6], dtype=torch.int32)
+    blockwise = orc.gather_cache(src, table, cu, 1, seq_starts=starts, token_granular_starts=False)
+    exact = orc.gather_cache(src, table, cu, 1, seq_starts=starts, token_granular_starts=True)
+    assert torch.equal(blockwise, torch.cat([src[2], src[0, :1]]))           # starts at token 4 = block index 1
+    assert torch.equal(exact, torch.cat([src[2, 2:], src[0, :3]]))           # starts at token 6
+
+
+def test_paged_attention_lse_merges_back_to_full_attention():
+    """Splitting a sequence's keys in two, attending to each half and merging with merge_attn_states reproduces
+    attention over the whole sequence (section 2.2 of arXiv 2501.01005) — ties the LSE oracle to the attention oracle."""
+    S, H, Hkv, D, B, L, NB = 3, 8, 2, 64, 16, 90, 32
+    d = orc.make_decode_inputs(S, H, Hkv, D, B, L, NB, dtype=torch.float32, seed=5, unique_blocks=True)
+    lens = d["seq_lens"]
+    full = orc.paged_attention_f64(d["query"], d["key_cache"], d["value_cache"], d["block_tables"], lens, d["scale"])
+    cut = (lens // 2 // B * B).to(torch.int32)  # block-aligned split point
+    first = orc.paged_attention_f64(d["query"], d["key_cache"], d["value_cache"], d["block_tables"], cut, d["scale"])
+    lse1 = orc.paged_attention_lse(d["query"], d["key_cache"], d["value_cache"], d["block_tables"], cut, d["scale"])
+    bt2 = torch.stack([torch.roll(d["block_tables"][i], -int(cut[i]) // B) for i in range(S)])
+    rest = lens - cut
+    second = orc.paged_attention_f64(d["query"], d["key_cache"], d["value_cache"], bt2, rest, d["scale"])
+    lse2 = orc.paged_attention_lse(d["query"], d["key_cache"], d["value_cache"], bt2, rest, d["scale"])
+    first = torch.nan_to_num(first)  # an empty first half (cut == 0) has lse = -inf and weight 0
+    out, lse = orc.merge_attn_states(first.float(), lse1, second.float(), lse2)
+    full_lse = orc.paged_attention_lse(d["query"], d["key_cache"], d["value_cache"], d["block_tables"], lens, d["scale"])
+    torch.testing.assert_close(out.double(), full, atol=1e-5, rtol=1e-5)
+    torch.testing.assert_close(lse, full_lse, atol=1e-5, rtol=1e-5)

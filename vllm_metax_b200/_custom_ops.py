@@ -104,3 +104,78 @@ def reshape_and_cache_flash(
 
 def convert_fp8(output: torch.Tensor, input: torch.Tensor, scale: float = 1.0, kv_dtype: str = "fp8") -> None:
     torch.ops._C_cache_ops.convert_fp8(output, input, scale, kv_dtype)
+
+
+def merge_attn_states(
+    output: torch.Tensor,
+    prefix_output: torch.Tensor,
+    prefix_lse: torch.Tensor,
+    suffix_output: torch.Tensor,
+    suffix_lse: torch.Tensor,
+    output_lse: torch.Tensor | None = None,
+) -> None:
+    """Argument order of the wrapper the reference dispatches to (reference:
+    vllm_metax/attention/ops/merge_attn_states.py:9-16,39-43; op schema csrc/torch_bindings.cpp:74-82)."""
+    torch.ops._C.merge_attn_states(output, output_lse, prefix_output, prefix_lse, suffix_output, suffix_lse)
+
+
+def copy_blocks(key_caches: list[torch.Tensor], value_caches: list[torch.Tensor], block_mapping: torch.Tensor) -> None:
+    """reference: tests/kernels/attention/test_cache.py:104 -> csrc/cache_kernels.cu:113-163"""
+    torch.ops._C_cache_ops.copy_blocks(key_caches, value_caches, block_mapping)
+
+
+def swap_blocks(src: torch.Tensor, dst: torch.Tensor, block_mapping: torch.Tensor) -> None:
+    """reference: tests/kernels/attention/test_cache.py:422-425 -> csrc/cache_kernels.cu:18-60"""
+    torch.ops._C_cache_ops.swap_blocks(src, dst, block_mapping)
+
+
+def gather_and_maybe_dequant_cache(
+    src_cache: torch.Tensor,
+    dst: torch.Tensor,
+    block_table: torch.Tensor,
+    cu_seq_lens: torch.Tensor,
+    batch_size: int,
+    kv_cache_dtype: str,
+    scale: torch.Tensor,
+    seq_starts: torch.Tensor | None = None,
+) -> None:
+    """reference: tests/kernels/attention/test_cache.py:787-789 -> csrc/cache_kernels.cu:702-773"""
+    torch.ops._C_cache_ops.gather_and_maybe_dequant_cache(src_cache, dst, block_table, cu_seq_lens, batch_size,
+                                                          kv_cache_dtype, scale, seq_starts)
+
+
+def cp_gather_cache(
+    src_cache: torch.Tensor,
+    dst: torch.Tensor,
+    block_table: torch.Tensor,
+    cu_seq_lens: torch.Tensor,
+    batch_size: int,
+    seq_starts: torch.Tensor | None = None,
+) -> None:
+    """reference: tests/kernels/attention/test_cache.py:861 -> csrc/cache_kernels.cu:1075-1134"""
+    torch.ops._C_cache_ops.cp_gather_cache(src_cache, dst, block_table, cu_seq_lens, batch_size, seq_starts)
+
+
+def paged_attention_v1_lse(
+    out: torch.Tensor,
+    lse: torch.Tensor,
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    num_kv_heads: int,
+    scale: float,
+    block_tables: torch.Tensor,
+    seq_lens: torch.Tensor,
+    block_size: int,
+    max_seq_len: int,
+    alibi_slopes: torch.Tensor | None,
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+) -> None:
+    """paged_attention_v1 that also writes lse[num_heads, num_seqs] (natural-log sum-exp of the scaled logits, -inf for
+    an empty sequence) — the operand merge_attn_states needs to merge this decode result with another partial result.
+    Not a reference op (namespace `_C_b200`)."""
+    torch.ops._C_b200.paged_attention_v1_lse(out, lse, query, key_cache, value_cache, num_kv_heads, scale, block_tables,
+                                             seq_lens, block_size, max_seq_len, alibi_slopes, kv_cache_dtype, k_scale,
+                                             v_scale)

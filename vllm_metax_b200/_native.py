@@ -27,6 +27,10 @@ EXPORTED_SYMBOLS = (
     "b200_reshape_and_cache",
     "b200_reshape_and_cache_flash",
     "b200_convert_fp8",
+    "b200_merge_attn_states",
+    "b200_copy_blocks",
+    "b200_swap_blocks",
+    "b200_gather_cache",
     "b200_kv_dtype_from_string",
     "b200_last_error",
     "b200_abi_version",
@@ -70,6 +74,7 @@ class PagedAttnParams(C.Structure):
         ("blocksparse_vert_stride", C.c_int32),
         ("blocksparse_block_size", C.c_int32),
         ("blocksparse_head_sliding_step", C.c_int32),
+        ("out_lse", C.c_void_p),
     ]
 
 
@@ -96,6 +101,48 @@ class CacheWriteParams(C.Structure):
         ("kv_dtype", C.c_int32),
     ]
 
+
+class MergeAttnStatesParams(C.Structure):
+    _fields_ = [
+        ("output", C.c_void_p),
+        ("output_lse", C.c_void_p),
+        ("prefix_output", C.c_void_p),
+        ("prefix_lse", C.c_void_p),
+        ("suffix_output", C.c_void_p),
+        ("suffix_lse", C.c_void_p),
+        ("output_stride", C.c_int64),
+        ("prefix_stride", C.c_int64),
+        ("suffix_stride", C.c_int64),
+        ("num_tokens", C.c_int32),
+        ("num_heads", C.c_int32),
+        ("head_size", C.c_int32),
+        ("dtype", C.c_int32),
+    ]
+
+
+class GatherCacheParams(C.Structure):
+    _fields_ = [
+        ("src_cache", C.c_void_p),
+        ("dst", C.c_void_p),
+        ("block_table", C.c_void_p),
+        ("cu_seq_lens", C.c_void_p),
+        ("seq_starts", C.c_void_p),
+        ("scale", C.c_void_p),
+        ("block_table_stride", C.c_int64),
+        ("cache_block_stride", C.c_int64),
+        ("cache_entry_stride", C.c_int64),
+        ("dst_entry_stride", C.c_int64),
+        ("batch_size", C.c_int32),
+        ("block_size", C.c_int32),
+        ("entry_size", C.c_int32),
+        ("src_dtype", C.c_int32),
+        ("dst_dtype", C.c_int32),
+        ("kv_dtype", C.c_int32),
+        ("token_granular_starts", C.c_int32),
+    ]
+
+
+COPY_D2D, COPY_D2H, COPY_H2D = 0, 1, 2
 
 _lib = None
 
@@ -131,6 +178,15 @@ def load() -> C.CDLL:
     lib.b200_convert_fp8.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_int32, C.c_int32, C.c_int32,
                                      C.c_void_p]
     lib.b200_convert_fp8.restype = C.c_int
+    lib.b200_merge_attn_states.argtypes = [P(MergeAttnStatesParams), C.c_void_p]
+    lib.b200_merge_attn_states.restype = C.c_int
+    lib.b200_copy_blocks.argtypes = [P(C.c_void_p), P(C.c_void_p), C.c_int32, C.c_void_p, C.c_int32, C.c_int64,
+                                     C.c_void_p]
+    lib.b200_copy_blocks.restype = C.c_int
+    lib.b200_swap_blocks.argtypes = [C.c_void_p, C.c_void_p, P(C.c_int64), C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
+    lib.b200_swap_blocks.restype = C.c_int
+    lib.b200_gather_cache.argtypes = [P(GatherCacheParams), C.c_void_p]
+    lib.b200_gather_cache.restype = C.c_int
     lib.b200_kv_dtype_from_string.argtypes = [C.c_char_p]
     lib.b200_kv_dtype_from_string.restype = C.c_int
     lib.b200_last_error.argtypes = []
@@ -181,7 +237,7 @@ def kv_dtype_code(s: str) -> int:
 
 def attn_params(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables, seq_lens, block_size,
                 max_seq_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale, exp_sums=None, max_logits=None,
-                tmp_out=None, workspace=None) -> PagedAttnParams:
+                tmp_out=None, workspace=None, out_lse=None) -> PagedAttnParams:
     p = PagedAttnParams()
     p.out = out.data_ptr()
     p.query = query.data_ptr()
@@ -208,6 +264,8 @@ def attn_params(out, query, key_cache, value_cache, num_kv_heads, scale, block_t
     p.kv_dtype = kv_dtype_code(kv_cache_dtype)
     p.scale = scale
     p.blocksparse_block_size = 64
+    if out_lse is not None:
+        p.out_lse = out_lse.data_ptr()
     return p
 
 
@@ -250,3 +308,15 @@ def reshape_and_cache(p: CacheWriteParams, stream: int) -> None:
 
 def reshape_and_cache_flash(p: CacheWriteParams, stream: int) -> None:
     check(load().b200_reshape_and_cache_flash(C.byref(p), C.c_void_p(stream)))
+
+
+def merge_attn_states(output, prefix_output, prefix_lse, suffix_output, suffix_lse, output_lse, stream: int) -> None:
+    p = MergeAttnStatesParams()
+    p.output = output.data_ptr()
+    p.output_lse = output_lse.data_ptr() if output_lse is not None else None
+    p.prefix_output, p.prefix_lse = prefix_output.data_ptr(), prefix_lse.data_ptr()
+    p.suffix_output, p.suffix_lse = suffix_output.data_ptr(), suffix_lse.data_ptr()
+    p.output_stride, p.prefix_stride, p.suffix_stride = output.stride(0), prefix_output.stride(0), suffix_output.stride(0)
+    p.num_tokens, p.num_heads, p.head_size = output.shape
+    p.dtype = _torch_dtype_code(output.dtype)
+    check(load().b200_merge_attn_states(C.byref(p), C.c_void_p(stream)))

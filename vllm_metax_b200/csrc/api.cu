@@ -107,7 +107,11 @@ int pick_variant(const b200_paged_attn_params_t& p) {
   const char* why = nullptr;
   const bool ok = stream_variant_eligible(p, &why);
   const char* why_u = nullptr;
-  const bool ok_u = umma_fp8_variant_eligible(p, &why_u);
+  bool ok_u = umma_fp8_variant_eligible(p, &why_u);
+  if (ok_u && p.out_lse != nullptr) {
+    ok_u = false;
+    why_u = "the tcgen05 fp8 kernel has no LSE output";
+  }
   if (g_forced_variant == B200_VARIANT_UMMA_FP8) {
     if (!ok_u) {
       set_error("tcgen05 fp8 variant forced but not eligible: %s", why_u);
@@ -140,6 +144,24 @@ uint64_t generic_split_bytes(const b200_paged_attn_params_t& p) {
   return (uint64_t)p.num_seqs * p.num_heads * P * (p.head_size + 2) * sizeof(float);
 }
 
+// Sequences of length 0 own no tile in the streaming schedules, so nothing would write their rows.  When the
+// caller wants the LSE (to merge this result with another one) those rows must be well defined: out = 0, lse = -inf.
+__global__ void init_empty_rows_kernel(const int32_t* seq_lens, void* out, float* lse, int S, int H, int row_bytes) {
+  const int s = blockIdx.x;
+  if (seq_lens[s] > 0) return;
+  uint32_t* o = reinterpret_cast<uint32_t*>(static_cast<char*>(out) + (int64_t)s * row_bytes);
+  for (int i = threadIdx.x; i < row_bytes / 4; i += blockDim.x) o[i] = 0u;
+  for (int h = threadIdx.x; h < H; h += blockDim.x) lse[(int64_t)h * S + s] = -INFINITY;
+}
+
+int init_empty_rows(const b200_paged_attn_params_t& p, cudaStream_t s) {
+  if (p.out_lse == nullptr) return B200_OK;
+  const int row_bytes = p.num_heads * p.head_size * dtype_bytes(p.dtype);  // multiple of 4: head sizes are even
+  init_empty_rows_kernel<<<p.num_seqs, 128, 0, s>>>(p.seq_lens, p.out, p.out_lse, p.num_seqs, p.num_heads, row_bytes);
+  count_launch();
+  return check_launch("paged_attention (empty rows)");
+}
+
 }  // namespace
 }  // namespace b200
 
@@ -153,10 +175,12 @@ extern "C" uint64_t b200_paged_attention_workspace_bytes(const b200_paged_attn_p
 extern "C" int b200_paged_attention_v1(const b200_paged_attn_params_t* p, void* stream) {
   int rc = validate_attn(p, false);
   if (rc != B200_OK) return rc;
-  if (p->num_seqs == 0 || p->max_seq_len == 0) return B200_OK;
+  if (p->num_seqs == 0) return B200_OK;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  rc = init_empty_rows(*p, s);
+  if (rc != B200_OK || p->max_seq_len == 0) return rc;
   const int variant = pick_variant(*p);
   if (variant < 0) return -variant;
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (variant == B200_VARIANT_STREAM_MMA || variant == B200_VARIANT_UMMA_FP8) {
     B200_REQUIRE(p->workspace != nullptr && p->workspace_bytes >= kFlatWorkspaceBytes, B200_ERR_WORKSPACE,
                  "paged_attention_v1 needs %llu bytes of workspace, got %llu", (unsigned long long)kFlatWorkspaceBytes,
@@ -197,10 +221,12 @@ extern "C" int b200_paged_attention_v1(const b200_paged_attn_params_t* p, void* 
 extern "C" int b200_paged_attention_v2(const b200_paged_attn_params_t* p, void* stream) {
   int rc = validate_attn(p, true);
   if (rc != B200_OK) return rc;
-  if (p->num_seqs == 0 || p->max_seq_len == 0) return B200_OK;
+  if (p->num_seqs == 0) return B200_OK;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  rc = init_empty_rows(*p, s);
+  if (rc != B200_OK || p->max_seq_len == 0) return rc;
   const int variant = pick_variant(*p);
   if (variant < 0) return -variant;
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
   // the caller sized exp_sums / max_logits / tmp_out for 512-token partitions
   // (csrc/attention/paged_attention_v2.cu:45,82)
   SplitOut so;

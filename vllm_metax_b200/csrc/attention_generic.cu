@@ -39,9 +39,10 @@ struct GenericParams {
   const float* k_scale;
   const float* v_scale;
   void* out;
+  float* lse;  // optional [H, S] log-sum-exp of the scaled logits (natural log); written with the final output
   SplitOut so;
   int64_t q_stride, kv_block_stride, kv_head_stride;
-  int H, Hkv, G, D, B, max_blocks;
+  int S, H, Hkv, G, D, B, max_blocks;
   float scale;
 };
 
@@ -230,6 +231,8 @@ paged_attention_generic_kernel(GenericParams p) {
         }
       }
     }
+    if (tid < nh && single && p.lse != nullptr)
+      p.lse[(int64_t)(head0 + tid) * p.S + s] = l_s[tid] > 0.f ? m_s[tid] + logf(l_s[tid]) : -INFINITY;
     if (tid < nh && p.so.m != nullptr && (!single || p.so.normalized)) {
       const int64_t pi = ((int64_t)s * p.H + head0 + tid) * p.so.num_partitions + part;
       p.so.m[pi] = m_s[tid];
@@ -245,8 +248,9 @@ paged_attention_generic_kernel(GenericParams p) {
 struct ReduceParams {
   const int32_t* seq_lens;
   void* out;
+  float* lse;  // optional [H, S]
   SplitOut so;
-  int H, D;
+  int S, H, D;
 };
 
 template <typename T, bool NORMALIZED>
@@ -286,6 +290,7 @@ __global__ void __launch_bounds__(kThreads) split_reduce_kernel(ReduceParams p) 
 #pragma unroll
   for (int w = 0; w < kWarps; ++w) sum += red[w];
   const float inv = __fdividef(1.f, sum + 1e-6f);
+  if (tid == 0 && p.lse != nullptr) p.lse[(int64_t)head * p.S + s] = m + logf(sum);
 
   using TO = typename std::conditional<NORMALIZED, T, float>::type;
   const TO* o = reinterpret_cast<const TO*>(p.so.o) + base * p.D;
@@ -313,9 +318,9 @@ int launch_attention_generic(const b200_paged_attn_params_t& p, const SplitOut& 
   GenericParams gp;
   gp.q = p.query; gp.kc = p.key_cache; gp.vc = p.value_cache;
   gp.bt = p.block_tables; gp.seq_lens = p.seq_lens; gp.alibi = p.alibi_slopes;
-  gp.k_scale = p.k_scale; gp.v_scale = p.v_scale; gp.out = p.out; gp.so = so;
+  gp.k_scale = p.k_scale; gp.v_scale = p.v_scale; gp.out = p.out; gp.lse = p.out_lse; gp.so = so;
   gp.q_stride = p.q_stride; gp.kv_block_stride = p.kv_block_stride; gp.kv_head_stride = p.kv_head_stride;
-  gp.H = p.num_heads; gp.Hkv = p.num_kv_heads; gp.G = p.num_heads / p.num_kv_heads;
+  gp.S = p.num_seqs; gp.H = p.num_heads; gp.Hkv = p.num_kv_heads; gp.G = p.num_heads / p.num_kv_heads;
   gp.D = p.head_size; gp.B = p.block_size; gp.max_blocks = p.max_num_blocks_per_seq;
   gp.scale = p.scale;
   const int P = so.num_partitions;
@@ -339,7 +344,8 @@ int launch_attention_generic(const b200_paged_attn_params_t& p, const SplitOut& 
 int launch_split_reduce(const b200_paged_attn_params_t& p, const SplitOut& so, cudaStream_t s) {
   if (so.num_partitions <= 1) return B200_OK;  // every sequence was written directly
   ReduceParams rp;
-  rp.seq_lens = p.seq_lens; rp.out = p.out; rp.so = so; rp.H = p.num_heads; rp.D = p.head_size;
+  rp.seq_lens = p.seq_lens; rp.out = p.out; rp.lse = p.out_lse; rp.so = so; rp.S = p.num_seqs; rp.H = p.num_heads;
+  rp.D = p.head_size;
   dim3 grid(p.num_heads, p.num_seqs), block(kThreads);
   const size_t smem = (size_t)so.num_partitions * sizeof(float);
 #define RUN(T)                                                                   \

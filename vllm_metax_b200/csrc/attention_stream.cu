@@ -415,7 +415,11 @@ paged_attention_stream_kernel(const StreamParams p) {
         o *= vsc;
         const int head = it.kvh * p.G + h;
         const float on = o * __fdividef(1.f, lsum + 1e-6f);
-        if (single) p.out[((int64_t)it.s * p.H + head) * kD + d] = __float2bfloat16_rn(on);
+        if (single) {
+          p.out[((int64_t)it.s * p.H + head) * kD + d] = __float2bfloat16_rn(on);
+          if (d == 0 && p.lse != nullptr)
+            p.lse[(int64_t)head * p.S + it.s] = lsum > 0.f ? fmaf(M, kLn2, logf(lsum)) : -INFINITY;
+        }
         if (want_partials) {
           const int64_t pi = ((int64_t)it.s * p.H + head) * p.so.num_partitions + it.part;
           if (p.so.normalized)
@@ -450,6 +454,8 @@ paged_attention_stream_kernel(const StreamParams p) {
         if (whole) {
           p.out[((int64_t)it.s * p.H + it.kvh * p.G + h) * kD + d] =
               __float2bfloat16_rn(o * __fdividef(1.f, lsum + 1e-6f));
+          if (d == 0 && p.lse != nullptr)
+            p.lse[(int64_t)(it.kvh * p.G + h) * p.S + it.s] = lsum > 0.f ? fmaf(M, kLn2, logf(lsum)) : -INFINITY;
         } else {
           p.ws_o[(int64_t)(slot + h) * kD + d] = o;
           if (d == 0) {
@@ -487,6 +493,8 @@ paged_attention_stream_kernel(const StreamParams p) {
             }
             p.out[((int64_t)it.s * p.H + it.kvh * p.G + h) * kD + d] =
                 __float2bfloat16_rn(o * __fdividef(1.f, lsum + 1e-6f));
+            if (d == 0 && p.lse != nullptr)
+              p.lse[(int64_t)(it.kvh * p.G + h) * p.S + it.s] = fmaf(M, kLn2, logf(lsum));
           }
         }
       }

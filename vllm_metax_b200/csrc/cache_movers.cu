@@ -1,0 +1,243 @@
+// KV-cache block movers and gathers around the decode path:
+//   copy_blocks                      (reference csrc/cache_kernels.cu:64-92, :113-163)
+//   swap_blocks                      (:18-60)
+//   gather_and_maybe_dequant_cache   (:618-773)
+//   cp_gather_cache                  (:775-839, :1075-1134)
+// All of it is byte movement bound by HBM (or PCIe/NVLink-C2C for swaps), so the
+// kernels are 16-byte vectorised copies with the grid spread over every SM; the
+// FP8 gather fuses the e4m3 -> dtype dequantisation (float(e4m3) * scale).
+#include <string.h>
+
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace b200 {
+namespace {
+
+// ---- copy_blocks ---------------------------------------------------------------------------------------
+// The per-layer cache pointers ride in the kernel parameter block (<= kLayersPerLaunch layers per launch),
+// so nothing is staged through device memory and the call neither synchronises nor allocates.
+constexpr int kLayersPerLaunch = 128;
+struct CopyBlocksArgs {
+  uint8_t* key[kLayersPerLaunch];
+  uint8_t* value[kLayersPerLaunch];
+  const int64_t* mapping;
+  int64_t block_bytes;
+};
+
+// grid (pairs, layers * 2, slices): one CTA copies one slice of one block of the K or the V cache of a layer.
+template <bool VEC>
+__global__ void __launch_bounds__(256) copy_blocks_kernel(const __grid_constant__ CopyBlocksArgs a) {
+  const int pair = blockIdx.x;
+  const int layer = blockIdx.y >> 1;
+  uint8_t* base = (blockIdx.y & 1) ? a.value[layer] : a.key[layer];
+  const int64_t src = a.mapping[2 * pair], dst = a.mapping[2 * pair + 1];
+  const uint8_t* s = base + src * a.block_bytes;
+  uint8_t* d = base + dst * a.block_bytes;
+  if constexpr (VEC) {
+    const int64_t n = a.block_bytes >> 4;
+    for (int64_t i = (int64_t)blockIdx.z * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.z * blockDim.x)
+      reinterpret_cast<Vec16*>(d)[i] = ld_global_16(s + (i << 4));
+  } else {
+    for (int64_t i = (int64_t)blockIdx.z * blockDim.x + threadIdx.x; i < a.block_bytes;
+         i += (int64_t)gridDim.z * blockDim.x)
+      d[i] = s[i];
+  }
+}
+
+// ---- gather ----------------------------------------------------------------------------------------------
+// One warp per destination row (token).  grid (batch, splits): a CTA of 8 warps walks the tokens of its
+// slice of one sequence; the block-table entry is read once per token by every lane (broadcast).
+//   MODE 0: same-width byte move, 16-byte vectors      MODE 1: same-width byte move, scalar elements
+//   MODE 2: e4m3 -> T dequantisation, 16 source bytes per lane step   MODE 3: same, scalar
+template <typename T, int MODE>
+__global__ void __launch_bounds__(256) gather_cache_kernel(const b200_gather_cache_params_t p, const int elem_bytes) {
+  const int b = blockIdx.x;
+  const int seq_start = p.cu_seq_lens[b];
+  const int seq_len = p.cu_seq_lens[b + 1] - seq_start;
+  const int per = (seq_len + gridDim.y - 1) / gridDim.y;
+  const int t0 = blockIdx.y * per;
+  const int t1 = min(seq_len, t0 + per);
+  if (t0 >= t1) return;
+  int first = 0;
+  if (p.seq_starts != nullptr) {
+    first = p.seq_starts[b];
+    if (!p.token_granular_starts) first = first / p.block_size * p.block_size;  // cache_kernels.cu:660-662
+  }
+  const int32_t* table = p.block_table + (int64_t)b * p.block_table_stride;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const float scale = (MODE >= 2) ? *p.scale : 0.f;
+  for (int t = t0 + warp; t < t1; t += nwarps) {
+    const int pos = first + t;
+    const int64_t blk = table[pos / p.block_size];
+    const int off = pos % p.block_size;
+    const int64_t src_elt = blk * p.cache_block_stride + (int64_t)off * p.cache_entry_stride;
+    const int64_t dst_elt = (int64_t)(seq_start + t) * p.dst_entry_stride;
+    if constexpr (MODE == 0) {
+      const uint8_t* s = reinterpret_cast<const uint8_t*>(p.src_cache) + src_elt * elem_bytes;
+      uint8_t* d = reinterpret_cast<uint8_t*>(p.dst) + dst_elt * elem_bytes;
+      const int n = (p.entry_size * elem_bytes) >> 4;
+      for (int i = lane; i < n; i += 32) reinterpret_cast<Vec16*>(d)[i] = ld_global_16(s + (i << 4));
+    } else if constexpr (MODE == 1) {
+      const T* s = reinterpret_cast<const T*>(p.src_cache) + src_elt;
+      T* d = reinterpret_cast<T*>(p.dst) + dst_elt;
+      for (int i = lane; i < p.entry_size; i += 32) d[i] = s[i];
+    } else if constexpr (MODE == 2) {
+      const uint8_t* s = reinterpret_cast<const uint8_t*>(p.src_cache) + src_elt;
+      T* d = reinterpret_cast<T*>(p.dst) + dst_elt;
+      for (int i = lane * 16; i < p.entry_size; i += 32 * 16) {
+        const Vec16 v = ld_global_16(s + i);
+        const uint8_t* e = reinterpret_cast<const uint8_t*>(&v);
+        constexpr int kPer = 16 / sizeof(T);  // elements per 16-byte store
+#pragma unroll
+        for (int j = 0; j < 16 / kPer; ++j) {
+          Vec16 o;
+          T* oe = reinterpret_cast<T*>(&o);
+#pragma unroll
+          for (int k = 0; k < kPer; ++k) oe[k] = dequant_e4m3<T>(e[j * kPer + k], scale);
+          *reinterpret_cast<Vec16*>(d + i + j * kPer) = o;
+        }
+      }
+    } else {
+      const uint8_t* s = reinterpret_cast<const uint8_t*>(p.src_cache) + src_elt;
+      T* d = reinterpret_cast<T*>(p.dst) + dst_elt;
+      for (int i = lane; i < p.entry_size; i += 32) d[i] = dequant_e4m3<T>(s[i], scale);
+    }
+  }
+}
+
+inline bool aligned(const void* q, size_t a) { return (reinterpret_cast<uintptr_t>(q) % a) == 0; }
+
+template <typename T, bool FP8>
+void launch_gather(const b200_gather_cache_params_t& p, bool vec, int elem_bytes, dim3 grid, cudaStream_t s) {
+  if constexpr (FP8) {
+    if (vec) gather_cache_kernel<T, 2><<<grid, 256, 0, s>>>(p, elem_bytes);
+    else gather_cache_kernel<T, 3><<<grid, 256, 0, s>>>(p, elem_bytes);
+  } else {
+    if (vec) gather_cache_kernel<T, 0><<<grid, 256, 0, s>>>(p, elem_bytes);
+    else gather_cache_kernel<T, 1><<<grid, 256, 0, s>>>(p, elem_bytes);
+  }
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200_copy_blocks(void* const* key_caches, void* const* value_caches, int32_t num_layers,
+                                const int64_t* block_mapping, int32_t num_pairs, int64_t block_bytes,
+                                void* stream) {
+  using namespace b200;
+  B200_REQUIRE(num_layers >= 0 && num_pairs >= 0 && block_bytes >= 0, B200_ERR_INVALID_ARGUMENT,
+               "bad sizes: layers=%d pairs=%d block_bytes=%lld", num_layers, num_pairs, (long long)block_bytes);
+  if (num_layers == 0 || num_pairs == 0 || block_bytes == 0) return B200_OK;  // cache_kernels.cu:118-120
+  B200_REQUIRE(key_caches && value_caches && block_mapping, B200_ERR_INVALID_ARGUMENT, "NULL pointer");
+  B200_REQUIRE(num_pairs <= 0x7fffffff && num_layers <= 32767, B200_ERR_UNSUPPORTED, "too many layers / pairs");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  for (int l0 = 0; l0 < num_layers; l0 += kLayersPerLaunch) {
+    const int nl = std::min(kLayersPerLaunch, num_layers - l0);
+    CopyBlocksArgs a;
+    memset(&a, 0, sizeof(a));
+    bool vec = block_bytes % 16 == 0;
+    for (int l = 0; l < nl; ++l) {
+      B200_REQUIRE(key_caches[l0 + l] && value_caches[l0 + l], B200_ERR_INVALID_ARGUMENT, "NULL cache pointer");
+      a.key[l] = static_cast<uint8_t*>(key_caches[l0 + l]);
+      a.value[l] = static_cast<uint8_t*>(value_caches[l0 + l]);
+      vec = vec && aligned(a.key[l], 16) && aligned(a.value[l], 16);
+    }
+    a.mapping = block_mapping;
+    a.block_bytes = block_bytes;
+    // slices: enough CTAs to cover the machine a few times over, each moving >= 4 KiB
+    const int64_t ctas = (int64_t)num_pairs * nl * 2;
+    int slices = (int)((4 * (int64_t)device_sm_count() + ctas - 1) / ctas);
+    const int max_slices = (int)std::min<int64_t>(65535, std::max<int64_t>(1, block_bytes / 4096));
+    slices = std::max(1, std::min(slices, max_slices));
+    dim3 grid(num_pairs, nl * 2, slices);
+    if (vec) copy_blocks_kernel<true><<<grid, 256, 0, s>>>(a);
+    else copy_blocks_kernel<false><<<grid, 256, 0, s>>>(a);
+    count_launch();
+    const int rc = check_launch("copy_blocks");
+    if (rc != B200_OK) return rc;
+  }
+  return B200_OK;
+}
+
+extern "C" int b200_swap_blocks(void* dst, const void* src, const int64_t* block_mapping, int64_t num_pairs,
+                                int64_t block_bytes, int32_t kind, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(num_pairs >= 0 && block_bytes >= 0, B200_ERR_INVALID_ARGUMENT, "bad sizes");
+  if (num_pairs == 0 || block_bytes == 0) return B200_OK;
+  B200_REQUIRE(dst && src && block_mapping, B200_ERR_INVALID_ARGUMENT, "NULL pointer");
+  cudaMemcpyKind k;
+  switch (kind) {
+    case B200_COPY_D2D: k = cudaMemcpyDeviceToDevice; break;
+    case B200_COPY_D2H: k = cudaMemcpyDeviceToHost; break;
+    case B200_COPY_H2D: k = cudaMemcpyHostToDevice; break;
+    default: B200_REQUIRE(false, B200_ERR_INVALID_ARGUMENT, "Invalid device combination"); return 0;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int64_t i = 0;
+  while (i < num_pairs) {
+    const int64_t sb = block_mapping[2 * i], db = block_mapping[2 * i + 1];
+    B200_REQUIRE(sb >= 0 && db >= 0, B200_ERR_INVALID_ARGUMENT, "negative block number in block_mapping");
+    int64_t run = 1;  // pairs consecutive on both sides travel as one copy
+    while (i + run < num_pairs && block_mapping[2 * (i + run)] == sb + run &&
+           block_mapping[2 * (i + run) + 1] == db + run)
+      ++run;
+    cudaError_t e = cudaMemcpyAsync(static_cast<char*>(dst) + db * block_bytes,
+                                    static_cast<const char*>(src) + sb * block_bytes, (size_t)(run * block_bytes), k, s);
+    if (e != cudaSuccess) {
+      set_error("swap_blocks: cudaMemcpyAsync failed: %s", cudaGetErrorString(e));
+      return B200_ERR_CUDA;
+    }
+    i += run;
+  }
+  return B200_OK;
+}
+
+extern "C" int b200_gather_cache(const b200_gather_cache_params_t* p, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(p != nullptr, B200_ERR_INVALID_ARGUMENT, "params is NULL");
+  B200_REQUIRE(p->batch_size >= 0 && p->block_size > 0 && p->entry_size > 0, B200_ERR_INVALID_ARGUMENT,
+               "bad sizes: batch=%d block=%d entry=%d", p->batch_size, p->block_size, p->entry_size);
+  if (p->batch_size == 0) return B200_OK;
+  B200_REQUIRE(p->src_cache && p->dst && p->block_table && p->cu_seq_lens, B200_ERR_INVALID_ARGUMENT,
+               "NULL tensor pointer");
+  const bool fp8 = p->kv_dtype == B200_KV_FP8_E4M3;
+  B200_REQUIRE(fp8 || p->kv_dtype == B200_KV_AUTO, B200_ERR_UNSUPPORTED, "Unsupported data type of kv cache: %d",
+               p->kv_dtype);
+  const int sb = dtype_bytes(p->src_dtype), db = dtype_bytes(p->dst_dtype);
+  B200_REQUIRE(sb > 0 && db > 0, B200_ERR_UNSUPPORTED, "Unsupported data type: src=%d dst=%d", p->src_dtype,
+               p->dst_dtype);
+  if (fp8) {
+    B200_REQUIRE(p->src_dtype == B200_DTYPE_U8 && p->dst_dtype != B200_DTYPE_U8, B200_ERR_UNSUPPORTED,
+                 "fp8 gather needs a uint8 cache and a float/half/bf16 destination");
+    B200_REQUIRE(p->scale != nullptr, B200_ERR_INVALID_ARGUMENT, "fp8 gather needs scale");
+  } else {
+    B200_REQUIRE(sb == db, B200_ERR_UNSUPPORTED, "src_cache and dst must have the same dtype");
+  }
+  // splits: cover the machine ~4x with CTAs of 8 warps (the reference fixes 2/4/16, cache_kernels.cu:747)
+  int splits = (4 * device_sm_count() + p->batch_size - 1) / p->batch_size;
+  splits = std::max(1, std::min(splits, 1024));
+  dim3 grid(p->batch_size, splits);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (fp8) {
+    const bool vec = p->entry_size % 16 == 0 && p->cache_block_stride % 16 == 0 && p->cache_entry_stride % 16 == 0 &&
+                     aligned(p->src_cache, 16) && aligned(p->dst, 16) && (p->dst_entry_stride * db) % 16 == 0;
+    switch (p->dst_dtype) {
+      case B200_DTYPE_F32: launch_gather<float, true>(*p, vec, 1, grid, s); break;
+      case B200_DTYPE_F16: launch_gather<__half, true>(*p, vec, 1, grid, s); break;
+      default: launch_gather<__nv_bfloat16, true>(*p, vec, 1, grid, s); break;
+    }
+  } else {
+    const bool vec = ((int64_t)p->entry_size * sb) % 16 == 0 && (p->cache_block_stride * sb) % 16 == 0 &&
+                     (p->cache_entry_stride * sb) % 16 == 0 && (p->dst_entry_stride * sb) % 16 == 0 &&
+                     aligned(p->src_cache, 16) && aligned(p->dst, 16);
+    switch (sb) {
+      case 4: launch_gather<uint32_t, false>(*p, vec, 4, grid, s); break;
+      case 2: launch_gather<uint16_t, false>(*p, vec, 2, grid, s); break;
+      default: launch_gather<uint8_t, false>(*p, vec, 1, grid, s); break;
+    }
+  }
+  count_launch();
+  return check_launch("gather_cache");
+}

@@ -35,6 +35,7 @@ struct StreamParams {
   const float* k_scale;
   const float* v_scale;
   __nv_bfloat16* out;
+  float* lse;               // optional [H, S] log-sum-exp of the scaled logits (natural log), with the final output
   SplitOut so;              // item schedule only
   float* ws_o;              // flat schedule: slots [cta][2][kFlatMaxGroup][kD] (unnormalised partial outputs)
   float* ws_m;              //                      [cta][2][kFlatMaxGroup]     (max logit, log2 units)
@@ -379,6 +380,7 @@ StreamParams fill_stream_params(const b200_paged_attn_params_t& p) {
   sp.bt = p.block_tables; sp.seq_lens = p.seq_lens; sp.alibi = p.alibi_slopes;
   sp.k_scale = p.k_scale; sp.v_scale = p.v_scale;
   sp.out = static_cast<__nv_bfloat16*>(p.out);
+  sp.lse = p.out_lse;
   sp.q_stride = p.q_stride;
   sp.kv_block_stride = p.kv_block_stride * eb;
   sp.kv_head_stride = p.kv_head_stride * eb;

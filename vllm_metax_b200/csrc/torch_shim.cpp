@@ -16,6 +16,9 @@
 #include <torch/library.h>
 #include <torch/types.h>
 
+#include <string.h>
+
+#include <algorithm>
 #include <memory>
 #include <mutex>
 #include <optional>
@@ -161,6 +164,78 @@ void paged_attention_v1(at::Tensor& out, at::Tensor& query, at::Tensor& key_cach
   check_status(b200_paged_attention_v1(&p, stream), "paged_attention_v1");
 }
 
+// Not a reference op: paged_attention_v1 that also returns the log-sum-exp of the scaled logits,
+// lse [num_heads, num_seqs] float32 — the second operand merge_attn_states needs (csrc/attention/merge_attn_states.cu:43-44)
+// when a decode result is merged with another partial result (cascade attention, decode context parallel:
+// vllm_metax/v1/attention/backends/flash_attn.py:794-872).  Registered under `_C_b200`, outside the reference namespaces.
+void paged_attention_v1_lse(at::Tensor& out, at::Tensor& lse, at::Tensor& query, at::Tensor& key_cache,
+                            at::Tensor& value_cache, int64_t num_kv_heads, double scale, at::Tensor& block_tables,
+                            at::Tensor& seq_lens, int64_t block_size, int64_t max_seq_len,
+                            const std::optional<at::Tensor>& alibi_slopes, const std::string& kv_cache_dtype,
+                            at::Tensor& k_scale, at::Tensor& v_scale) {
+  b200_paged_attn_params_t p;
+  fill_attn_params(p, out, query, key_cache, value_cache, num_kv_heads, scale, block_tables, seq_lens, block_size,
+                   max_seq_len, alibi_slopes, kv_cache_dtype, k_scale, v_scale, 0, 0, 0, 64, 0);
+  TORCH_CHECK(lse.is_cuda() && lse.scalar_type() == at::kFloat && lse.is_contiguous() && lse.dim() == 2 &&
+                  lse.size(0) == query.size(1) && lse.size(1) == query.size(0),
+              "lse must be a contiguous float32 CUDA tensor [num_heads, num_seqs]");
+  p.out_lse = lse.data_ptr<float>();
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  p.workspace_bytes = b200_paged_attention_workspace_bytes(&p);
+  p.workspace = v1_workspace(p.workspace_bytes, query, stream);
+  check_status(b200_paged_attention_v1(&p, stream), "paged_attention_v1_lse");
+}
+
+// csrc/ops.h (merge_attn_states) ; csrc/attention/merge_attn_states.cu:129-178
+void merge_attn_states(at::Tensor& output, std::optional<at::Tensor> output_lse, const at::Tensor& prefix_output,
+                       const at::Tensor& prefix_lse, const at::Tensor& suffix_output, const at::Tensor& suffix_lse) {
+  const int dt = to_dtype(output.scalar_type());
+  TORCH_CHECK(dt == B200_DTYPE_F32 || dt == B200_DTYPE_F16 || dt == B200_DTYPE_BF16,
+              "Unsupported data type of O: ", output.scalar_type());  // merge_attn_states.cu:104
+  TORCH_CHECK(output.dim() == 3 && prefix_output.sizes() == output.sizes() && suffix_output.sizes() == output.sizes(),
+              "output / prefix_output / suffix_output must share the shape [num_tokens, num_heads, head_size]");
+  TORCH_CHECK(prefix_output.scalar_type() == output.scalar_type() && suffix_output.scalar_type() == output.scalar_type(),
+              "output / prefix_output / suffix_output dtypes differ");
+  const int64_t N = output.size(0), H = output.size(1), D = output.size(2);
+  const int64_t pack = 16 / output.element_size();
+  TORCH_CHECK(D % pack == 0, "headsize must be multiple of pack_size:", pack);  // :138-139
+  TORCH_CHECK(output.stride(-2) == D && output.stride(-1) == 1, "output heads must be contiguous in memory");
+  TORCH_CHECK(prefix_output.stride(-2) == D && prefix_output.stride(-1) == 1,
+              "prefix_output heads must be contiguous in memory");
+  TORCH_CHECK(suffix_output.stride(-2) == D && suffix_output.stride(-1) == 1,
+              "suffix_output heads must be contiguous in memory");
+  TORCH_CHECK(prefix_lse.scalar_type() == at::kFloat && suffix_lse.scalar_type() == at::kFloat &&
+                  prefix_lse.is_contiguous() && suffix_lse.is_contiguous() && prefix_lse.numel() == H * N &&
+                  suffix_lse.numel() == H * N,
+              "prefix_lse / suffix_lse must be contiguous float32 [num_heads, num_tokens]");
+  TORCH_CHECK(output.is_cuda() && prefix_output.is_cuda() && suffix_output.is_cuda() && prefix_lse.is_cuda() &&
+                  suffix_lse.is_cuda(),
+              "all tensors must be on the CUDA device");
+  b200_merge_attn_states_params_t p;
+  memset(&p, 0, sizeof(p));
+  p.output = output.data_ptr();
+  if (output_lse.has_value() && output_lse->defined()) {
+    TORCH_CHECK(output_lse->scalar_type() == at::kFloat && output_lse->is_contiguous() && output_lse->numel() == H * N &&
+                    output_lse->is_cuda(),
+                "output_lse must be contiguous float32 [num_heads, num_tokens]");
+    p.output_lse = output_lse->data_ptr<float>();
+  }
+  p.prefix_output = prefix_output.data_ptr();
+  p.prefix_lse = prefix_lse.data_ptr<float>();
+  p.suffix_output = suffix_output.data_ptr();
+  p.suffix_lse = suffix_lse.data_ptr<float>();
+  p.output_stride = output.stride(0);
+  p.prefix_stride = prefix_output.stride(0);
+  p.suffix_stride = suffix_output.stride(0);
+  p.num_tokens = static_cast<int32_t>(N);
+  p.num_heads = static_cast<int32_t>(H);
+  p.head_size = static_cast<int32_t>(D);
+  p.dtype = dt;
+  const at::cuda::OptionalCUDAGuard guard(device_of(prefix_output));
+  check_status(b200_merge_attn_states(&p, at::cuda::getCurrentCUDAStream()), "merge_attn_states");
+}
+
 // csrc/ops.h:43-53
 void paged_attention_v2(at::Tensor& out, at::Tensor& exp_sums, at::Tensor& max_logits, at::Tensor& tmp_out,
                         at::Tensor& query, at::Tensor& key_cache, at::Tensor& value_cache, int64_t num_kv_heads,
@@ -296,6 +371,150 @@ void convert_fp8(at::Tensor& dst_cache, at::Tensor& src_cache, const double scal
                "convert_fp8");
 }
 
+// csrc/cache.h ; csrc/cache_kernels.cu:18-60
+void swap_blocks(at::Tensor& src, at::Tensor& dst, const at::Tensor& block_mapping) {
+  int kind;
+  if (src.is_cuda() && dst.is_cuda()) {
+    TORCH_CHECK(src.get_device() == dst.get_device(), "src and dst must be on the same GPU");
+    kind = B200_COPY_D2D;
+  } else if (src.is_cuda() && dst.is_cpu()) {
+    kind = B200_COPY_D2H;
+  } else if (src.is_cpu() && dst.is_cuda()) {
+    kind = B200_COPY_H2D;
+  } else {
+    TORCH_CHECK(false, "Invalid device combination");
+  }
+  TORCH_CHECK(block_mapping.device().is_cpu(), "block_mapping must be on CPU");
+  TORCH_CHECK(block_mapping.scalar_type() == at::kLong && block_mapping.dim() == 2 && block_mapping.size(1) == 2,
+              "block_mapping must be an int64 tensor [num_pairs, 2]");
+  const at::Tensor mapping = block_mapping.contiguous();
+  // stride, not numel: blocks may be padded (cache_kernels.cu:43-46)
+  const int64_t block_bytes = src.element_size() * src.stride(0);
+  TORCH_CHECK(dst.element_size() * dst.stride(0) == block_bytes, "src and dst blocks differ in size");
+  const at::cuda::OptionalCUDAGuard guard(src.is_cuda() ? src.device() : dst.device());
+  check_status(b200_swap_blocks(dst.data_ptr(), src.data_ptr(), mapping.data_ptr<int64_t>(), mapping.size(0),
+                                block_bytes, kind, at::cuda::getCurrentCUDAStream()),
+               "swap_blocks");
+}
+
+// csrc/cache.h ; csrc/cache_kernels.cu:113-163
+void copy_blocks(std::vector<at::Tensor> const& key_caches, std::vector<at::Tensor> const& value_caches,
+                 const at::Tensor& block_mapping) {
+  const size_t num_layers = key_caches.size();
+  TORCH_CHECK(num_layers == value_caches.size());
+  if (num_layers == 0) return;
+  TORCH_CHECK(key_caches[0].is_cuda());
+  TORCH_CHECK(block_mapping.is_cuda() && block_mapping.scalar_type() == at::kLong && block_mapping.is_contiguous() &&
+                  block_mapping.dim() == 2 && block_mapping.size(1) == 2,
+              "block_mapping must be a contiguous int64 CUDA tensor [num_pairs, 2]");
+  std::vector<void*> kp(num_layers), vp(num_layers);
+  const int64_t block_bytes = key_caches[0][0].numel() * key_caches[0].element_size();  // cache_kernels.cu:148
+  for (size_t l = 0; l < num_layers; ++l) {
+    TORCH_CHECK(key_caches[l].device() == key_caches[0].device() && value_caches[l].device() == key_caches[0].device(),
+                "all caches must be on the same device");
+    kp[l] = key_caches[l].data_ptr();
+    vp[l] = value_caches[l].data_ptr();
+  }
+  const at::cuda::OptionalCUDAGuard guard(key_caches[0].device());
+  check_status(b200_copy_blocks(kp.data(), vp.data(), static_cast<int32_t>(num_layers), block_mapping.data_ptr<int64_t>(),
+                                static_cast<int32_t>(block_mapping.size(0)), block_bytes,
+                                at::cuda::getCurrentCUDAStream()),
+               "copy_blocks");
+}
+
+void fill_gather_params(b200_gather_cache_params_t& p, const at::Tensor& src_cache, const at::Tensor& dst,
+                        const at::Tensor& block_table, const at::Tensor& cu_seq_lens, int64_t batch_size,
+                        const std::optional<at::Tensor>& seq_starts) {
+  TORCH_CHECK(block_table.scalar_type() == at::kInt, "block_table must be int32");
+  TORCH_CHECK(cu_seq_lens.scalar_type() == at::kInt, "cu_seq_lens must be int32");
+  TORCH_CHECK(src_cache.is_cuda(), "src_cache must be on a GPU");
+  TORCH_CHECK(src_cache.device() == dst.device(), "src_cache and dst must be on the same device");
+  TORCH_CHECK(src_cache.device() == block_table.device(), "src_cache and block_table must be on the same device");
+  TORCH_CHECK(src_cache.device() == cu_seq_lens.device(), "src_cache and cu_seq_lens must be on the same device");
+  TORCH_CHECK(src_cache.dim() >= 3, "src_cache must be [num_blocks, block_size, entries...]");
+  TORCH_CHECK(cu_seq_lens.is_contiguous() && cu_seq_lens.numel() >= batch_size + 1, "cu_seq_lens needs batch_size + 1 entries");
+  TORCH_CHECK(block_table.dim() == 2 && block_table.stride(1) == 1 && block_table.size(0) >= batch_size,
+              "block_table must be [batch, blocks] with contiguous rows");
+  memset(&p, 0, sizeof(p));
+  p.src_cache = src_cache.data_ptr();
+  p.dst = dst.data_ptr();
+  p.block_table = block_table.data_ptr<int32_t>();
+  p.cu_seq_lens = cu_seq_lens.data_ptr<int32_t>();
+  if (seq_starts.has_value() && seq_starts->defined()) {
+    TORCH_CHECK(seq_starts->scalar_type() == at::kInt, "seq_starts must be int32");
+    TORCH_CHECK(src_cache.device() == seq_starts->device(), "src_cache and seq_starts must be on the same device");
+    TORCH_CHECK(seq_starts->is_contiguous() && seq_starts->numel() >= batch_size, "seq_starts needs batch_size entries");
+    p.seq_starts = seq_starts->data_ptr<int32_t>();
+  }
+  int64_t entry = 1;
+  for (int64_t i = 2; i < src_cache.dim(); ++i) entry *= src_cache.size(i);  // flatten(2, -1), cache_kernels.cu:720
+  // the entry (and each dst row) must be one contiguous run
+  int64_t expect = 1;
+  for (int64_t i = src_cache.dim() - 1; i >= 2; --i) {
+    TORCH_CHECK(src_cache.size(i) == 1 || src_cache.stride(i) == expect, "src_cache entries must be contiguous");
+    expect *= src_cache.size(i);
+  }
+  TORCH_CHECK(dst.dim() >= 2 && dst.numel() == dst.size(0) * entry, "dst must be [tot_tokens, entries...]");
+  p.block_table_stride = block_table.stride(0);
+  p.cache_block_stride = src_cache.stride(0);
+  p.cache_entry_stride = src_cache.stride(1);
+  p.dst_entry_stride = dst.stride(0);
+  p.batch_size = static_cast<int32_t>(batch_size);
+  p.block_size = static_cast<int32_t>(src_cache.size(1));
+  p.entry_size = static_cast<int32_t>(entry);
+}
+
+int width_dtype(int64_t bytes) {
+  switch (bytes) {
+    case 4: return B200_DTYPE_F32;
+    case 2: return B200_DTYPE_F16;
+    case 1: return B200_DTYPE_U8;
+    default: return -1;
+  }
+}
+
+// csrc/cache.h ; csrc/cache_kernels.cu:702-773
+void gather_and_maybe_dequant_cache(const at::Tensor& src_cache, const at::Tensor& dst, const at::Tensor& block_table,
+                                    const at::Tensor& cu_seq_lens, int64_t batch_size,
+                                    const std::string& kv_cache_dtype, const at::Tensor& scale,
+                                    std::optional<at::Tensor> seq_starts) {
+  b200_gather_cache_params_t p;
+  fill_gather_params(p, src_cache, dst, block_table, cu_seq_lens, batch_size, seq_starts);
+  const int kv = kv_dtype_or_throw(kv_cache_dtype);
+  p.kv_dtype = kv;
+  p.token_granular_starts = 0;
+  if (kv == B200_KV_AUTO) {
+    TORCH_CHECK(src_cache.scalar_type() == dst.scalar_type(), "kv_cache_dtype 'auto' needs src_cache of the dst dtype");
+    p.src_dtype = p.dst_dtype = width_dtype(dst.element_size());
+    TORCH_CHECK(p.src_dtype >= 0, "Unsupported data type width: ", dst.element_size() * 8);
+  } else {
+    TORCH_CHECK(is_cache_byte_type(src_cache.scalar_type()), "fp8 kv cache must be stored as uint8");
+    const int dt = to_dtype(dst.scalar_type());
+    TORCH_CHECK(dt == B200_DTYPE_F32 || dt == B200_DTYPE_F16 || dt == B200_DTYPE_BF16, "Unsupported data type: ",
+                dst.scalar_type());
+    TORCH_CHECK(scale.is_cuda() && scale.scalar_type() == at::kFloat, "scale must be a float32 CUDA tensor");
+    p.src_dtype = B200_DTYPE_U8;
+    p.dst_dtype = dt;
+    p.scale = scale.data_ptr<float>();
+  }
+  const at::cuda::OptionalCUDAGuard guard(device_of(src_cache));
+  check_status(b200_gather_cache(&p, at::cuda::getCurrentCUDAStream()), "gather_and_maybe_dequant_cache");
+}
+
+// csrc/cache.h ; csrc/cache_kernels.cu:1075-1134
+void cp_gather_cache(const at::Tensor& src_cache, const at::Tensor& dst, const at::Tensor& block_table,
+                     const at::Tensor& cu_seq_lens, int64_t batch_size, std::optional<at::Tensor> seq_starts) {
+  b200_gather_cache_params_t p;
+  fill_gather_params(p, src_cache, dst, block_table, cu_seq_lens, batch_size, seq_starts);
+  TORCH_CHECK(src_cache.scalar_type() == dst.scalar_type(), "src_cache and dst must have the same dtype");
+  p.kv_dtype = B200_KV_AUTO;
+  p.token_granular_starts = 1;
+  p.src_dtype = p.dst_dtype = width_dtype(src_cache.element_size());
+  TORCH_CHECK(p.src_dtype >= 0, "Unsupported data type width: ", src_cache.element_size() * 8);
+  const at::cuda::OptionalCUDAGuard guard(device_of(src_cache));
+  check_status(b200_gather_cache(&p, at::cuda::getCurrentCUDAStream()), "cp_gather_cache");
+}
+
 const char* kSchemaV1 =
     "paged_attention_v1("
     "    Tensor! out, Tensor query, Tensor key_cache,"
@@ -334,6 +553,35 @@ const char* kSchemaConvert =
     "convert_fp8(Tensor! dst_cache, Tensor src_cache, float scale, "
     "str kv_cache_dtype) -> ()";
 
+// csrc/torch_bindings.cpp:74-82
+const char* kSchemaMerge =
+    "merge_attn_states("
+    "    Tensor! output,"
+    "    Tensor!? output_lse,"
+    "    Tensor prefix_output,"
+    "    Tensor prefix_lse,"
+    "    Tensor suffix_output,"
+    "    Tensor suffix_lse) -> ()";
+// csrc/torch_bindings.cpp:380, :385-386, :431-435, :440-441
+const char* kSchemaSwap = "swap_blocks(Tensor src, Tensor! dst, Tensor block_mapping) -> ()";
+const char* kSchemaCopy =
+    "copy_blocks(Tensor(a!)[] key_caches, Tensor[](b!) value_caches, "
+    "Tensor block_mapping) -> ()";
+const char* kSchemaGather =
+    "gather_and_maybe_dequant_cache(Tensor src_cache, Tensor! dst, "
+    "                               Tensor block_table, Tensor cu_seq_lens, "
+    "                               int batch_size, "
+    "                               str kv_cache_dtype, "
+    "                               Tensor scale, Tensor? seq_starts) -> ()";
+const char* kSchemaCpGather =
+    "cp_gather_cache(Tensor src_cache, Tensor! dst, Tensor block_table, "
+    "Tensor cu_seq_lens, int batch_size, Tensor? seq_starts) -> ()";
+// ours (namespace _C_b200): decode attention that also returns the LSE
+const char* kSchemaV1Lse =
+    "paged_attention_v1_lse(Tensor! out, Tensor! lse, Tensor query, Tensor key_cache, Tensor value_cache, "
+    "int num_kv_heads, float scale, Tensor block_tables, Tensor seq_lens, int block_size, int max_seq_len, "
+    "Tensor? alibi_slopes, str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()";
+
 bool op_exists(const char* qualified) {
   return c10::Dispatcher::singleton().findSchema({qualified, ""}).has_value();
 }
@@ -342,6 +590,13 @@ template <typename F>
 void register_op(std::vector<std::unique_ptr<torch::Library>>& keep, const char* ns, const char* name,
                  const char* schema, F* fn) {
   const std::string qualified = std::string(ns) + "::" + name;
+  if (auto h = c10::Dispatcher::singleton().findSchema({qualified.c_str(), ""})) {
+    // another library (upstream vllm._C) already defined this op.  Newer upstream releases changed some of these
+    // signatures (swap_blocks, gather_and_maybe_dequant_cache, merge_attn_states); a kernel with the reference's
+    // argument list must not be bound to a different schema, so such ops keep their upstream implementation.
+    const size_t nargs = std::count(schema, schema + strlen(schema), ',') + 1;
+    if (h->schema().arguments().size() != nargs) return;
+  }
   if (!op_exists(qualified.c_str())) {
     auto frag = std::make_unique<torch::Library>(torch::Library::FRAGMENT, ns, std::nullopt, __FILE__, __LINE__);
     frag->def(schema);
@@ -361,6 +616,12 @@ void register_all() {
     register_op(keep, "_C_cache_ops", "reshape_and_cache", kSchemaReshape, &reshape_and_cache);
     register_op(keep, "_C_cache_ops", "reshape_and_cache_flash", kSchemaReshapeFlash, &reshape_and_cache_flash);
     register_op(keep, "_C_cache_ops", "convert_fp8", kSchemaConvert, &convert_fp8);
+    register_op(keep, "_C", "merge_attn_states", kSchemaMerge, &merge_attn_states);
+    register_op(keep, "_C_cache_ops", "swap_blocks", kSchemaSwap, &swap_blocks);
+    register_op(keep, "_C_cache_ops", "copy_blocks", kSchemaCopy, &copy_blocks);
+    register_op(keep, "_C_cache_ops", "gather_and_maybe_dequant_cache", kSchemaGather, &gather_and_maybe_dequant_cache);
+    register_op(keep, "_C_cache_ops", "cp_gather_cache", kSchemaCpGather, &cp_gather_cache);
+    register_op(keep, "_C_b200", "paged_attention_v1_lse", kSchemaV1Lse, &paged_attention_v1_lse);
   });
 }
 
