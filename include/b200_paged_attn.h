@@ -144,6 +144,9 @@ typedef struct b200_paged_attn_params {
    * output).  A sequence of length 0 yields -inf.  Feeds b200_merge_attn_states
    * (cascade / decode-context-parallel, vllm_metax/v1/attention/backends/flash_attn.py:794-872). */
   float* out_lse;
+  /* ABI v2, b200_paged_attention_flash only: stride between consecutive tokens
+   * of a block (key_cache.stride(1)), elements. */
+  int64_t kv_page_stride;
 } b200_paged_attn_params_t;
 
 /* Replaces torch.ops._C.paged_attention_v1 (csrc/torch_bindings.cpp:45-55;
@@ -154,6 +157,24 @@ int b200_paged_attention_v1(const b200_paged_attn_params_t* params, void* stream
  * (csrc/torch_bindings.cpp:58-69; csrc/attention/paged_attention_v2.cu:167-192;
  * csrc/attention/attention_kernels.cuh:556-658). */
 int b200_paged_attention_v2(const b200_paged_attn_params_t* params, void* stream);
+
+/*
+ * Decode attention over the FLASH cache layout — the layout reshape_and_cache_flash
+ * writes and the reference's serving path reads through the external flash-attention
+ * library: flash_attn_with_kvcache(q, k_cache, v_cache, block_table, cache_seqlens,
+ * softmax_scale, causal=True, alibi_slopes, ...) with one query token per sequence
+ * (vllm_metax/v1/attention/backends/flash_attn.py:742-757; import in
+ * vllm_metax/attention/utils/fa_utils.py:12).  Same math and arguments as
+ * b200_paged_attention_v1, except
+ *   key_cache / value_cache [num_blocks, block_size, num_kv_heads, head_size]
+ *       addressed by kv_block_stride (stride 0), kv_page_stride (stride 1) and
+ *       kv_head_stride (stride 2): NHD and HND storage both work (csrc/cache_kernels.cu:303);
+ *   supported: bf16 query and cache (kv_dtype auto — the reference's flash path has
+ *       no fp8 cache: fa_utils.py:26-30), head_size 128, block_size a multiple of 16,
+ *       GQA group <= 16; anything else -> B200_ERR_UNSUPPORTED;
+ *   out_lse (optional) as for v1; workspace as for v1.
+ */
+int b200_paged_attention_flash(const b200_paged_attn_params_t* params, void* stream);
 
 /* Bytes of workspace b200_paged_attention_v1 needs for these shapes (pointer
  * fields of params are ignored).  Host-only, no CUDA call. */

@@ -159,6 +159,33 @@ def make_merge(ref_fn):
         print("wrote", name, ref_out.dtype, tuple(ref_out.shape))
 
 
+REF_UNIFIED_TEST = "/root/reference/tests/kernels/attention/test_triton_unified_attention.py"
+
+
+def make_flash():
+    """Flash-layout decode goldens: the reference's ref_paged_attn (test_triton_unified_attention.py:25-76),
+    cut out unmodified, run with query_lens = 1."""
+    tree = ast.parse(open(REF_UNIFIED_TEST).read())
+    ns = {"torch": torch, "Optional": Optional}
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name == "ref_paged_attn":
+            exec(compile(ast.Module(body=[node], type_ignores=[]), REF_UNIFIED_TEST, "exec"), ns)
+    ref_fn = ns["ref_paged_attn"]
+    cases = [  # name, S, H, Hkv, D, B, L, NB, hnd
+        ("flash_bf16_gqa4_nhd", 3, 8, 2, 128, 16, 150, 40, False),
+        ("flash_bf16_gqa8_hnd_b32", 2, 8, 1, 128, 32, 130, 12, True),
+    ]
+    for idx, (name, S, H, Hkv, D, B, L, NB, hnd) in enumerate(cases):
+        d = orc.make_flash_decode_inputs(S, H, Hkv, D, B, L, NB, seed=200 + idx, hnd=hnd)
+        lens = d["seq_lens"].tolist()
+        # ref_paged_attn scales its query argument in place (:46) and views the cache (:51): hand it copies
+        out = ref_fn(d["query"].clone(), d["key_cache"].contiguous(), d["value_cache"].contiguous(), [1] * S, lens,
+                     d["block_tables"], d["scale"])
+        d["ref_out"] = out
+        torch.save(d, os.path.join(HERE, name + ".pt"))
+        print("wrote", name, tuple(out.shape))
+
+
 def make_movers():
     """copy_blocks / gather goldens: the reference tests' own expectation loops, transcribed next to their lines."""
     rnd = random.Random(5)
@@ -220,3 +247,4 @@ if __name__ == "__main__":
     make_cache()
     make_merge(load_reference_merge())
     make_movers()
+    make_flash()

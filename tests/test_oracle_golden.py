@@ -125,3 +125,30 @@ def test_paged_attention_lse_merges_back_to_full_attention():
     full_lse = orc.paged_attention_lse(d["query"], d["key_cache"], d["value_cache"], d["block_tables"], lens, d["scale"])
     torch.testing.assert_close(out.double(), full, atol=1e-5, rtol=1e-5)
     torch.testing.assert_close(lse, full_lse, atol=1e-5, rtol=1e-5)
+
+
+FLASH = sorted(glob.glob(os.path.join(GOLDEN, "flash_*.pt")))
+
+
+@pytest.mark.parametrize("path", FLASH, ids=[os.path.basename(p)[:-3] for p in FLASH])
+def test_flash_layout_oracle_matches_reference_ref_paged_attn(path):
+    """oracle.paged_attention_flash against the reference's ref_paged_attn
+    (tests/kernels/attention/test_triton_unified_attention.py:25-76, run by make_golden.py)."""
+    assert len(FLASH) >= 2
+    d = torch.load(path)
+    out = orc.paged_attention_flash(d["query"], d["key_cache"], d["value_cache"], d["block_tables"], d["seq_lens"],
+                                    d["scale"])
+    assert torch.equal(out, d["ref_out"])
+
+
+def test_flash_and_v1_layout_oracles_agree():
+    """The same keys/values stored in the v1/v2 layout and in the flash layout give the same attention (the two
+    reference oracles differ only in where the scale is applied)."""
+    S, H, Hkv, D, B, L, NB = 3, 8, 2, 128, 16, 100, 32
+    d = orc.make_flash_decode_inputs(S, H, Hkv, D, B, L, NB, seed=9)
+    x = 8
+    kc = d["key_cache"].permute(0, 2, 3, 1).reshape(NB, Hkv, D // x, x, B).permute(0, 1, 2, 4, 3).contiguous()
+    vc = d["value_cache"].permute(0, 2, 3, 1).contiguous()
+    a = orc.paged_attention_flash(d["query"], d["key_cache"], d["value_cache"], d["block_tables"], d["seq_lens"], d["scale"])
+    b = orc.paged_attention(d["query"], kc, vc, d["block_tables"], d["seq_lens"], d["scale"])
+    torch.testing.assert_close(a.float(), b.float(), atol=1e-3, rtol=1e-2)

@@ -40,6 +40,8 @@ def main():
     ap.add_argument("--L", type=int, default=4096)
     ap.add_argument("--fp8", action="store_true")
     ap.add_argument("--v2", action="store_true")
+    ap.add_argument("--flash", action="store_true", help="flash cache layout [NB, B, Hkv, D] (paged_attention_flash)")
+    ap.add_argument("--hnd", action="store_true", help="with --flash: HND storage [NB, Hkv, B, D]")
     ap.add_argument("--iters", type=int, default=30)
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--check", action="store_true", help="compare against the generic FMA kernel")
@@ -51,7 +53,26 @@ def main():
     kvd = "fp8" if a.fp8 else "auto"
     _native.set_attention_variant(a.variant)
     P = (a.L + 511) // 512
-    if a.v2:
+    if a.flash:
+        # same values, re-laid out: [NB, Hkv, D/x, B, x] -> [NB, B, Hkv, D]
+        NB = kc.shape[0]
+        kf = kc.permute(0, 3, 1, 2, 4).reshape(NB, a.B, a.Hkv, a.D)
+        vf = vc.permute(0, 3, 1, 2)
+        if a.hnd:
+            kf = kf.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+            vf = vf.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+        else:
+            kf, vf = kf.contiguous(), vf.contiguous()
+        fn = lambda: ops.paged_attention_flash(out, q, kf, vf, scale, bt, lens, a.L)
+        if a.check:
+            ref = torch.empty_like(q)
+            ops.paged_attention_v1(ref, q, kc, vc, a.Hkv, scale, bt, lens, a.B, a.L, None, kvd, one, one)
+            fn()
+            torch.cuda.synchronize()
+            print("check flash vs v1 layout: max abs diff %.3e (ref max %.3e)" % (
+                (ref.float() - out.float()).abs().max().item(), ref.float().abs().max().item()))
+            a.check = False
+    elif a.v2:
         tmp = torch.empty(a.S, a.H, P, a.D, dtype=q.dtype, device="cuda")
         es = torch.empty(a.S, a.H, P, dtype=torch.float32, device="cuda")
         ml = torch.empty_like(es)
@@ -81,7 +102,7 @@ def main():
     eb = 1 if a.fp8 else 2
     kvbytes = a.S * a.L * a.Hkv * a.D * 2 * eb
     total = kvbytes + a.S * a.H * a.D * 4 + a.S * math.ceil(a.L / a.B) * 4 + 4 * a.S
-    print("cfg S=%d H=%d Hkv=%d D=%d B=%d L=%d fp8=%d v2=%d variant=%d: median %.1f us  min %.1f us  -> %.0f GB/s (median) %.0f GB/s (best)  [%.3f GB]" % (
+    print(("flash %s " % ("hnd" if a.hnd else "nhd") if a.flash else "") + "cfg S=%d H=%d Hkv=%d D=%d B=%d L=%d fp8=%d v2=%d variant=%d: median %.1f us  min %.1f us  -> %.0f GB/s (median) %.0f GB/s (best)  [%.3f GB]" % (
         a.S, a.H, a.Hkv, a.D, a.B, a.L, a.fp8, a.v2, _native.last_attention_variant(), med * 1e3, ts[0] * 1e3,
         total / med / 1e6, total / ts[0] / 1e6, total / 1e9))
 

@@ -179,3 +179,24 @@ def paged_attention_v1_lse(
     torch.ops._C_b200.paged_attention_v1_lse(out, lse, query, key_cache, value_cache, num_kv_heads, scale, block_tables,
                                              seq_lens, block_size, max_seq_len, alibi_slopes, kv_cache_dtype, k_scale,
                                              v_scale)
+
+
+def paged_attention_flash(
+    out: torch.Tensor,
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    scale: float,
+    block_tables: torch.Tensor,
+    seq_lens: torch.Tensor,
+    max_seq_len: int,
+    alibi_slopes: torch.Tensor | None = None,
+    lse: torch.Tensor | None = None,
+) -> None:
+    """Decode attention over the flash cache layout [num_blocks, block_size, num_kv_heads, head_size] (NHD or HND
+    strides) written by reshape_and_cache_flash; one query token per sequence.  Not a reference op (namespace
+    `_C_b200`): the reference gets this from flash_attn_with_kvcache of the external flash-attention library
+    (reference: vllm_metax/v1/attention/backends/flash_attn.py:742-757); see attention/flash_decode.py for the wrapper
+    with that signature."""
+    torch.ops._C_b200.paged_attention_flash(out, lse, query, key_cache, value_cache, scale, block_tables, seq_lens,
+                                            max_seq_len, alibi_slopes)

@@ -23,6 +23,7 @@ PARTITION_SIZE = 512
 EXPORTED_SYMBOLS = (
     "b200_paged_attention_v1",
     "b200_paged_attention_v2",
+    "b200_paged_attention_flash",
     "b200_paged_attention_workspace_bytes",
     "b200_reshape_and_cache",
     "b200_reshape_and_cache_flash",
@@ -75,6 +76,7 @@ class PagedAttnParams(C.Structure):
         ("blocksparse_block_size", C.c_int32),
         ("blocksparse_head_sliding_step", C.c_int32),
         ("out_lse", C.c_void_p),
+        ("kv_page_stride", C.c_int64),
     ]
 
 
@@ -169,6 +171,8 @@ def load() -> C.CDLL:
     lib.b200_paged_attention_v1.restype = C.c_int
     lib.b200_paged_attention_v2.argtypes = [P(PagedAttnParams), C.c_void_p]
     lib.b200_paged_attention_v2.restype = C.c_int
+    lib.b200_paged_attention_flash.argtypes = [P(PagedAttnParams), C.c_void_p]
+    lib.b200_paged_attention_flash.restype = C.c_int
     lib.b200_paged_attention_workspace_bytes.argtypes = [P(PagedAttnParams)]
     lib.b200_paged_attention_workspace_bytes.restype = C.c_uint64
     lib.b200_reshape_and_cache.argtypes = [P(CacheWriteParams), C.c_void_p]
@@ -320,3 +324,32 @@ def merge_attn_states(output, prefix_output, prefix_lse, suffix_output, suffix_l
     p.num_tokens, p.num_heads, p.head_size = output.shape
     p.dtype = _torch_dtype_code(output.dtype)
     check(load().b200_merge_attn_states(C.byref(p), C.c_void_p(stream)))
+
+
+def flash_attn_params(out, query, key_cache, value_cache, scale, block_tables, seq_lens, max_seq_len, alibi_slopes=None,
+                      workspace=None, out_lse=None) -> PagedAttnParams:
+    """Parameters of b200_paged_attention_flash: caches [num_blocks, block_size, num_kv_heads, head_size]."""
+    p = PagedAttnParams()
+    p.out, p.query = out.data_ptr(), query.data_ptr()
+    p.key_cache, p.value_cache = key_cache.data_ptr(), value_cache.data_ptr()
+    p.block_tables, p.seq_lens = block_tables.data_ptr(), seq_lens.data_ptr()
+    p.alibi_slopes = alibi_slopes.data_ptr() if alibi_slopes is not None else None
+    if workspace is not None:
+        p.workspace, p.workspace_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+    if out_lse is not None:
+        p.out_lse = out_lse.data_ptr()
+    p.q_stride = query.stride(0)
+    p.kv_block_stride, p.kv_page_stride, p.kv_head_stride = key_cache.stride(0), key_cache.stride(1), key_cache.stride(2)
+    p.num_seqs, p.num_heads, p.head_size = query.shape
+    p.num_kv_heads, p.block_size = key_cache.shape[2], key_cache.shape[1]
+    p.max_seq_len = max_seq_len
+    p.max_num_blocks_per_seq = block_tables.shape[1]
+    p.dtype = _torch_dtype_code(query.dtype)
+    p.kv_dtype = KV_AUTO
+    p.scale = scale
+    p.blocksparse_block_size = 64
+    return p
+
+
+def paged_attention_flash(p: PagedAttnParams, stream: int) -> None:
+    check(load().b200_paged_attention_flash(C.byref(p), C.c_void_p(stream)))

@@ -218,6 +218,34 @@ extern "C" int b200_paged_attention_v1(const b200_paged_attn_params_t* p, void* 
   return launch_split_reduce(*p, so, s);
 }
 
+extern "C" int b200_paged_attention_flash(const b200_paged_attn_params_t* p, void* stream) {
+  B200_REQUIRE(p != nullptr, B200_ERR_INVALID_ARGUMENT, "params is NULL");
+  B200_REQUIRE(p->num_seqs >= 0 && p->num_heads > 0 && p->num_kv_heads > 0, B200_ERR_INVALID_ARGUMENT,
+               "bad sizes: seqs=%d heads=%d kv_heads=%d", p->num_seqs, p->num_heads, p->num_kv_heads);
+  B200_REQUIRE(p->num_heads % p->num_kv_heads == 0, B200_ERR_INVALID_ARGUMENT,
+               "num_heads %d is not a multiple of num_kv_heads %d", p->num_heads, p->num_kv_heads);
+  B200_REQUIRE(p->blocksparse_vert_stride <= 1, B200_ERR_UNSUPPORTED, "block-sparse attention is not supported");
+  const char* why = nullptr;
+  B200_REQUIRE(stream_flash_eligible(*p, &why), B200_ERR_UNSUPPORTED, "paged_attention_flash: %s", why);
+  if (p->num_seqs == 0) return B200_OK;
+  B200_REQUIRE(p->out && p->query && p->key_cache && p->value_cache && p->block_tables && p->seq_lens,
+               B200_ERR_INVALID_ARGUMENT, "NULL tensor pointer");
+  B200_REQUIRE(p->max_seq_len >= 0 && (int64_t)p->max_num_blocks_per_seq * p->block_size >= p->max_seq_len,
+               B200_ERR_INVALID_ARGUMENT, "max_seq_len %d exceeds the block table (%d blocks of %d)", p->max_seq_len,
+               p->max_num_blocks_per_seq, p->block_size);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int rc = init_empty_rows(*p, s);
+  if (rc != B200_OK || p->max_seq_len == 0) return rc;
+  B200_REQUIRE(p->workspace != nullptr && p->workspace_bytes >= kFlatWorkspaceBytes, B200_ERR_WORKSPACE,
+               "paged_attention_flash needs %llu bytes of workspace, got %llu", (unsigned long long)kFlatWorkspaceBytes,
+               (unsigned long long)(p->workspace ? p->workspace_bytes : 0));
+  B200_REQUIRE(reinterpret_cast<uintptr_t>(p->workspace) % 16 == 0, B200_ERR_WORKSPACE,
+               "workspace must be 16-byte aligned");
+  rc = launch_attention_stream_flash(*p, p->workspace, s);
+  if (rc == B200_OK) g_last_variant = B200_VARIANT_STREAM_MMA;
+  return rc;
+}
+
 extern "C" int b200_paged_attention_v2(const b200_paged_attn_params_t* p, void* stream) {
   int rc = validate_attn(p, true);
   if (rc != B200_OK) return rc;

@@ -39,18 +39,21 @@ namespace b200 {
 namespace {
 
 // ---- the kernel ------------------------------------------------------------------
-template <int B, bool FP8, int NT, bool FLAT, int NP>
+template <int B, bool FP8, int NT, bool FLAT, int NP, bool FLASH = false>
 __global__ void __launch_bounds__((kConsumerWarps + NP) * kWarpSize, 1)
 paged_attention_stream_kernel(const StreamParams p) {
   using C = Cfg<B, FP8>;
   static_assert(NP == 4 || NP == 8, "whole warpgroups of producers");
+  static_assert(!FLASH || (!FP8 && B == 16), "flash layout: bf16 cache; the block size is a runtime value");
+  // bytes of one ring stage (32 tokens of K and V)
+  constexpr int kStage = FLASH ? kFlashStageBytes : C::kStageBytes;
   constexpr bool F16 = FP8;  // MMA operand type: f16 for fp8 caches, bf16 otherwise
   constexpr int NH = 8 * NT;  // padded heads per kv head
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
   const int nst = p.nstages;
   uint8_t* ring = smem;
-  float* merge_o = reinterpret_cast<float*>(ring + (size_t)nst * C::kStageBytes);
+  float* merge_o = reinterpret_cast<float*>(ring + (size_t)nst * kStage);
   float* merge_m = merge_o + kConsumerWarps * NH * kMergeStride;
   float* merge_l = merge_m + kConsumerWarps * NH;
   uint64_t* bars = reinterpret_cast<uint64_t*>(merge_l + kConsumerWarps * NH);
@@ -79,6 +82,11 @@ paged_attention_stream_kernel(const StreamParams p) {
     // Producer warp pw owns the tiles gt == pw (mod kProducerWarps) of the CTA's tile stream; one
     // lane walks the block table and issues the bulk copies (a single issuing thread costs ~1000
     // cycles per tile, so four of them share the stream).
+    if constexpr (FLASH) {
+      // flash layout: every lane issues the two row copies of one token of the tile
+      producer_loop_flash<FLAT, NP>(p, sched, warp - kConsumerWarps, lane, ring_u32, full_u32, empty_u32, nst);
+      return;
+    }
     if (lane != 0) return;
     producer_loop<B, FP8, FLAT, NP>(p, sched, warp - kConsumerWarps, ring_u32, full_u32, empty_u32, nst);
     return;
@@ -89,7 +97,14 @@ paged_attention_stream_kernel(const StreamParams p) {
   // ldmatrix lane addressing (byte offsets inside a K / V chunk)
   const int mi = lane >> 3, r8 = lane & 7;
   uint32_t k_lane_off, v_lane_off;
-  if constexpr (!FP8) {
+  if constexpr (FLASH) {
+    // rows of the stage are tokens (kFlashRowBytes apart), 16 B = 8 dims.
+    // K (A = K, rows = tokens): matrices (tok 0-7, dims 0-7) (tok 8-15, dims 0-7) (tok 0-7, dims 8-15) (tok 8-15, dims 8-15)
+    k_lane_off = (uint32_t)((((mi & 1) * 8 + r8) * kFlashRowBytes) + (mi >> 1) * 16);
+    // V (A = V^T, rows = dims) through ldmatrix.trans: stored matrices (tok 0-7, dims 0-7) (tok 0-7, dims 8-15)
+    // (tok 8-15, dims 0-7) (tok 8-15, dims 8-15) come out as (dim g | tok 2c, 2c+1) fragments a0..a3
+    v_lane_off = (uint32_t)((((mi >> 1) * 8 + r8) * kFlashRowBytes) + (mi & 1) * 16);
+  } else if constexpr (!FP8) {
     // K: matrices (tok 0-7,g0) (tok 8-15,g0) (tok 0-7,g1) (tok 8-15,g1); unit = 16 B = 8 dims of a token
     k_lane_off = (uint32_t)(((mi >> 1) * B + (mi & 1) * 8 + r8) * 16);
     // V: matrices (dim 0-7,tok 0-7) (dim 8-15,tok 0-7) (dim 0-7,tok 8-15) (dim 8-15,tok 8-15)
@@ -200,7 +215,7 @@ paged_attention_stream_kernel(const StreamParams p) {
       // this warp's tiles are gt = warp, warp + 8, ... over the whole stream, so stage / parity advance
       // incrementally (no division by the runtime ring depth)
       MBAR_WAIT(full_u32 + 8u * stage, parity, 2, item, (int)(tile_base + (uint32_t)ti));
-      const uint32_t sb = ring_u32 + stage * C::kStageBytes;
+      const uint32_t sb = ring_u32 + stage * kStage;
       const int tok0 = it.t0 + ti * kTileTokens;   // first token of the tile
       const int nvalid = min(kTileTokens, it.t1 - tok0);
       const bool partial = nvalid < kTileTokens;
@@ -216,8 +231,17 @@ paged_attention_stream_kernel(const StreamParams p) {
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
         // half j: block j (B = 16) or tokens 16j.. of the block (B = 32)
-        const uint32_t kb = sb + (B == 16 ? j * C::kBlkBytes : j * 16 * 16) + k_lane_off;
-        if constexpr (!FP8) {
+        const uint32_t kb = FLASH ? sb + j * 16 * kFlashRowBytes + k_lane_off
+                                  : sb + (B == 16 ? j * C::kBlkBytes : j * 16 * 16) + k_lane_off;
+        if constexpr (FLASH) {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {
+            uint32_t a[4];
+            ldmatrix_x4(a, kb + ks * 32);
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) mma16816<F16>(sacc[j][nt], a, qf[nt][ks]);
+          }
+        } else if constexpr (!FP8) {
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks) {
             uint32_t a[4];
@@ -316,8 +340,21 @@ paged_attention_stream_kernel(const StreamParams p) {
         }
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-          const uint32_t vb = sb + C::kVOffset + (B == 16 ? j * C::kBlkBytes : j * 16 * C::kElemBytes) + v_lane_off;
-          if constexpr (!FP8) {
+          const uint32_t vb = FLASH ? sb + kFlashVOffset + j * 16 * kFlashRowBytes + v_lane_off
+                                    : sb + C::kVOffset + (B == 16 ? j * C::kBlkBytes : j * 16 * C::kElemBytes) + v_lane_off;
+          if constexpr (FLASH) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              uint32_t a[4];
+              ldmatrix_x4_trans(a, vb + i * 32);
+              if constexpr (kPartial) {  // rows past seq_len were not copied: stale ring contents
+                a[0] &= vmask[j][0]; a[1] &= vmask[j][0];
+                a[2] &= vmask[j][1]; a[3] &= vmask[j][1];
+              }
+#pragma unroll
+              for (int nt = 0; nt < NT; ++nt) mma16816<F16>(oacc[nt][i], a, pf[j][nt]);
+            }
+          } else if constexpr (!FP8) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               uint32_t a[4];
@@ -587,6 +624,77 @@ int dispatch_stream(const b200_paged_attn_params_t& p, StreamParams& sp, cudaStr
 #undef GO
 }
 }  // namespace
+
+// ---- flash layout (paged_attention_flash) -------------------------------------------------------------------
+bool stream_flash_eligible(const b200_paged_attn_params_t& p, const char** why) {
+  const char* w = nullptr;
+  const int G = p.num_kv_heads > 0 ? p.num_heads / p.num_kv_heads : 0;
+  if (p.dtype != B200_DTYPE_BF16) w = "query dtype is not bf16";
+  else if (p.kv_dtype != B200_KV_AUTO) w = "flash-layout decode takes a bf16 cache (the reference's flash-attention path has no fp8 cache)";
+  else if (p.head_size != kD) w = "head_size is not 128";
+  else if (p.block_size < 16 || p.block_size % 16 != 0) w = "block_size is not a multiple of 16";
+  else if (G < 1 || G > kFlatMaxGroup) w = "GQA group size above 16";
+  else if ((uint64_t)p.num_seqs * p.num_kv_heads > kFlatCounterSlots) w = "more (seq, kv head) pairs than arrival counters";
+  else if ((p.kv_block_stride * 2) % 16 != 0 || (p.kv_head_stride * 2) % 16 != 0 || (p.kv_page_stride * 2) % 16 != 0)
+    w = "KV strides not 16-byte multiples";
+  else if ((reinterpret_cast<uintptr_t>(p.key_cache) | reinterpret_cast<uintptr_t>(p.value_cache)) % 16 != 0) w = "KV cache not 16-byte aligned";
+  else if (p.q_stride % 8 != 0 || reinterpret_cast<uintptr_t>(p.query) % 16 != 0) w = "query rows not 16-byte aligned";
+  if (why) *why = w;
+  return w == nullptr;
+}
+
+namespace {
+template <int NT>
+int launch_stream_flash_t(StreamParams& sp, cudaStream_t s) {
+  constexpr int NP = 4;
+  // ring depth: a multiple of the consumer-warp count; 8 stages = 256 tokens = 128 KiB of rows in flight
+  int nst = kConsumerWarps;
+  auto smem_of = [](int n) {
+    return 128 + (size_t)n * kFlashStageBytes + (size_t)kConsumerWarps * 8 * NT * (kMergeStride + 2) * sizeof(float) +
+           (size_t)n * 16 + sizeof(Sched) + 16;
+  };
+  if (const char* e = getenv("B200_STREAM_NSTAGES")) {
+    const int want = atoi(e) / kConsumerWarps * kConsumerWarps;
+    if (want > nst && smem_of(want) <= kMaxSmem) nst = want;
+  }
+  sp.nstages = nst;
+  const size_t smem = smem_of(nst);
+  auto kern = paged_attention_stream_kernel<16, false, NT, true, NP, true>;
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxSmem);
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(smem) failed: %s", cudaGetErrorString(e));
+      return B200_ERR_CUDA;
+    }
+    configured_device = dev;
+  }
+  const int grid = min(min(device_sm_count(), kFlatMaxCtas), sp.total_items);
+  kern<<<grid, (kConsumerWarps + NP) * kWarpSize, smem, s>>>(sp);
+  count_launch();
+  return check_launch("paged_attention_flash");
+}
+}  // namespace
+
+int launch_attention_stream_flash(const b200_paged_attn_params_t& p, void* workspace, cudaStream_t s) {
+  const char* why = nullptr;
+  B200_REQUIRE(stream_flash_eligible(p, &why), B200_ERR_UNSUPPORTED, "paged_attention_flash: %s", why);
+  B200_REQUIRE(workspace != nullptr, B200_ERR_WORKSPACE, "paged_attention_flash: workspace missing");
+  StreamParams sp = fill_stream_params(p);
+  sp.kv_page_stride = p.kv_page_stride * 2;
+  sp.block_size = p.block_size;
+  sp.counters = static_cast<int*>(workspace);
+  float* slots = reinterpret_cast<float*>(static_cast<char*>(workspace) + kFlatCounterBytes);
+  sp.ws_o = slots;
+  sp.ws_m = slots + (size_t)kFlatMaxCtas * 2 * kFlatMaxGroup * kD;
+  sp.ws_l = sp.ws_m + (size_t)kFlatMaxCtas * 2 * kFlatMaxGroup;
+  const int64_t tiles = (int64_t)p.num_seqs * p.num_kv_heads * ((p.max_seq_len + kTileTokens - 1) / kTileTokens);
+  sp.total_items = (int)(tiles < (int64_t)kFlatMaxCtas ? tiles : (int64_t)kFlatMaxCtas);
+  if (sp.total_items == 0) return B200_OK;
+  return (sp.G + 7) / 8 == 1 ? launch_stream_flash_t<1>(sp, s) : launch_stream_flash_t<2>(sp, s);
+}
 
 int launch_attention_stream(const b200_paged_attn_params_t& p, const SplitOut& so, cudaStream_t s) {
   const char* why = nullptr;

@@ -158,6 +158,9 @@ int launch_attention_stream(const b200_paged_attn_params_t& p, const SplitOut& s
 // v1: flat schedule; `workspace` holds kFlatWorkspaceBytes laid out as above
 int launch_attention_stream_flat(const b200_paged_attn_params_t& p, void* workspace, cudaStream_t s);
 bool stream_variant_eligible(const b200_paged_attn_params_t& p, const char** why);
+// flash layout [num_blocks, block_size, num_kv_heads, D] (NHD or HND strides), bf16: flat schedule, one launch
+int launch_attention_stream_flash(const b200_paged_attn_params_t& p, void* workspace, cudaStream_t s);
+bool stream_flash_eligible(const b200_paged_attn_params_t& p, const char** why);
 // tcgen05 kernel for fp8 caches (attention_umma_fp8.cu): same two schedules
 int launch_attention_umma_fp8(const b200_paged_attn_params_t& p, const SplitOut& so, cudaStream_t s);
 int launch_attention_umma_fp8_flat(const b200_paged_attn_params_t& p, void* workspace, cudaStream_t s);

@@ -44,6 +44,8 @@ struct StreamParams {
   int64_t q_stride;         // elements
   int64_t kv_block_stride;  // bytes
   int64_t kv_head_stride;   // bytes
+  int64_t kv_page_stride;   // bytes; flash layout only: stride between the tokens of a block
+  int block_size;           // flash layout only (runtime; a multiple of 16)
   int S, H, Hkv, G, max_blocks, nstages, total_items;
   float scale;
   int debug_num_blocks;  // B200_DEBUG builds only: bound for block-table entries (0 = unchecked)
@@ -120,6 +122,11 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
 }
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
                : "r"(addr));
 }
@@ -367,6 +374,68 @@ __device__ __forceinline__ void producer_loop(const StreamParams& p, const Sched
     tile_base = tile_end;
   }
 
+}
+
+// ---- flash layout ([num_blocks, block_size, num_kv_heads, D], NHD or HND strides; bf16) ---------------------
+// One token row of one kv head is D contiguous elements (256 B); the rows of a block are page_stride apart
+// (NHD: Hkv*D elements, HND: D).  Every row travels as its own bulk copy into a ring stage laid out
+// [K rows of the tile's 32 tokens][V rows], each row padded to kFlashRowBytes so that the 8 rows an ldmatrix
+// phase touches fall into distinct bank groups (a dense 256-byte pitch would be an 8-way conflict; a 1-D bulk
+// copy cannot swizzle inside a row, but the destination of each row is free).
+constexpr int kFlashRowBytes = kD * 2 + 16;                        // 272
+constexpr int kFlashVOffset = kTileTokens * kFlashRowBytes;        // V rows follow the K rows
+constexpr int kFlashStageBytes = 2 * kTileTokens * kFlashRowBytes; // 17408
+
+// All 32 lanes of producer warp `pw` issue: lane l copies the K row and the V row of token l of the tile.
+template <bool FLAT, int NP>
+__device__ __forceinline__ void producer_loop_flash(const StreamParams& p, const Sched* sched, int pw, int lane,
+                                                    uint32_t ring_u32, uint32_t full_u32, uint32_t empty_u32,
+                                                    int nst) {
+  constexpr int kProducerWarps = NP;
+  uint32_t g_next = (uint32_t)pw;
+  int stage = pw;
+  uint32_t phase = 0;
+  uint32_t tile_base = 0;
+  const int B = p.block_size;
+  WorkIter<FLAT> wi;
+  wi.init(p, sched);
+  Seg it;
+  int item = -1;
+  while (wi.next(p, it)) {
+    ++item;
+    const uint32_t ntiles = (uint32_t)((it.t1 - it.t0 + kTileTokens - 1) / kTileTokens);
+    const int32_t* bt = p.bt + (int64_t)it.s * p.max_blocks;
+    const uint8_t* kbase = p.kc + (int64_t)it.kvh * p.kv_head_stride;
+    const uint8_t* vbase = p.vc + (int64_t)it.kvh * p.kv_head_stride;
+    const uint32_t tile_end = tile_base + ntiles;
+    // this lane's token of the next tile and its block id, fetched one step ahead
+    int ntok = it.t0 + (int)(g_next - tile_base) * kTileTokens + lane;
+    int nid = (g_next < tile_end && ntok < it.t1) ? __ldg(bt + ntok / B) : 0;
+    while (g_next < tile_end) {
+      const int tok = ntok, id = nid;
+      const int tile_tok0 = tok - lane;
+      const int nvalid = min(kTileTokens, it.t1 - tile_tok0);
+      ntok = tok + kProducerWarps * kTileTokens;
+      if (g_next + kProducerWarps < tile_end && ntok < it.t1) nid = __ldg(bt + ntok / B);
+      MBAR_WAIT(empty_u32 + 8u * stage, phase ^ 1u, 1, item, stage);
+      const uint32_t fb = full_u32 + 8u * stage;
+      if (lane == 0) mbar_expect_tx(fb, (uint32_t)(nvalid * 2 * kD * 2));
+      __syncwarp();
+      if (lane < nvalid) {
+        const int64_t off = (int64_t)id * p.kv_block_stride + (int64_t)(tok % B) * p.kv_page_stride;
+        const uint32_t dst = ring_u32 + (uint32_t)stage * kFlashStageBytes + (uint32_t)lane * kFlashRowBytes;
+        bulk_g2s(dst, kbase + off, kD * 2, fb);
+        bulk_g2s(dst + kFlashVOffset, vbase + off, kD * 2, fb);
+      }
+      g_next += kProducerWarps;
+      stage += kProducerWarps;
+      if (stage >= nst) {
+        stage -= nst;
+        phase ^= 1u;
+      }
+    }
+    tile_base = tile_end;
+  }
 }
 
 // host: C-ABI parameters -> kernel parameters (strides in bytes)

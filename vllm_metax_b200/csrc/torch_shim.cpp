@@ -187,6 +187,75 @@ void paged_attention_v1_lse(at::Tensor& out, at::Tensor& lse, at::Tensor& query,
   check_status(b200_paged_attention_v1(&p, stream), "paged_attention_v1_lse");
 }
 
+// Not a reference op: decode attention over the flash cache layout [num_blocks, block_size, num_kv_heads, head_size]
+// (NHD or HND strides) — what the reference's serving path gets from flash_attn_with_kvcache of the external
+// flash-attention library (vllm_metax/v1/attention/backends/flash_attn.py:742-757).  query/out [num_seqs, num_heads, D].
+void paged_attention_flash(at::Tensor& out, std::optional<at::Tensor> lse, const at::Tensor& query,
+                           const at::Tensor& key_cache, const at::Tensor& value_cache, double scale,
+                           const at::Tensor& block_tables, const at::Tensor& seq_lens, int64_t max_seq_len,
+                           const std::optional<at::Tensor>& alibi_slopes) {
+  TORCH_CHECK(query.dim() == 3 && out.dim() == 3 && out.sizes() == query.sizes(),
+              "query/out must be [num_seqs, num_heads, head_size]");
+  TORCH_CHECK(out.scalar_type() == query.scalar_type() && out.is_contiguous(), "out must be contiguous, of the query dtype");
+  TORCH_CHECK(query.stride(2) == 1 && query.stride(1) == query.size(2), "query heads must be contiguous");
+  TORCH_CHECK(key_cache.dim() == 4 && value_cache.dim() == 4 && key_cache.sizes() == value_cache.sizes(),
+              "key_cache / value_cache must be [num_blocks, block_size, num_kv_heads, head_size]");
+  TORCH_CHECK(key_cache.strides() == value_cache.strides() && key_cache.stride(3) == 1,
+              "key_cache and value_cache must share strides with contiguous head dims");
+  TORCH_CHECK(key_cache.scalar_type() == query.scalar_type() && value_cache.scalar_type() == query.scalar_type(),
+              "flash-layout decode needs caches of the query dtype");
+  TORCH_CHECK(key_cache.size(3) == query.size(2), "head_size of the cache and the query differ");
+  TORCH_CHECK(block_tables.scalar_type() == at::kInt && block_tables.dim() == 2 && block_tables.stride(1) == 1,
+              "block_tables must be a 2-D int32 tensor with contiguous rows");
+  TORCH_CHECK(seq_lens.scalar_type() == at::kInt && seq_lens.is_contiguous(), "seq_lens must be contiguous int32");
+  TORCH_CHECK(query.is_cuda() && key_cache.is_cuda() && value_cache.is_cuda() && block_tables.is_cuda() && seq_lens.is_cuda(),
+              "all tensors must be on the CUDA device");
+  TORCH_CHECK(block_tables.size(0) >= query.size(0) && seq_lens.numel() >= query.size(0),
+              "block_tables / seq_lens have fewer rows than query");
+  const int dt = to_dtype(query.scalar_type());
+  TORCH_CHECK(dt == B200_DTYPE_BF16, "paged_attention_flash: query dtype is not bf16");
+  b200_paged_attn_params_t p;
+  memset(&p, 0, sizeof(p));
+  p.out = out.data_ptr();
+  p.query = query.data_ptr();
+  p.key_cache = key_cache.data_ptr();
+  p.value_cache = value_cache.data_ptr();
+  p.block_tables = block_tables.data_ptr<int32_t>();
+  p.seq_lens = seq_lens.data_ptr<int32_t>();
+  if (alibi_slopes.has_value() && alibi_slopes->defined()) {
+    TORCH_CHECK(alibi_slopes->scalar_type() == at::kFloat && alibi_slopes->is_contiguous() &&
+                    alibi_slopes->numel() == query.size(1) && alibi_slopes->is_cuda(),
+                "alibi_slopes must be a contiguous float32 CUDA tensor of num_heads entries");
+    p.alibi_slopes = alibi_slopes->data_ptr<float>();
+  }
+  if (lse.has_value() && lse->defined()) {
+    TORCH_CHECK(lse->is_cuda() && lse->scalar_type() == at::kFloat && lse->is_contiguous() && lse->dim() == 2 &&
+                    lse->size(0) == query.size(1) && lse->size(1) == query.size(0),
+                "lse must be a contiguous float32 CUDA tensor [num_heads, num_seqs]");
+    p.out_lse = lse->data_ptr<float>();
+  }
+  p.q_stride = query.stride(0);
+  p.kv_block_stride = key_cache.stride(0);
+  p.kv_page_stride = key_cache.stride(1);
+  p.kv_head_stride = key_cache.stride(2);
+  p.num_seqs = static_cast<int32_t>(query.size(0));
+  p.num_heads = static_cast<int32_t>(query.size(1));
+  p.num_kv_heads = static_cast<int32_t>(key_cache.size(2));
+  p.head_size = static_cast<int32_t>(query.size(2));
+  p.block_size = static_cast<int32_t>(key_cache.size(1));
+  p.max_seq_len = static_cast<int32_t>(max_seq_len);
+  p.max_num_blocks_per_seq = static_cast<int32_t>(block_tables.size(1));
+  p.dtype = dt;
+  p.kv_dtype = B200_KV_AUTO;
+  p.scale = static_cast<float>(scale);
+  p.blocksparse_block_size = 64;
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  p.workspace_bytes = b200_paged_attention_workspace_bytes(&p);
+  p.workspace = v1_workspace(p.workspace_bytes, query, stream);
+  check_status(b200_paged_attention_flash(&p, stream), "paged_attention_flash");
+}
+
 // csrc/ops.h (merge_attn_states) ; csrc/attention/merge_attn_states.cu:129-178
 void merge_attn_states(at::Tensor& output, std::optional<at::Tensor> output_lse, const at::Tensor& prefix_output,
                        const at::Tensor& prefix_lse, const at::Tensor& suffix_output, const at::Tensor& suffix_lse) {
@@ -497,6 +566,7 @@ void gather_and_maybe_dequant_cache(const at::Tensor& src_cache, const at::Tenso
     p.dst_dtype = dt;
     p.scale = scale.data_ptr<float>();
   }
+  if (dst.numel() == 0) return;  // every sequence is empty: nothing to gather
   const at::cuda::OptionalCUDAGuard guard(device_of(src_cache));
   check_status(b200_gather_cache(&p, at::cuda::getCurrentCUDAStream()), "gather_and_maybe_dequant_cache");
 }
@@ -511,6 +581,7 @@ void cp_gather_cache(const at::Tensor& src_cache, const at::Tensor& dst, const a
   p.token_granular_starts = 1;
   p.src_dtype = p.dst_dtype = width_dtype(src_cache.element_size());
   TORCH_CHECK(p.src_dtype >= 0, "Unsupported data type width: ", src_cache.element_size() * 8);
+  if (dst.numel() == 0) return;  // every sequence is empty: nothing to gather
   const at::cuda::OptionalCUDAGuard guard(device_of(src_cache));
   check_status(b200_gather_cache(&p, at::cuda::getCurrentCUDAStream()), "cp_gather_cache");
 }
@@ -582,6 +653,10 @@ const char* kSchemaV1Lse =
     "int num_kv_heads, float scale, Tensor block_tables, Tensor seq_lens, int block_size, int max_seq_len, "
     "Tensor? alibi_slopes, str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()";
 
+const char* kSchemaFlash =
+    "paged_attention_flash(Tensor! out, Tensor!? lse, Tensor query, Tensor key_cache, Tensor value_cache, "
+    "float scale, Tensor block_tables, Tensor seq_lens, int max_seq_len, Tensor? alibi_slopes) -> ()";
+
 bool op_exists(const char* qualified) {
   return c10::Dispatcher::singleton().findSchema({qualified, ""}).has_value();
 }
@@ -622,6 +697,7 @@ void register_all() {
     register_op(keep, "_C_cache_ops", "gather_and_maybe_dequant_cache", kSchemaGather, &gather_and_maybe_dequant_cache);
     register_op(keep, "_C_cache_ops", "cp_gather_cache", kSchemaCpGather, &cp_gather_cache);
     register_op(keep, "_C_b200", "paged_attention_v1_lse", kSchemaV1Lse, &paged_attention_v1_lse);
+    register_op(keep, "_C_b200", "paged_attention_flash", kSchemaFlash, &paged_attention_flash);
   });
 }
 
