@@ -147,6 +147,9 @@ typedef struct b200_paged_attn_params {
   /* ABI v2, b200_paged_attention_flash only: stride between consecutive tokens
    * of a block (key_cache.stride(1)), elements. */
   int64_t kv_page_stride;
+  /* ABI v2, b200_paged_attention_flash only: key_cache.size(0).  Bounds the TMA
+   * tensor map of the cache (no block id at or above it is ever dereferenced). */
+  int64_t kv_num_blocks;
 } b200_paged_attn_params_t;
 
 /* Replaces torch.ops._C.paged_attention_v1 (csrc/torch_bindings.cpp:45-55;

@@ -77,6 +77,7 @@ class PagedAttnParams(C.Structure):
         ("blocksparse_head_sliding_step", C.c_int32),
         ("out_lse", C.c_void_p),
         ("kv_page_stride", C.c_int64),
+        ("kv_num_blocks", C.c_int64),
     ]
 
 
@@ -342,6 +343,7 @@ def flash_attn_params(out, query, key_cache, value_cache, scale, block_tables, s
     p.kv_block_stride, p.kv_page_stride, p.kv_head_stride = key_cache.stride(0), key_cache.stride(1), key_cache.stride(2)
     p.num_seqs, p.num_heads, p.head_size = query.shape
     p.num_kv_heads, p.block_size = key_cache.shape[2], key_cache.shape[1]
+    p.kv_num_blocks = key_cache.shape[0]
     p.max_seq_len = max_seq_len
     p.max_num_blocks_per_seq = block_tables.shape[1]
     p.dtype = _torch_dtype_code(query.dtype)

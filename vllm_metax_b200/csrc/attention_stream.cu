@@ -33,6 +33,8 @@
 //    memory once per work item;
 //  * fp8: e4m3 bytes are expanded to f16 in registers (exact), the MMA runs in
 //    f16, k_scale is folded into the logit scale and v_scale into the output.
+#include <cuda.h>
+
 #include "stream_common.cuh"
 
 namespace b200 {
@@ -41,7 +43,7 @@ namespace {
 // ---- the kernel ------------------------------------------------------------------
 template <int B, bool FP8, int NT, bool FLAT, int NP, bool FLASH = false>
 __global__ void __launch_bounds__((kConsumerWarps + NP) * kWarpSize, 1)
-paged_attention_stream_kernel(const StreamParams p) {
+paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
   using C = Cfg<B, FP8>;
   static_assert(NP == 4 || NP == 8, "whole warpgroups of producers");
   static_assert(!FLASH || (!FP8 && B == 16), "flash layout: bf16 cache; the block size is a runtime value");
@@ -50,7 +52,9 @@ paged_attention_stream_kernel(const StreamParams p) {
   constexpr bool F16 = FP8;  // MMA operand type: f16 for fp8 caches, bf16 otherwise
   constexpr int NH = 8 * NT;  // padded heads per kv head
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  // ring base: 128-byte aligned; 1024 for the flash layout (the 128-byte TMA swizzle pattern repeats every 1 KiB)
+  constexpr uintptr_t kAlign = FLASH ? 1024 : 128;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + kAlign - 1) & ~(kAlign - 1));
   const int nst = p.nstages;
   uint8_t* ring = smem;
   float* merge_o = reinterpret_cast<float*>(ring + (size_t)nst * kStage);
@@ -82,12 +86,11 @@ paged_attention_stream_kernel(const StreamParams p) {
     // Producer warp pw owns the tiles gt == pw (mod kProducerWarps) of the CTA's tile stream; one
     // lane walks the block table and issues the bulk copies (a single issuing thread costs ~1000
     // cycles per tile, so four of them share the stream).
+    if (lane != 0) return;
     if constexpr (FLASH) {
-      // flash layout: every lane issues the two row copies of one token of the tile
-      producer_loop_flash<FLAT, NP>(p, sched, warp - kConsumerWarps, lane, ring_u32, full_u32, empty_u32, nst);
+      producer_loop_flash<FLAT, NP>(p, &p.tm_k, &p.tm_v, sched, warp - kConsumerWarps, ring_u32, full_u32, empty_u32, nst);
       return;
     }
-    if (lane != 0) return;
     producer_loop<B, FP8, FLAT, NP>(p, sched, warp - kConsumerWarps, ring_u32, full_u32, empty_u32, nst);
     return;
   }
@@ -97,13 +100,17 @@ paged_attention_stream_kernel(const StreamParams p) {
   // ldmatrix lane addressing (byte offsets inside a K / V chunk)
   const int mi = lane >> 3, r8 = lane & 7;
   uint32_t k_lane_off, v_lane_off;
+  [[maybe_unused]] uint32_t k_swz = 0, v_swz = 0;  // flash layout: swizzle term of this lane's 16-byte chunk
   if constexpr (FLASH) {
-    // rows of the stage are tokens (kFlashRowBytes apart), 16 B = 8 dims.
-    // K (A = K, rows = tokens): matrices (tok 0-7, dims 0-7) (tok 8-15, dims 0-7) (tok 0-7, dims 8-15) (tok 8-15, dims 8-15)
-    k_lane_off = (uint32_t)((((mi & 1) * 8 + r8) * kFlashRowBytes) + (mi >> 1) * 16);
+    // a box is 16 token rows of 128 B (64 dims), 16-byte chunk c of row r stored at chunk c ^ (r & 7) (128B swizzle).
+    // K (A = K, rows = tokens): matrices (tok 0-7, dims 0-7) (tok 8-15, dims 0-7) (tok 0-7, dims 8-15) (tok 8-15, dims 8-15):
+    // row = (mi&1)*8 + r8, chunk = 2*kk + (mi>>1)  ->  byte = row*128 + ((kk*32) ^ k_swz)
+    k_lane_off = (uint32_t)(((mi & 1) * 8 + r8) * 128);
+    k_swz = (uint32_t)(((mi >> 1) ^ r8) << 4);
     // V (A = V^T, rows = dims) through ldmatrix.trans: stored matrices (tok 0-7, dims 0-7) (tok 0-7, dims 8-15)
     // (tok 8-15, dims 0-7) (tok 8-15, dims 8-15) come out as (dim g | tok 2c, 2c+1) fragments a0..a3
-    v_lane_off = (uint32_t)((((mi >> 1) * 8 + r8) * kFlashRowBytes) + (mi & 1) * 16);
+    v_lane_off = (uint32_t)(((mi >> 1) * 8 + r8) * 128);
+    v_swz = (uint32_t)(((mi & 1) ^ r8) << 4);
   } else if constexpr (!FP8) {
     // K: matrices (tok 0-7,g0) (tok 8-15,g0) (tok 0-7,g1) (tok 8-15,g1); unit = 16 B = 8 dims of a token
     k_lane_off = (uint32_t)(((mi >> 1) * B + (mi & 1) * 8 + r8) * 16);
@@ -231,13 +238,13 @@ paged_attention_stream_kernel(const StreamParams p) {
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
         // half j: block j (B = 16) or tokens 16j.. of the block (B = 32)
-        const uint32_t kb = FLASH ? sb + j * 16 * kFlashRowBytes + k_lane_off
+        const uint32_t kb = FLASH ? sb + j * 2 * kFlashBoxBytes + k_lane_off
                                   : sb + (B == 16 ? j * C::kBlkBytes : j * 16 * 16) + k_lane_off;
         if constexpr (FLASH) {
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks) {
             uint32_t a[4];
-            ldmatrix_x4(a, kb + ks * 32);
+            ldmatrix_x4(a, kb + (ks >> 2) * kFlashBoxBytes + (((ks & 3) * 32) ^ k_swz));
 #pragma unroll
             for (int nt = 0; nt < NT; ++nt) mma16816<F16>(sacc[j][nt], a, qf[nt][ks]);
           }
@@ -340,14 +347,14 @@ paged_attention_stream_kernel(const StreamParams p) {
         }
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-          const uint32_t vb = FLASH ? sb + kFlashVOffset + j * 16 * kFlashRowBytes + v_lane_off
+          const uint32_t vb = FLASH ? sb + kFlashVOffset + j * 2 * kFlashBoxBytes + v_lane_off
                                     : sb + C::kVOffset + (B == 16 ? j * C::kBlkBytes : j * 16 * C::kElemBytes) + v_lane_off;
           if constexpr (FLASH) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               uint32_t a[4];
-              ldmatrix_x4_trans(a, vb + i * 32);
-              if constexpr (kPartial) {  // rows past seq_len were not copied: stale ring contents
+              ldmatrix_x4_trans(a, vb + (i >> 2) * kFlashBoxBytes + (((i & 3) * 32) ^ v_swz));
+              if constexpr (kPartial) {  // rows past seq_len: stale cache (or a half that was not loaded)
                 a[0] &= vmask[j][0]; a[1] &= vmask[j][0];
                 a[2] &= vmask[j][1]; a[3] &= vmask[j][1];
               }
@@ -644,13 +651,54 @@ bool stream_flash_eligible(const b200_paged_attn_params_t& p, const char** why) 
 }
 
 namespace {
+// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (no link-time dependency on libcuda).
+// Pure host computation: nothing is enqueued, allocated or read from the device.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      f = nullptr;
+    }
+    return reinterpret_cast<EncodeTiledFn>(f);
+  }();
+  return fn;
+}
+
+// 4-D map over (dim, kv head, token in block, block); box = 64 dims x 1 head x 16 tokens x 1 block, 128-byte swizzle.
+int encode_flash_map(TmaDesc* out, const void* cache, const b200_paged_attn_params_t& p) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  B200_REQUIRE(enc != nullptr, B200_ERR_CUDA, "paged_attention_flash: cuTensorMapEncodeTiled is not available from the driver");
+  const cuuint64_t nb = p.kv_num_blocks > 0 ? (cuuint64_t)p.kv_num_blocks : (cuuint64_t)1 << 24;
+  const cuuint64_t dims[4] = {(cuuint64_t)kD, (cuuint64_t)p.num_kv_heads, (cuuint64_t)p.block_size, nb};
+  const cuuint64_t strides[3] = {(cuuint64_t)p.kv_head_stride * 2, (cuuint64_t)p.kv_page_stride * 2,
+                                 (cuuint64_t)p.kv_block_stride * 2};
+  const cuuint32_t box[4] = {64, 1, 16, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUtensorMap m;
+  const CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(cache), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, B200_ERR_INVALID_ARGUMENT,
+               "paged_attention_flash: cuTensorMapEncodeTiled failed (%d) for strides %lld/%lld/%lld elements", (int)r,
+               (long long)p.kv_block_stride, (long long)p.kv_page_stride, (long long)p.kv_head_stride);
+  static_assert(sizeof(CUtensorMap) == sizeof(TmaDesc), "CUtensorMap is 128 bytes");
+  memcpy(out, &m, sizeof(m));
+  return B200_OK;
+}
+
 template <int NT>
 int launch_stream_flash_t(StreamParams& sp, cudaStream_t s) {
   constexpr int NP = 4;
   // ring depth: a multiple of the consumer-warp count; 8 stages = 256 tokens = 128 KiB of rows in flight
   int nst = kConsumerWarps;
   auto smem_of = [](int n) {
-    return 128 + (size_t)n * kFlashStageBytes + (size_t)kConsumerWarps * 8 * NT * (kMergeStride + 2) * sizeof(float) +
+    return 1024 + (size_t)n * kFlashStageBytes + (size_t)kConsumerWarps * 8 * NT * (kMergeStride + 2) * sizeof(float) +
            (size_t)n * 16 + sizeof(Sched) + 16;
   };
   if (const char* e = getenv("B200_STREAM_NSTAGES")) {
@@ -685,6 +733,10 @@ int launch_attention_stream_flash(const b200_paged_attn_params_t& p, void* works
   StreamParams sp = fill_stream_params(p);
   sp.kv_page_stride = p.kv_page_stride * 2;
   sp.block_size = p.block_size;
+  int rc = encode_flash_map(&sp.tm_k, p.key_cache, p);
+  if (rc != B200_OK) return rc;
+  rc = encode_flash_map(&sp.tm_v, p.value_cache, p);
+  if (rc != B200_OK) return rc;
   sp.counters = static_cast<int*>(workspace);
   float* slots = reinterpret_cast<float*>(static_cast<char*>(workspace) + kFlatCounterBytes);
   sp.ws_o = slots;

@@ -25,7 +25,11 @@ constexpr int kMergeStride = kD + 4;  // fp32 words per (warp, head) row
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
+struct alignas(64) TmaDesc {
+  uint64_t w[16];  // a CUtensorMap (128 bytes), filled on the host by cuTensorMapEncodeTiled
+};
 struct StreamParams {
+  TmaDesc tm_k, tm_v;       // flash layout only: 4-D tensor maps of the key / value cache
   const __nv_bfloat16* q;
   const uint8_t* kc;
   const uint8_t* vc;
@@ -378,19 +382,27 @@ __device__ __forceinline__ void producer_loop(const StreamParams& p, const Sched
 
 // ---- flash layout ([num_blocks, block_size, num_kv_heads, D], NHD or HND strides; bf16) ---------------------
 // One token row of one kv head is D contiguous elements (256 B); the rows of a block are page_stride apart
-// (NHD: Hkv*D elements, HND: D).  Every row travels as its own bulk copy into a ring stage laid out
-// [K rows of the tile's 32 tokens][V rows], each row padded to kFlashRowBytes so that the 8 rows an ldmatrix
-// phase touches fall into distinct bank groups (a dense 256-byte pitch would be an 8-way conflict; a 1-D bulk
-// copy cannot swizzle inside a row, but the destination of each row is free).
-constexpr int kFlashRowBytes = kD * 2 + 16;                        // 272
-constexpr int kFlashVOffset = kTileTokens * kFlashRowBytes;        // V rows follow the K rows
-constexpr int kFlashStageBytes = 2 * kTileTokens * kFlashRowBytes; // 17408
+// (NHD: Hkv*D elements, HND: D).  Separate 256-byte bulk copies top out at ~4 TB/s (one TMA operation per ~18
+// cycles per SM; profiles/), so the rows travel as TILED TMA boxes through a 4-D tensor map over
+// (dim, kv head, token in block, block): one box = 16 tokens x 64 dims of one kv head = 2 KiB, written to shared
+// memory with the 128-byte swizzle so that the 8 rows an ldmatrix phase touches fall into distinct bank groups.
+// A ring stage (32 tokens) = [K: half 0 dims 0-63 | half 0 dims 64-127 | half 1 ... ][V: same], 8 boxes, 16 KiB.
+constexpr int kFlashBoxBytes = 16 * 128;                 // 16 token rows of 128 B (64 bf16 dims)
+constexpr int kFlashVOffset = 4 * kFlashBoxBytes;        // V boxes follow the K boxes
+constexpr int kFlashStageBytes = 8 * kFlashBoxBytes;     // 16384
 
-// All 32 lanes of producer warp `pw` issue: lane l copies the K row and the V row of token l of the tile.
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* tmap, int c0, int c1, int c2, int c3, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
+// One issuing lane of producer warp `pw`: per tile, up to 8 boxes (K and V, two 16-token halves, two 64-dim halves).
 template <bool FLAT, int NP>
-__device__ __forceinline__ void producer_loop_flash(const StreamParams& p, const Sched* sched, int pw, int lane,
-                                                    uint32_t ring_u32, uint32_t full_u32, uint32_t empty_u32,
-                                                    int nst) {
+__device__ __forceinline__ void producer_loop_flash(const StreamParams& p, const void* tm_k, const void* tm_v,
+                                                    const Sched* sched, int pw, uint32_t ring_u32, uint32_t full_u32,
+                                                    uint32_t empty_u32, int nst) {
   constexpr int kProducerWarps = NP;
   uint32_t g_next = (uint32_t)pw;
   int stage = pw;
@@ -405,27 +417,37 @@ __device__ __forceinline__ void producer_loop_flash(const StreamParams& p, const
     ++item;
     const uint32_t ntiles = (uint32_t)((it.t1 - it.t0 + kTileTokens - 1) / kTileTokens);
     const int32_t* bt = p.bt + (int64_t)it.s * p.max_blocks;
-    const uint8_t* kbase = p.kc + (int64_t)it.kvh * p.kv_head_stride;
-    const uint8_t* vbase = p.vc + (int64_t)it.kvh * p.kv_head_stride;
     const uint32_t tile_end = tile_base + ntiles;
-    // this lane's token of the next tile and its block id, fetched one step ahead
-    int ntok = it.t0 + (int)(g_next - tile_base) * kTileTokens + lane;
-    int nid = (g_next < tile_end && ntok < it.t1) ? __ldg(bt + ntok / B) : 0;
+    // block ids of the two 16-token halves of the next tile, fetched one step ahead
+    int ntok = it.t0 + (int)(g_next - tile_base) * kTileTokens;
+    int nid0 = 0, nid1 = 0;
+    if (g_next < tile_end) {
+      nid0 = __ldg(bt + ntok / B);
+      if (ntok + 16 < it.t1) nid1 = __ldg(bt + (ntok + 16) / B);
+    }
     while (g_next < tile_end) {
-      const int tok = ntok, id = nid;
-      const int tile_tok0 = tok - lane;
-      const int nvalid = min(kTileTokens, it.t1 - tile_tok0);
+      const int tok = ntok, id0 = nid0, id1 = nid1;
+      const bool two = tok + 16 < it.t1;  // the second half holds at least one valid token
       ntok = tok + kProducerWarps * kTileTokens;
-      if (g_next + kProducerWarps < tile_end && ntok < it.t1) nid = __ldg(bt + ntok / B);
+      if (g_next + kProducerWarps < tile_end) {
+        nid0 = __ldg(bt + ntok / B);
+        if (ntok + 16 < it.t1) nid1 = __ldg(bt + (ntok + 16) / B);
+      }
       MBAR_WAIT(empty_u32 + 8u * stage, phase ^ 1u, 1, item, stage);
       const uint32_t fb = full_u32 + 8u * stage;
-      if (lane == 0) mbar_expect_tx(fb, (uint32_t)(nvalid * 2 * kD * 2));
-      __syncwarp();
-      if (lane < nvalid) {
-        const int64_t off = (int64_t)id * p.kv_block_stride + (int64_t)(tok % B) * p.kv_page_stride;
-        const uint32_t dst = ring_u32 + (uint32_t)stage * kFlashStageBytes + (uint32_t)lane * kFlashRowBytes;
-        bulk_g2s(dst, kbase + off, kD * 2, fb);
-        bulk_g2s(dst + kFlashVOffset, vbase + off, kD * 2, fb);
+      mbar_expect_tx(fb, (uint32_t)((two ? 8 : 4) * kFlashBoxBytes));
+      const uint32_t dst = ring_u32 + (uint32_t)stage * kFlashStageBytes;
+      const int off0 = tok % B;
+      tma_load_4d(dst, tm_k, 0, it.kvh, off0, id0, fb);
+      tma_load_4d(dst + kFlashBoxBytes, tm_k, 64, it.kvh, off0, id0, fb);
+      tma_load_4d(dst + kFlashVOffset, tm_v, 0, it.kvh, off0, id0, fb);
+      tma_load_4d(dst + kFlashVOffset + kFlashBoxBytes, tm_v, 64, it.kvh, off0, id0, fb);
+      if (two) {
+        const int off1 = (tok + 16) % B;
+        tma_load_4d(dst + 2 * kFlashBoxBytes, tm_k, 0, it.kvh, off1, id1, fb);
+        tma_load_4d(dst + 3 * kFlashBoxBytes, tm_k, 64, it.kvh, off1, id1, fb);
+        tma_load_4d(dst + kFlashVOffset + 2 * kFlashBoxBytes, tm_v, 0, it.kvh, off1, id1, fb);
+        tma_load_4d(dst + kFlashVOffset + 3 * kFlashBoxBytes, tm_v, 64, it.kvh, off1, id1, fb);
       }
       g_next += kProducerWarps;
       stage += kProducerWarps;

@@ -237,6 +237,7 @@ void paged_attention_flash(at::Tensor& out, std::optional<at::Tensor> lse, const
   p.q_stride = query.stride(0);
   p.kv_block_stride = key_cache.stride(0);
   p.kv_page_stride = key_cache.stride(1);
+  p.kv_num_blocks = key_cache.size(0);
   p.kv_head_stride = key_cache.stride(2);
   p.num_seqs = static_cast<int32_t>(query.size(0));
   p.num_heads = static_cast<int32_t>(query.size(1));
