@@ -38,6 +38,10 @@ WORKLOADS = {
            "Llama-3-8B decode attention, GQA 32q/8kv, head 128, block 16, batch 64, ctx 4096, bf16 KV"),
     "c3": (64, 32, 8, 128, 16, 4096, "fp8",
            "Llama-3-8B decode attention, GQA 32q/8kv, head 128, block 16, batch 64, ctx 4096, FP8-e4m3 KV"),
+    # the serving path of the reference: flash cache layout [NB, B, Hkv, D] (NHD), reshape_and_cache_flash +
+    # flash-layout decode (flash_attn_with_kvcache in the reference).  Same shapes and bytes as c2.
+    "c2_flash": (64, 32, 8, 128, 16, 4096, "auto",
+                 "Llama-3-8B decode attention, GQA 32q/8kv, head 128, block 16, batch 64, ctx 4096, bf16 KV, flash NHD cache layout"),
 }
 N_LAYERS = 32  # Llama-3-8B; tokens/s = S / (n_layers * t_step)  
 METRIC = "paged-attn decode HBM GB/s"
@@ -128,14 +132,18 @@ def make_workload(name, dev, seed=0):
         return (torch.rand(shape, device=dev, generator=g) * 2 - 1) * scale
 
     x = 16 if fp8 else 8
-    if fp8:
+    flash = name.endswith("_flash")
+    if flash:
+        kc = uni((NB, B, Hkv, D)).to(torch.bfloat16)
+        vc = uni((NB, B, Hkv, D)).to(torch.bfloat16)
+    elif fp8:
         kc = uni((NB, Hkv, D // x, B, x)).to(torch.float8_e4m3fn).view(torch.uint8)
         vc = uni((NB, Hkv, D, B)).to(torch.float8_e4m3fn).view(torch.uint8)
     else:
         kc = uni((NB, Hkv, D // x, B, x)).to(torch.bfloat16)
         vc = uni((NB, Hkv, D, B)).to(torch.bfloat16)
     w = dict(
-        name=name, S=S, H=H, Hkv=Hkv, D=D, B=B, L=L, kvd=kvd, scale=scale, kv_eb=1 if fp8 else 2,
+        name=name, flash=flash, S=S, H=H, Hkv=Hkv, D=D, B=B, L=L, kvd=kvd, scale=scale, kv_eb=1 if fp8 else 2,
         key_cache=kc, value_cache=vc,
         query=uni((S, H, D)).to(torch.bfloat16), key=uni((S, Hkv, D)).to(torch.bfloat16),
         value=uni((S, Hkv, D)).to(torch.bfloat16),
@@ -165,6 +173,8 @@ def run_ours(args):
     if world > 1:
         import torch.distributed as dist
 
+        # NCCL writes its version banner / debug lines to stdout; stdout carries the one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -176,11 +186,18 @@ def run_ours(args):
     S, H, Hkv, D, B, L = w["S"], w["H"], w["Hkv"], w["D"], w["B"], w["L"]
 
     def cache_write(key, value, slots):
-        ops.reshape_and_cache(key, value, w["key_cache"], w["value_cache"], slots, w["kvd"], w["k_scale"], w["v_scale"])
+        if w["flash"]:
+            ops.reshape_and_cache_flash(key, value, w["key_cache"], w["value_cache"], slots, w["kvd"], w["k_scale"],
+                                        w["v_scale"])
+        else:
+            ops.reshape_and_cache(key, value, w["key_cache"], w["value_cache"], slots, w["kvd"], w["k_scale"], w["v_scale"])
 
     def attention(q, bt, lens, out):
-        ops.paged_attention_v1(out, q, w["key_cache"], w["value_cache"], Hkv, w["scale"], bt, lens, B, L, None,
-                               w["kvd"], w["k_scale"], w["v_scale"])
+        if w["flash"]:
+            ops.paged_attention_flash(out, q, w["key_cache"], w["value_cache"], w["scale"], bt, lens, L)
+        else:
+            ops.paged_attention_v1(out, q, w["key_cache"], w["value_cache"], Hkv, w["scale"], bt, lens, B, L, None,
+                                   w["kvd"], w["k_scale"], w["v_scale"])
 
     def step():
         cache_write(w["key"], w["value"], w["slot_mapping"])
@@ -281,7 +298,8 @@ def run_ours(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16" if w["kvd"] == "auto" else "bf16 (q/out) + fp8-e4m3 (KV)", "data": "synthetic",
-        "config": {"workload": WORKLOADS[args.workload][7], "name": args.workload, "step": "reshape_and_cache + paged_attention_v1",
+        "config": {"workload": WORKLOADS[args.workload][7], "name": args.workload,
+                   "step": "reshape_and_cache_flash + paged_attention_flash" if w["flash"] else "reshape_and_cache + paged_attention_v1",
                    "l2": "inputs larger than L2 (KV working set %.2f GB vs 126 MB L2)" % (attn_bytes / 1e9),
                    "parallelism": "dp%d (independent sequences per GPU, no collective)" % world,
                    "block_tables": "unique random permutation, 1.25x over-provisioned cache", "seed": 0},
@@ -290,7 +308,7 @@ def run_ours(args):
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                      "frac": achieved / pk["hbm_gbs"], "traffic": TRAFFIC_BYTES.get(args.workload),
-                     "kernel": "paged_attention_stream_kernel (+ split reduce)", "algorithmic_bytes": attn_bytes,
+                     "kernel": "paged_attention_stream_kernel" + (" (flash layout, tiled TMA)" if w["flash"] else " (+ split reduce)"), "algorithmic_bytes": attn_bytes,
                      "peak_source": pk_src},
         "cpu_baseline": cpu,
         "extra": extra,
@@ -299,13 +317,14 @@ def run_ours(args):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the attention kernel, from the ncu --set full
-# captures committed under profiles/ (r1_c2_bf16_ncu_summary.txt, r1_c3_fp8_ncu_summary.txt); null where no capture exists.
-TRAFFIC_BYTES = {"c2": 1075123000 + 4585728, "c3": 538070016 + 4122624}
+# captures committed under profiles/ (r1_c2_bf16_ncu_summary.txt, r1_c3_fp8_ncu_summary.txt, r1_c2_flash_ncu_summary.txt); null where no capture exists.
+TRAFFIC_BYTES = {"c2": 1075123000 + 4585728, "c3": 538070016 + 4122624, "c2_flash": 1075082000 + 7046144}
 
 
 # ---- CPU arm --------------------------------------------------------------------------------------------
 def cpu_sample(workload, n_seqs, seed=0):
-    """A bounded sample of the workload for the CPU arm: the first n_seqs sequences (same shapes)."""
+    """A bounded sample of the workload for the CPU arm: the first n_seqs sequences (same shapes).  The C restatement
+    reads the v1/v2 cache layout; the flash workload is the same arithmetic over the same bytes, so it is timed on that."""
     S, H, Hkv, D, B, L, kvd, _ = WORKLOADS[workload]
     nblk = (L + B - 1) // B
     NB = n_seqs * nblk
