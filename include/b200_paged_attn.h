@@ -344,6 +344,61 @@ typedef struct b200_gather_cache_params {
  * torch.ops._C_cache_ops.cp_gather_cache (see the struct). */
 int b200_gather_cache(const b200_gather_cache_params_t* params, void* stream);
 
+/*
+ * Arguments of rotary_embedding, optionally fused with the flash-layout cache write that follows it in the
+ * serving step.
+ *   reference op  : csrc/torch_bindings.cpp:216-219
+ *   reference C++ : csrc/pos_encoding_kernels.cu:9-96 (kernels), :126-209 (host)
+ *   positions     [num_tokens] int64
+ *   query         [num_tokens, num_heads, head_size] dtype, rotated IN PLACE; token stride query_stride,
+ *                 head stride head_stride (the reference uses the query's head stride for the key too, :187-188)
+ *   key           nullable, [num_tokens, num_kv_heads, head_size], rotated in place; token stride key_stride
+ *   cos_sin_cache [max_position, rot_dim] dtype: cos in [0, rot_dim/2), sin in [rot_dim/2, rot_dim)
+ *   is_neox       1: pairs (i, i + rot_dim/2) (GPT-NeoX); 0: pairs (2i, 2i+1) (GPT-J)   (:15-29)
+ * Arithmetic as the reference kernel writes it (:31-34): x*cos - y*sin and y*cos + x*sin with every product and
+ * the sum rounded to dtype — bit-identical to the PyTorch-native implementation the reference tests against.
+ * Fused cache write (b200_rotary_embedding_and_cache_flash only): after the rotation the kernel scatters the
+ * rotated key and the value of the first num_cache_tokens tokens into the flash-layout caches exactly as
+ * b200_reshape_and_cache_flash would (same fields as b200_cache_write_params_t) — one launch instead of two.
+ */
+typedef struct b200_rotary_params {
+  const int64_t* positions;
+  void* query;
+  void* key; /* nullable */
+  const void* cos_sin_cache;
+  int64_t query_stride;
+  int64_t key_stride;
+  int64_t head_stride;
+  int32_t num_tokens;
+  int32_t num_heads;
+  int32_t num_kv_heads;
+  int32_t head_size;
+  int32_t rot_dim;
+  int32_t is_neox;
+  int32_t dtype; /* b200_dtype_t */
+  /* fused cache write */
+  int32_t num_cache_tokens; /* slot_mapping.size(0) <= num_tokens */
+  const void* value;
+  void* key_cache;
+  void* value_cache;
+  const int64_t* slot_mapping;
+  const float* k_scale;
+  const float* v_scale;
+  int64_t value_stride;
+  int64_t block_stride;
+  int64_t page_stride;
+  int64_t cache_head_stride;
+  int32_t block_size;
+  int32_t kv_dtype; /* b200_kv_dtype_t */
+} b200_rotary_params_t;
+
+/* Replaces torch.ops._C.rotary_embedding (the cache-write fields are ignored). */
+int b200_rotary_embedding(const b200_rotary_params_t* params, void* stream);
+
+/* rotary_embedding followed by reshape_and_cache_flash in one launch (no reference op: the reference runs the
+ * two ops back to back, vllm_metax/v1/attention/backends/flash_attn.py:678-687 after the model's rotary layer). */
+int b200_rotary_embedding_and_cache_flash(const b200_rotary_params_t* params, void* stream);
+
 /* "auto" -> B200_KV_AUTO, "fp8" | "fp8_e4m3" -> B200_KV_FP8_E4M3, anything
  * else (incl. "fp8_e5m2") -> -1. */
 int b200_kv_dtype_from_string(const char* kv_cache_dtype);

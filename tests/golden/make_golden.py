@@ -186,6 +186,30 @@ def make_flash():
         print("wrote", name, tuple(out.shape))
 
 
+def make_rotary():
+    """Rotary goldens from upstream vLLM's own PyTorch-native implementation — the oracle of the reference's kernel
+    test (tests/kernels/core/test_pos_encoding.py:79-81 `rope.forward_native`).  The class cannot be instantiated
+    without an engine config, so the static method that forward_native calls is used directly; the installed
+    upstream (0.22) differs from the plugin's pinned version only in packaging, not in this arithmetic."""
+    from vllm.model_executor.layers.rotary_embedding.base import RotaryEmbedding
+
+    cases = [  # name, tokens, H, Hkv, head_size, rot_dim, neox, dtype
+        ("rotary_bf16_neox_d128", 9, 8, 2, 128, 128, True, torch.bfloat16),
+        ("rotary_f16_gptj_d80_r32", 7, 4, 4, 80, 32, False, torch.float16),
+        ("rotary_f32_neox_d64", 5, 4, 2, 64, 64, True, torch.float32),
+    ]
+    for idx, (name, n, H, Hkv, D, R, neox, dtype) in enumerate(cases):
+        g = torch.Generator().manual_seed(400 + idx)
+        cache = orc.compute_cos_sin_cache(R, 512, dtype=dtype)
+        positions = torch.randint(0, 512, (n,), generator=g)
+        q = torch.randn(n, H * D, generator=g).to(dtype)
+        k = torch.randn(n, Hkv * D, generator=g).to(dtype)
+        rq, rk = RotaryEmbedding.forward_static(positions, q.clone(), k.clone(), D, R, cache, neox)
+        torch.save(dict(positions=positions, query=q, key=k, head_size=D, cos_sin_cache=cache, is_neox=neox,
+                        ref_query=rq, ref_key=rk), os.path.join(HERE, name + ".pt"))
+        print("wrote", name)
+
+
 def make_movers():
     """copy_blocks / gather goldens: the reference tests' own expectation loops, transcribed next to their lines."""
     rnd = random.Random(5)
@@ -248,3 +272,4 @@ if __name__ == "__main__":
     make_merge(load_reference_merge())
     make_movers()
     make_flash()
+    make_rotary()

@@ -48,7 +48,8 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
     for cname, st in (("b200_paged_attn_params_t", native.PagedAttnParams),
                       ("b200_cache_write_params_t", native.CacheWriteParams),
                       ("b200_merge_attn_states_params_t", native.MergeAttnStatesParams),
-                      ("b200_gather_cache_params_t", native.GatherCacheParams)):
+                      ("b200_gather_cache_params_t", native.GatherCacheParams),
+                      ("b200_rotary_params_t", native.RotaryParams)):
         prog.append('printf("%%zu\\n", sizeof(%s));' % cname)
         for f in fields(st):
             prog.append('printf("%%zu\\n", offsetof(%s, %s));' % (cname, f))
@@ -59,7 +60,8 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     vals = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     it = iter(vals)
-    for st in (native.PagedAttnParams, native.CacheWriteParams, native.MergeAttnStatesParams, native.GatherCacheParams):
+    for st in (native.PagedAttnParams, native.CacheWriteParams, native.MergeAttnStatesParams, native.GatherCacheParams,
+               native.RotaryParams):
         assert next(it) == C.sizeof(st)
         for f in fields(st):
             assert next(it) == getattr(st, f).offset, f
@@ -144,6 +146,14 @@ def test_new_entry_points_validate_on_the_host(native):
     gp.src_dtype, gp.dst_dtype, gp.kv_dtype = native.DTYPE_F32, native.DTYPE_F16, native.KV_AUTO
     assert lib.b200_gather_cache(C.byref(gp), None) == native.ERR_UNSUPPORTED
     assert "same dtype" in lib.b200_last_error().decode()
+    rp = native.RotaryParams()
+    rp.num_tokens, rp.num_heads, rp.num_kv_heads, rp.head_size, rp.rot_dim, rp.dtype = 0, 8, 2, 128, 128, native.DTYPE_BF16
+    assert lib.b200_rotary_embedding(C.byref(rp), None) == 0
+    rp.num_tokens = 4
+    assert lib.b200_rotary_embedding(C.byref(rp), None) == native.ERR_INVALID_ARGUMENT  # NULL tensors
+    rp.rot_dim = 130
+    assert lib.b200_rotary_embedding(C.byref(rp), None) == native.ERR_INVALID_ARGUMENT
+    assert "rot_dim" in lib.b200_last_error().decode()
     assert lib.b200_copy_blocks(None, None, 0, None, 0, 0, None) == 0
     assert lib.b200_swap_blocks(None, None, None, 0, 4096, native.COPY_D2D, None) == 0
     m = (C.c_int64 * 2)(0, 1)
@@ -197,6 +207,9 @@ def test_torch_shim_registers_reference_schemas_and_has_no_cpu_fallback(native):
     assert str(torch.ops._C_cache_ops.cp_gather_cache.default._schema) == (
         "_C_cache_ops::cp_gather_cache(Tensor src_cache, Tensor($0! -> ) dst, Tensor block_table, Tensor cu_seq_lens, "
         "int batch_size, Tensor? seq_starts) -> ()")
+    assert str(torch.ops._C.rotary_embedding.default._schema) == (
+        "_C::rotary_embedding(Tensor positions, Tensor($0! -> ) query, Tensor($1! -> )? key, int head_size, "
+        "Tensor cos_sin_cache, bool is_neox) -> ()")
     # CPU tensors: the dispatcher must refuse (only the CUDA key is implemented, as in the reference)
     q = torch.zeros(1, 8, 128, dtype=torch.bfloat16)
     kc = torch.zeros(4, 2, 16, 16, 8, dtype=torch.bfloat16)

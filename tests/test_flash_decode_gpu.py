@@ -126,3 +126,109 @@ def test_paged_attention_flash_rejects_unsupported(ops):
     sl = torch.ones(2, dtype=torch.int32, device="cuda")
     with pytest.raises(RuntimeError, match="head_size is not 128"):
         ops.paged_attention_flash(torch.empty_like(q), q, kc, kc.clone(), 0.1, bt, sl, 16)
+
+
+def test_decode_step_is_cuda_graph_capturable(ops):
+    """The C-ABI calls only enqueue work (no sync, no allocation, no host read of device memory), so a decode step —
+    cache write, v1-layout and flash-layout attention, LSE, merge — can be captured once and replayed with new
+    inputs in the same buffers (the reference's ops are used under CUDA graphs the same way)."""
+    S, H, Hkv, D, B, L = 6, 32, 8, 128, 16, 900
+    d = orc.make_flash_decode_inputs(S, H, Hkv, D, B, L, S * ((L + B - 1) // B) + 3, seed=8)
+    g = _to(d)
+    v1 = orc.make_decode_inputs(S, H, Hkv, D, B, L, S * ((L + B - 1) // B) + 3, seed=8, unique_blocks=True)
+    v1g = _to(v1)
+    one = torch.ones(1, device="cuda")
+    key = torch.zeros(S, Hkv, D, dtype=torch.bfloat16, device="cuda")
+    value = torch.zeros_like(key)
+    slots = torch.zeros(S, dtype=torch.long, device="cuda")
+    q = g["query"].clone()
+    out_f, out_1, merged = torch.empty_like(q), torch.empty_like(q), torch.empty_like(q)
+    lse_f = torch.empty(H, S, dtype=torch.float32, device="cuda")
+    lse_1 = torch.empty_like(lse_f)
+
+    def step():
+        ops.reshape_and_cache_flash(key, value, g["key_cache"], g["value_cache"], slots, "auto", one, one)
+        ops.paged_attention_flash(out_f, q, g["key_cache"], g["value_cache"], d["scale"], g["block_tables"],
+                                  g["seq_lens"], L, None, lse_f)
+        ops.paged_attention_v1_lse(out_1, lse_1, q, v1g["key_cache"], v1g["value_cache"], Hkv, v1["scale"],
+                                   v1g["block_tables"], v1g["seq_lens"], B, L, None, "auto", one, one)
+        ops.merge_attn_states(merged, out_f, lse_f, out_1, lse_1)
+
+    stream = torch.cuda.Stream()
+    stream.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(stream):
+        step()  # warm-up on the capture stream: the shim allocates its per-stream scratch here
+    torch.cuda.current_stream().wait_stream(stream)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=stream):
+        step()
+    lens = d["seq_lens"]
+    gen = torch.Generator().manual_seed(5)
+    for it in range(3):  # new query / new token each replay, same buffers
+        qn = ((torch.rand(S, H, D, generator=gen) * 2 - 1) * d["scale"]).to(torch.bfloat16)
+        kn = (torch.randn(S, Hkv, D, generator=gen) * 0.05).to(torch.bfloat16)
+        vn = (torch.randn(S, Hkv, D, generator=gen) * 0.05).to(torch.bfloat16)
+        sl = torch.tensor([int(d["block_tables"][s, (int(lens[s]) - 1) // B]) * B + (int(lens[s]) - 1) % B
+                           for s in range(S)], dtype=torch.long)
+        q.copy_(qn); key.copy_(kn); value.copy_(vn); slots.copy_(sl)
+        graph.replay()
+        torch.cuda.synchronize()
+        rk, rv = g["key_cache"].cpu(), g["value_cache"].cpu()  # the cache after this replay's write
+        ref_f = orc.paged_attention_flash(qn, rk, rv, d["block_tables"], lens, d["scale"])
+        ref_1 = orc.paged_attention(qn, v1["key_cache"], v1["value_cache"], v1["block_tables"], v1["seq_lens"], v1["scale"])
+        assert torch.equal(rk[sl // B, sl % B], kn) and torch.equal(rv[sl // B, sl % B], vn)
+        assert (out_f.cpu().float() - ref_f.float()).abs().max() <= 2e-3
+        assert (out_1.cpu().float() - ref_1.float()).abs().max() <= 2e-3
+        l_f = orc.paged_attention_flash_lse(qn, rk, rv, d["block_tables"], lens, d["scale"])
+        l_1 = orc.paged_attention_lse(qn, v1["key_cache"], v1["value_cache"], v1["block_tables"], v1["seq_lens"], v1["scale"])
+        ref_m, _ = orc.merge_attn_states(ref_f, l_f, ref_1, l_1)
+        assert (merged.cpu().float() - ref_m.float()).abs().max() <= 4e-3
+
+
+@pytest.mark.parametrize("layout", ["NHD", "HND"])
+def test_decode_impl_forward_and_split_merge(ops, layout):
+    """B200FlashDecodeImpl.forward = the decode branch of the reference's FlashAttentionImpl.forward
+    (vllm_metax/v1/attention/backends/flash_attn.py:661-762): cache write from slot_mapping, then decode attention."""
+    from vllm_metax_b200.attention import B200FlashDecodeBackend, B200FlashDecodeImpl, DecodeMetadata
+
+    S, H, Hkv, D, B, L = 9, 32, 8, 128, 16, 500
+    NB = S * ((L + B - 1) // B) + 3
+    d = orc.make_flash_decode_inputs(S, H, Hkv, D, B, L, NB, seed=12, hnd=(layout == "HND"))
+    lens = d["seq_lens"]
+    shape = B200FlashDecodeBackend.get_kv_cache_shape(NB, B, Hkv, D)
+    order = B200FlashDecodeBackend.get_kv_cache_stride_order(layout)
+    # allocate in storage order, view in logical order — as the engine does with the stride order
+    storage = torch.empty([shape[i] for i in order], dtype=torch.bfloat16, device="cuda")
+    inv = [order.index(i) for i in range(5)]
+    kv_cache = storage.permute(*inv)
+    assert tuple(kv_cache.shape) == shape
+    kv_cache[0].copy_(d["key_cache"].cuda())
+    kv_cache[1].copy_(d["value_cache"].cuda())
+    gen = torch.Generator().manual_seed(3)
+    pad = 3  # key/value padded past slot_mapping (CUDA-graph padding, flash_attn.py:671-677)
+    key = (torch.randn(S + pad, Hkv, D, generator=gen) * 0.05).to(torch.bfloat16)
+    value = (torch.randn(S + pad, Hkv, D, generator=gen) * 0.05).to(torch.bfloat16)
+    slots = torch.tensor([int(d["block_tables"][s, (int(lens[s]) - 1) // B]) * B + (int(lens[s]) - 1) % B
+                          for s in range(S)], dtype=torch.long)
+    one = torch.ones(1)
+    rk, rv = d["key_cache"].clone(), d["value_cache"].clone()
+    orc.reshape_and_cache_flash(key, value, rk, rv, slots, "auto", one, one)
+    ref = orc.paged_attention_flash(d["query"], rk, rv, d["block_tables"], lens, d["scale"])
+    impl = B200FlashDecodeImpl(H, D, d["scale"], Hkv)
+    md = DecodeMetadata(num_actual_tokens=S, num_decode_tokens=S, slot_mapping=slots.cuda(),
+                        decode_block_table=d["block_tables"].cuda(), decode_seq_lens=lens.cuda(), max_seq_len=L)
+    q = torch.cat([d["query"], torch.zeros(pad, H, D, dtype=torch.bfloat16)]).cuda()
+    output = torch.zeros_like(q)
+    impl.forward(q, key.cuda(), value.cuda(), kv_cache, md, output)
+    assert torch.equal(kv_cache[0].cpu(), rk) and torch.equal(kv_cache[1].cpu(), rv)
+    assert (output[:S].cpu().float() - ref.float()).abs().max() <= 2e-3
+    assert (output[S:] == 0).all()
+    # split at a block boundary + merge_attn_states == attention over the whole sequence
+    split = (lens // 3 // B * B).to(torch.int32)
+    merged = torch.empty(S, H, D, dtype=torch.bfloat16, device="cuda")
+    mlse = torch.empty(H, S, dtype=torch.float32, device="cuda")
+    impl.forward_decode_split(q[:S], kv_cache, d["block_tables"].cuda(), lens.cuda(), split.cuda(), L, merged, mlse)
+    assert (merged.cpu().float() - ref.float()).abs().max() <= 2e-3
+    ref_lse = orc.paged_attention_flash_lse(d["query"], rk, rv, d["block_tables"], lens, d["scale"])
+    torch.testing.assert_close(mlse.cpu(), ref_lse, atol=2e-3, rtol=1e-4)

@@ -152,3 +152,17 @@ def test_flash_and_v1_layout_oracles_agree():
     a = orc.paged_attention_flash(d["query"], d["key_cache"], d["value_cache"], d["block_tables"], d["seq_lens"], d["scale"])
     b = orc.paged_attention(d["query"], kc, vc, d["block_tables"], d["seq_lens"], d["scale"])
     torch.testing.assert_close(a.float(), b.float(), atol=1e-3, rtol=1e-2)
+
+
+ROTARY = sorted(glob.glob(os.path.join(GOLDEN, "rotary_*.pt")))
+
+
+@pytest.mark.parametrize("path", ROTARY, ids=[os.path.basename(p)[:-3] for p in ROTARY])
+def test_rotary_oracle_matches_upstream_native(path):
+    """oracle.rotary_embedding against upstream vLLM's RotaryEmbedding.forward_static (the `forward_native` the
+    reference's tests/kernels/core/test_pos_encoding.py compares the kernel with), run by make_golden.py."""
+    assert len(ROTARY) >= 3
+    d = torch.load(path)
+    q, k = orc.rotary_embedding(d["positions"], d["query"], d["key"], d["head_size"], d["cos_sin_cache"], d["is_neox"])
+    assert torch.equal(q, d["ref_query"]) and torch.equal(k, d["ref_key"])
+    assert not torch.equal(q, d["query"])

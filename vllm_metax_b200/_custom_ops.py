@@ -200,3 +200,38 @@ def paged_attention_flash(
     with that signature."""
     torch.ops._C_b200.paged_attention_flash(out, lse, query, key_cache, value_cache, scale, block_tables, seq_lens,
                                             max_seq_len, alibi_slopes)
+
+
+def rotary_embedding(
+    positions: torch.Tensor,
+    query: torch.Tensor,
+    key: torch.Tensor | None,
+    head_size: int,
+    cos_sin_cache: torch.Tensor,
+    is_neox: bool,
+) -> None:
+    """In-place rotary position embedding of query (and key).  reference: csrc/torch_bindings.cpp:216-219,
+    csrc/pos_encoding_kernels.cu:126-209; wrapper as upstream `ops.rotary_embedding`."""
+    torch.ops._C.rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox)
+
+
+def rotary_embedding_and_cache_flash(
+    positions: torch.Tensor,
+    query: torch.Tensor,
+    key: torch.Tensor,
+    value: torch.Tensor,
+    head_size: int,
+    cos_sin_cache: torch.Tensor,
+    is_neox: bool,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+) -> None:
+    """rotary_embedding(positions, query, key, ...) followed by reshape_and_cache_flash(key, value, ...) in ONE launch
+    (same results, byte for byte, as the two reference ops back to back).  Not a reference op (namespace `_C_b200`)."""
+    torch.ops._C_b200.rotary_embedding_and_cache_flash(positions, query, key, value, head_size, cos_sin_cache, is_neox,
+                                                       key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale,
+                                                       v_scale)

@@ -28,6 +28,8 @@ EXPORTED_SYMBOLS = (
     "b200_reshape_and_cache",
     "b200_reshape_and_cache_flash",
     "b200_convert_fp8",
+    "b200_rotary_embedding",
+    "b200_rotary_embedding_and_cache_flash",
     "b200_merge_attn_states",
     "b200_copy_blocks",
     "b200_swap_blocks",
@@ -145,6 +147,38 @@ class GatherCacheParams(C.Structure):
     ]
 
 
+class RotaryParams(C.Structure):
+    _fields_ = [
+        ("positions", C.c_void_p),
+        ("query", C.c_void_p),
+        ("key", C.c_void_p),
+        ("cos_sin_cache", C.c_void_p),
+        ("query_stride", C.c_int64),
+        ("key_stride", C.c_int64),
+        ("head_stride", C.c_int64),
+        ("num_tokens", C.c_int32),
+        ("num_heads", C.c_int32),
+        ("num_kv_heads", C.c_int32),
+        ("head_size", C.c_int32),
+        ("rot_dim", C.c_int32),
+        ("is_neox", C.c_int32),
+        ("dtype", C.c_int32),
+        ("num_cache_tokens", C.c_int32),
+        ("value", C.c_void_p),
+        ("key_cache", C.c_void_p),
+        ("value_cache", C.c_void_p),
+        ("slot_mapping", C.c_void_p),
+        ("k_scale", C.c_void_p),
+        ("v_scale", C.c_void_p),
+        ("value_stride", C.c_int64),
+        ("block_stride", C.c_int64),
+        ("page_stride", C.c_int64),
+        ("cache_head_stride", C.c_int64),
+        ("block_size", C.c_int32),
+        ("kv_dtype", C.c_int32),
+    ]
+
+
 COPY_D2D, COPY_D2H, COPY_H2D = 0, 1, 2
 
 _lib = None
@@ -183,6 +217,10 @@ def load() -> C.CDLL:
     lib.b200_convert_fp8.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_int32, C.c_int32, C.c_int32,
                                      C.c_void_p]
     lib.b200_convert_fp8.restype = C.c_int
+    lib.b200_rotary_embedding.argtypes = [P(RotaryParams), C.c_void_p]
+    lib.b200_rotary_embedding.restype = C.c_int
+    lib.b200_rotary_embedding_and_cache_flash.argtypes = [P(RotaryParams), C.c_void_p]
+    lib.b200_rotary_embedding_and_cache_flash.restype = C.c_int
     lib.b200_merge_attn_states.argtypes = [P(MergeAttnStatesParams), C.c_void_p]
     lib.b200_merge_attn_states.restype = C.c_int
     lib.b200_copy_blocks.argtypes = [P(C.c_void_p), P(C.c_void_p), C.c_int32, C.c_void_p, C.c_int32, C.c_int64,

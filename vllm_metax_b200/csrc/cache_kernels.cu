@@ -9,6 +9,10 @@
 // head_stride == head_size.  The kernels are written for B200: one CTA per
 // token, 16-byte loads of the source row, 16-byte (auto) / 8-byte (fp8)
 // stores wherever the destination run is contiguous, scalar path otherwise.
+#include <string.h>
+
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -92,8 +96,7 @@ __global__ void reshape_and_cache_kernel(b200_cache_write_params_t p) {
 // (+ h*head_stride); every head's D elements are contiguous in both layouts,
 // so one vector never straddles a head when D % kElems == 0.
 template <typename T, bool FP8, bool VEC>
-__global__ void reshape_and_cache_flash_kernel(b200_cache_write_params_t p) {
-  const int64_t token = blockIdx.x;
+__device__ __forceinline__ void scatter_flash_token(const b200_cache_write_params_t& p, int64_t token) {
   const int64_t slot = p.slot_mapping[token];
   if (slot < 0) return;  // padding token (csrc/cache_kernels.cu:285-289)
   const int64_t blk = slot / p.block_size;
@@ -130,6 +133,55 @@ __global__ void reshape_and_cache_flash_kernel(b200_cache_write_params_t p) {
   }
 }
 
+template <typename T, bool FP8, bool VEC>
+__global__ void reshape_and_cache_flash_kernel(b200_cache_write_params_t p) {
+  scatter_flash_token<T, FP8, VEC>(p, blockIdx.x);
+}
+
+// ---- rotary_embedding (+ fused flash cache write) ---------------------------------------------------------------
+// Reference: csrc/pos_encoding_kernels.cu:9-96.  One CTA per token.  The rotation is written as the reference
+// writes it in scalar_t arithmetic (:31-34): each product and the sum are rounded to T, which is also what the
+// PyTorch-native implementation the reference tests against does — so results are bit-identical to that oracle.
+template <typename T>
+__device__ __forceinline__ T rnd(float v) { return from_f32<T>(v); }
+
+template <typename T, bool NEOX>
+__device__ __forceinline__ void rotate_heads(T* base, int64_t head_stride, int nheads, int embed, const T* cos_ptr,
+                                             const T* sin_ptr) {
+  const int n = nheads * embed;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int head = i / embed, r = i % embed;
+    T* arr = base + (int64_t)head * head_stride;
+    const int xi = NEOX ? r : 2 * r;
+    const int yi = NEOX ? embed + r : 2 * r + 1;
+    const float c = to_f32<T>(cos_ptr[r]), sn = to_f32<T>(sin_ptr[r]);
+    const float x = to_f32<T>(arr[xi]), y = to_f32<T>(arr[yi]);
+    const float xc = to_f32<T>(rnd<T>(__fmul_rn(x, c))), ys = to_f32<T>(rnd<T>(__fmul_rn(y, sn)));
+    const float yc = to_f32<T>(rnd<T>(__fmul_rn(y, c))), xs = to_f32<T>(rnd<T>(__fmul_rn(x, sn)));
+    arr[xi] = rnd<T>(__fsub_rn(xc, ys));
+    arr[yi] = rnd<T>(__fadd_rn(yc, xs));
+  }
+}
+
+template <typename T, bool NEOX, int FUSE>  // FUSE: 0 none, 1 auto scalar, 2 auto vec, 3 fp8 scalar, 4 fp8 vec
+__global__ void rotary_embedding_kernel(const b200_rotary_params_t p, const b200_cache_write_params_t cw) {
+  const int64_t token = blockIdx.x;
+  const int64_t pos = p.positions[token];
+  const int embed = p.rot_dim / 2;
+  const T* cos_ptr = reinterpret_cast<const T*>(p.cos_sin_cache) + pos * p.rot_dim;
+  const T* sin_ptr = cos_ptr + embed;
+  rotate_heads<T, NEOX>(reinterpret_cast<T*>(p.query) + token * p.query_stride, p.head_stride, p.num_heads, embed,
+                        cos_ptr, sin_ptr);
+  if (p.key != nullptr)
+    rotate_heads<T, NEOX>(reinterpret_cast<T*>(p.key) + token * p.key_stride, p.head_stride, p.num_kv_heads, embed,
+                          cos_ptr, sin_ptr);
+  if constexpr (FUSE != 0) {
+    if (token >= p.num_cache_tokens) return;  // CUDA-graph padding: slot_mapping is shorter than key
+    __syncthreads();  // the rotated key row of this token is visible to the whole CTA
+    scatter_flash_token<T, (FUSE >= 3), (FUSE == 2 || FUSE == 4)>(cw, token);
+  }
+}
+
 // ---- convert_fp8 ---------------------------------------------------------------
 template <typename T>
 __global__ void fp8_quant_kernel(uint8_t* __restrict__ dst, const T* __restrict__ src,
@@ -152,7 +204,6 @@ template <typename T>
 int launch_reshape_and_cache(const b200_cache_write_params_t& p, cudaStream_t s) {
   constexpr int N = VecOf<T>::kElems;
   const bool fp8 = p.kv_dtype == B200_KV_FP8_E4M3;
-  const int n = p.num_heads * p.head_size;
   // vector path: x-units are whole vectors, source rows and the destination
   // units are vector aligned.
   const int cache_bytes = fp8 ? 1 : (int)sizeof(T);
@@ -282,4 +333,103 @@ extern "C" int b200_convert_fp8(void* dst, const void* src, int64_t n, float sca
 #undef DQ
   count_launch();
   return check_launch("convert_fp8");
+}
+
+namespace b200 {
+namespace {
+
+int validate_rotary(const b200_rotary_params_t* p) {
+  B200_REQUIRE(p != nullptr, B200_ERR_INVALID_ARGUMENT, "params is NULL");
+  B200_REQUIRE(p->num_tokens >= 0 && p->num_heads > 0 && p->num_kv_heads > 0 && p->head_size > 0,
+               B200_ERR_INVALID_ARGUMENT, "bad sizes: tokens=%d heads=%d kv_heads=%d head_size=%d", p->num_tokens,
+               p->num_heads, p->num_kv_heads, p->head_size);
+  B200_REQUIRE(p->rot_dim > 0 && p->rot_dim % 2 == 0 && p->rot_dim <= p->head_size, B200_ERR_INVALID_ARGUMENT,
+               "rot_dim %d must be even and at most head_size %d", p->rot_dim, p->head_size);
+  B200_REQUIRE(p->num_heads % p->num_kv_heads == 0, B200_ERR_INVALID_ARGUMENT,
+               "num_heads %d is not a multiple of num_kv_heads %d", p->num_heads, p->num_kv_heads);  // :182
+  B200_REQUIRE(p->dtype == B200_DTYPE_F32 || p->dtype == B200_DTYPE_F16 || p->dtype == B200_DTYPE_BF16,
+               B200_ERR_UNSUPPORTED, "Unsupported data type: %d", p->dtype);
+  if (p->num_tokens == 0) return B200_OK;
+  B200_REQUIRE(p->positions && p->query && p->cos_sin_cache, B200_ERR_INVALID_ARGUMENT, "NULL tensor pointer");
+  return B200_OK;
+}
+
+template <typename T>
+int launch_rotary(const b200_rotary_params_t& p, bool fuse, cudaStream_t s) {
+  b200_cache_write_params_t cw;
+  memset(&cw, 0, sizeof(cw));
+  int mode = 0;
+  if (fuse) {
+    cw.key = p.key; cw.value = p.value; cw.key_cache = p.key_cache; cw.value_cache = p.value_cache;
+    cw.slot_mapping = p.slot_mapping; cw.k_scale = p.k_scale; cw.v_scale = p.v_scale;
+    cw.key_stride = p.key_stride; cw.value_stride = p.value_stride;
+    cw.block_stride = p.block_stride; cw.page_stride = p.page_stride; cw.head_stride = p.cache_head_stride;
+    cw.num_tokens = p.num_cache_tokens; cw.num_heads = p.num_kv_heads; cw.head_size = p.head_size;
+    cw.block_size = p.block_size; cw.dtype = p.dtype; cw.kv_dtype = p.kv_dtype;
+    constexpr int N = VecOf<T>::kElems;
+    const bool fp8 = p.kv_dtype == B200_KV_FP8_E4M3;
+    const size_t dst_align = (size_t)N * (fp8 ? 1 : sizeof(T));
+    // the vector path reads the key row as contiguous heads: needs head_stride == head_size
+    const bool vec = (p.head_stride == p.head_size) && (p.head_size % N == 0) && (p.key_stride % N == 0) &&
+                     (p.value_stride % N == 0) && (p.block_stride % N == 0) && (p.page_stride % N == 0) &&
+                     (p.cache_head_stride % N == 0) && aligned(p.key, 16) && aligned(p.value, 16) &&
+                     aligned(p.key_cache, dst_align) && aligned(p.value_cache, dst_align);
+    mode = fp8 ? (vec ? 4 : 3) : (vec ? 2 : 1);
+  }
+  const int work = p.num_heads * p.rot_dim / 2;
+  const int threads = std::max(32, std::min(512, (work + 31) / 32 * 32));  // csrc/pos_encoding_kernels.cu:191
+  dim3 grid(p.num_tokens), block(threads);
+#define ROT(NEOX, MODE) rotary_embedding_kernel<T, NEOX, MODE><<<grid, block, 0, s>>>(p, cw)
+#define ROT_MODE(NEOX)                                                                              \
+  switch (mode) {                                                                                   \
+    case 0: ROT(NEOX, 0); break;                                                                    \
+    case 1: ROT(NEOX, 1); break;                                                                    \
+    case 2: ROT(NEOX, 2); break;                                                                    \
+    case 3: ROT(NEOX, 3); break;                                                                    \
+    default: ROT(NEOX, 4); break;                                                                   \
+  }
+  if (p.is_neox) { ROT_MODE(true) } else { ROT_MODE(false) }
+#undef ROT_MODE
+#undef ROT
+  count_launch();
+  return check_launch(fuse ? "rotary_embedding_and_cache_flash" : "rotary_embedding");
+}
+
+int dispatch_rotary(const b200_rotary_params_t* p, bool fuse, void* stream) {
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (p->dtype) {
+    case B200_DTYPE_F32: return launch_rotary<float>(*p, fuse, s);
+    case B200_DTYPE_F16: return launch_rotary<__half>(*p, fuse, s);
+    default: return launch_rotary<__nv_bfloat16>(*p, fuse, s);
+  }
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200_rotary_embedding(const b200_rotary_params_t* p, void* stream) {
+  using namespace b200;
+  int rc = validate_rotary(p);
+  if (rc != B200_OK || p->num_tokens == 0) return rc;
+  return dispatch_rotary(p, false, stream);
+}
+
+extern "C" int b200_rotary_embedding_and_cache_flash(const b200_rotary_params_t* p, void* stream) {
+  using namespace b200;
+  int rc = validate_rotary(p);
+  if (rc != B200_OK || p->num_tokens == 0) return rc;
+  B200_REQUIRE(p->key && p->value && p->key_cache && p->value_cache && p->slot_mapping, B200_ERR_INVALID_ARGUMENT,
+               "NULL tensor pointer (the fused cache write needs key, value, both caches and slot_mapping)");
+  B200_REQUIRE(p->num_cache_tokens >= 0 && p->num_cache_tokens <= p->num_tokens && p->block_size > 0,
+               B200_ERR_INVALID_ARGUMENT, "bad sizes: cache tokens=%d tokens=%d block=%d", p->num_cache_tokens,
+               p->num_tokens, p->block_size);
+  B200_REQUIRE(p->kv_dtype == B200_KV_AUTO || p->kv_dtype == B200_KV_FP8_E4M3, B200_ERR_UNSUPPORTED,
+               "Unsupported data type of kv cache: %d", p->kv_dtype);
+  if (p->kv_dtype != B200_KV_AUTO)
+    B200_REQUIRE(p->k_scale && p->v_scale, B200_ERR_INVALID_ARGUMENT, "fp8 cache needs k_scale/v_scale");
+  // the cache writer reads a token's heads as one contiguous run (as reshape_and_cache_flash does)
+  B200_REQUIRE(p->head_stride == p->head_size, B200_ERR_UNSUPPORTED,
+               "the fused cache write needs contiguous heads (head_stride %lld != head_size %d)",
+               (long long)p->head_stride, p->head_size);
+  return dispatch_rotary(p, true, stream);
 }

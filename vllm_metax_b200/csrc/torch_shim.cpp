@@ -257,6 +257,112 @@ void paged_attention_flash(at::Tensor& out, std::optional<at::Tensor> lse, const
   check_status(b200_paged_attention_flash(&p, stream), "paged_attention_flash");
 }
 
+void fill_cache_params(b200_cache_write_params_t& p, const at::Tensor& key, const at::Tensor& value,
+                       const at::Tensor& key_cache, const at::Tensor& value_cache, const at::Tensor& slot_mapping,
+                       const std::string& kv_cache_dtype, const at::Tensor& k_scale, const at::Tensor& v_scale);
+
+// csrc/ops.h (rotary_embedding) ; csrc/pos_encoding_kernels.cu:126-209
+void fill_rotary_params(b200_rotary_params_t& p, const at::Tensor& positions, at::Tensor& query,
+                        std::optional<at::Tensor>& key, int64_t head_size, const at::Tensor& cos_sin_cache,
+                        bool is_neox) {
+  const int64_t num_tokens = positions.numel();
+  const int64_t pd = positions.dim();
+  TORCH_CHECK(pd == 1 || pd == 2, "positions must have shape [num_tokens] or [batch_size, seq_len]");
+  const bool has_key = key.has_value() && key->defined();
+  if (pd == 1) {
+    TORCH_CHECK(query.size(0) == positions.size(0) && (!has_key || key->size(0) == positions.size(0)),
+                "query, key and positions must have the same number of tokens");
+  } else {
+    TORCH_CHECK(query.size(0) == positions.size(0) && (!has_key || key->size(0) == positions.size(0)) &&
+                    query.size(1) == positions.size(1) && (!has_key || key->size(1) == positions.size(1)),
+                "query, key and positions must have the same batch_size and seq_len");
+  }
+  TORCH_CHECK(positions.scalar_type() == at::kLong && positions.is_contiguous(), "positions must be contiguous int64");
+  TORCH_CHECK(query.is_cuda() && positions.is_cuda() && cos_sin_cache.is_cuda() && (!has_key || key->is_cuda()),
+              "all tensors must be on the CUDA device");
+  TORCH_CHECK(cos_sin_cache.scalar_type() == query.scalar_type() && (!has_key || key->scalar_type() == query.scalar_type()),
+              "query, key and cos_sin_cache dtypes differ");
+  TORCH_CHECK(cos_sin_cache.dim() == 2 && cos_sin_cache.is_contiguous(), "cos_sin_cache must be contiguous [max_position, rot_dim]");
+  memset(&p, 0, sizeof(p));
+  if (num_tokens == 0) return;
+  const int64_t q_hidden = query.numel() / num_tokens;
+  const int64_t k_hidden = has_key ? key->numel() / num_tokens : 0;
+  TORCH_CHECK(q_hidden % head_size == 0);
+  TORCH_CHECK(k_hidden % head_size == 0);
+  const int64_t num_heads = q_hidden / head_size;
+  const int64_t num_kv_heads = has_key ? k_hidden / head_size : num_heads;
+  TORCH_CHECK(num_heads % num_kv_heads == 0);
+  const int64_t seq_dim = pd - 1;
+  if (pd == 2) {  // [batch, seq, ...]: token t = b * seq_len + s must be one stride apart
+    TORCH_CHECK(query.stride(0) == query.stride(1) * query.size(1) &&
+                    (!has_key || key->stride(0) == key->stride(1) * key->size(1)),
+                "batched query/key must be dense over (batch, seq)");
+  }
+  const int dt = to_dtype(query.scalar_type());
+  TORCH_CHECK(dt == B200_DTYPE_F32 || dt == B200_DTYPE_F16 || dt == B200_DTYPE_BF16, "Unsupported data type: ",
+              query.scalar_type());
+  p.positions = positions.data_ptr<int64_t>();
+  p.query = query.data_ptr();
+  p.key = has_key ? key->data_ptr() : nullptr;
+  p.cos_sin_cache = cos_sin_cache.data_ptr();
+  p.query_stride = query.stride(seq_dim);
+  p.key_stride = has_key ? key->stride(seq_dim) : 0;
+  p.head_stride = (query.dim() == pd + 2) ? query.stride(-2) : head_size;  // pos_encoding_kernels.cu:187-188
+  p.num_tokens = static_cast<int32_t>(num_tokens);
+  p.num_heads = static_cast<int32_t>(num_heads);
+  p.num_kv_heads = static_cast<int32_t>(num_kv_heads);
+  p.head_size = static_cast<int32_t>(head_size);
+  p.rot_dim = static_cast<int32_t>(cos_sin_cache.size(1));
+  p.is_neox = is_neox ? 1 : 0;
+  p.dtype = dt;
+}
+
+void rotary_embedding(at::Tensor& positions, at::Tensor& query, std::optional<at::Tensor> key, int64_t head_size,
+                      at::Tensor& cos_sin_cache, bool is_neox) {
+  b200_rotary_params_t p;
+  fill_rotary_params(p, positions, query, key, head_size, cos_sin_cache, is_neox);
+  if (positions.numel() == 0) return;
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  check_status(b200_rotary_embedding(&p, at::cuda::getCurrentCUDAStream()), "rotary_embedding");
+}
+
+// Not a reference op: rotary_embedding and the reshape_and_cache_flash that follows it in the serving step, one launch.
+void rotary_embedding_and_cache_flash(at::Tensor& positions, at::Tensor& query, at::Tensor& key, at::Tensor& value,
+                                      int64_t head_size, at::Tensor& cos_sin_cache, bool is_neox, at::Tensor& key_cache,
+                                      at::Tensor& value_cache, at::Tensor& slot_mapping, const std::string& kv_cache_dtype,
+                                      at::Tensor& k_scale, at::Tensor& v_scale) {
+  TORCH_CHECK(positions.dim() == 1 && key.dim() == 3 && value.dim() == 3,
+              "fused op takes positions [num_tokens] and key/value [num_tokens, num_kv_heads, head_size]");
+  b200_rotary_params_t p;
+  std::optional<at::Tensor> okey = key;
+  fill_rotary_params(p, positions, query, okey, head_size, cos_sin_cache, is_neox);
+  b200_cache_write_params_t c;
+  fill_cache_params(c, key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale, v_scale);
+  TORCH_CHECK(key_cache.dim() == 4 && value_cache.dim() == 4, "caches must be [nb, bs, nh, hs]");
+  TORCH_CHECK(key_cache.stride(0) == value_cache.stride(0) && key_cache.stride(1) == value_cache.stride(1) &&
+                  key_cache.stride(2) == value_cache.stride(2) && key_cache.stride(3) == 1 && value_cache.stride(3) == 1,
+              "key_cache and value_cache must share strides with contiguous head dims");
+  TORCH_CHECK(key.stride(0) == value.stride(0), "key and value token strides differ");
+  TORCH_CHECK(key_cache.size(2) == key.size(1) && key_cache.size(3) == key.size(2), "cache shapes do not match key");
+  if (positions.numel() == 0) return;
+  p.num_cache_tokens = c.num_tokens;
+  p.value = c.value;
+  p.key_cache = c.key_cache;
+  p.value_cache = c.value_cache;
+  p.slot_mapping = c.slot_mapping;
+  p.k_scale = c.k_scale;
+  p.v_scale = c.v_scale;
+  p.value_stride = c.value_stride;
+  p.block_stride = key_cache.stride(0);
+  p.page_stride = key_cache.stride(1);
+  p.cache_head_stride = key_cache.stride(2);
+  p.block_size = static_cast<int32_t>(key_cache.size(1));
+  p.kv_dtype = c.kv_dtype;
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  check_status(b200_rotary_embedding_and_cache_flash(&p, at::cuda::getCurrentCUDAStream()),
+               "rotary_embedding_and_cache_flash");
+}
+
 // csrc/ops.h (merge_attn_states) ; csrc/attention/merge_attn_states.cu:129-178
 void merge_attn_states(at::Tensor& output, std::optional<at::Tensor> output_lse, const at::Tensor& prefix_output,
                        const at::Tensor& prefix_lse, const at::Tensor& suffix_output, const at::Tensor& suffix_lse) {
@@ -654,6 +760,15 @@ const char* kSchemaV1Lse =
     "int num_kv_heads, float scale, Tensor block_tables, Tensor seq_lens, int block_size, int max_seq_len, "
     "Tensor? alibi_slopes, str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()";
 
+// csrc/torch_bindings.cpp:216-218
+const char* kSchemaRotary =
+    "rotary_embedding(Tensor positions, Tensor! query,"
+    "                 Tensor!? key, int head_size,"
+    "                 Tensor cos_sin_cache, bool is_neox) -> ()";
+const char* kSchemaRotaryCache =
+    "rotary_embedding_and_cache_flash(Tensor positions, Tensor! query, Tensor! key, Tensor value, int head_size, "
+    "Tensor cos_sin_cache, bool is_neox, Tensor! key_cache, Tensor! value_cache, Tensor slot_mapping, "
+    "str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()";
 const char* kSchemaFlash =
     "paged_attention_flash(Tensor! out, Tensor!? lse, Tensor query, Tensor key_cache, Tensor value_cache, "
     "float scale, Tensor block_tables, Tensor seq_lens, int max_seq_len, Tensor? alibi_slopes) -> ()";
@@ -699,6 +814,8 @@ void register_all() {
     register_op(keep, "_C_cache_ops", "cp_gather_cache", kSchemaCpGather, &cp_gather_cache);
     register_op(keep, "_C_b200", "paged_attention_v1_lse", kSchemaV1Lse, &paged_attention_v1_lse);
     register_op(keep, "_C_b200", "paged_attention_flash", kSchemaFlash, &paged_attention_flash);
+    register_op(keep, "_C", "rotary_embedding", kSchemaRotary, &rotary_embedding);
+    register_op(keep, "_C_b200", "rotary_embedding_and_cache_flash", kSchemaRotaryCache, &rotary_embedding_and_cache_flash);
   });
 }
 
