@@ -170,11 +170,15 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist = None
+    saved_stdout = None
     if world > 1:
         import torch.distributed as dist
 
-        # NCCL writes its version banner / debug lines to stdout; stdout carries the one JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        # NCCL prints its version banner to stdout when the first communicator comes up; stdout carries the ONE JSON
+        # line, so file descriptor 1 points at stderr until the line is printed (restore_stdout below)
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -313,7 +317,10 @@ def run_ours(args):
         "cpu_baseline": cpu,
         "extra": extra,
     }
-    print(json.dumps(line))
+    if saved_stdout is not None:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+    print(json.dumps(line), flush=True)
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the attention kernel, from the ncu --set full

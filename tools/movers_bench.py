@@ -73,6 +73,38 @@ def main():
     src8 = torch.randint(0, 120, (NB, B, E), dtype=torch.uint8, device=dev, generator=g)
     med, best = timeit(lambda: ops.gather_and_maybe_dequant_cache(src8, dst16, table, cu, S, "fp8", scale, None), a.iters)
     report("gather_and_maybe_dequant_cache fp8 -> bf16 64x4096x576", dst16.numel() * 3, med, best)
+    rotary_bench(a.iters)
+
+
+def rotary_bench(iters):
+    """rotary_embedding + reshape_and_cache_flash as two launches vs the fused op (Llama-3-8B heads, bf16)."""
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(1)
+    H, Hkv, D, B = 32, 8, 128, 16
+    for T in (64, 8192):
+        NB = T // B + 64
+        cache = torch.randn(8192, D, device=dev, generator=g).bfloat16()
+        pos = torch.randint(0, 8192, (T,), device=dev, generator=g)
+        qkv = torch.randn(T, (H + 2 * Hkv) * D, device=dev, generator=g).bfloat16()
+        q, k, v = qkv.split([H * D, Hkv * D, Hkv * D], dim=-1)
+        k3, v3 = k.view(T, Hkv, D), v.view(T, Hkv, D)
+        kc = torch.zeros(NB, B, Hkv, D, dtype=torch.bfloat16, device=dev)
+        vc = torch.zeros_like(kc)
+        slots = torch.randperm(NB * B, device=dev, generator=g)[:T]
+        one = torch.ones(1, device=dev)
+
+        def two():
+            ops.rotary_embedding(pos, q, k, D, cache, True)
+            ops.reshape_and_cache_flash(k3, v3, kc, vc, slots, "auto", one, one)
+
+        def fused():
+            ops.rotary_embedding_and_cache_flash(pos, q, k3, v3, D, cache, True, kc, vc, slots, "auto", one, one)
+
+        nbytes = T * (2 * H * D * 2 + 2 * Hkv * D * 2 + 2 * Hkv * D * 2 + 2 * Hkv * D * 2)  # q r/w, k r/w, v read, cache writes
+        med, best = timeit(two, iters)
+        report("rotary_embedding + reshape_and_cache_flash, T=%d (2 launches)" % T, nbytes + T * 2 * Hkv * D * 2, med, best)
+        med, best = timeit(fused, iters)
+        report("rotary_embedding_and_cache_flash, T=%d (1 launch)" % T, nbytes, med, best)
 
 
 if __name__ == "__main__":

@@ -145,6 +145,15 @@ __global__ void reshape_and_cache_flash_kernel(b200_cache_write_params_t p) {
 template <typename T>
 __device__ __forceinline__ T rnd(float v) { return from_f32<T>(v); }
 
+template <typename T>
+__device__ __forceinline__ void rotate_pair(T x, T y, T c, T sn, T& ox, T& oy) {
+  const float xf = to_f32<T>(x), yf = to_f32<T>(y), cf = to_f32<T>(c), sf = to_f32<T>(sn);
+  const float xc = to_f32<T>(rnd<T>(__fmul_rn(xf, cf))), ys = to_f32<T>(rnd<T>(__fmul_rn(yf, sf)));
+  const float yc = to_f32<T>(rnd<T>(__fmul_rn(yf, cf))), xs = to_f32<T>(rnd<T>(__fmul_rn(xf, sf)));
+  ox = rnd<T>(__fsub_rn(xc, ys));
+  oy = rnd<T>(__fadd_rn(yc, xs));
+}
+
 template <typename T, bool NEOX>
 __device__ __forceinline__ void rotate_heads(T* base, int64_t head_stride, int nheads, int embed, const T* cos_ptr,
                                              const T* sin_ptr) {
@@ -154,27 +163,66 @@ __device__ __forceinline__ void rotate_heads(T* base, int64_t head_stride, int n
     T* arr = base + (int64_t)head * head_stride;
     const int xi = NEOX ? r : 2 * r;
     const int yi = NEOX ? embed + r : 2 * r + 1;
-    const float c = to_f32<T>(cos_ptr[r]), sn = to_f32<T>(sin_ptr[r]);
-    const float x = to_f32<T>(arr[xi]), y = to_f32<T>(arr[yi]);
-    const float xc = to_f32<T>(rnd<T>(__fmul_rn(x, c))), ys = to_f32<T>(rnd<T>(__fmul_rn(y, sn)));
-    const float yc = to_f32<T>(rnd<T>(__fmul_rn(y, c))), xs = to_f32<T>(rnd<T>(__fmul_rn(x, sn)));
-    arr[xi] = rnd<T>(__fsub_rn(xc, ys));
-    arr[yi] = rnd<T>(__fadd_rn(yc, xs));
+    rotate_pair<T>(arr[xi], arr[yi], cos_ptr[r], sin_ptr[r], arr[xi], arr[yi]);
   }
 }
 
-template <typename T, bool NEOX, int FUSE>  // FUSE: 0 none, 1 auto scalar, 2 auto vec, 3 fp8 scalar, 4 fp8 vec
+// 16-byte version: NeoX — one vector of x (dims r..r+N-1), the matching vector of y (embed + r..), one vector each of
+// cos and sin; GPT-J — one vector holds N/2 adjacent (x, y) pairs.  Same arithmetic as rotate_heads.
+template <typename T, bool NEOX>
+__device__ __forceinline__ void rotate_heads_vec(T* base, int64_t head_stride, int nheads, int embed, const T* cos_ptr,
+                                                 const T* sin_ptr) {
+  constexpr int N = VecOf<T>::kElems;
+  if constexpr (NEOX) {
+    const int cph = embed / N;  // chunks per head
+    for (int i = threadIdx.x; i < nheads * cph; i += blockDim.x) {
+      const int head = i / cph, r = (i % cph) * N;
+      T* arr = base + (int64_t)head * head_stride;
+      Vec16 xv = *reinterpret_cast<const Vec16*>(arr + r);
+      Vec16 yv = *reinterpret_cast<const Vec16*>(arr + embed + r);
+      const Vec16 cv = *reinterpret_cast<const Vec16*>(cos_ptr + r);
+      const Vec16 sv = *reinterpret_cast<const Vec16*>(sin_ptr + r);
+      T* x = reinterpret_cast<T*>(&xv);
+      T* y = reinterpret_cast<T*>(&yv);
+      const T* c = reinterpret_cast<const T*>(&cv);
+      const T* sn = reinterpret_cast<const T*>(&sv);
+#pragma unroll
+      for (int j = 0; j < N; ++j) rotate_pair<T>(x[j], y[j], c[j], sn[j], x[j], y[j]);
+      *reinterpret_cast<Vec16*>(arr + r) = xv;
+      *reinterpret_cast<Vec16*>(arr + embed + r) = yv;
+    }
+  } else {
+    const int cph = 2 * embed / N;
+    for (int i = threadIdx.x; i < nheads * cph; i += blockDim.x) {
+      const int head = i / cph, e0 = (i % cph) * N;  // first element of the chunk; its first pair is e0 / 2
+      T* arr = base + (int64_t)head * head_stride;
+      Vec16 v = *reinterpret_cast<const Vec16*>(arr + e0);
+      T* e = reinterpret_cast<T*>(&v);
+#pragma unroll
+      for (int j = 0; j < N / 2; ++j)
+        rotate_pair<T>(e[2 * j], e[2 * j + 1], cos_ptr[e0 / 2 + j], sin_ptr[e0 / 2 + j], e[2 * j], e[2 * j + 1]);
+      *reinterpret_cast<Vec16*>(arr + e0) = v;
+    }
+  }
+}
+
+// FUSE: 0 none, 1 auto scalar, 2 auto vec, 3 fp8 scalar, 4 fp8 vec (the flash cache write); RVEC: 16-byte rotation
+template <typename T, bool NEOX, int FUSE, bool RVEC>
 __global__ void rotary_embedding_kernel(const b200_rotary_params_t p, const b200_cache_write_params_t cw) {
   const int64_t token = blockIdx.x;
   const int64_t pos = p.positions[token];
   const int embed = p.rot_dim / 2;
   const T* cos_ptr = reinterpret_cast<const T*>(p.cos_sin_cache) + pos * p.rot_dim;
   const T* sin_ptr = cos_ptr + embed;
-  rotate_heads<T, NEOX>(reinterpret_cast<T*>(p.query) + token * p.query_stride, p.head_stride, p.num_heads, embed,
-                        cos_ptr, sin_ptr);
-  if (p.key != nullptr)
-    rotate_heads<T, NEOX>(reinterpret_cast<T*>(p.key) + token * p.key_stride, p.head_stride, p.num_kv_heads, embed,
-                          cos_ptr, sin_ptr);
+  T* q = reinterpret_cast<T*>(p.query) + token * p.query_stride;
+  T* k = p.key != nullptr ? reinterpret_cast<T*>(p.key) + token * p.key_stride : nullptr;
+  if constexpr (RVEC) {
+    rotate_heads_vec<T, NEOX>(q, p.head_stride, p.num_heads, embed, cos_ptr, sin_ptr);
+    if (k != nullptr) rotate_heads_vec<T, NEOX>(k, p.head_stride, p.num_kv_heads, embed, cos_ptr, sin_ptr);
+  } else {
+    rotate_heads<T, NEOX>(q, p.head_stride, p.num_heads, embed, cos_ptr, sin_ptr);
+    if (k != nullptr) rotate_heads<T, NEOX>(k, p.head_stride, p.num_kv_heads, embed, cos_ptr, sin_ptr);
+  }
   if constexpr (FUSE != 0) {
     if (token >= p.num_cache_tokens) return;  // CUDA-graph padding: slot_mapping is shorter than key
     __syncthreads();  // the rotated key row of this token is visible to the whole CTA
@@ -376,10 +424,18 @@ int launch_rotary(const b200_rotary_params_t& p, bool fuse, cudaStream_t s) {
                      aligned(p.key_cache, dst_align) && aligned(p.value_cache, dst_align);
     mode = fp8 ? (vec ? 4 : 3) : (vec ? 2 : 1);
   }
-  const int work = p.num_heads * p.rot_dim / 2;
-  const int threads = std::max(32, std::min(512, (work + 31) / 32 * 32));  // csrc/pos_encoding_kernels.cu:191
+  // 16-byte rotation: whole vectors inside each half (NeoX) / each head (GPT-J), vector-aligned rows and cos/sin
+  constexpr int NV = VecOf<T>::kElems;
+  const int embed = p.rot_dim / 2;
+  const bool rvec = (p.is_neox ? embed % NV == 0 : p.rot_dim % NV == 0) && p.head_stride % NV == 0 &&
+                    p.query_stride % NV == 0 && (p.key == nullptr || p.key_stride % NV == 0) && aligned(p.query, 16) &&
+                    (p.key == nullptr || aligned(p.key, 16)) && aligned(p.cos_sin_cache, 16);
+  const int work = rvec ? (p.num_heads + p.num_kv_heads) * p.rot_dim / NV : p.num_heads * embed;
+  const int threads = std::max(32, std::min(rvec ? 256 : 512, (work + 31) / 32 * 32));  // csrc/pos_encoding_kernels.cu:191
   dim3 grid(p.num_tokens), block(threads);
-#define ROT(NEOX, MODE) rotary_embedding_kernel<T, NEOX, MODE><<<grid, block, 0, s>>>(p, cw)
+#define ROT(NEOX, MODE) \
+  (rvec ? rotary_embedding_kernel<T, NEOX, MODE, true><<<grid, block, 0, s>>>(p, cw) \
+        : rotary_embedding_kernel<T, NEOX, MODE, false><<<grid, block, 0, s>>>(p, cw))
 #define ROT_MODE(NEOX)                                                                              \
   switch (mode) {                                                                                   \
     case 0: ROT(NEOX, 0); break;                                                                    \
