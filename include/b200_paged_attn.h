@@ -282,6 +282,39 @@ int b200_merge_attn_states(const b200_merge_attn_states_params_t* params, void* 
 int b200_copy_blocks(void* const* key_caches, void* const* value_caches, int32_t num_layers,
                      const int64_t* block_mapping, int32_t num_pairs, int64_t block_bytes, void* stream);
 
+/* Replaces torch.ops._C_cache_ops.copy_blocks_mla (csrc/torch_bindings.cpp:389-391; csrc/cache_kernels.cu:94-110,
+ * :165-201): as b200_copy_blocks for one joint cache per layer; block_bytes = stride(0) * element size (:186-189). */
+int b200_copy_blocks_mla(void* const* kv_caches, int32_t num_layers, const int64_t* block_mapping, int32_t num_pairs,
+                         int64_t block_bytes, void* stream);
+
+/*
+ * Replaces torch.ops._C_cache_ops.concat_and_cache_mla (csrc/torch_bindings.cpp:415-420;
+ * csrc/cache_kernels.cu:346-389, :490-539): cache entry of token t at slot_mapping[t] =
+ * [kv_c[t] (kv_lora_rank) | k_pe[t] (pe_dim)], optionally e4m3-quantised with one scale; slot < 0 skipped;
+ * num_tokens = slot_mapping.size(0).
+ *   kv_c [.., kv_lora_rank] row stride kv_c_stride; k_pe [.., pe_dim] row stride k_pe_stride (elements)
+ *   kv_cache [num_blocks, block_size, kv_lora_rank + pe_dim] addressed by block_stride / entry_stride
+ */
+typedef struct b200_concat_mla_params {
+  const void* kv_c;
+  const void* k_pe;
+  void* kv_cache;
+  const int64_t* slot_mapping;
+  const float* scale; /* device; read only when kv_dtype != auto */
+  int64_t kv_c_stride;
+  int64_t k_pe_stride;
+  int64_t block_stride;
+  int64_t entry_stride;
+  int32_t num_tokens;
+  int32_t kv_lora_rank;
+  int32_t pe_dim;
+  int32_t block_size;
+  int32_t dtype;    /* b200_dtype_t of kv_c / k_pe */
+  int32_t kv_dtype; /* b200_kv_dtype_t */
+} b200_concat_mla_params_t;
+
+int b200_concat_and_cache_mla(const b200_concat_mla_params_t* params, void* stream);
+
 /* memcpy direction of b200_swap_blocks (csrc/cache_kernels.cu:22-34). */
 typedef enum b200_copy_kind {
   B200_COPY_D2D = 0,

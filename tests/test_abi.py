@@ -49,7 +49,8 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
                       ("b200_cache_write_params_t", native.CacheWriteParams),
                       ("b200_merge_attn_states_params_t", native.MergeAttnStatesParams),
                       ("b200_gather_cache_params_t", native.GatherCacheParams),
-                      ("b200_rotary_params_t", native.RotaryParams)):
+                      ("b200_rotary_params_t", native.RotaryParams),
+                      ("b200_concat_mla_params_t", native.ConcatMlaParams)):
         prog.append('printf("%%zu\\n", sizeof(%s));' % cname)
         for f in fields(st):
             prog.append('printf("%%zu\\n", offsetof(%s, %s));' % (cname, f))
@@ -61,7 +62,7 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
     vals = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     it = iter(vals)
     for st in (native.PagedAttnParams, native.CacheWriteParams, native.MergeAttnStatesParams, native.GatherCacheParams,
-               native.RotaryParams):
+               native.RotaryParams, native.ConcatMlaParams):
         assert next(it) == C.sizeof(st)
         for f in fields(st):
             assert next(it) == getattr(st, f).offset, f
@@ -154,6 +155,12 @@ def test_new_entry_points_validate_on_the_host(native):
     rp.rot_dim = 130
     assert lib.b200_rotary_embedding(C.byref(rp), None) == native.ERR_INVALID_ARGUMENT
     assert "rot_dim" in lib.b200_last_error().decode()
+    cm = native.ConcatMlaParams()
+    cm.num_tokens, cm.kv_lora_rank, cm.pe_dim, cm.block_size, cm.dtype = 0, 512, 64, 16, native.DTYPE_BF16
+    assert lib.b200_concat_and_cache_mla(C.byref(cm), None) == 0
+    cm.num_tokens = 3
+    assert lib.b200_concat_and_cache_mla(C.byref(cm), None) == native.ERR_INVALID_ARGUMENT
+    assert lib.b200_copy_blocks_mla(None, 0, None, 0, 0, None) == 0
     assert lib.b200_copy_blocks(None, None, 0, None, 0, 0, None) == 0
     assert lib.b200_swap_blocks(None, None, None, 0, 4096, native.COPY_D2D, None) == 0
     m = (C.c_int64 * 2)(0, 1)

@@ -288,3 +288,55 @@ def test_gather_rejects_mismatched_dtypes(ops):
         ops.cp_gather_cache(src, dst, t, cu, 1)
     with pytest.raises(RuntimeError, match="must be int32"):
         ops.cp_gather_cache(src, src.new_zeros(8, 32), t.long(), cu, 1)
+
+
+# ---- MLA cache ops ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kv_lora_rank,pe_dim", [(512, 64), (500, 60)])
+@pytest.mark.parametrize("num_tokens", [1, 42, 300])
+@pytest.mark.parametrize("block_size", [16, 64])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32, torch.float16])
+@pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8"])
+def test_concat_and_cache_mla(ops, kv_lora_rank, pe_dim, num_tokens, block_size, dtype, kv_cache_dtype):
+    """Grid of tests/kernels/attention/test_cache.py:494-572 (kv_lora_rank 512, rope dim 64) plus an unaligned entry."""
+    NB, pad = 40, 4
+    g = torch.Generator().manual_seed(3)
+    random.seed(3)
+    slots = random.sample(range(NB * block_size), num_tokens)
+    if num_tokens > 2:
+        slots[1] = -1
+    slot_mapping = torch.tensor(slots, dtype=torch.long)
+    kv_c = torch.randn(num_tokens + pad, kv_lora_rank, generator=g).to(dtype)
+    wide = torch.randn(num_tokens + pad, pe_dim + 8, generator=g).to(dtype)
+    k_pe = wide[:, :pe_dim]  # row stride != pe_dim, as the squeeze of a [T, 1, pe] slice gives in the model
+    cdt = torch.uint8 if kv_cache_dtype == "fp8" else dtype
+    cache = torch.randint(0, 100, (NB, block_size, kv_lora_rank + pe_dim), generator=g).to(cdt)
+    scale = torch.tensor(0.1, dtype=torch.float32)
+    ref = cache.clone()
+    orc.concat_and_cache_mla(kv_c, k_pe, ref, slot_mapping, kv_cache_dtype, scale)
+    cd = cache.cuda()
+    ops.concat_and_cache_mla(kv_c.cuda(), wide.cuda()[:, :pe_dim], cd, slot_mapping.cuda(), kv_cache_dtype, scale.cuda())
+    assert torch.equal(cd.cpu().view(torch.uint8), ref.view(torch.uint8))
+
+
+@pytest.mark.parametrize("num_layers", [1, 5, 130])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.uint8])
+def test_copy_blocks_mla(ops, num_layers, dtype):
+    """tests/kernels/attention/test_cache.py:591-652: every source block copied onto two destinations, all layers."""
+    NB, B, E, nmap = 64, 16, 576, 9
+    random.seed(5)
+    src_blocks = random.sample(range(NB), nmap)
+    remaining = sorted(set(range(NB)) - set(src_blocks))
+    dst_blocks = random.sample(remaining, 2 * nmap)
+    mapping = []
+    for i in range(nmap):
+        mapping += [(src_blocks[i], dst_blocks[2 * i]), (src_blocks[i], dst_blocks[2 * i + 1])]
+    m = torch.tensor(mapping, dtype=torch.int64).view(-1, 2)
+    g = torch.Generator().manual_seed(6)
+    caches = [torch.randint(0, 200, (NB, B, E), generator=g).to(dtype) for _ in range(num_layers)]
+    dev = [c.cuda() for c in caches]
+    ops.copy_blocks_mla(dev, m.cuda())
+    for s_, d_ in mapping:  # the reference loop (:644-647)
+        for c in caches:
+            c[d_].copy_(c[s_])
+    for a, b in zip(dev, caches):
+        assert torch.equal(a.cpu(), b)

@@ -235,3 +235,20 @@ def rotary_embedding_and_cache_flash(
     torch.ops._C_b200.rotary_embedding_and_cache_flash(positions, query, key, value, head_size, cos_sin_cache, is_neox,
                                                        key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale,
                                                        v_scale)
+
+
+def concat_and_cache_mla(
+    kv_c: torch.Tensor,
+    k_pe: torch.Tensor,
+    kv_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,
+    kv_cache_dtype: str,
+    scale: torch.Tensor,
+) -> None:
+    """reference: tests/kernels/attention/test_cache.py:563-564 -> csrc/cache_kernels.cu:490-539"""
+    torch.ops._C_cache_ops.concat_and_cache_mla(kv_c, k_pe, kv_cache, slot_mapping, kv_cache_dtype, scale)
+
+
+def copy_blocks_mla(kv_caches: list[torch.Tensor], block_mapping: torch.Tensor) -> None:
+    """reference: tests/kernels/attention/test_cache.py:642 -> csrc/cache_kernels.cu:165-201"""
+    torch.ops._C_cache_ops.copy_blocks_mla(kv_caches, block_mapping)

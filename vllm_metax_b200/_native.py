@@ -32,6 +32,8 @@ EXPORTED_SYMBOLS = (
     "b200_rotary_embedding_and_cache_flash",
     "b200_merge_attn_states",
     "b200_copy_blocks",
+    "b200_copy_blocks_mla",
+    "b200_concat_and_cache_mla",
     "b200_swap_blocks",
     "b200_gather_cache",
     "b200_kv_dtype_from_string",
@@ -179,6 +181,26 @@ class RotaryParams(C.Structure):
     ]
 
 
+class ConcatMlaParams(C.Structure):
+    _fields_ = [
+        ("kv_c", C.c_void_p),
+        ("k_pe", C.c_void_p),
+        ("kv_cache", C.c_void_p),
+        ("slot_mapping", C.c_void_p),
+        ("scale", C.c_void_p),
+        ("kv_c_stride", C.c_int64),
+        ("k_pe_stride", C.c_int64),
+        ("block_stride", C.c_int64),
+        ("entry_stride", C.c_int64),
+        ("num_tokens", C.c_int32),
+        ("kv_lora_rank", C.c_int32),
+        ("pe_dim", C.c_int32),
+        ("block_size", C.c_int32),
+        ("dtype", C.c_int32),
+        ("kv_dtype", C.c_int32),
+    ]
+
+
 COPY_D2D, COPY_D2H, COPY_H2D = 0, 1, 2
 
 _lib = None
@@ -226,6 +248,10 @@ def load() -> C.CDLL:
     lib.b200_copy_blocks.argtypes = [P(C.c_void_p), P(C.c_void_p), C.c_int32, C.c_void_p, C.c_int32, C.c_int64,
                                      C.c_void_p]
     lib.b200_copy_blocks.restype = C.c_int
+    lib.b200_copy_blocks_mla.argtypes = [P(C.c_void_p), C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p]
+    lib.b200_copy_blocks_mla.restype = C.c_int
+    lib.b200_concat_and_cache_mla.argtypes = [P(ConcatMlaParams), C.c_void_p]
+    lib.b200_concat_and_cache_mla.restype = C.c_int
     lib.b200_swap_blocks.argtypes = [C.c_void_p, C.c_void_p, P(C.c_int64), C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
     lib.b200_swap_blocks.restype = C.c_int
     lib.b200_gather_cache.argtypes = [P(GatherCacheParams), C.c_void_p]

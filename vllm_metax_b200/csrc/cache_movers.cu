@@ -15,6 +15,8 @@
 namespace b200 {
 namespace {
 
+inline bool aligned(const void* q, size_t a) { return (reinterpret_cast<uintptr_t>(q) % a) == 0; }
+
 // ---- copy_blocks ---------------------------------------------------------------------------------------
 // The per-layer cache pointers ride in the kernel parameter block (<= kLayersPerLaunch layers per launch),
 // so nothing is staged through device memory and the call neither synchronises nor allocates.
@@ -27,11 +29,12 @@ struct CopyBlocksArgs {
 };
 
 // grid (pairs, layers * 2, slices): one CTA copies one slice of one block of the K or the V cache of a layer.
-template <bool VEC>
+// NC = 2: key and value cache per layer (copy_blocks); NC = 1: one joint cache per layer (copy_blocks_mla)
+template <bool VEC, int NC>
 __global__ void __launch_bounds__(256) copy_blocks_kernel(const __grid_constant__ CopyBlocksArgs a) {
   const int pair = blockIdx.x;
-  const int layer = blockIdx.y >> 1;
-  uint8_t* base = (blockIdx.y & 1) ? a.value[layer] : a.key[layer];
+  const int layer = blockIdx.y / NC;
+  uint8_t* base = (NC == 2 && (blockIdx.y & 1)) ? a.value[layer] : a.key[layer];
   const int64_t src = a.mapping[2 * pair], dst = a.mapping[2 * pair + 1];
   const uint8_t* s = base + src * a.block_bytes;
   uint8_t* d = base + dst * a.block_bytes;
@@ -145,8 +148,6 @@ __global__ void __launch_bounds__(256) gather_cache_kernel(const b200_gather_cac
   }
 }
 
-inline bool aligned(const void* q, size_t a) { return (reinterpret_cast<uintptr_t>(q) % a) == 0; }
-
 template <typename T, bool FP8>
 void launch_gather(const b200_gather_cache_params_t& p, bool vec, int elem_bytes, dim3 grid, cudaStream_t s) {
   if constexpr (FP8) {
@@ -161,14 +162,15 @@ void launch_gather(const b200_gather_cache_params_t& p, bool vec, int elem_bytes
 }  // namespace
 }  // namespace b200
 
-extern "C" int b200_copy_blocks(void* const* key_caches, void* const* value_caches, int32_t num_layers,
-                                const int64_t* block_mapping, int32_t num_pairs, int64_t block_bytes,
-                                void* stream) {
-  using namespace b200;
+namespace b200 {
+namespace {
+template <int NC>
+int copy_blocks_impl(void* const* key_caches, void* const* value_caches, int32_t num_layers, const int64_t* block_mapping,
+                     int32_t num_pairs, int64_t block_bytes, void* stream, const char* what) {
   B200_REQUIRE(num_layers >= 0 && num_pairs >= 0 && block_bytes >= 0, B200_ERR_INVALID_ARGUMENT,
                "bad sizes: layers=%d pairs=%d block_bytes=%lld", num_layers, num_pairs, (long long)block_bytes);
   if (num_layers == 0 || num_pairs == 0 || block_bytes == 0) return B200_OK;  // cache_kernels.cu:118-120
-  B200_REQUIRE(key_caches && value_caches && block_mapping, B200_ERR_INVALID_ARGUMENT, "NULL pointer");
+  B200_REQUIRE(key_caches && (NC == 1 || value_caches) && block_mapping, B200_ERR_INVALID_ARGUMENT, "NULL pointer");
   B200_REQUIRE(num_pairs <= 0x7fffffff && num_layers <= 32767, B200_ERR_UNSUPPORTED, "too many layers / pairs");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   for (int l0 = 0; l0 < num_layers; l0 += kLayersPerLaunch) {
@@ -177,26 +179,126 @@ extern "C" int b200_copy_blocks(void* const* key_caches, void* const* value_cach
     memset(&a, 0, sizeof(a));
     bool vec = block_bytes % 16 == 0;
     for (int l = 0; l < nl; ++l) {
-      B200_REQUIRE(key_caches[l0 + l] && value_caches[l0 + l], B200_ERR_INVALID_ARGUMENT, "NULL cache pointer");
+      B200_REQUIRE(key_caches[l0 + l] && (NC == 1 || value_caches[l0 + l]), B200_ERR_INVALID_ARGUMENT,
+                   "NULL cache pointer");
       a.key[l] = static_cast<uint8_t*>(key_caches[l0 + l]);
-      a.value[l] = static_cast<uint8_t*>(value_caches[l0 + l]);
-      vec = vec && aligned(a.key[l], 16) && aligned(a.value[l], 16);
+      vec = vec && aligned(a.key[l], 16);
+      if (NC == 2) {
+        a.value[l] = static_cast<uint8_t*>(value_caches[l0 + l]);
+        vec = vec && aligned(a.value[l], 16);
+      }
     }
     a.mapping = block_mapping;
     a.block_bytes = block_bytes;
     // slices: enough CTAs to cover the machine a few times over, each moving >= 4 KiB
-    const int64_t ctas = (int64_t)num_pairs * nl * 2;
+    const int64_t ctas = (int64_t)num_pairs * nl * NC;
     int slices = (int)((4 * (int64_t)device_sm_count() + ctas - 1) / ctas);
     const int max_slices = (int)std::min<int64_t>(65535, std::max<int64_t>(1, block_bytes / 4096));
     slices = std::max(1, std::min(slices, max_slices));
-    dim3 grid(num_pairs, nl * 2, slices);
-    if (vec) copy_blocks_kernel<true><<<grid, 256, 0, s>>>(a);
-    else copy_blocks_kernel<false><<<grid, 256, 0, s>>>(a);
+    dim3 grid(num_pairs, nl * NC, slices);
+    if (vec) copy_blocks_kernel<true, NC><<<grid, 256, 0, s>>>(a);
+    else copy_blocks_kernel<false, NC><<<grid, 256, 0, s>>>(a);
     count_launch();
-    const int rc = check_launch("copy_blocks");
+    const int rc = check_launch(what);
     if (rc != B200_OK) return rc;
   }
   return B200_OK;
+}
+
+// ---- concat_and_cache_mla ------------------------------------------------------------------------------------
+// Reference: csrc/cache_kernels.cu:346-389.  One CTA per token: entry = [kv_c (kv_lora_rank) | k_pe (pe_dim)] written at
+// slot_mapping[token]; 16-byte source vectors when both parts and the entry are vector-aligned.
+template <typename T, bool FP8, bool VEC>
+__global__ void __launch_bounds__(256) concat_and_cache_mla_kernel(const b200_concat_mla_params_t p) {
+  const int64_t token = blockIdx.x;
+  const int64_t slot = p.slot_mapping[token];
+  if (slot < 0) return;  // padded token (:364-367)
+  const int64_t blk = slot / p.block_size, off = slot % p.block_size;
+  const float scale = FP8 ? *p.scale : 0.f;
+  constexpr int CB = FP8 ? 1 : (int)sizeof(T);
+  constexpr int N = 16 / sizeof(T);
+  uint8_t* dst = reinterpret_cast<uint8_t*>(p.kv_cache) + (blk * p.block_stride + off * p.entry_stride) * CB;
+  const T* a = reinterpret_cast<const T*>(p.kv_c) + token * p.kv_c_stride;
+  const T* b = reinterpret_cast<const T*>(p.k_pe) + token * p.k_pe_stride;
+  const int total = p.kv_lora_rank + p.pe_dim;
+  if constexpr (VEC) {
+    for (int i = threadIdx.x * N; i < total; i += blockDim.x * N) {
+      const Vec16 v = *reinterpret_cast<const Vec16*>(i < p.kv_lora_rank ? a + i : b + (i - p.kv_lora_rank));
+      if constexpr (!FP8) {
+        *reinterpret_cast<Vec16*>(dst + (int64_t)i * CB) = v;
+      } else {
+        const T* e = reinterpret_cast<const T*>(&v);
+        alignas(8) uint8_t q[N];
+#pragma unroll
+        for (int j = 0; j < N; ++j) q[j] = quant_e4m3<T>(e[j], scale);
+        if constexpr (N == 8) *reinterpret_cast<uint2*>(dst + i) = *reinterpret_cast<const uint2*>(q);
+        else *reinterpret_cast<uint32_t*>(dst + i) = *reinterpret_cast<const uint32_t*>(q);
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+      const T x = i < p.kv_lora_rank ? a[i] : b[i - p.kv_lora_rank];
+      if constexpr (!FP8) reinterpret_cast<T*>(dst)[i] = x;
+      else dst[i] = quant_e4m3<T>(x, scale);
+    }
+  }
+}
+
+template <typename T>
+int launch_concat_mla(const b200_concat_mla_params_t& p, cudaStream_t s) {
+  constexpr int N = 16 / sizeof(T);
+  const bool fp8 = p.kv_dtype == B200_KV_FP8_E4M3;
+  const int cb = fp8 ? 1 : (int)sizeof(T);
+  const bool vec = p.kv_lora_rank % N == 0 && p.pe_dim % N == 0 && p.kv_c_stride % N == 0 && p.k_pe_stride % N == 0 &&
+                   aligned(p.kv_c, 16) && aligned(p.k_pe, 16) && aligned(p.kv_cache, (size_t)N * cb) &&
+                   (p.block_stride * cb) % (N * cb) == 0 && (p.entry_stride * cb) % (N * cb) == 0;
+  const int work = vec ? (p.kv_lora_rank + p.pe_dim) / N : p.kv_lora_rank + p.pe_dim;
+  const int threads = std::max(32, std::min(256, (work + 31) / 32 * 32));
+  if (fp8) {
+    if (vec) concat_and_cache_mla_kernel<T, true, true><<<p.num_tokens, threads, 0, s>>>(p);
+    else concat_and_cache_mla_kernel<T, true, false><<<p.num_tokens, threads, 0, s>>>(p);
+  } else {
+    if (vec) concat_and_cache_mla_kernel<T, false, true><<<p.num_tokens, threads, 0, s>>>(p);
+    else concat_and_cache_mla_kernel<T, false, false><<<p.num_tokens, threads, 0, s>>>(p);
+  }
+  count_launch();
+  return check_launch("concat_and_cache_mla");
+}
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200_copy_blocks(void* const* key_caches, void* const* value_caches, int32_t num_layers,
+                                const int64_t* block_mapping, int32_t num_pairs, int64_t block_bytes,
+                                void* stream) {
+  return b200::copy_blocks_impl<2>(key_caches, value_caches, num_layers, block_mapping, num_pairs, block_bytes, stream,
+                                   "copy_blocks");
+}
+
+extern "C" int b200_copy_blocks_mla(void* const* kv_caches, int32_t num_layers, const int64_t* block_mapping,
+                                    int32_t num_pairs, int64_t block_bytes, void* stream) {
+  return b200::copy_blocks_impl<1>(kv_caches, nullptr, num_layers, block_mapping, num_pairs, block_bytes, stream,
+                                   "copy_blocks_mla");
+}
+
+extern "C" int b200_concat_and_cache_mla(const b200_concat_mla_params_t* p, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(p != nullptr, B200_ERR_INVALID_ARGUMENT, "params is NULL");
+  B200_REQUIRE(p->num_tokens >= 0 && p->kv_lora_rank > 0 && p->pe_dim >= 0 && p->block_size > 0,
+               B200_ERR_INVALID_ARGUMENT, "bad sizes: tokens=%d kv_lora_rank=%d pe_dim=%d block=%d", p->num_tokens,
+               p->kv_lora_rank, p->pe_dim, p->block_size);
+  if (p->num_tokens == 0) return B200_OK;
+  B200_REQUIRE(p->kv_c && p->k_pe && p->kv_cache && p->slot_mapping, B200_ERR_INVALID_ARGUMENT, "NULL tensor pointer");
+  B200_REQUIRE(p->kv_dtype == B200_KV_AUTO || p->kv_dtype == B200_KV_FP8_E4M3, B200_ERR_UNSUPPORTED,
+               "Unsupported data type of kv cache: %d", p->kv_dtype);
+  B200_REQUIRE(p->dtype == B200_DTYPE_F32 || p->dtype == B200_DTYPE_F16 || p->dtype == B200_DTYPE_BF16,
+               B200_ERR_UNSUPPORTED, "Unsupported input type of kv cache: %d", p->dtype);
+  if (p->kv_dtype != B200_KV_AUTO) B200_REQUIRE(p->scale != nullptr, B200_ERR_INVALID_ARGUMENT, "fp8 cache needs scale");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (p->dtype) {
+    case B200_DTYPE_F32: return launch_concat_mla<float>(*p, s);
+    case B200_DTYPE_F16: return launch_concat_mla<__half>(*p, s);
+    default: return launch_concat_mla<__nv_bfloat16>(*p, s);
+  }
 }
 
 extern "C" int b200_swap_blocks(void* dst, const void* src, const int64_t* block_mapping, int64_t num_pairs,

@@ -598,6 +598,70 @@ void copy_blocks(std::vector<at::Tensor> const& key_caches, std::vector<at::Tens
                "copy_blocks");
 }
 
+// csrc/cache.h ; csrc/cache_kernels.cu:165-201
+void copy_blocks_mla(std::vector<at::Tensor> const& kv_caches, const at::Tensor& block_mapping) {
+  const size_t num_layers = kv_caches.size();
+  if (num_layers == 0) return;
+  TORCH_CHECK(kv_caches[0].is_cuda(), "kv_cache must be on CUDA");
+  TORCH_CHECK(block_mapping.is_cuda() && block_mapping.scalar_type() == at::kLong && block_mapping.is_contiguous() &&
+                  block_mapping.dim() == 2 && block_mapping.size(1) == 2,
+              "block_mapping must be a contiguous int64 CUDA tensor [num_pairs, 2]");
+  std::vector<void*> ptrs(num_layers);
+  for (size_t l = 0; l < num_layers; ++l) {
+    TORCH_CHECK(kv_caches[l].device() == kv_caches[0].device(), "all caches must be on the same device");
+    ptrs[l] = kv_caches[l].data_ptr();
+  }
+  // stride, not numel: blocks may be padded (cache_kernels.cu:186-189)
+  const int64_t block_bytes = kv_caches[0].stride(0) * kv_caches[0].element_size();
+  const at::cuda::OptionalCUDAGuard guard(kv_caches[0].device());
+  check_status(b200_copy_blocks_mla(ptrs.data(), static_cast<int32_t>(num_layers), block_mapping.data_ptr<int64_t>(),
+                                    static_cast<int32_t>(block_mapping.size(0)), block_bytes,
+                                    at::cuda::getCurrentCUDAStream()),
+               "copy_blocks_mla");
+}
+
+// csrc/cache.h ; csrc/cache_kernels.cu:490-539
+void concat_and_cache_mla(at::Tensor& kv_c, at::Tensor& k_pe, at::Tensor& kv_cache, at::Tensor& slot_mapping,
+                          const std::string& kv_cache_dtype, at::Tensor& scale) {
+  TORCH_CHECK(kv_c.dim() == 2 && k_pe.dim() == 2 && kv_cache.dim() == 3, "kv_c [T, rank], k_pe [T, pe], kv_cache [nb, bs, rank + pe]");
+  TORCH_CHECK(kv_cache.size(2) == kv_c.size(1) + k_pe.size(1));  // :511
+  TORCH_CHECK(kv_c.scalar_type() == k_pe.scalar_type(), "kv_c and k_pe dtypes differ");
+  TORCH_CHECK(kv_c.stride(1) == 1 && k_pe.stride(1) == 1 && kv_cache.stride(2) == 1, "innermost dims must be contiguous");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::kLong && slot_mapping.is_contiguous(), "slot_mapping must be contiguous int64");
+  TORCH_CHECK(slot_mapping.size(0) <= kv_c.size(0) && slot_mapping.size(0) <= k_pe.size(0), "slot_mapping longer than kv_c / k_pe");
+  TORCH_CHECK(kv_c.is_cuda() && k_pe.is_cuda() && kv_cache.is_cuda() && slot_mapping.is_cuda() && scale.is_cuda(),
+              "all tensors must be on the CUDA device");
+  const int kv = kv_dtype_or_throw(kv_cache_dtype);
+  if (kv == B200_KV_AUTO) {
+    TORCH_CHECK(kv_cache.scalar_type() == kv_c.scalar_type(), "kv_cache_dtype 'auto' needs a cache of the kv_c dtype");
+  } else {
+    TORCH_CHECK(is_cache_byte_type(kv_cache.scalar_type()), "fp8 kv cache must be stored as uint8");
+    TORCH_CHECK(scale.scalar_type() == at::kFloat, "scale must be a float32 tensor");
+  }
+  const int dt = to_dtype(kv_c.scalar_type());
+  TORCH_CHECK(dt == B200_DTYPE_F32 || dt == B200_DTYPE_F16 || dt == B200_DTYPE_BF16,
+              "Unsupported input type of kv cache: ", kv_c.scalar_type());
+  b200_concat_mla_params_t p;
+  memset(&p, 0, sizeof(p));
+  p.kv_c = kv_c.data_ptr();
+  p.k_pe = k_pe.data_ptr();
+  p.kv_cache = kv_cache.data_ptr();
+  p.slot_mapping = slot_mapping.data_ptr<int64_t>();
+  p.scale = kv == B200_KV_AUTO ? nullptr : scale.data_ptr<float>();
+  p.kv_c_stride = kv_c.stride(0);
+  p.k_pe_stride = k_pe.stride(0);
+  p.block_stride = kv_cache.stride(0);
+  p.entry_stride = kv_cache.stride(1);
+  p.num_tokens = static_cast<int32_t>(slot_mapping.size(0));
+  p.kv_lora_rank = static_cast<int32_t>(kv_c.size(1));
+  p.pe_dim = static_cast<int32_t>(k_pe.size(1));
+  p.block_size = static_cast<int32_t>(kv_cache.size(1));
+  p.dtype = dt;
+  p.kv_dtype = kv;
+  const at::cuda::OptionalCUDAGuard guard(device_of(kv_c));
+  check_status(b200_concat_and_cache_mla(&p, at::cuda::getCurrentCUDAStream()), "concat_and_cache_mla");
+}
+
 void fill_gather_params(b200_gather_cache_params_t& p, const at::Tensor& src_cache, const at::Tensor& dst,
                         const at::Tensor& block_table, const at::Tensor& cu_seq_lens, int64_t batch_size,
                         const std::optional<at::Tensor>& seq_starts) {
@@ -745,6 +809,14 @@ const char* kSchemaSwap = "swap_blocks(Tensor src, Tensor! dst, Tensor block_map
 const char* kSchemaCopy =
     "copy_blocks(Tensor(a!)[] key_caches, Tensor[](b!) value_caches, "
     "Tensor block_mapping) -> ()";
+// csrc/torch_bindings.cpp:389-390, :415-419
+const char* kSchemaCopyMla = "copy_blocks_mla(Tensor(a!)[] kv_caches, Tensor block_mapping) -> ()";
+const char* kSchemaConcatMla =
+    "concat_and_cache_mla(Tensor kv_c, Tensor k_pe,"
+    "                     Tensor! kv_cache,"
+    "                     Tensor slot_mapping,"
+    "                     str kv_cache_dtype,"
+    "                     Tensor scale) -> ()";
 const char* kSchemaGather =
     "gather_and_maybe_dequant_cache(Tensor src_cache, Tensor! dst, "
     "                               Tensor block_table, Tensor cu_seq_lens, "
@@ -812,6 +884,8 @@ void register_all() {
     register_op(keep, "_C_cache_ops", "copy_blocks", kSchemaCopy, &copy_blocks);
     register_op(keep, "_C_cache_ops", "gather_and_maybe_dequant_cache", kSchemaGather, &gather_and_maybe_dequant_cache);
     register_op(keep, "_C_cache_ops", "cp_gather_cache", kSchemaCpGather, &cp_gather_cache);
+    register_op(keep, "_C_cache_ops", "copy_blocks_mla", kSchemaCopyMla, &copy_blocks_mla);
+    register_op(keep, "_C_cache_ops", "concat_and_cache_mla", kSchemaConcatMla, &concat_and_cache_mla);
     register_op(keep, "_C_b200", "paged_attention_v1_lse", kSchemaV1Lse, &paged_attention_v1_lse);
     register_op(keep, "_C_b200", "paged_attention_flash", kSchemaFlash, &paged_attention_flash);
     register_op(keep, "_C", "rotary_embedding", kSchemaRotary, &rotary_embedding);
