@@ -137,36 +137,43 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
   uint32_t stage = (uint32_t)warp, parity = 0;  // ring stage / phase of this warp's next tile
   WorkIter<FLAT> wi;
   wi.init(p, sched);
-  Seg it;
-  int item = -1;
-  while (wi.next(p, it)) {
-    ++item;
-    const int ntiles = (it.t1 - it.t0 + kTileTokens - 1) / kTileTokens;
-
-    // ---- Q fragments (B operand: k = dims, n = heads) ------------------------------
-    uint32_t qf[NT][8][2];
-    float sc2[NT][2];   // logit multiplier (log2 units) of heads 2c, 2c+1
-    float al2[NT][2];   // alibi slope * log2(e)
+  // ---- Q fragments (B operand: k = dims, n = heads) of a segment --------------------------------------
+  // Loaded in two steps so that the global-memory latency of the NEXT segment's query overlaps the merge of the
+  // current one (with 512-token items the exposed wait was ~1/3 of the per-item overhead): q_issue only issues the
+  // loads (into qf for bf16, raw words for fp8), q_finish converts and derives the per-head scalars.
+  uint32_t qf[NT][8][2];
+  [[maybe_unused]] uint2 qraw[NT][8];
+  float sc2[NT][2];   // logit multiplier (log2 units) of heads 2c, 2c+1
+  float al2[NT][2];   // alibi slope * log2(e)
+  auto q_issue = [&](const Seg& sg) {
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
       const int hl = nt * 8 + g;  // head inside the group owned by this lane's B column
       const bool hv = hl < p.G;
-      const __nv_bfloat16* qrow = p.q + (int64_t)it.s * p.q_stride + (int64_t)(it.kvh * p.G + hl) * kD;
-      float qscale_inv = 1.f;
-      if constexpr (!FP8) {
+      const __nv_bfloat16* qrow = p.q + (int64_t)sg.s * p.q_stride + (int64_t)(sg.kvh * p.G + hl) * kD;
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) {
+      for (int ks = 0; ks < 8; ++ks) {
+        if constexpr (!FP8) {
           qf[nt][ks][0] = hv ? __ldg(reinterpret_cast<const uint32_t*>(qrow + 16 * ks + 2 * c)) : 0u;
           qf[nt][ks][1] = hv ? __ldg(reinterpret_cast<const uint32_t*>(qrow + 16 * ks + 8 + 2 * c)) : 0u;
+        } else {
+          qraw[nt][ks] = hv ? __ldg(reinterpret_cast<const uint2*>(qrow + 16 * ks + 4 * c)) : make_uint2(0u, 0u);
         }
-      } else {
+      }
+    }
+  };
+  auto q_finish = [&](const Seg& sg) {
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      float qscale_inv = 1.f;
+      if constexpr (FP8) {
         // bf16 -> f16 with a per-head power-of-two prescale so that no value
         // overflows f16; the prescale is undone in the logit multiplier.
         float qv[8][4];
         float amax = 0.f;
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
-          uint2 raw = hv ? __ldg(reinterpret_cast<const uint2*>(qrow + 16 * ks + 4 * c)) : make_uint2(0u, 0u);
+          const uint2 raw = qraw[nt][ks];
           const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162*>(&raw.x);
           const __nv_bfloat162 hi = *reinterpret_cast<const __nv_bfloat162*>(&raw.y);
           qv[ks][0] = __low2float(lo); qv[ks][1] = __high2float(lo);
@@ -196,9 +203,24 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int hc = nt * 8 + 2 * c + e;
-        al2[nt][e] = (p.alibi != nullptr && hc < p.G) ? __ldg(p.alibi + it.kvh * p.G + hc) * kLog2e : 0.f;
+        al2[nt][e] = (p.alibi != nullptr && hc < p.G) ? __ldg(p.alibi + sg.kvh * p.G + hc) * kLog2e : 0.f;
       }
     }
+  };
+
+  // Prefetching costs registers across the merge: worth it (and spill-free) for the item schedule with one head
+  // tile, where a CTA walks dozens of short items; the flat schedule has <= 3 segments per CTA.
+  constexpr bool kPrefetchQ = !FLAT && NT == 1;
+  Seg it, nx;
+  int item = -1;
+  bool has = wi.next(p, nx);
+  if (kPrefetchQ && has) q_issue(nx);
+  while (has) {
+    it = nx;
+    ++item;
+    const int ntiles = (it.t1 - it.t0 + kTileTokens - 1) / kTileTokens;
+    if constexpr (!kPrefetchQ) q_issue(it);
+    q_finish(it);
     const bool use_alibi = p.alibi != nullptr;
 
     // ---- running state ----------------------------------------------------------------
@@ -412,6 +434,10 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
       }
     }
     tile_base += (uint32_t)ntiles;
+    if constexpr (kPrefetchQ) {
+      has = wi.next(p, nx);
+      if (has) q_issue(nx);  // in flight during the merge below
+    }
 
     // ---- merge the consumer warps' partial results ------------------------------------------
 #pragma unroll
@@ -544,6 +570,7 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
       }
     }
     consumer_bar_sync();  // merge buffers are free again
+    if constexpr (!kPrefetchQ) has = wi.next(p, nx);
   }
 }
 
