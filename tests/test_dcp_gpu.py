@@ -1,0 +1,104 @@
+"""Decode context parallel on the CUDA kernels.
+
+`test_dcp_kernels_one_gpu`: the per-rank attention launches (paged_attention_flash with LSE over each rank's token
+shard, all heads) and the merge_attn_states fold, with the exchange done in-process — runs on a 1-GPU box and covers what
+DCP asks of the kernels (empty local shards -> out 0 / lse -inf, fold in fp32).
+`test_dcp_nccl`: `forward_decode_dcp` itself, one process per GPU over NCCL (skipped below 2 GPUs)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import torch_oracle as orc
+from dcp_common import make_problem, shard_for_rank
+
+pytestmark = pytest.mark.gpu
+
+TOL = 2e-3  # bf16 attention tolerance of the suite (tests/test_attention_gpu.py)
+
+
+def _full(d):
+    out = orc.paged_attention_flash(d["query"].float(), d["key_cache"].float(), d["value_cache"].float(),
+                                    d["block_tables"], d["seq_lens"], d["scale"])
+    lse = orc.paged_attention_flash_lse(d["query"].float(), d["key_cache"].float(), d["value_cache"].float(),
+                                        d["block_tables"], d["seq_lens"], d["scale"])
+    return out, lse
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_dcp_kernels_one_gpu(world):
+    from vllm_metax_b200 import _custom_ops as ops
+    from vllm_metax_b200.attention.dcp import _cuda_attend, _cuda_merge
+
+    dev = "cuda:0"
+    d = make_problem(S=5, H=8, Hkv=2, D=128, L=333)
+    d["seq_lens"][2] = world - 1 if world > 2 else 1  # the last rank(s) hold nothing of this sequence
+    q = d["query"].to(dev)
+    out = lse = None
+    for r in range(world):
+        lk, lv, table, lens = shard_for_rank(d, world, r)
+        o, l = _cuda_attend(q, lk.to(dev), lv.to(dev), d["scale"], table.to(dev), lens.to(dev), int(lens.max()))
+        empty = (lens == 0).nonzero().flatten().tolist()
+        for s in empty:
+            assert torch.isneginf(l[:, s]).all() and (o[s] == 0).all()
+        o = o.float()
+        out, lse = (o, l) if out is None else _cuda_merge(out, lse, o, l)
+    full, full_lse = _full(d)
+    assert (out.cpu() - full).abs().max().item() <= TOL
+    assert (lse.cpu() - full_lse).abs().max().item() <= TOL
+    del ops
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _rank_main(rank: int, world: int, port: int, ret):
+    from vllm_metax_b200.attention.dcp import dcp_local_seq_lens, forward_decode_dcp
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        H = 4 * world
+        d = make_problem(S=6, H=H, Hkv=2, D=128, L=1000)
+        Hl = H // world
+        lk, lv, table, local_lens = shard_for_rank(d, world, rank)
+        assert torch.equal(local_lens, dcp_local_seq_lens(d["seq_lens"], world, rank))
+        q_local = d["query"][:, rank * Hl:(rank + 1) * Hl].contiguous().to(dev)
+        out, lse = forward_decode_dcp(q_local, lk.to(dev), lv.to(dev), table.to(dev), local_lens.to(dev),
+                                      int(local_lens.max()), d["scale"])
+        torch.cuda.synchronize()
+        full, full_lse = _full(d)
+        err = (out.float().cpu() - full[:, rank * Hl:(rank + 1) * Hl]).abs().max().item()
+        lerr = (lse.cpu() - full_lse[rank * Hl:(rank + 1) * Hl]).abs().max().item()
+        ret[rank] = (err, lerr)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_dcp_nccl(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        ret = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_rank_main, args=(r, world, port, ret)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(300)
+            assert p.exitcode == 0
+        for r in range(world):
+            err, lerr = ret[r]
+            # bf16 output: one rounding of the merged value on top of the kernel tolerance
+            assert err <= 2 * TOL and lerr <= TOL, (r, err, lerr)

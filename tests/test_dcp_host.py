@@ -1,0 +1,87 @@
+"""Decode context parallel, host logic on CPU (gloo, world_size 2 and 3): the query all-gather, the packed all-to-all of
+(output, lse) head slices and the fold with the merge rule reproduce attention over the whole, unsharded sequences.
+The attention / merge callables are the CPU oracle here (the checker stands in for the kernels in this tier of the
+suite); tests/test_dcp_gpu.py runs the same function on the CUDA kernels over NCCL."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import torch_oracle as orc
+from dcp_common import make_problem, shard_for_rank
+from vllm_metax_b200.attention.dcp import dcp_local_seq_lens, dcp_token_owner, forward_decode_dcp
+
+
+def test_local_seq_lens_match_token_ownership():
+    for world in (1, 2, 3, 8):
+        lens = torch.tensor([0, 1, 2, 7, 8, 9, 4096, 4097], dtype=torch.int32)
+        counts = torch.zeros(world, len(lens), dtype=torch.int32)
+        for i, L in enumerate(lens.tolist()):
+            for t in range(L):
+                r, local = dcp_token_owner(t, world)
+                assert local == counts[r, i]  # tokens of a rank are dense, in order
+                counts[r, i] += 1
+        for r in range(world):
+            assert torch.equal(dcp_local_seq_lens(lens, world, r), counts[r])
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _oracle_attend(query, key_cache, value_cache, scale, block_table, seq_lens, max_seq_len):
+    out = orc.paged_attention_flash(query, key_cache, value_cache, block_table, seq_lens, scale)
+    lse = orc.paged_attention_flash_lse(query, key_cache, value_cache, block_table, seq_lens, scale)
+    return out, lse
+
+
+def _oracle_merge(po, pl, so, sl):
+    return orc.merge_attn_states(po, pl, so, sl)
+
+
+def _rank_main(rank: int, world: int, port: int, ret):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.set_num_threads(1)
+        H = 4 * world
+        d = make_problem(H=H, Hkv=2, D=64, L=150, dtype=torch.float32)
+        Hl = H // world
+        lk, lv, table, local_lens = shard_for_rank(d, world, rank)
+        assert torch.equal(local_lens, dcp_local_seq_lens(d["seq_lens"], world, rank))
+        q_local = d["query"][:, rank * Hl:(rank + 1) * Hl].contiguous()
+        out, lse = forward_decode_dcp(q_local, lk, lv, table, local_lens, int(local_lens.max()), d["scale"],
+                                      attend=_oracle_attend, merge=_oracle_merge)
+        full = orc.paged_attention_flash(d["query"], d["key_cache"], d["value_cache"], d["block_tables"], d["seq_lens"],
+                                         d["scale"])
+        full_lse = orc.paged_attention_flash_lse(d["query"], d["key_cache"], d["value_cache"], d["block_tables"],
+                                                 d["seq_lens"], d["scale"])
+        err = (out - full[:, rank * Hl:(rank + 1) * Hl]).abs().max().item()
+        lerr = (lse - full_lse[rank * Hl:(rank + 1) * Hl]).abs().max().item()
+        ret[rank] = (err, lerr)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_dcp_decode_equals_unsharded_attention(world):
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        ret = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_rank_main, args=(r, world, port, ret)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(180)
+            assert p.exitcode == 0
+        assert len(ret) == world
+        for r in range(world):
+            err, lerr = ret[r]
+            assert err <= 1e-5 and lerr <= 1e-5, (r, err, lerr)

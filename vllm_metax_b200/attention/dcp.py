@@ -1,0 +1,98 @@
+"""Decode context parallel (DCP): the one place where the decode path has a real exchange step.
+
+For long contexts the reference can shard the TOKENS of every sequence across the ranks of a DCP group instead of
+(or on top of) sharding heads: token t of a sequence lives on rank t % N, stored densely in that rank's own paged cache
+(reference: vllm_metax/v1/attention/backends/flash_attn.py:421-431).
+A decode step then is (flash_attn.py:794-872, `_forward_with_dcp`):
+
+  1. all-gather the query over the group along the head dimension: every rank attends with ALL heads of the group,
+  2. attention over the local token shard, returning the partial output and its log-sum-exp,
+  3. exchange: every rank needs, for ITS heads, the partial (output, lse) of all ranks (upstream's `cp_lse_ag_out_rs`:
+     all-gather of the lse + reduce-scatter of the corrected outputs),
+  4. combine the N partials with the merge_attn_states rule.
+
+Here step 2 is `paged_attention_flash(..., lse)` (or `paged_attention_v1_lse`), step 3 is ONE all-to-all of the packed
+(output, lse) head slices — each rank receives exactly the N partials of its own heads, N x less than an all-gather —
+and step 4 folds them with `merge_attn_states`.  `torch.distributed` (NCCL over NVLink/NVSwitch) is plumbing; the
+attention and merge kernels are the product.  The attention / merge callables are parameters so that the host logic can
+be exercised on CPU (gloo) in the tests.
+"""
+from __future__ import annotations
+
+from typing import Callable
+
+import torch
+import torch.distributed as dist
+
+
+def dcp_local_seq_lens(seq_lens: torch.Tensor, world_size: int, rank: int) -> torch.Tensor:
+    """Tokens of each sequence that live on `rank` when token t is stored on rank t % world_size: L // N plus one for
+    the ranks below L % N.  (The reference computes `L // N + (rank <= (L - 1) % N)` at flash_attn.py:425-429, which is
+    the same count except when L is a multiple of N, where it is one too many on every rank; the ownership count is
+    used here.)"""
+    return seq_lens // world_size + (rank < seq_lens % world_size).to(seq_lens.dtype)
+
+
+def dcp_token_owner(position: int, world_size: int) -> tuple[int, int]:
+    """(rank, local position) of global token `position`."""
+    return position % world_size, position // world_size
+
+
+def _cuda_attend(query, key_cache, value_cache, scale, block_table, seq_lens, max_seq_len):
+    from .. import _custom_ops as ops
+
+    S, H, _ = query.shape
+    out = torch.empty_like(query)
+    lse = torch.empty((H, S), dtype=torch.float32, device=query.device)
+    ops.paged_attention_flash(out, query, key_cache, value_cache, scale, block_table, seq_lens, max_seq_len, None, lse)
+    return out, lse
+
+
+def _cuda_merge(prefix_out, prefix_lse, suffix_out, suffix_lse):
+    from .. import _custom_ops as ops
+
+    out = torch.empty_like(prefix_out)
+    lse = torch.empty_like(prefix_lse)
+    ops.merge_attn_states(out, prefix_out, prefix_lse, suffix_out, suffix_lse, lse)
+    return out, lse
+
+
+def forward_decode_dcp(
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    block_table: torch.Tensor,
+    local_seq_lens: torch.Tensor,
+    max_local_seq_len: int,
+    scale: float,
+    group: dist.ProcessGroup | None = None,
+    attend: Callable = _cuda_attend,
+    merge: Callable = _cuda_merge,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """One DCP decode step.  query [S, H_local, D] (this rank's heads); key_cache / value_cache: this rank's token shard
+    in the flash layout; block_table / local_seq_lens describe the shard.  Returns (out [S, H_local, D], lse [H_local, S])
+    of attention over the WHOLE sequences for this rank's heads."""
+    world = dist.get_world_size(group)
+    S, Hl, D = query.shape
+    # 1. all heads of the group on every rank: [S, N * H_local, D], rank-major along heads
+    gathered = torch.empty((world * S, Hl, D), dtype=query.dtype, device=query.device)
+    dist.all_gather_into_tensor(gathered, query.contiguous(), group=group)
+    q_all = gathered.view(world, S, Hl, D).permute(1, 0, 2, 3).reshape(S, world * Hl, D).contiguous()
+    # 2. partial attention over the local tokens
+    out_all, lse_all = attend(q_all, key_cache, value_cache, scale, block_table, local_seq_lens, max_local_seq_len)
+    # a rank that holds no token of a sequence contributes weight 0: its row must be finite (0) with lse = -inf
+    # 3. exchange: head slice j of (out, lse) goes to rank j.  Packed as float32 [N, S, H_local, D + 1] so that one
+    #    all-to-all carries both (the lse rides in the last column).
+    send = torch.empty((world, S, Hl, D + 1), dtype=torch.float32, device=query.device)
+    send[..., :D] = out_all.view(S, world, Hl, D).permute(1, 0, 2, 3)
+    send[..., D] = lse_all.view(world, Hl, S).permute(0, 2, 1)
+    recv = torch.empty_like(send)
+    dist.all_to_all_single(recv.view(world * S, Hl, D + 1), send.view(world * S, Hl, D + 1), group=group)
+    # 4. fold the N partials of this rank's heads (merge_attn_states is associative on (out, lse) pairs)
+    #    in float32, rounded once at the end.  Rank 0 holds token 0 of every non-empty sequence, so the running
+    #    pair never starts from two empty partials.
+    out = recv[0, ..., :D].contiguous()
+    lse = recv[0, ..., D].t().contiguous()
+    for r in range(1, world):
+        out, lse = merge(out, lse, recv[r, ..., :D].contiguous(), recv[r, ..., D].t().contiguous())
+    return out.to(query.dtype), lse
