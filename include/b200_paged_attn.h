@@ -432,6 +432,58 @@ int b200_rotary_embedding(const b200_rotary_params_t* params, void* stream);
  * two ops back to back, vllm_metax/v1/attention/backends/flash_attn.py:678-687 after the model's rotary layer). */
 int b200_rotary_embedding_and_cache_flash(const b200_rotary_params_t* params, void* stream);
 
+/*
+ * Decode context parallel (DCP): exchange + combine of the per-rank partial
+ * attention results in ONE launch over peer-mapped memory.  Replaces the
+ * collective pair + correction the reference runs after its DCP attention call
+ * (vllm_metax/v1/attention/backends/flash_attn.py:836-841, upstream
+ * `cp_lse_ag_out_rs`: all-gather of the lse, reduce-scatter of the corrected
+ * outputs), with the combination rule of merge_attn_states
+ * (csrc/attention/merge_attn_states.cu:14-88) applied to world partials at once.
+ *
+ * Every rank r has written, with an attention call that precedes this one on
+ * `stream`, its partial over its own token shard for ALL heads of the group:
+ *   peer_out[r]   [num_seqs, world*heads_local, head_size] dtype, contiguous
+ *   peer_lse[r]   [world*heads_local, num_seqs] float32
+ * (pointers valid in THIS process: the local buffer for r == rank, an IPC
+ * mapping otherwise — b200_peer_alloc / b200_peer_open).  peer_flags[r] is rank
+ * r's array of `world` uint32 arrival flags, zero-initialised, writable through
+ * the mapping.  The launch publishes `epoch` to flag[rank] of every peer, waits
+ * for flag[r] >= epoch of every r, pulls the slices of heads
+ * [rank*heads_local, (rank+1)*heads_local) and writes
+ *   out [num_seqs, heads_local, head_size] dtype,
+ *   out_lse [heads_local, num_seqs] float32 (nullable).
+ * `epoch` starts at 1 and grows by one per step on every rank; the partial
+ * buffers must alternate between two allocations by epoch parity (a peer may
+ * be one step ahead).  A peer that does not arrive within 10 s traps the
+ * kernel.  world <= B200_DCP_MAX_WORLD.
+ */
+#define B200_DCP_MAX_WORLD 16
+typedef struct b200_dcp_fold_params {
+  const void* const* peer_out;  /* [world] host array of device pointers */
+  const float* const* peer_lse; /* [world] */
+  uint32_t* const* peer_flags;  /* [world] */
+  void* out;
+  float* out_lse; /* nullable */
+  int32_t rank;
+  int32_t world;
+  int32_t num_seqs;
+  int32_t heads_local;
+  int32_t head_size;
+  int32_t dtype; /* b200_dtype_t of the partial and final outputs */
+  uint32_t epoch;
+} b200_dcp_fold_params_t;
+int b200_dcp_exchange_fold(const b200_dcp_fold_params_t* params, void* stream);
+
+/* Peer-mappable device memory for the DCP buffers: one cudaMalloc (zero-filled)
+ * and its 64-byte CUDA IPC handle; b200_peer_open maps a handle received from
+ * another process of the same node (peer access enabled lazily) and returns a
+ * pointer valid in the calling process.  Synchronous host calls. */
+int b200_peer_alloc(uint64_t bytes, void** ptr, void* handle64);
+int b200_peer_open(const void* handle64, void** ptr);
+int b200_peer_close(void* ptr);
+int b200_peer_free(void* ptr);
+
 /* "auto" -> B200_KV_AUTO, "fp8" | "fp8_e4m3" -> B200_KV_FP8_E4M3, anything
  * else (incl. "fp8_e5m2") -> -1. */
 int b200_kv_dtype_from_string(const char* kv_cache_dtype);

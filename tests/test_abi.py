@@ -50,7 +50,8 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
                       ("b200_merge_attn_states_params_t", native.MergeAttnStatesParams),
                       ("b200_gather_cache_params_t", native.GatherCacheParams),
                       ("b200_rotary_params_t", native.RotaryParams),
-                      ("b200_concat_mla_params_t", native.ConcatMlaParams)):
+                      ("b200_concat_mla_params_t", native.ConcatMlaParams),
+                      ("b200_dcp_fold_params_t", native.DcpFoldParams)):
         prog.append('printf("%%zu\\n", sizeof(%s));' % cname)
         for f in fields(st):
             prog.append('printf("%%zu\\n", offsetof(%s, %s));' % (cname, f))
@@ -62,7 +63,7 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
     vals = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     it = iter(vals)
     for st in (native.PagedAttnParams, native.CacheWriteParams, native.MergeAttnStatesParams, native.GatherCacheParams,
-               native.RotaryParams, native.ConcatMlaParams):
+               native.RotaryParams, native.ConcatMlaParams, native.DcpFoldParams):
         assert next(it) == C.sizeof(st)
         for f in fields(st):
             assert next(it) == getattr(st, f).offset, f
@@ -166,6 +167,24 @@ def test_new_entry_points_validate_on_the_host(native):
     m = (C.c_int64 * 2)(0, 1)
     assert lib.b200_swap_blocks(4096, 8192, m, 1, 64, 9, None) == native.ERR_INVALID_ARGUMENT
     assert "Invalid device combination" in lib.b200_last_error().decode()
+
+
+def test_dcp_exchange_fold_validates_on_the_host(native):
+    import torch
+
+    out = torch.empty(2, 4, 128, dtype=torch.bfloat16)
+    with pytest.raises(native.B200Error, match="NULL buffer of rank 1") as e:
+        native.dcp_exchange_fold([4096, 0], [4096, 0], [4096, 0], out, None, 0, 2, 4, 128, 1, 0)
+    assert e.value.code == native.ERR_INVALID_ARGUMENT
+    with pytest.raises(native.B200Error, match="epoch 0"):
+        native.dcp_exchange_fold([4096], [4096], [4096], out, None, 0, 2, 4, 128, 0, 0)
+    with pytest.raises(native.B200Error, match="rank 3 of 2"):
+        native.dcp_exchange_fold([4096, 4096], [4096, 4096], [4096, 4096], out, None, 3, 2, 4, 128, 1, 0)
+    with pytest.raises(native.B200Error, match="world size 17"):
+        native.dcp_exchange_fold([4096] * 17, [4096] * 17, [4096] * 17, out, None, 0, 2, 4, 128, 1, 0)
+    with pytest.raises(native.B200Error, match="not 16-byte aligned"):
+        native.dcp_exchange_fold([4104], [4096], [4096], out, None, 0, 2, 4, 128, 1, 0)
+    assert native.DCP_MAX_WORLD == 16
 
 
 def test_workspace_sizing_is_host_only_and_monotone(native):

@@ -58,8 +58,8 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
-def _rank_main(rank: int, world: int, port: int, ret):
-    from vllm_metax_b200.attention.dcp import dcp_local_seq_lens, forward_decode_dcp
+def _rank_main(rank: int, world: int, port: int, fused: bool, ret):
+    from vllm_metax_b200.attention.dcp import DcpExchange, dcp_local_seq_lens, forward_decode_dcp
 
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -72,27 +72,41 @@ def _rank_main(rank: int, world: int, port: int, ret):
         Hl = H // world
         lk, lv, table, local_lens = shard_for_rank(d, world, rank)
         assert torch.equal(local_lens, dcp_local_seq_lens(d["seq_lens"], world, rank))
-        q_local = d["query"][:, rank * Hl:(rank + 1) * Hl].contiguous().to(dev)
-        out, lse = forward_decode_dcp(q_local, lk.to(dev), lv.to(dev), table.to(dev), local_lens.to(dev),
-                                      int(local_lens.max()), d["scale"])
-        torch.cuda.synchronize()
-        full, full_lse = _full(d)
-        err = (out.float().cpu() - full[:, rank * Hl:(rank + 1) * Hl]).abs().max().item()
-        lerr = (lse.cpu() - full_lse[rank * Hl:(rank + 1) * Hl]).abs().max().item()
-        ret[rank] = (err, lerr)
+        lk, lv, table, lens_dev = lk.to(dev), lv.to(dev), table.to(dev), local_lens.to(dev)
+        max_local = int(local_lens.max())
+        xch = DcpExchange(8, H, 128, torch.bfloat16) if fused else None
+        errs = []
+        # several steps with different queries: the fused path alternates its two partial buffers and its flags grow
+        for step in range(5 if fused else 1):
+            q = d["query"] if step == 0 else torch.randn(d["query"].shape, generator=torch.Generator().manual_seed(step)).bfloat16()
+            d_step = dict(d, query=q)
+            q_local = q[:, rank * Hl:(rank + 1) * Hl].contiguous().to(dev)
+            if fused:
+                out, lse = xch.forward_decode(q_local, lk, lv, table, lens_dev, max_local, d["scale"])
+            else:
+                out, lse = forward_decode_dcp(q_local, lk, lv, table, lens_dev, max_local, d["scale"])
+            torch.cuda.synchronize()
+            full, full_lse = _full(d_step)
+            err = (out.float().cpu() - full[:, rank * Hl:(rank + 1) * Hl]).abs().max().item()
+            lerr = (lse.cpu() - full_lse[rank * Hl:(rank + 1) * Hl]).abs().max().item()
+            errs.append((err, lerr))
+        if fused:
+            xch.close()
+        ret[rank] = (max(e for e, _ in errs), max(l for _, l in errs))
     finally:
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("fused", [False, True], ids=["nccl_all_to_all", "peer_memory_fold"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_dcp_nccl(world):
+def test_dcp_nccl(world, fused):
     if torch.cuda.device_count() < world:
         pytest.skip("needs %d GPUs" % world)
     ctx = mp.get_context("spawn")
     with ctx.Manager() as mgr:
         ret = mgr.dict()
         port = _free_port()
-        procs = [ctx.Process(target=_rank_main, args=(r, world, port, ret)) for r in range(world)]
+        procs = [ctx.Process(target=_rank_main, args=(r, world, port, fused, ret)) for r in range(world)]
         for p in procs:
             p.start()
         for p in procs:
@@ -102,3 +116,26 @@ def test_dcp_nccl(world):
             err, lerr = ret[r]
             # bf16 output: one rounding of the merged value on top of the kernel tolerance
             assert err <= 2 * TOL and lerr <= TOL, (r, err, lerr)
+
+
+def test_dcp_exchange_world1():
+    """The fused exchange on one GPU (group of one): flags, double buffering and the fold with a single partial."""
+    from vllm_metax_b200.attention.dcp import DcpExchange
+
+    port = _free_port()
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % port, rank=0, world_size=1, device_id=dev)
+    try:
+        d = make_problem(S=5, H=8, Hkv=2, D=128, L=333)
+        xch = DcpExchange(8, 8, 128, torch.bfloat16)
+        kc, vc = d["key_cache"].to(dev), d["value_cache"].to(dev)
+        table, lens = d["block_tables"].to(dev), d["seq_lens"].to(dev)
+        full, full_lse = _full(d)
+        for _ in range(3):
+            out, lse = xch.forward_decode(d["query"].to(dev), kc, vc, table, lens, int(d["seq_lens"].max()), d["scale"])
+            assert (out.float().cpu() - full).abs().max().item() <= TOL
+            assert (lse.cpu() - full_lse).abs().max().item() <= TOL
+        xch.close()
+    finally:
+        dist.destroy_process_group()

@@ -36,6 +36,11 @@ EXPORTED_SYMBOLS = (
     "b200_concat_and_cache_mla",
     "b200_swap_blocks",
     "b200_gather_cache",
+    "b200_dcp_exchange_fold",
+    "b200_peer_alloc",
+    "b200_peer_open",
+    "b200_peer_close",
+    "b200_peer_free",
     "b200_kv_dtype_from_string",
     "b200_last_error",
     "b200_abi_version",
@@ -201,6 +206,24 @@ class ConcatMlaParams(C.Structure):
     ]
 
 
+class DcpFoldParams(C.Structure):
+    _fields_ = [
+        ("peer_out", C.POINTER(C.c_void_p)),
+        ("peer_lse", C.POINTER(C.c_void_p)),
+        ("peer_flags", C.POINTER(C.c_void_p)),
+        ("out", C.c_void_p),
+        ("out_lse", C.c_void_p),
+        ("rank", C.c_int32),
+        ("world", C.c_int32),
+        ("num_seqs", C.c_int32),
+        ("heads_local", C.c_int32),
+        ("head_size", C.c_int32),
+        ("dtype", C.c_int32),
+        ("epoch", C.c_uint32),
+    ]
+
+
+DCP_MAX_WORLD = 16
 COPY_D2D, COPY_D2H, COPY_H2D = 0, 1, 2
 
 _lib = None
@@ -256,6 +279,16 @@ def load() -> C.CDLL:
     lib.b200_swap_blocks.restype = C.c_int
     lib.b200_gather_cache.argtypes = [P(GatherCacheParams), C.c_void_p]
     lib.b200_gather_cache.restype = C.c_int
+    lib.b200_dcp_exchange_fold.argtypes = [P(DcpFoldParams), C.c_void_p]
+    lib.b200_dcp_exchange_fold.restype = C.c_int
+    lib.b200_peer_alloc.argtypes = [C.c_uint64, P(C.c_void_p), C.c_void_p]
+    lib.b200_peer_alloc.restype = C.c_int
+    lib.b200_peer_open.argtypes = [C.c_void_p, P(C.c_void_p)]
+    lib.b200_peer_open.restype = C.c_int
+    lib.b200_peer_close.argtypes = [C.c_void_p]
+    lib.b200_peer_close.restype = C.c_int
+    lib.b200_peer_free.argtypes = [C.c_void_p]
+    lib.b200_peer_free.restype = C.c_int
     lib.b200_kv_dtype_from_string.argtypes = [C.c_char_p]
     lib.b200_kv_dtype_from_string.restype = C.c_int
     lib.b200_last_error.argtypes = []
@@ -419,3 +452,42 @@ def flash_attn_params(out, query, key_cache, value_cache, scale, block_tables, s
 
 def paged_attention_flash(p: PagedAttnParams, stream: int) -> None:
     check(load().b200_paged_attention_flash(C.byref(p), C.c_void_p(stream)))
+
+
+def peer_alloc(nbytes: int) -> tuple[int, bytes]:
+    """(device pointer, 64-byte IPC handle) of a zero-filled cudaMalloc on the current device."""
+    ptr = C.c_void_p()
+    handle = C.create_string_buffer(64)
+    check(load().b200_peer_alloc(C.c_uint64(nbytes), C.byref(ptr), handle))
+    return ptr.value, handle.raw
+
+
+def peer_open(handle: bytes) -> int:
+    ptr = C.c_void_p()
+    buf = C.create_string_buffer(handle, 64)
+    check(load().b200_peer_open(buf, C.byref(ptr)))
+    return ptr.value
+
+
+def peer_close(ptr: int) -> None:
+    check(load().b200_peer_close(C.c_void_p(ptr)))
+
+
+def peer_free(ptr: int) -> None:
+    check(load().b200_peer_free(C.c_void_p(ptr)))
+
+
+def dcp_exchange_fold(peer_out, peer_lse, peer_flags, out, out_lse, rank, num_seqs, heads_local, head_size, epoch,
+                      stream: int) -> None:
+    """peer_out / peer_lse / peer_flags: sequences of `world` device addresses (ints)."""
+    world = len(peer_out)
+    arr = C.c_void_p * world
+    p = DcpFoldParams()
+    a_out, a_lse, a_flags = arr(*peer_out), arr(*peer_lse), arr(*peer_flags)
+    p.peer_out, p.peer_lse, p.peer_flags = a_out, a_lse, a_flags
+    p.out = out.data_ptr()
+    p.out_lse = out_lse.data_ptr() if out_lse is not None else None
+    p.rank, p.world, p.num_seqs, p.heads_local, p.head_size = rank, world, num_seqs, heads_local, head_size
+    p.dtype = _torch_dtype_code(out.dtype)
+    p.epoch = epoch
+    check(load().b200_dcp_exchange_fold(C.byref(p), C.c_void_p(stream)))

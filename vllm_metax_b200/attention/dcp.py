@@ -96,3 +96,95 @@ def forward_decode_dcp(
     for r in range(1, world):
         out, lse = merge(out, lse, recv[r, ..., :D].contiguous(), recv[r, ..., D].t().contiguous())
     return out.to(query.dtype), lse
+
+
+class _DeviceBytes:
+    """A raw device allocation seen through __cuda_array_interface__ (torch.as_tensor wraps it without copying)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3,
+                                         "strides": None}
+
+
+def _align256(n: int) -> int:
+    return (n + 255) // 256 * 256
+
+
+class DcpExchange:
+    """DCP decode step with the exchange + combine fused into one kernel over peer memory (b200_dcp_exchange_fold).
+
+    Steps 3 and 4 of `forward_decode_dcp` — pack, all-to-all, N-1 merge launches — become ONE launch: the attention
+    kernel writes its partial (out, lse) for all heads straight into a buffer that the peers have mapped through CUDA
+    IPC (NVLink / NVSwitch peer access), and the fold kernel signals the peers, waits for their flags and pulls the N
+    slices of this rank's heads, combining them in fp32 on the fly.  The partial buffers are double-buffered by step
+    parity (csrc/dcp_exchange.cu explains why two suffice).  One instance per (group, shape bound); every rank of the
+    group must call `forward_decode` the same number of times.  Same node only (CUDA IPC).
+    """
+
+    def __init__(self, max_seqs: int, num_heads_total: int, head_size: int, dtype: torch.dtype,
+                 group: dist.ProcessGroup | None = None):
+        from .. import _native as native
+
+        self._native = native
+        self.group = group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if self.world > native.DCP_MAX_WORLD:
+            raise ValueError("DCP group of %d ranks (max %d)" % (self.world, native.DCP_MAX_WORLD))
+        if num_heads_total % self.world != 0:
+            raise ValueError("num_heads_total must be a multiple of the group size")
+        self.max_seqs, self.num_heads_total, self.head_size, self.dtype = max_seqs, num_heads_total, head_size, dtype
+        self._esize = torch.empty((), dtype=dtype).element_size()
+        self._out_bytes = _align256(max_seqs * num_heads_total * head_size * self._esize)
+        self._lse_bytes = _align256(num_heads_total * max_seqs * 4)
+        self._half = self._out_bytes + self._lse_bytes
+        total = 2 * self._half + 256  # two partial buffers + the flag words
+        self._device = torch.device("cuda", torch.cuda.current_device())
+        self._ptr, handle = native.peer_alloc(total)
+        handles: list = [None] * self.world
+        dist.all_gather_object(handles, handle, group=group)
+        self._bases = [self._ptr if r == self.rank else native.peer_open(handles[r]) for r in range(self.world)]
+        self._local = torch.as_tensor(_DeviceBytes(self._ptr, total), device=self._device)
+        self._epoch = 0
+        dist.barrier(group=group)  # every flag array is zeroed and mapped before the first signal
+
+    def close(self) -> None:
+        if self._bases is None:
+            return
+        torch.cuda.synchronize(self._device)
+        dist.barrier(group=self.group)  # nobody is still reading this rank's buffers
+        for r, b in enumerate(self._bases):
+            if r != self.rank:
+                self._native.peer_close(b)
+        self._native.peer_free(self._ptr)
+        self._bases = None
+        self._local = None
+
+    def forward_decode(self, query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                       block_table: torch.Tensor, local_seq_lens: torch.Tensor, max_local_seq_len: int,
+                       scale: float) -> tuple[torch.Tensor, torch.Tensor]:
+        """Same contract as `forward_decode_dcp`: (out [S, H_local, D], lse [H_local, S])."""
+        from .. import _custom_ops as ops
+
+        world, rank = self.world, self.rank
+        S, Hl, D = query.shape
+        H = Hl * world
+        if H != self.num_heads_total or D != self.head_size or query.dtype != self.dtype or S > self.max_seqs:
+            raise ValueError("query %s %s does not fit the exchange buffers (max_seqs %d, heads %d, head_size %d, %s)"
+                             % (tuple(query.shape), query.dtype, self.max_seqs, self.num_heads_total, self.head_size,
+                                self.dtype))
+        gathered = torch.empty((world * S, Hl, D), dtype=query.dtype, device=query.device)
+        dist.all_gather_into_tensor(gathered, query.contiguous(), group=self.group)
+        q_all = gathered.view(world, S, Hl, D).permute(1, 0, 2, 3).reshape(S, H, D)
+        self._epoch += 1
+        off = (self._epoch & 1) * self._half
+        out_all = self._local[off:off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
+        lse_all = self._local[off + self._out_bytes:off + self._out_bytes + H * S * 4].view(torch.float32).view(H, S)
+        ops.paged_attention_flash(out_all, q_all, key_cache, value_cache, scale, block_table, local_seq_lens,
+                                  max_local_seq_len, None, lse_all)
+        out = torch.empty((S, Hl, D), dtype=query.dtype, device=query.device)
+        lse = torch.empty((Hl, S), dtype=torch.float32, device=query.device)
+        self._native.dcp_exchange_fold(
+            [b + off for b in self._bases], [b + off + self._out_bytes for b in self._bases],
+            [b + 2 * self._half for b in self._bases], out, lse, rank, S, Hl, D, self._epoch,
+            torch.cuda.current_stream(query.device).cuda_stream)
+        return out, lse

@@ -1,0 +1,233 @@
+// Decode context parallel: the exchange + combine step as ONE kernel over peer memory.
+//
+// After the local attention launch every rank r of the group holds, in a buffer that its peers have mapped
+// (CUDA IPC over NVLink / NVSwitch), the partial result of ALL query heads over ITS token shard:
+//     partial_out_r [num_seqs, world * heads_local, head_size]   (dtype)
+//     partial_lse_r [world * heads_local, num_seqs]              (float32)
+// Rank `rank` needs, for its heads_local heads, the N partials and their combination by the merge_attn_states rule
+// (reference: all-gather of the lse + reduce-scatter of the corrected outputs, then nothing else —
+// vllm_metax/v1/attention/backends/flash_attn.py:836-841 `cp_lse_ag_out_rs`; combination rule
+// csrc/attention/merge_attn_states.cu:14-88).  This kernel
+//   1. publishes "my partial of step `epoch` is complete" by storing `epoch` into flag[rank] of every peer
+//      (st.release.sys after a system fence; the attention launch that produced the partial precedes this kernel on
+//      the stream),
+//   2. waits until flag[r] >= epoch for every r (ld.acquire.sys on local memory),
+//   3. pulls the head slice [rank*heads_local, (rank+1)*heads_local) of every peer's partial with 16-byte loads over
+//      NVLink and folds the N partials in fp32:  m = max_r lse_r, w_r = exp(lse_r - m),
+//      out = sum_r w_r o_r / sum_r w_r,  lse = m + log sum_r w_r   (one rounding, at the store).
+// Each rank pulls exactly the N-1 remote slices of its own heads — (N-1) * num_seqs * heads_local * (head_size *
+// sizeof(T) + 4) bytes over the fabric, the volume of a reduce-scatter — with no staging copy, pack or second launch.
+//
+// Buffer reuse: the caller alternates two partial buffers by step parity.  A peer can be at most one step ahead
+// (it cannot pass the wait of step k+1 before this rank has launched its step-k+1 kernel, which follows this rank's
+// step-k kernel on the stream), so the buffer of parity k%2 is not overwritten while step k is still being read.
+// Flags only grow, so "a peer is already one step ahead" also satisfies the wait.
+#include "common.cuh"
+
+namespace b200 {
+namespace {
+
+struct DcpFoldArgs {
+  const void* peer_out[B200_DCP_MAX_WORLD];
+  const float* peer_lse[B200_DCP_MAX_WORLD];
+  uint32_t* peer_flags[B200_DCP_MAX_WORLD];
+  void* out;
+  float* out_lse;
+  int32_t rank, world, num_seqs, heads_local, head_size;
+  uint32_t epoch;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_relaxed_sys_f32(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ Vec16 ld_relaxed_sys_16(const void* p) {
+  Vec16 v;
+  uint32_t* w = reinterpret_cast<uint32_t*>(&v);
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3])
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+constexpr uint64_t kWaitLimitNs = 10ull * 1000 * 1000 * 1000;  // a peer that never arrives traps instead of hanging
+
+template <typename T>
+__global__ void __launch_bounds__(256) dcp_exchange_fold_kernel(const __grid_constant__ DcpFoldArgs a) {
+  constexpr int kPack = 16 / sizeof(T);
+  // 1. publish (one CTA; every CTA of this launch is past the producing attention launch)
+  if (blockIdx.x == 0 && threadIdx.x < a.world) {
+    __threadfence_system();
+    st_release_sys(a.peer_flags[threadIdx.x] + a.rank, a.epoch);
+  }
+  // 2. wait for every rank's partial
+  if (threadIdx.x < a.world) {
+    const uint32_t* f = a.peer_flags[a.rank] + threadIdx.x;
+    const uint64_t t0 = globaltimer_ns();
+    // flags only grow; the signed difference keeps the comparison right across a 2^32 wrap
+    while ((int32_t)(ld_acquire_sys(f) - a.epoch) < 0) {
+      __nanosleep(64);
+      if (globaltimer_ns() - t0 > kWaitLimitNs) __trap();
+    }
+  }
+  __syncthreads();
+
+  // 3. pull + fold
+  const uint32_t packs_per_head = a.head_size / kPack;
+  const uint64_t total = (uint64_t)a.num_seqs * a.heads_local * packs_per_head;
+  const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const uint32_t pack = idx % packs_per_head;
+  const uint64_t sh = idx / packs_per_head;
+  const uint32_t hl = sh % a.heads_local;
+  const uint64_t seq = sh / a.heads_local;
+  const uint32_t heads_all = a.world * a.heads_local;
+  const uint32_t head = a.rank * a.heads_local + hl;
+  const uint64_t lse_off = (uint64_t)head * a.num_seqs + seq;
+  const uint64_t out_off = (seq * heads_all + head) * a.head_size + (uint64_t)pack * kPack;
+
+  float lse[B200_DCP_MAX_WORLD];
+  Vec16 v[B200_DCP_MAX_WORLD];
+  float m = -INFINITY;
+#pragma unroll
+  for (int r = 0; r < B200_DCP_MAX_WORLD; ++r) {
+    if (r < a.world) {
+      float l = ld_relaxed_sys_f32(a.peer_lse[r] + lse_off);
+      l = isinf(l) ? -INFINITY : l;  // merge_attn_states.cu:45-46
+      lse[r] = l;
+      v[r] = ld_relaxed_sys_16(reinterpret_cast<const T*>(a.peer_out[r]) + out_off);
+      m = fmaxf(m, l);
+    }
+  }
+  float acc[kPack];
+#pragma unroll
+  for (int i = 0; i < kPack; ++i) acc[i] = 0.f;
+  float se = 0.f;
+#pragma unroll
+  for (int r = 0; r < B200_DCP_MAX_WORLD; ++r) {
+    if (r < a.world) {
+      const float w = expf(lse[r] - m);
+      se += w;
+      const T* e = reinterpret_cast<const T*>(&v[r]);
+#pragma unroll
+      for (int i = 0; i < kPack; ++i) acc[i] = __fmaf_rn(to_f32<T>(e[i]), w, acc[i]);
+    }
+  }
+  const float inv = 1.f / se;
+  Vec16 ov;
+  T* oe = reinterpret_cast<T*>(&ov);
+#pragma unroll
+  for (int i = 0; i < kPack; ++i) oe[i] = from_f32<T>(acc[i] * inv);
+  *reinterpret_cast<Vec16*>(reinterpret_cast<T*>(a.out) + (seq * a.heads_local + hl) * a.head_size + (uint64_t)pack * kPack) = ov;
+  if (a.out_lse != nullptr && pack == 0) a.out_lse[(uint64_t)hl * a.num_seqs + seq] = logf(se) + m;
+}
+
+}  // namespace
+}  // namespace b200
+
+extern "C" int b200_dcp_exchange_fold(const b200_dcp_fold_params_t* p, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(p != nullptr, B200_ERR_INVALID_ARGUMENT, "params is NULL");
+  B200_REQUIRE(p->world >= 1 && p->world <= B200_DCP_MAX_WORLD, B200_ERR_UNSUPPORTED,
+               "dcp_exchange_fold: world size %d outside 1..%d", p->world, B200_DCP_MAX_WORLD);
+  B200_REQUIRE(p->rank >= 0 && p->rank < p->world, B200_ERR_INVALID_ARGUMENT, "dcp_exchange_fold: rank %d of %d", p->rank,
+               p->world);
+  B200_REQUIRE(p->num_seqs >= 0 && p->heads_local > 0 && p->head_size > 0, B200_ERR_INVALID_ARGUMENT,
+               "bad sizes: seqs=%d heads_local=%d head_size=%d", p->num_seqs, p->heads_local, p->head_size);
+  B200_REQUIRE(p->dtype == B200_DTYPE_F32 || p->dtype == B200_DTYPE_F16 || p->dtype == B200_DTYPE_BF16,
+               B200_ERR_UNSUPPORTED, "Unsupported data type of O: %d", p->dtype);
+  const int pack = 16 / dtype_bytes(p->dtype);
+  B200_REQUIRE(p->head_size % pack == 0, B200_ERR_UNSUPPORTED, "headsize must be multiple of pack_size:%d", pack);
+  B200_REQUIRE(p->epoch != 0, B200_ERR_INVALID_ARGUMENT, "dcp_exchange_fold: epoch 0 is the initial flag value");
+  B200_REQUIRE(p->peer_out && p->peer_lse && p->peer_flags && p->out, B200_ERR_INVALID_ARGUMENT, "NULL pointer");
+  DcpFoldArgs a{};
+  for (int r = 0; r < p->world; ++r) {
+    B200_REQUIRE(p->peer_out[r] && p->peer_lse[r] && p->peer_flags[r], B200_ERR_INVALID_ARGUMENT,
+                 "dcp_exchange_fold: NULL buffer of rank %d", r);
+    B200_REQUIRE((reinterpret_cast<uintptr_t>(p->peer_out[r]) & 15) == 0, B200_ERR_INVALID_ARGUMENT,
+                 "dcp_exchange_fold: partial of rank %d not 16-byte aligned", r);
+    a.peer_out[r] = p->peer_out[r];
+    a.peer_lse[r] = p->peer_lse[r];
+    a.peer_flags[r] = p->peer_flags[r];
+  }
+  B200_REQUIRE((reinterpret_cast<uintptr_t>(p->out) & 15) == 0, B200_ERR_INVALID_ARGUMENT, "out not 16-byte aligned");
+  a.out = p->out;
+  a.out_lse = p->out_lse;
+  a.rank = p->rank, a.world = p->world, a.num_seqs = p->num_seqs, a.heads_local = p->heads_local;
+  a.head_size = p->head_size, a.epoch = p->epoch;
+  const uint64_t total = (uint64_t)p->num_seqs * p->heads_local * (p->head_size / pack);
+  const int threads = 256;
+  // at least one CTA even for an empty batch: the peers wait for this rank's flag
+  const uint64_t blocks = total == 0 ? 1 : (total + threads - 1) / threads;
+  B200_REQUIRE(blocks <= 0x7fffffffull, B200_ERR_UNSUPPORTED, "dcp_exchange_fold: too many elements");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (p->dtype) {
+    case B200_DTYPE_F32: dcp_exchange_fold_kernel<float><<<(unsigned)blocks, threads, 0, s>>>(a); break;
+    case B200_DTYPE_F16: dcp_exchange_fold_kernel<__half><<<(unsigned)blocks, threads, 0, s>>>(a); break;
+    default: dcp_exchange_fold_kernel<__nv_bfloat16><<<(unsigned)blocks, threads, 0, s>>>(a); break;
+  }
+  count_launch();
+  return check_launch("dcp_exchange_fold");
+}
+
+// Peer-mappable device memory for the partial buffers: plain cudaMalloc (one allocation = one IPC handle, offset 0),
+// outside any caching allocator.
+extern "C" int b200_peer_alloc(uint64_t bytes, void** ptr, void* handle64) {
+  using namespace b200;
+  B200_REQUIRE(ptr != nullptr && handle64 != nullptr && bytes > 0, B200_ERR_INVALID_ARGUMENT, "peer_alloc: bad arguments");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle is 64 bytes");
+  void* d = nullptr;
+  cudaError_t e = cudaMalloc(&d, bytes);
+  B200_REQUIRE(e == cudaSuccess, B200_ERR_CUDA, "peer_alloc: cudaMalloc(%llu): %s", (unsigned long long)bytes, cudaGetErrorString(e));
+  e = cudaMemset(d, 0, bytes);
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(static_cast<cudaIpcMemHandle_t*>(handle64), d);
+  if (e != cudaSuccess) {
+    cudaFree(d);
+    B200_REQUIRE(false, B200_ERR_CUDA, "peer_alloc: %s", cudaGetErrorString(e));
+  }
+  *ptr = d;
+  return B200_OK;
+}
+
+extern "C" int b200_peer_open(const void* handle64, void** ptr) {
+  using namespace b200;
+  B200_REQUIRE(ptr != nullptr && handle64 != nullptr, B200_ERR_INVALID_ARGUMENT, "peer_open: bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  void* d = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&d, h, cudaIpcMemLazyEnablePeerAccess);
+  B200_REQUIRE(e == cudaSuccess, B200_ERR_CUDA, "peer_open: cudaIpcOpenMemHandle: %s", cudaGetErrorString(e));
+  *ptr = d;
+  return B200_OK;
+}
+
+extern "C" int b200_peer_close(void* ptr) {
+  using namespace b200;
+  if (ptr == nullptr) return B200_OK;
+  cudaError_t e = cudaIpcCloseMemHandle(ptr);
+  B200_REQUIRE(e == cudaSuccess, B200_ERR_CUDA, "peer_close: %s", cudaGetErrorString(e));
+  return B200_OK;
+}
+
+extern "C" int b200_peer_free(void* ptr) {
+  using namespace b200;
+  if (ptr == nullptr) return B200_OK;
+  cudaError_t e = cudaFree(ptr);
+  B200_REQUIRE(e == cudaSuccess, B200_ERR_CUDA, "peer_free: %s", cudaGetErrorString(e));
+  return B200_OK;
+}
