@@ -475,6 +475,35 @@ typedef struct b200_dcp_fold_params {
 } b200_dcp_fold_params_t;
 int b200_dcp_exchange_fold(const b200_dcp_fold_params_t* params, void* stream);
 
+/*
+ * Query all-gather of the DCP step over peer memory.  Replaces
+ * `get_dcp_group().all_gather(query, dim=1)`
+ * (vllm_metax/v1/attention/backends/flash_attn.py:812).  Stores this rank's
+ * query [num_seqs, heads_local, head_size] (q_stride elements between
+ * sequences, heads contiguous) into heads [rank*heads_local, ...) of every
+ * rank's gathered query peer_q[r] [num_seqs, world*heads_local, head_size],
+ * publishes `epoch` to flag[rank] of every peer and returns (on the stream)
+ * once every rank has published: the attention call that follows reads a whole
+ * gathered query.  peer_flags are arrays of `world` uint32 distinct from the
+ * fold's; cta_counter is one zero-initialised uint32 of local device memory.
+ * The gathered-query buffers alternate by epoch parity like the partials.
+ */
+typedef struct b200_dcp_gather_params {
+  void* const* peer_q;         /* [world] host array of device pointers */
+  uint32_t* const* peer_flags; /* [world] */
+  const void* query;
+  uint32_t* cta_counter;
+  int64_t q_stride;
+  int32_t rank;
+  int32_t world;
+  int32_t num_seqs;
+  int32_t heads_local;
+  int32_t head_size;
+  int32_t dtype;
+  uint32_t epoch;
+} b200_dcp_gather_params_t;
+int b200_dcp_gather_query(const b200_dcp_gather_params_t* params, void* stream);
+
 /* Peer-mappable device memory for the DCP buffers: one cudaMalloc (zero-filled)
  * and its 64-byte CUDA IPC handle; b200_peer_open maps a handle received from
  * another process of the same node (peer access enabled lazily) and returns a

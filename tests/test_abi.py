@@ -51,7 +51,8 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
                       ("b200_gather_cache_params_t", native.GatherCacheParams),
                       ("b200_rotary_params_t", native.RotaryParams),
                       ("b200_concat_mla_params_t", native.ConcatMlaParams),
-                      ("b200_dcp_fold_params_t", native.DcpFoldParams)):
+                      ("b200_dcp_fold_params_t", native.DcpFoldParams),
+                      ("b200_dcp_gather_params_t", native.DcpGatherParams)):
         prog.append('printf("%%zu\\n", sizeof(%s));' % cname)
         for f in fields(st):
             prog.append('printf("%%zu\\n", offsetof(%s, %s));' % (cname, f))
@@ -63,7 +64,8 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
     vals = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     it = iter(vals)
     for st in (native.PagedAttnParams, native.CacheWriteParams, native.MergeAttnStatesParams, native.GatherCacheParams,
-               native.RotaryParams, native.ConcatMlaParams, native.DcpFoldParams):
+               native.RotaryParams, native.ConcatMlaParams, native.DcpFoldParams,
+               native.DcpGatherParams):
         assert next(it) == C.sizeof(st)
         for f in fields(st):
             assert next(it) == getattr(st, f).offset, f
@@ -185,6 +187,13 @@ def test_dcp_exchange_fold_validates_on_the_host(native):
     with pytest.raises(native.B200Error, match="not 16-byte aligned"):
         native.dcp_exchange_fold([4104], [4096], [4096], out, None, 0, 2, 4, 128, 1, 0)
     assert native.DCP_MAX_WORLD == 16
+    q = torch.empty(2, 4, 128, dtype=torch.bfloat16)
+    with pytest.raises(native.B200Error, match="NULL buffer of rank 1"):
+        native.dcp_gather_query([4096, 0], [4096, 4096], q, 4096, 0, 1, 0)
+    with pytest.raises(native.B200Error, match="epoch 0"):
+        native.dcp_gather_query([4096], [4096], q, 4096, 0, 0, 0)
+    with pytest.raises(native.B200Error, match="NULL pointer"):
+        native.dcp_gather_query([4096], [4096], q, 0, 0, 1, 0)
 
 
 def test_workspace_sizing_is_host_only_and_monotone(native):

@@ -37,6 +37,7 @@ EXPORTED_SYMBOLS = (
     "b200_swap_blocks",
     "b200_gather_cache",
     "b200_dcp_exchange_fold",
+    "b200_dcp_gather_query",
     "b200_peer_alloc",
     "b200_peer_open",
     "b200_peer_close",
@@ -223,6 +224,23 @@ class DcpFoldParams(C.Structure):
     ]
 
 
+class DcpGatherParams(C.Structure):
+    _fields_ = [
+        ("peer_q", C.POINTER(C.c_void_p)),
+        ("peer_flags", C.POINTER(C.c_void_p)),
+        ("query", C.c_void_p),
+        ("cta_counter", C.c_void_p),
+        ("q_stride", C.c_int64),
+        ("rank", C.c_int32),
+        ("world", C.c_int32),
+        ("num_seqs", C.c_int32),
+        ("heads_local", C.c_int32),
+        ("head_size", C.c_int32),
+        ("dtype", C.c_int32),
+        ("epoch", C.c_uint32),
+    ]
+
+
 DCP_MAX_WORLD = 16
 COPY_D2D, COPY_D2H, COPY_H2D = 0, 1, 2
 
@@ -281,6 +299,8 @@ def load() -> C.CDLL:
     lib.b200_gather_cache.restype = C.c_int
     lib.b200_dcp_exchange_fold.argtypes = [P(DcpFoldParams), C.c_void_p]
     lib.b200_dcp_exchange_fold.restype = C.c_int
+    lib.b200_dcp_gather_query.argtypes = [P(DcpGatherParams), C.c_void_p]
+    lib.b200_dcp_gather_query.restype = C.c_int
     lib.b200_peer_alloc.argtypes = [C.c_uint64, P(C.c_void_p), C.c_void_p]
     lib.b200_peer_alloc.restype = C.c_int
     lib.b200_peer_open.argtypes = [C.c_void_p, P(C.c_void_p)]
@@ -491,3 +511,18 @@ def dcp_exchange_fold(peer_out, peer_lse, peer_flags, out, out_lse, rank, num_se
     p.dtype = _torch_dtype_code(out.dtype)
     p.epoch = epoch
     check(load().b200_dcp_exchange_fold(C.byref(p), C.c_void_p(stream)))
+
+
+def dcp_gather_query(peer_q, peer_flags, query, cta_counter: int, rank, epoch, stream: int) -> None:
+    """query [S, H_local, D] with contiguous heads; peer_q / peer_flags: `world` device addresses."""
+    world = len(peer_q)
+    arr = C.c_void_p * world
+    p = DcpGatherParams()
+    a_q, a_flags = arr(*peer_q), arr(*peer_flags)
+    p.peer_q, p.peer_flags = a_q, a_flags
+    p.query, p.cta_counter, p.q_stride = query.data_ptr(), cta_counter, query.stride(0)
+    p.rank, p.world = rank, world
+    p.num_seqs, p.heads_local, p.head_size = query.shape
+    p.dtype = _torch_dtype_code(query.dtype)
+    p.epoch = epoch
+    check(load().b200_dcp_gather_query(C.byref(p), C.c_void_p(stream)))

@@ -111,7 +111,8 @@ def _align256(n: int) -> int:
 
 
 class DcpExchange:
-    """DCP decode step with the exchange + combine fused into one kernel over peer memory (b200_dcp_exchange_fold).
+    """DCP decode step in three launches, no NCCL call on the data path: query gather by peer stores
+    (b200_dcp_gather_query), attention, exchange + combine over peer loads (b200_dcp_exchange_fold).
 
     Steps 3 and 4 of `forward_decode_dcp` — pack, all-to-all, N-1 merge launches — become ONE launch: the attention
     kernel writes its partial (out, lse) for all heads straight into a buffer that the peers have mapped through CUDA
@@ -136,8 +137,11 @@ class DcpExchange:
         self._esize = torch.empty((), dtype=dtype).element_size()
         self._out_bytes = _align256(max_seqs * num_heads_total * head_size * self._esize)
         self._lse_bytes = _align256(num_heads_total * max_seqs * 4)
-        self._half = self._out_bytes + self._lse_bytes
-        total = 2 * self._half + 256  # two partial buffers + the flag words
+        self._q_bytes = self._out_bytes  # the gathered query has the shape of the partial output
+        self._half = self._out_bytes + self._lse_bytes + self._q_bytes
+        # two (partial out, partial lse, gathered query) buffers + 256 bytes of control words:
+        # fold flags [16] at +0, gather flags [16] at +64, the gather kernel's CTA counter at +128
+        total = 2 * self._half + 256
         self._device = torch.device("cuda", torch.cuda.current_device())
         self._ptr, handle = native.peer_alloc(total)
         handles: list = [None] * self.world
@@ -172,19 +176,26 @@ class DcpExchange:
             raise ValueError("query %s %s does not fit the exchange buffers (max_seqs %d, heads %d, head_size %d, %s)"
                              % (tuple(query.shape), query.dtype, self.max_seqs, self.num_heads_total, self.head_size,
                                 self.dtype))
-        gathered = torch.empty((world * S, Hl, D), dtype=query.dtype, device=query.device)
-        dist.all_gather_into_tensor(gathered, query.contiguous(), group=self.group)
-        q_all = gathered.view(world, S, Hl, D).permute(1, 0, 2, 3).reshape(S, H, D)
+        stream = torch.cuda.current_stream(query.device).cuda_stream
         self._epoch += 1
         off = (self._epoch & 1) * self._half
+        ctl = 2 * self._half
+        # 1. every rank pushes its heads into every rank's gathered query and waits for the others' pushes
+        q_off = off + self._out_bytes + self._lse_bytes
+        if query.stride(1) != D or query.stride(2) != 1:
+            query = query.contiguous()
+        self._native.dcp_gather_query([b + q_off for b in self._bases], [b + ctl + 64 for b in self._bases], query,
+                                      self._ptr + ctl + 128, rank, self._epoch, stream)
+        q_all = self._local[q_off:q_off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
+        # 2. local attention, partial (out, lse) of all heads written into the peer-mapped buffer
         out_all = self._local[off:off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
         lse_all = self._local[off + self._out_bytes:off + self._out_bytes + H * S * 4].view(torch.float32).view(H, S)
         ops.paged_attention_flash(out_all, q_all, key_cache, value_cache, scale, block_table, local_seq_lens,
                                   max_local_seq_len, None, lse_all)
+        # 3 + 4. signal, wait, pull this rank's head slices from every peer and fold them
         out = torch.empty((S, Hl, D), dtype=query.dtype, device=query.device)
         lse = torch.empty((Hl, S), dtype=torch.float32, device=query.device)
         self._native.dcp_exchange_fold(
             [b + off for b in self._bases], [b + off + self._out_bytes for b in self._bases],
-            [b + 2 * self._half for b in self._bases], out, lse, rank, S, Hl, D, self._epoch,
-            torch.cuda.current_stream(query.device).cuda_stream)
+            [b + ctl for b in self._bases], out, lse, rank, S, Hl, D, self._epoch, stream)
         return out, lse

@@ -137,6 +137,58 @@ __global__ void __launch_bounds__(256) dcp_exchange_fold_kernel(const __grid_con
   if (a.out_lse != nullptr && pack == 0) a.out_lse[(uint64_t)hl * a.num_seqs + seq] = logf(se) + m;
 }
 
+// Query all-gather of the DCP step as pushes over peer memory: rank `rank` stores its [num_seqs, heads_local, head_size]
+// query slice into the gathered query [num_seqs, world*heads_local, head_size] of EVERY rank (its own included) at heads
+// [rank*heads_local, ...), then the last CTA to finish publishes `epoch` to the peers' flags and waits for theirs; when
+// the launch completes, this rank's gathered query is whole and the attention launch that follows on the stream may
+// read it.  Replaces `get_dcp_group().all_gather(query, dim=1)` (flash_attn.py:812) and the layout permute after it.
+struct DcpGatherArgs {
+  void* peer_q[B200_DCP_MAX_WORLD];
+  uint32_t* peer_flags[B200_DCP_MAX_WORLD];
+  const void* query;
+  uint32_t* cta_counter;
+  int64_t q_stride;  // elements between sequences of `query`
+  int32_t rank, world, num_seqs, heads_local, head_size;
+  uint32_t epoch;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) dcp_gather_query_kernel(const __grid_constant__ DcpGatherArgs a) {
+  constexpr int kPack = 16 / sizeof(T);
+  const uint32_t packs_per_seq = a.heads_local * a.head_size / kPack;  // the local heads of a sequence are contiguous
+  const uint64_t per_dest = (uint64_t)a.num_seqs * packs_per_seq;
+  const uint64_t total = per_dest * a.world;
+  const uint64_t row_all = (uint64_t)a.world * a.heads_local * a.head_size;
+  for (uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t dest = idx / per_dest;
+    const uint64_t rem = idx % per_dest;
+    const uint64_t seq = rem / packs_per_seq;
+    const uint32_t pk = rem % packs_per_seq;
+    const Vec16 v = *reinterpret_cast<const Vec16*>(reinterpret_cast<const T*>(a.query) + seq * a.q_stride + (uint64_t)pk * kPack);
+    T* dst = reinterpret_cast<T*>(a.peer_q[dest]) + seq * row_all + (uint64_t)a.rank * a.heads_local * a.head_size +
+             (uint64_t)pk * kPack;
+    *reinterpret_cast<Vec16*>(dst) = v;
+  }
+  __threadfence_system();
+  __syncthreads();
+  __shared__ bool last;
+  if (threadIdx.x == 0) {
+    const uint32_t prev = atomicAdd(a.cta_counter, 1u);
+    last = prev == gridDim.x - 1;
+    if (last) *a.cta_counter = 0;  // the next launch on this stream starts from zero
+  }
+  __syncthreads();
+  if (!last || threadIdx.x >= a.world) return;
+  __threadfence_system();
+  st_release_sys(a.peer_flags[threadIdx.x] + a.rank, a.epoch);
+  const uint32_t* f = a.peer_flags[a.rank] + threadIdx.x;
+  const uint64_t t0 = globaltimer_ns();
+  while ((int32_t)(ld_acquire_sys(f) - a.epoch) < 0) {
+    __nanosleep(64);
+    if (globaltimer_ns() - t0 > kWaitLimitNs) __trap();
+  }
+}
+
 }  // namespace
 }  // namespace b200
 
@@ -183,6 +235,50 @@ extern "C" int b200_dcp_exchange_fold(const b200_dcp_fold_params_t* p, void* str
   }
   count_launch();
   return check_launch("dcp_exchange_fold");
+}
+
+extern "C" int b200_dcp_gather_query(const b200_dcp_gather_params_t* p, void* stream) {
+  using namespace b200;
+  B200_REQUIRE(p != nullptr, B200_ERR_INVALID_ARGUMENT, "params is NULL");
+  B200_REQUIRE(p->world >= 1 && p->world <= B200_DCP_MAX_WORLD, B200_ERR_UNSUPPORTED,
+               "dcp_gather_query: world size %d outside 1..%d", p->world, B200_DCP_MAX_WORLD);
+  B200_REQUIRE(p->rank >= 0 && p->rank < p->world, B200_ERR_INVALID_ARGUMENT, "dcp_gather_query: rank %d of %d", p->rank,
+               p->world);
+  B200_REQUIRE(p->num_seqs >= 0 && p->heads_local > 0 && p->head_size > 0, B200_ERR_INVALID_ARGUMENT,
+               "bad sizes: seqs=%d heads_local=%d head_size=%d", p->num_seqs, p->heads_local, p->head_size);
+  B200_REQUIRE(p->dtype == B200_DTYPE_F32 || p->dtype == B200_DTYPE_F16 || p->dtype == B200_DTYPE_BF16,
+               B200_ERR_UNSUPPORTED, "Unsupported data type of Q: %d", p->dtype);
+  const int pack = 16 / dtype_bytes(p->dtype);
+  B200_REQUIRE(p->head_size % pack == 0, B200_ERR_UNSUPPORTED, "headsize must be multiple of pack_size:%d", pack);
+  B200_REQUIRE(p->epoch != 0, B200_ERR_INVALID_ARGUMENT, "dcp_gather_query: epoch 0 is the initial flag value");
+  B200_REQUIRE(p->peer_q && p->peer_flags && p->cta_counter && (p->query || p->num_seqs == 0), B200_ERR_INVALID_ARGUMENT,
+               "NULL pointer");
+  B200_REQUIRE(p->q_stride >= (int64_t)p->heads_local * p->head_size && p->q_stride % pack == 0 &&
+                   (reinterpret_cast<uintptr_t>(p->query) & 15) == 0,
+               B200_ERR_INVALID_ARGUMENT, "dcp_gather_query: query rows must be 16-byte aligned, heads contiguous");
+  DcpGatherArgs a{};
+  for (int r = 0; r < p->world; ++r) {
+    B200_REQUIRE(p->peer_q[r] && p->peer_flags[r], B200_ERR_INVALID_ARGUMENT, "dcp_gather_query: NULL buffer of rank %d", r);
+    B200_REQUIRE((reinterpret_cast<uintptr_t>(p->peer_q[r]) & 15) == 0, B200_ERR_INVALID_ARGUMENT,
+                 "dcp_gather_query: gathered query of rank %d not 16-byte aligned", r);
+    a.peer_q[r] = p->peer_q[r];
+    a.peer_flags[r] = p->peer_flags[r];
+  }
+  a.query = p->query, a.cta_counter = p->cta_counter, a.q_stride = p->q_stride;
+  a.rank = p->rank, a.world = p->world, a.num_seqs = p->num_seqs, a.heads_local = p->heads_local;
+  a.head_size = p->head_size, a.epoch = p->epoch;
+  const uint64_t total = (uint64_t)p->num_seqs * p->heads_local * (p->head_size / pack) * p->world;
+  const int threads = 256;
+  uint64_t blocks = (total + threads - 1) / threads;
+  blocks = blocks < 1 ? 1 : (blocks > 64 ? 64 : blocks);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (p->dtype) {
+    case B200_DTYPE_F32: dcp_gather_query_kernel<float><<<(unsigned)blocks, threads, 0, s>>>(a); break;
+    case B200_DTYPE_F16: dcp_gather_query_kernel<__half><<<(unsigned)blocks, threads, 0, s>>>(a); break;
+    default: dcp_gather_query_kernel<__nv_bfloat16><<<(unsigned)blocks, threads, 0, s>>>(a); break;
+  }
+  count_launch();
+  return check_launch("dcp_gather_query");
 }
 
 // Peer-mappable device memory for the partial buffers: plain cudaMalloc (one allocation = one IPC handle, offset 0),
