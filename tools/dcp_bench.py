@@ -73,6 +73,12 @@ def main():
     step = timed(lambda: dcp.forward_decode_dcp(q, kv[0], kv[1], table, lens, max_local, scale), a.iters)
     xch = dcp.DcpExchange(S, H, D, torch.bfloat16)
     fused = timed(lambda: xch.forward_decode(q, kv[0], kv[1], table, lens, max_local, scale), a.iters)
+    def fold_only():
+        xch._epoch += 1  # a fold of its own epoch over whatever the partial buffers hold
+        xch._fold(S, Hl, D, dev)
+
+    gather = timed(lambda: xch._gather(q), a.iters)
+    fold = timed(fold_only, a.iters)
     attend = timed(lambda: dcp._cuda_attend(q_all, kv[0], kv[1], scale, table, lens, max_local), a.iters)
     kv_bytes = 2 * S * a.ctx * Hkv * D * 2
     if rank == 0:
@@ -81,6 +87,7 @@ def main():
             "bench": "dcp_decode", "n_gpus": world, "seqs": S, "ctx": a.ctx, "heads": H, "kv_heads": Hkv,
             "step_us": round(step * 1e3, 1), "fused_step_us": round(fused * 1e3, 1),
             "fused_step_gbs": round(kv_bytes / fused / 1e6), "attend_us": round(attend * 1e3, 1),
+            "gather_launch_us": round(gather * 1e3, 1), "fold_launch_us": round(fold * 1e3, 1),
             "exchange_us": round((step - attend) * 1e3, 1),
             "step_gbs": round(kv_bytes / step / 1e6), "attend_gbs": round(kv_bytes / attend / 1e6),
             "kv_bytes_total": kv_bytes, "timing": "cuda events, median of %d, max over ranks" % a.iters}), flush=True)

@@ -176,26 +176,38 @@ class DcpExchange:
             raise ValueError("query %s %s does not fit the exchange buffers (max_seqs %d, heads %d, head_size %d, %s)"
                              % (tuple(query.shape), query.dtype, self.max_seqs, self.num_heads_total, self.head_size,
                                 self.dtype))
-        stream = torch.cuda.current_stream(query.device).cuda_stream
-        self._epoch += 1
-        off = (self._epoch & 1) * self._half
-        ctl = 2 * self._half
-        # 1. every rank pushes its heads into every rank's gathered query and waits for the others' pushes
-        q_off = off + self._out_bytes + self._lse_bytes
-        if query.stride(1) != D or query.stride(2) != 1:
-            query = query.contiguous()
-        self._native.dcp_gather_query([b + q_off for b in self._bases], [b + ctl + 64 for b in self._bases], query,
-                                      self._ptr + ctl + 128, rank, self._epoch, stream)
-        q_all = self._local[q_off:q_off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
+        q_all = self._gather(query)
         # 2. local attention, partial (out, lse) of all heads written into the peer-mapped buffer
+        off = (self._epoch & 1) * self._half
         out_all = self._local[off:off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
         lse_all = self._local[off + self._out_bytes:off + self._out_bytes + H * S * 4].view(torch.float32).view(H, S)
         ops.paged_attention_flash(out_all, q_all, key_cache, value_cache, scale, block_table, local_seq_lens,
                                   max_local_seq_len, None, lse_all)
-        # 3 + 4. signal, wait, pull this rank's head slices from every peer and fold them
-        out = torch.empty((S, Hl, D), dtype=query.dtype, device=query.device)
-        lse = torch.empty((Hl, S), dtype=torch.float32, device=query.device)
+        return self._fold(S, Hl, D, query.device)
+
+    def _gather(self, query: torch.Tensor) -> torch.Tensor:
+        """Step 1 (starts a new epoch): every rank pushes its heads into every rank's gathered query and waits for the
+        others' pushes.  Returns this rank's gathered query [S, H, D] (a view of the exchange buffer)."""
+        S, Hl, D = query.shape
+        H = Hl * self.world
+        self._epoch += 1
+        ctl = 2 * self._half
+        q_off = (self._epoch & 1) * self._half + self._out_bytes + self._lse_bytes
+        if query.stride(1) != D or query.stride(2) != 1:
+            query = query.contiguous()
+        self._native.dcp_gather_query([b + q_off for b in self._bases], [b + ctl + 64 for b in self._bases], query,
+                                      self._ptr + ctl + 128, self.rank, self._epoch,
+                                      torch.cuda.current_stream(query.device).cuda_stream)
+        return self._local[q_off:q_off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
+
+    def _fold(self, S: int, Hl: int, D: int, device) -> tuple[torch.Tensor, torch.Tensor]:
+        """Steps 3 + 4 of the current epoch: signal, wait, pull this rank's head slices from every peer and fold them."""
+        off = (self._epoch & 1) * self._half
+        ctl = 2 * self._half
+        out = torch.empty((S, Hl, D), dtype=self.dtype, device=device)
+        lse = torch.empty((Hl, S), dtype=torch.float32, device=device)
         self._native.dcp_exchange_fold(
             [b + off for b in self._bases], [b + off + self._out_bytes for b in self._bases],
-            [b + ctl for b in self._bases], out, lse, rank, S, Hl, D, self._epoch, stream)
+            [b + ctl for b in self._bases], out, lse, self.rank, S, Hl, D, self._epoch,
+            torch.cuda.current_stream(device).cuda_stream)
         return out, lse
