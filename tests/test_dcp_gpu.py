@@ -52,6 +52,57 @@ def test_dcp_kernels_one_gpu(world):
     del ops
 
 
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_dcp_peer_kernels_with_emulated_peers(world):
+    """b200_dcp_gather_query / b200_dcp_exchange_fold at world > 1 on ONE GPU: the `world` peers' buffers are distinct
+    local allocations and the launches of the ranks run one after the other, with the arrival flags preset (5) above the
+    epoch (3) so that no launch waits for a rank that has not run yet.  Checks the addressing of the pushes and pulls,
+    the N-way fold against attention over the unsharded sequences, and where each rank's signal lands."""
+    from vllm_metax_b200 import _native as native
+    from vllm_metax_b200.attention.dcp import _cuda_attend
+
+    dev = torch.device("cuda", 0)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    H = 4 * world
+    Hl = H // world
+    d = make_problem(S=6, H=H, Hkv=2, D=128, L=500)
+    S, D = d["query"].shape[0], 128
+    epoch, preset = 3, 5
+
+    # gather: every rank pushes its head slice into every rank's gathered query
+    qbuf = [torch.zeros(S, H, D, dtype=torch.bfloat16, device=dev) for _ in range(world)]
+    gflags = torch.full((world, 16), preset, dtype=torch.int32, device=dev)
+    counter = torch.zeros(1, dtype=torch.int32, device=dev)
+    for r in range(world):
+        q_local = d["query"][:, r * Hl:(r + 1) * Hl].contiguous().to(dev)
+        native.dcp_gather_query([b.data_ptr() for b in qbuf], [gflags[t].data_ptr() for t in range(world)], q_local,
+                                counter.data_ptr(), r, epoch, stream)
+    torch.cuda.synchronize()
+    for b in qbuf:
+        assert torch.equal(b.cpu(), d["query"])
+    assert counter.item() == 0
+    assert (gflags[:, :world] == epoch).all() and (gflags[:, world:] == preset).all()
+
+    # partial attention of every rank over its token shard, all heads
+    partial = []
+    for r in range(world):
+        lk, lv, table, lens = shard_for_rank(d, world, r)
+        partial.append(_cuda_attend(qbuf[r], lk.to(dev), lv.to(dev), d["scale"], table.to(dev), lens.to(dev), int(lens.max())))
+    full, full_lse = _full(d)
+
+    # exchange + fold of every rank
+    fflags = torch.full((world, 16), preset, dtype=torch.int32, device=dev)
+    for r in range(world):
+        out = torch.empty(S, Hl, D, dtype=torch.bfloat16, device=dev)
+        lse = torch.empty(Hl, S, dtype=torch.float32, device=dev)
+        native.dcp_exchange_fold([o.data_ptr() for o, _ in partial], [l.data_ptr() for _, l in partial],
+                                 [fflags[t].data_ptr() for t in range(world)], out, lse, r, S, Hl, D, epoch, stream)
+        torch.cuda.synchronize()
+        assert (out.float().cpu() - full[:, r * Hl:(r + 1) * Hl]).abs().max().item() <= 2 * TOL
+        assert (lse.cpu() - full_lse[r * Hl:(r + 1) * Hl]).abs().max().item() <= TOL
+        assert (fflags[:, r] == epoch).all()
+
+
 def _free_port() -> int:
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
