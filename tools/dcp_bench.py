@@ -9,6 +9,8 @@ Timed with CUDA events on the current stream, max over ranks, median of --iters 
   step    = forward_decode_dcp (query all-gather, attention with LSE, pack, all-to-all, merge fold)
   fused   = DcpExchange.forward_decode (query all-gather, attention with LSE into peer-mapped memory, one
             exchange + fold launch over NVLink peer loads)
+  gather_launch / fold_launch = back-to-back launches of b200_dcp_gather_query / b200_dcp_exchange_fold alone; at these
+            sizes the interval is the HOST's issue time per launch (python + ctypes), an upper bound on the kernel
   attend  = the attention launch alone on the gathered query (what the step would cost with a free exchange)
 GB/s = the KV bytes of the WHOLE problem (all ranks) / time, comparable with the 1-GPU number of the same problem."""
 import argparse

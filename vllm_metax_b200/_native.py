@@ -497,32 +497,52 @@ def peer_free(ptr: int) -> None:
     check(load().b200_peer_free(C.c_void_p(ptr)))
 
 
-def dcp_exchange_fold(peer_out, peer_lse, peer_flags, out, out_lse, rank, num_seqs, heads_local, head_size, epoch,
-                      stream: int) -> None:
-    """peer_out / peer_lse / peer_flags: sequences of `world` device addresses (ints)."""
+def dcp_fold_params(peer_out, peer_lse, peer_flags, rank, num_seqs, heads_local, head_size, dtype) -> DcpFoldParams:
+    """Everything of a fold launch that does not change from step to step (peer_*: `world` device addresses)."""
     world = len(peer_out)
     arr = C.c_void_p * world
     p = DcpFoldParams()
-    a_out, a_lse, a_flags = arr(*peer_out), arr(*peer_lse), arr(*peer_flags)
-    p.peer_out, p.peer_lse, p.peer_flags = a_out, a_lse, a_flags
+    p._keep = (arr(*peer_out), arr(*peer_lse), arr(*peer_flags))  # the struct only holds their addresses
+    p.peer_out, p.peer_lse, p.peer_flags = p._keep
+    p.rank, p.world, p.num_seqs, p.heads_local, p.head_size = rank, world, num_seqs, heads_local, head_size
+    p.dtype = _torch_dtype_code(dtype)
+    return p
+
+
+def dcp_fold_launch(p: DcpFoldParams, out, out_lse, epoch: int, stream: int) -> None:
     p.out = out.data_ptr()
     p.out_lse = out_lse.data_ptr() if out_lse is not None else None
-    p.rank, p.world, p.num_seqs, p.heads_local, p.head_size = rank, world, num_seqs, heads_local, head_size
-    p.dtype = _torch_dtype_code(out.dtype)
     p.epoch = epoch
     check(load().b200_dcp_exchange_fold(C.byref(p), C.c_void_p(stream)))
 
 
-def dcp_gather_query(peer_q, peer_flags, query, cta_counter: int, rank, epoch, stream: int) -> None:
-    """query [S, H_local, D] with contiguous heads; peer_q / peer_flags: `world` device addresses."""
+def dcp_exchange_fold(peer_out, peer_lse, peer_flags, out, out_lse, rank, num_seqs, heads_local, head_size, epoch,
+                      stream: int) -> None:
+    """peer_out / peer_lse / peer_flags: sequences of `world` device addresses (ints)."""
+    p = dcp_fold_params(peer_out, peer_lse, peer_flags, rank, num_seqs, heads_local, head_size, out.dtype)
+    dcp_fold_launch(p, out, out_lse, epoch, stream)
+
+
+def dcp_gather_params(peer_q, peer_flags, cta_counter: int, rank, num_seqs, heads_local, head_size,
+                      dtype) -> DcpGatherParams:
     world = len(peer_q)
     arr = C.c_void_p * world
     p = DcpGatherParams()
-    a_q, a_flags = arr(*peer_q), arr(*peer_flags)
-    p.peer_q, p.peer_flags = a_q, a_flags
-    p.query, p.cta_counter, p.q_stride = query.data_ptr(), cta_counter, query.stride(0)
-    p.rank, p.world = rank, world
-    p.num_seqs, p.heads_local, p.head_size = query.shape
-    p.dtype = _torch_dtype_code(query.dtype)
-    p.epoch = epoch
+    p._keep = (arr(*peer_q), arr(*peer_flags))
+    p.peer_q, p.peer_flags = p._keep
+    p.cta_counter = cta_counter
+    p.rank, p.world, p.num_seqs, p.heads_local, p.head_size = rank, world, num_seqs, heads_local, head_size
+    p.dtype = _torch_dtype_code(dtype)
+    return p
+
+
+def dcp_gather_launch(p: DcpGatherParams, query, epoch: int, stream: int) -> None:
+    p.query, p.q_stride, p.epoch = query.data_ptr(), query.stride(0), epoch
     check(load().b200_dcp_gather_query(C.byref(p), C.c_void_p(stream)))
+
+
+def dcp_gather_query(peer_q, peer_flags, query, cta_counter: int, rank, epoch, stream: int) -> None:
+    """query [S, H_local, D] with contiguous heads; peer_q / peer_flags: `world` device addresses."""
+    S, Hl, D = query.shape
+    p = dcp_gather_params(peer_q, peer_flags, cta_counter, rank, S, Hl, D, query.dtype)
+    dcp_gather_launch(p, query, epoch, stream)

@@ -106,6 +106,10 @@ class _DeviceBytes:
                                          "strides": None}
 
 
+class _Plan:
+    __slots__ = ("q_all", "out_all", "lse_all", "gather", "fold")
+
+
 def _align256(n: int) -> int:
     return (n + 255) // 256 * 256
 
@@ -149,6 +153,7 @@ class DcpExchange:
         self._bases = [self._ptr if r == self.rank else native.peer_open(handles[r]) for r in range(self.world)]
         self._local = torch.as_tensor(_DeviceBytes(self._ptr, total), device=self._device)
         self._epoch = 0
+        self._plans: dict[int, list[_Plan]] = {}
         dist.barrier(group=group)  # every flag array is zeroed and mapped before the first signal
 
     def close(self) -> None:
@@ -162,6 +167,7 @@ class DcpExchange:
         self._native.peer_free(self._ptr)
         self._bases = None
         self._local = None
+        self._plans = {}
 
     def forward_decode(self, query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
                        block_table: torch.Tensor, local_seq_lens: torch.Tensor, max_local_seq_len: int,
@@ -178,36 +184,51 @@ class DcpExchange:
                                 self.dtype))
         q_all = self._gather(query)
         # 2. local attention, partial (out, lse) of all heads written into the peer-mapped buffer
-        off = (self._epoch & 1) * self._half
-        out_all = self._local[off:off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
-        lse_all = self._local[off + self._out_bytes:off + self._out_bytes + H * S * 4].view(torch.float32).view(H, S)
-        ops.paged_attention_flash(out_all, q_all, key_cache, value_cache, scale, block_table, local_seq_lens,
-                                  max_local_seq_len, None, lse_all)
+        plan = self._plan(S, Hl, D)[self._epoch & 1]
+        ops.paged_attention_flash(plan.out_all, q_all, key_cache, value_cache, scale, block_table, local_seq_lens,
+                                  max_local_seq_len, None, plan.lse_all)
         return self._fold(S, Hl, D, query.device)
+
+    def _plan(self, S: int, Hl: int, D: int):
+        """Per batch size, for both parities: the views of the exchange buffer and the launch parameters that do not
+        change from step to step (built once; a decode step then only fills in pointers and the epoch)."""
+        plans = self._plans.get(S)
+        if plans is None:
+            native, H, ctl = self._native, Hl * self.world, 2 * self._half
+            plans = []
+            for par in (0, 1):
+                off = par * self._half
+                lse_off = off + self._out_bytes
+                q_off = lse_off + self._lse_bytes
+                plan = _Plan()
+                plan.q_all = self._local[q_off:q_off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
+                plan.out_all = self._local[off:off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
+                plan.lse_all = self._local[lse_off:lse_off + H * S * 4].view(torch.float32).view(H, S)
+                plan.gather = native.dcp_gather_params([b + q_off for b in self._bases],
+                                                       [b + ctl + 64 for b in self._bases], self._ptr + ctl + 128,
+                                                       self.rank, S, Hl, D, self.dtype)
+                plan.fold = native.dcp_fold_params([b + off for b in self._bases], [b + lse_off for b in self._bases],
+                                                   [b + ctl for b in self._bases], self.rank, S, Hl, D, self.dtype)
+                plans.append(plan)
+            self._plans[S] = plans
+        return plans
 
     def _gather(self, query: torch.Tensor) -> torch.Tensor:
         """Step 1 (starts a new epoch): every rank pushes its heads into every rank's gathered query and waits for the
         others' pushes.  Returns this rank's gathered query [S, H, D] (a view of the exchange buffer)."""
         S, Hl, D = query.shape
-        H = Hl * self.world
         self._epoch += 1
-        ctl = 2 * self._half
-        q_off = (self._epoch & 1) * self._half + self._out_bytes + self._lse_bytes
+        plan = self._plan(S, Hl, D)[self._epoch & 1]
         if query.stride(1) != D or query.stride(2) != 1:
             query = query.contiguous()
-        self._native.dcp_gather_query([b + q_off for b in self._bases], [b + ctl + 64 for b in self._bases], query,
-                                      self._ptr + ctl + 128, self.rank, self._epoch,
-                                      torch.cuda.current_stream(query.device).cuda_stream)
-        return self._local[q_off:q_off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
+        self._native.dcp_gather_launch(plan.gather, query, self._epoch,
+                                       torch.cuda.current_stream(query.device).cuda_stream)
+        return plan.q_all
 
     def _fold(self, S: int, Hl: int, D: int, device) -> tuple[torch.Tensor, torch.Tensor]:
         """Steps 3 + 4 of the current epoch: signal, wait, pull this rank's head slices from every peer and fold them."""
-        off = (self._epoch & 1) * self._half
-        ctl = 2 * self._half
+        plan = self._plan(S, Hl, D)[self._epoch & 1]
         out = torch.empty((S, Hl, D), dtype=self.dtype, device=device)
         lse = torch.empty((Hl, S), dtype=torch.float32, device=device)
-        self._native.dcp_exchange_fold(
-            [b + off for b in self._bases], [b + off + self._out_bytes for b in self._bases],
-            [b + ctl for b in self._bases], out, lse, self.rank, S, Hl, D, self._epoch,
-            torch.cuda.current_stream(device).cuda_stream)
+        self._native.dcp_fold_launch(plan.fold, out, lse, self._epoch, torch.cuda.current_stream(device).cuda_stream)
         return out, lse

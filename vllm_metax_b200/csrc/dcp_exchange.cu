@@ -71,10 +71,9 @@ template <typename T>
 __global__ void __launch_bounds__(256) dcp_exchange_fold_kernel(const __grid_constant__ DcpFoldArgs a) {
   constexpr int kPack = 16 / sizeof(T);
   // 1. publish (one CTA; every CTA of this launch is past the producing attention launch)
-  if (blockIdx.x == 0 && threadIdx.x < a.world) {
-    __threadfence_system();
-    st_release_sys(a.peer_flags[threadIdx.x] + a.rank, a.epoch);
-  }
+  // (st.release.sys orders the partial — written by the previous launch on this stream — before the flag; a separate
+  // membar.sys per thread on top of it cost ~10 us per launch in the first version)
+  if (blockIdx.x == 0 && threadIdx.x < a.world) st_release_sys(a.peer_flags[threadIdx.x] + a.rank, a.epoch);
   // 2. wait for every rank's partial
   if (threadIdx.x < a.world) {
     const uint32_t* f = a.peer_flags[a.rank] + threadIdx.x;
@@ -169,17 +168,18 @@ __global__ void __launch_bounds__(256) dcp_gather_query_kernel(const __grid_cons
              (uint64_t)pk * kPack;
     *reinterpret_cast<Vec16*>(dst) = v;
   }
-  __threadfence_system();
+  // One system fence per CTA, by the thread that counts the CTA in: the barrier orders every thread's stores before
+  // it (fences are cumulative), and the flag stores below are releases at system scope.
   __syncthreads();
   __shared__ bool last;
   if (threadIdx.x == 0) {
+    asm volatile("fence.acq_rel.sys;" ::: "memory");
     const uint32_t prev = atomicAdd(a.cta_counter, 1u);
     last = prev == gridDim.x - 1;
     if (last) *a.cta_counter = 0;  // the next launch on this stream starts from zero
   }
   __syncthreads();
   if (!last || threadIdx.x >= a.world) return;
-  __threadfence_system();
   st_release_sys(a.peer_flags[threadIdx.x] + a.rank, a.epoch);
   const uint32_t* f = a.peer_flags[a.rank] + threadIdx.x;
   const uint64_t t0 = globaltimer_ns();
