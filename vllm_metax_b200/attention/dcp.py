@@ -175,9 +175,8 @@ class DcpExchange:
         """Same contract as `forward_decode_dcp`: (out [S, H_local, D], lse [H_local, S])."""
         from .. import _custom_ops as ops
 
-        world, rank = self.world, self.rank
         S, Hl, D = query.shape
-        H = Hl * world
+        H = Hl * self.world
         if H != self.num_heads_total or D != self.head_size or query.dtype != self.dtype or S > self.max_seqs:
             raise ValueError("query %s %s does not fit the exchange buffers (max_seqs %d, heads %d, head_size %d, %s)"
                              % (tuple(query.shape), query.dtype, self.max_seqs, self.num_heads_total, self.head_size,
