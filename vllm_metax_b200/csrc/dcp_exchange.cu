@@ -291,6 +291,7 @@ extern "C" int b200_peer_alloc(uint64_t bytes, void** ptr, void* handle64) {
   cudaError_t e = cudaMalloc(&d, bytes);
   B200_REQUIRE(e == cudaSuccess, B200_ERR_CUDA, "peer_alloc: cudaMalloc(%llu): %s", (unsigned long long)bytes, cudaGetErrorString(e));
   e = cudaMemset(d, 0, bytes);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();  // the zeroes are in place before any stream or peer touches the flags
   if (e == cudaSuccess) e = cudaIpcGetMemHandle(static_cast<cudaIpcMemHandle_t*>(handle64), d);
   if (e != cudaSuccess) {
     cudaFree(d);
