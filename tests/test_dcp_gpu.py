@@ -89,6 +89,8 @@ def test_dcp_peer_kernels_with_emulated_peers(world):
         lk, lv, table, lens = shard_for_rank(d, world, r)
         partial.append(_cuda_attend(qbuf[r], lk.to(dev), lv.to(dev), d["scale"], table.to(dev), lens.to(dev), int(lens.max())))
     full, full_lse = _full(d)
+    # the fold kernel against the oracle's N-way fold of the SAME partials: fp32 arithmetic, one bf16 rounding
+    ref_out, ref_lse = orc.fold_attn_partials([o.cpu() for o, _ in partial], [l.cpu() for _, l in partial])
 
     # exchange + fold of every rank
     fflags = torch.full((world, 16), preset, dtype=torch.int32, device=dev)
@@ -100,6 +102,8 @@ def test_dcp_peer_kernels_with_emulated_peers(world):
         torch.cuda.synchronize()
         assert (out.float().cpu() - full[:, r * Hl:(r + 1) * Hl]).abs().max().item() <= 2 * TOL
         assert (lse.cpu() - full_lse[r * Hl:(r + 1) * Hl]).abs().max().item() <= TOL
+        assert (out.float().cpu() - ref_out[:, r * Hl:(r + 1) * Hl].float()).abs().max().item() <= 2 ** -8  # <= 1 bf16 ulp below 1.0
+        assert (lse.cpu() - ref_lse[r * Hl:(r + 1) * Hl]).abs().max().item() <= 1e-5
         assert (fflags[:, r] == epoch).all()
 
 

@@ -28,6 +28,29 @@ def test_local_seq_lens_match_token_ownership():
             assert torch.equal(dcp_local_seq_lens(lens, world, r), counts[r])
 
 
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_fold_of_token_shards_is_attention_over_the_whole_sequence(world):
+    """The N-way combination rule (what b200_dcp_exchange_fold computes) on the oracle: per-rank attention over the
+    token shards, folded at once, equals attention over the unsharded sequences and equals the chain of pairwise
+    merge_attn_states calls; a rank without tokens of a sequence (lse -inf) contributes nothing."""
+    d = make_problem(S=4, H=8, Hkv=2, D=64, L=90, dtype=torch.float32)
+    outs, lses = [], []
+    for r in range(world):
+        lk, lv, table, lens = shard_for_rank(d, world, r)
+        outs.append(orc.paged_attention_flash(d["query"], lk, lv, table, lens, d["scale"]))
+        lses.append(orc.paged_attention_flash_lse(d["query"], lk, lv, table, lens, d["scale"]))
+    assert torch.isneginf(lses[-1][:, 0]).all()  # sequence 0 has one token: only rank 0 holds it
+    out, lse = orc.fold_attn_partials(outs, lses)
+    full = orc.paged_attention_flash(d["query"], d["key_cache"], d["value_cache"], d["block_tables"], d["seq_lens"], d["scale"])
+    full_lse = orc.paged_attention_flash_lse(d["query"], d["key_cache"], d["value_cache"], d["block_tables"],
+                                             d["seq_lens"], d["scale"])
+    assert (out - full).abs().max().item() <= 1e-5 and (lse - full_lse).abs().max().item() <= 1e-5
+    co, cl = outs[0], lses[0]
+    for r in range(1, world):
+        co, cl = orc.merge_attn_states(co, cl, outs[r], lses[r])
+    assert (out - co).abs().max().item() <= 1e-5 and (lse - cl).abs().max().item() <= 1e-5
+
+
 def _free_port() -> int:
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
