@@ -183,6 +183,13 @@ int b200_paged_attention_flash(const b200_paged_attn_params_t* params, void* str
  * fields of params are ignored).  Host-only, no CUDA call. */
 uint64_t b200_paged_attention_workspace_bytes(const b200_paged_attn_params_t* params);
 
+/* Re-zero the arrival counters at the head of a v1 / flash workspace (enqueued on `stream`; graph-capturable).
+ * Never needed after launches that completed (each leaves the counters at zero).  It exists for hosts that recycle a
+ * workspace from an unknown state (a pool, or a buffer some other code wrote into).  Note that a launch that
+ * FAULTED cannot poison later calls through the workspace: a device fault is a sticky context error, after which no
+ * call on that context runs at all.  No reference counterpart (the reference's v1 never splits). */
+int b200_paged_attention_workspace_reset(void* workspace, uint64_t workspace_bytes, void* stream);
+
 /*
  * Arguments of reshape_and_cache / reshape_and_cache_flash.
  *   reference ops : csrc/torch_bindings.cpp:394-400, :403-411

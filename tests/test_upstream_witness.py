@@ -1,0 +1,224 @@
+"""FP8 bytes pinned to something outside this repository (VERDICT r1 "missing" #4 / "weak" #1).
+
+tests/golden/fp8_upstream_{convert,cache,attn}.pt were recorded on a B200 by tools/upstream_witness.py from UPSTREAM vLLM
+0.22.0's compiled kernels (`vllm/_C.abi3.so`: the same SIMT algorithm as the reference's csrc/ with the real
+`__nv_cvt_float_to_fp8` FP8 path the MetaX fork stubs out, csrc/quantization/fp8/metax/quant_utils.cuh:13-23).  The
+inputs are regenerated here from tests/golden/witness_inputs.py; only upstream's OUTPUTS are stored.
+
+  CPU  (-m "not gpu")  the oracle's FP8 definition (oracle/torch_oracle.py, oracle/e4m3_np.py, the C restatement) against
+                       upstream's bytes: every bf16 and f16 bit pattern and the fp32 rounding-boundary set at six scales,
+                       the dequantisation of every e4m3 code, the cache writers' bytes; the attention oracle against
+                       upstream's paged_attention_v1/v2 outputs.
+  GPU  (-m gpu)        this repository's kernels against the same bytes / outputs.
+"""
+import os
+import sys
+
+import pytest
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN = os.path.join(HERE, "golden")
+sys.path.insert(0, GOLDEN)
+
+import witness_inputs as wi  # noqa: E402
+from oracle import torch_oracle as orc  # noqa: E402
+
+
+def _load(name):
+    path = os.path.join(GOLDEN, "fp8_upstream_%s.pt" % name)
+    if not os.path.exists(path):
+        pytest.skip("no upstream witness recorded (%s)" % os.path.basename(path))
+    return torch.load(path, map_location="cpu")
+
+
+def _finite_mask(src):
+    return torch.isfinite(src.float())
+
+
+QUANT_SOURCES = {"bf16": wi.all_bf16_patterns, "f16": wi.all_f16_patterns, "f32": wi.tricky_f32}
+
+
+# ---- CPU: the oracle against upstream --------------------------------------------------------------------------
+@pytest.mark.parametrize("src_name", sorted(QUANT_SOURCES))
+def test_oracle_quant_bytes_match_upstream(src_name):
+    rec = _load("convert")
+    src = QUANT_SOURCES[src_name]()
+    fin = _finite_mask(src)
+    for sc in wi.QUANT_SCALES:
+        up = rec["quant_%s_%r" % (src_name, sc)]
+        mine = orc.fp8_e4m3_quant(src, sc)
+        assert torch.equal(mine[fin], up[fin]), (src_name, sc, int((mine[fin] != up[fin]).sum()))
+
+
+def test_oracle_quant_bytes_match_upstream_scaled_boundaries():
+    """x = boundary * scale (and its fp32 neighbours): separates an IEEE divide from a multiply by the reciprocal."""
+    rec = _load("convert")
+    for sc in wi.QUANT_SCALES:
+        src = wi.tricky_f32_scaled(sc)
+        fin = _finite_mask(src)
+        up = rec["quant_f32_scaled_%r" % sc]
+        mine = orc.fp8_e4m3_quant(src, sc)
+        assert torch.equal(mine[fin], up[fin]), (sc, int((mine[fin] != up[fin]).sum()))
+
+
+def test_independent_encoders_match_upstream():
+    """The integer encoder (oracle/e4m3_np.py) and the C restatement against upstream on the fp32 boundary set."""
+    import numpy as np
+
+    from oracle import c_oracle, e4m3_np
+
+    rec = _load("convert")
+    for sc in (1.0, 0.0123, 3.7):
+        src = wi.tricky_f32_scaled(sc)
+        fin = _finite_mask(src)
+        up = rec["quant_f32_scaled_%r" % sc]
+        x = src.numpy().astype(np.float32) / np.float32(sc)
+        enc = torch.from_numpy(e4m3_np.encode(x.reshape(-1)).reshape(src.shape))
+        assert torch.equal(enc[fin], up[fin]), sc
+        dst = torch.zeros(src.shape, dtype=torch.uint8)
+        c_oracle.convert_fp8(dst, src.contiguous(), sc)
+        assert torch.equal(dst[fin], up[fin]), sc
+
+
+@pytest.mark.parametrize("dname,dt", [("bf16", torch.bfloat16), ("f16", torch.float16), ("f32", torch.float32)])
+def test_oracle_dequant_matches_upstream(dname, dt):
+    rec = _load("convert")
+    codes = wi.all_bytes()
+    ok = (codes & 0x7F) != 0x7F  # the two NaN codes
+    for sc in wi.DEQUANT_SCALES:
+        up = rec["dequant_%s_%r" % (dname, sc)]
+        mine = orc.fp8_e4m3_dequant(codes, sc, dt)
+        assert torch.equal(mine[ok].view(torch.uint8 if dt != torch.float32 else torch.int32).flatten(),
+                           up[ok].view(torch.uint8 if dt != torch.float32 else torch.int32).flatten()), (dname, sc)
+
+
+def _oracle_cache(name, flash):
+    c = wi.cache_case(name)
+    if flash:
+        kc = torch.zeros(c["NB"], c["B"], c["Hkv"], c["D"], dtype=torch.uint8)
+        vc = torch.zeros_like(kc)
+        orc.reshape_and_cache_flash(c["key"], c["value"], kc, vc, c["slot_mapping"], "fp8", torch.tensor(c["k_scale"]),
+                                    torch.tensor(c["v_scale"]))
+    else:
+        kc = torch.zeros(c["NB"], c["Hkv"], c["D"] // 16, c["B"], 16, dtype=torch.uint8)
+        vc = torch.zeros(c["NB"], c["Hkv"], c["D"], c["B"], dtype=torch.uint8)
+        orc.reshape_and_cache(c["key"], c["value"], kc, vc, c["slot_mapping"], "fp8", torch.tensor(c["k_scale"]),
+                              torch.tensor(c["v_scale"]))
+    return kc, vc
+
+
+@pytest.mark.parametrize("name", wi.CACHE_CASES_V1 + wi.CACHE_CASES_FLASH)
+def test_oracle_cache_bytes_match_upstream(name):
+    rec = _load("cache")
+    kc, vc = _oracle_cache(name, name in wi.CACHE_CASES_FLASH)
+    assert torch.equal(kc, rec[name]["key_cache"]) and torch.equal(vc, rec[name]["value_cache"])
+
+
+def test_oracle_mla_cache_bytes_match_upstream():
+    rec = _load("cache")
+    if "mla" not in rec:
+        pytest.skip("upstream concat_and_cache_mla witness not recorded: %s" % rec.get("mla_error"))
+    m = wi.mla_case()
+    cache = torch.zeros(m["NB"], m["B"], m["LORA"] + m["ROPE"], dtype=torch.uint8)
+    orc.concat_and_cache_mla(m["kv_c"], m["k_pe"], cache, m["slot_mapping"], "fp8", torch.tensor(m["scale"]))
+    assert torch.equal(cache, rec["mla"]["kv_cache"])
+
+
+@pytest.mark.parametrize("name", sorted(wi.ATTN_CASES))
+def test_oracle_attention_matches_upstream(name):
+    """Upstream's SIMT kernels and the oracle are two implementations of the reference algorithm; the reference's own
+    tolerance between kernel and oracle is atol 1e-3 (auto) / 1e-2 (fp8) (tests/kernels/attention/test_attention.py:342-345).
+    Both are held to the tighter 2e-3 here."""
+    rec = _load("attn")
+    c = wi.attn_case(name)
+    ref = orc.paged_attention(c["query"], c["key_cache"], c["value_cache"], c["block_tables"], c["seq_lens"], c["scale"], None,
+                              c["kv"], c["k_scale"], c["v_scale"])
+    for v in ("v1", "v2"):
+        err = (rec[name][v].float() - ref.float()).abs().max().item()
+        assert err <= 2e-3, (name, v, err)
+
+
+# ---- GPU: this repository's kernels against upstream ---------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("src_name", sorted(QUANT_SOURCES))
+def test_kernel_quant_bytes_match_upstream(ops, src_name):
+    rec = _load("convert")
+    src = QUANT_SOURCES[src_name]()
+    fin = _finite_mask(src)
+    for sc in wi.QUANT_SCALES:
+        dst = torch.zeros(src.shape, dtype=torch.uint8, device="cuda")
+        ops.convert_fp8(dst, src.cuda(), float(sc), "fp8")
+        up = rec["quant_%s_%r" % (src_name, sc)]
+        assert torch.equal(dst.cpu()[fin], up[fin]), (src_name, sc)
+    if src_name == "f32":
+        for sc in wi.QUANT_SCALES:
+            s2 = wi.tricky_f32_scaled(sc)
+            dst = torch.zeros(s2.shape, dtype=torch.uint8, device="cuda")
+            ops.convert_fp8(dst, s2.cuda(), float(sc), "fp8")
+            f2 = _finite_mask(s2)
+            assert torch.equal(dst.cpu()[f2], rec["quant_f32_scaled_%r" % sc][f2]), sc
+
+
+@pytest.mark.gpu
+def test_kernel_dequant_matches_upstream(ops):
+    rec = _load("convert")
+    codes = wi.all_bytes()
+    ok = (codes & 0x7F) != 0x7F
+    for dname, dt in (("bf16", torch.bfloat16), ("f16", torch.float16), ("f32", torch.float32)):
+        for sc in wi.DEQUANT_SCALES:
+            dst = torch.zeros(codes.shape, dtype=dt, device="cuda")
+            ops.convert_fp8(dst, codes.cuda(), float(sc), "fp8")
+            assert torch.equal(dst.cpu()[ok], rec["dequant_%s_%r" % (dname, sc)][ok]), (dname, sc)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", wi.CACHE_CASES_V1 + wi.CACHE_CASES_FLASH)
+def test_kernel_cache_bytes_match_upstream(ops, name):
+    rec = _load("cache")
+    c = wi.cache_case(name)
+    ks = torch.tensor([c["k_scale"]], dtype=torch.float32, device="cuda")
+    vs = torch.tensor([c["v_scale"]], dtype=torch.float32, device="cuda")
+    if name in wi.CACHE_CASES_FLASH:
+        kc = torch.zeros(c["NB"], c["B"], c["Hkv"], c["D"], dtype=torch.uint8, device="cuda")
+        vc = torch.zeros_like(kc)
+        ops.reshape_and_cache_flash(c["key"].cuda(), c["value"].cuda(), kc, vc, c["slot_mapping"].cuda(), "fp8", ks, vs)
+    else:
+        kc = torch.zeros(c["NB"], c["Hkv"], c["D"] // 16, c["B"], 16, dtype=torch.uint8, device="cuda")
+        vc = torch.zeros(c["NB"], c["Hkv"], c["D"], c["B"], dtype=torch.uint8, device="cuda")
+        ops.reshape_and_cache(c["key"].cuda(), c["value"].cuda(), kc, vc, c["slot_mapping"].cuda(), "fp8", ks, vs)
+    assert torch.equal(kc.cpu(), rec[name]["key_cache"]) and torch.equal(vc.cpu(), rec[name]["value_cache"])
+
+
+@pytest.mark.gpu
+def test_kernel_mla_cache_bytes_match_upstream(ops):
+    rec = _load("cache")
+    if "mla" not in rec:
+        pytest.skip("upstream concat_and_cache_mla witness not recorded")
+    m = wi.mla_case()
+    cache = torch.zeros(m["NB"], m["B"], m["LORA"] + m["ROPE"], dtype=torch.uint8, device="cuda")
+    ops.concat_and_cache_mla(m["kv_c"].cuda(), m["k_pe"].cuda(), cache, m["slot_mapping"].cuda(), "fp8",
+                             torch.tensor([m["scale"]], dtype=torch.float32, device="cuda"))
+    assert torch.equal(cache.cpu(), rec["mla"]["kv_cache"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(wi.ATTN_CASES))
+def test_kernel_attention_matches_upstream(ops, name):
+    rec = _load("attn")
+    c = wi.attn_case(name)
+    dev = "cuda"
+    q, kc, vc = c["query"].to(dev), c["key_cache"].to(dev), c["value_cache"].to(dev)
+    bt, lens = c["block_tables"].to(dev), c["seq_lens"].to(dev)
+    ks = torch.tensor([c["k_scale"]], dtype=torch.float32, device=dev)
+    vs = torch.tensor([c["v_scale"]], dtype=torch.float32, device=dev)
+    L = c["max_len"]
+    out = torch.empty_like(q)
+    ops.paged_attention_v1(out, q, kc, vc, c["Hkv"], c["scale"], bt, lens, c["B"], L, None, c["kv"], ks, vs)
+    assert (out.cpu().float() - rec[name]["v1"].float()).abs().max().item() <= 2e-3
+    P = (L + 511) // 512
+    es = torch.empty(c["S"], c["H"], P, dtype=torch.float32, device=dev)
+    ml, tmp = torch.empty_like(es), torch.empty(c["S"], c["H"], P, c["D"], dtype=q.dtype, device=dev)
+    out2 = torch.empty_like(q)
+    ops.paged_attention_v2(out2, es, ml, tmp, q, kc, vc, c["Hkv"], c["scale"], bt, lens, c["B"], L, None, c["kv"], ks, vs)
+    assert (out2.cpu().float() - rec[name]["v2"].float()).abs().max().item() <= 2e-3

@@ -25,6 +25,7 @@ EXPORTED_SYMBOLS = (
     "b200_paged_attention_v2",
     "b200_paged_attention_flash",
     "b200_paged_attention_workspace_bytes",
+    "b200_paged_attention_workspace_reset",
     "b200_reshape_and_cache",
     "b200_reshape_and_cache_flash",
     "b200_convert_fp8",
@@ -273,6 +274,8 @@ def load() -> C.CDLL:
     lib.b200_paged_attention_flash.restype = C.c_int
     lib.b200_paged_attention_workspace_bytes.argtypes = [P(PagedAttnParams)]
     lib.b200_paged_attention_workspace_bytes.restype = C.c_uint64
+    lib.b200_paged_attention_workspace_reset.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
+    lib.b200_paged_attention_workspace_reset.restype = C.c_int
     lib.b200_reshape_and_cache.argtypes = [P(CacheWriteParams), C.c_void_p]
     lib.b200_reshape_and_cache.restype = C.c_int
     lib.b200_reshape_and_cache_flash.argtypes = [P(CacheWriteParams), C.c_void_p]

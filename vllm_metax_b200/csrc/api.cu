@@ -144,18 +144,21 @@ uint64_t generic_split_bytes(const b200_paged_attn_params_t& p) {
   return (uint64_t)p.num_seqs * p.num_heads * P * (p.head_size + 2) * sizeof(float);
 }
 
-// Sequences of length 0 own no tile in the streaming schedules, so nothing would write their rows.  When the
-// caller wants the LSE (to merge this result with another one) those rows must be well defined: out = 0, lse = -inf.
+// Sequences of length 0 own no tile in the streaming schedules, so nothing would write their rows: out = 0, and
+// lse = -inf when the caller wants the LSE (to merge this result with another one).
 __global__ void init_empty_rows_kernel(const int32_t* seq_lens, void* out, float* lse, int S, int H, int row_bytes) {
   const int s = blockIdx.x;
   if (seq_lens[s] > 0) return;
   uint32_t* o = reinterpret_cast<uint32_t*>(static_cast<char*>(out) + (int64_t)s * row_bytes);
   for (int i = threadIdx.x; i < row_bytes / 4; i += blockDim.x) o[i] = 0u;
-  for (int h = threadIdx.x; h < H; h += blockDim.x) lse[(int64_t)h * S + s] = -INFINITY;
+  if (lse != nullptr)
+    for (int h = threadIdx.x; h < H; h += blockDim.x) lse[(int64_t)h * S + s] = -INFINITY;
 }
 
+// The out rows are zeroed whether or not an LSE is asked for: the reference kernels write zeros for an empty
+// sequence (acc = 0 times 1/(0 + 1e-6), csrc/attention/attention_kernels.cuh:331), and CUDA-graph-padded decode batches
+// carry such rows.
 int init_empty_rows(const b200_paged_attn_params_t& p, cudaStream_t s) {
-  if (p.out_lse == nullptr) return B200_OK;
   const int row_bytes = p.num_heads * p.head_size * dtype_bytes(p.dtype);  // multiple of 4: head sizes are even
   init_empty_rows_kernel<<<p.num_seqs, 128, 0, s>>>(p.seq_lens, p.out, p.out_lse, p.num_seqs, p.num_heads, row_bytes);
   count_launch();
@@ -172,15 +175,28 @@ extern "C" uint64_t b200_paged_attention_workspace_bytes(const b200_paged_attn_p
   return kFlatWorkspaceBytes + generic_split_bytes(*p);
 }
 
+extern "C" int b200_paged_attention_workspace_reset(void* workspace, uint64_t workspace_bytes, void* stream) {
+  B200_REQUIRE(workspace != nullptr && workspace_bytes >= kFlatCounterBytes, B200_ERR_WORKSPACE,
+               "workspace_reset: workspace missing or smaller than its counter region (%llu bytes)",
+               (unsigned long long)kFlatCounterBytes);
+  cudaError_t e = cudaMemsetAsync(workspace, 0, kFlatCounterBytes, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) {
+    set_error("workspace_reset: cudaMemsetAsync failed: %s", cudaGetErrorString(e));
+    return B200_ERR_CUDA;
+  }
+  return B200_OK;
+}
+
 extern "C" int b200_paged_attention_v1(const b200_paged_attn_params_t* p, void* stream) {
   int rc = validate_attn(p, false);
   if (rc != B200_OK) return rc;
   if (p->num_seqs == 0) return B200_OK;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  rc = init_empty_rows(*p, s);
-  if (rc != B200_OK || p->max_seq_len == 0) return rc;
+  if (p->max_seq_len == 0) return init_empty_rows(*p, s);
   const int variant = pick_variant(*p);
   if (variant < 0) return -variant;
+  // the streaming and generic kernels write the rows of empty sequences themselves; the tcgen05 kernel does not
+  if (variant == B200_VARIANT_UMMA_FP8 && (rc = init_empty_rows(*p, s)) != B200_OK) return rc;
   if (variant == B200_VARIANT_STREAM_MMA || variant == B200_VARIANT_UMMA_FP8) {
     B200_REQUIRE(p->workspace != nullptr && p->workspace_bytes >= kFlatWorkspaceBytes, B200_ERR_WORKSPACE,
                  "paged_attention_v1 needs %llu bytes of workspace, got %llu", (unsigned long long)kFlatWorkspaceBytes,
@@ -234,8 +250,8 @@ extern "C" int b200_paged_attention_flash(const b200_paged_attn_params_t* p, voi
                B200_ERR_INVALID_ARGUMENT, "max_seq_len %d exceeds the block table (%d blocks of %d)", p->max_seq_len,
                p->max_num_blocks_per_seq, p->block_size);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  int rc = init_empty_rows(*p, s);
-  if (rc != B200_OK || p->max_seq_len == 0) return rc;
+  if (p->max_seq_len == 0) return init_empty_rows(*p, s);
+  int rc;
   B200_REQUIRE(p->workspace != nullptr && p->workspace_bytes >= kFlatWorkspaceBytes, B200_ERR_WORKSPACE,
                "paged_attention_flash needs %llu bytes of workspace, got %llu", (unsigned long long)kFlatWorkspaceBytes,
                (unsigned long long)(p->workspace ? p->workspace_bytes : 0));
@@ -251,10 +267,10 @@ extern "C" int b200_paged_attention_v2(const b200_paged_attn_params_t* p, void* 
   if (rc != B200_OK) return rc;
   if (p->num_seqs == 0) return B200_OK;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  rc = init_empty_rows(*p, s);
-  if (rc != B200_OK || p->max_seq_len == 0) return rc;
+  if (p->max_seq_len == 0) return init_empty_rows(*p, s);
   const int variant = pick_variant(*p);
   if (variant < 0) return -variant;
+  if (variant == B200_VARIANT_UMMA_FP8 && (rc = init_empty_rows(*p, s)) != B200_OK) return rc;
   // the caller sized exp_sums / max_logits / tmp_out for 512-token partitions
   // (csrc/attention/paged_attention_v2.cu:45,82)
   SplitOut so;

@@ -87,7 +87,17 @@ paged_attention_generic_kernel(GenericParams p) {
   const int L = p.seq_lens[s];
   const int chunk = p.so.chunk;
   const int t0 = part * chunk;
-  if (t0 >= L) return;
+  if (t0 >= L) {
+    // an empty sequence (CUDA-graph padding): the reference kernels leave zeros (acc = 0 times 1/(0 + 1e-6),
+    // csrc/attention/attention_kernels.cuh:331); lse = -inf so that a merge ignores the row
+    if (L <= 0 && part == 0) {
+      T* o = reinterpret_cast<T*>(p.out) + ((int64_t)s * p.H + (int64_t)kvh * p.G) * p.D;
+      for (int i = threadIdx.x; i < p.G * p.D; i += kThreads) o[i] = from_f32<T>(0.f);
+      if (p.lse != nullptr)
+        for (int h = threadIdx.x; h < p.G; h += kThreads) p.lse[(int64_t)(kvh * p.G + h) * p.S + s] = -INFINITY;
+    }
+    return;
+  }
   const int t1 = min(t0 + chunk, L);
   const int n = t1 - t0;
   const int D = p.D, B = p.B, G = p.G;

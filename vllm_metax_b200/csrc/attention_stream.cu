@@ -86,7 +86,21 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
     // Producer warp pw owns the tiles gt == pw (mod kProducerWarps) of the CTA's tile stream; one
     // lane walks the block table and issues the bulk copies (a single issuing thread costs ~1000
     // cycles per tile, so four of them share the stream).
-    if (lane != 0) return;
+    if (lane != 0) {
+      // The idle lanes of the last producer warp give empty sequences (seq_len 0: CUDA-graph padding) their result:
+      // a zero row, as the reference kernels leave (acc = 0 times 1/(0 + 1e-6), csrc/attention/attention_kernels.cuh:331),
+      // and lse = -inf.  Such sequences own no tile, so no consumer ever writes them.
+      if (warp == kConsumerWarps + NP - 1) {
+        for (int s = (int)blockIdx.x; s < p.S; s += (int)gridDim.x) {
+          if (__ldg(p.seq_lens + s) > 0) continue;
+          uint4* row = reinterpret_cast<uint4*>(p.out + (int64_t)s * p.H * kD);
+          for (int i = lane - 1; i < p.H * (kD * 2 / 16); i += 31) row[i] = make_uint4(0u, 0u, 0u, 0u);
+          if (p.lse != nullptr)
+            for (int h = lane - 1; h < p.H; h += 31) p.lse[(int64_t)h * p.S + s] = -INFINITY;
+        }
+      }
+      return;
+    }
     if constexpr (FLASH) {
       producer_loop_flash<FLAT, NP>(p, &p.tm_k, &p.tm_v, sched, warp - kConsumerWarps, ring_u32, full_u32, empty_u32, nst);
       return;
@@ -593,8 +607,7 @@ int launch_stream_np(StreamParams& sp, cudaStream_t s) {
   while (stream_smem_bytes<B, FP8, NT>(nst + kConsumerWarps) <= kMaxSmem &&
          (size_t)(nst + kConsumerWarps) * C::kStageBytes <= 128 * 1024)
     nst += kConsumerWarps;
-  if (const char* e = getenv("B200_STREAM_NSTAGES"))
-    nst = max(kConsumerWarps, min(nst, atoi(e) / kConsumerWarps * kConsumerWarps));
+  if (const int want = env_int("B200_STREAM_NSTAGES")) nst = max(kConsumerWarps, min(nst, want / kConsumerWarps * kConsumerWarps));
   sp.nstages = nst;
   const size_t smem = stream_smem_bytes<B, FP8, NT>(nst);
   auto kern = paged_attention_stream_kernel<B, FP8, NT, FLAT, NP>;
@@ -622,7 +635,7 @@ int launch_stream_t(StreamParams& sp, cudaStream_t s) {
   // 8 producer warps leave 128 registers per thread: enough for one head tile (NT = 1), spills with two
   if constexpr (FP8 && NT == 1) {
     int np = B == 16 ? 8 : 4;
-    if (const char* e = getenv("B200_STREAM_NPROD")) np = atoi(e) >= 8 ? 8 : 4;
+    if (const int want = env_int("B200_STREAM_NPROD")) np = want >= 8 ? 8 : 4;
     if (np == 8) return launch_stream_np<B, FP8, NT, FLAT, 8>(sp, s);
   }
   return launch_stream_np<B, FP8, NT, FLAT, 4>(sp, s);
@@ -642,6 +655,7 @@ bool stream_variant_eligible(const b200_paged_attn_params_t& p, const char** why
   else if ((p.kv_block_stride * eb) % 16 != 0 || (p.kv_head_stride * eb) % 16 != 0) w = "KV strides not 16-byte multiples";
   else if ((reinterpret_cast<uintptr_t>(p.key_cache) | reinterpret_cast<uintptr_t>(p.value_cache)) % 16 != 0) w = "KV cache not 16-byte aligned";
   else if (p.q_stride % 8 != 0 || reinterpret_cast<uintptr_t>(p.query) % 16 != 0) w = "query rows not 16-byte aligned";
+  else if (reinterpret_cast<uintptr_t>(p.out) % 16 != 0) w = "out not 16-byte aligned";
   if (why) *why = w;
   return w == nullptr;
 }
@@ -673,6 +687,7 @@ bool stream_flash_eligible(const b200_paged_attn_params_t& p, const char** why) 
     w = "KV strides not 16-byte multiples";
   else if ((reinterpret_cast<uintptr_t>(p.key_cache) | reinterpret_cast<uintptr_t>(p.value_cache)) % 16 != 0) w = "KV cache not 16-byte aligned";
   else if (p.q_stride % 8 != 0 || reinterpret_cast<uintptr_t>(p.query) % 16 != 0) w = "query rows not 16-byte aligned";
+  else if (reinterpret_cast<uintptr_t>(p.out) % 16 != 0) w = "out not 16-byte aligned";
   if (why) *why = w;
   return w == nullptr;
 }
@@ -728,8 +743,8 @@ int launch_stream_flash_t(StreamParams& sp, cudaStream_t s) {
     return 1024 + (size_t)n * kFlashStageBytes + (size_t)kConsumerWarps * 8 * NT * (kMergeStride + 2) * sizeof(float) +
            (size_t)n * 16 + sizeof(Sched) + 16;
   };
-  if (const char* e = getenv("B200_STREAM_NSTAGES")) {
-    const int want = atoi(e) / kConsumerWarps * kConsumerWarps;
+  if (const int e = env_int("B200_STREAM_NSTAGES")) {
+    const int want = e / kConsumerWarps * kConsumerWarps;
     if (want > nst && smem_of(want) <= kMaxSmem) nst = want;
   }
   sp.nstages = nst;

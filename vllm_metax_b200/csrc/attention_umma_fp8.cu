@@ -655,7 +655,7 @@ __global__ void __launch_bounds__(kUThreads, 1) paged_attention_umma_fp8_kernel(
 template <bool FLAT>
 int launch_umma_t(StreamParams& sp, cudaStream_t s) {
   int nst = 16;  // 128 KiB in flight (profiles/r1_gather_read_bench.log); a multiple of 8 producers and 4 classes
-  if (const char* e = getenv("B200_STREAM_NSTAGES")) nst = max(8, min(16, atoi(e) / 8 * 8));
+  if (const int e = env_int("B200_STREAM_NSTAGES")) nst = max(8, min(16, e / 8 * 8));
   sp.nstages = nst;
   const size_t smem = usmem_bytes(nst);
   auto kern = paged_attention_umma_fp8_kernel<FLAT>;

@@ -8,6 +8,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <type_traits>
 
 #include "common.cuh"
@@ -460,6 +461,22 @@ __device__ __forceinline__ void producer_loop_flash(const StreamParams& p, const
   }
 }
 
+// Developer knobs (B200_STREAM_NSTAGES, B200_STREAM_NPROD, B200_DEBUG_NUM_BLOCKS) are read from the environment ONCE
+// per process and name (the launch path never calls getenv); 0 = unset.
+inline int env_int(const char* name) {
+  struct Slot { const char* name; int value; };
+  static Slot slots[8];
+  static int nslots = 0;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  for (int i = 0; i < nslots; ++i)
+    if (strcmp(slots[i].name, name) == 0) return slots[i].value;
+  const char* e = getenv(name);
+  const int v = e ? atoi(e) : 0;
+  if (nslots < 8) slots[nslots++] = Slot{name, v};
+  return v;
+}
+
 // host: C-ABI parameters -> kernel parameters (strides in bytes)
 StreamParams fill_stream_params(const b200_paged_attn_params_t& p) {
   const int eb = p.kv_dtype == B200_KV_FP8_E4M3 ? 1 : 2;
@@ -478,7 +495,7 @@ StreamParams fill_stream_params(const b200_paged_attn_params_t& p) {
   sp.S = p.num_seqs; sp.H = p.num_heads; sp.Hkv = p.num_kv_heads; sp.G = p.num_heads / p.num_kv_heads;
   sp.max_blocks = p.max_num_blocks_per_seq;
   sp.scale = p.scale;
-  if (const char* e = getenv("B200_DEBUG_NUM_BLOCKS")) sp.debug_num_blocks = atoi(e);
+  sp.debug_num_blocks = env_int("B200_DEBUG_NUM_BLOCKS");
   return sp;
 }
 

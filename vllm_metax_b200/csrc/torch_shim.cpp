@@ -54,22 +54,71 @@ void check_status(int rc, const char* op) {
 
 bool is_cache_byte_type(at::ScalarType t) { return t == at::kByte || t == at::kFloat8_e4m3fn; }
 
-// v1 split-KV scratch: one growing buffer per (device, stream).  The op has no
-// workspace argument (csrc/torch_bindings.cpp:45-55), so the shim owns it;
-// work on one stream is ordered, so reuse across calls is safe.
-void* v1_workspace(uint64_t bytes, const at::Tensor& like, cudaStream_t stream) {
-  if (bytes == 0) return nullptr;
-  static std::mutex mu;
-  static std::unordered_map<uint64_t, at::Tensor> cache;
-  const uint64_t key = (static_cast<uint64_t>(like.get_device()) << 56) ^ reinterpret_cast<uint64_t>(stream);
-  std::lock_guard<std::mutex> lock(mu);
-  at::Tensor& t = cache[key];
+// v1 split-KV scratch: one buffer per (device, stream).  The op has no workspace argument
+// (csrc/torch_bindings.cpp:45-55) and the reference's ops allocate nothing (SURVEY.md §8b "Ownership"), so the
+// allocation lives OUTSIDE the attention ops: `_C_b200::reserve_workspace` (called by import_kernels()-time warm-up /
+// the plugin's profile run) sizes it; the attention ops only look it up.  For the streaming kernels the size is a
+// constant (kFlatWorkspaceBytes, ~5.3 MB); only the generic kernel's split-KV partials grow with the shape.  A
+// call that finds no (or too small a) buffer allocates it lazily — unless the stream is being captured into a CUDA
+// graph, where an allocation would be illegal: that raises and names reserve_workspace.  Work on one stream is
+// ordered, so reuse across calls is safe.
+struct WorkspaceCache {
+  std::mutex mu;
+  std::unordered_map<uint64_t, at::Tensor> map;
+};
+WorkspaceCache& workspace_cache() {
+  static WorkspaceCache c;
+  return c;
+}
+uint64_t workspace_key(int device, cudaStream_t stream) {
+  return (static_cast<uint64_t>(device) << 56) ^ reinterpret_cast<uint64_t>(stream);
+}
+bool stream_is_capturing(cudaStream_t stream) {
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return st != cudaStreamCaptureStatusNone;
+}
+at::Tensor& grow_workspace(uint64_t bytes, const at::TensorOptions& opts, int device, cudaStream_t stream, const char* op) {
+  WorkspaceCache& c = workspace_cache();
+  at::Tensor& t = c.map[workspace_key(device, stream)];
   if (!t.defined() || static_cast<uint64_t>(t.numel()) < bytes) {
+    TORCH_CHECK(!stream_is_capturing(stream), op, ": the split-KV workspace of this stream (", t.defined() ? t.numel() : 0,
+                " bytes) is smaller than the ", bytes, " bytes this shape needs and the stream is being captured into a CUDA "
+                "graph; call torch.ops._C_b200.reserve_workspace(query, max_seq_len) once before capture");
     const uint64_t want = bytes + bytes / 4;
     // zero-filled once: the arrival counters inside must start at zero; every launch leaves them at zero
-    t = at::zeros({static_cast<int64_t>(want)}, like.options().dtype(at::kByte));
+    t = at::zeros({static_cast<int64_t>(want)}, opts.dtype(at::kByte));
   }
-  return t.data_ptr();
+  return t;
+}
+void* v1_workspace(uint64_t bytes, const at::Tensor& like, cudaStream_t stream, const char* op = "paged_attention") {
+  if (bytes == 0) return nullptr;
+  std::lock_guard<std::mutex> lock(workspace_cache().mu);
+  return grow_workspace(bytes, like.options(), like.get_device(), stream, op).data_ptr();
+}
+
+// _C_b200::reserve_workspace(Tensor query_like, int max_seq_len, bool reset) -> ()
+// Sizes (and with reset = true re-zeroes) the current stream's workspace for decode batches shaped like `query_like`
+// [num_seqs, num_heads, head_size] with contexts up to max_seq_len.  Call it at warm-up, outside graph capture.
+void reserve_workspace(const at::Tensor& query_like, int64_t max_seq_len, bool reset) {
+  TORCH_CHECK(query_like.is_cuda() && query_like.dim() == 3, "reserve_workspace: query_like must be a CUDA tensor [num_seqs, num_heads, head_size]");
+  b200_paged_attn_params_t p;
+  memset(&p, 0, sizeof(p));
+  p.num_seqs = static_cast<int32_t>(query_like.size(0));
+  p.num_heads = static_cast<int32_t>(query_like.size(1));
+  p.num_kv_heads = p.num_heads;
+  p.head_size = static_cast<int32_t>(query_like.size(2));
+  p.max_seq_len = static_cast<int32_t>(max_seq_len);
+  const at::cuda::OptionalCUDAGuard guard(device_of(query_like));
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  const uint64_t bytes = b200_paged_attention_workspace_bytes(&p);
+  if (bytes == 0) return;
+  std::lock_guard<std::mutex> lock(workspace_cache().mu);
+  at::Tensor& t = grow_workspace(bytes, query_like.options(), query_like.get_device(), stream, "reserve_workspace");
+  if (reset) check_status(b200_paged_attention_workspace_reset(t.data_ptr(), static_cast<uint64_t>(t.numel()), stream), "reserve_workspace");
 }
 
 void fill_attn_params(b200_paged_attn_params_t& p, at::Tensor& out, const at::Tensor& query,
@@ -841,6 +890,7 @@ const char* kSchemaRotaryCache =
     "rotary_embedding_and_cache_flash(Tensor positions, Tensor! query, Tensor! key, Tensor value, int head_size, "
     "Tensor cos_sin_cache, bool is_neox, Tensor! key_cache, Tensor! value_cache, Tensor slot_mapping, "
     "str kv_cache_dtype, Tensor k_scale, Tensor v_scale) -> ()";
+const char* kSchemaReserve = "reserve_workspace(Tensor query_like, int max_seq_len, bool reset=False) -> ()";
 const char* kSchemaFlash =
     "paged_attention_flash(Tensor! out, Tensor!? lse, Tensor query, Tensor key_cache, Tensor value_cache, "
     "float scale, Tensor block_tables, Tensor seq_lens, int max_seq_len, Tensor? alibi_slopes) -> ()";
@@ -889,6 +939,7 @@ void register_all() {
     register_op(keep, "_C_b200", "paged_attention_v1_lse", kSchemaV1Lse, &paged_attention_v1_lse);
     register_op(keep, "_C_b200", "paged_attention_flash", kSchemaFlash, &paged_attention_flash);
     register_op(keep, "_C", "rotary_embedding", kSchemaRotary, &rotary_embedding);
+    register_op(keep, "_C_b200", "reserve_workspace", kSchemaReserve, &reserve_workspace);
     register_op(keep, "_C_b200", "rotary_embedding_and_cache_flash", kSchemaRotaryCache, &rotary_embedding_and_cache_flash);
   });
 }
