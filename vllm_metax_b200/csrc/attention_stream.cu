@@ -40,12 +40,34 @@
 namespace b200 {
 namespace {
 
+#ifdef B200_TIMELINE
+// Developer build (-DB200_TIMELINE): per-CTA %globaltimer stamps of the last streaming launch, read back with
+// b200_debug_timeline(): [cta][0] entry, [1] schedule ready, [2] first tile landed (warp 0), [3] last tile consumed,
+// [4] merges done / exit.
+__device__ unsigned long long g_timeline[256][8];
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define TL(slot) do { if ((threadIdx.x & 31) == 0) atomicMax(&g_timeline[blockIdx.x][slot], gtime()); } while (0)
+#define TL_FIRST(slot) do { if ((threadIdx.x & 31) == 0) atomicMin(&g_timeline[blockIdx.x][slot], gtime()); } while (0)
+#else
+#define TL(slot) do { } while (0)
+#define TL_FIRST(slot) do { } while (0)
+#endif
+
 // ---- the kernel ------------------------------------------------------------------
-template <int B, bool FP8, int NT, bool FLAT, int NP, bool FLASH = false>
+// PW ("per-warp items", item schedule only): every consumer warp owns WHOLE work items (512-token partitions) and is
+// fed by its own producer lane through its own slice of the ring, so an item ends without any cross-warp merge —
+// the warp normalises and writes its partial itself.  With fp8 caches the consumers are the busy side and the
+// CTA-wide merge per 512-token item (barrier, 32 KiB through shared memory, barrier) cost 0.88 -> 0.66 of peak.
+template <int B, bool FP8, int NT, bool FLAT, int NP, bool FLASH = false, bool PW = false>
 __global__ void __launch_bounds__((kConsumerWarps + NP) * kWarpSize, 1)
 paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
   using C = Cfg<B, FP8>;
   static_assert(NP == 4 || NP == 8, "whole warpgroups of producers");
+  static_assert(!PW || (!FLAT && !FLASH && NT == 1 && NP == kConsumerWarps), "per-warp items: item schedule, one head tile, one producer per consumer");
   static_assert(!FLASH || (!FP8 && B == 16), "flash layout: bf16 cache; the block size is a runtime value");
   // bytes of one ring stage (32 tokens of K and V)
   constexpr int kStage = FLASH ? kFlashStageBytes : C::kStageBytes;
@@ -68,6 +90,13 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
   const uint32_t empty_u32 = full_u32 + 8u * nst;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#ifdef B200_TIMELINE
+  if (tid == 0) {
+    g_timeline[blockIdx.x][0] = gtime();
+    g_timeline[blockIdx.x][2] = ~0ull;
+    g_timeline[blockIdx.x][3] = 0; g_timeline[blockIdx.x][4] = 0;
+  }
+#endif
   if (tid == 0) {
     for (int i = 0; i < nst; ++i) {
       mbar_init(full_u32 + 8u * i, 1);
@@ -80,6 +109,9 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
     if (warp == 0) compute_sched(p, sched, lane);
   }
   __syncthreads();
+#ifdef B200_TIMELINE
+  if (tid == 0) g_timeline[blockIdx.x][1] = gtime();
+#endif
 
   if (warp >= kConsumerWarps) {
     // ===================== producer warps ========================================
@@ -103,6 +135,10 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
     }
     if constexpr (FLASH) {
       producer_loop_flash<FLAT, NP>(p, &p.tm_k, &p.tm_v, sched, warp - kConsumerWarps, ring_u32, full_u32, empty_u32, nst);
+      return;
+    }
+    if constexpr (PW) {
+      producer_loop_pw<B, FP8>(p, warp - kConsumerWarps, ring_u32, full_u32, empty_u32, nst / kConsumerWarps);
       return;
     }
     producer_loop<B, FP8, FLAT, NP>(p, sched, warp - kConsumerWarps, ring_u32, full_u32, empty_u32, nst);
@@ -148,9 +184,22 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
   const float vsc = FP8 ? __ldg(p.v_scale) : 1.f;
 
   uint32_t tile_base = 0;  // tiles issued to the ring before this segment
-  uint32_t stage = (uint32_t)warp, parity = 0;  // ring stage / phase of this warp's next tile
+  // ring stage / phase of this warp's next tile (PW: the warp's own slice [warp * spw, (warp + 1) * spw) of the ring)
+  [[maybe_unused]] const uint32_t spw = (uint32_t)nst / kConsumerWarps;
+  [[maybe_unused]] uint32_t lstage = 0;
+  uint32_t stage = PW ? (uint32_t)warp * spw : (uint32_t)warp, parity = 0;
   WorkIter<FLAT> wi;
   wi.init(p, sched);
+  [[maybe_unused]] int kitem = -1;  // PW: ordinal of the item in the CTA's list; item k belongs to warp k mod 8
+  auto next_item = [&](Seg& sg) -> bool {
+    if constexpr (PW) {
+      while (wi.next(p, sg))
+        if ((++kitem & (kConsumerWarps - 1)) == warp) return true;
+      return false;
+    } else {
+      return wi.next(p, sg);
+    }
+  };
   // ---- Q fragments (B operand: k = dims, n = heads) of a segment --------------------------------------
   // Loaded in two steps so that the global-memory latency of the NEXT segment's query overlaps the merge of the
   // current one (with 512-token items the exposed wait was ~1/3 of the per-item overhead): q_issue only issues the
@@ -227,7 +276,7 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
   constexpr bool kPrefetchQ = !FLAT && NT == 1;
   Seg it, nx;
   int item = -1;
-  bool has = wi.next(p, nx);
+  bool has = next_item(nx);
   if (kPrefetchQ && has) q_issue(nx);
   while (has) {
     it = nx;
@@ -254,12 +303,8 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
     // of 8, so every use of a stage is consumed by the same warp, in order.  (A warp that skipped a
     // phase of a stage could pass a parity wait one round early: mbarrier parity only tells odd from
     // even.)
-    for (int ti = (int)((warp - tile_base) & (kConsumerWarps - 1)); ti < ntiles; ti += kConsumerWarps) {
-      // this warp's tiles are gt = warp, warp + 8, ... over the whole stream, so stage / parity advance
-      // incrementally (no division by the runtime ring depth)
-      MBAR_WAIT(full_u32 + 8u * stage, parity, 2, item, (int)(tile_base + (uint32_t)ti));
-      const uint32_t sb = ring_u32 + stage * kStage;
-      const int tok0 = it.t0 + ti * kTileTokens;   // first token of the tile
+    // one 32-token tile at shared-memory address sb, first token tok0: S^T = K.Q^T, online softmax, O^T += V^T.P^T
+    auto do_tile = [&](const uint32_t sb, const int tok0) {
       const int nvalid = min(kTileTokens, it.t1 - tok0);
       const bool partial = nvalid < kTileTokens;
 
@@ -433,6 +478,30 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
         }
       };
       if (partial) pv(std::true_type{}); else pv(std::false_type{});
+    };
+
+    if constexpr (PW) {
+      // the warp walks ALL tiles of its item through its own ring slice
+      for (int ti = 0; ti < ntiles; ++ti) {
+        MBAR_WAIT(full_u32 + 8u * stage, parity, 2, item, ti);
+        TL_FIRST(2);
+        do_tile(ring_u32 + stage * kStage, it.t0 + ti * kTileTokens);
+        __threadfence_block();  // see the note in the shared-ring loop below
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_u32 + 8u * stage);
+        if (++lstage == spw) {
+          lstage = 0;
+          parity ^= 1u;
+        }
+        stage = (uint32_t)warp * spw + lstage;
+      }
+    }
+    for (int ti = PW ? ntiles : (int)((warp - tile_base) & (kConsumerWarps - 1)); ti < ntiles; ti += kConsumerWarps) {
+      // this warp's tiles are gt = warp, warp + 8, ... over the whole stream, so stage / parity advance
+      // incrementally (no division by the runtime ring depth)
+      MBAR_WAIT(full_u32 + 8u * stage, parity, 2, item, (int)(tile_base + (uint32_t)ti));
+      TL_FIRST(2);
+      do_tile(ring_u32 + stage * kStage, it.t0 + ti * kTileTokens);
       // All lanes have consumed the stage: hand it back to the producer.  The fence is REQUIRED: ptxas
       // issues the mbarrier arrive without waiting for the LDSMs still in flight (it even hoists it above the
       // last HMMAs), and with bank-conflicted V fragments (B = 32 bf16: 64-byte rows, 4-way conflicts) the
@@ -448,11 +517,64 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
       }
     }
     tile_base += (uint32_t)ntiles;
+    TL(3);
     if constexpr (kPrefetchQ) {
-      has = wi.next(p, nx);
+      has = next_item(nx);
       if (has) q_issue(nx);  // in flight during the merge below
     }
 
+    if constexpr (PW) {
+      // ---- per-warp items: the warp finishes its partition alone ----------------------------------------
+      float lsum[2], inv[2];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {  // sum over the 8 lanes that share a head column
+        float l = lrun[0][e];
+        l += __shfl_xor_sync(0xffffffffu, l, 4);
+        l += __shfl_xor_sync(0xffffffffu, l, 8);
+        l += __shfl_xor_sync(0xffffffffu, l, 16);
+        lsum[e] = l;
+        inv[e] = vsc * __fdividef(1.f, l + 1e-6f);
+      }
+      // normalised rows staged in the warp's scratch [8 heads][128 dims] (the merge area is unused in this mode),
+      // then written with 16-byte stores: a head's row is 256 contiguous bytes in out and in tmp_out
+      __nv_bfloat16* scr = reinterpret_cast<__nv_bfloat16*>(merge_o) + warp * (8 * kD);
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          scr[(2 * c + (e & 1)) * kD + 16 * i + g + 8 * (e >> 1)] = __float2bfloat16_rn(oacc[0][i][e] * inv[e & 1]);
+      __syncwarp();
+      const bool single = it.L <= p.so.chunk;
+      const bool want_partials = p.so.o != nullptr;  // normalised format (the host selects this mode only for it)
+      for (int ch = lane; ch < 8 * 16; ch += 32) {
+        const int h = ch >> 4, part16 = ch & 15;
+        if (h >= p.G) break;
+        const uint4 v = *reinterpret_cast<const uint4*>(scr + h * kD + part16 * 8);
+        const int64_t row = (int64_t)it.s * p.H + it.kvh * p.G + h;
+        if (single) *reinterpret_cast<uint4*>(p.out + row * kD + part16 * 8) = v;
+        if (want_partials)
+          *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.so.o) + (row * p.so.num_partitions + it.part) * kD + part16 * 8) = v;
+      }
+      if (g == 0) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int h = 2 * c + e;
+          if (h < p.G) {
+            const int head = it.kvh * p.G + h;
+            if (want_partials) {
+              const int64_t pi = ((int64_t)it.s * p.H + head) * p.so.num_partitions + it.part;
+              p.so.m[pi] = mrun[0][e] * kLn2;
+              p.so.l[pi] = lsum[e];
+            }
+            if (single && p.lse != nullptr)
+              p.lse[(int64_t)head * p.S + it.s] = lsum[e] > 0.f ? fmaf(mrun[0][e], kLn2, logf(lsum[e])) : -INFINITY;
+          }
+        }
+      }
+      __syncwarp();  // the scratch is reused by this warp's next item
+      TL(4);
+      continue;
+    }
     // ---- merge the consumer warps' partial results ------------------------------------------
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
@@ -584,7 +706,8 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
       }
     }
     consumer_bar_sync();  // merge buffers are free again
-    if constexpr (!kPrefetchQ) has = wi.next(p, nx);
+    TL(4);
+    if constexpr (!kPrefetchQ) has = next_item(nx);
   }
 }
 
@@ -597,20 +720,22 @@ size_t stream_smem_bytes(int nstages) {
 
 constexpr size_t kMaxSmem = 227 * 1024;
 
-template <int B, bool FP8, int NT, bool FLAT, int NP>
+template <int B, bool FP8, int NT, bool FLAT, int NP, bool PW = false>
 int launch_stream_np(StreamParams& sp, cudaStream_t s) {
   using C = Cfg<B, FP8>;
   // ring depth: a multiple of the consumer-warp count (see the tile -> warp mapping in the kernel), capped at
   // 128 KiB in flight — the random-chunk gather does not get faster beyond that, and with 2 KiB chunks it gets
-  // slower (profiles/r1_gather_read_bench.log, r1_sweep.log: fp8 16 stages 5.67 TB/s vs 24 stages 5.23 TB/s)
+  // slower (profiles/r1_gather_read_bench.log, r1_sweep.log: fp8 16 stages 5.67 TB/s vs 24 stages 5.23 TB/s).
+  // Per-warp items: every warp's slice is its own pipeline, three stages deep (two leave the warp waiting on HBM
+  // latency: 8 warps x 2 x 8 KiB / ~3 us < the 47 GB/s an SM has to sustain).
   int nst = kConsumerWarps;
   while (stream_smem_bytes<B, FP8, NT>(nst + kConsumerWarps) <= kMaxSmem &&
-         (size_t)(nst + kConsumerWarps) * C::kStageBytes <= 128 * 1024)
+         (size_t)(nst + kConsumerWarps) * C::kStageBytes <= (PW ? 192 : 128) * 1024)
     nst += kConsumerWarps;
   if (const int want = env_int("B200_STREAM_NSTAGES")) nst = max(kConsumerWarps, min(nst, want / kConsumerWarps * kConsumerWarps));
   sp.nstages = nst;
   const size_t smem = stream_smem_bytes<B, FP8, NT>(nst);
-  auto kern = paged_attention_stream_kernel<B, FP8, NT, FLAT, NP>;
+  auto kern = paged_attention_stream_kernel<B, FP8, NT, FLAT, NP, false, PW>;
   static thread_local int configured_device = -1;
   int dev = 0;
   cudaGetDevice(&dev);
@@ -633,6 +758,11 @@ int launch_stream_np(StreamParams& sp, cudaStream_t s) {
 template <int B, bool FP8, int NT, bool FLAT>
 int launch_stream_t(StreamParams& sp, cudaStream_t s) {
   // 8 producer warps leave 128 registers per thread: enough for one head tile (NT = 1), spills with two
+  if constexpr (FP8 && NT == 1 && !FLAT) {
+    // v2 partitions in the reference's normalised format: per-warp items (B200_STREAM_PW=-1 switches it off)
+    if (sp.so.normalized && sp.so.o != nullptr && reinterpret_cast<uintptr_t>(sp.so.o) % 16 == 0 && env_int("B200_STREAM_PW") >= 0)
+      return launch_stream_np<B, FP8, NT, FLAT, 8, true>(sp, s);
+  }
   if constexpr (FP8 && NT == 1) {
     int np = B == 16 ? 8 : 4;
     if (const int want = env_int("B200_STREAM_NPROD")) np = want >= 8 ? 8 : 4;
@@ -789,6 +919,12 @@ int launch_attention_stream_flash(const b200_paged_attn_params_t& p, void* works
   if (sp.total_items == 0) return B200_OK;
   return (sp.G + 7) / 8 == 1 ? launch_stream_flash_t<1>(sp, s) : launch_stream_flash_t<2>(sp, s);
 }
+
+#ifdef B200_TIMELINE
+extern "C" int b200_debug_timeline(unsigned long long* host_dst) {
+  return cudaMemcpyFromSymbol(host_dst, g_timeline, sizeof(unsigned long long) * 256 * 8) == cudaSuccess ? 0 : 1;
+}
+#endif
 
 int launch_attention_stream(const b200_paged_attn_params_t& p, const SplitOut& so, cudaStream_t s) {
   const char* why = nullptr;

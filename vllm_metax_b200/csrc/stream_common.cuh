@@ -381,6 +381,54 @@ __device__ __forceinline__ void producer_loop(const StreamParams& p, const Sched
 
 }
 
+// Per-warp items (item schedule): producer lane pw feeds consumer warp pw alone.  It walks the CTA's item list, takes
+// the items k == pw (mod 8) — the same rule the consumer applies — and streams ALL tiles of each through the
+// warp's ring slice [pw * spw, (pw + 1) * spw).
+template <int B, bool FP8>
+__device__ __forceinline__ void producer_loop_pw(const StreamParams& p, int pw, uint32_t ring_u32, uint32_t full_u32,
+                                                 uint32_t empty_u32, int spw) {
+  using C = Cfg<B, FP8>;
+  WorkIter<false> wi;
+  wi.init(p, nullptr);
+  Seg it;
+  int k = -1, ls = 0;
+  uint32_t phase = 0;
+  while (wi.next(p, it)) {
+    if ((++k & (kConsumerWarps - 1)) != pw) continue;
+    const int nblk = (it.t1 - it.t0 + B - 1) / B;
+    const int ntiles = (it.t1 - it.t0 + kTileTokens - 1) / kTileTokens;
+    const int32_t* bt = p.bt + (int64_t)it.s * p.max_blocks + it.t0 / B;
+    const uint8_t* kbase = p.kc + (int64_t)it.kvh * p.kv_head_stride;
+    const uint8_t* vbase = p.vc + (int64_t)it.kvh * p.kv_head_stride;
+    int nid0 = __ldg(bt), nid1 = (C::kBlocksPerTile == 2 && nblk > 1) ? __ldg(bt + 1) : 0;
+    for (int t = 0; t < ntiles; ++t) {
+      const int b0 = t * C::kBlocksPerTile;
+      const int id0 = nid0, id1 = nid1;
+      const int nvalid = min(C::kBlocksPerTile, nblk - b0);
+      const int bn = b0 + C::kBlocksPerTile;
+      if (bn < nblk) {
+        nid0 = __ldg(bt + bn);
+        if (C::kBlocksPerTile == 2 && bn + 1 < nblk) nid1 = __ldg(bt + bn + 1);
+      }
+      const int stage = pw * spw + ls;
+      MBAR_WAIT(empty_u32 + 8u * stage, phase ^ 1u, 1, k, stage);
+      const uint32_t fb = full_u32 + 8u * stage;
+      mbar_expect_tx(fb, (uint32_t)(nvalid * 2 * C::kBlkBytes));
+      const uint32_t dst = ring_u32 + (uint32_t)stage * C::kStageBytes;
+      bulk_g2s(dst, kbase + (int64_t)id0 * p.kv_block_stride, C::kBlkBytes, fb);
+      bulk_g2s(dst + C::kVOffset, vbase + (int64_t)id0 * p.kv_block_stride, C::kBlkBytes, fb);
+      if (C::kBlocksPerTile == 2 && nvalid == 2) {
+        bulk_g2s(dst + C::kBlkBytes, kbase + (int64_t)id1 * p.kv_block_stride, C::kBlkBytes, fb);
+        bulk_g2s(dst + C::kVOffset + C::kBlkBytes, vbase + (int64_t)id1 * p.kv_block_stride, C::kBlkBytes, fb);
+      }
+      if (++ls == spw) {
+        ls = 0;
+        phase ^= 1u;
+      }
+    }
+  }
+}
+
 // ---- flash layout ([num_blocks, block_size, num_kv_heads, D], NHD or HND strides; bf16) ---------------------
 // One token row of one kv head is D contiguous elements (256 B); the rows of a block are page_stride apart
 // (NHD: Hkv*D elements, HND: D).  Separate 256-byte bulk copies top out at ~4 TB/s (one TMA operation per ~18
