@@ -259,6 +259,6 @@ def reserve_workspace(query_like: torch.Tensor, max_seq_len: int, reset: bool = 
     `query_like` [num_seqs, num_heads, head_size] with contexts up to `max_seq_len`.  Not a reference op: the
     reference's paged_attention_v1 never splits and so has no workspace (csrc/attention/paged_attention_v1.cu:43-125).
     Call it once at warm-up on every stream that will run (or capture) paged_attention_v1 / paged_attention_flash, so
-    that those ops never allocate; without it their first call on a stream allocates ~5 MB lazily, and raises if that
+    that those ops never allocate; without it their first call on a stream allocates ~27 MB lazily, and raises if that
     first call happens under CUDA-graph capture."""
     torch.ops._C_b200.reserve_workspace(query_like, max_seq_len, reset)

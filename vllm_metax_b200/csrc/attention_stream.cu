@@ -643,7 +643,7 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
       // head / tail slot and the CTA that delivers the pair's last segment merges them (same arithmetic
       // as the reference reduce, csrc/attention/attention_kernels.cuh:594-657) ----------------------------
       const bool whole = it.starts && it.ends;
-      const int slot = ((int)blockIdx.x * 2 + (it.starts ? 1 : 0)) * kFlatMaxGroup;
+      const int slot = (it.rid * 2 + (it.starts ? 1 : 0)) * p.G;
       for (int h = tid >> 7; h < NH; h += (kConsumerWarps * kWarpSize) >> 7) {
         if (h >= p.G) break;
         float M = -INFINITY;
@@ -673,8 +673,9 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
       if (!whole) {
         __threadfence();       // this thread's partials are visible device-wide
         consumer_bar_sync();   // ... and so are everyone's
-        const int c0 = cta_of_tile(it.pb, sched->T, sched->neff);
-        const int c1 = cta_of_tile(it.pb + it.n - 1, sched->T, sched->neff);
+        // ranges (static shares and dynamic chunks, numbered in tile order) that hold a piece of this pair
+        const int c0 = range_of_tile(sched, it.pb);
+        const int c1 = range_of_tile(sched, it.pb + it.n - 1);
         if (tid == 0) {
           int* cnt = p.counters + it.s * p.Hkv + it.kvh;
           const int old = atomicAdd(cnt, 1);
@@ -686,13 +687,13 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
         if (*merge_flag) {
           __threadfence();
           for (int h = tid >> 7; h < p.G; h += (kConsumerWarps * kWarpSize) >> 7) {
-            // CTA c0 holds the segment that starts the pair (tail slot), the others their head slot
+            // range c0 holds the segment that starts the pair (tail slot), the others their head slot
             float M = -INFINITY;
             for (int c = c0; c <= c1; ++c)
-              M = fmaxf(M, __ldcg(p.ws_m + (c * 2 + (c == c0 ? 1 : 0)) * kFlatMaxGroup + h));
+              M = fmaxf(M, __ldcg(p.ws_m + (c * 2 + (c == c0 ? 1 : 0)) * p.G + h));
             float lsum = 0.f, o = 0.f;
             for (int c = c0; c <= c1; ++c) {
-              const int sl = (c * 2 + (c == c0 ? 1 : 0)) * kFlatMaxGroup + h;
+              const int sl = (c * 2 + (c == c0 ? 1 : 0)) * p.G + h;
               const float wgt = exp2f(__ldcg(p.ws_m + sl) - M);
               lsum = fmaf(__ldcg(p.ws_l + sl), wgt, lsum);
               o = fmaf(__ldcg(p.ws_o + (int64_t)sl * kD + d), wgt, o);
@@ -781,7 +782,7 @@ bool stream_variant_eligible(const b200_paged_attn_params_t& p, const char** why
   else if (p.head_size != kD) w = "head_size is not 128";
   else if (p.block_size != 16 && p.block_size != 32) w = "block_size is not 16 or 32";
   else if (G < 1 || G > kFlatMaxGroup) w = "GQA group size above 16";
-  else if ((uint64_t)p.num_seqs * p.num_kv_heads > kFlatCounterSlots) w = "more (seq, kv head) pairs than arrival counters";
+  else if ((uint64_t)p.num_seqs * p.num_kv_heads >= kFlatCounterSlots) w = "more (seq, kv head) pairs than arrival counters";
   else if ((p.kv_block_stride * eb) % 16 != 0 || (p.kv_head_stride * eb) % 16 != 0) w = "KV strides not 16-byte multiples";
   else if ((reinterpret_cast<uintptr_t>(p.key_cache) | reinterpret_cast<uintptr_t>(p.value_cache)) % 16 != 0) w = "KV cache not 16-byte aligned";
   else if (p.q_stride % 8 != 0 || reinterpret_cast<uintptr_t>(p.query) % 16 != 0) w = "query rows not 16-byte aligned";
@@ -812,7 +813,7 @@ bool stream_flash_eligible(const b200_paged_attn_params_t& p, const char** why) 
   else if (p.head_size != kD) w = "head_size is not 128";
   else if (p.block_size < 16 || p.block_size % 16 != 0) w = "block_size is not a multiple of 16";
   else if (G < 1 || G > kFlatMaxGroup) w = "GQA group size above 16";
-  else if ((uint64_t)p.num_seqs * p.num_kv_heads > kFlatCounterSlots) w = "more (seq, kv head) pairs than arrival counters";
+  else if ((uint64_t)p.num_seqs * p.num_kv_heads >= kFlatCounterSlots) w = "more (seq, kv head) pairs than arrival counters";
   else if ((p.kv_block_stride * 2) % 16 != 0 || (p.kv_head_stride * 2) % 16 != 0 || (p.kv_page_stride * 2) % 16 != 0)
     w = "KV strides not 16-byte multiples";
   else if ((reinterpret_cast<uintptr_t>(p.key_cache) | reinterpret_cast<uintptr_t>(p.value_cache)) % 16 != 0) w = "KV cache not 16-byte aligned";
@@ -898,6 +899,23 @@ int launch_stream_flash_t(StreamParams& sp, cudaStream_t s) {
 }
 }  // namespace
 
+namespace {
+// flat schedule: arrival counters, the claim counter of the dynamic region, partial-result slots packed by G
+void set_flat_workspace(StreamParams& sp, void* workspace, bool fp8) {
+  sp.counters = static_cast<int*>(workspace);
+  sp.claim_counter = sp.counters + (kFlatCounterSlots - 1);
+  float* slots = reinterpret_cast<float*>(static_cast<char*>(workspace) + kFlatCounterBytes);
+  const size_t nslots = (size_t)kFlatMaxRanges * 2 * sp.G;
+  sp.ws_o = slots;
+  sp.ws_m = slots + nslots * kD;
+  sp.ws_l = sp.ws_m + nslots;
+  // smallest dynamic chunk: ~64 KiB of cache (4 tiles bf16, 8 tiles fp8) — about a microsecond of one SM's stream, and
+  // the price of one partial-result hand-over.  B200_STREAM_DYN=-1 switches the dynamic region off, > 0 sets the size.
+  const int knob = env_int("B200_STREAM_DYN");
+  sp.dyn_min = knob < 0 ? 0 : knob > 0 ? knob : (fp8 ? 8 : 4);
+}
+}  // namespace
+
 int launch_attention_stream_flash(const b200_paged_attn_params_t& p, void* workspace, cudaStream_t s) {
   const char* why = nullptr;
   B200_REQUIRE(stream_flash_eligible(p, &why), B200_ERR_UNSUPPORTED, "paged_attention_flash: %s", why);
@@ -909,11 +927,7 @@ int launch_attention_stream_flash(const b200_paged_attn_params_t& p, void* works
   if (rc != B200_OK) return rc;
   rc = encode_flash_map(&sp.tm_v, p.value_cache, p);
   if (rc != B200_OK) return rc;
-  sp.counters = static_cast<int*>(workspace);
-  float* slots = reinterpret_cast<float*>(static_cast<char*>(workspace) + kFlatCounterBytes);
-  sp.ws_o = slots;
-  sp.ws_m = slots + (size_t)kFlatMaxCtas * 2 * kFlatMaxGroup * kD;
-  sp.ws_l = sp.ws_m + (size_t)kFlatMaxCtas * 2 * kFlatMaxGroup;
+  set_flat_workspace(sp, workspace, p.kv_dtype == B200_KV_FP8_E4M3);
   const int64_t tiles = (int64_t)p.num_seqs * p.num_kv_heads * ((p.max_seq_len + kTileTokens - 1) / kTileTokens);
   sp.total_items = (int)(tiles < (int64_t)kFlatMaxCtas ? tiles : (int64_t)kFlatMaxCtas);
   if (sp.total_items == 0) return B200_OK;
@@ -943,11 +957,7 @@ int launch_attention_stream_flat(const b200_paged_attn_params_t& p, void* worksp
   B200_REQUIRE(stream_variant_eligible(p, &why), B200_ERR_UNSUPPORTED, "stream kernel not eligible: %s", why);
   B200_REQUIRE(workspace != nullptr, B200_ERR_WORKSPACE, "stream kernel: workspace missing");
   StreamParams sp = fill_stream_params(p);
-  sp.counters = static_cast<int*>(workspace);
-  float* slots = reinterpret_cast<float*>(static_cast<char*>(workspace) + kFlatCounterBytes);
-  sp.ws_o = slots;
-  sp.ws_m = slots + (size_t)kFlatMaxCtas * 2 * kFlatMaxGroup * kD;
-  sp.ws_l = sp.ws_m + (size_t)kFlatMaxCtas * 2 * kFlatMaxGroup;
+  set_flat_workspace(sp, workspace, p.kv_dtype == B200_KV_FP8_E4M3);
   // upper bound of the tile count (the kernel derives the real one from seq_lens on the device)
   const int64_t tiles = (int64_t)p.num_seqs * p.num_kv_heads * ((p.max_seq_len + kTileTokens - 1) / kTileTokens);
   sp.total_items = (int)(tiles < (int64_t)kFlatMaxCtas ? tiles : (int64_t)kFlatMaxCtas);

@@ -141,14 +141,20 @@ struct SplitOut {
 // CTA it touches in that CTA's "head" slot (segment that does not start the pair) or "tail" slot (segment
 // that starts the pair but does not finish it); the CTA that delivers the pair's last segment — found with
 // an arrival counter per pair — merges them.  Slots and counters live in the caller's workspace:
-//   [counters: kFlatCounterSlots ints, all zero between launches][slots: kFlatMaxCtas x 2 x kFlatMaxGroup x (D+2) f32]
+//   [counters: kFlatCounterSlots ints, all zero between launches][slots: kFlatMaxRanges x 2 x kFlatMaxGroup x (D+2) f32]
+// (a "range" is a CTA's static share or one dynamically claimed chunk of the tail region; the streaming kernel packs
+// its slots by the launch's group size G: slot (range, head/tail, h) = (range * 2 + tail) * G + h).
 constexpr int kFlatMaxCtas = 256;
 constexpr int kFlatMaxGroup = 16;   // query heads per kv head served by the streaming kernel
 constexpr int kFlatHeadSize = 128;
-constexpr uint64_t kFlatCounterSlots = 1u << 18;
+// Ranges of the flat tile sequence: one static range per CTA plus the dynamically claimed chunks of the tail
+// region (stream_common.cuh: "guided" chunk sizes, at most kDynMaxLevels levels of one chunk per CTA each).
+constexpr int kDynMaxLevels = 5;
+constexpr int kFlatMaxRanges = kFlatMaxCtas * (1 + kDynMaxLevels);
+constexpr uint64_t kFlatCounterSlots = 1u << 18;  // the last int is the claim counter of the dynamic region
 constexpr uint64_t kFlatCounterBytes = kFlatCounterSlots * sizeof(int);
 constexpr uint64_t kFlatSlotBytes =
-    (uint64_t)kFlatMaxCtas * 2 * kFlatMaxGroup * (kFlatHeadSize + 2) * sizeof(float);
+    (uint64_t)kFlatMaxRanges * 2 * kFlatMaxGroup * (kFlatHeadSize + 2) * sizeof(float);
 constexpr uint64_t kFlatWorkspaceBytes = kFlatCounterBytes + kFlatSlotBytes;
 
 // ---- kernel-family entry points (defined in the .cu files) ------------------

@@ -42,10 +42,12 @@ struct StreamParams {
   __nv_bfloat16* out;
   float* lse;               // optional [H, S] log-sum-exp of the scaled logits (natural log), with the final output
   SplitOut so;              // item schedule only
-  float* ws_o;              // flat schedule: slots [cta][2][kFlatMaxGroup][kD] (unnormalised partial outputs)
-  float* ws_m;              //                      [cta][2][kFlatMaxGroup]     (max logit, log2 units)
-  float* ws_l;              //                      [cta][2][kFlatMaxGroup]     (sum exp)
+  float* ws_o;              // flat schedule: slots [range][2][G][kD] (unnormalised partial outputs)
+  float* ws_m;              //                      [range][2][G]     (max logit, log2 units)
+  float* ws_l;              //                      [range][2][G]     (sum exp)
   int* counters;            //                      [S * Hkv] arrival counters, zero between launches
+  int* claim_counter;       //                      next chunk of the dynamic tail region, zero between launches
+  int dyn_min;              //                      tiles of the smallest dynamic chunk (0: static schedule only)
   int64_t q_stride;         // elements
   int64_t kv_block_stride;  // bytes
   int64_t kv_head_stride;   // bytes
@@ -189,14 +191,29 @@ struct Seg {
   bool starts, ends;   // flat: the segment contains the first / last tile of its pair
   long long pb;        // flat: position of the pair's first tile in the flat tile sequence
   int n;               // flat: tiles of the pair
+  int rid;             // flat: range (static share of a CTA, or dynamic chunk) the segment belongs to
 };
-// flat schedule of this CTA, computed once by warp 0 (shared memory)
+// Flat schedule of this CTA, computed once by warp 0 (shared memory).
+// The flat tile sequence [0, T) is cut into a STATIC region [0, Ts): one equal contiguous range per CTA (range id =
+// CTA index), and a DYNAMIC tail region [Ts, T) that CTAs claim chunk by chunk as they run out of work (range ids
+// neff, neff + 1, ... in tile order), so that SMs that stream faster than others (the spread between the first and the
+// last CTA of an equal split is ~10 % of the kernel: profiles/r2_timeline.log) take more of it.  Chunk sizes are "guided":
+// nlev levels of neff chunks each, level l made of chunks of dyn_min << (nlev - 1 - l) tiles — big chunks first, dyn_min
+// tiles at the very end.
+constexpr int kDynMaxClaims = kFlatMaxCtas * kDynMaxLevels / 2 + 2;  // claims one CTA can make (in practice a handful)
+constexpr int kSeqBlocks = 256;  // 32-sequence blocks with a prefix entry: dynamic region only for S <= 8192
 struct Sched {
-  long long f0, f1;    // this CTA's tile range
+  long long f0, f1;    // this CTA's static tile range
   long long base0;     // flat position of the first tile of sequence s0
   long long T;         // tiles in the batch
+  long long Ts;        // tiles in the static region
   int s0;              // sequence holding tile f0
-  int neff;            // CTAs that own a non-empty range = min(gridDim.x, T)
+  int neff;            // CTAs that own a non-empty static range = min(gridDim.x, T)
+  int nlev;            // levels of the dynamic region (0: none)
+  int ndyn;            // dynamic chunks = neff * nlev
+  int dyn_min;
+  int claims[kDynMaxClaims];       // k-th claim of this CTA: -1 not made, -2 being made, else the chunk index
+  long long blkpre[kSeqBlocks + 1];  // tiles (per kv head) of the sequences before sequence 32 * b
 };
 __device__ __forceinline__ int tiles_of(int L) { return L > 0 ? (L + kTileTokens - 1) / kTileTokens : 0; }
 __device__ __forceinline__ long long warp_sum_ll(long long v) {
@@ -208,22 +225,57 @@ __device__ __forceinline__ long long warp_sum_ll(long long v) {
 __device__ __forceinline__ int cta_of_tile(long long x, long long T, int n) {
   return (int)(((x + 1) * n - 1) / T);
 }
+// first tile / tile count of dynamic chunk j
+__device__ __forceinline__ void dyn_chunk(const Sched* sc, int j, long long& start, int& len) {
+  const int l = j / sc->neff, i = j - l * sc->neff;
+  len = sc->dyn_min << (sc->nlev - 1 - l);
+  // levels before l hold neff * dyn_min * (2^nlev - 2^(nlev - l)) tiles
+  start = sc->Ts + (long long)sc->neff * sc->dyn_min * ((1 << sc->nlev) - (1 << (sc->nlev - l))) + (long long)i * len;
+}
+// range id of flat tile x (ranges are numbered in tile order)
+__device__ __forceinline__ int range_of_tile(const Sched* sc, long long x) {
+  if (x < sc->Ts) return cta_of_tile(x, sc->Ts, sc->neff);
+  long long y = x - sc->Ts;
+  for (int l = 0; l < sc->nlev; ++l) {
+    const int len = sc->dyn_min << (sc->nlev - 1 - l);
+    const long long lvl = (long long)sc->neff * len;
+    if (y < lvl) return sc->neff * (1 + l) + (int)(y / len);
+    y -= lvl;
+  }
+  return sc->neff * (1 + sc->nlev) - 1;  // not reached for x < T
+}
 __device__ void compute_sched(const StreamParams& p, Sched* sc, int lane) {
-  long long tot = 0;
-  for (int i = lane; i < p.S; i += 32) tot += tiles_of(__ldg(p.seq_lens + i));
-  tot = warp_sum_ll(tot);
-  const long long T = tot * p.Hkv;
+  // tiles per kv head before every 32nd sequence, and the total
+  long long running = 0;
+  for (int b = 0; b < p.S; b += 32) {
+    const long long n = b + lane < p.S ? tiles_of(__ldg(p.seq_lens + b + lane)) : 0;
+    if (lane == 0 && (b >> 5) <= kSeqBlocks) sc->blkpre[b >> 5] = running;
+    running += warp_sum_ll(n);
+  }
+  if (lane == 0 && ((p.S + 31) >> 5) <= kSeqBlocks) sc->blkpre[(p.S + 31) >> 5] = running;
+  const long long T = running * p.Hkv;
   const int neff = (int)(T < (long long)gridDim.x ? T : (long long)gridDim.x);
+  // dynamic region: ~15 % of the tiles, only when every CTA has a static share worth splitting
+  int nlev = 0;
+  if (p.dyn_min > 0 && neff == (int)gridDim.x && p.S <= 32 * kSeqBlocks) {
+    const long long per = T / neff;
+    while (nlev < kDynMaxLevels && (long long)p.dyn_min * ((2 << nlev) - 1) * 100 <= per * 15) ++nlev;
+    while (nlev > 0 && neff * (1 + nlev) > kFlatMaxRanges) --nlev;
+  }
+  const long long Ts = T - (long long)neff * p.dyn_min * ((1 << nlev) - 1);
   long long f0 = 0, f1 = 0;
   if ((int)blockIdx.x < neff) {
-    f0 = (long long)blockIdx.x * T / neff;
-    f1 = (long long)(blockIdx.x + 1) * T / neff;
+    f0 = (long long)blockIdx.x * Ts / neff;
+    f1 = (long long)(blockIdx.x + 1) * Ts / neff;
   }
   if (lane == 0) {
-    sc->f0 = f0; sc->f1 = f1; sc->T = T; sc->neff = neff; sc->s0 = 0; sc->base0 = 0;
+    sc->f0 = f0; sc->f1 = f1; sc->T = T; sc->Ts = Ts; sc->neff = neff; sc->s0 = 0; sc->base0 = 0;
+    sc->nlev = nlev; sc->ndyn = neff * nlev; sc->dyn_min = p.dyn_min;
   }
+  if (nlev > 0)
+    for (int i = lane; i < kDynMaxClaims; i += 32) sc->claims[i] = -1;
   if (f0 >= f1) return;
-  long long running = 0;  // tiles per kv head before sequence `b`
+  running = 0;  // tiles per kv head before sequence `b`
   for (int b = 0; b < p.S; b += 32) {
     const int n = b + lane < p.S ? tiles_of(__ldg(p.seq_lens + b + lane)) : 0;
     long long incl = n;
@@ -246,13 +298,17 @@ __device__ void compute_sched(const StreamParams& p, Sched* sc, int lane) {
   }
 }
 
-template <bool FLAT>
+// SOLO: the caller is a single live lane of its warp (producer lanes); otherwise all 32 lanes call in lockstep.
+template <bool FLAT, bool SOLO = false>
 struct WorkIter {
   long long f, f1, base;
-  int s, n, L, item;
-  __device__ __forceinline__ void init(const StreamParams& p, const Sched* sc) {
+  int s, n, L, item, rid, kclaim;
+  Sched* sc;
+  __device__ __forceinline__ void init(const StreamParams& p, Sched* sched) {
     if constexpr (FLAT) {
+      sc = sched;
       f = sc->f0; f1 = sc->f1; base = sc->base0; s = sc->s0;
+      rid = (int)blockIdx.x; kclaim = 0;
       L = 0; n = 0;
       if (f < f1) {
         L = __ldg(p.seq_lens + s);
@@ -262,12 +318,49 @@ struct WorkIter {
       item = (int)blockIdx.x - (int)gridDim.x;
     }
   }
+  // Claim the CTA's next dynamic chunk.  The first of the CTA's iterators (producer lanes, consumer warps) to get
+  // here takes it from the global counter and publishes it in shared memory; the others read it there.
+  __device__ __forceinline__ bool next_range(const StreamParams& p) {
+    if (sc->nlev == 0 || kclaim >= kDynMaxClaims) return false;
+    int j = 0;
+    if (SOLO || (threadIdx.x & 31) == 0) {
+      volatile int* slot = sc->claims + kclaim;
+      j = atomicCAS(sc->claims + kclaim, -1, -2);
+      if (j == -1) {
+        j = atomicAdd(p.claim_counter, 1);
+        // every CTA makes exactly one failing claim: the last of them leaves the counter at zero for the next launch
+        if (j == sc->ndyn + (int)gridDim.x - 1) *p.claim_counter = 0;
+        if (j > sc->ndyn) j = sc->ndyn;
+        __threadfence_block();
+        *slot = j;
+      } else {
+        while (j < 0) j = *slot;
+      }
+    }
+    if constexpr (!SOLO) j = __shfl_sync(0xffffffffu, j, 0);
+    ++kclaim;
+    if (j >= sc->ndyn) {
+      kclaim = kDynMaxClaims;  // exhausted
+      return false;
+    }
+    int len;
+    dyn_chunk(sc, j, f, len);
+    f1 = f + len;
+    rid = sc->neff + j;
+    return true;
+  }
   __device__ __forceinline__ bool next(const StreamParams& p, Seg& g) {
     if constexpr (FLAT) {
-      if (f >= f1) return false;
+      if (f >= f1 && !next_range(p)) return false;
       while (f >= base + (long long)p.Hkv * n) {  // f < f1 <= T: a later sequence holds tile f
         base += (long long)p.Hkv * n;
         ++s;
+        if ((s & 31) == 0 && sc->nlev > 0) {  // whole 32-sequence blocks before tile f are skipped through the prefix table
+          int b = s >> 5;
+          while (32 * (b + 1) < p.S && sc->blkpre[b + 1] * p.Hkv <= f) ++b;
+          s = 32 * b;
+          base = sc->blkpre[b] * p.Hkv;
+        }
         L = __ldg(p.seq_lens + s);
         n = tiles_of(L);
       }
@@ -280,7 +373,7 @@ struct WorkIter {
       g.s = s; g.kvh = kvh; g.L = L; g.part = 0;
       g.t0 = tile0 * kTileTokens;
       g.t1 = min(tile1 * kTileTokens, L);
-      g.starts = tile0 == 0; g.ends = se == pe; g.pb = pb; g.n = n;
+      g.starts = tile0 == 0; g.ends = se == pe; g.pb = pb; g.n = n; g.rid = rid;
       f = se;
       return true;
     } else {
@@ -296,7 +389,7 @@ struct WorkIter {
         g.t0 = g.part * p.so.chunk;
         if (g.t0 >= g.L) continue;
         g.t1 = min(g.t0 + p.so.chunk, g.L);
-        g.starts = g.ends = false; g.pb = 0; g.n = 0;
+        g.starts = g.ends = false; g.pb = 0; g.n = 0; g.rid = 0;
         return true;
       }
     }
@@ -315,7 +408,7 @@ struct Cfg {
 // One issuing lane of producer warp `pw` (of NP): walks the block table of the CTA's tile stream and streams the
 // K chunk and V chunk of every block of its tiles (gt == pw mod NP) into the ring with 1-D TMA bulk copies.
 template <int B, bool FP8, bool FLAT, int NP>
-__device__ __forceinline__ void producer_loop(const StreamParams& p, const Sched* sched, int pw, uint32_t ring_u32,
+__device__ __forceinline__ void producer_loop(const StreamParams& p, Sched* sched, int pw, uint32_t ring_u32,
                                               uint32_t full_u32, uint32_t empty_u32, int nst) {
   using C = Cfg<B, FP8>;
   constexpr int kProducerWarps = NP;
@@ -323,7 +416,7 @@ __device__ __forceinline__ void producer_loop(const StreamParams& p, const Sched
   int stage = pw;                   // g_next % nst (nst >= kProducerWarps)
   uint32_t phase = 0;               // (g_next / nst) & 1
   uint32_t tile_base = 0;
-  WorkIter<FLAT> wi;
+  WorkIter<FLAT, true> wi;
   wi.init(p, sched);
   Seg it;
   int item = -1;  // segment ordinal (debug messages)
@@ -388,19 +481,36 @@ template <int B, bool FP8>
 __device__ __forceinline__ void producer_loop_pw(const StreamParams& p, int pw, uint32_t ring_u32, uint32_t full_u32,
                                                  uint32_t empty_u32, int spw) {
   using C = Cfg<B, FP8>;
-  WorkIter<false> wi;
+  WorkIter<false, true> wi;
   wi.init(p, nullptr);
-  Seg it;
   int k = -1, ls = 0;
   uint32_t phase = 0;
-  while (wi.next(p, it)) {
-    if ((++k & (kConsumerWarps - 1)) != pw) continue;
+  auto next_mine = [&](Seg& sg) -> bool {
+    while (wi.next(p, sg))
+      if ((++k & (kConsumerWarps - 1)) == pw) return true;
+    return false;
+  };
+  // The first block ids of the NEXT item are fetched while the current item streams: at 16 tiles per item an exposed
+  // block-table load per item (~1 us under load) left the warp's three-stage slice empty for ~10 % of the time.
+  Seg it, nx;
+  bool has = next_mine(nx);
+  int fid0 = 0, fid1 = 0;
+  auto first_ids = [&](const Seg& sg) {
+    const int32_t* b = p.bt + (int64_t)sg.s * p.max_blocks + sg.t0 / B;
+    fid0 = __ldg(b);
+    fid1 = (C::kBlocksPerTile == 2 && sg.t1 - sg.t0 > B) ? __ldg(b + 1) : 0;
+  };
+  if (has) first_ids(nx);
+  while (has) {
+    it = nx;
     const int nblk = (it.t1 - it.t0 + B - 1) / B;
     const int ntiles = (it.t1 - it.t0 + kTileTokens - 1) / kTileTokens;
     const int32_t* bt = p.bt + (int64_t)it.s * p.max_blocks + it.t0 / B;
     const uint8_t* kbase = p.kc + (int64_t)it.kvh * p.kv_head_stride;
     const uint8_t* vbase = p.vc + (int64_t)it.kvh * p.kv_head_stride;
-    int nid0 = __ldg(bt), nid1 = (C::kBlocksPerTile == 2 && nblk > 1) ? __ldg(bt + 1) : 0;
+    int nid0 = fid0, nid1 = fid1;
+    has = next_mine(nx);
+    if (has) first_ids(nx);
     for (int t = 0; t < ntiles; ++t) {
       const int b0 = t * C::kBlocksPerTile;
       const int id0 = nid0, id1 = nid1;
@@ -450,7 +560,7 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* tmap, int 
 // One issuing lane of producer warp `pw`: per tile, up to 8 boxes (K and V, two 16-token halves, two 64-dim halves).
 template <bool FLAT, int NP>
 __device__ __forceinline__ void producer_loop_flash(const StreamParams& p, const void* tm_k, const void* tm_v,
-                                                    const Sched* sched, int pw, uint32_t ring_u32, uint32_t full_u32,
+                                                    Sched* sched, int pw, uint32_t ring_u32, uint32_t full_u32,
                                                     uint32_t empty_u32, int nst) {
   constexpr int kProducerWarps = NP;
   uint32_t g_next = (uint32_t)pw;
@@ -458,7 +568,7 @@ __device__ __forceinline__ void producer_loop_flash(const StreamParams& p, const
   uint32_t phase = 0;
   uint32_t tile_base = 0;
   const int B = p.block_size;
-  WorkIter<FLAT> wi;
+  WorkIter<FLAT, true> wi;
   wi.init(p, sched);
   Seg it;
   int item = -1;

@@ -58,7 +58,7 @@ bool is_cache_byte_type(at::ScalarType t) { return t == at::kByte || t == at::kF
 // (csrc/torch_bindings.cpp:45-55) and the reference's ops allocate nothing (SURVEY.md §8b "Ownership"), so the
 // allocation lives OUTSIDE the attention ops: `_C_b200::reserve_workspace` (called by import_kernels()-time warm-up /
 // the plugin's profile run) sizes it; the attention ops only look it up.  For the streaming kernels the size is a
-// constant (kFlatWorkspaceBytes, ~5.3 MB); only the generic kernel's split-KV partials grow with the shape.  A
+// constant (kFlatWorkspaceBytes, ~27 MB); only the generic kernel's split-KV partials grow with the shape.  A
 // call that finds no (or too small a) buffer allocates it lazily — unless the stream is being captured into a CUDA
 // graph, where an allocation would be illegal: that raises and names reserve_workspace.  Work on one stream is
 // ordered, so reuse across calls is safe.
