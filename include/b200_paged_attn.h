@@ -536,6 +536,10 @@ int b200_abi_version(void);
  * B200_ERR_UNSUPPORTED instead of falling back. */
 int b200_set_attention_variant(int variant);
 int b200_last_attention_variant(void);
+/* Experiment switch (no reference counterpart): min_chunk_tiles > 0 lets the flat schedule of the streaming kernel hand
+ * out the last ~15 % of the tiles dynamically in chunks of at least that many 32-token tiles; 0 = static split
+ * (default); < 0 = follow the B200_STREAM_DYN environment variable.  Results are identical either way. */
+int b200_set_stream_dynamic(int min_chunk_tiles);
 
 /* Number of kernel launches the library has enqueued from this process since
  * load (bench.py reports it as gpu_launches). */

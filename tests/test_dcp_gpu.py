@@ -194,3 +194,32 @@ def test_dcp_exchange_world1():
         xch.close()
     finally:
         dist.destroy_process_group()
+
+
+def test_dcp_kernels_refuse_cuda_graph_capture():
+    """The step number is a host-side kernel argument: a replayed graph would wait for a step that has long passed
+    (ADVICE r1).  Both C entry points return B200_ERR_UNSUPPORTED under capture; DcpExchange raises."""
+    from vllm_metax_b200 import _native as native
+
+    dev = torch.device("cuda", 0)
+    S, Hl, D, world = 2, 4, 128, 1
+    q = torch.zeros(S, Hl, D, dtype=torch.bfloat16, device=dev)
+    qbuf = torch.zeros(S, Hl, D, dtype=torch.bfloat16, device=dev)
+    flags = torch.zeros(1, 16, dtype=torch.int32, device=dev)
+    counter = torch.zeros(1, dtype=torch.int32, device=dev)
+    side = torch.cuda.Stream()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        torch.cuda.synchronize()
+        g.capture_begin()
+        try:
+            with pytest.raises(RuntimeError, match="CUDA graph"):
+                native.dcp_gather_query([qbuf.data_ptr()], [flags[0].data_ptr()], q, counter.data_ptr(), 0, 1, side.cuda_stream)
+            out = torch.empty(S, Hl, D, dtype=torch.bfloat16, device=dev)
+            lse = torch.empty(Hl, S, dtype=torch.float32, device=dev)
+            with pytest.raises(RuntimeError, match="CUDA graph"):
+                native.dcp_exchange_fold([qbuf.data_ptr()], [lse.data_ptr()], [flags[0].data_ptr()], out, lse, 0, S, Hl, D, 1,
+                                         side.cuda_stream)
+        finally:
+            g.capture_end()
+    torch.cuda.synchronize()

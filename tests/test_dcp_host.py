@@ -108,3 +108,37 @@ def test_dcp_decode_equals_unsharded_attention(world):
         for r in range(world):
             err, lerr = ret[r]
             assert err <= 1e-5 and lerr <= 1e-5, (r, err, lerr)
+
+
+def test_reference_local_length_rule_over_reads_when_world_divides_length():
+    """The reference computes the per-rank length as L // N + (rank <= (L - 1) % N)
+    (vllm_metax/v1/attention/backends/flash_attn.py:425-429).  With token t stored on rank t % N, that is the ownership
+    count except when N divides L, where it is ONE TOO MANY ON EVERY RANK: the extra position is the slot the NEXT token
+    will be written to — stale cache today.  This test demonstrates the over-read on a concrete shard (the deliberate
+    divergence of dcp_local_seq_lens from the reference formula) and that attention over the over-read shard differs
+    from attention over the sequence."""
+    for world in (2, 4, 8):
+        for L in (world, 4 * world, 64 * world):
+            lens = torch.tensor([L], dtype=torch.int32)
+            for rank in range(world):
+                owned = sum(1 for t in range(L) if dcp_token_owner(t, world)[0] == rank)
+                ours = int(dcp_local_seq_lens(lens, world, rank))
+                ref_rule = L // world + (1 if rank <= (L - 1) % world else 0)
+                assert ours == owned == L // world
+                assert ref_rule == owned + 1, "the reference rule reads one slot past the rank's tokens when N | L"
+        # one off a multiple: the two rules agree
+        lens = torch.tensor([4 * world + 1], dtype=torch.int32)
+        for rank in range(world):
+            L = int(lens[0])
+            assert int(dcp_local_seq_lens(lens, world, rank)) == L // world + (1 if rank <= (L - 1) % world else 0)
+    # effect on the result: a shard padded by one stale slot changes the attention output
+    world, L, D = 2, 8, 16
+    g = torch.Generator().manual_seed(0)
+    q = torch.randn(1, D, generator=g)
+    kv = torch.randn(L, D, generator=g)
+    stale = torch.full((1, D), 3.0)  # what an earlier request left in the next slot of rank 0
+    shard0 = kv[0::2]
+    exact = torch.softmax(q @ shard0.T / D ** 0.5, -1) @ shard0
+    over = torch.cat([shard0, stale])
+    wrong = torch.softmax(q @ over.T / D ** 0.5, -1) @ over
+    assert (exact - wrong).abs().max() > 1e-2

@@ -355,3 +355,27 @@ def test_umma_fp8_deterministic(ops):
     for _ in range(5):
         b, _ = _run_umma(ops, "v1", d)
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("min_chunk", [2, 8])
+@pytest.mark.parametrize("shape", [(64, 32, 8, 16, "auto", 2100), (40, 16, 16, 32, "fp8", 3000), (9, 64, 8, 16, "auto", 9000),
+                                   (200, 8, 1, 16, "fp8", 700)])
+def test_flat_schedule_dynamic_tail_region(ops, min_chunk, shape):
+    """The opt-in dynamic tail of the flat schedule (b200_set_stream_dynamic; off by default because it measured slower):
+    chunks claimed through a device counter, partial slots indexed by range.  Same results as the oracle, counters and
+    claim counter left at zero (a second launch on the same workspace agrees), v1 and the flash layout."""
+    from vllm_metax_b200 import _native
+
+    S, H, Hkv, B, kvd, L = shape
+    d = orc.make_decode_inputs(S, H, Hkv, 128, B, max_seq_len=L, num_blocks=max(2048, S * ((L + B - 1) // B)),
+                               kv_cache_dtype=kvd, seed=S + L, unique_blocks=False)
+    ref = _oracle(d)
+    _native.set_stream_dynamic(min_chunk)
+    try:
+        for _ in range(3):
+            out, _ = _run(ops, "v1", d)
+            _check(out, ref, ATOL_AUTO if kvd == "auto" else ATOL_BAR)
+    finally:
+        _native.set_stream_dynamic(-1)
+    out, _ = _run(ops, "v1", d)  # the static schedule on the same workspace afterwards
+    _check(out, ref, ATOL_AUTO if kvd == "auto" else ATOL_BAR)

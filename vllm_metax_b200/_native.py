@@ -48,6 +48,7 @@ EXPORTED_SYMBOLS = (
     "b200_abi_version",
     "b200_set_attention_variant",
     "b200_last_attention_variant",
+    "b200_set_stream_dynamic",
     "b200_launch_count",
 )
 
@@ -343,6 +344,14 @@ def set_attention_variant(v: int) -> None:
 
 def last_attention_variant() -> int:
     return int(load().b200_last_attention_variant())
+
+
+def set_stream_dynamic(min_chunk_tiles: int) -> None:
+    """Experiment switch of the flat schedule's dynamic tail region (0 = static split, the default)."""
+    lib = load()
+    lib.b200_set_stream_dynamic.argtypes = [C.c_int]
+    lib.b200_set_stream_dynamic.restype = C.c_int
+    check(lib.b200_set_stream_dynamic(int(min_chunk_tiles)))
 
 
 # ---- torch-tensor conveniences (pointers only; torch is plumbing here) ----------------------

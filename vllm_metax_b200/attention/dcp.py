@@ -216,6 +216,10 @@ class DcpExchange:
         """Step 1 (starts a new epoch): every rank pushes its heads into every rank's gathered query and waits for the
         others' pushes.  Returns this rank's gathered query [S, H, D] (a view of the exchange buffer)."""
         S, Hl, D = query.shape
+        if torch.cuda.is_current_stream_capturing():
+            # the step number is a host-side kernel argument: a replayed graph would wait for a step that has long
+            # passed and read the peers' buffers unsynchronised (the C entry points refuse capture as well)
+            raise RuntimeError("DcpExchange.forward_decode cannot be captured into a CUDA graph")
         self._epoch += 1
         plan = self._plan(S, Hl, D)[self._epoch & 1]
         if query.stride(1) != D or query.stride(2) != 1:

@@ -308,4 +308,12 @@ extern "C" int b200_set_attention_variant(int variant) {
   return B200_OK;
 }
 extern "C" int b200_last_attention_variant(void) { return g_last_variant; }
+extern "C" int b200_set_stream_dynamic(int min_chunk_tiles) {
+  if (min_chunk_tiles > 64) {
+    set_error("stream_dynamic: minimum chunk of %d tiles (max 64)", min_chunk_tiles);
+    return B200_ERR_INVALID_ARGUMENT;
+  }
+  set_stream_dynamic(min_chunk_tiles);
+  return B200_OK;
+}
 extern "C" uint64_t b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }

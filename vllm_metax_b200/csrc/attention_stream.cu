@@ -190,16 +190,8 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
   uint32_t stage = PW ? (uint32_t)warp * spw : (uint32_t)warp, parity = 0;
   WorkIter<FLAT> wi;
   wi.init(p, sched);
-  [[maybe_unused]] int kitem = -1;  // PW: ordinal of the item in the CTA's list; item k belongs to warp k mod 8
-  auto next_item = [&](Seg& sg) -> bool {
-    if constexpr (PW) {
-      while (wi.next(p, sg))
-        if ((++kitem & (kConsumerWarps - 1)) == warp) return true;
-      return false;
-    } else {
-      return wi.next(p, sg);
-    }
-  };
+  if constexpr (PW) wi.init_warp_items(warp);  // items k == warp (mod 8) of the CTA's list, as the warp's producer lane
+  auto next_item = [&](Seg& sg) -> bool { return wi.next(p, sg); };
   // ---- Q fragments (B operand: k = dims, n = heads) of a segment --------------------------------------
   // Loaded in two steps so that the global-memory latency of the NEXT segment's query overlaps the merge of the
   // current one (with 512-token items the exposed wait was ~1/3 of the per-item overhead): q_issue only issues the
@@ -900,6 +892,7 @@ int launch_stream_flash_t(StreamParams& sp, cudaStream_t s) {
 }  // namespace
 
 namespace {
+int g_dyn_override = -1;  // b200_set_stream_dynamic(): test hook, overrides the environment knob
 // flat schedule: arrival counters, the claim counter of the dynamic region, partial-result slots packed by G
 void set_flat_workspace(StreamParams& sp, void* workspace, bool fp8) {
   sp.counters = static_cast<int*>(workspace);
@@ -909,12 +902,19 @@ void set_flat_workspace(StreamParams& sp, void* workspace, bool fp8) {
   sp.ws_o = slots;
   sp.ws_m = slots + nslots * kD;
   sp.ws_l = sp.ws_m + nslots;
-  // smallest dynamic chunk: ~64 KiB of cache (4 tiles bf16, 8 tiles fp8) — about a microsecond of one SM's stream, and
-  // the price of one partial-result hand-over.  B200_STREAM_DYN=-1 switches the dynamic region off, > 0 sets the size.
-  const int knob = env_int("B200_STREAM_DYN");
-  sp.dyn_min = knob < 0 ? 0 : knob > 0 ? knob : (fp8 ? 8 : 4);
+  // The dynamic tail region is an EXPERIMENT that measured slower than the static split and is off unless
+  // B200_STREAM_DYN=<tiles of the smallest chunk> asks for it (profiles/r2_dyn_bench.log: C2 168 us static, 211 / 197 /
+  // 183 us with 4 / 8 / 16-tile minimum chunks): every claimed chunk costs a global atomic, a block-table fetch and a
+  // partial-result hand-over (fence + arrival counter) back to back, ~4 us under load, against the ~9 us of tail
+  // imbalance it was meant to recover.  Parity of the mechanism is covered by tests/test_paged_attention_gpu.py
+  // (b200_set_stream_dynamic).
+  (void)fp8;
+  const int knob = g_dyn_override >= 0 ? g_dyn_override : env_int("B200_STREAM_DYN");
+  sp.dyn_min = knob > 0 ? knob : 0;
 }
 }  // namespace
+
+void set_stream_dynamic(int min_chunk_tiles) { g_dyn_override = min_chunk_tiles; }
 
 int launch_attention_stream_flash(const b200_paged_attn_params_t& p, void* workspace, cudaStream_t s) {
   const char* why = nullptr;

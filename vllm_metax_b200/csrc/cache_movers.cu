@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(256) copy_blocks_kernel(const __grid_constant_
   if constexpr (VEC) {
     const int64_t n = a.block_bytes >> 4;
     for (int64_t i = (int64_t)blockIdx.z * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.z * blockDim.x)
-      reinterpret_cast<Vec16*>(d)[i] = ld_global_16(s + (i << 4));
+      reinterpret_cast<Vec16*>(d)[i] = ld_global_16_coherent(s + (i << 4));  // src and dst blocks share the allocation
   } else {
     for (int64_t i = (int64_t)blockIdx.z * blockDim.x + threadIdx.x; i < a.block_bytes;
          i += (int64_t)gridDim.z * blockDim.x)

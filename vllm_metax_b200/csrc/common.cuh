@@ -92,6 +92,17 @@ __device__ __forceinline__ Vec16 ld_global_16(const void* p) {
   return v;
 }
 
+// the same without the non-coherent path: for kernels that may read and write the same allocation (copy_blocks with
+// chained mappings, merge_attn_states whose output aliases an input), where ld.global.nc would be undefined
+__device__ __forceinline__ Vec16 ld_global_16_coherent(const void* p) {
+  Vec16 v;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.w[0]), "=r"(v.w[1]), "=r"(v.w[2]), "=r"(v.w[3])
+               : "l"(p)
+               : "memory");
+  return v;
+}
+
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
   for (int m = 16; m >= 1; m >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, m));
@@ -171,6 +182,7 @@ bool stream_flash_eligible(const b200_paged_attn_params_t& p, const char** why);
 int launch_attention_umma_fp8(const b200_paged_attn_params_t& p, const SplitOut& so, cudaStream_t s);
 int launch_attention_umma_fp8_flat(const b200_paged_attn_params_t& p, void* workspace, cudaStream_t s);
 bool umma_fp8_variant_eligible(const b200_paged_attn_params_t& p, const char** why);
+void set_stream_dynamic(int min_chunk_tiles);  // experiment switch of the flat schedule's dynamic tail region
 int launch_split_reduce(const b200_paged_attn_params_t& p, const SplitOut& so, cudaStream_t s);
 int device_sm_count();
 

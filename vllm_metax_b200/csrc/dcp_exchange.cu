@@ -22,6 +22,9 @@
 // (it cannot pass the wait of step k+1 before this rank has launched its step-k+1 kernel, which follows this rank's
 // step-k kernel on the stream), so the buffer of parity k%2 is not overwritten while step k is still being read.
 // Flags only grow, so "a peer is already one step ahead" also satisfies the wait.
+#include <stdio.h>
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -35,6 +38,7 @@ struct DcpFoldArgs {
   float* out_lse;
   int32_t rank, world, num_seqs, heads_local, head_size;
   uint32_t epoch;
+  uint64_t wait_limit_ns;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -65,7 +69,13 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
   return t;
 }
 
-constexpr uint64_t kWaitLimitNs = 10ull * 1000 * 1000 * 1000;  // a peer that never arrives traps instead of hanging
+// A peer that never arrives traps the kernel instead of hanging the GPU.  The limit rides in the kernel arguments
+// (B200_DCP_WAIT_SECONDS, default 120 s: a peer can be late for ordinary reasons — first-use module load, an
+// allocator stall, a debugger — and NCCL's own watchdog counts minutes); the trap reports who waited for whom.
+__device__ __noinline__ void wait_timed_out(const char* what, int rank, int peer, uint32_t epoch, uint32_t seen) {
+  printf("[b200 dcp] %s: rank %d waited for rank %d to reach step %u (flag at %u): giving up\n", what, rank, peer, epoch, seen);
+  __trap();
+}
 
 template <typename T>
 __global__ void __launch_bounds__(256) dcp_exchange_fold_kernel(const __grid_constant__ DcpFoldArgs a) {
@@ -79,9 +89,10 @@ __global__ void __launch_bounds__(256) dcp_exchange_fold_kernel(const __grid_con
     const uint32_t* f = a.peer_flags[a.rank] + threadIdx.x;
     const uint64_t t0 = globaltimer_ns();
     // flags only grow; the signed difference keeps the comparison right across a 2^32 wrap
-    while ((int32_t)(ld_acquire_sys(f) - a.epoch) < 0) {
+    uint32_t seen;
+    while ((int32_t)((seen = ld_acquire_sys(f)) - a.epoch) < 0) {
       __nanosleep(64);
-      if (globaltimer_ns() - t0 > kWaitLimitNs) __trap();
+      if (globaltimer_ns() - t0 > a.wait_limit_ns) wait_timed_out("exchange_fold", a.rank, (int)threadIdx.x, a.epoch, seen);
     }
   }
   __syncthreads();
@@ -149,6 +160,7 @@ struct DcpGatherArgs {
   int64_t q_stride;  // elements between sequences of `query`
   int32_t rank, world, num_seqs, heads_local, head_size;
   uint32_t epoch;
+  uint64_t wait_limit_ns;
 };
 
 template <typename T>
@@ -169,26 +181,51 @@ __global__ void __launch_bounds__(256) dcp_gather_query_kernel(const __grid_cons
     *reinterpret_cast<Vec16*>(dst) = v;
   }
   // One system fence per CTA, by the thread that counts the CTA in: the barrier orders every thread's stores before
-  // it (fences are cumulative), and the flag stores below are releases at system scope.
+  // the fence, the fence before the counter increment (release side).  The CTA that sees the full count fences AGAIN
+  // after reading the counter (acquire side), so that the other CTAs' peer stores are ordered before the flag stores
+  // below in the PTX memory model and not only in practice.
   __syncthreads();
   __shared__ bool last;
   if (threadIdx.x == 0) {
     asm volatile("fence.acq_rel.sys;" ::: "memory");
     const uint32_t prev = atomicAdd(a.cta_counter, 1u);
     last = prev == gridDim.x - 1;
-    if (last) *a.cta_counter = 0;  // the next launch on this stream starts from zero
+    if (last) {
+      asm volatile("fence.acq_rel.sys;" ::: "memory");
+      *a.cta_counter = 0;  // the next launch on this stream starts from zero
+    }
   }
   __syncthreads();
   if (!last || threadIdx.x >= a.world) return;
   st_release_sys(a.peer_flags[threadIdx.x] + a.rank, a.epoch);
   const uint32_t* f = a.peer_flags[a.rank] + threadIdx.x;
   const uint64_t t0 = globaltimer_ns();
-  while ((int32_t)(ld_acquire_sys(f) - a.epoch) < 0) {
+  uint32_t seen;
+  while ((int32_t)((seen = ld_acquire_sys(f)) - a.epoch) < 0) {
     __nanosleep(64);
-    if (globaltimer_ns() - t0 > kWaitLimitNs) __trap();
+    if (globaltimer_ns() - t0 > a.wait_limit_ns) wait_timed_out("gather_query", a.rank, (int)threadIdx.x, a.epoch, seen);
   }
 }
 
+uint64_t wait_limit_ns() {
+  static const uint64_t ns = [] {
+    const char* e = getenv("B200_DCP_WAIT_SECONDS");
+    const long long sec = e ? atoll(e) : 120;
+    return (uint64_t)(sec > 0 ? sec : 120) * 1000000000ull;
+  }();
+  return ns;
+}
+// The step number (epoch) is a host-side kernel argument: a CUDA graph would freeze it, every `flag >= epoch` wait of a
+// replay would already be satisfied and the ranks would read each other's buffers unsynchronised.  Until the step
+// number lives in device memory the exchange kernels refuse to be captured.
+bool stream_is_capturing(cudaStream_t s) {
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(s, &st) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return st != cudaStreamCaptureStatusNone;
+}
 }  // namespace
 }  // namespace b200
 
@@ -222,6 +259,9 @@ extern "C" int b200_dcp_exchange_fold(const b200_dcp_fold_params_t* p, void* str
   a.out_lse = p->out_lse;
   a.rank = p->rank, a.world = p->world, a.num_seqs = p->num_seqs, a.heads_local = p->heads_local;
   a.head_size = p->head_size, a.epoch = p->epoch;
+  a.wait_limit_ns = wait_limit_ns();
+  B200_REQUIRE(!stream_is_capturing(static_cast<cudaStream_t>(stream)), B200_ERR_UNSUPPORTED,
+               "dcp_exchange_fold cannot be captured into a CUDA graph: the step number is a host-side argument");
   const uint64_t total = (uint64_t)p->num_seqs * p->heads_local * (p->head_size / pack);
   const int threads = 256;
   // at least one CTA even for an empty batch: the peers wait for this rank's flag
@@ -267,6 +307,9 @@ extern "C" int b200_dcp_gather_query(const b200_dcp_gather_params_t* p, void* st
   a.query = p->query, a.cta_counter = p->cta_counter, a.q_stride = p->q_stride;
   a.rank = p->rank, a.world = p->world, a.num_seqs = p->num_seqs, a.heads_local = p->heads_local;
   a.head_size = p->head_size, a.epoch = p->epoch;
+  a.wait_limit_ns = wait_limit_ns();
+  B200_REQUIRE(!stream_is_capturing(static_cast<cudaStream_t>(stream)), B200_ERR_UNSUPPORTED,
+               "dcp_gather_query cannot be captured into a CUDA graph: the step number is a host-side argument");
   const uint64_t total = (uint64_t)p->num_seqs * p->heads_local * (p->head_size / pack) * p->world;
   const int threads = 256;
   uint64_t blocks = (total + threads - 1) / threads;

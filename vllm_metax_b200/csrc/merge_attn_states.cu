@@ -41,8 +41,8 @@ __global__ void __launch_bounds__(256) merge_attn_states_kernel(b200_merge_attn_
   const float sw = sse / se;
 
   const int64_t hoff = (int64_t)head * p.head_size + (int64_t)pack * kPack;
-  const Vec16 pv = ld_global_16(reinterpret_cast<const T*>(p.prefix_output) + token * p.prefix_stride + hoff);
-  const Vec16 sv = ld_global_16(reinterpret_cast<const T*>(p.suffix_output) + token * p.suffix_stride + hoff);
+  const Vec16 pv = ld_global_16_coherent(reinterpret_cast<const T*>(p.prefix_output) + token * p.prefix_stride + hoff);
+  const Vec16 sv = ld_global_16_coherent(reinterpret_cast<const T*>(p.suffix_output) + token * p.suffix_stride + hoff);
   Vec16 ov;
   const T* pe = reinterpret_cast<const T*>(&pv);
   const T* se_ = reinterpret_cast<const T*>(&sv);

@@ -302,7 +302,7 @@ __device__ void compute_sched(const StreamParams& p, Sched* sc, int lane) {
 template <bool FLAT, bool SOLO = false>
 struct WorkIter {
   long long f, f1, base;
-  int s, n, L, item, rid, kclaim;
+  int s, n, L, item, step, rid, kclaim;
   Sched* sc;
   __device__ __forceinline__ void init(const StreamParams& p, Sched* sched) {
     if constexpr (FLAT) {
@@ -316,7 +316,13 @@ struct WorkIter {
       }
     } else {
       item = (int)blockIdx.x - (int)gridDim.x;
+      step = (int)gridDim.x;
     }
+  }
+  // item schedule, per-warp items: of the CTA's item list blockIdx + k * gridDim, warp w takes k == w (mod 8)
+  __device__ __forceinline__ void init_warp_items(int w) {
+    step = (int)gridDim.x * kConsumerWarps;
+    item = (int)blockIdx.x + w * (int)gridDim.x - step;
   }
   // Claim the CTA's next dynamic chunk.  The first of the CTA's iterators (producer lanes, consumer warps) to get
   // here takes it from the global counter and publishes it in shared memory; the others read it there.
@@ -379,7 +385,7 @@ struct WorkIter {
     } else {
       const int SH = p.S * p.Hkv;
       for (;;) {
-        item += (int)gridDim.x;
+        item += step;
         if (item >= p.total_items) return false;
         g.part = item / SH;
         const int r = item - g.part * SH;
@@ -483,13 +489,11 @@ __device__ __forceinline__ void producer_loop_pw(const StreamParams& p, int pw, 
   using C = Cfg<B, FP8>;
   WorkIter<false, true> wi;
   wi.init(p, nullptr);
-  int k = -1, ls = 0;
+  wi.init_warp_items(pw);
+  int ls = 0;
+  [[maybe_unused]] int k = 0;
   uint32_t phase = 0;
-  auto next_mine = [&](Seg& sg) -> bool {
-    while (wi.next(p, sg))
-      if ((++k & (kConsumerWarps - 1)) == pw) return true;
-    return false;
-  };
+  auto next_mine = [&](Seg& sg) -> bool { return wi.next(p, sg); };
   // The first block ids of the NEXT item are fetched while the current item streams: at 16 tiles per item an exposed
   // block-table load per item (~1 us under load) left the warp's three-stage slice empty for ~10 % of the time.
   Seg it, nx;
