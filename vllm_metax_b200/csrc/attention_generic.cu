@@ -302,12 +302,38 @@ __global__ void __launch_bounds__(kThreads) split_reduce_kernel(ReduceParams p) 
   const float inv = __fdividef(1.f, sum + 1e-6f);
   if (tid == 0 && p.lse != nullptr) p.lse[(int64_t)head * p.S + s] = m + logf(sum);
 
+  // Weighted sum of the partitions' rows.  The threads split into groups of D / kPack lanes: a group reads whole rows
+  // with 16-byte loads and takes the partitions j == group (mod groups), so that at P = 256 (ctx 131072) a thread
+  // walks 32 rows with independent loads in flight instead of 256 one after the other (the first version: 35 us of a
+  // 670 us step at C5); the groups' sums meet in shared memory.
   using TO = typename std::conditional<NORMALIZED, T, float>::type;
+  constexpr int kPack = 16 / sizeof(TO);
+  __shared__ float acc_s[kThreads * kPack];  // [groups][D]
   const TO* o = reinterpret_cast<const TO*>(p.so.o) + base * p.D;
+  const int lanes = p.D / kPack;           // 16-byte packs per row (head sizes are multiples of 8)
+  const int groups = kThreads / lanes;
+  const int grp = tid / lanes, pk = tid - grp * lanes;
+  __syncthreads();  // w_s is complete
+  if (grp < groups) {
+    float acc[kPack];
+#pragma unroll
+    for (int i = 0; i < kPack; ++i) acc[i] = 0.f;
+#pragma unroll 4
+    for (int j = grp; j < n; j += groups) {
+      const Vec16 v = ld_global_16(o + (int64_t)j * p.D + pk * kPack);
+      const float w = w_s[j];
+      const TO* e = reinterpret_cast<const TO*>(&v);
+#pragma unroll
+      for (int i = 0; i < kPack; ++i) acc[i] = fmaf(to_f32<TO>(e[i]), w, acc[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < kPack; ++i) acc_s[grp * p.D + pk * kPack + i] = acc[i];
+  }
+  __syncthreads();
   for (int d = tid; d < p.D; d += kThreads) {
-    float acc = 0.f;
-    for (int j = 0; j < n; ++j) acc = fmaf(to_f32<TO>(o[(int64_t)j * p.D + d]), w_s[j], acc);
-    reinterpret_cast<T*>(p.out)[((int64_t)s * p.H + head) * p.D + d] = from_f32<T>(acc * inv);
+    float a = 0.f;
+    for (int g = 0; g < groups; ++g) a += acc_s[g * p.D + d];
+    reinterpret_cast<T*>(p.out)[((int64_t)s * p.H + head) * p.D + d] = from_f32<T>(a * inv);
   }
 }
 
