@@ -1,4 +1,4 @@
-"""The v1-engine backend (vllm_metax_b200/attention/v1_backend.py) under the reference's backend test template
+"""The v1-engine backend (vllm_metax_b200/v1_backend.py) under the reference's backend test template
 (tests/v1/attention/test_attention_backends.py:285-460): BatchSpec -> CommonAttentionMetadata -> builder.build() ->
 Impl.forward over a prepopulated, block-permuted paged cache, against per-sequence scaled_dot_product_attention with the
 template's tolerances (rtol 1e-2, atol 5e-3).  CPU part: the class hierarchy, the metadata builder and the selection
@@ -6,7 +6,7 @@ rule (no kernel is called)."""
 import pytest
 import torch
 
-vb = pytest.importorskip("vllm_metax_b200.attention.v1_backend")  # needs upstream vLLM's interface module
+vb = pytest.importorskip("vllm_metax_b200.v1_backend")  # needs upstream vLLM's interface module
 
 from v1_backend_common import BATCH_SPECS, BatchSpec, MockAttentionLayer, create_common_attn_metadata, stand_in_config  # noqa: E402
 
@@ -31,7 +31,7 @@ def test_class_hierarchy_and_backend_contract():
     assert B.supports_head_size(128) and not B.supports_head_size(64)
     assert B.supports_dtype(torch.bfloat16) and not B.supports_dtype(torch.float32)
     assert B.supports_block_size(16) and B.supports_block_size(64) and not B.supports_block_size(8)
-    assert B.full_cls_name() == ("vllm_metax_b200.attention.v1_backend", "B200PagedAttentionBackend")
+    assert B.full_cls_name() == ("vllm_metax_b200.v1_backend", "B200PagedAttentionBackend")
     Impl = B.get_impl_cls()
     with pytest.raises(NotImplementedError):
         Impl(32, 128, 0.1, 8, sliding_window=128)

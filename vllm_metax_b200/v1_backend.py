@@ -22,7 +22,8 @@ over the first `context + i + 1` tokens of its sequence, read back from the page
 re-reads the context once per query token: correct (bit-for-bit the decode kernel), not fast; `prefill_as_decode=False`
 makes forward() raise instead.
 
-No engine, scheduler or model-runner code is here or needed: the builder consumes upstream's CommonAttentionMetadata.
+Load order: import this module (or vllm) BEFORE anything that loads the kernels of this package — see the note at
+the imports.  No engine, scheduler or model-runner code is here or needed: the builder consumes upstream's CommonAttentionMetadata.
 """
 from __future__ import annotations
 
@@ -42,9 +43,13 @@ from vllm.v1.attention.backend import (  # upstream interfaces (pure Python)
 )
 from vllm.v1.attention.backends.utils import split_decodes_and_prefills
 
-from .. import _custom_ops as ops
+# Upstream first, this repository's kernels second: on a CUDA box the imports above load upstream's compiled
+# `vllm._C`, which DEFINES the torch.ops._C schemas; our shim then only overrides the CUDA kernels of the identical ones
+# (csrc/torch_shim.cpp register_op).  The other order aborts inside upstream's TORCH_LIBRARY definition — which is why
+# this module sits at the top of the package: importing it must not run a package __init__ that loads the kernels.
+from . import _custom_ops as ops  # noqa: E402
 
-BACKEND_PATH = "vllm_metax_b200.attention.v1_backend.B200PagedAttentionBackend"
+BACKEND_PATH = "vllm_metax_b200.v1_backend.B200PagedAttentionBackend"
 
 
 class B200PagedAttentionBackend(AttentionBackend):
