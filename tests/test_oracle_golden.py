@@ -166,3 +166,23 @@ def test_rotary_oracle_matches_upstream_native(path):
     q, k = orc.rotary_embedding(d["positions"], d["query"], d["key"], d["head_size"], d["cos_sin_cache"], d["is_neox"])
     assert torch.equal(q, d["ref_query"]) and torch.equal(k, d["ref_key"])
     assert not torch.equal(q, d["query"])
+
+
+MLA = sorted(glob.glob(os.path.join(GOLDEN, "mla_*.pt")))
+
+
+@pytest.mark.parametrize("path", MLA, ids=[os.path.basename(p)[:-3] for p in MLA])
+def test_mla_oracle_matches_reference_oracles(path):
+    """oracle.mla_decode against the outputs of the reference's own `ref_mla` (test_mla_decode_cpu.py:13-40) and
+    of the cutlass test's fp32 oracle (test_cutlass_mla_decode.py:133-154), tests/golden/make_golden_mla.py."""
+    d = torch.load(path)
+    out, lse = orc.mla_decode(d["query"], d["kv_cache"], d["scale"], d["block_tables"], d["seq_lens"])
+    torch.testing.assert_close(out, d["ref_out_f32"], atol=2e-6, rtol=1e-5)
+    torch.testing.assert_close(lse, d["ref_lse_f32"], atol=5e-6, rtol=1e-6)
+    # ref_mla runs SDPA in the cache dtype: agreement to that dtype's rounding of O(1) values
+    tol = 4e-3 if d["query"].dtype == torch.bfloat16 else 5e-4
+    assert (out - d["ref_out_sdpa_cpu"].float()).abs().max().item() <= tol
+
+
+def test_mla_fixtures_present():
+    assert len(MLA) >= 3
