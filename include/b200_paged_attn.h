@@ -520,6 +520,53 @@ int b200_peer_open(const void* handle64, void** ptr);
 int b200_peer_close(void* ptr);
 int b200_peer_free(void* ptr);
 
+/*
+ * MLA decode attention.  Replaces torch.ops._C.cutlass_mla_decode (csrc/torch_bindings.cpp:287-290; entry
+ * csrc/attention/mla/cutlass_mla_entry.cu:28-38; checks and launch csrc/attention/mla/cutlass_mla_kernels.cu:154-225)
+ * and the Triton split-K MLA decode (vllm_metax/attention/ops/triton_decode_attention.py:673-721) for the MLA shape:
+ *   out[s, h, :512] = softmax_t(scale * [q_nope[s,h] | q_pe[s,h]] . kv[t, :576]) . kv[t, :512],  t < seq_lens[s]
+ * where row t of sequence s is kv_cache[page_table[s, t / page_size], t % page_size, :] (one shared latent head).
+ *   q_nope [num_seqs, num_heads, 512], q_pe [num_seqs, num_heads, 64], out [num_seqs, num_heads, 512]: element type
+ *     `dtype` (bf16 / f16), innermost contiguous, seq / head strides in elements (16-byte aligned rows)
+ *   kv_cache [num_blocks, page_size, 576] same element type; block_stride / entry_stride in elements
+ *   seq_lens int32[num_seqs]; page_table int32[num_seqs, max_pages] (row stride page_table_stride)
+ *   lse (optional) float32 [num_seqs, num_heads] (row stride lse_stride): natural-log sum of exp of the scaled logits
+ *   num_heads <= 128 (the reference requires exactly 128 and pads; any count works here), page_size a power of two >= 16
+ *   workspace: b200_mla_decode_workspace_bytes(num_seqs, num_heads, max_pages * page_size, num_kv_splits) bytes, used when the
+ *     launch splits sequences along tokens (fp32 partial outputs + LSEs, merged by a second kernel); may be NULL when
+ *     num_kv_splits == 1.  num_kv_splits: 0 = choose, 1 = never split, n = at most n splits per sequence.
+ * A sequence of length 0 writes zeros (lse = -inf).  All pointers are device pointers; nothing is allocated.
+ */
+typedef struct b200_mla_decode_params {
+  void* out;
+  float* lse;
+  const void* q_nope;
+  const void* q_pe;
+  const void* kv_cache;
+  const int32_t* seq_lens;
+  const int32_t* page_table;
+  void* workspace;
+  uint64_t workspace_bytes;
+  int64_t out_seq_stride, out_head_stride;
+  int64_t q_nope_seq_stride, q_nope_head_stride;
+  int64_t q_pe_seq_stride, q_pe_head_stride;
+  int64_t block_stride, entry_stride;
+  int64_t page_table_stride;
+  int64_t lse_stride;
+  int64_t num_blocks;
+  float scale;
+  int32_t num_seqs;
+  int32_t num_heads;
+  int32_t page_size;
+  int32_t max_pages;
+  int32_t dtype; /* b200_dtype_t: BF16 or F16 */
+  int32_t num_kv_splits;
+  float* debug_logits; /* NULL, or [128 x 64] fp32: raw S^T of the first tile of CTA 0 (tools/ only) */
+} b200_mla_decode_params_t;
+
+int b200_mla_decode(const b200_mla_decode_params_t* params, void* stream);
+uint64_t b200_mla_decode_workspace_bytes(int32_t num_seqs, int32_t num_heads, int64_t max_seq_len, int32_t num_kv_splits);
+
 /* "auto" -> B200_KV_AUTO, "fp8" | "fp8_e4m3" -> B200_KV_FP8_E4M3, anything
  * else (incl. "fp8_e5m2") -> -1. */
 int b200_kv_dtype_from_string(const char* kv_cache_dtype);

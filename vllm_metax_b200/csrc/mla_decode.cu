@@ -1,0 +1,688 @@
+// MLA decode attention for B200 (sm_100a): tcgen05 tensor cores, TMEM accumulators, TMA-fed paged latent rows.
+// Replaces torch.ops._C.cutlass_mla_decode (csrc/attention/mla/cutlass_mla_entry.cu:28-38, checks and launch
+// csrc/attention/mla/cutlass_mla_kernels.cu:154-225, schema csrc/torch_bindings.cpp:287-290) and the Triton split-K
+// MLA decode (vllm_metax/attention/ops/triton_decode_attention.py:673-721).  DESIGN.md §10.
+//
+//   out[s,h,:512] = softmax_t(scale * [q_nope|q_pe][s,h] . kv[t,:576]) . kv[t,:512]       (one shared latent head)
+//
+// Formulation (everything transposed so that the head count is the MMA N extent and the accumulators fit one SM):
+//   S^T[128 tokens x NG heads] = Ktile[128 x 576] . Q^T      9 chunks of 64 dims, 4 K-steps each  (A, B K-major SW128)
+//   O^T[512 dv x NG heads]    += V^T[512 x 128] . P^T        4 M=128 blocks, 8 K-steps of 16 tokens (A MN-major SW128)
+// A TMA box [64 dims x rows] with the 128-byte swizzle is the K-major A operand of the first product and the MN-major
+// A operand of the second, so K chunks and V chunks are the same 16 KiB ring stages, loaded once for each product.
+// TMEM: S^T double-buffered (2 x NG columns) + O^T (4 x NG columns).
+//
+// One CTA per (sequence, head group of NG <= 64, token split).  Warps: 0 = TMA producer (one lane), 1 = MMA issuer,
+// 2..5 = softmax / epilogue (one TMEM lane = one token row each).  Softmax uses a lazily updated per-head reference
+// m_ref (log2 units): p = 2^(s - m_ref); the column-wise (cross-lane) maximum is only taken when some logit passes
+// m_ref by kTau, after which O^T and the running sums are rescaled.  Row sums are kept per thread and reduced once.
+#include <cuda.h>
+#include <string.h>
+
+#include "stream_common.cuh"
+
+namespace b200 {
+namespace {
+
+constexpr int kTile = 128;            // tokens per tile (MMA M of S^T)
+constexpr int kChunkBytes = 16384;    // ring stage: 128 rows x 128 B
+constexpr int kKChunks = 9;           // 576 / 64
+constexpr int kVChunks = 8;           // 512 / 64
+constexpr int kMlaThreads = 192;
+constexpr int kSoftmaxThreads = 128;
+constexpr int kMaxSlots = 16;
+constexpr float kTau = 16.f;          // re-reference when a logit passes m_ref by 2^16
+constexpr int kMaxSplits = 32;
+constexpr int kMinSplitTiles = 4;
+
+struct MlaParams {
+  void* out;
+  float* lse;
+  const int32_t* seq_lens;
+  const int32_t* page_table;
+  float* part_out;   // [S][H][max_splits][512] fp32 (normalised partial outputs)
+  float* part_lse;   // [S][H][max_splits]
+  float* debug_logits;
+  long long out_seq_stride, out_head_stride, page_table_stride, lse_stride;
+  float scale_log2;
+  int S, H, groups, page_size, page_shift, box_rows, max_splits, split_tokens, nslots, f16;
+};
+
+// ---- tcgen05 / TMA wrappers ---------------------------------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a, uint64_t b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(d_tmem),
+      "l"(a), "l"(b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// shared-memory matrix descriptor, 128-byte swizzle (layout type 2), descriptor version 1
+__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return (uint64_t)((addr & 0x3FFFF) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
+         (1ull << 46) | (2ull << 61);
+}
+// kind::f16 instruction descriptor: f32 accumulate, A/B element format (0 f16, 1 bf16), A major (0 K, 1 MN), B K-major
+__host__ __device__ constexpr uint32_t idesc_f16(int M, int N, int fmt, int a_mn_major) {
+  return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)a_mn_major << 15) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const void* tmap, int c0, int c1, int c2, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void softmax_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ bool softmax_bar_or(bool v) {
+  uint32_t r;
+  asm volatile("{\n.reg .pred p, q;\nsetp.ne.b32 q, %1, 0;\nbar.red.or.pred p, 1, 128, q;\nselp.u32 %0, 1, 0, p;\n}\n"
+               : "=r"(r)
+               : "r"((uint32_t)v)
+               : "memory");
+  return r != 0;
+}
+__device__ __forceinline__ int f32_sortable(float x) {
+  const int i = __float_as_int(x);
+  return i ^ ((i >> 31) & 0x7fffffff);
+}
+__device__ __forceinline__ float sortable_f32(int i) { return __int_as_float(i ^ ((i >> 31) & 0x7fffffff)); }
+
+// 32 TMEM lanes x N consecutive 32-bit columns -> N registers per thread (thread = lane)
+template <int N>
+__device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t* r);
+template <>
+__device__ __forceinline__ void tmem_ld<16>(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+}
+template <>
+__device__ __forceinline__ void tmem_ld<32>(uint32_t taddr, uint32_t* r) {
+  tmem_ld<16>(taddr, r);
+  tmem_ld<16>(taddr + 16, r + 16);
+}
+template <>
+__device__ __forceinline__ void tmem_ld<64>(uint32_t taddr, uint32_t* r) {
+  tmem_ld<32>(taddr, r);
+  tmem_ld<32>(taddr + 32, r + 32);
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// ---- shared-memory carve-up ----------------------------------------------------------------------------------
+struct MlaMisc {
+  uint64_t full[kMaxSlots], empty[kMaxSlots];
+  uint64_t s_full[2], s_free[2], p_full, p_free, o_full, q_full;
+  uint32_t tmem_base;
+  uint32_t pad[3];
+  float mref[64];      // per-head softmax reference, log2 units
+  float fac[64];       // rescale factor of the last re-reference; 1 / row sum in the epilogue
+  int colmax[4][64];   // per-warp column maxima (sortable-int encoding)
+};
+__host__ __device__ constexpr size_t mla_smem_bytes(int NG, int nslots) {
+  return 1024 + (size_t)NG * 128 * (kKChunks + 2) + (size_t)nslots * kChunkBytes + sizeof(MlaMisc);
+}
+
+template <int NG>
+__global__ void __launch_bounds__(kMlaThreads, 1)
+mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, const __grid_constant__ TmaDesc tm_qn,
+                  const __grid_constant__ TmaDesc tm_qp) {
+  // ---- which item ----
+  const int seq = blockIdx.y;
+  const int group = blockIdx.x % p.groups;
+  const int split = blockIdx.x / p.groups;
+  const int L = p.seq_lens[seq];
+  const int t0 = split * p.split_tokens;
+  const int t1 = min(L, t0 + p.split_tokens);
+  const int h0 = group * NG;
+  const int nh = min(NG, p.H - h0);           // real heads of this group
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nsplit = L > 0 ? (L + p.split_tokens - 1) / p.split_tokens : 1;
+  if (L <= 0) {  // empty sequence: zeros and lse = -inf, written by the split-0 CTAs
+    if (split == 0) {
+      for (int i = tid; i < nh * 512; i += kMlaThreads) {
+        const long long o = (long long)seq * p.out_seq_stride + (long long)(h0 + i / 512) * p.out_head_stride + i % 512;
+        if (p.f16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(0.f);
+        else reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(0.f);
+      }
+      if (p.lse != nullptr && tid < nh) p.lse[(long long)seq * p.lse_stride + h0 + tid] = -INFINITY;
+    }
+    return;
+  }
+  if (t0 >= t1) return;
+  const int T = (t1 - t0 + kTile - 1) / kTile;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* const base_ptr = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t q_u32 = base;                                  // 9 chunks [NG rows x 128 B]
+  const uint32_t p_u32 = q_u32 + kKChunks * NG * 128;           // 2 chunks [NG rows x 128 B] (64 tokens each)
+  const uint32_t ring_u32 = p_u32 + 2 * NG * 128;
+  uint8_t* const ring_ptr = base_ptr + (ring_u32 - base);
+  MlaMisc* const misc = reinterpret_cast<MlaMisc*>(ring_ptr + (size_t)p.nslots * kChunkBytes);
+  const int nslots = p.nslots;
+
+  if (tid == 0) {
+    for (int i = 0; i < nslots; ++i) {
+      mbar_init(smem_u32(&misc->full[i]), 1);
+      mbar_init(smem_u32(&misc->empty[i]), 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&misc->s_full[i]), 1);
+      mbar_init(smem_u32(&misc->s_free[i]), kSoftmaxThreads);
+    }
+    mbar_init(smem_u32(&misc->p_full), kSoftmaxThreads);
+    mbar_init(smem_u32(&misc->p_free), 1);
+    mbar_init(smem_u32(&misc->o_full), 1);
+    mbar_init(smem_u32(&misc->q_full), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (tid < 64) misc->mref[tid] = -INFINITY;
+  constexpr uint32_t kCols = NG == 64 ? 512 : (NG == 32 ? 256 : 128);  // power of two >= 6 * NG
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&misc->tmem_base)),
+                 "r"(kCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = misc->tmem_base;
+  const uint32_t tm_s[2] = {tmem, tmem + NG};
+  const uint32_t tm_o = tmem + 2 * NG;
+
+  if (warp == 0) {
+    // =================== TMA producer (one lane) ===================
+    if (lane == 0) {
+      // query group: 8 latent chunks + the rope chunk, heads beyond H zero-filled by the tensor map bounds
+      mbar_expect_tx(smem_u32(&misc->q_full), (uint32_t)(kKChunks * NG * 128));
+      for (int c = 0; c < kVChunks; ++c) tma_load_3d(q_u32 + c * NG * 128, &tm_qn, c * 64, h0, seq, smem_u32(&misc->q_full));
+      tma_load_3d(q_u32 + kVChunks * NG * 128, &tm_qp, 0, h0, seq, smem_u32(&misc->q_full));
+
+      const int32_t* table = p.page_table + (long long)seq * p.page_table_stride;
+      const int box_rows = p.box_rows;
+      const uint32_t box_bytes = (uint32_t)box_rows * 128u;
+      int slot = 0;
+      uint32_t phase = 0;  // parity of the ring pass
+      auto advance = [&]() {
+        if (++slot == nslots) { slot = 0; phase ^= 1; }
+      };
+      // chunks c0 .. c0+n-1 of the tile starting at token tok0 (9 K chunks, or 8 V chunks)
+      auto load_chunks = [&](int tok0, int nchunks) {
+        const int valid = min(kTile, L - tok0);                  // rows of this tile that hold cache entries
+        const int vbox = (valid + box_rows - 1) / box_rows;
+        int page[8], row[8];
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+          if (b < vbox) {
+            const int tok = tok0 + b * box_rows;
+            page[b] = table[tok >> p.page_shift];
+            row[b] = tok & (p.page_size - 1);
+          }
+        }
+        for (int c = 0; c < nchunks; ++c) {
+          mbar_wait(smem_u32(&misc->empty[slot]), phase ^ 1);
+          const uint32_t full = smem_u32(&misc->full[slot]);
+          mbar_expect_tx(full, box_bytes * (uint32_t)vbox);
+          const uint32_t dst = ring_u32 + (uint32_t)slot * kChunkBytes;
+#pragma unroll
+          for (int b = 0; b < 8; ++b)
+            if (b < vbox) tma_load_3d(dst + b * box_bytes, &tm_kv, c * 64, row[b], page[b], full);
+          advance();
+        }
+      };
+      auto k_phase = [&](int i) {
+        load_chunks(t0 + i * kTile, kKChunks);
+        // filler stage: keeps every V pair on an even slot, so a pair never straddles the ring's wrap-around
+        mbar_wait(smem_u32(&misc->empty[slot]), phase ^ 1);
+        mbar_arrive(smem_u32(&misc->full[slot]));
+        advance();
+      };
+      k_phase(0);
+      for (int i = 0; i < T; ++i) {
+        if (i + 1 < T) k_phase(i + 1);
+        load_chunks(t0 + i * kTile, kVChunks);
+      }
+    }
+  } else if (warp == 1) {
+    // =================== MMA issuer ===================
+    const int fmt = p.f16 ? 0 : 1;
+    const uint32_t idesc_s = idesc_f16(128, NG, fmt, 0);
+    const uint32_t idesc_o = idesc_f16(128, NG, fmt, 1);
+    int slot = 0;
+    uint32_t phase = 0;
+    auto advance = [&]() {
+      if (++slot == nslots) { slot = 0; phase ^= 1; }
+    };
+    mbar_wait(smem_u32(&misc->q_full), 0);
+    auto issue_s = [&](int i) {
+      const int b = i & 1;
+      if (i >= 2) mbar_wait(smem_u32(&misc->s_free[b]), ((i >> 1) & 1) ^ 1);
+      tc_fence_after();
+      for (int c = 0; c < kKChunks; ++c) {
+        mbar_wait(smem_u32(&misc->full[slot]), phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_addr = ring_u32 + (uint32_t)slot * kChunkBytes;
+          const uint32_t b_addr = q_u32 + c * NG * 128;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_f16(tm_s[b], smem_desc_sw128(a_addr + k * 32, 0, 1024), smem_desc_sw128(b_addr + k * 32, 0, 1024),
+                     idesc_s, (c | k) != 0);
+          umma_commit(smem_u32(&misc->empty[slot]));
+        }
+        __syncwarp();
+        advance();
+      }
+      mbar_wait(smem_u32(&misc->full[slot]), phase);  // filler stage
+      if (lane == 0) {
+        umma_commit(smem_u32(&misc->empty[slot]));
+        umma_commit(smem_u32(&misc->s_full[b]));
+      }
+      __syncwarp();
+      advance();
+    };
+    auto issue_pv = [&](int i) {
+      const int rows = min(kTile, t1 - (t0 + i * kTile));   // valid token rows of this tile
+      const int ksteps = (rows + 15) >> 4;
+      const int zero_from = rows, zero_to = ksteps << 4;     // rows of the last K step that are past the sequence
+      mbar_wait(smem_u32(&misc->p_full), i & 1);
+      tc_fence_after();
+      for (int j = 0; j < 4; ++j) {
+        const int s0 = slot;
+        mbar_wait(smem_u32(&misc->full[s0]), phase);
+        mbar_wait(smem_u32(&misc->full[s0 + 1]), phase);
+        tc_fence_after();
+        const uint32_t a_addr = ring_u32 + (uint32_t)s0 * kChunkBytes;
+        if (zero_from < zero_to) {
+          // V rows past the sequence end may hold anything (0 * NaN = NaN): zero them before the tensor core reads
+          const int n16 = (zero_to - zero_from) * 8;  // 16-byte units per chunk
+          for (int u = lane; u < 2 * n16; u += 32) {
+            uint8_t* dst = ring_ptr + (size_t)(s0 + u / n16) * kChunkBytes + (size_t)zero_from * 128 + (size_t)(u % n16) * 16;
+            *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
+          }
+          fence_async_smem();
+          __syncwarp();
+        }
+        if (lane == 0) {
+          for (int ks = 0; ks < ksteps; ++ks)
+            umma_f16(tm_o + j * NG, smem_desc_sw128(a_addr + ks * 2048, kChunkBytes, 1024),
+                     smem_desc_sw128(p_u32 + (ks >> 2) * NG * 128 + (ks & 3) * 32, 0, 1024), idesc_o, (i | ks) != 0);
+          umma_commit(smem_u32(&misc->empty[s0]));
+          umma_commit(smem_u32(&misc->empty[s0 + 1]));
+        }
+        __syncwarp();
+        advance();
+        advance();
+      }
+      if (lane == 0) umma_commit(smem_u32(&misc->p_free));
+      __syncwarp();
+    };
+    issue_s(0);
+    for (int i = 0; i < T; ++i) {
+      if (i + 1 < T) issue_s(i + 1);
+      issue_pv(i);
+    }
+    if (lane == 0) umma_commit(smem_u32(&misc->o_full));
+    __syncwarp();
+  } else {
+    // =================== softmax / epilogue warps (2..5): thread = one token row = one TMEM lane ===================
+    const int quad = warp & 3;                   // TMEM lane quadrant this warp may access
+    const int row = quad * 32 + lane;            // token row within the tile / dv row within an O^T block
+    const int st = tid - 64;                     // 0..127
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    float lsum[NG];
+#pragma unroll
+    for (int h = 0; h < NG; ++h) lsum[h] = 0.f;
+
+    for (int i = 0; i < T; ++i) {
+      const int b = i & 1;
+      mbar_wait(smem_u32(&misc->s_full[b]), (i >> 1) & 1);
+      tc_fence_after();
+      uint32_t r[NG];
+      tmem_ld<NG>(tm_s[b] + lane_base, r);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(smem_u32(&misc->s_free[b]));
+      if (p.debug_logits != nullptr && i == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
+#pragma unroll
+        for (int h = 0; h < NG; ++h) p.debug_logits[row * 64 + h] = __uint_as_float(r[h]);
+      }
+      const bool valid = t0 + i * kTile + row < t1;
+      float x[NG];
+      bool over = false;
+#pragma unroll
+      for (int h = 0; h < NG; ++h) {
+        x[h] = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
+        over |= x[h] > misc->mref[h] + kTau;
+      }
+      if (softmax_bar_or(over)) {
+        // ---- rare path: raise the references to this tile's column maxima, rescale O^T and the running sums ----
+#pragma unroll
+        for (int h = 0; h < NG; ++h) {
+          const int m = __reduce_max_sync(0xffffffffu, f32_sortable(x[h]));
+          if (lane == 0) misc->colmax[warp - 2][h] = m;
+        }
+        softmax_bar_sync();
+        if (st < NG) {
+          const int m = max(max(misc->colmax[0][st], misc->colmax[1][st]), max(misc->colmax[2][st], misc->colmax[3][st]));
+          const float m_old = misc->mref[st];
+          float m_new = fmaxf(m_old, sortable_f32(m));
+          if (m_new == -INFINITY) m_new = 0.f;
+          misc->fac[st] = m_old == -INFINITY ? 0.f : exp2f(m_old - m_new);
+          misc->mref[st] = m_new;
+        }
+        softmax_bar_sync();
+#pragma unroll
+        for (int h = 0; h < NG; ++h) lsum[h] *= misc->fac[h];
+        if (i > 0) {
+          mbar_wait(smem_u32(&misc->p_free), (i - 1) & 1);  // P.V of the previous tile has landed in O^T
+          tc_fence_after();
+          for (int j = 0; j < 4; ++j) {
+#pragma unroll
+            for (int c = 0; c < NG; c += 16) {
+              uint32_t o[16];
+              tmem_ld<16>(tm_o + j * NG + c + lane_base, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int e = 0; e < 16; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * misc->fac[c + e]);
+              tmem_st16(tm_o + j * NG + c + lane_base, o);
+            }
+          }
+          tmem_st_wait();
+          tc_fence_before();
+        }
+      }
+      // ---- probabilities: p = 2^(x - m_ref); bf16/f16 into the P^T operand, fp32 into the running sums ----
+      uint32_t pk[NG];  // one 16-bit value per head
+#pragma unroll
+      for (int h = 0; h < NG; ++h) {
+        const float pv = fast_exp2(x[h] - misc->mref[h]);
+        lsum[h] += pv;
+        pk[h] = p.f16 ? (uint32_t)__half_as_ushort(__float2half_rn(pv)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(pv));
+      }
+      if (i > 0) mbar_wait(smem_u32(&misc->p_free), (i - 1) & 1);
+      // P^T[h][token]: K-major SW128, chunk = row / 64, 16-byte unit (row % 64) / 8 XOR (h % 8)
+      {
+        const uint32_t chunk = p_u32 + (row >> 6) * NG * 128;
+        const uint32_t unit = (row & 63) >> 3, within = (row & 7) * 2;
+#pragma unroll
+        for (int h = 0; h < NG; ++h) {
+          const uint32_t addr = chunk + h * 128 + ((unit ^ (h & 7)) << 4) + within;
+          asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)pk[h]) : "memory");
+        }
+      }
+      fence_async_smem();
+      mbar_arrive(smem_u32(&misc->p_full));
+    }
+
+    // ---- epilogue: reduce the per-thread row sums over the 128 token rows, normalise O^T, store ----
+    mbar_wait(smem_u32(&misc->o_full), 0);   // every MMA (hence every ring read) is complete: the ring is scratch now
+    tc_fence_after();
+    float* scratch = reinterpret_cast<float*>(ring_ptr);  // [128][NG + 1]
+#pragma unroll
+    for (int h = 0; h < NG; ++h) scratch[row * (NG + 1) + h] = lsum[h];
+    softmax_bar_sync();
+    const bool direct = nsplit == 1;
+    if (st < NG) {
+      float l = 0.f;
+      for (int t = 0; t < kTile; ++t) l += scratch[t * (NG + 1) + st];
+      misc->fac[st] = 1.f / l;
+      if (st < nh) {
+        const float lse = (misc->mref[st] + log2f(l)) * kLn2;
+        if (direct) {
+          if (p.lse != nullptr) p.lse[(long long)seq * p.lse_stride + h0 + st] = lse;
+        } else {
+          p.part_lse[((long long)seq * p.H + h0 + st) * p.max_splits + split] = lse;
+        }
+      }
+    }
+    softmax_bar_sync();
+    for (int j = 0; j < 4; ++j) {
+      const int dv = j * 128 + row;
+#pragma unroll
+      for (int c = 0; c < NG; c += 16) {
+        uint32_t o[16];
+        tmem_ld<16>(tm_o + j * NG + c + lane_base, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const int h = c + e;
+          if (h < nh) {
+            const float v = __uint_as_float(o[e]) * misc->fac[h];
+            if (direct) {
+              const long long off = (long long)seq * p.out_seq_stride + (long long)(h0 + h) * p.out_head_stride + dv;
+              if (p.f16) reinterpret_cast<__half*>(p.out)[off] = __float2half_rn(v);
+              else reinterpret_cast<__nv_bfloat16*>(p.out)[off] = __float2bfloat16_rn(v);
+            } else {
+              p.part_out[(((long long)seq * p.H + h0 + h) * p.max_splits + split) * 512 + dv] = v;
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kCols) : "memory");
+  }
+}
+
+// ---- merge of the token splits (flash-decoding reduce): out = sum_j w_j O_j, w_j = exp(lse_j - max) / sum ----
+__global__ void __launch_bounds__(128) mla_merge_kernel(const MlaParams p) {
+  const int seq = blockIdx.y, h = blockIdx.x;
+  const int L = p.seq_lens[seq];
+  const int n = L > 0 ? (L + p.split_tokens - 1) / p.split_tokens : 1;
+  if (n <= 1) return;  // written directly by the decode kernel
+  const float* lse = p.part_lse + ((long long)seq * p.H + h) * p.max_splits;
+  float m = -INFINITY;
+  for (int j = 0; j < n; ++j) m = fmaxf(m, lse[j]);
+  float denom = 0.f;
+  for (int j = 0; j < n; ++j) denom += __expf(lse[j] - m);
+  const float inv = 1.f / denom;
+  const float4* po = reinterpret_cast<const float4*>(p.part_out + ((long long)seq * p.H + h) * p.max_splits * 512);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int j = 0; j < n; ++j) {
+    const float w = __expf(lse[j] - m) * inv;
+    const float4 v = po[j * 128 + threadIdx.x];
+    acc.x += w * v.x, acc.y += w * v.y, acc.z += w * v.z, acc.w += w * v.w;
+  }
+  const long long off = (long long)seq * p.out_seq_stride + (long long)h * p.out_head_stride + threadIdx.x * 4;
+  if (p.f16) {
+    __half2* o = reinterpret_cast<__half2*>(reinterpret_cast<__half*>(p.out) + off);
+    o[0] = __floats2half2_rn(acc.x, acc.y);
+    o[1] = __floats2half2_rn(acc.z, acc.w);
+  } else {
+    __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off);
+    o[0] = __floats2bfloat162_rn(acc.x, acc.y);
+    o[1] = __floats2bfloat162_rn(acc.z, acc.w);
+  }
+  if (p.lse != nullptr && threadIdx.x == 0) p.lse[(long long)seq * p.lse_stride + h] = m + __logf(denom);
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn mla_encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      f = nullptr;
+    }
+    return reinterpret_cast<EncodeTiledFn>(f);
+  }();
+  return fn;
+}
+
+// 3-D map (inner dim, rows, outer) with a [64 x box_rows x 1] box and the 128-byte swizzle; strides in elements
+int encode_map3(TmaDesc* out, const void* ptr, bool f16, uint64_t d0, uint64_t d1, uint64_t d2, int64_t s1, int64_t s2,
+                uint32_t box_rows, const char* what) {
+  EncodeTiledFn enc = mla_encode_fn();
+  B200_REQUIRE(enc != nullptr, B200_ERR_CUDA, "mla_decode: cuTensorMapEncodeTiled is not available from the driver");
+  const cuuint64_t dims[3] = {d0, d1, d2};
+  const cuuint64_t strides[2] = {(cuuint64_t)s1 * 2, (cuuint64_t)s2 * 2};
+  const cuuint32_t box[3] = {64, box_rows, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  CUtensorMap m;
+  const CUresult r = enc(&m, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3,
+                         const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, B200_ERR_INVALID_ARGUMENT,
+               "mla_decode: cuTensorMapEncodeTiled failed (%d) for %s (dims %llu/%llu/%llu, strides %lld/%lld elements)",
+               (int)r, what, (unsigned long long)d0, (unsigned long long)d1, (unsigned long long)d2, (long long)s1,
+               (long long)s2);
+  static_assert(sizeof(CUtensorMap) == sizeof(TmaDesc), "CUtensorMap is 128 bytes");
+  memcpy(out, &m, sizeof(m));
+  return B200_OK;
+}
+
+int mla_group_width(int H) { return H <= 16 ? 16 : (H <= 32 ? 32 : 64); }
+
+// number of token splits: minimise waves(items) / splits over the allowed range (every split >= kMinSplitTiles tiles)
+int mla_choose_splits(int S, int H, long long max_seq_len, int requested) {
+  const long long tiles = (max_seq_len + kTile - 1) / kTile;
+  int cap = (int)min((long long)kMaxSplits, max(1LL, tiles / kMinSplitTiles));
+  if (requested == 1) return 1;
+  if (requested > 1) return (int)min((long long)min(requested, kMaxSplits), max(1LL, tiles));
+  const int NG = mla_group_width(H);
+  const long long base = (long long)S * ((H + NG - 1) / NG);
+  const int sms = device_sm_count();
+  int best = 1;
+  double best_cost = 1e30;
+  for (int s = 1; s <= cap; ++s) {
+    const long long per = (tiles + s - 1) / s;                       // tiles per split
+    const long long waves = (base * s + sms - 1) / sms;
+    const double cost = (double)waves * ((double)per + 1.5) + (s > 1 ? 0.5 : 0.0);  // 1.5 tiles of fixed cost per CTA
+    if (cost < best_cost - 1e-9) best_cost = cost, best = s;
+  }
+  return best;
+}
+
+template <int NG>
+int launch_mla(const MlaParams& mp, const TmaDesc& kv, const TmaDesc& qn, const TmaDesc& qp, dim3 grid, cudaStream_t s) {
+  auto kern = mla_decode_kernel<NG>;
+  const size_t smem = mla_smem_bytes(NG, mp.nslots);
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+    if (e != cudaSuccess) {
+      set_error("mla_decode: cudaFuncSetAttribute(smem) failed: %s", cudaGetErrorString(e));
+      return B200_ERR_CUDA;
+    }
+    configured_device = dev;
+  }
+  kern<<<grid, kMlaThreads, smem, s>>>(mp, kv, qn, qp);
+  count_launch();
+  return check_launch("mla_decode");
+}
+}  // namespace
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" uint64_t b200_mla_decode_workspace_bytes(int32_t num_seqs, int32_t num_heads, int64_t max_seq_len,
+                                                    int32_t num_kv_splits) {
+  if (num_seqs <= 0 || num_heads <= 0 || max_seq_len <= 0) return 0;
+  const int splits = mla_choose_splits(num_seqs, num_heads, max_seq_len, num_kv_splits);
+  if (splits <= 1) return 0;
+  return (uint64_t)num_seqs * num_heads * splits * (512 + 1) * sizeof(float);
+}
+
+extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream) {
+  B200_REQUIRE(pp != nullptr, B200_ERR_INVALID_ARGUMENT, "mla_decode: null params");
+  const b200_mla_decode_params_t& p = *pp;
+  B200_REQUIRE(p.out && p.q_nope && p.q_pe && p.kv_cache && p.seq_lens && p.page_table, B200_ERR_INVALID_ARGUMENT,
+               "mla_decode: null tensor pointer");
+  B200_REQUIRE(p.num_seqs >= 0 && p.num_heads > 0 && p.max_pages > 0 && p.num_blocks > 0, B200_ERR_INVALID_ARGUMENT,
+               "mla_decode: negative or zero size");
+  B200_REQUIRE(p.dtype == B200_DTYPE_BF16 || p.dtype == B200_DTYPE_F16, B200_ERR_UNSUPPORTED,
+               "mla_decode: q / cache must be bf16 or f16 (dtype %d)", p.dtype);
+  B200_REQUIRE(p.num_heads <= 128, B200_ERR_UNSUPPORTED, "mla_decode: num_heads %d > 128", p.num_heads);
+  B200_REQUIRE(p.page_size >= 16 && (p.page_size & (p.page_size - 1)) == 0, B200_ERR_UNSUPPORTED,
+               "mla_decode: page_size %d must be a power of two >= 16", p.page_size);
+  B200_REQUIRE(p.entry_stride % 8 == 0 && p.block_stride % 8 == 0 && p.q_nope_head_stride % 8 == 0 &&
+                   p.q_nope_seq_stride % 8 == 0 && p.q_pe_head_stride % 8 == 0 && p.q_pe_seq_stride % 8 == 0 &&
+                   p.out_head_stride % 4 == 0 && p.out_seq_stride % 4 == 0,
+               B200_ERR_UNSUPPORTED, "mla_decode: rows must be 16-byte aligned (strides multiple of 8 elements)");
+  B200_REQUIRE(((uintptr_t)p.kv_cache | (uintptr_t)p.q_nope | (uintptr_t)p.q_pe) % 16 == 0 && (uintptr_t)p.out % 8 == 0,
+               B200_ERR_UNSUPPORTED, "mla_decode: base pointers must be 16-byte aligned");
+  if (p.num_seqs == 0) return B200_OK;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const bool f16 = p.dtype == B200_DTYPE_F16;
+  const long long max_len = (long long)p.max_pages * p.page_size;
+  const int splits = mla_choose_splits(p.num_seqs, p.num_heads, max_len, p.num_kv_splits);
+  const int NG = mla_group_width(p.num_heads);
+
+  MlaParams mp;
+  memset(&mp, 0, sizeof(mp));
+  mp.out = p.out, mp.lse = p.lse, mp.seq_lens = p.seq_lens, mp.page_table = p.page_table;
+  mp.debug_logits = p.debug_logits;
+  mp.out_seq_stride = p.out_seq_stride, mp.out_head_stride = p.out_head_stride;
+  mp.page_table_stride = p.page_table_stride, mp.lse_stride = p.lse_stride;
+  mp.scale_log2 = p.scale * kLog2e;
+  mp.S = p.num_seqs, mp.H = p.num_heads, mp.groups = (p.num_heads + NG - 1) / NG;
+  mp.page_size = p.page_size;
+  for (mp.page_shift = 0; (1 << mp.page_shift) < p.page_size; ++mp.page_shift) {}
+  mp.box_rows = p.page_size < kTile ? p.page_size : kTile;
+  mp.max_splits = splits;
+  const long long tiles = (max_len + kTile - 1) / kTile;
+  mp.split_tokens = (int)((tiles + splits - 1) / splits) * kTile;
+  mp.f16 = f16 ? 1 : 0;
+  int nslots = (int)((232448 - 1024 - (size_t)NG * 128 * (kKChunks + 2) - sizeof(MlaMisc)) / kChunkBytes);
+  nslots = min(nslots & ~1, kMaxSlots);
+  mp.nslots = nslots;
+  if (splits > 1) {
+    const uint64_t need = (uint64_t)p.num_seqs * p.num_heads * splits * (512 + 1) * sizeof(float);
+    B200_REQUIRE(p.workspace != nullptr && p.workspace_bytes >= need, B200_ERR_WORKSPACE,
+                 "mla_decode: %d token splits need a workspace of %llu bytes (got %llu)", splits, (unsigned long long)need,
+                 (unsigned long long)p.workspace_bytes);
+    B200_REQUIRE((uintptr_t)p.workspace % 16 == 0, B200_ERR_WORKSPACE, "mla_decode: workspace must be 16-byte aligned");
+    mp.part_out = static_cast<float*>(p.workspace);
+    mp.part_lse = mp.part_out + (size_t)p.num_seqs * p.num_heads * splits * 512;
+  }
+  TmaDesc kv, qn, qp;
+  int rc = encode_map3(&kv, p.kv_cache, f16, 576, (uint64_t)p.page_size, (uint64_t)p.num_blocks, p.entry_stride, p.block_stride,
+                       (uint32_t)mp.box_rows, "kv_cache");
+  if (rc != B200_OK) return rc;
+  rc = encode_map3(&qn, p.q_nope, f16, 512, (uint64_t)p.num_heads, (uint64_t)p.num_seqs, p.q_nope_head_stride,
+                   p.q_nope_seq_stride, (uint32_t)NG, "q_nope");
+  if (rc != B200_OK) return rc;
+  rc = encode_map3(&qp, p.q_pe, f16, 64, (uint64_t)p.num_heads, (uint64_t)p.num_seqs, p.q_pe_head_stride, p.q_pe_seq_stride,
+                   (uint32_t)NG, "q_pe");
+  if (rc != B200_OK) return rc;
+  const dim3 grid((unsigned)(mp.groups * splits), (unsigned)p.num_seqs);
+  if (NG == 16) rc = launch_mla<16>(mp, kv, qn, qp, grid, s);
+  else if (NG == 32) rc = launch_mla<32>(mp, kv, qn, qp, grid, s);
+  else rc = launch_mla<64>(mp, kv, qn, qp, grid, s);
+  if (rc != B200_OK) return rc;
+  if (splits > 1) {
+    mla_merge_kernel<<<dim3((unsigned)p.num_heads, (unsigned)p.num_seqs), 128, 0, s>>>(mp);
+    count_launch();
+    rc = check_launch("mla_merge");
+  }
+  return rc;
+}
