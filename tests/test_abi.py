@@ -51,6 +51,7 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
                       ("b200_gather_cache_params_t", native.GatherCacheParams),
                       ("b200_rotary_params_t", native.RotaryParams),
                       ("b200_concat_mla_params_t", native.ConcatMlaParams),
+                      ("b200_mla_decode_params_t", native.MlaDecodeParams),
                       ("b200_dcp_fold_params_t", native.DcpFoldParams),
                       ("b200_dcp_gather_params_t", native.DcpGatherParams)):
         prog.append('printf("%%zu\\n", sizeof(%s));' % cname)
@@ -64,7 +65,7 @@ def test_ctypes_structs_match_header_layout(native, tmp_path):
     vals = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     it = iter(vals)
     for st in (native.PagedAttnParams, native.CacheWriteParams, native.MergeAttnStatesParams, native.GatherCacheParams,
-               native.RotaryParams, native.ConcatMlaParams, native.DcpFoldParams,
+               native.RotaryParams, native.ConcatMlaParams, native.MlaDecodeParams, native.DcpFoldParams,
                native.DcpGatherParams):
         assert next(it) == C.sizeof(st)
         for f in fields(st):
@@ -164,6 +165,15 @@ def test_new_entry_points_validate_on_the_host(native):
     cm.num_tokens = 3
     assert lib.b200_concat_and_cache_mla(C.byref(cm), None) == native.ERR_INVALID_ARGUMENT
     assert lib.b200_copy_blocks_mla(None, 0, None, 0, 0, None) == 0
+    assert lib.b200_mla_decode(None, None) == native.ERR_INVALID_ARGUMENT
+    md = native.MlaDecodeParams()
+    assert lib.b200_mla_decode(C.byref(md), None) == native.ERR_INVALID_ARGUMENT  # NULL tensors
+    assert "null tensor" in lib.b200_last_error().decode()
+    # no token split for a batch that already fills the GPU twice over; splits (hence a workspace) for one long sequence
+    assert lib.b200_mla_decode_workspace_bytes(296, 64, 4096, 0) == 0
+    assert lib.b200_mla_decode_workspace_bytes(1, 128, 131072, 0) > 0
+    assert lib.b200_mla_decode_workspace_bytes(1, 128, 131072, 1) == 0
+    assert lib.b200_mla_decode_workspace_bytes(2, 16, 4096, 4) == 2 * 16 * 4 * 513 * 4
     assert lib.b200_copy_blocks(None, None, 0, None, 0, 0, None) == 0
     assert lib.b200_swap_blocks(None, None, None, 0, 4096, native.COPY_D2D, None) == 0
     m = (C.c_int64 * 2)(0, 1)

@@ -1,0 +1,71 @@
+"""Stage-by-stage check of the MLA decode kernel on a GPU box (development tool, not a test):
+raw S^T of the first tile (debug_logits) against q.k^T, then the output against the oracle, for a few tiny shapes.
+
+    python tools/mla_debug.py
+"""
+import ctypes as C
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import torch_oracle as orc  # noqa: E402
+from vllm_metax_b200 import _native  # noqa: E402
+
+lib = _native.load()
+DEV = "cuda:0"
+
+
+def run(d, splits=1, debug=True):
+    q = d["query"].to(DEV)
+    B, H, _ = q.shape
+    qn, qp = q[..., :512].contiguous(), q[..., 512:].contiguous()
+    cache, table, lens = d["kv_cache"].to(DEV), d["block_tables"].to(DEV), d["seq_lens"].to(DEV)
+    out = torch.full((B, H, 512), float("nan"), dtype=q.dtype, device=DEV)
+    lse = torch.full((B, H), float("nan"), dtype=torch.float32, device=DEV)
+    dbg = torch.full((128, 64), float("nan"), dtype=torch.float32, device=DEV)
+    p = _native.MlaDecodeParams()
+    p.out, p.lse, p.q_nope, p.q_pe, p.kv_cache = out.data_ptr(), lse.data_ptr(), qn.data_ptr(), qp.data_ptr(), cache.data_ptr()
+    p.seq_lens, p.page_table = lens.data_ptr(), table.data_ptr()
+    p.out_seq_stride, p.out_head_stride = out.stride(0), out.stride(1)
+    p.q_nope_seq_stride, p.q_nope_head_stride = qn.stride(0), qn.stride(1)
+    p.q_pe_seq_stride, p.q_pe_head_stride = qp.stride(0), qp.stride(1)
+    p.block_stride, p.entry_stride = cache.stride(0), cache.stride(1)
+    p.page_table_stride, p.lse_stride, p.num_blocks = table.stride(0), lse.stride(0), cache.shape[0]
+    p.scale, p.num_seqs, p.num_heads, p.page_size, p.max_pages = d["scale"], B, H, cache.shape[1], table.shape[1]
+    p.dtype = _native.DTYPE_BF16 if q.dtype == torch.bfloat16 else _native.DTYPE_F16
+    p.num_kv_splits = splits
+    need = lib.b200_mla_decode_workspace_bytes(B, H, table.shape[1] * cache.shape[1], splits)
+    ws = torch.empty(max(need, 16), dtype=torch.uint8, device=DEV)
+    p.workspace, p.workspace_bytes = ws.data_ptr(), need
+    p.debug_logits = dbg.data_ptr() if debug else None
+    rc = lib.b200_mla_decode(C.byref(p), None)
+    assert rc == 0, lib.b200_last_error().decode()
+    torch.cuda.synchronize()
+    return out.cpu(), lse.cpu(), dbg.cpu()
+
+
+def main():
+    for (B, H, page, L, splits) in [(1, 16, 64, 128, 1), (1, 16, 16, 128, 1), (1, 64, 64, 128, 1), (1, 16, 64, 100, 1),
+                                    (2, 16, 64, 300, 1), (1, 128, 64, 700, 1), (2, 32, 128, 1500, 3)]:
+        d = orc.make_mla_inputs(B, H, page, L, seed=3, varlen=False)
+        ref_out, ref_lse = orc.mla_decode(d["query"], d["kv_cache"], d["scale"], d["block_tables"], d["seq_lens"])
+        out, lse, dbg = run(d, splits)
+        kv = d["kv_cache"][d["block_tables"][0].long()].reshape(-1, 576)[:min(L, 128)].float()
+        s_ref = kv @ d["query"][0, :min(H, 64)].float().t()                      # [tokens, heads]
+        n = s_ref.shape[0]
+        s_err = (dbg[:n, :s_ref.shape[1]] - s_ref).abs().max().item()
+        o_err = (out.float() - ref_out).abs().max().item()
+        l_err = (lse - ref_lse).abs().max().item()
+        print("B%d H%d page%d L%d splits%d: S^T err %.3e (|S| max %.1f)  out err %.3e (|out| max %.2f)  lse err %.3e" % (
+            B, H, page, L, splits, s_err, s_ref.abs().max().item(), o_err, ref_out.abs().max().item(), l_err), flush=True)
+        if o_err > 1e-2:
+            bad = (out.float() - ref_out).abs()
+            print("   worst (seq, head, dv):", [int(v) for v in torch.unravel_index(bad.argmax(), bad.shape)],
+                  " per-dv-block err:", [round(bad[..., j * 128:(j + 1) * 128].max().item(), 4) for j in range(4)],
+                  " nan count:", int(torch.isnan(out.float()).sum()))
+
+
+if __name__ == "__main__":
+    main()

@@ -262,3 +262,43 @@ def reserve_workspace(query_like: torch.Tensor, max_seq_len: int, reset: bool = 
     that those ops never allocate; without it their first call on a stream allocates ~27 MB lazily, and raises if that
     first call happens under CUDA-graph capture."""
     torch.ops._C_b200.reserve_workspace(query_like, max_seq_len, reset)
+
+
+def cutlass_mla_decode(
+    out: torch.Tensor,
+    q_nope: torch.Tensor,
+    q_pe: torch.Tensor,
+    kv_c_and_k_pe_cache: torch.Tensor,
+    seq_lens: torch.Tensor,
+    page_table: torch.Tensor,
+    scale: float,
+) -> torch.Tensor:
+    """reference: csrc/torch_bindings.cpp:287-290 -> csrc/attention/mla/cutlass_mla_entry.cu:28-38.  q_nope
+    [B, H, 512], q_pe [B, H, 64], cache [num_blocks, page, 576], out [B, H, 512]; H <= 128 (the reference needs 128)."""
+    torch.ops._C.cutlass_mla_decode(out, q_nope, q_pe, kv_c_and_k_pe_cache, seq_lens, page_table, scale)
+    return out
+
+
+def sm100_cutlass_mla_decode(
+    out: torch.Tensor,
+    lse: torch.Tensor,
+    q_nope: torch.Tensor,
+    q_pe: torch.Tensor,
+    kv_c_and_k_pe_cache: torch.Tensor,
+    seq_lens: torch.Tensor,
+    page_table: torch.Tensor,
+    workspace: torch.Tensor,
+    scale: float,
+    num_kv_splits: int,
+) -> torch.Tensor:
+    """the call the reference's test makes (tests/kernels/attention/test_cutlass_mla_decode.py:121-123; upstream
+    wrapper _custom_ops.py:3017-3041): also writes lse [B, H] (natural log), workspace from
+    sm100_cutlass_mla_get_workspace_size, num_kv_splits -1 = choose / 1 = no token split."""
+    torch.ops._C.sm100_cutlass_mla_decode(out, lse, q_nope, q_pe, kv_c_and_k_pe_cache, seq_lens, page_table, workspace,
+                                          scale, num_kv_splits)
+    return out
+
+
+def sm100_cutlass_mla_get_workspace_size(max_seq_len: int, num_batches: int, sm_count: int, num_kv_splits: int) -> int:
+    """reference test :112-113; upstream wrapper _custom_ops.py:3044-3049"""
+    return torch.ops._C.sm100_cutlass_mla_get_workspace_size(max_seq_len, num_batches, sm_count, num_kv_splits)

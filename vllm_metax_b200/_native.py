@@ -35,6 +35,8 @@ EXPORTED_SYMBOLS = (
     "b200_copy_blocks",
     "b200_copy_blocks_mla",
     "b200_concat_and_cache_mla",
+    "b200_mla_decode",
+    "b200_mla_decode_workspace_bytes",
     "b200_swap_blocks",
     "b200_gather_cache",
     "b200_dcp_exchange_fold",
@@ -209,6 +211,39 @@ class ConcatMlaParams(C.Structure):
     ]
 
 
+class MlaDecodeParams(C.Structure):
+    _fields_ = [
+        ("out", C.c_void_p),
+        ("lse", C.c_void_p),
+        ("q_nope", C.c_void_p),
+        ("q_pe", C.c_void_p),
+        ("kv_cache", C.c_void_p),
+        ("seq_lens", C.c_void_p),
+        ("page_table", C.c_void_p),
+        ("workspace", C.c_void_p),
+        ("workspace_bytes", C.c_uint64),
+        ("out_seq_stride", C.c_int64),
+        ("out_head_stride", C.c_int64),
+        ("q_nope_seq_stride", C.c_int64),
+        ("q_nope_head_stride", C.c_int64),
+        ("q_pe_seq_stride", C.c_int64),
+        ("q_pe_head_stride", C.c_int64),
+        ("block_stride", C.c_int64),
+        ("entry_stride", C.c_int64),
+        ("page_table_stride", C.c_int64),
+        ("lse_stride", C.c_int64),
+        ("num_blocks", C.c_int64),
+        ("scale", C.c_float),
+        ("num_seqs", C.c_int32),
+        ("num_heads", C.c_int32),
+        ("page_size", C.c_int32),
+        ("max_pages", C.c_int32),
+        ("dtype", C.c_int32),
+        ("num_kv_splits", C.c_int32),
+        ("debug_logits", C.c_void_p),
+    ]
+
+
 class DcpFoldParams(C.Structure):
     _fields_ = [
         ("peer_out", C.POINTER(C.c_void_p)),
@@ -297,6 +332,10 @@ def load() -> C.CDLL:
     lib.b200_copy_blocks_mla.restype = C.c_int
     lib.b200_concat_and_cache_mla.argtypes = [P(ConcatMlaParams), C.c_void_p]
     lib.b200_concat_and_cache_mla.restype = C.c_int
+    lib.b200_mla_decode.argtypes = [P(MlaDecodeParams), C.c_void_p]
+    lib.b200_mla_decode.restype = C.c_int
+    lib.b200_mla_decode_workspace_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int64, C.c_int32]
+    lib.b200_mla_decode_workspace_bytes.restype = C.c_uint64
     lib.b200_swap_blocks.argtypes = [C.c_void_p, C.c_void_p, P(C.c_int64), C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
     lib.b200_swap_blocks.restype = C.c_int
     lib.b200_gather_cache.argtypes = [P(GatherCacheParams), C.c_void_p]

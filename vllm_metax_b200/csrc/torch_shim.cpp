@@ -711,6 +711,111 @@ void concat_and_cache_mla(at::Tensor& kv_c, at::Tensor& k_pe, at::Tensor& kv_cac
   check_status(b200_concat_and_cache_mla(&p, at::cuda::getCurrentCUDAStream()), "concat_and_cache_mla");
 }
 
+// ---- MLA decode attention -------------------------------------------------------------------------------------
+// csrc/attention/mla/cutlass_mla_kernels.cu:154-202 (the reference's checks; it requires exactly 128 heads and the
+// caller pads, any count <= 128 is accepted here) and :141-147 (the reference allocates its workspace inside the op).
+void mla_decode_common(const at::Tensor& out, const at::Tensor* lse, const at::Tensor& q_nope, const at::Tensor& q_pe,
+                       const at::Tensor& cache, const at::Tensor& seq_lens, const at::Tensor& page_table,
+                       const at::Tensor* workspace, double scale, int64_t num_kv_splits, const char* what) {
+  TORCH_CHECK(q_nope.is_cuda(), "q_nope must be on CUDA");
+  TORCH_CHECK(q_nope.dim() == 3, "q_nope must be a 3D tensor");
+  TORCH_CHECK(q_pe.dim() == 3, "q_pe must be a 3D tensor");
+  TORCH_CHECK(cache.dim() == 3, "kv_c_and_k_pe_cache must be a 3D tensor");
+  TORCH_CHECK(seq_lens.dim() == 1, "seq_lens must be a 1D tensor");
+  TORCH_CHECK(page_table.dim() == 2, "page_table must be a 2D tensor");
+  TORCH_CHECK(out.dim() == 3, "out must be a 3D tensor");
+  const int64_t B = q_nope.size(0), H = q_nope.size(1);
+  TORCH_CHECK(q_nope.size(2) == 512, "D_q_nope must be equal to 512");
+  TORCH_CHECK(q_pe.size(2) == 64, "D_q_pe must be equal to 64");
+  TORCH_CHECK(cache.size(2) == 576, "D_ckv must be equal to 576");
+  TORCH_CHECK(out.size(2) == 512, "D_o must be equal to 512");
+  TORCH_CHECK(H == q_pe.size(1) && H == out.size(1) && H >= 1 && H <= 128,
+              "H_q_nope, H_q_pe, and H_o must be equal and at most 128");
+  const int64_t page = cache.size(1);
+  TORCH_CHECK(page > 0 && (page & (page - 1)) == 0, "PAGE_SIZE must be a power of 2");
+  TORCH_CHECK(page >= 16, "PAGE_SIZE must be at least 16");
+  TORCH_CHECK(B == q_pe.size(0) && B == page_table.size(0) && B == out.size(0) && B == seq_lens.size(0),
+              "Batch dims must be same for page_table, q_nope and q_pe, and out");
+  TORCH_CHECK(q_nope.scalar_type() == at::kHalf || q_nope.scalar_type() == at::kBFloat16,
+              "q_nope must be a half or bfloat16 tensor (float8_e4m3fn MLA is not implemented)");
+  TORCH_CHECK(cache.scalar_type() == q_nope.scalar_type() && q_pe.scalar_type() == q_nope.scalar_type() &&
+                  out.scalar_type() == q_nope.scalar_type(),
+              "kv_c_and_k_pe_cache, q_nope, q_pe and out must be the same type");
+  TORCH_CHECK(seq_lens.scalar_type() == at::kInt, "seq_lens must be a 32-bit integer tensor");
+  TORCH_CHECK(page_table.scalar_type() == at::kInt, "page_table must be a 32-bit integer tensor");
+  TORCH_CHECK(q_nope.stride(2) == 1 && q_pe.stride(2) == 1 && cache.stride(2) == 1 && out.stride(2) == 1 &&
+                  page_table.stride(1) == 1 && seq_lens.is_contiguous(),
+              "innermost dims must be contiguous");
+  TORCH_CHECK(q_pe.is_cuda() && cache.is_cuda() && seq_lens.is_cuda() && page_table.is_cuda() && out.is_cuda(),
+              "all tensors must be on the CUDA device");
+  b200_mla_decode_params_t p;
+  memset(&p, 0, sizeof(p));
+  p.out = out.data_ptr();
+  p.q_nope = q_nope.data_ptr();
+  p.q_pe = q_pe.data_ptr();
+  p.kv_cache = cache.data_ptr();
+  p.seq_lens = seq_lens.data_ptr<int32_t>();
+  p.page_table = page_table.data_ptr<int32_t>();
+  p.out_seq_stride = out.stride(0), p.out_head_stride = out.stride(1);
+  p.q_nope_seq_stride = q_nope.stride(0), p.q_nope_head_stride = q_nope.stride(1);
+  p.q_pe_seq_stride = q_pe.stride(0), p.q_pe_head_stride = q_pe.stride(1);
+  p.block_stride = cache.stride(0), p.entry_stride = cache.stride(1);
+  p.page_table_stride = page_table.stride(0);
+  p.num_blocks = cache.size(0);
+  p.scale = static_cast<float>(scale);
+  p.num_seqs = static_cast<int32_t>(B);
+  p.num_heads = static_cast<int32_t>(H);
+  p.page_size = static_cast<int32_t>(page);
+  p.max_pages = static_cast<int32_t>(page_table.size(1));
+  p.dtype = to_dtype(q_nope.scalar_type());
+  p.num_kv_splits = num_kv_splits <= 0 ? 0 : static_cast<int32_t>(num_kv_splits);
+  if (lse != nullptr) {
+    TORCH_CHECK(lse->scalar_type() == at::kFloat && lse->dim() == 2 && lse->size(0) == B && lse->size(1) >= H &&
+                    lse->stride(1) == 1 && lse->is_cuda(),
+                "lse must be a float32 [batch, heads] CUDA tensor");
+    p.lse = lse->data_ptr<float>();
+    p.lse_stride = lse->stride(0);
+  }
+  const at::cuda::OptionalCUDAGuard guard(device_of(q_nope));
+  const uint64_t need = b200_mla_decode_workspace_bytes(p.num_seqs, p.num_heads, (int64_t)p.max_pages * p.page_size,
+                                                        p.num_kv_splits);
+  at::Tensor own;
+  if (need > 0) {
+    if (workspace != nullptr && workspace->is_cuda() && (uint64_t)workspace->nbytes() >= need &&
+        reinterpret_cast<uintptr_t>(workspace->data_ptr()) % 16 == 0) {
+      p.workspace = workspace->data_ptr();
+      p.workspace_bytes = workspace->nbytes();
+    } else {  // as the reference op does (cutlass_mla_kernels.cu:141-147)
+      own = at::empty({static_cast<int64_t>(need)}, q_nope.options().dtype(at::kByte));
+      p.workspace = own.data_ptr();
+      p.workspace_bytes = need;
+    }
+  }
+  check_status(b200_mla_decode(&p, at::cuda::getCurrentCUDAStream()), what);
+}
+
+// csrc/torch_bindings.cpp:287-290 ; csrc/attention/mla/cutlass_mla_entry.cu:28-38
+void cutlass_mla_decode(at::Tensor& out, const at::Tensor& q_nope, const at::Tensor& q_pe, const at::Tensor& cache,
+                        const at::Tensor& seq_lens, const at::Tensor& page_table, double scale) {
+  mla_decode_common(out, nullptr, q_nope, q_pe, cache, seq_lens, page_table, nullptr, scale, 0, "cutlass_mla_decode");
+}
+
+// upstream 0.22's form of the same op (the one the reference's test calls, tests/kernels/attention/
+// test_cutlass_mla_decode.py:121-123): LSE output, caller-provided workspace, split count (-1 = choose)
+void sm100_cutlass_mla_decode(at::Tensor& out, at::Tensor& lse, const at::Tensor& q_nope, const at::Tensor& q_pe,
+                              const at::Tensor& cache, const at::Tensor& seq_lens, const at::Tensor& page_table,
+                              const at::Tensor& workspace, double scale, int64_t num_kv_splits) {
+  mla_decode_common(out, &lse, q_nope, q_pe, cache, seq_lens, page_table, &workspace, scale, num_kv_splits,
+                    "sm100_cutlass_mla_decode");
+}
+
+int64_t sm100_cutlass_mla_get_workspace_size(int64_t max_seq_len, int64_t num_batches, int64_t sm_count,
+                                             int64_t num_kv_splits) {
+  (void)sm_count;
+  return static_cast<int64_t>(b200_mla_decode_workspace_bytes(static_cast<int32_t>(num_batches), 128, max_seq_len,
+                                                              num_kv_splits <= 0 ? 0 : static_cast<int32_t>(num_kv_splits)));
+}
+
 void fill_gather_params(b200_gather_cache_params_t& p, const at::Tensor& src_cache, const at::Tensor& dst,
                         const at::Tensor& block_table, const at::Tensor& cu_seq_lens, int64_t batch_size,
                         const std::optional<at::Tensor>& seq_starts) {
@@ -895,6 +1000,22 @@ const char* kSchemaFlash =
     "paged_attention_flash(Tensor! out, Tensor!? lse, Tensor query, Tensor key_cache, Tensor value_cache, "
     "float scale, Tensor block_tables, Tensor seq_lens, int max_seq_len, Tensor? alibi_slopes) -> ()";
 
+// csrc/torch_bindings.cpp:287-290
+const char* kSchemaCutlassMla =
+    "cutlass_mla_decode(Tensor! out, Tensor q_nope, Tensor q_pe,"
+    "                   Tensor kv_c_and_k_pe_cache, Tensor seq_lens,"
+    "                   Tensor page_table, float scale) -> ()";
+// upstream vLLM 0.22.0 (_C_stable_libtorch), string-identical
+const char* kSchemaSm100Mla =
+    "sm100_cutlass_mla_decode(Tensor! out, Tensor! lse, Tensor q_nope,"
+    "                         Tensor q_pe, Tensor kv_c_and_k_pe_cache,"
+    "                         Tensor seq_lens, Tensor page_table,"
+    "                         Tensor workspace, float scale,"
+    "                         int num_kv_splits) -> ()";
+const char* kSchemaSm100MlaWs =
+    "sm100_cutlass_mla_get_workspace_size(int max_seq_len, int num_batches,"
+    "                                     int sm_count, int num_kv_splits) -> int";
+
 bool op_exists(const char* qualified) {
   return c10::Dispatcher::singleton().findSchema({qualified, ""}).has_value();
 }
@@ -936,6 +1057,14 @@ void register_all() {
     register_op(keep, "_C_cache_ops", "cp_gather_cache", kSchemaCpGather, &cp_gather_cache);
     register_op(keep, "_C_cache_ops", "copy_blocks_mla", kSchemaCopyMla, &copy_blocks_mla);
     register_op(keep, "_C_cache_ops", "concat_and_cache_mla", kSchemaConcatMla, &concat_and_cache_mla);
+    register_op(keep, "_C", "cutlass_mla_decode", kSchemaCutlassMla, &cutlass_mla_decode);
+    register_op(keep, "_C", "sm100_cutlass_mla_decode", kSchemaSm100Mla, &sm100_cutlass_mla_decode);
+    if (!op_exists("_C::sm100_cutlass_mla_get_workspace_size")) {  // no tensor arguments: a catch-all kernel
+      auto frag = std::make_unique<torch::Library>(torch::Library::FRAGMENT, "_C", std::nullopt, __FILE__, __LINE__);
+      frag->def(kSchemaSm100MlaWs);
+      frag->impl("sm100_cutlass_mla_get_workspace_size", &sm100_cutlass_mla_get_workspace_size);
+      keep.push_back(std::move(frag));
+    }
     register_op(keep, "_C_b200", "paged_attention_v1_lse", kSchemaV1Lse, &paged_attention_v1_lse);
     register_op(keep, "_C_b200", "paged_attention_flash", kSchemaFlash, &paged_attention_flash);
     register_op(keep, "_C", "rotary_embedding", kSchemaRotary, &rotary_embedding);
