@@ -1,0 +1,122 @@
+"""MLA decode timing on a GPU box: this repository's kernel (--impl ours) or the stock sm_100a CUTLASS kernel that
+upstream vLLM 0.22 ships (--impl upstream; the reference's csrc/attention/mla/cutlass_mla_kernels.cu is the same
+kernel).  The two run in separate processes on identical seeded inputs; each writes a JSON line per shape and a small
+output sample so the results can be compared afterwards (--compare a.pt b.pt).
+
+    python tools/mla_bench.py --impl ours --out gpurun_out/mla_ours
+    python tools/mla_bench.py --impl upstream --out gpurun_out/mla_upstream
+    python tools/mla_bench.py --compare gpurun_out/mla_ours.pt gpurun_out/mla_upstream.pt
+"""
+import argparse
+import json
+import math
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SHAPES = [  # batch, ctx, heads
+    (128, 4096, 128), (128, 8192, 128), (16, 32768, 128), (1, 131072, 128),
+    (128, 4096, 16), (128, 8192, 16), (128, 8192, 64), (1, 131072, 16),
+]
+PAGE = 64
+
+
+def make(b, L, H, dev):
+    g = torch.Generator(device=dev).manual_seed(b * 7 + L + H)
+    pages = L // PAGE
+    nb = b * pages
+    cache = torch.randn(nb, PAGE, 576, generator=g, device=dev, dtype=torch.bfloat16)
+    q = torch.randn(b, H, 576, generator=g, device=dev, dtype=torch.bfloat16)
+    table = torch.randperm(nb, generator=g, device=dev).to(torch.int32).view(b, pages)
+    lens = torch.full((b,), L, dtype=torch.int32, device=dev)
+    return q, cache, table, lens
+
+
+def time_it(fn, reps, flush):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(reps):
+        if flush is not None:
+            flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--impl", choices=["ours", "upstream"])
+    ap.add_argument("--out", default="gpurun_out/mla")
+    ap.add_argument("--compare", nargs=2)
+    ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--splits", type=int, default=-1)
+    ap.add_argument("--only", type=int, default=-1)
+    args = ap.parse_args()
+    if args.compare:
+        a, b = torch.load(args.compare[0]), torch.load(args.compare[1])
+        for k in sorted(set(a) & set(b)):
+            x, y = a[k].double(), b[k].double()
+            cd = 1 - 2 * (x * y).sum().item() / max((x * x + y * y).sum().item(), 1e-12)
+            print("%s: max-abs diff %.3e cos-diff %.2e" % (k, (x - y).abs().max().item(), cd))
+        return
+    dev = "cuda:0"
+    if args.impl == "ours":
+        sys.path.insert(0, ROOT)
+        import vllm_metax_b200
+        vllm_metax_b200.import_kernels()
+    else:
+        import vllm  # noqa: F401
+        try:
+            import vllm._C_stable_libtorch  # noqa: F401
+        except Exception as e:
+            print(json.dumps({"impl": "upstream", "unavailable": "%s: %s" % (type(e).__name__, e)}))
+            return
+    op = torch.ops._C.sm100_cutlass_mla_decode
+    ws_size = torch.ops._C.sm100_cutlass_mla_get_workspace_size
+    samples = {}
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for idx, (b, L, H) in enumerate(SHAPES):
+        if args.only >= 0 and idx != args.only:
+            continue
+        q, cache, table, lens = make(b, L, H, dev)
+        Hk = H if args.impl == "ours" else 128   # the stock kernel needs exactly 128 heads: the caller pads
+        qn = torch.zeros(b, Hk, 512, dtype=q.dtype, device=dev)
+        qp = torch.zeros(b, Hk, 64, dtype=q.dtype, device=dev)
+        qn[:, :H], qp[:, :H] = q[..., :512], q[..., 512:]
+        out = torch.empty(b, Hk, 512, dtype=q.dtype, device=dev)
+        lse = torch.empty(b, Hk, dtype=torch.float32, device=dev)
+        ws = torch.empty(max(16, ws_size(L, b, 148, args.splits)), dtype=torch.uint8, device=dev)
+        scale = 1.0 / math.sqrt(576)
+
+        def fn():
+            op(out, lse, qn, qp, cache, lens, table, ws, scale, args.splits)
+
+        try:
+            med, mn = time_it(fn, args.reps, flush if b * L * 1152 < (300 << 20) else None)
+        except Exception as e:
+            print(json.dumps({"impl": args.impl, "shape": [b, L, H], "error": "%s: %s" % (type(e).__name__, str(e)[:300])}), flush=True)
+            continue
+        kv_bytes = b * L * 1152
+        byt = kv_bytes + b * H * (576 + 512) * 2
+        flops = 2.0 * b * L * H * (576 + 512)
+        print(json.dumps({"impl": args.impl, "shape": {"batch": b, "ctx": L, "heads": H, "page": PAGE}, "us": med * 1e3,
+                          "us_min": mn * 1e3, "gbs": byt / med / 1e6, "tflops": flops / med / 1e9,
+                          "heads_computed": Hk}), flush=True)
+        samples["out_b%d_L%d_H%d" % (b, L, H)] = out[:2, :H].float().cpu()
+        samples["lse_b%d_L%d_H%d" % (b, L, H)] = lse[:2, :H].cpu()
+        del q, cache, table, lens, qn, qp, out, lse, ws
+        torch.cuda.empty_cache()
+    torch.save(samples, args.out + ".pt")
+
+
+if __name__ == "__main__":
+    main()
