@@ -80,7 +80,6 @@ def test_grid(ops, H, page, L):
     check(out, lse, ref_out, ref_lse, torch.bfloat16)
 
 
-@pytest.mark.parametrize("splits", [1, 2, 5, -1])
 def test_small_magnitude_data_meets_the_2e_3_bar(ops):
     """north_star's max-abs 2e-3 on data scaled like the reference's attention tests (|x| <= D^-0.5 ... here std 0.2)"""
     d = orc.make_mla_inputs(4, 128, 64, 900, seed=11, std=0.2)
@@ -91,6 +90,7 @@ def test_small_magnitude_data_meets_the_2e_3_bar(ops):
     torch.testing.assert_close(lse, ref_lse, atol=2e-3, rtol=1e-4)
 
 
+@pytest.mark.parametrize("splits", [1, 2, 5, -1])
 def test_token_splits(ops, splits):
     d = orc.make_mla_inputs(2, 32, 64, 3000, seed=splits + 50)
     ref_out, ref_lse = orc.mla_decode(d["query"], d["kv_cache"], d["scale"], d["block_tables"], d["seq_lens"])
