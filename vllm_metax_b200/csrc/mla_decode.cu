@@ -12,8 +12,8 @@
 // A operand of the second, so K chunks and V chunks are the same 16 KiB ring stages, loaded once for each product.
 // TMEM: S^T double-buffered (2 x NG columns) + O^T (4 x NG columns).
 //
-// One CTA per (sequence, head group of NG <= 64, token split).  Warps: 0 = TMA producer (one lane), 1 = MMA issuer,
-// 2..5 = softmax / epilogue (one TMEM lane = one token row each).  Softmax uses a lazily updated per-head reference
+// One CTA per (sequence, head group of NG <= 64, token split).  Warps: 0..3 = softmax / epilogue (one TMEM lane = one
+// token row each), 4 = MMA issuer, 5..8 = TMA producers (one issuing lane each, ring fills dealt round-robin).  Softmax uses a lazily updated per-head reference
 // m_ref (log2 units): p = 2^(s - m_ref); the column-wise (cross-lane) maximum is only taken when some logit passes
 // m_ref by kTau, after which O^T and the running sums are rescaled.  Row sums are kept per thread and reduced once.
 #include <cuda.h>
@@ -28,7 +28,9 @@ constexpr int kTile = 128;            // tokens per tile (MMA M of S^T)
 constexpr int kChunkBytes = 16384;    // ring stage: 128 rows x 128 B
 constexpr int kKChunks = 9;           // 576 / 64
 constexpr int kVChunks = 8;           // 512 / 64
-constexpr int kMlaThreads = 192;
+constexpr int kProducers = 4;         // issuing warps: one thread tops out near 47 GB/s, four reach ~120 GB/s per SM
+constexpr int kMmaWarp = 4;
+constexpr int kMlaThreads = (4 + 1 + kProducers) * 32;  // warps 0-3 softmax, 4 MMA issuer, 5-8 producers
 constexpr int kSoftmaxThreads = 128;
 constexpr int kMaxSlots = 16;
 constexpr float kTau = 16.f;          // re-reference when a logit passes m_ref by 2^16
@@ -193,7 +195,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   }
   if (tid < 64) misc->mref[tid] = -INFINITY;
   constexpr uint32_t kCols = NG == 64 ? 512 : (NG == 32 ? 256 : 128);  // power of two >= 6 * NG
-  if (warp == 1) {
+  if (warp == kMmaWarp) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&misc->tmem_base)),
                  "r"(kCols)
                  : "memory");
@@ -206,23 +208,27 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   const uint32_t tm_s[2] = {tmem, tmem + NG};
   const uint32_t tm_o = tmem + 2 * NG;
 
-  if (warp == 0) {
-    // =================== TMA producer (one lane) ===================
+  if (warp > kMmaWarp) {
+    // =================== TMA producers: fill f of the ring sequence is issued by producer f % kProducers ===================
+    const int pw = warp - kMmaWarp - 1;
     if (lane == 0) {
-      // query group: 8 latent chunks + the rope chunk, heads beyond H zero-filled by the tensor map bounds
-      mbar_expect_tx(smem_u32(&misc->q_full), (uint32_t)(kKChunks * NG * 128));
-      for (int c = 0; c < kVChunks; ++c) tma_load_3d(q_u32 + c * NG * 128, &tm_qn, c * 64, h0, seq, smem_u32(&misc->q_full));
-      tma_load_3d(q_u32 + kVChunks * NG * 128, &tm_qp, 0, h0, seq, smem_u32(&misc->q_full));
+      if (pw == 0) {
+        // query group: 8 latent chunks + the rope chunk, heads beyond H zero-filled by the tensor map bounds
+        mbar_expect_tx(smem_u32(&misc->q_full), (uint32_t)(kKChunks * NG * 128));
+        for (int c = 0; c < kVChunks; ++c) tma_load_3d(q_u32 + c * NG * 128, &tm_qn, c * 64, h0, seq, smem_u32(&misc->q_full));
+        tma_load_3d(q_u32 + kVChunks * NG * 128, &tm_qp, 0, h0, seq, smem_u32(&misc->q_full));
+      }
 
       const int32_t* table = p.page_table + (long long)seq * p.page_table_stride;
       const int box_rows = p.box_rows;
       const uint32_t box_bytes = (uint32_t)box_rows * 128u;
-      int slot = 0;
+      int slot = 0, turn = 0;
       uint32_t phase = 0;  // parity of the ring pass
       auto advance = [&]() {
         if (++slot == nslots) { slot = 0; phase ^= 1; }
+        if (++turn == kProducers) turn = 0;
       };
-      // chunks c0 .. c0+n-1 of the tile starting at token tok0 (9 K chunks, or 8 V chunks)
+      // chunks 0 .. n-1 of the tile starting at token tok0 (9 K chunks, or 8 V chunks)
       auto load_chunks = [&](int tok0, int nchunks) {
         const int valid = min(kTile, L - tok0);                  // rows of this tile that hold cache entries
         const int vbox = (valid + box_rows - 1) / box_rows;
@@ -236,21 +242,25 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           }
         }
         for (int c = 0; c < nchunks; ++c) {
-          mbar_wait(smem_u32(&misc->empty[slot]), phase ^ 1);
-          const uint32_t full = smem_u32(&misc->full[slot]);
-          mbar_expect_tx(full, box_bytes * (uint32_t)vbox);
-          const uint32_t dst = ring_u32 + (uint32_t)slot * kChunkBytes;
+          if (turn == pw) {
+            mbar_wait(smem_u32(&misc->empty[slot]), phase ^ 1);
+            const uint32_t full = smem_u32(&misc->full[slot]);
+            mbar_expect_tx(full, box_bytes * (uint32_t)vbox);
+            const uint32_t dst = ring_u32 + (uint32_t)slot * kChunkBytes;
 #pragma unroll
-          for (int b = 0; b < 8; ++b)
-            if (b < vbox) tma_load_3d(dst + b * box_bytes, &tm_kv, c * 64, row[b], page[b], full);
+            for (int b = 0; b < 8; ++b)
+              if (b < vbox) tma_load_3d(dst + b * box_bytes, &tm_kv, c * 64, row[b], page[b], full);
+          }
           advance();
         }
       };
       auto k_phase = [&](int i) {
         load_chunks(t0 + i * kTile, kKChunks);
         // filler stage: keeps every V pair on an even slot, so a pair never straddles the ring's wrap-around
-        mbar_wait(smem_u32(&misc->empty[slot]), phase ^ 1);
-        mbar_arrive(smem_u32(&misc->full[slot]));
+        if (turn == pw) {
+          mbar_wait(smem_u32(&misc->empty[slot]), phase ^ 1);
+          mbar_arrive(smem_u32(&misc->full[slot]));
+        }
         advance();
       };
       k_phase(0);
@@ -259,7 +269,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
         load_chunks(t0 + i * kTile, kVChunks);
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarp) {
     // =================== MMA issuer ===================
     const int fmt = p.f16 ? 0 : 1;
     const uint32_t idesc_s = idesc_f16(128, NG, fmt, 0);
@@ -341,42 +351,49 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     if (lane == 0) umma_commit(smem_u32(&misc->o_full));
     __syncwarp();
   } else {
-    // =================== softmax / epilogue warps (2..5): thread = one token row = one TMEM lane ===================
+    // =================== softmax / epilogue warps (0..3): thread = one token row = one TMEM lane ===================
     const int quad = warp & 3;                   // TMEM lane quadrant this warp may access
     const int row = quad * 32 + lane;            // token row within the tile / dv row within an O^T block
-    const int st = tid - 64;                     // 0..127
+    const int st = tid;                          // 0..127
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     float lsum[NG];
 #pragma unroll
     for (int h = 0; h < NG; ++h) lsum[h] = 0.f;
 
+    constexpr int HC = NG < 32 ? NG : 32;        // columns handled per pass (register budget)
     for (int i = 0; i < T; ++i) {
       const int b = i & 1;
       mbar_wait(smem_u32(&misc->s_full[b]), (i >> 1) & 1);
       tc_fence_after();
-      uint32_t r[NG];
-      tmem_ld<NG>(tm_s[b] + lane_base, r);
-      tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(smem_u32(&misc->s_free[b]));
-      if (p.debug_logits != nullptr && i == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
-#pragma unroll
-        for (int h = 0; h < NG; ++h) p.debug_logits[row * 64 + h] = __uint_as_float(r[h]);
-      }
       const bool valid = t0 + i * kTile + row < t1;
-      float x[NG];
+      // ---- pass 1: does any logit pass its reference by kTau?  (S^T is read again in pass 2: TMEM reads are cheap) ----
       bool over = false;
 #pragma unroll
-      for (int h = 0; h < NG; ++h) {
-        x[h] = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
-        over |= x[h] > misc->mref[h] + kTau;
+      for (int c0 = 0; c0 < NG; c0 += HC) {
+        uint32_t r[HC];
+        tmem_ld<HC>(tm_s[b] + c0 + lane_base, r);
+        tmem_ld_wait();
+        if (p.debug_logits != nullptr && i == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
+#pragma unroll
+          for (int h = 0; h < HC; ++h) p.debug_logits[row * 64 + c0 + h] = __uint_as_float(r[h]);
+        }
+#pragma unroll
+        for (int h = 0; h < HC; ++h)
+          over |= valid && __uint_as_float(r[h]) * p.scale_log2 > misc->mref[c0 + h] + kTau;
       }
       if (softmax_bar_or(over)) {
         // ---- rare path: raise the references to this tile's column maxima, rescale O^T and the running sums ----
 #pragma unroll
-        for (int h = 0; h < NG; ++h) {
-          const int m = __reduce_max_sync(0xffffffffu, f32_sortable(x[h]));
-          if (lane == 0) misc->colmax[warp - 2][h] = m;
+        for (int c0 = 0; c0 < NG; c0 += HC) {
+          uint32_t r[HC];
+          tmem_ld<HC>(tm_s[b] + c0 + lane_base, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int h = 0; h < HC; ++h) {
+            const float x = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
+            const int m = __reduce_max_sync(0xffffffffu, f32_sortable(x));
+            if (lane == 0) misc->colmax[warp][c0 + h] = m;
+          }
         }
         softmax_bar_sync();
         if (st < NG) {
@@ -408,23 +425,31 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           tc_fence_before();
         }
       }
-      // ---- probabilities: p = 2^(x - m_ref); bf16/f16 into the P^T operand, fp32 into the running sums ----
-      uint32_t pk[NG];  // one 16-bit value per head
-#pragma unroll
-      for (int h = 0; h < NG; ++h) {
-        const float pv = fast_exp2(x[h] - misc->mref[h]);
-        lsum[h] += pv;
-        pk[h] = p.f16 ? (uint32_t)__half_as_ushort(__float2half_rn(pv)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(pv));
-      }
-      if (i > 0) mbar_wait(smem_u32(&misc->p_free), (i - 1) & 1);
+      // ---- pass 2: p = 2^(x - m_ref); 16-bit values into the P^T operand, fp32 into the running sums ----
       // P^T[h][token]: K-major SW128, chunk = row / 64, 16-byte unit (row % 64) / 8 XOR (h % 8)
-      {
-        const uint32_t chunk = p_u32 + (row >> 6) * NG * 128;
-        const uint32_t unit = (row & 63) >> 3, within = (row & 7) * 2;
+      const uint32_t chunk = p_u32 + (row >> 6) * NG * 128;
+      const uint32_t unit = (row & 63) >> 3, within = (row & 7) * 2;
 #pragma unroll
-        for (int h = 0; h < NG; ++h) {
-          const uint32_t addr = chunk + h * 128 + ((unit ^ (h & 7)) << 4) + within;
-          asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)pk[h]) : "memory");
+      for (int c0 = 0; c0 < NG; c0 += HC) {
+        uint32_t r[HC];
+        tmem_ld<HC>(tm_s[b] + c0 + lane_base, r);
+        tmem_ld_wait();
+        if (c0 + HC == NG) {   // last read of this S^T buffer
+          tc_fence_before();
+          mbar_arrive(smem_u32(&misc->s_free[b]));
+        }
+#pragma unroll
+        for (int h = 0; h < HC; ++h) {
+          const float x = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
+          const float pv = fast_exp2(x - misc->mref[c0 + h]);
+          lsum[c0 + h] += pv;
+          r[h] = p.f16 ? (uint32_t)__half_as_ushort(__float2half_rn(pv)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(pv));
+        }
+        if (c0 == 0 && i > 0) mbar_wait(smem_u32(&misc->p_free), (i - 1) & 1);
+#pragma unroll
+        for (int h = 0; h < HC; ++h) {
+          const uint32_t addr = chunk + (c0 + h) * 128 + ((unit ^ (h & 7)) << 4) + within;
+          asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)r[h]) : "memory");
         }
       }
       fence_async_smem();
@@ -480,7 +505,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   }
 
   __syncthreads();
-  if (warp == 1) {
+  if (warp == kMmaWarp) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kCols) : "memory");
   }
