@@ -24,7 +24,7 @@ def run(d, splits=1, debug=True):
     cache, table, lens = d["kv_cache"].to(DEV), d["block_tables"].to(DEV), d["seq_lens"].to(DEV)
     out = torch.full((B, H, 512), float("nan"), dtype=q.dtype, device=DEV)
     lse = torch.full((B, H), float("nan"), dtype=torch.float32, device=DEV)
-    dbg = torch.full((128, 64), float("nan"), dtype=torch.float32, device=DEV)
+    dbg = torch.zeros(128 * 64 + 3 * 64 * 4 * 2, dtype=torch.float32, device=DEV)
     p = _native.MlaDecodeParams()
     p.out, p.lse, p.q_nope, p.q_pe, p.kv_cache = out.data_ptr(), lse.data_ptr(), qn.data_ptr(), qp.data_ptr(), cache.data_ptr()
     p.seq_lens, p.page_table = lens.data_ptr(), table.data_ptr()
@@ -43,7 +43,8 @@ def run(d, splits=1, debug=True):
     rc = lib.b200_mla_decode(C.byref(p), None)
     assert rc == 0, lib.b200_last_error().decode()
     torch.cuda.synchronize()
-    return out.cpu(), lse.cpu(), dbg.cpu()
+    stamps = dbg[128 * 64:].cpu().view(torch.int64).view(3, 64, 4)
+    return out.cpu(), lse.cpu(), dbg[:128 * 64].view(128, 64).cpu(), stamps
 
 
 def main():
@@ -51,7 +52,7 @@ def main():
                                     (2, 16, 64, 300, 1), (1, 128, 64, 700, 1), (2, 32, 128, 1500, 3)]:
         d = orc.make_mla_inputs(B, H, page, L, seed=3, varlen=False)
         ref_out, ref_lse = orc.mla_decode(d["query"], d["kv_cache"], d["scale"], d["block_tables"], d["seq_lens"])
-        out, lse, dbg = run(d, splits)
+        out, lse, dbg, _ = run(d, splits)
         kv = d["kv_cache"][d["block_tables"][0].long()].reshape(-1, 576)[:min(L, 128)].float()
         s_ref = kv @ d["query"][0, :min(H, 64)].float().t()                      # [tokens, heads]
         n = s_ref.shape[0]
@@ -67,5 +68,24 @@ def main():
                   " nan count:", int(torch.isnan(out.float()).sum()))
 
 
+def timeline(B, H, L, page=64):
+    """per-tile clock64 stamps of CTA 0 (seq 0, group 0, split 0) while the whole batch runs"""
+    d = orc.make_mla_inputs(B, H, page, L, seed=3, varlen=False)
+    for _ in range(3):
+        out, lse, dbg, st = run(d, 1)
+    t0 = int(st[2, 0, 0])
+    print("timeline B%d H%d L%d (cycles from the first producer stamp)" % (B, H, L))
+    print(" tile | MMA: S-start S-issued PV-start PV-issued | softmax: S-ready pass1 P-free P-written | producer0: K-start K-end V-start V-end")
+    print(" MMA lane of CTA 0 over %d tiles: cycles in full-barrier waits %d, S^T mma issue %d, O^T mma issue %d, commits %d" % (
+        int(st[1, 63, 0]), int(st[0, 63, 0]), int(st[0, 63, 1]), int(st[0, 63, 2]), int(st[0, 63, 3])))
+    for i in range(min(63, L // 128)):
+        r = lambda a: " ".join("%7d" % (int(v) - t0 if int(v) else -1) for v in a)
+        print(" %4d | %s | %s | %s" % (i, r(st[0, i]), r(st[1, i]), r(st[2, i])))
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "--timeline":
+        timeline(296, 16, 2048)
+        timeline(148, 128, 2048)
+    else:
+        main()

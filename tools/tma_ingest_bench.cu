@@ -13,6 +13,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %d\n", cudaGetErrorString(e_), __LINE__); exit(1); } } while (0)
 
@@ -24,6 +25,12 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile("{\n.reg .pred p;\nW_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra D_%=;\nbra W_%=;\nD_%=:\n}\n" ::"r"(bar), "r"(parity) : "memory");
 }
+__device__ __forceinline__ void mbar_spin(uint32_t bar, uint32_t parity) {
+  uint32_t ok = 0;
+  while (!ok)
+    asm volatile("{\n.reg .pred p;\nmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+}
+__device__ long long g_cyc[4];
 __device__ __forceinline__ void tma2(uint32_t dst, const void* m, int c0, int c1, uint32_t bar) {
   asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                ::"r"(dst), "l"(m), "r"(bar), "r"(c0), "r"(c1) : "memory");
@@ -39,7 +46,7 @@ __device__ __forceinline__ void bulk(uint32_t dst, const void* src, uint32_t byt
 struct alignas(64) Map { uint64_t w[16]; };
 
 // rows_per_cta rows of 1152 B per CTA region; the CTA walks its region `passes` times
-template <int MODE>
+template <int MODE, bool SPIN = false, bool TRANSPOSED = false>
 __global__ void __launch_bounds__(128, 1) ingest(const __grid_constant__ Map m2, const __grid_constant__ Map m3,
                                                  const __grid_constant__ Map mdense, const uint8_t* base, int rows_per_cta,
                                                  int passes, int nslots, int slot_bytes) {
@@ -62,28 +69,33 @@ __global__ void __launch_bounds__(128, 1) ingest(const __grid_constant__ Map m2,
   else if (MODE == 3 || MODE == 6) { rows_per_fill = 0; fills_per_group = 1; }
   else { rows_per_fill = 128; fills_per_group = 9; }   // 9 chunks of 64 dims over the same 128 rows
   const long long region_bytes = (long long)rows_per_cta * 1152;
-  long long fills;
-  if (MODE == 3 || MODE == 6) fills = region_bytes / 16384;
+  int fills;
+  if (MODE == 3 || MODE == 6) fills = (int)(region_bytes / 16384);
   else if (MODE == 2) fills = rows_per_cta / 64;
   else if (MODE == 4) fills = rows_per_cta / 14;
-  else fills = (long long)(rows_per_cta / 128) * 9;
+  else fills = (rows_per_cta / 128) * 9;
   (void)rows_per_fill; (void)fills_per_group;
-  long long issued = 0, waited = 0;
-  const long long total = fills * passes;
+  long long issued = 0, waited = 0, t_wait = 0, t_issue = 0;
+  const int total = fills * passes;
   const int my_first = warp, my_step = nissuers;   // mode 5: fill f handled by issuer f % 4, slot = f % nslots
-  for (long long f = my_first; f < total + nslots; f += my_step) {
+  for (int f = my_first; f < total + nslots; f += my_step) {
     // retire the fill that used this slot nslots fills ago
     if (f >= nslots) {
-      const long long g = f - nslots;
-      mbar_wait(smem_u32(&bars[g % nslots]), (uint32_t)((g / nslots) & 1));
+      const int g = f - nslots;
+      const long long c0 = clock64();
+      if (SPIN) mbar_spin(smem_u32(&bars[g % nslots]), (uint32_t)((g / nslots) & 1));
+      else mbar_wait(smem_u32(&bars[g % nslots]), (uint32_t)((g / nslots) & 1));
+      t_wait += clock64() - c0;
       ++waited;
     }
     if (f < total) {
-      const long long ff = f % fills;
+      const int ff = f % fills;
       const int slot = (int)(f % nslots);
       const uint32_t dst = s0 + (uint32_t)slot * slot_bytes, bar = smem_u32(&bars[slot]);
+      const long long c1 = clock64();
       if (MODE == 0 || MODE == 5) {
-        const int grp = (int)(ff / 9), c = (int)(ff % 9);
+        const int ngrp = rows_per_cta / 128;
+        const int grp = TRANSPOSED ? ff % ngrp : ff / 9, c = TRANSPOSED ? ff / ngrp : ff % 9;
         mbar_expect_tx(bar, 16384);
         tma2(dst, &m2, c * 64, row0 + grp * 128, bar);
       } else if (MODE == 1) {
@@ -104,9 +116,17 @@ __global__ void __launch_bounds__(128, 1) ingest(const __grid_constant__ Map m2,
         mbar_expect_tx(bar, 16384);
         tma2(dst, &mdense, 0, (int)(((long long)row0 * 1152 + ff * 16384) / 128), bar);
       }
+      t_issue += clock64() - c1;
       ++issued;
     }
   }
+  if (blockIdx.x == 0 && warp == 0) { g_cyc[0] = t_wait; g_cyc[1] = t_issue; g_cyc[2] = issued; }
+}
+
+__global__ void spin_kernel(long long cycles, long long* out) {
+  const long long t0 = clock64();
+  while (clock64() - t0 < cycles) {}
+  if (threadIdx.x == 0 && blockIdx.x == 0) *out = clock64() - t0;
 }
 
 typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -154,15 +174,28 @@ int main(int argc, char** argv) {
   const Map m3 = make3(), md = makedense();
   cudaEvent_t e0, e1;
   CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  {  // warm the clocks up and measure them: 148 CTAs spinning for 1e9 cycles
+    long long* d; CK(cudaMalloc(&d, 8));
+    for (int k = 0; k < 2; ++k) {
+      CK(cudaEventRecord(e0));
+      spin_kernel<<<sms, 128>>>(1000000000LL, d);
+      CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+      float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+      printf("spin: 1e9 cycles in %.1f ms -> SM clock %.0f MHz\n", ms, 1e6 / ms);
+    }
+  }
   struct Case { int mode; const char* name; int slot_bytes; };
   const Case cases[] = {{0, "2D box 64x128 pitch1152", 16384}, {1, "2x 2D box 64x64 pitch1152", 16384},
                         {2, "3D box 64x64x9 (whole rows)", 73728}, {3, "1D bulk 16 KiB", 16384},
                         {4, "1D bulk 14 rows x 1152 B", 16384}, {5, "2D box 64x128, 4 issuers", 16384},
-                        {6, "2D box 64x128 dense pitch128", 16384}, {7, "2D box 64x128 pitch1152 no L2 promotion", 16384}};
+                        {6, "2D box 64x128 dense pitch128", 16384}, {7, "2D box 64x128 pitch1152 no L2 promotion", 16384}, {8, "2D box 64x128 pitch1152, test_wait spin", 16384},
+                        {9, "1D bulk 16 KiB, test_wait spin", 16384},
+                        {10, "2D box 64x128 pitch1152, chunk-major order, no L2 promotion", 16384},
+                        {11, "2D box 64x128 pitch1152, chunk-major order, 256 B promotion", 16384}};
   for (int hbm = 1; hbm >= 0; --hbm) {
     // HBM: every CTA walks 6272 rows (7.2 MB; 1.07 GB in total) once; L2: 224 rows (258 KB; 38 MB in total) 32 times
     const int rows_per_cta = hbm ? 7040 - 7040 % (128 * 7) : 256;   // L2: 295 KB per CTA, 44 MB in total
-    const int passes = hbm ? 1 : 32;
+    const int passes = hbm ? 4 : 128;
     for (const Case& c : cases) {
       for (int ring_kb : {128, 192}) {
         const int nslots = ring_kb * 1024 / c.slot_bytes;
@@ -183,6 +216,14 @@ int main(int argc, char** argv) {
             case 5: LAUNCH(5, m128); break;
             case 6: LAUNCH(6, m128); break;
             case 7: LAUNCH(0, m128np); break;
+            case 8: CK(cudaFuncSetAttribute(ingest<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+                    ingest<0, true><<<sms, 128, smem>>>(m128, m3, md, buf, rows_per_cta, passes, nslots, c.slot_bytes); break;
+            case 10: CK(cudaFuncSetAttribute(ingest<0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+                    ingest<0, false, true><<<sms, 128, smem>>>(m128np, m3, md, buf, rows_per_cta, passes, nslots, c.slot_bytes); break;
+            case 11: CK(cudaFuncSetAttribute(ingest<0, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+                    ingest<0, false, true><<<sms, 128, smem>>>(m128, m3, md, buf, rows_per_cta, passes, nslots, c.slot_bytes); break;
+            case 9: CK(cudaFuncSetAttribute(ingest<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+                    ingest<3, true><<<sms, 128, smem>>>(m128, m3, md, buf, rows_per_cta, passes, nslots, c.slot_bytes); break;
           }
           CK(cudaEventRecord(e1));
           CK(cudaEventSynchronize(e1));
@@ -197,8 +238,11 @@ int main(int argc, char** argv) {
         else if (c.mode == 3 || c.mode == 6) bytes_per_cta = (long long)rows_per_cta * 1152 / 16384 * 16384;
         else bytes_per_cta = (long long)(rows_per_cta / 128) * 9 * 16384;
         const double tot = (double)bytes_per_cta * passes * sms;
-        printf("%s ring %3d KiB  mode %d %-42s %8.1f us  %7.1f GB/s total  %6.1f GB/s per SM\n", hbm ? "HBM" : "L2 ", ring_kb,
-               c.mode, c.name, best * 1e3, tot / best / 1e6, tot / best / 1e6 / sms);
+        long long cyc[4];
+        CK(cudaMemcpyFromSymbol(cyc, g_cyc, sizeof(cyc)));
+        printf("%s ring %3d KiB  mode %d %-42s %8.1f us  %7.1f GB/s total  %6.1f GB/s per SM   (CTA 0 issuer 0: %lld cyc/wait, %lld cyc/issue; CTA 0 busy %.0f us at 1.9 GHz)\n",
+               hbm ? "HBM" : "L2 ", ring_kb, c.mode, c.name, best * 1e3, tot / best / 1e6, tot / best / 1e6 / sms,
+               cyc[2] ? cyc[0] / cyc[2] : 0, cyc[2] ? cyc[1] / cyc[2] : 0, (cyc[0] + cyc[1]) / 1.9e3);
         fflush(stdout);
       }
     }

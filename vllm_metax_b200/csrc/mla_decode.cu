@@ -179,9 +179,9 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   const int nslots = p.nslots;
 
   if (tid == 0) {
-    for (int i = 0; i < nslots; ++i) {
-      mbar_init(smem_u32(&misc->full[i]), 1);
-      mbar_init(smem_u32(&misc->empty[i]), 1);
+    for (int i = 0; i < (nslots >> 1); ++i) {
+      mbar_init(smem_u32(&misc->full[i]), 2);   // the two producers that fill the pair's halves
+      mbar_init(smem_u32(&misc->empty[i]), 1);  // one tcgen05.commit
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&misc->s_full[i]), 1);
@@ -207,9 +207,19 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   const uint32_t tmem = misc->tmem_base;
   const uint32_t tm_s[2] = {tmem, tmem + NG};
   const uint32_t tm_o = tmem + 2 * NG;
+  // development timeline (tools/mla_debug.py --timeline): clock64 stamps of CTA 0, [role][tile][4], after the logits
+  long long* const stamps = (p.debug_logits != nullptr && blockIdx.x == 0 && blockIdx.y == 0)
+                                ? reinterpret_cast<long long*>(p.debug_logits + 128 * 64) : nullptr;
+  auto stamp = [&](int role, int tile, int k) {
+    if (stamps != nullptr && tile < 64) stamps[(role * 64 + tile) * 4 + k] = clock64();
+  };
 
+  // Ring protocol: the ring is npairs pairs of 16 KiB chunks.  A pair has ONE full barrier (two producer arrivals,
+  // each announcing its chunk's bytes) and ONE empty barrier (one tcgen05.commit), so the MMA lane pays one wait and
+  // one commit per 32 KiB.  Per tile: 5 K pairs (chunks 0..8 + an unused half) for S^T, then 4 V pairs for O^T.
+  const int npairs = nslots >> 1;
   if (warp > kMmaWarp) {
-    // =================== TMA producers: fill f of the ring sequence is issued by producer f % kProducers ===================
+    // =================== TMA producers: half-pair f of the ring sequence is filled by producer f % kProducers ===================
     const int pw = warp - kMmaWarp - 1;
     if (lane == 0) {
       if (pw == 0) {
@@ -218,18 +228,13 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
         for (int c = 0; c < kVChunks; ++c) tma_load_3d(q_u32 + c * NG * 128, &tm_qn, c * 64, h0, seq, smem_u32(&misc->q_full));
         tma_load_3d(q_u32 + kVChunks * NG * 128, &tm_qp, 0, h0, seq, smem_u32(&misc->q_full));
       }
-
       const int32_t* table = p.page_table + (long long)seq * p.page_table_stride;
       const int box_rows = p.box_rows;
       const uint32_t box_bytes = (uint32_t)box_rows * 128u;
-      int slot = 0, turn = 0;
+      int pair = 0, turn = 0;
       uint32_t phase = 0;  // parity of the ring pass
-      auto advance = [&]() {
-        if (++slot == nslots) { slot = 0; phase ^= 1; }
-        if (++turn == kProducers) turn = 0;
-      };
-      // chunks 0 .. n-1 of the tile starting at token tok0 (9 K chunks, or 8 V chunks)
-      auto load_chunks = [&](int tok0, int nchunks) {
+      // halves 0 .. nhalves-1 of the tile starting at token tok0: chunk index = half (the 10th K half is left unused)
+      auto load_halves = [&](int tok0, int nhalves, int nchunks) {
         const int valid = min(kTile, L - tok0);                  // rows of this tile that hold cache entries
         const int vbox = (valid + box_rows - 1) / box_rows;
         int page[8], row[8];
@@ -241,114 +246,133 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
             row[b] = tok & (p.page_size - 1);
           }
         }
-        for (int c = 0; c < nchunks; ++c) {
+        for (int c = 0; c < nhalves; ++c) {
           if (turn == pw) {
-            mbar_wait(smem_u32(&misc->empty[slot]), phase ^ 1);
-            const uint32_t full = smem_u32(&misc->full[slot]);
-            mbar_expect_tx(full, box_bytes * (uint32_t)vbox);
-            const uint32_t dst = ring_u32 + (uint32_t)slot * kChunkBytes;
+            mbar_wait(smem_u32(&misc->empty[pair]), phase ^ 1);
+            const uint32_t full = smem_u32(&misc->full[pair]);
+            if (c < nchunks) {
+              mbar_expect_tx(full, box_bytes * (uint32_t)vbox);
+              const uint32_t dst = ring_u32 + (uint32_t)(2 * pair + (c & 1)) * kChunkBytes;
 #pragma unroll
-            for (int b = 0; b < 8; ++b)
-              if (b < vbox) tma_load_3d(dst + b * box_bytes, &tm_kv, c * 64, row[b], page[b], full);
+              for (int b = 0; b < 8; ++b)
+                if (b < vbox) tma_load_3d(dst + b * box_bytes, &tm_kv, c * 64, row[b], page[b], full);
+            } else {
+              mbar_arrive(full);
+            }
           }
-          advance();
+          if (++turn == kProducers) turn = 0;
+          if (c & 1) {
+            if (++pair == npairs) { pair = 0; phase ^= 1; }
+          }
         }
       };
-      auto k_phase = [&](int i) {
-        load_chunks(t0 + i * kTile, kKChunks);
-        // filler stage: keeps every V pair on an even slot, so a pair never straddles the ring's wrap-around
-        if (turn == pw) {
-          mbar_wait(smem_u32(&misc->empty[slot]), phase ^ 1);
-          mbar_arrive(smem_u32(&misc->full[slot]));
-        }
-        advance();
-      };
-      k_phase(0);
+      if (pw == 0) stamp(2, 0, 0);
+      load_halves(t0, 10, kKChunks);
+      if (pw == 0) stamp(2, 0, 1);
       for (int i = 0; i < T; ++i) {
-        if (i + 1 < T) k_phase(i + 1);
-        load_chunks(t0 + i * kTile, kVChunks);
+        if (i + 1 < T) {
+          if (pw == 0) stamp(2, i + 1, 0);
+          load_halves(t0 + (i + 1) * kTile, 10, kKChunks);
+          if (pw == 0) stamp(2, i + 1, 1);
+        }
+        if (pw == 0) stamp(2, i, 2);
+        load_halves(t0 + i * kTile, 8, kVChunks);
+        if (pw == 0) stamp(2, i, 3);
       }
     }
   } else if (warp == kMmaWarp) {
-    // =================== MMA issuer ===================
-    const int fmt = p.f16 ? 0 : 1;
-    const uint32_t idesc_s = idesc_f16(128, NG, fmt, 0);
-    const uint32_t idesc_o = idesc_f16(128, NG, fmt, 1);
-    int slot = 0;
-    uint32_t phase = 0;
-    auto advance = [&]() {
-      if (++slot == nslots) { slot = 0; phase ^= 1; }
-    };
-    mbar_wait(smem_u32(&misc->q_full), 0);
-    auto issue_s = [&](int i) {
-      const int b = i & 1;
-      if (i >= 2) mbar_wait(smem_u32(&misc->s_free[b]), ((i >> 1) & 1) ^ 1);
-      tc_fence_after();
-      for (int c = 0; c < kKChunks; ++c) {
-        mbar_wait(smem_u32(&misc->full[slot]), phase);
+    // =================== MMA issuer (one lane) ===================
+    if (lane == 0) {
+      const int fmt = p.f16 ? 0 : 1;
+      const uint32_t idesc_s = idesc_f16(128, NG, fmt, 0);
+      const uint32_t idesc_o = idesc_f16(128, NG, fmt, 1);
+      int pair = 0;
+      uint32_t phase = 0;
+      auto advance = [&]() {
+        if (++pair == npairs) { pair = 0; phase ^= 1; }
+      };
+      long long acc[4] = {0, 0, 0, 0}, tmark = 0;   // development: cycles in waits / S issue / PV issue / commits
+      auto tick = [&]() { if (stamps != nullptr) tmark = clock64(); };
+      auto tock = [&](int k) { if (stamps != nullptr) acc[k] += clock64() - tmark; };
+      const uint64_t q_desc = smem_desc_sw128(q_u32, 0, 1024);
+      const uint64_t p_desc = smem_desc_sw128(p_u32, 0, 1024);
+      mbar_wait(smem_u32(&misc->q_full), 0);
+      auto issue_s = [&](int i) {
+        const int b = i & 1;
+        if (i >= 2) mbar_wait(smem_u32(&misc->s_free[b]), ((i >> 1) & 1) ^ 1);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t a_addr = ring_u32 + (uint32_t)slot * kChunkBytes;
-          const uint32_t b_addr = q_u32 + c * NG * 128;
+        stamp(0, i, 0);
+        for (int c2 = 0; c2 < 5; ++c2) {
+          tick();
+          mbar_wait(smem_u32(&misc->full[pair]), phase);
+          tc_fence_after();
+          tock(0);
+          const uint64_t a_desc = smem_desc_sw128(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, 0, 1024);
+          tick();
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            umma_f16(tm_s[b], smem_desc_sw128(a_addr + k * 32, 0, 1024), smem_desc_sw128(b_addr + k * 32, 0, 1024),
-                     idesc_s, (c | k) != 0);
-          umma_commit(smem_u32(&misc->empty[slot]));
-        }
-        __syncwarp();
-        advance();
-      }
-      mbar_wait(smem_u32(&misc->full[slot]), phase);  // filler stage
-      if (lane == 0) {
-        umma_commit(smem_u32(&misc->empty[slot]));
-        umma_commit(smem_u32(&misc->s_full[b]));
-      }
-      __syncwarp();
-      advance();
-    };
-    auto issue_pv = [&](int i) {
-      const int rows = min(kTile, t1 - (t0 + i * kTile));   // valid token rows of this tile
-      const int ksteps = (rows + 15) >> 4;
-      const int zero_from = rows, zero_to = ksteps << 4;     // rows of the last K step that are past the sequence
-      mbar_wait(smem_u32(&misc->p_full), i & 1);
-      tc_fence_after();
-      for (int j = 0; j < 4; ++j) {
-        const int s0 = slot;
-        mbar_wait(smem_u32(&misc->full[s0]), phase);
-        mbar_wait(smem_u32(&misc->full[s0 + 1]), phase);
-        tc_fence_after();
-        const uint32_t a_addr = ring_u32 + (uint32_t)s0 * kChunkBytes;
-        if (zero_from < zero_to) {
-          // V rows past the sequence end may hold anything (0 * NaN = NaN): zero them before the tensor core reads
-          const int n16 = (zero_to - zero_from) * 8;  // 16-byte units per chunk
-          for (int u = lane; u < 2 * n16; u += 32) {
-            uint8_t* dst = ring_ptr + (size_t)(s0 + u / n16) * kChunkBytes + (size_t)zero_from * 128 + (size_t)(u % n16) * 16;
-            *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
+          for (int h = 0; h < 2; ++h) {
+            const int c = 2 * c2 + h;
+            if (c < kKChunks) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma_f16(tm_s[b], a_desc + (uint64_t)((h * kChunkBytes + k * 32) >> 4),
+                         q_desc + (uint64_t)((c * NG * 128 + k * 32) >> 4), idesc_s, (c | k) != 0);
+            }
           }
-          fence_async_smem();
-          __syncwarp();
+          tock(1);
+          tick();
+          umma_commit(smem_u32(&misc->empty[pair]));
+          tock(3);
+          advance();
         }
-        if (lane == 0) {
+        umma_commit(smem_u32(&misc->s_full[b]));
+        stamp(0, i, 1);
+      };
+      auto issue_pv = [&](int i) {
+        const int rows = min(kTile, t1 - (t0 + i * kTile));   // valid token rows of this tile
+        const int ksteps = (rows + 15) >> 4;
+        const int zero_from = rows, zero_to = ksteps << 4;     // rows of the last K step that are past the sequence
+        mbar_wait(smem_u32(&misc->p_full), i & 1);
+        tc_fence_after();
+        stamp(0, i, 2);
+        for (int j = 0; j < 4; ++j) {
+          tick();
+          mbar_wait(smem_u32(&misc->full[pair]), phase);
+          tc_fence_after();
+          tock(0);
+          const uint32_t a_addr = ring_u32 + (uint32_t)pair * 2 * kChunkBytes;
+          if (zero_from < zero_to) {
+            // V rows past the sequence end may hold anything (0 * NaN = NaN): zero them before the tensor core reads
+            for (int hlf = 0; hlf < 2; ++hlf)
+              for (int u = zero_from * 8; u < zero_to * 8; ++u)
+                *reinterpret_cast<uint4*>(ring_ptr + (size_t)(2 * pair + hlf) * kChunkBytes + (size_t)u * 16) = make_uint4(0, 0, 0, 0);
+            fence_async_smem();
+          }
+          const uint64_t a_desc = smem_desc_sw128(a_addr, kChunkBytes, 1024);
+          tick();
           for (int ks = 0; ks < ksteps; ++ks)
-            umma_f16(tm_o + j * NG, smem_desc_sw128(a_addr + ks * 2048, kChunkBytes, 1024),
-                     smem_desc_sw128(p_u32 + (ks >> 2) * NG * 128 + (ks & 3) * 32, 0, 1024), idesc_o, (i | ks) != 0);
-          umma_commit(smem_u32(&misc->empty[s0]));
-          umma_commit(smem_u32(&misc->empty[s0 + 1]));
+            umma_f16(tm_o + j * NG, a_desc + (uint64_t)((ks * 2048) >> 4),
+                     p_desc + (uint64_t)(((ks >> 2) * NG * 128 + (ks & 3) * 32) >> 4), idesc_o, (i | ks) != 0);
+          tock(2);
+          tick();
+          umma_commit(smem_u32(&misc->empty[pair]));
+          tock(3);
+          advance();
         }
-        __syncwarp();
-        advance();
-        advance();
+        umma_commit(smem_u32(&misc->p_free));
+        stamp(0, i, 3);
+      };
+      issue_s(0);
+      for (int i = 0; i < T; ++i) {
+        if (i + 1 < T) issue_s(i + 1);
+        issue_pv(i);
       }
-      if (lane == 0) umma_commit(smem_u32(&misc->p_free));
-      __syncwarp();
-    };
-    issue_s(0);
-    for (int i = 0; i < T; ++i) {
-      if (i + 1 < T) issue_s(i + 1);
-      issue_pv(i);
+      umma_commit(smem_u32(&misc->o_full));
+      if (stamps != nullptr) {
+        for (int k = 0; k < 4; ++k) stamps[(0 * 64 + 63) * 4 + k] = acc[k];
+        stamps[(1 * 64 + 63) * 4 + 0] = T;
+      }
     }
-    if (lane == 0) umma_commit(smem_u32(&misc->o_full));
     __syncwarp();
   } else {
     // =================== softmax / epilogue warps (0..3): thread = one token row = one TMEM lane ===================
@@ -366,6 +390,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
       mbar_wait(smem_u32(&misc->s_full[b]), (i >> 1) & 1);
       tc_fence_after();
       const bool valid = t0 + i * kTile + row < t1;
+      if (tid == 0) stamp(1, i, 0);
       // ---- pass 1: does any logit pass its reference by kTau?  (S^T is read again in pass 2: TMEM reads are cheap) ----
       bool over = false;
 #pragma unroll
@@ -425,6 +450,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           tc_fence_before();
         }
       }
+      if (tid == 0) stamp(1, i, 1);
       // ---- pass 2: p = 2^(x - m_ref); 16-bit values into the P^T operand, fp32 into the running sums ----
       // P^T[h][token]: K-major SW128, chunk = row / 64, 16-byte unit (row % 64) / 8 XOR (h % 8)
       const uint32_t chunk = p_u32 + (row >> 6) * NG * 128;
@@ -446,6 +472,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           r[h] = p.f16 ? (uint32_t)__half_as_ushort(__float2half_rn(pv)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(pv));
         }
         if (c0 == 0 && i > 0) mbar_wait(smem_u32(&misc->p_free), (i - 1) & 1);
+        if (c0 == 0 && tid == 0) stamp(1, i, 2);
 #pragma unroll
         for (int h = 0; h < HC; ++h) {
           const uint32_t addr = chunk + (c0 + h) * 128 + ((unit ^ (h & 7)) << 4) + within;
@@ -454,6 +481,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
       }
       fence_async_smem();
       mbar_arrive(smem_u32(&misc->p_full));
+      if (tid == 0) stamp(1, i, 3);
     }
 
     // ---- epilogue: reduce the per-thread row sums over the 128 token rows, normalise O^T, store ----
