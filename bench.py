@@ -297,6 +297,62 @@ def extra_config(ops, name, dev, steps, warmup, pk, n_parity, kv_heads=None, see
     return entry, ms
 
 
+MLA_SHAPES = [  # (name, batch, ctx, heads): DeepSeek-style MLA decode, latent 512 + rope 64, page 64, bf16
+    ("mla_h128", 128, 8192, 128), ("mla_h16_tp8", 128, 8192, 16),
+]
+
+
+def mla_config(ops, name, b, L, H, dev, steps, warmup, pk, n_parity):
+    """MLA decode attention: the reference op cutlass_mla_decode / sm100_cutlass_mla_decode on the
+    test's shapes (tests/kernels/attention/test_cutlass_mla_decode.py:41-52).  bound: the op sits on the tensor/HBM
+    ridge at 128 heads (242 flop/B), so both fractions are reported: HBM (bytes = sum L*1152 + q + out) and tensor
+    (flops = 2*L*H*(576+512) per sequence) against MEASURED_PEAKS.json."""
+    from oracle import torch_oracle as orc
+    page = 64
+    g = torch.Generator(device=dev).manual_seed(b + L + H)
+    pages = L // page
+    cache = torch.randn(b * pages, page, 576, generator=g, device=dev, dtype=torch.bfloat16)
+    q = torch.randn(b, H, 576, generator=g, device=dev, dtype=torch.bfloat16)
+    table = torch.randperm(b * pages, generator=g, device=dev).to(torch.int32).view(b, pages)
+    lens = torch.full((b,), L, dtype=torch.int32, device=dev)
+    qn, qp = q[..., :512].contiguous(), q[..., 512:].contiguous()
+    out = torch.empty(b, H, 512, dtype=q.dtype, device=dev)
+    lse = torch.empty(b, H, dtype=torch.float32, device=dev)
+    ws = torch.empty(max(16, ops.sm100_cutlass_mla_get_workspace_size(L, b, 148, -1)), dtype=torch.uint8, device=dev)
+    scale = 1.0 / math.sqrt(576)
+
+    def run():
+        ops.sm100_cutlass_mla_decode(out, lse, qn, qp, cache, lens, table, ws, scale, -1)
+
+    for _ in range(max(warmup, 3)):
+        run()
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2 * steps)]
+    for i in range(steps):
+        ev[2 * i].record()
+        run()
+        ev[2 * i + 1].record()
+    torch.cuda.synchronize()
+    ms = sum(ev[2 * i].elapsed_time(ev[2 * i + 1]) for i in range(steps)) / steps
+    byt = b * L * 1152 + b * H * (576 + 512) * 2
+    flops = 2.0 * b * L * H * (576 + 512)
+    e = {"name": name, "op": "sm100_cutlass_mla_decode", "batch": b, "ctx": L, "heads": H, "page": page,
+         "attention_us": ms * 1e3, "gbs": byt / ms / 1e6, "frac_hbm": byt / ms / 1e6 / pk["hbm_gbs"],
+         "tflops": flops / ms / 1e9, "frac_tensor": flops / ms / 1e9 / pk.get("bf16_tflops", 1674.0),
+         "algorithmic_bytes": byt, "l2": "working set larger than L2"}
+    if n_parity > 0:
+        picks = sorted(set(int(round(i * (b - 1) / max(n_parity - 1, 1))) for i in range(n_parity)))
+        worst = 0.0
+        for s_ in picks:
+            ref, _ = orc.mla_decode(q[s_:s_ + 1].cpu(), cache[table[s_].long()].cpu(), scale,
+                                    torch.arange(pages, dtype=torch.int32).view(1, -1), lens[s_:s_ + 1].cpu())
+            worst = max(worst, (out[s_:s_ + 1].float().cpu() - ref).abs().max().item())
+        e["max_abs"], e["parity_seqs"], e["parity_ok"] = worst, len(picks), bool(worst <= PARITY_TOL)
+    del cache, q, table, out, ws
+    torch.cuda.empty_cache()
+    return e
+
+
 def run_ours(args):
     from vllm_metax_b200 import _custom_ops as ops  # loads the native libraries; raises if they are missing
     from vllm_metax_b200 import _native
@@ -443,6 +499,14 @@ def run_ours(args):
                 torch.cuda.empty_cache()
             cfgs.append(e)
         extra["configs"] = cfgs
+        mla = []
+        for name, b, L, H in MLA_SHAPES:
+            try:
+                mla.append(mla_config(ops, name, b, L, H, dev, min(args.steps, 20), args.warmup, pk, 0 if args.no_parity else 2))
+            except Exception as ex:
+                mla.append({"name": name, "error": "%s: %s" % (type(ex).__name__, ex)})
+                torch.cuda.empty_cache()
+        extra["mla"] = mla
 
     # ---- tensor parallel: BASELINE.json configs[3], KV-head shards over the ranks (N > 1) --------------------------
     tp = None

@@ -152,6 +152,68 @@ def _rank_main(rank: int, world: int, port: int, fused: bool, ret):
         dist.destroy_process_group()
 
 
+def _soak_main(rank: int, world: int, port: int, steps: int, ret):
+    """The fused peer-memory step under skew: every rank delays a random amount (up to ~200 us of torch.cuda._sleep)
+    before each step, alternately before the gather and before the fold; queries cycle through 4 seeds and every
+    step's output is compared bit for bit with the first time that query was run."""
+    import random as _random
+
+    from vllm_metax_b200.attention.dcp import DcpExchange
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        H = 4 * world
+        d = make_problem(S=6, H=H, Hkv=2, D=128, L=1000)
+        Hl = H // world
+        lk, lv, table, local_lens = shard_for_rank(d, world, rank)
+        lk, lv, table, lens_dev = lk.to(dev), lv.to(dev), table.to(dev), local_lens.to(dev)
+        max_local = int(local_lens.max())
+        xch = DcpExchange(8, H, 128, torch.bfloat16)
+        rnd = _random.Random(1000 + rank)
+        queries = [torch.randn(d["query"].shape, generator=torch.Generator().manual_seed(k)).bfloat16()[:, rank * Hl:(rank + 1) * Hl]
+                   .contiguous().to(dev) for k in range(4)]
+        first = {}
+        mismatches = 0
+        for step in range(steps):
+            k = step % 4
+            torch.cuda._sleep(rnd.randint(0, 400000))
+            out, lse = xch.forward_decode(queries[k], lk, lv, table, lens_dev, max_local, d["scale"])
+            if step % 50 == 49 or step < 8:
+                torch.cuda.synchronize()
+            if k not in first:
+                first[k] = (out.clone(), lse.clone())
+            elif not (torch.equal(out, first[k][0]) and torch.equal(lse, first[k][1])):
+                mismatches += 1
+        torch.cuda.synchronize()
+        xch.close()
+        ret[rank] = mismatches
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_dcp_soak_skewed_ranks(world):
+    """B200_DCP_SOAK_STEPS steps (default 200; the round-2 evidence run used 2000)."""
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    steps = int(os.environ.get("B200_DCP_SOAK_STEPS", "200"))
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        ret = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_soak_main, args=(r, world, port, steps, ret)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(600)
+            assert p.exitcode == 0
+        assert all(ret[r] == 0 for r in range(world)), dict(ret)
+
+
 @pytest.mark.parametrize("fused", [False, True], ids=["nccl_all_to_all", "peer_memory_fold"])
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_dcp_nccl(world, fused):

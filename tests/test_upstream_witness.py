@@ -222,3 +222,35 @@ def test_kernel_attention_matches_upstream(ops, name):
     out2 = torch.empty_like(q)
     ops.paged_attention_v2(out2, es, ml, tmp, q, kc, vc, c["Hkv"], c["scale"], bt, lens, c["B"], L, None, c["kv"], ks, vs)
     assert (out2.cpu().float() - rec[name]["v2"].float()).abs().max().item() <= 2e-3
+
+
+# ---- MLA decode: outputs of the stock sm_100a CUTLASS kernel (the reference's csrc/attention/mla/cutlass_mla_kernels.cu
+# as built in upstream vLLM 0.22.0), recorded on a B200 by tools/mla_bench.py --impl upstream --witness ----
+MLA_WITNESS = os.path.join(GOLDEN, "mla_upstream_bf16_h128.pt")
+
+
+@pytest.mark.skipif(not os.path.exists(MLA_WITNESS), reason="MLA witness fixture not recorded")
+def test_mla_oracle_matches_stock_kernel_outputs():
+    d = torch.load(MLA_WITNESS)
+    out, lse = orc.mla_decode(d["query"], d["kv_cache"], d["scale"], d["block_tables"], d["seq_lens"])
+    # the stock kernel rounds its output to bf16 (values O(0.1..1)): one bf16 ulp
+    torch.testing.assert_close(out, d["upstream_out"].float(), atol=4e-3, rtol=1.6e-2)
+    torch.testing.assert_close(lse, d["upstream_lse"], atol=1e-4, rtol=1e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not os.path.exists(MLA_WITNESS), reason="MLA witness fixture not recorded")
+def test_mla_kernel_matches_stock_kernel_outputs():
+    import vllm_metax_b200
+    vllm_metax_b200.import_kernels()
+    from vllm_metax_b200 import _custom_ops as ops
+    d = torch.load(MLA_WITNESS)
+    dev = "cuda:0"
+    q = d["query"].to(dev)
+    out = torch.empty(q.shape[0], q.shape[1], 512, dtype=q.dtype, device=dev)
+    lse = torch.empty(q.shape[0], q.shape[1], dtype=torch.float32, device=dev)
+    ws = torch.empty(16, dtype=torch.uint8, device=dev)
+    ops.sm100_cutlass_mla_decode(out, lse, q[..., :512].contiguous(), q[..., 512:].contiguous(), d["kv_cache"].to(dev),
+                                 d["seq_lens"].to(dev), d["block_tables"].to(dev), ws, d["scale"], 1)
+    torch.testing.assert_close(out.float().cpu(), d["upstream_out"].float(), atol=4e-3, rtol=1.6e-2)
+    torch.testing.assert_close(lse.cpu(), d["upstream_lse"], atol=1e-4, rtol=1e-5)

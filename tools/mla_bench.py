@@ -60,6 +60,7 @@ def main():
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--splits", type=int, default=-1)
     ap.add_argument("--only", type=int, default=-1)
+    ap.add_argument("--witness", help="(--impl upstream) run the stock kernel on small CPU-seeded inputs and save inputs + outputs")
     args = ap.parse_args()
     if args.compare:
         a, b = torch.load(args.compare[0]), torch.load(args.compare[1])
@@ -82,6 +83,27 @@ def main():
             return
     op = torch.ops._C.sm100_cutlass_mla_decode
     ws_size = torch.ops._C.sm100_cutlass_mla_get_workspace_size
+    if args.witness:
+        # small fixture for tests/golden: CPU-seeded inputs (no project code), stock kernel outputs
+        g = torch.Generator().manual_seed(2026)
+        b, H, page, pages = 3, 128, 64, 6
+        lens = torch.tensor([384, 201, 77], dtype=torch.int32)
+        nb = b * pages + 2
+        cache = torch.randn(nb, page, 576, generator=g).to(torch.bfloat16)
+        q = torch.randn(b, H, 576, generator=g).to(torch.bfloat16)
+        table = torch.randperm(nb, generator=g)[:b * pages].to(torch.int32).view(b, pages)
+        out = torch.empty(b, H, 512, dtype=torch.bfloat16, device=dev)
+        lse = torch.empty(b, H, dtype=torch.float32, device=dev)
+        ws = torch.empty(max(16, ws_size(pages * page, b, 148, 1)), dtype=torch.uint8, device=dev)
+        scale = 1.0 / math.sqrt(576)
+        op(out, lse, q[..., :512].contiguous().to(dev), q[..., 512:].contiguous().to(dev), cache.to(dev), lens.to(dev),
+           table.to(dev), ws, scale, 1)
+        torch.cuda.synchronize()
+        torch.save(dict(query=q, kv_cache=cache, block_tables=table, seq_lens=lens, scale=scale, upstream_out=out.cpu(),
+                        upstream_lse=lse.cpu(), producer="vLLM 0.22.0 torch.ops._C.sm100_cutlass_mla_decode on B200"),
+                   args.witness)
+        print("witness written:", args.witness)
+        return
     samples = {}
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     for idx, (b, L, H) in enumerate(SHAPES):

@@ -85,7 +85,10 @@ def timeline(B, H, L, page=64):
 
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "--timeline":
-        timeline(296, 16, 2048)
-        timeline(148, 128, 2048)
+        if len(sys.argv) > 4:
+            timeline(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]))
+        else:
+            timeline(296, 16, 2048)
+            timeline(148, 128, 2048)
     else:
         main()

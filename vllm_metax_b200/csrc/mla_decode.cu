@@ -34,7 +34,7 @@ constexpr int kMlaThreads = (4 + 1 + kProducers) * 32;  // warps 0-3 softmax, 4 
 constexpr int kSoftmaxThreads = 128;
 constexpr int kMaxSlots = 16;
 constexpr float kTau = 16.f;          // re-reference when a logit passes m_ref by 2^16
-constexpr int kMaxSplits = 32;
+constexpr int kMaxSplits = 256;
 constexpr int kMinSplitTiles = 4;
 
 struct MlaParams {
@@ -140,7 +140,7 @@ __host__ __device__ constexpr size_t mla_smem_bytes(int NG, int nslots) {
 }
 
 template <int NG>
-__global__ void __launch_bounds__(kMlaThreads, 1)
+__global__ void __launch_bounds__(kMlaThreads, NG <= 32 ? 2 : 1)
 mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, const __grid_constant__ TmaDesc tm_qn,
                   const __grid_constant__ TmaDesc tm_qp) {
   // ---- which item ----
@@ -621,13 +621,15 @@ int mla_choose_splits(int S, int H, long long max_seq_len, int requested) {
   if (requested > 1) return (int)min((long long)min(requested, kMaxSplits), max(1LL, tiles));
   const int NG = mla_group_width(H);
   const long long base = (long long)S * ((H + NG - 1) / NG);
-  const int sms = device_sm_count();
+  const int sms = device_sm_count() * ((NG <= 32 && env_int("B200_MLA_OCC2") != 0) ? 2 : 1);  // resident CTAs
   int best = 1;
   double best_cost = 1e30;
   for (int s = 1; s <= cap; ++s) {
     const long long per = (tiles + s - 1) / s;                       // tiles per split
     const long long waves = (base * s + sms - 1) / sms;
-    const double cost = (double)waves * ((double)per + 1.5) + (s > 1 ? 0.5 : 0.0);  // 1.5 tiles of fixed cost per CTA
+    // measured on B200 (profiles/r2_mla_*): a CTA costs ~4 tile-times beyond its tiles (query load, pipeline fill,
+    // epilogue), and every extra split adds fp32 partials for the merge kernel to re-read
+    const double cost = (double)waves * ((double)per + 4.0) + (s > 1 ? 1.0 + 0.25 * s : 0.0);
     if (cost < best_cost - 1e-9) best_cost = cost, best = s;
   }
   return best;
@@ -705,7 +707,11 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   const long long tiles = (max_len + kTile - 1) / kTile;
   mp.split_tokens = (int)((tiles + splits - 1) / splits) * kTile;
   mp.f16 = f16 ? 1 : 0;
-  int nslots = (int)((232448 - 1024 - (size_t)NG * 128 * (kKChunks + 2) - sizeof(MlaMisc)) / kChunkBytes);
+  // shared memory: one CTA per SM for 64-head groups; two for the narrow groups (their MMA lanes then hide each
+  // other's barrier waits and commits), each with half of the SM's 228 KiB minus the per-block reservation
+  static const bool occ2 = env_int("B200_MLA_OCC2") != 0;
+  const size_t budget = (NG <= 32 && occ2) ? (233472 / 2 - 1024) : 232448;
+  int nslots = (int)((budget - 1024 - (size_t)NG * 128 * (kKChunks + 2) - sizeof(MlaMisc)) / kChunkBytes);
   nslots = min(nslots & ~1, kMaxSlots);
   mp.nslots = nslots;
   if (splits > 1) {
