@@ -539,6 +539,505 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   }
 }
 
+// =====================================================================================================================
+// Pair kernel (65..128 heads): a cluster of two CTAs drives the tensor cores of both SMs with cta_group::2 instructions.
+//   S^T: M = 256 = the 128-token tiles of BOTH CTAs (CTA r owns tile 2u + r of super-tile u), N = 128 heads; the B operand
+//        Q^T is split by the hardware across the pair (CTA r keeps heads 64r..64r+63: 72 KiB each instead of 144).
+//   O^T: M = 256 = two 128-row dv slices (CTA r accumulates dv rows 256j + 128r .. +127, j = 0, 1), N = 128 heads,
+//        K = the tokens of tile X_t (t = 0, 1 in turn); B operand P^T[X_t] split by heads across the pair, so the
+//        softmax threads of CTA t write the probabilities of heads 64..127 / 0..63 into the PEER's shared memory.
+// One instruction therefore covers what four instructions of the single-CTA kernel do (two token tiles x two head
+// groups): 68 tcgen05.mma per 256 tokens x 128 heads instead of 272, and each CTA streams 17 chunks per TWO tiles
+// (9 K chunks of its own tile + its 4-chunk dv slice of V for both tiles).  TMEM per CTA: 2 x 128 (S^T) + 2 x 128 (O^T).
+// The softmax reference m_ref[h] must be the same in both CTAs (their probabilities add up in one accumulator): every
+// super-tile the CTAs exchange an "a logit passed the reference" flag (and, if set, their column maxima) through
+// distributed shared memory and take the same decision.
+constexpr int kPairSoftmaxWarps = 8;   // thread = (token row, head half): warps w and w + 4 share a TMEM lane quadrant
+constexpr int kPairMmaWarp = 8;
+constexpr int kPairThreads = (kPairSoftmaxWarps + 1 + kProducers) * 32;
+constexpr int kPairSoftmaxThreads = kPairSoftmaxWarps * 32;
+
+struct PairPost {           // what one CTA tells the pair about a super-tile
+  int flag;                 // some logit of its tile passed m_ref + kTau
+  int pad[3];
+  int colmax[128];          // per-head maximum of its tile (sortable-int encoding), valid when flag != 0
+};
+struct PairMisc {
+  uint64_t full[kMaxSlots / 2], empty[kMaxSlots / 2];
+  uint64_t s_full[2], s_free[2], p_full, p_free, o_full, q_full;
+  uint64_t post_bar[2];     // both CTAs' posts of a super-tile have landed (parity by super-tile)
+  uint32_t tmem_base;
+  uint32_t pad[3];
+  float mref[128];
+  float fac[128];
+  float lpart[2][128];      // row sums of each CTA's tokens, exchanged at the end
+  int colmax_w[kPairSoftmaxWarps][64];
+  PairPost post[2][2];      // [super-tile parity][source CTA]
+};
+__host__ __device__ constexpr size_t pair_smem_bytes(int nslots) {
+  return 1024 + (size_t)64 * 128 * kKChunks + 2 * 16384 + (size_t)nslots * kChunkBytes + sizeof(PairMisc);
+}
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank) {   // same offset in CTA `rank` of the cluster
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {   // release at cluster scope, possibly remote
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t cluster_addr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_addr), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {   // acquire at cluster scope
+  asm volatile(
+      "{\n.reg .pred p;\nW_%=:\nmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n@p bra D_%=;\nbra W_%=;\nD_%=:\n}\n" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void st_cluster_u16(uint32_t cluster_addr, uint16_t v) {
+  asm volatile("st.shared::cluster.u16 [%0], %1;" ::"r"(cluster_addr), "h"(v) : "memory");
+}
+__device__ __forceinline__ void st_cluster_u32(uint32_t cluster_addr, uint32_t v) {
+  asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(cluster_addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void umma_f16_2sm(uint32_t d_tmem, uint64_t a, uint64_t b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(d_tmem),
+      "l"(a), "l"(b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrives (once all MMAs issued so far are complete) on the barrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
+}
+// tiled load whose completion bytes are counted on the LEADER CTA's barrier
+__device__ __forceinline__ void tma_load_3d_2sm(uint32_t dst, const void* tmap, int c0, int c1, int c2, uint32_t leader_bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(tmap), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
+mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, const __grid_constant__ TmaDesc tm_qn,
+                       const __grid_constant__ TmaDesc tm_qp) {
+  const int seq = blockIdx.y;
+  const int split = blockIdx.x >> 1;
+  const uint32_t rank = cluster_ctarank();       // 0 = leader (issues the MMAs), 1 = peer
+  const int L = p.seq_lens[seq];
+  const int t0 = split * p.split_tokens;
+  const int t1 = min(L, t0 + p.split_tokens);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nsplit = L > 0 ? (L + p.split_tokens - 1) / p.split_tokens : 1;
+  if (L <= 0) {  // empty sequence (both CTAs take this branch): zeros and lse = -inf
+    if (split == 0) {
+      for (int i = tid + rank * kPairThreads; i < p.H * 512; i += 2 * kPairThreads) {
+        const long long o = (long long)seq * p.out_seq_stride + (long long)(i / 512) * p.out_head_stride + i % 512;
+        if (p.f16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(0.f);
+        else reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(0.f);
+      }
+      if (p.lse != nullptr && rank == 0 && tid < p.H) p.lse[(long long)seq * p.lse_stride + tid] = -INFINITY;
+    }
+    return;
+  }
+  if (t0 >= t1) return;
+  const int T = (t1 - t0 + kTile - 1) / kTile;   // token tiles of this split
+  const int U = (T + 1) >> 1;                    // super-tiles: CTA r owns tile 2u + r (which may not exist for r = 1)
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* const base_ptr = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t q_u32 = base;                              // 9 chunks [64 heads x 128 B]: heads 64r .. 64r+63
+  const uint32_t p_u32 = q_u32 + kKChunks * 64 * 128;       // P^T[X_0], P^T[X_1]: 2 x (2 chunks [64 heads x 128 B])
+  const uint32_t ring_u32 = p_u32 + 2 * 16384;
+  uint8_t* const ring_ptr = base_ptr + (ring_u32 - base);
+  PairMisc* const misc = reinterpret_cast<PairMisc*>(ring_ptr + (size_t)p.nslots * kChunkBytes);
+  const int npairs = p.nslots >> 1;
+
+  if (tid == 0) {
+    for (int i = 0; i < npairs; ++i) {
+      mbar_init(smem_u32(&misc->full[i]), 2 * 2);   // leader's copy is the one used: two producers in each CTA
+      mbar_init(smem_u32(&misc->empty[i]), 1);      // one multicast tcgen05.commit
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&misc->s_full[i]), 1);
+      mbar_init(smem_u32(&misc->s_free[i]), 2 * kPairSoftmaxWarps);   // leader's copy: one arrival per softmax warp of the pair
+      mbar_init(smem_u32(&misc->post_bar[i]), 2);                     // one post from each CTA
+    }
+    mbar_init(smem_u32(&misc->p_full), 2 * kPairSoftmaxWarps);        // leader's copy
+    mbar_init(smem_u32(&misc->p_free), 1);
+    mbar_init(smem_u32(&misc->o_full), 1);
+    mbar_init(smem_u32(&misc->q_full), 2);                            // leader's copy: both CTAs' query loads
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (tid < 128) misc->mref[tid] = -INFINITY;
+  if (warp == kPairMmaWarp) {   // the same warp in both CTAs, the same destination address
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&misc->tmem_base)),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem = misc->tmem_base;
+  const uint32_t tm_s[2] = {tmem, tmem + 128};
+  const uint32_t tm_o = tmem + 256;              // O^T blocks j = 0, 1: 128 columns each
+  long long* const stamps = (p.debug_logits != nullptr && blockIdx.x == 0 && blockIdx.y == 0)
+                                ? reinterpret_cast<long long*>(p.debug_logits + 128 * 64) : nullptr;
+  auto stamp = [&](int role, int tile, int k) {
+    if (stamps != nullptr && tile < 64) stamps[(role * 64 + tile) * 4 + k] = clock64();
+  };
+  // leader-CTA addresses of the barriers that gather arrivals from both CTAs
+  const uint32_t lead_q_full = mapa_u32(smem_u32(&misc->q_full), 0);
+  const uint32_t lead_p_full = mapa_u32(smem_u32(&misc->p_full), 0);
+
+  if (warp > kPairMmaWarp) {
+    // =================== TMA producers (both CTAs): half-pair f of the ring sequence by producer f % kProducers ===================
+    const int pw = warp - kPairMmaWarp - 1;
+    if (lane == 0) {
+      if (pw == 0) {
+        // this CTA's 64 query heads; bytes are counted on the leader's barrier
+        mbar_expect_tx_cluster(lead_q_full, (uint32_t)(kKChunks * 64 * 128));
+        for (int c = 0; c < kVChunks; ++c) tma_load_3d_2sm(q_u32 + c * 64 * 128, &tm_qn, c * 64, 64 * (int)rank, seq, lead_q_full);
+        tma_load_3d_2sm(q_u32 + kVChunks * 64 * 128, &tm_qp, 0, 64 * (int)rank, seq, lead_q_full);
+      }
+      const int32_t* table = p.page_table + (long long)seq * p.page_table_stride;
+      const int box_rows = p.box_rows;
+      const uint32_t box_bytes = (uint32_t)box_rows * 128u;
+      int pair = 0, turn = 0;
+      uint32_t phase = 0;
+      // `nhalves` ring halves holding chunks chunk0, chunk0 + 1, ... (at most nchunks of them) of token tile `tile`
+      auto load_halves = [&](int tile, int chunk0, int nhalves, int nchunks) {
+        const int tok0 = t0 + tile * kTile;
+        const int valid = max(0, min(kTile, L - tok0));          // rows of this tile that hold cache entries
+        const int vbox = (valid + box_rows - 1) / box_rows;
+        int page[8], row[8];
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+          if (b < vbox) {
+            const int tok = tok0 + b * box_rows;
+            page[b] = table[tok >> p.page_shift];
+            row[b] = tok & (p.page_size - 1);
+          }
+        }
+        for (int c = 0; c < nhalves; ++c) {
+          if (turn == pw) {
+            mbar_wait(smem_u32(&misc->empty[pair]), phase ^ 1);
+            const uint32_t full = mapa_u32(smem_u32(&misc->full[pair]), 0);
+            if (c < nchunks) {
+              mbar_expect_tx_cluster(full, box_bytes * (uint32_t)vbox);
+              const uint32_t dst = ring_u32 + (uint32_t)(2 * pair + (c & 1)) * kChunkBytes;
+#pragma unroll
+              for (int b = 0; b < 8; ++b)
+                if (b < vbox) tma_load_3d_2sm(dst + b * box_bytes, &tm_kv, (chunk0 + c) * 64, row[b], page[b], full);
+            } else {
+              mbar_arrive_cluster(full);
+            }
+          }
+          if (++turn == kProducers) turn = 0;
+          if (c & 1) {
+            if (++pair == npairs) { pair = 0; phase ^= 1; }
+          }
+        }
+      };
+      // S^T of super-tile u: the 9 K chunks (+ an unused half) of this CTA's own tile 2u + rank
+      // O^T of super-tile u: for t = 0, 1 and j = 0, 1 the chunk pair (4j + 2 rank, +1) of tile 2u + t (this CTA's dv slice)
+      load_halves((int)rank, 0, 10, kKChunks);
+      for (int u = 0; u < U; ++u) {
+        if (u + 1 < U) load_halves(2 * (u + 1) + (int)rank, 0, 10, kKChunks);
+        for (int t = 0; t < 2; ++t)
+          for (int j = 0; j < 2; ++j) load_halves(2 * u + t, 4 * j + 2 * (int)rank, 2, 2);
+      }
+    }
+  } else if (warp == kPairMmaWarp) {
+    // =================== MMA issuer: one lane of the leader CTA drives both tensor cores ===================
+    if (rank == 0 && lane == 0) {
+      const int fmt = p.f16 ? 0 : 1;
+      const uint32_t idesc_s = idesc_f16(256, 128, fmt, 0);
+      const uint32_t idesc_o = idesc_f16(256, 128, fmt, 1);
+      int pair = 0;
+      uint32_t phase = 0;
+      auto advance = [&]() {
+        if (++pair == npairs) { pair = 0; phase ^= 1; }
+      };
+      const uint64_t q_desc = smem_desc_sw128(q_u32, 0, 1024);
+      mbar_wait_cluster(smem_u32(&misc->q_full), 0);
+      auto issue_s = [&](int u) {
+        const int b = u & 1;
+        if (u >= 2) mbar_wait_cluster(smem_u32(&misc->s_free[b]), ((u >> 1) & 1) ^ 1);
+        tc_fence_after();
+        stamp(0, u, 0);
+        for (int c2 = 0; c2 < 5; ++c2) {
+          mbar_wait_cluster(smem_u32(&misc->full[pair]), phase);
+          tc_fence_after();
+          const uint64_t a_desc = smem_desc_sw128(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, 0, 1024);
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int c = 2 * c2 + h;
+            if (c < kKChunks) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                umma_f16_2sm(tm_s[b], a_desc + (uint64_t)((h * kChunkBytes + k * 32) >> 4),
+                             q_desc + (uint64_t)((c * 64 * 128 + k * 32) >> 4), idesc_s, (c | k) != 0);
+            }
+          }
+          umma_commit_2sm(smem_u32(&misc->empty[pair]));
+          advance();
+        }
+        umma_commit_2sm(smem_u32(&misc->s_full[b]));
+        stamp(0, u, 1);
+      };
+      auto issue_pv = [&](int u) {
+        mbar_wait_cluster(smem_u32(&misc->p_full), u & 1);
+        tc_fence_after();
+        stamp(0, u, 2);
+        for (int t = 0; t < 2; ++t) {
+          const int rows = max(0, min(kTile, t1 - (t0 + (2 * u + t) * kTile)));   // valid token rows of tile X_t
+          const int ksteps = (rows + 15) >> 4;
+          const uint64_t p_desc = smem_desc_sw128(p_u32 + t * 16384, 0, 1024);
+          for (int j = 0; j < 2; ++j) {
+            mbar_wait_cluster(smem_u32(&misc->full[pair]), phase);
+            tc_fence_after();
+            if (rows < (ksteps << 4)) {
+              // V rows past the sequence end may hold anything (0 * NaN = NaN): zero them in BOTH CTAs' stages
+              for (uint32_t r2 = 0; r2 < 2; ++r2)
+                for (int hlf = 0; hlf < 2; ++hlf) {
+                  const uint32_t stage = mapa_u32(ring_u32 + (uint32_t)(2 * pair + hlf) * kChunkBytes, r2);
+                  for (int un = rows * 8; un < (ksteps << 4) * 8; ++un)
+                    asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(stage + un * 16), "r"(0u) : "memory");
+                }
+              asm volatile("fence.acq_rel.cluster;" ::: "memory");
+              asm volatile("fence.proxy.async;" ::: "memory");
+            }
+            const uint64_t a_desc = smem_desc_sw128(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, kChunkBytes, 1024);
+            for (int ks = 0; ks < ksteps; ++ks)
+              umma_f16_2sm(tm_o + j * 128, a_desc + (uint64_t)((ks * 2048) >> 4),
+                           p_desc + (uint64_t)(((ks >> 2) * 64 * 128 + (ks & 3) * 32) >> 4), idesc_o, (u | t | ks) != 0);
+            umma_commit_2sm(smem_u32(&misc->empty[pair]));
+            advance();
+          }
+        }
+        umma_commit_2sm(smem_u32(&misc->p_free));
+        stamp(0, u, 3);
+      };
+      issue_s(0);
+      for (int u = 0; u < U; ++u) {
+        if (u + 1 < U) issue_s(u + 1);
+        issue_pv(u);
+      }
+      umma_commit_2sm(smem_u32(&misc->o_full));
+    }
+    __syncwarp();
+  } else {
+    // =================== softmax / epilogue warps 0..7: thread = (token row of this CTA's tile, head half) ===================
+    const int quad = warp & 3, hh = warp >> 2;
+    const int row = quad * 32 + lane;
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const int cbase = 64 * hh;                   // first S^T column (head) of this thread
+    auto sm_bar = [&]() { asm volatile("bar.sync 1, 256;" ::: "memory"); };
+    float lsum[64];
+#pragma unroll
+    for (int h = 0; h < 64; ++h) lsum[h] = 0.f;
+    // P^T[X_rank] lives in CTA hh (the CTA that supplies heads 64hh.. as its half of the B operand)
+    const uint32_t p_dst = mapa_u32(p_u32 + rank * 16384 + (row >> 6) * 64 * 128, (uint32_t)hh);
+    const uint32_t unit = (row & 63) >> 3, within = (row & 7) * 2;
+    const uint32_t peer = rank ^ 1;
+
+    for (int u = 0; u < U; ++u) {
+      const int b = u & 1;
+      mbar_wait(smem_u32(&misc->s_full[b]), (u >> 1) & 1);
+      tc_fence_after();
+      const bool valid = t0 + (2 * u + (int)rank) * kTile + row < t1;
+      if (tid == 0) stamp(1, u, 0);
+      bool over = false;
+#pragma unroll
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld<32>(tm_s[b] + cbase + c0 + lane_base, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int h = 0; h < 32; ++h)
+          over |= valid && __uint_as_float(r[h]) * p.scale_log2 > misc->mref[cbase + c0 + h] + kTau;
+      }
+      uint32_t over_cta;
+      asm volatile("{\n.reg .pred p, q;\nsetp.ne.b32 q, %1, 0;\nbar.red.or.pred p, 1, 256, q;\nselp.u32 %0, 1, 0, p;\n}\n"
+                   : "=r"(over_cta) : "r"((uint32_t)over) : "memory");
+      PairPost* const mine = &misc->post[b][rank];
+      if (over_cta) {   // this CTA's column maxima, posted to both CTAs
+#pragma unroll
+        for (int c0 = 0; c0 < 64; c0 += 32) {
+          uint32_t r[32];
+          tmem_ld<32>(tm_s[b] + cbase + c0 + lane_base, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int h = 0; h < 32; ++h) {
+            const float x = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
+            const int m = __reduce_max_sync(0xffffffffu, f32_sortable(x));
+            if (lane == 0) misc->colmax_w[warp][c0 + h] = m;
+          }
+        }
+        sm_bar();
+        if (tid < 128) {
+          const int w0 = (tid >> 6) * 4, c = tid & 63;
+          const int m = max(max(misc->colmax_w[w0][c], misc->colmax_w[w0 + 1][c]), max(misc->colmax_w[w0 + 2][c], misc->colmax_w[w0 + 3][c]));
+          mine->colmax[tid] = m;
+          st_cluster_u32(mapa_u32(smem_u32(&mine->colmax[tid]), peer), (uint32_t)m);
+        }
+      }
+      sm_bar();
+      if (tid == 0) {
+        mine->flag = (int)over_cta;
+        st_cluster_u32(mapa_u32(smem_u32(&mine->flag), peer), over_cta);
+        mbar_arrive_cluster(mapa_u32(smem_u32(&misc->post_bar[b]), rank));
+        mbar_arrive_cluster(mapa_u32(smem_u32(&misc->post_bar[b]), peer));
+      }
+      mbar_wait_cluster(smem_u32(&misc->post_bar[b]), (u >> 1) & 1);
+      const int f0 = misc->post[b][0].flag, f1 = misc->post[b][1].flag;
+      if (f0 | f1) {
+        // ---- rare path, taken by both CTAs together: raise the references, rescale O^T and the running sums ----
+        if (tid < 128) {
+          float m_new = misc->mref[tid];
+          const float m_old = m_new;
+          if (f0) m_new = fmaxf(m_new, sortable_f32(misc->post[b][0].colmax[tid]));
+          if (f1) m_new = fmaxf(m_new, sortable_f32(misc->post[b][1].colmax[tid]));
+          if (m_new == -INFINITY) m_new = 0.f;
+          misc->fac[tid] = m_old == -INFINITY ? 0.f : exp2f(m_old - m_new);
+          misc->mref[tid] = m_new;
+        }
+        sm_bar();
+#pragma unroll
+        for (int h = 0; h < 64; ++h) lsum[h] *= misc->fac[cbase + h];
+        if (u > 0) {
+          mbar_wait(smem_u32(&misc->p_free), (u - 1) & 1);  // the previous super-tile's P.V has landed in O^T
+          tc_fence_after();
+          for (int j = 0; j < 2; ++j) {
+#pragma unroll
+            for (int c = 0; c < 64; c += 16) {
+              uint32_t o[16];
+              tmem_ld<16>(tm_o + j * 128 + cbase + c + lane_base, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int e = 0; e < 16; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * misc->fac[cbase + c + e]);
+              tmem_st16(tm_o + j * 128 + cbase + c + lane_base, o);
+            }
+          }
+          tmem_st_wait();
+          tc_fence_before();
+        }
+      }
+      if (tid == 0) stamp(1, u, 1);
+      // ---- probabilities of this thread's 64 heads ----
+#pragma unroll
+      for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld<32>(tm_s[b] + cbase + c0 + lane_base, r);
+        tmem_ld_wait();
+        if (c0 == 32) {   // last read of this S^T buffer: one arrival per warp on the leader's barrier
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&misc->s_free[b]), 0));
+        }
+#pragma unroll
+        for (int h = 0; h < 32; ++h) {
+          const float x = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
+          const float pv = fast_exp2(x - misc->mref[cbase + c0 + h]);
+          lsum[c0 + h] += pv;
+          r[h] = p.f16 ? (uint32_t)__half_as_ushort(__float2half_rn(pv)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(pv));
+        }
+        if (c0 == 0 && u > 0) mbar_wait(smem_u32(&misc->p_free), (u - 1) & 1);
+        if (c0 == 0 && tid == 0) stamp(1, u, 2);
+#pragma unroll
+        for (int h = 0; h < 32; ++h)
+          st_cluster_u16(p_dst + (c0 + h) * 128 + ((unit ^ (h & 7)) << 4) + within, (uint16_t)r[h]);
+      }
+      asm volatile("fence.proxy.async;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(lead_p_full);
+      if (tid == 0) stamp(1, u, 3);
+    }
+
+    // ---- row sums of this CTA's tokens, per head, posted to both CTAs ----
+    mbar_wait(smem_u32(&misc->o_full), 0);   // every MMA of the pair is complete: the ring is scratch now
+    tc_fence_after();
+    float* scratch = reinterpret_cast<float*>(ring_ptr);  // [128 rows][129]
+#pragma unroll
+    for (int h = 0; h < 64; ++h) scratch[row * 129 + cbase + h] = lsum[h];
+    sm_bar();
+    if (tid < 128) {
+      float l = 0.f;
+      for (int t = 0; t < kTile; ++t) l += scratch[t * 129 + tid];
+      misc->lpart[rank][tid] = l;
+      st_cluster_u32(mapa_u32(smem_u32(&misc->lpart[rank][tid]), peer), __float_as_uint(l));
+    }
+
+  }
+
+  // everyone: the row sums of both CTAs are in place (and no CTA touches the peer's shared memory after this point)
+  cluster_sync_all();
+  if (warp < kPairSoftmaxWarps) {
+    const int quad = warp & 3, hh = warp >> 2;
+    const int row = quad * 32 + lane;
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const int cbase = 64 * hh;
+    const bool direct = nsplit == 1;
+    if (tid < 128) {
+      const float l = misc->lpart[0][tid] + misc->lpart[1][tid];
+      misc->fac[tid] = 1.f / l;
+      if (rank == 0 && tid < p.H) {
+        const float lse = (misc->mref[tid] + log2f(l)) * kLn2;
+        if (direct) {
+          if (p.lse != nullptr) p.lse[(long long)seq * p.lse_stride + tid] = lse;
+        } else {
+          p.part_lse[((long long)seq * p.H + tid) * p.max_splits + split] = lse;
+        }
+      }
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    for (int j = 0; j < 2; ++j) {
+      const int dv = 256 * j + 128 * (int)rank + row;
+#pragma unroll
+      for (int c = 0; c < 64; c += 16) {
+        uint32_t o[16];
+        tmem_ld<16>(tm_o + j * 128 + cbase + c + lane_base, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const int h = cbase + c + e;
+          if (h < p.H) {
+            const float v = __uint_as_float(o[e]) * misc->fac[h];
+            if (direct) {
+              const long long off = (long long)seq * p.out_seq_stride + (long long)h * p.out_head_stride + dv;
+              if (p.f16) reinterpret_cast<__half*>(p.out)[off] = __float2half_rn(v);
+              else reinterpret_cast<__nv_bfloat16*>(p.out)[off] = __float2bfloat16_rn(v);
+            } else {
+              p.part_out[(((long long)seq * p.H + h) * p.max_splits + split) * 512 + dv] = v;
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  cluster_sync_all();
+  if (warp == kPairMmaWarp) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+  }
+}
+
 // ---- merge of the token splits (flash-decoding reduce): out = sum_j w_j O_j, w_j = exp(lse_j - max) / sum ----
 __global__ void __launch_bounds__(128) mla_merge_kernel(const MlaParams p) {
   const int seq = blockIdx.y, h = blockIdx.x;
@@ -613,26 +1112,52 @@ int encode_map3(TmaDesc* out, const void* ptr, bool f16, uint64_t d0, uint64_t d
 
 int mla_group_width(int H) { return H <= 16 ? 16 : (H <= 32 ? 32 : 64); }
 
+bool mla_use_pair(int H) {   // 65..128 heads: the two-CTA kernel (B200_MLA_PAIR_OFF=1 keeps two independent 64-head groups)
+  static const int off = env_int("B200_MLA_PAIR_OFF");
+  return H > 64 && !off;
+}
+
 // number of token splits: minimise waves(items) / splits over the allowed range (every split >= kMinSplitTiles tiles)
 int mla_choose_splits(int S, int H, long long max_seq_len, int requested) {
-  const long long tiles = (max_seq_len + kTile - 1) / kTile;
-  int cap = (int)min((long long)kMaxSplits, max(1LL, tiles / kMinSplitTiles));
+  const bool pair = mla_use_pair(H);
+  const int unit = pair ? 2 * kTile : kTile;                        // tokens per scheduling unit (tile / super-tile)
+  const long long tiles = (max_seq_len + unit - 1) / unit;
+  int cap = (int)min((long long)kMaxSplits, max(1LL, tiles / (pair ? kMinSplitTiles / 2 : kMinSplitTiles)));
   if (requested == 1) return 1;
   if (requested > 1) return (int)min((long long)min(requested, kMaxSplits), max(1LL, tiles));
   const int NG = mla_group_width(H);
-  const long long base = (long long)S * ((H + NG - 1) / NG);
-  const int sms = device_sm_count() * ((NG <= 32 && env_int("B200_MLA_OCC2") != 0) ? 2 : 1);  // resident CTAs
+  const long long base = pair ? (long long)S : (long long)S * ((H + NG - 1) / NG);
+  int sms = device_sm_count() * ((NG <= 32 && env_int("B200_MLA_OCC2") != 0) ? 2 : 1);  // resident CTAs (or CTA pairs)
+  if (pair) sms /= 2;
   int best = 1;
   double best_cost = 1e30;
   for (int s = 1; s <= cap; ++s) {
-    const long long per = (tiles + s - 1) / s;                       // tiles per split
+    const long long per = (tiles + s - 1) / s;                       // units per split
     const long long waves = (base * s + sms - 1) / sms;
     // measured on B200 (profiles/r2_mla_*): a CTA costs ~4 tile-times beyond its tiles (query load, pipeline fill,
     // epilogue), and every extra split adds fp32 partials for the merge kernel to re-read
-    const double cost = (double)waves * ((double)per + 4.0) + (s > 1 ? 1.0 + 0.25 * s : 0.0);
+    const double cost = (double)waves * ((double)per + (pair ? 2.0 : 4.0)) + (s > 1 ? 1.0 + 0.25 * s : 0.0);
     if (cost < best_cost - 1e-9) best_cost = cost, best = s;
   }
   return best;
+}
+
+int launch_mla_pair(const MlaParams& mp, const TmaDesc& kv, const TmaDesc& qn, const TmaDesc& qp, dim3 grid, cudaStream_t s) {
+  const size_t smem = pair_smem_bytes(mp.nslots);
+  static thread_local int configured_device = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (configured_device != dev) {
+    cudaError_t e = cudaFuncSetAttribute(mla_decode_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+    if (e != cudaSuccess) {
+      set_error("mla_decode: cudaFuncSetAttribute(smem, pair kernel) failed: %s", cudaGetErrorString(e));
+      return B200_ERR_CUDA;
+    }
+    configured_device = dev;
+  }
+  mla_decode_pair_kernel<<<grid, kPairThreads, smem, s>>>(mp, kv, qn, qp);
+  count_launch();
+  return check_launch("mla_decode (pair kernel)");
 }
 
 template <int NG>
@@ -704,8 +1229,10 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   for (mp.page_shift = 0; (1 << mp.page_shift) < p.page_size; ++mp.page_shift) {}
   mp.box_rows = p.page_size < kTile ? p.page_size : kTile;
   mp.max_splits = splits;
-  const long long tiles = (max_len + kTile - 1) / kTile;
-  mp.split_tokens = (int)((tiles + splits - 1) / splits) * kTile;
+  const bool pair = mla_use_pair(p.num_heads);
+  const int unit = pair ? 2 * kTile : kTile;
+  const long long tiles = (max_len + unit - 1) / unit;
+  mp.split_tokens = (int)((tiles + splits - 1) / splits) * unit;
   mp.f16 = f16 ? 1 : 0;
   // shared memory: one CTA per SM for 64-head groups; two for the narrow groups (their MMA lanes then hide each
   // other's barrier waits and commits), each with half of the SM's 228 KiB minus the per-block reservation
@@ -713,6 +1240,7 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   const size_t budget = (NG <= 32 && occ2) ? (233472 / 2 - 1024) : 232448;
   int nslots = (int)((budget - 1024 - (size_t)NG * 128 * (kKChunks + 2) - sizeof(MlaMisc)) / kChunkBytes);
   nslots = min(nslots & ~1, kMaxSlots);
+  if (pair) nslots = (int)((232448 - 1024 - (size_t)64 * 128 * kKChunks - 2 * 16384 - sizeof(PairMisc)) / kChunkBytes) & ~1;
   mp.nslots = nslots;
   if (splits > 1) {
     const uint64_t need = (uint64_t)p.num_seqs * p.num_heads * splits * (512 + 1) * sizeof(float);
@@ -733,8 +1261,9 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   rc = encode_map3(&qp, p.q_pe, f16, 64, (uint64_t)p.num_heads, (uint64_t)p.num_seqs, p.q_pe_head_stride, p.q_pe_seq_stride,
                    (uint32_t)NG, "q_pe");
   if (rc != B200_OK) return rc;
-  const dim3 grid((unsigned)(mp.groups * splits), (unsigned)p.num_seqs);
-  if (NG == 16) rc = launch_mla<16>(mp, kv, qn, qp, grid, s);
+  const dim3 grid((unsigned)((pair ? 2 : mp.groups) * splits), (unsigned)p.num_seqs);
+  if (pair) rc = launch_mla_pair(mp, kv, qn, qp, grid, s);
+  else if (NG == 16) rc = launch_mla<16>(mp, kv, qn, qp, grid, s);
   else if (NG == 32) rc = launch_mla<32>(mp, kv, qn, qp, grid, s);
   else rc = launch_mla<64>(mp, kv, qn, qp, grid, s);
   if (rc != B200_OK) return rc;
