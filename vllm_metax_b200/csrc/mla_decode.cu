@@ -575,7 +575,7 @@ struct PairMisc {
   PairPost post[2][2];      // [super-tile parity][source CTA]
 };
 __host__ __device__ constexpr size_t pair_smem_bytes(int nslots) {
-  return 1024 + (size_t)64 * 128 * kKChunks + 2 * 16384 + (size_t)nslots * kChunkBytes + sizeof(PairMisc);
+  return 1024 + (size_t)64 * 128 * kKChunks + 3 * 16384 + (size_t)nslots * kChunkBytes + sizeof(PairMisc);
 }
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -661,7 +661,8 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
   uint8_t* const base_ptr = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t q_u32 = base;                              // 9 chunks [64 heads x 128 B]: heads 64r .. 64r+63
   const uint32_t p_u32 = q_u32 + kKChunks * 64 * 128;       // P^T[X_0], P^T[X_1]: 2 x (2 chunks [64 heads x 128 B])
-  const uint32_t ring_u32 = p_u32 + 2 * 16384;
+  const uint32_t stage_u32 = p_u32 + 2 * 16384;             // staging of the probabilities bound for the peer (16 KiB)
+  const uint32_t ring_u32 = stage_u32 + 16384;
   uint8_t* const ring_ptr = base_ptr + (ring_u32 - base);
   PairMisc* const misc = reinterpret_cast<PairMisc*>(ring_ptr + (size_t)p.nslots * kChunkBytes);
   const int npairs = p.nslots >> 1;
@@ -856,12 +857,54 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
     const uint32_t unit = (row & 63) >> 3, within = (row & 7) * 2;
     const uint32_t peer = rank ^ 1;
 
+    // The CTAs agree on the references through "posts": after looking at its S^T tile, each CTA tells both CTAs whether a
+    // logit passed m_ref + kTau and, if so, its column maxima.  The post of super-tile u is consumed at the START of
+    // super-tile u + 1 (so the exchange is off the critical path); only the first super-tile, where no reference
+    // exists yet, waits for it.  A logit may therefore exceed its reference by more than kTau for one super-tile:
+    // harmless in bf16 / fp32 unless it jumps by more than ~2^100 within 256 tokens (the exponent is clamped).
+    const bool remote_half = (uint32_t)hh != rank;
     for (int u = 0; u < U; ++u) {
       const int b = u & 1;
+      // ---- references: posts of the previous super-tile (both CTAs take the same decision) ----
+      if (u > 0) {
+        const int pb = (u - 1) & 1;
+        mbar_wait_cluster(smem_u32(&misc->post_bar[pb]), ((u - 1) >> 1) & 1);
+        const int f0 = misc->post[pb][0].flag, f1 = misc->post[pb][1].flag;
+        if (u > 1 && (f0 | f1)) {   // (the posts of super-tile 0 were applied synchronously below)
+          if (tid < 128) {
+            float m_new = misc->mref[tid];
+            const float m_old = m_new;
+            if (f0) m_new = fmaxf(m_new, sortable_f32(misc->post[pb][0].colmax[tid]));
+            if (f1) m_new = fmaxf(m_new, sortable_f32(misc->post[pb][1].colmax[tid]));
+            misc->fac[tid] = exp2f(m_old - m_new);
+            misc->mref[tid] = m_new;
+          }
+          sm_bar();
+#pragma unroll
+          for (int h = 0; h < 64; ++h) lsum[h] *= misc->fac[cbase + h];
+          mbar_wait(smem_u32(&misc->p_free), (u - 1) & 1);  // the previous super-tile's P.V has landed in O^T
+          tc_fence_after();
+          for (int j = 0; j < 2; ++j) {
+#pragma unroll
+            for (int c = 0; c < 64; c += 16) {
+              uint32_t o[16];
+              tmem_ld<16>(tm_o + j * 128 + cbase + c + lane_base, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int e = 0; e < 16; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * misc->fac[cbase + c + e]);
+              tmem_st16(tm_o + j * 128 + cbase + c + lane_base, o);
+            }
+          }
+          tmem_st_wait();
+          tc_fence_before();
+          sm_bar();   // fac / mref are rewritten by the next rare path only after everyone is done with them
+        }
+      }
       mbar_wait(smem_u32(&misc->s_full[b]), (u >> 1) & 1);
       tc_fence_after();
       const bool valid = t0 + (2 * u + (int)rank) * kTile + row < t1;
       if (tid == 0) stamp(1, u, 0);
+      // ---- pass 1: does a logit of this tile pass its reference?  Post the answer (and the column maxima) ----
       bool over = false;
 #pragma unroll
       for (int c0 = 0; c0 < 64; c0 += 32) {
@@ -876,7 +919,7 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
       asm volatile("{\n.reg .pred p, q;\nsetp.ne.b32 q, %1, 0;\nbar.red.or.pred p, 1, 256, q;\nselp.u32 %0, 1, 0, p;\n}\n"
                    : "=r"(over_cta) : "r"((uint32_t)over) : "memory");
       PairPost* const mine = &misc->post[b][rank];
-      if (over_cta) {   // this CTA's column maxima, posted to both CTAs
+      if (over_cta) {
 #pragma unroll
         for (int c0 = 0; c0 < 64; c0 += 32) {
           uint32_t r[32];
@@ -896,50 +939,29 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
           mine->colmax[tid] = m;
           st_cluster_u32(mapa_u32(smem_u32(&mine->colmax[tid]), peer), (uint32_t)m);
         }
+        sm_bar();
       }
-      sm_bar();
       if (tid == 0) {
         mine->flag = (int)over_cta;
         st_cluster_u32(mapa_u32(smem_u32(&mine->flag), peer), over_cta);
         mbar_arrive_cluster(mapa_u32(smem_u32(&misc->post_bar[b]), rank));
         mbar_arrive_cluster(mapa_u32(smem_u32(&misc->post_bar[b]), peer));
       }
-      mbar_wait_cluster(smem_u32(&misc->post_bar[b]), (u >> 1) & 1);
-      const int f0 = misc->post[b][0].flag, f1 = misc->post[b][1].flag;
-      if (f0 | f1) {
-        // ---- rare path, taken by both CTAs together: raise the references, rescale O^T and the running sums ----
+      if (u == 0) {   // no reference yet: this one exchange is synchronous (O^T and the sums are still empty)
+        mbar_wait_cluster(smem_u32(&misc->post_bar[0]), 0);
+        const int f0 = misc->post[0][0].flag, f1 = misc->post[0][1].flag;
         if (tid < 128) {
-          float m_new = misc->mref[tid];
-          const float m_old = m_new;
-          if (f0) m_new = fmaxf(m_new, sortable_f32(misc->post[b][0].colmax[tid]));
-          if (f1) m_new = fmaxf(m_new, sortable_f32(misc->post[b][1].colmax[tid]));
+          float m_new = -INFINITY;
+          if (f0) m_new = fmaxf(m_new, sortable_f32(misc->post[0][0].colmax[tid]));
+          if (f1) m_new = fmaxf(m_new, sortable_f32(misc->post[0][1].colmax[tid]));
           if (m_new == -INFINITY) m_new = 0.f;
-          misc->fac[tid] = m_old == -INFINITY ? 0.f : exp2f(m_old - m_new);
           misc->mref[tid] = m_new;
         }
         sm_bar();
-#pragma unroll
-        for (int h = 0; h < 64; ++h) lsum[h] *= misc->fac[cbase + h];
-        if (u > 0) {
-          mbar_wait(smem_u32(&misc->p_free), (u - 1) & 1);  // the previous super-tile's P.V has landed in O^T
-          tc_fence_after();
-          for (int j = 0; j < 2; ++j) {
-#pragma unroll
-            for (int c = 0; c < 64; c += 16) {
-              uint32_t o[16];
-              tmem_ld<16>(tm_o + j * 128 + cbase + c + lane_base, o);
-              tmem_ld_wait();
-#pragma unroll
-              for (int e = 0; e < 16; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * misc->fac[cbase + c + e]);
-              tmem_st16(tm_o + j * 128 + cbase + c + lane_base, o);
-            }
-          }
-          tmem_st_wait();
-          tc_fence_before();
-        }
       }
       if (tid == 0) stamp(1, u, 1);
-      // ---- probabilities of this thread's 64 heads ----
+      // ---- pass 2: probabilities of this thread's 64 heads ----
+      const uint32_t wr_base = remote_half ? stage_u32 + (row >> 6) * 64 * 128 : p_u32 + rank * 16384 + (row >> 6) * 64 * 128;
 #pragma unroll
       for (int c0 = 0; c0 < 64; c0 += 32) {
         uint32_t r[32];
@@ -953,15 +975,35 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
 #pragma unroll
         for (int h = 0; h < 32; ++h) {
           const float x = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
-          const float pv = fast_exp2(x - misc->mref[cbase + c0 + h]);
+          const float pv = fast_exp2(fminf(x - misc->mref[cbase + c0 + h], 120.f));
           lsum[c0 + h] += pv;
           r[h] = p.f16 ? (uint32_t)__half_as_ushort(__float2half_rn(pv)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(pv));
         }
-        if (c0 == 0 && u > 0) mbar_wait(smem_u32(&misc->p_free), (u - 1) & 1);
+        // the local half goes straight into this CTA's P^T[X_rank] (once the previous P.V released it); the half bound
+        // for the peer is staged locally first
+        if (c0 == 0 && u > 0 && !remote_half) mbar_wait(smem_u32(&misc->p_free), (u - 1) & 1);
         if (c0 == 0 && tid == 0) stamp(1, u, 2);
 #pragma unroll
-        for (int h = 0; h < 32; ++h)
-          st_cluster_u16(p_dst + (c0 + h) * 128 + ((unit ^ (h & 7)) << 4) + within, (uint16_t)r[h]);
+        for (int h = 0; h < 32; ++h) {
+          const uint32_t addr = wr_base + (c0 + h) * 128 + ((unit ^ (h & 7)) << 4) + within;
+          asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)r[h]) : "memory");
+        }
+      }
+      if (remote_half) {
+        // this warp's 32 token rows are 4 sixteen-byte units per head: ship them to the peer's P^T[X_rank], 8 units per lane
+        __syncwarp();
+        if (u > 0) mbar_wait(smem_u32(&misc->p_free), (u - 1) & 1);
+        const uint32_t src0 = stage_u32 + (quad >> 1) * 64 * 128;
+        const uint32_t dst0 = mapa_u32(p_u32 + rank * 16384 + (quad >> 1) * 64 * 128, peer);
+        const uint32_t ubase = (quad & 1) * 4;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const int idx = k * 32 + lane, h = idx >> 2;
+          const uint32_t off = h * 128 + (((ubase + (idx & 3)) ^ (h & 7)) << 4);
+          uint32_t v0, v1, v2, v3;
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v0), "=r"(v1), "=r"(v2), "=r"(v3) : "r"(src0 + off) : "memory");
+          asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst0 + off), "r"(v0), "r"(v1), "r"(v2), "r"(v3) : "memory");
+        }
       }
       asm volatile("fence.proxy.async;" ::: "memory");
       __syncwarp();
@@ -1240,7 +1282,7 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   const size_t budget = (NG <= 32 && occ2) ? (233472 / 2 - 1024) : 232448;
   int nslots = (int)((budget - 1024 - (size_t)NG * 128 * (kKChunks + 2) - sizeof(MlaMisc)) / kChunkBytes);
   nslots = min(nslots & ~1, kMaxSlots);
-  if (pair) nslots = (int)((232448 - 1024 - (size_t)64 * 128 * kKChunks - 2 * 16384 - sizeof(PairMisc)) / kChunkBytes) & ~1;
+  if (pair) nslots = (int)((232448 - 1024 - (size_t)64 * 128 * kKChunks - 3 * 16384 - sizeof(PairMisc)) / kChunkBytes) & ~1;
   mp.nslots = nslots;
   if (splits > 1) {
     const uint64_t need = (uint64_t)p.num_seqs * p.num_heads * splits * (512 + 1) * sizeof(float);
