@@ -135,3 +135,20 @@ def test_stale_rows_past_the_sequence_do_not_leak(ops):
     d["kv_cache"] = cache
     out, lse = run(ops, d)
     check(out, lse, ref_out, ref_lse, torch.bfloat16)
+
+
+@pytest.mark.parametrize("page,splits", [(16, 4), (64, 1)])
+def test_triton_decode_attention_fwd_call_shape(ops, page, splits):
+    """the Triton MLA backend's call (vllm_metax/v1/attention/backends/mla/triton_mla.py:160-200) on our kernel"""
+    from vllm_metax_b200.attention.mla_decode import decode_attention_fwd
+    d = orc.make_mla_inputs(3, 16, page, 900, seed=21)
+    ref_out, ref_lse = orc.mla_decode(d["query"], d["kv_cache"], d["scale"], d["block_tables"], d["seq_lens"])
+    q = d["query"].to(DEV)
+    cache = d["kv_cache"].to(DEV).unsqueeze(2)
+    o = torch.zeros(3, 16, 512, dtype=q.dtype, device=DEV)
+    lse = torch.zeros(3, 16, dtype=q.dtype, device=DEV)
+    attn_logits = torch.empty(3, 16, splits, 513, dtype=torch.float32, device=DEV)
+    decode_attention_fwd(q, cache, cache[..., :512], o, lse, d["block_tables"].to(DEV), d["seq_lens"].to(DEV), attn_logits,
+                         splits, d["scale"], page)
+    check(o.cpu(), None, ref_out, None, torch.bfloat16)
+    torch.testing.assert_close(lse.float().cpu(), ref_lse, atol=5e-2, rtol=1e-2)  # lse in the query dtype, as the caller allocates it
