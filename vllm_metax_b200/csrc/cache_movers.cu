@@ -10,10 +10,16 @@
 
 #include <algorithm>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200 {
 namespace {
+inline int env_int_or(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v != nullptr && *v ? atoi(v) : dflt;
+}
 
 inline bool aligned(const void* q, size_t a) { return (reinterpret_cast<uintptr_t>(q) % a) == 0; }
 
@@ -355,8 +361,11 @@ extern "C" int b200_gather_cache(const b200_gather_cache_params_t* p, void* stre
   } else {
     B200_REQUIRE(sb == db, B200_ERR_UNSUPPORTED, "src_cache and dst must have the same dtype");
   }
-  // splits: cover the machine ~4x with CTAs of 8 warps (the reference fixes 2/4/16, cache_kernels.cu:747)
-  int splits = (4 * device_sm_count() + p->batch_size - 1) / p->batch_size;
+  // splits: a warp keeps one row (about 1 KiB) in flight, so the copy needs every warp slot of the machine (8 CTAs of
+  // 8 warps per SM) and a few waves: ~32 CTAs per SM (the reference fixes 2/4/16 splits, cache_kernels.cu:747; with 4
+  // CTAs per SM this kernel was latency-bound at 4.6-4.8 TB/s)
+  static const int cover = env_int_or("B200_GATHER_COVER", 32);
+  int splits = (cover * device_sm_count() + p->batch_size - 1) / p->batch_size;
   splits = std::max(1, std::min(splits, 1024));
   dim3 grid(p->batch_size, splits);
   cudaStream_t s = static_cast<cudaStream_t>(stream);

@@ -8,8 +8,8 @@
 //   out_lse = log(w_p + w_s) + m
 //
 // HBM-bound elementwise op (3 x N x H x D elements moved, 2 lse reads per head):
-// one thread per 16-byte pack, loads marked no-allocate, grid sized from the pack
-// count.  The per-(token, head) weights are recomputed by each of the D/pack
+// one CTA per token, 16-byte packs, two packs in flight per thread, 32-bit index
+// arithmetic.  The per-(token, head) weights are recomputed by each of the D/pack
 // threads of a head (the lse values are broadcast hits in L1); that keeps the
 // kernel barrier-free.
 #include "common.cuh"
@@ -17,42 +17,65 @@
 namespace b200 {
 namespace {
 
+// one CTA per token; thread t walks the token's packs t, t + 256, ... (32-bit index arithmetic only), two packs per
+// step with all four 16-byte loads issued before the arithmetic
 template <typename T>
 __global__ void __launch_bounds__(256) merge_attn_states_kernel(b200_merge_attn_states_params_t p) {
   constexpr int kPack = 16 / sizeof(T);
   const uint32_t packs_per_head = p.head_size / kPack;
-  const uint64_t total = (uint64_t)p.num_tokens * p.num_heads * packs_per_head;
-  const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
-  const uint32_t pack = idx % packs_per_head;
-  const uint64_t th = idx / packs_per_head;
-  const uint32_t head = th % p.num_heads;
-  const uint64_t token = th / p.num_heads;
+  const uint32_t packs = p.num_heads * packs_per_head;     // per token
+  const uint64_t token = blockIdx.x;
+  const T* pbase = reinterpret_cast<const T*>(p.prefix_output) + token * p.prefix_stride;
+  const T* sbase = reinterpret_cast<const T*>(p.suffix_output) + token * p.suffix_stride;
+  T* obase = reinterpret_cast<T*>(p.output) + token * p.output_stride;
 
-  float pl = p.prefix_lse[(uint64_t)head * p.num_tokens + token];
-  float sl = p.suffix_lse[(uint64_t)head * p.num_tokens + token];
-  pl = isinf(pl) ? -INFINITY : pl;
-  sl = isinf(sl) ? -INFINITY : sl;
-  const float m = fmaxf(pl, sl);
-  const float pse = expf(pl - m);
-  const float sse = expf(sl - m);
-  const float se = pse + sse;
-  const float pw = pse / se;
-  const float sw = sse / se;
-
-  const int64_t hoff = (int64_t)head * p.head_size + (int64_t)pack * kPack;
-  const Vec16 pv = ld_global_16_coherent(reinterpret_cast<const T*>(p.prefix_output) + token * p.prefix_stride + hoff);
-  const Vec16 sv = ld_global_16_coherent(reinterpret_cast<const T*>(p.suffix_output) + token * p.suffix_stride + hoff);
-  Vec16 ov;
-  const T* pe = reinterpret_cast<const T*>(&pv);
-  const T* se_ = reinterpret_cast<const T*>(&sv);
-  T* oe = reinterpret_cast<T*>(&ov);
+  auto weights = [&](uint32_t head, float& pw, float& sw, float& lse) {
+    float pl = p.prefix_lse[(uint64_t)head * p.num_tokens + token];
+    float sl = p.suffix_lse[(uint64_t)head * p.num_tokens + token];
+    pl = isinf(pl) ? -INFINITY : pl;
+    sl = isinf(sl) ? -INFINITY : sl;
+    const float m = fmaxf(pl, sl);
+    const float pse = expf(pl - m);
+    const float sse = expf(sl - m);
+    const float se = pse + sse;
+    pw = pse / se;
+    sw = sse / se;
+    lse = logf(se) + m;  // :84-85
+  };
+  auto combine = [&](const Vec16& pv, const Vec16& sv, float pw, float sw) {
+    Vec16 ov;
+    const T* pe = reinterpret_cast<const T*>(&pv);
+    const T* se_ = reinterpret_cast<const T*>(&sv);
+    T* oe = reinterpret_cast<T*>(&ov);
 #pragma unroll
-  for (int i = 0; i < kPack; ++i)
-    oe[i] = from_f32<T>(__fmaf_rn(to_f32<T>(pe[i]), pw, __fmul_rn(to_f32<T>(se_[i]), sw)));  // :73
-  *reinterpret_cast<Vec16*>(reinterpret_cast<T*>(p.output) + token * p.output_stride + hoff) = ov;
-  if (p.output_lse != nullptr && pack == 0)
-    p.output_lse[(uint64_t)head * p.num_tokens + token] = logf(se) + m;  // :84-85
+    for (int i = 0; i < kPack; ++i)
+      oe[i] = from_f32<T>(__fmaf_rn(to_f32<T>(pe[i]), pw, __fmul_rn(to_f32<T>(se_[i]), sw)));  // :73
+    return ov;
+  };
+  uint32_t i = threadIdx.x;
+  for (; i + 256 < packs; i += 512) {
+    const uint32_t j = i + 256;
+    const Vec16 pv0 = ld_global_16_coherent(pbase + (uint64_t)i * kPack), sv0 = ld_global_16_coherent(sbase + (uint64_t)i * kPack);
+    const Vec16 pv1 = ld_global_16_coherent(pbase + (uint64_t)j * kPack), sv1 = ld_global_16_coherent(sbase + (uint64_t)j * kPack);
+    const uint32_t h0 = i / packs_per_head, h1 = j / packs_per_head;
+    float pw0, sw0, l0, pw1, sw1, l1;
+    weights(h0, pw0, sw0, l0);
+    weights(h1, pw1, sw1, l1);
+    *reinterpret_cast<Vec16*>(obase + (uint64_t)i * kPack) = combine(pv0, sv0, pw0, sw0);
+    *reinterpret_cast<Vec16*>(obase + (uint64_t)j * kPack) = combine(pv1, sv1, pw1, sw1);
+    if (p.output_lse != nullptr) {
+      if (i % packs_per_head == 0) p.output_lse[(uint64_t)h0 * p.num_tokens + token] = l0;
+      if (j % packs_per_head == 0) p.output_lse[(uint64_t)h1 * p.num_tokens + token] = l1;
+    }
+  }
+  for (; i < packs; i += 256) {
+    const Vec16 pv = ld_global_16_coherent(pbase + (uint64_t)i * kPack), sv = ld_global_16_coherent(sbase + (uint64_t)i * kPack);
+    const uint32_t h = i / packs_per_head;
+    float pw, sw, l;
+    weights(h, pw, sw, l);
+    *reinterpret_cast<Vec16*>(obase + (uint64_t)i * kPack) = combine(pv, sv, pw, sw);
+    if (p.output_lse != nullptr && i % packs_per_head == 0) p.output_lse[(uint64_t)h * p.num_tokens + token] = l;
+  }
 }
 
 inline bool aligned16(const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; }
@@ -79,10 +102,8 @@ extern "C" int b200_merge_attn_states(const b200_merge_attn_states_params_t* p, 
   B200_REQUIRE(aligned16(p->output) && aligned16(p->prefix_output) && aligned16(p->suffix_output) &&
                    p->output_stride % pack == 0 && p->prefix_stride % pack == 0 && p->suffix_stride % pack == 0,
                B200_ERR_INVALID_ARGUMENT, "outputs must be 16-byte aligned with 16-byte aligned token rows");
-  const uint64_t total = (uint64_t)p->num_tokens * p->num_heads * (p->head_size / pack);
   const int threads = 256;
-  const uint64_t blocks = (total + threads - 1) / threads;
-  B200_REQUIRE(blocks <= 0x7fffffffull, B200_ERR_UNSUPPORTED, "merge_attn_states: too many elements");
+  const uint64_t blocks = (uint64_t)p->num_tokens;   // one CTA per token
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (p->dtype) {
     case B200_DTYPE_F32: merge_attn_states_kernel<float><<<(unsigned)blocks, threads, 0, s>>>(*p); break;
