@@ -23,6 +23,9 @@ SHAPES = [  # batch, ctx, heads
 PAGE = 64
 
 
+VARLEN = False
+
+
 def make(b, L, H, dev):
     g = torch.Generator(device=dev).manual_seed(b * 7 + L + H)
     pages = L // PAGE
@@ -31,6 +34,9 @@ def make(b, L, H, dev):
     q = torch.randn(b, H, 576, generator=g, device=dev, dtype=torch.bfloat16)
     table = torch.randperm(nb, generator=g, device=dev).to(torch.int32).view(b, pages)
     lens = torch.full((b,), L, dtype=torch.int32, device=dev)
+    if VARLEN:  # ragged batch like the reference test's varlen case (normal around the mean, sigma = mean / 2), capped at L
+        gc = torch.Generator().manual_seed(b + L)
+        lens = torch.empty(b).normal_(0.6 * L, 0.3 * L, generator=gc).clamp_(128, L).to(torch.int32).to(dev)
     return q, cache, table, lens
 
 
@@ -60,8 +66,11 @@ def main():
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--splits", type=int, default=-1)
     ap.add_argument("--only", type=int, default=-1)
+    ap.add_argument("--varlen", action="store_true", help="ragged sequence lengths (mean 0.6 ctx, sigma 0.3 ctx, capped at ctx)")
     ap.add_argument("--witness", help="(--impl upstream) run the stock kernel on small CPU-seeded inputs and save inputs + outputs")
     args = ap.parse_args()
+    global VARLEN
+    VARLEN = args.varlen
     if args.compare:
         a, b = torch.load(args.compare[0]), torch.load(args.compare[1])
         for k in sorted(set(a) & set(b)):
@@ -127,12 +136,13 @@ def main():
         except Exception as e:
             print(json.dumps({"impl": args.impl, "shape": [b, L, H], "error": "%s: %s" % (type(e).__name__, str(e)[:300])}), flush=True)
             continue
-        kv_bytes = b * L * 1152
+        tot = int(lens.sum().item())
+        kv_bytes = tot * 1152
         byt = kv_bytes + b * H * (576 + 512) * 2
-        flops = 2.0 * b * L * H * (576 + 512)
+        flops = 2.0 * tot * H * (576 + 512)
         print(json.dumps({"impl": args.impl, "shape": {"batch": b, "ctx": L, "heads": H, "page": PAGE}, "us": med * 1e3,
                           "us_min": mn * 1e3, "gbs": byt / med / 1e6, "tflops": flops / med / 1e9,
-                          "heads_computed": Hk}), flush=True)
+                          "heads_computed": Hk, "varlen": VARLEN, "tokens": tot}), flush=True)
         samples["out_b%d_L%d_H%d" % (b, L, H)] = out[:2, :H].float().cpu()
         samples["lse_b%d_L%d_H%d" % (b, L, H)] = lse[:2, :H].cpu()
         del q, cache, table, lens, qn, qp, out, lse, ws

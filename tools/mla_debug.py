@@ -14,6 +14,7 @@ from oracle import torch_oracle as orc  # noqa: E402
 from vllm_metax_b200 import _native  # noqa: E402
 
 lib = _native.load()
+CTA_TIMES = None
 DEV = "cuda:0"
 
 
@@ -24,7 +25,7 @@ def run(d, splits=1, debug=True):
     cache, table, lens = d["kv_cache"].to(DEV), d["block_tables"].to(DEV), d["seq_lens"].to(DEV)
     out = torch.full((B, H, 512), float("nan"), dtype=q.dtype, device=DEV)
     lse = torch.full((B, H), float("nan"), dtype=torch.float32, device=DEV)
-    dbg = torch.zeros(128 * 64 + 3 * 64 * 4 * 2, dtype=torch.float32, device=DEV)
+    dbg = torch.zeros(128 * 64 + 3 * 64 * 4 * 2 + 3 * 2 * 4096, dtype=torch.float32, device=DEV)
     p = _native.MlaDecodeParams()
     p.out, p.lse, p.q_nope, p.q_pe, p.kv_cache = out.data_ptr(), lse.data_ptr(), qn.data_ptr(), qp.data_ptr(), cache.data_ptr()
     p.seq_lens, p.page_table = lens.data_ptr(), table.data_ptr()
@@ -43,7 +44,9 @@ def run(d, splits=1, debug=True):
     rc = lib.b200_mla_decode(C.byref(p), None)
     assert rc == 0, lib.b200_last_error().decode()
     torch.cuda.synchronize()
-    stamps = dbg[128 * 64:].cpu().view(torch.int64).view(3, 64, 4)
+    global CTA_TIMES
+    CTA_TIMES = dbg[128 * 64 + 3 * 64 * 4 * 2:].cpu().view(torch.int64).view(-1, 3)
+    stamps = dbg[128 * 64:128 * 64 + 3 * 64 * 4 * 2].cpu().view(torch.int64).view(3, 64, 4)
     return out.cpu(), lse.cpu(), dbg[:128 * 64].view(128, 64).cpu(), stamps
 
 
@@ -72,7 +75,7 @@ def timeline(B, H, L, page=64):
     """per-tile clock64 stamps of CTA 0 (seq 0, group 0, split 0) while the whole batch runs"""
     d = orc.make_mla_inputs(B, H, page, L, seed=3, varlen=False)
     for _ in range(3):
-        out, lse, dbg, st = run(d, 1)
+        out, lse, dbg, st = run(d, 0 if os.environ.get("B200_MLA_STAMP_CTA") else 1)   # a stamped CTA index means the flat schedule
     t0 = int(st[2, 0, 0])
     print("timeline B%d H%d L%d (cycles from the first producer stamp)" % (B, H, L))
     print(" tile | MMA: S-start S-issued PV-start PV-issued | softmax: S-ready pass1 P-free P-written | producer0: K-start K-end V-start V-end")
@@ -83,8 +86,26 @@ def timeline(B, H, L, page=64):
         print(" %4d | %s | %s | %s" % (i, r(st[0, i]), r(st[1, i]), r(st[2, i])))
 
 
+def cta_times(B, H, L, page=64):
+    """start / end (globaltimer ns) and SM of every CTA of the decode kernel (B200_MLA_CTA_TIMES=1)"""
+    os.environ["B200_MLA_CTA_TIMES"] = "1"
+    d = orc.make_mla_inputs(B, H, page, L, seed=3, varlen=False)
+    for _ in range(3):
+        run(d, 0)
+    t = CTA_TIMES[CTA_TIMES[:, 1] > 0]
+    t0 = int(t[:, 0].min())
+    dur = (t[:, 1] - t[:, 0]).float() / 1e3
+    print("cta times B%d H%d L%d: %d CTAs, kernel span %.1f us; start spread %.1f us; duration min/median/max %.1f/%.1f/%.1f us" % (
+        B, H, L, t.shape[0], (int(t[:, 1].max()) - t0) / 1e3, (int(t[:, 0].max()) - t0) / 1e3, dur.min(), dur.median(), dur.max()))
+    print(" per CTA (us):", " ".join("%d" % round(float(x)) for x in dur))
+    order = torch.argsort(dur, descending=True)[:8]
+    print(" slowest:", [(int(i), round(float(dur[i]), 1), "sm%d" % int(t[i, 2]), "start+%.1f" % ((int(t[i, 0]) - t0) / 1e3)) for i in order])
+
+
 if __name__ == "__main__":
-    if len(sys.argv) > 1 and sys.argv[1] == "--timeline":
+    if len(sys.argv) > 1 and sys.argv[1] == "--cta-times":
+        cta_times(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]))
+    elif len(sys.argv) > 1 and sys.argv[1] == "--timeline":
         if len(sys.argv) > 4:
             timeline(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]))
         else:

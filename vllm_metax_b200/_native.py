@@ -10,7 +10,7 @@ import ctypes as C
 import os
 from pathlib import Path
 
-LIB_PATH = Path(__file__).resolve().parent / "libb200_paged_attn.so"
+LIB_PATH = Path(os.environ.get("B200_PAGED_ATTN_LIB") or Path(__file__).resolve().parent / "libb200_paged_attn.so")  # override: development A/B runs
 
 B200_OK = 0
 ERR_INVALID_ARGUMENT, ERR_UNSUPPORTED, ERR_CUDA, ERR_WORKSPACE = 1, 2, 3, 4

@@ -48,6 +48,10 @@ struct MlaParams {
   long long out_seq_stride, out_head_stride, page_table_stride, lse_stride;
   float scale_log2;
   int S, H, groups, page_size, page_shift, box_rows, max_splits, split_tokens, nslots, f16;
+  int flat;                 // persistent grid over the flat (sequence, group, tile) list
+  int stamp_cta;            // development: the CTA whose timeline is stamped
+  long long* cta_times;     // development: [cta][3] = globaltimer at start, at end, SM id
+  long long* flat_prefix;   // [S + 2] unit prefix per sequence, the total and the mode, written by CTA 0 for the merge kernel
 };
 
 // ---- tcgen05 / TMA wrappers ---------------------------------------------------------------------------------
@@ -57,17 +61,22 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a, uint64_t b, uint32_t idesc, uint32_t accumulate) {
+// The issuing lane's own instruction stream is what bounds these kernels (profiles/r2_mla_*: ~30 scalar instructions of
+// 64-bit descriptor arithmetic per MMA cost more than the MMA), so descriptors travel as two 32-bit halves: the high
+// half (SBO, version, swizzle mode) is a constant, the low half (start address, LBO) takes one 32-bit add per MMA.
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                         uint32_t idesc, uint32_t accumulate) {
   asm volatile(
-      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(d_tmem),
-      "l"(a), "l"(b), "r"(idesc), "r"(accumulate)
+      "{\n.reg .pred p;\n.reg .b64 da, db;\nmov.b64 da, {%1, %2};\nmov.b64 db, {%3, %4};\nsetp.ne.b32 p, %6, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n}\n" ::"r"(d_tmem),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
-// shared-memory matrix descriptor, 128-byte swizzle (layout type 2), descriptor version 1
-__device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  return (uint64_t)((addr & 0x3FFFF) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
-         (1ull << 46) | (2ull << 61);
+// descriptor halves for the 128-byte swizzle: lo = (addr >> 4) | (LBO >> 4) << 16, hi = (SBO >> 4) | version 1 | layout 2
+__device__ __forceinline__ uint32_t desc_lo(uint32_t addr, uint32_t lbo_bytes) {
+  return ((addr & 0x3FFFF) >> 4) | ((lbo_bytes >> 4) << 16);
 }
+constexpr uint32_t kDescHiSw128 = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO = 1024 B (8 rows x 128 B)
 // kind::f16 instruction descriptor: f32 accumulate, A/B element format (0 f16, 1 bf16), A major (0 K, 1 MN), B K-major
 __host__ __device__ constexpr uint32_t idesc_f16(int M, int N, int fmt, int a_mn_major) {
   return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)a_mn_major << 15) |
@@ -128,7 +137,7 @@ __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.
 // ---- shared-memory carve-up ----------------------------------------------------------------------------------
 struct MlaMisc {
   uint64_t full[kMaxSlots], empty[kMaxSlots];
-  uint64_t s_full[2], s_free[2], p_full, p_free, o_full, q_full;
+  uint64_t s_full[2], s_free[2], p_full, p_free, o_full, q_full, q_free, o_free;
   uint32_t tmem_base;
   uint32_t pad[3];
   float mref[64];      // per-head softmax reference, log2 units
@@ -139,35 +148,211 @@ __host__ __device__ constexpr size_t mla_smem_bytes(int NG, int nslots) {
   return 1024 + (size_t)NG * 128 * (kKChunks + 2) + (size_t)nslots * kChunkBytes + sizeof(MlaMisc);
 }
 
+// A segment = consecutive tiles of one (sequence, head group).  Two ways to get them:
+//  * split mode (p.flat == 0): the CTA's one segment comes from blockIdx (sequence, group, token split);
+//  * flat mode  (p.flat == 1): the grid is persistent (one CTA per SM); the list of all (sequence, group, tile)
+//    units is cut into gridDim.x equal ranges and CTA c walks range c, which may end one item, cover several whole
+//    ones and begin another.  Partial items go to the CTA's two partial slots (first / last segment of its range)
+//    and mla_merge_flat_kernel folds them; whole items are written directly.  No wave quantisation, and ragged
+//    batches are balanced by construction.
+struct MlaSeg {
+  int seq, group, tile0, tile1, tiles_seq, L;
+  int slot;      // flat mode: -1 = whole item (direct), else the CTA's partial slot 0 / 1; split mode: unused
+  bool valid;
+};
+
+struct MlaFlatStart {   // computed once per CTA (warp 0), shared through smem
+  long long u0, u1;     // this CTA's unit range (range mode)
+  int seq, group, tile; // position of u0
+  int item_mode;        // 1: whole items dealt round-robin (item c, c + P, ...): no partials; 0: equal unit ranges
+  int sums[160];        // item mode's per-CTA tile totals (scratch for the decision)
+};
+
+__device__ __forceinline__ int mla_tiles_of(int L) { return L > 0 ? (L + kTile - 1) / kTile : 0; }
+
 template <int NG>
-__global__ void __launch_bounds__(kMlaThreads, NG <= 32 ? 2 : 1)
+__global__ void __launch_bounds__(kMlaThreads, 1)
 mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, const __grid_constant__ TmaDesc tm_qn,
                   const __grid_constant__ TmaDesc tm_qp) {
-  // ---- which item ----
-  const int seq = blockIdx.y;
-  const int group = blockIdx.x % p.groups;
-  const int split = blockIdx.x / p.groups;
-  const int L = p.seq_lens[seq];
-  const int t0 = split * p.split_tokens;
-  const int t1 = min(L, t0 + p.split_tokens);
-  const int h0 = group * NG;
-  const int nh = min(NG, p.H - h0);           // real heads of this group
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int nsplit = L > 0 ? (L + p.split_tokens - 1) / p.split_tokens : 1;
-  if (L <= 0) {  // empty sequence: zeros and lse = -inf, written by the split-0 CTAs
-    if (split == 0) {
-      for (int i = tid; i < nh * 512; i += kMlaThreads) {
-        const long long o = (long long)seq * p.out_seq_stride + (long long)(h0 + i / 512) * p.out_head_stride + i % 512;
+  __shared__ MlaFlatStart fstart;
+  if (!p.flat) {
+    const int seq = blockIdx.y, group = blockIdx.x % p.groups, split = blockIdx.x / p.groups;
+    const int L = p.seq_lens[seq];
+    if (L <= 0) {  // empty sequence: zeros and lse = -inf, written by the split-0 CTAs
+      if (split == 0) {
+        const int h0 = group * NG, nh = min(NG, p.H - h0);
+        for (int i = tid; i < nh * 512; i += kMlaThreads) {
+          const long long o = (long long)seq * p.out_seq_stride + (long long)(h0 + i / 512) * p.out_head_stride + i % 512;
+          if (p.f16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(0.f);
+          else reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(0.f);
+        }
+        if (p.lse != nullptr && tid < nh) p.lse[(long long)seq * p.lse_stride + h0 + tid] = -INFINITY;
+      }
+      return;
+    }
+    if (split * p.split_tokens >= L) return;
+  }
+  if (p.flat) {
+    // empty sequences never show up in the unit list: their zeros / -inf are written here
+    for (int s = blockIdx.x; s < p.S; s += gridDim.x) {
+      if (p.seq_lens[s] > 0) continue;
+      for (int i = tid; i < p.H * 512; i += kMlaThreads) {
+        const long long o = (long long)s * p.out_seq_stride + (long long)(i / 512) * p.out_head_stride + i % 512;
         if (p.f16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(0.f);
         else reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(0.f);
       }
-      if (p.lse != nullptr && tid < nh) p.lse[(long long)seq * p.lse_stride + h0 + tid] = -INFINITY;
+      if (p.lse != nullptr && tid < p.H) p.lse[(long long)s * p.lse_stride + tid] = -INFINITY;
     }
-    return;
+    // Two ways to deal the work: whole items round-robin (no partial results, but only balanced when the items are
+    // alike) or equal unit ranges (always balanced; items cut across CTAs go through fp32 partials and the merge
+    // kernel, ~10 % extra).  Every CTA evaluates both makespans from seq_lens and picks the same one.
+    for (int i = tid; i < 160; i += kMlaThreads) fstart.sums[i] = 0;
+    __syncthreads();
+    {
+      const int P = min((int)gridDim.x, 160);
+      for (int i = tid; i < p.S * p.groups; i += kMlaThreads) {
+        const int t = mla_tiles_of(p.seq_lens[i / p.groups]);
+        if (t > 0) atomicAdd(&fstart.sums[i % P], t);
+      }
+    }
+    __syncthreads();
+    if (warp == 0) {
+      // W = groups * sum of tiles; this CTA's range; where it starts.  (CTA 0 also leaves the per-sequence prefix, W and
+      // the mode in the workspace header for the merge kernel.)
+      long long run = 0;
+      long long W = 0;
+      for (int s0 = 0; s0 < p.S; s0 += 32) {
+        const int s = s0 + lane;
+        long long v = s < p.S ? (long long)mla_tiles_of(p.seq_lens[s]) * p.groups : 0;
+        long long inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const long long up = __shfl_up_sync(0xffffffffu, inc, o);
+          if (lane >= o) inc += up;
+        }
+        if (blockIdx.x == 0 && s < p.S) p.flat_prefix[s] = run + inc - v;
+        run += __shfl_sync(0xffffffffu, inc, 31);
+      }
+      W = run;
+      int worst = 0;
+      for (int c = lane; c < min((int)gridDim.x, 160); c += 32) worst = max(worst, fstart.sums[c]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) worst = max(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+      const long long quota = (W + gridDim.x - 1) / gridDim.x;
+      // partials cost in proportion to the group width: accept 3 % (16 heads) .. 15 % (64 heads) + 2 tiles of imbalance
+      const int slack = NG == 64 ? 15 : (NG == 32 ? 8 : 3);
+      const int item_mode = gridDim.x <= 160 && (long long)worst * 100 <= quota * (100 + slack) + 200;
+      if (blockIdx.x == 0 && lane == 0) {
+        p.flat_prefix[p.S] = W;
+        p.flat_prefix[p.S + 1] = item_mode;
+      }
+      if (lane == 0) fstart.item_mode = item_mode;
+      if (item_mode) {
+        // first non-empty item of this CTA: items c, c + P, ... in (sequence, group) order
+        int it = blockIdx.x;
+        const int n_items = p.S * p.groups;
+        while (it < n_items && p.seq_lens[it / p.groups] <= 0) it += gridDim.x;
+        if (lane == 0) {
+          fstart.u0 = 0, fstart.u1 = it < n_items ? 1 : 0;
+          fstart.seq = it < n_items ? it / p.groups : -1, fstart.group = it < n_items ? it % p.groups : 0, fstart.tile = 0;
+        }
+      } else {
+      const long long u0 = W * blockIdx.x / gridDim.x, u1 = W * (blockIdx.x + 1) / gridDim.x;
+      // locate u0: the sequence whose span contains it
+      int fseq = -1, fgroup = 0, ftile = 0;
+      long long acc = 0;
+      if (u0 < u1) {
+        for (int s0 = 0; s0 < p.S && fseq < 0; s0 += 32) {
+          const int s = s0 + lane;
+          const long long v = s < p.S ? (long long)mla_tiles_of(p.seq_lens[s]) * p.groups : 0;
+          long long inc = v;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const long long up = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += up;
+          }
+          const bool here = v > 0 && acc + inc - v <= u0 && u0 < acc + inc;
+          const unsigned m = __ballot_sync(0xffffffffu, here);
+          if (m != 0) {
+            const int src = __ffs(m) - 1;
+            const long long before = __shfl_sync(0xffffffffu, acc + inc - v, src);
+            const long long span = __shfl_sync(0xffffffffu, v, src);
+            fseq = s0 + src;
+            const int ts = (int)(span / p.groups);
+            fgroup = (int)((u0 - before) / ts);
+            ftile = (int)((u0 - before) % ts);
+          }
+          acc += __shfl_sync(0xffffffffu, inc, 31);
+        }
+      }
+      if (lane == 0) {
+        fstart.u0 = u0, fstart.u1 = u1;
+        fstart.seq = fseq, fstart.group = fgroup, fstart.tile = ftile;
+      }
+      }
+    }
+    __syncthreads();
+    if (fstart.u0 >= fstart.u1) return;   // more CTAs than units
   }
-  if (t0 >= t1) return;
-  const int T = (t1 - t0 + kTile - 1) / kTile;
+  // the segment walk: every role runs the same deterministic sequence
+  auto first_seg = [&]() {
+    MlaSeg g;
+    if (!p.flat) {
+      g.seq = blockIdx.y, g.group = blockIdx.x % p.groups;
+      g.L = p.seq_lens[g.seq];
+      g.tiles_seq = mla_tiles_of(g.L);
+      const int split = blockIdx.x / p.groups;
+      g.tile0 = split * (p.split_tokens / kTile);
+      g.tile1 = min(g.tiles_seq, g.tile0 + p.split_tokens / kTile);
+      g.slot = split;
+      g.valid = g.tile0 < g.tile1;
+      return g;
+    }
+    g.seq = fstart.seq, g.group = fstart.group;
+    g.L = p.seq_lens[g.seq];
+    g.tiles_seq = mla_tiles_of(g.L);
+    if (fstart.item_mode) {
+      g.tile0 = 0, g.tile1 = g.tiles_seq, g.slot = -1, g.valid = true;
+      return g;
+    }
+    g.tile0 = fstart.tile;
+    g.tile1 = (int)min((long long)g.tiles_seq, g.tile0 + (fstart.u1 - fstart.u0));
+    g.slot = (g.tile0 == 0 && g.tile1 == g.tiles_seq) ? -1 : 0;
+    g.valid = true;
+    return g;
+  };
+  // `done` = units consumed so far by this CTA (flat mode)
+  auto next_seg = [&](MlaSeg g, long long& done) {
+    if (!p.flat) { g.valid = false; return g; }
+    if (fstart.item_mode) {
+      int it = g.seq * p.groups + g.group;
+      const int n_items = p.S * p.groups;
+      do { it += gridDim.x; } while (it < n_items && p.seq_lens[it / p.groups] <= 0);
+      if (it >= n_items) { g.valid = false; return g; }
+      g.seq = it / p.groups, g.group = it % p.groups;
+      g.L = p.seq_lens[g.seq];
+      g.tiles_seq = mla_tiles_of(g.L);
+      g.tile0 = 0, g.tile1 = g.tiles_seq, g.slot = -1;
+      return g;
+    }
+    done += g.tile1 - g.tile0;
+    const long long left = (fstart.u1 - fstart.u0) - done;
+    if (left <= 0) { g.valid = false; return g; }
+    if (g.tile1 < g.tiles_seq) { g.valid = false; return g; }   // cannot happen: a segment only stops early at the range end
+    if (++g.group == p.groups) {
+      g.group = 0;
+      do { ++g.seq; g.L = p.seq_lens[g.seq]; } while (g.L <= 0);
+      g.tiles_seq = mla_tiles_of(g.L);
+    }
+    g.tile0 = 0;
+    g.tile1 = (int)min((long long)g.tiles_seq, left);
+    g.slot = g.tile1 == g.tiles_seq ? -1 : 1;
+    return g;
+  };
 
+  long long cta_t0 = 0;
+  if (p.cta_times != nullptr && tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cta_t0));
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* const base_ptr = smem_raw + (base - smem_u32(smem_raw));
@@ -191,9 +376,10 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     mbar_init(smem_u32(&misc->p_free), 1);
     mbar_init(smem_u32(&misc->o_full), 1);
     mbar_init(smem_u32(&misc->q_full), 1);
+    mbar_init(smem_u32(&misc->q_free), 1);               // the segment's last S^T product has read the query
+    mbar_init(smem_u32(&misc->o_free), kSoftmaxThreads); // the segment's O^T has been read out
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (tid < 64) misc->mref[tid] = -INFINITY;
   constexpr uint32_t kCols = NG == 64 ? 512 : (NG == 32 ? 256 : 128);  // power of two >= 6 * NG
   if (warp == kMmaWarp) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&misc->tmem_base)),
@@ -207,8 +393,8 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   const uint32_t tmem = misc->tmem_base;
   const uint32_t tm_s[2] = {tmem, tmem + NG};
   const uint32_t tm_o = tmem + 2 * NG;
-  // development timeline (tools/mla_debug.py --timeline): clock64 stamps of CTA 0, [role][tile][4], after the logits
-  long long* const stamps = (p.debug_logits != nullptr && blockIdx.x == 0 && blockIdx.y == 0)
+  // development timeline (tools/mla_debug.py --timeline): clock64 stamps of CTA 0's first segment, [role][tile][4]
+  long long* const stamps = (p.debug_logits != nullptr && blockIdx.x == p.stamp_cta && blockIdx.y == 0)
                                 ? reinterpret_cast<long long*>(p.debug_logits + 128 * 64) : nullptr;
   auto stamp = [&](int role, int tile, int k) {
     if (stamps != nullptr && tile < 64) stamps[(role * 64 + tile) * 4 + k] = clock64();
@@ -217,67 +403,68 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   // Ring protocol: the ring is npairs pairs of 16 KiB chunks.  A pair has ONE full barrier (two producer arrivals,
   // each announcing its chunk's bytes) and ONE empty barrier (one tcgen05.commit), so the MMA lane pays one wait and
   // one commit per 32 KiB.  Per tile: 5 K pairs (chunks 0..8 + an unused half) for S^T, then 4 V pairs for O^T.
+  // Tile-indexed barriers (S^T buffers, P^T) run on a tile counter that continues across segments; segment-indexed
+  // ones (query, O^T) on the segment counter.
   const int npairs = nslots >> 1;
   if (warp > kMmaWarp) {
     // =================== TMA producers: half-pair f of the ring sequence is filled by producer f % kProducers ===================
     const int pw = warp - kMmaWarp - 1;
     if (lane == 0) {
-      if (pw == 0) {
-        // query group: 8 latent chunks + the rope chunk, heads beyond H zero-filled by the tensor map bounds
-        mbar_expect_tx(smem_u32(&misc->q_full), (uint32_t)(kKChunks * NG * 128));
-        for (int c = 0; c < kVChunks; ++c) tma_load_3d(q_u32 + c * NG * 128, &tm_qn, c * 64, h0, seq, smem_u32(&misc->q_full));
-        tma_load_3d(q_u32 + kVChunks * NG * 128, &tm_qp, 0, h0, seq, smem_u32(&misc->q_full));
-      }
-      const int32_t* table = p.page_table + (long long)seq * p.page_table_stride;
       const int box_rows = p.box_rows;
       const uint32_t box_bytes = (uint32_t)box_rows * 128u;
       int pair = 0, turn = 0;
       uint32_t phase = 0;  // parity of the ring pass
-      // halves 0 .. nhalves-1 of the tile starting at token tok0: chunk index = half (the 10th K half is left unused)
-      auto load_halves = [&](int tok0, int nhalves, int nchunks) {
-        const int valid = min(kTile, L - tok0);                  // rows of this tile that hold cache entries
-        const int vbox = (valid + box_rows - 1) / box_rows;
-        int page[8], row[8];
-#pragma unroll
-        for (int b = 0; b < 8; ++b) {
-          if (b < vbox) {
-            const int tok = tok0 + b * box_rows;
-            page[b] = table[tok >> p.page_shift];
-            row[b] = tok & (p.page_size - 1);
-          }
+      long long done = 0;
+      int nseg = 0;
+      for (MlaSeg g = first_seg(); g.valid; g = next_seg(g, done), ++nseg) {
+        const int L = g.L, t0 = g.tile0 * kTile, T = g.tile1 - g.tile0;
+        if (pw == 0) {
+          // query group: 8 latent chunks + the rope chunk, heads beyond H zero-filled by the tensor map bounds
+          if (nseg > 0) mbar_wait(smem_u32(&misc->q_free), (nseg - 1) & 1);
+          mbar_expect_tx(smem_u32(&misc->q_full), (uint32_t)(kKChunks * NG * 128));
+          for (int c = 0; c < kVChunks; ++c)
+            tma_load_3d(q_u32 + c * NG * 128, &tm_qn, c * 64, g.group * NG, g.seq, smem_u32(&misc->q_full));
+          tma_load_3d(q_u32 + kVChunks * NG * 128, &tm_qp, 0, g.group * NG, g.seq, smem_u32(&misc->q_full));
         }
-        for (int c = 0; c < nhalves; ++c) {
-          if (turn == pw) {
-            mbar_wait(smem_u32(&misc->empty[pair]), phase ^ 1);
-            const uint32_t full = smem_u32(&misc->full[pair]);
-            if (c < nchunks) {
-              mbar_expect_tx(full, box_bytes * (uint32_t)vbox);
-              const uint32_t dst = ring_u32 + (uint32_t)(2 * pair + (c & 1)) * kChunkBytes;
+        const int32_t* table = p.page_table + (long long)g.seq * p.page_table_stride;
+        // halves 0 .. nhalves-1 of the tile starting at token tok0: chunk index = half (the 10th K half is left unused)
+        auto load_halves = [&](int tok0, int nhalves, int nchunks) {
+          const int valid = min(kTile, L - tok0);                  // rows of this tile that hold cache entries
+          const int vbox = (valid + box_rows - 1) / box_rows;
+          int page[8], row[8];
 #pragma unroll
-              for (int b = 0; b < 8; ++b)
-                if (b < vbox) tma_load_3d(dst + b * box_bytes, &tm_kv, c * 64, row[b], page[b], full);
-            } else {
-              mbar_arrive(full);
+          for (int b = 0; b < 8; ++b) {
+            if (b < vbox) {
+              const int tok = tok0 + b * box_rows;
+              page[b] = table[tok >> p.page_shift];
+              row[b] = tok & (p.page_size - 1);
             }
           }
-          if (++turn == kProducers) turn = 0;
-          if (c & 1) {
-            if (++pair == npairs) { pair = 0; phase ^= 1; }
+          for (int c = 0; c < nhalves; ++c) {
+            if (turn == pw) {
+              mbar_wait(smem_u32(&misc->empty[pair]), phase ^ 1);
+              const uint32_t full = smem_u32(&misc->full[pair]);
+              if (c < nchunks) {
+                mbar_expect_tx(full, box_bytes * (uint32_t)vbox);
+                const uint32_t dst = ring_u32 + (uint32_t)(2 * pair + (c & 1)) * kChunkBytes;
+#pragma unroll
+                for (int b = 0; b < 8; ++b)
+                  if (b < vbox) tma_load_3d(dst + b * box_bytes, &tm_kv, c * 64, row[b], page[b], full);
+              } else {
+                mbar_arrive(full);
+              }
+            }
+            if (++turn == kProducers) turn = 0;
+            if (c & 1) {
+              if (++pair == npairs) { pair = 0; phase ^= 1; }
+            }
           }
+        };
+        load_halves(t0, 10, kKChunks);
+        for (int i = 0; i < T; ++i) {
+          if (i + 1 < T) load_halves(t0 + (i + 1) * kTile, 10, kKChunks);
+          load_halves(t0 + i * kTile, 8, kVChunks);
         }
-      };
-      if (pw == 0) stamp(2, 0, 0);
-      load_halves(t0, 10, kKChunks);
-      if (pw == 0) stamp(2, 0, 1);
-      for (int i = 0; i < T; ++i) {
-        if (i + 1 < T) {
-          if (pw == 0) stamp(2, i + 1, 0);
-          load_halves(t0 + (i + 1) * kTile, 10, kKChunks);
-          if (pw == 0) stamp(2, i + 1, 1);
-        }
-        if (pw == 0) stamp(2, i, 2);
-        load_halves(t0 + i * kTile, 8, kVChunks);
-        if (pw == 0) stamp(2, i, 3);
       }
     }
   } else if (warp == kMmaWarp) {
@@ -294,83 +481,96 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
       long long acc[4] = {0, 0, 0, 0}, tmark = 0;   // development: cycles in waits / S issue / PV issue / commits
       auto tick = [&]() { if (stamps != nullptr) tmark = clock64(); };
       auto tock = [&](int k) { if (stamps != nullptr) acc[k] += clock64() - tmark; };
-      const uint64_t q_desc = smem_desc_sw128(q_u32, 0, 1024);
-      const uint64_t p_desc = smem_desc_sw128(p_u32, 0, 1024);
-      mbar_wait(smem_u32(&misc->q_full), 0);
-      auto issue_s = [&](int i) {
-        const int b = i & 1;
-        if (i >= 2) mbar_wait(smem_u32(&misc->s_free[b]), ((i >> 1) & 1) ^ 1);
-        tc_fence_after();
-        stamp(0, i, 0);
-        for (int c2 = 0; c2 < 5; ++c2) {
-          tick();
-          mbar_wait(smem_u32(&misc->full[pair]), phase);
+      const uint32_t q_lo = desc_lo(q_u32, 0), p_lo = desc_lo(p_u32, 0);
+      long long done = 0;
+      int nseg = 0;
+      int gt = 0;   // tile counter across segments
+      for (MlaSeg g = first_seg(); g.valid; g = next_seg(g, done), ++nseg) {
+        const int t0 = g.tile0 * kTile, t1 = min(g.L, g.tile1 * kTile), T = g.tile1 - g.tile0;
+        const int gt0 = gt;
+        mbar_wait(smem_u32(&misc->q_full), nseg & 1);
+        auto issue_s = [&](int i) {
+          const int x = gt0 + i, b = x & 1;
+          if (x >= 2) mbar_wait(smem_u32(&misc->s_free[b]), ((x >> 1) & 1) ^ 1);
           tc_fence_after();
-          tock(0);
-          const uint64_t a_desc = smem_desc_sw128(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, 0, 1024);
-          tick();
+          stamp(0, x, 0);
+          for (int c2 = 0; c2 < 5; ++c2) {
+            tick();
+            mbar_wait(smem_u32(&misc->full[pair]), phase);
+            tc_fence_after();
+            tock(0);
+            const uint32_t a_lo = desc_lo(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, 0);
+            const uint32_t b_lo = q_lo + (uint32_t)(c2 * 2 * NG * 128 >> 4);
+            tick();
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const int c = 2 * c2 + h;
-            if (c < kKChunks) {
+            for (int h = 0; h < 2; ++h) {
+              if (2 * c2 + h < kKChunks) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
-                umma_f16(tm_s[b], a_desc + (uint64_t)((h * kChunkBytes + k * 32) >> 4),
-                         q_desc + (uint64_t)((c * NG * 128 + k * 32) >> 4), idesc_s, (c | k) != 0);
+                for (int k = 0; k < 4; ++k)
+                  umma_f16(tm_s[b], a_lo + ((h * kChunkBytes + k * 32) >> 4), kDescHiSw128,
+                           b_lo + ((h * NG * 128 + k * 32) >> 4), kDescHiSw128, idesc_s, (c2 | h | k) != 0);
+              }
             }
+            tock(1);
+            tick();
+            umma_commit(smem_u32(&misc->empty[pair]));
+            tock(3);
+            advance();
           }
-          tock(1);
-          tick();
-          umma_commit(smem_u32(&misc->empty[pair]));
-          tock(3);
-          advance();
-        }
-        umma_commit(smem_u32(&misc->s_full[b]));
-        stamp(0, i, 1);
-      };
-      auto issue_pv = [&](int i) {
-        const int rows = min(kTile, t1 - (t0 + i * kTile));   // valid token rows of this tile
-        const int ksteps = (rows + 15) >> 4;
-        const int zero_from = rows, zero_to = ksteps << 4;     // rows of the last K step that are past the sequence
-        mbar_wait(smem_u32(&misc->p_full), i & 1);
-        tc_fence_after();
-        stamp(0, i, 2);
-        for (int j = 0; j < 4; ++j) {
-          tick();
-          mbar_wait(smem_u32(&misc->full[pair]), phase);
+          umma_commit(smem_u32(&misc->s_full[b]));
+          if (i == T - 1) umma_commit(smem_u32(&misc->q_free));   // the query buffer may be reloaded once this is done
+          stamp(0, gt0 + i, 1);
+        };
+        auto issue_pv = [&](int i) {
+          const int x = gt0 + i;
+          const int rows = min(kTile, t1 - (t0 + i * kTile));   // valid token rows of this tile
+          const int ksteps = (rows + 15) >> 4;
+          const int zero_from = rows, zero_to = ksteps << 4;     // rows of the last K step that are past the sequence
+          mbar_wait(smem_u32(&misc->p_full), x & 1);
+          if (i == 0 && nseg > 0) mbar_wait(smem_u32(&misc->o_free), (nseg - 1) & 1);  // previous O^T has been read out
           tc_fence_after();
-          tock(0);
-          const uint32_t a_addr = ring_u32 + (uint32_t)pair * 2 * kChunkBytes;
-          if (zero_from < zero_to) {
-            // V rows past the sequence end may hold anything (0 * NaN = NaN): zero them before the tensor core reads
-            for (int hlf = 0; hlf < 2; ++hlf)
-              for (int u = zero_from * 8; u < zero_to * 8; ++u)
-                *reinterpret_cast<uint4*>(ring_ptr + (size_t)(2 * pair + hlf) * kChunkBytes + (size_t)u * 16) = make_uint4(0, 0, 0, 0);
-            fence_async_smem();
+          stamp(0, x, 2);
+          for (int j = 0; j < 4; ++j) {
+            tick();
+            mbar_wait(smem_u32(&misc->full[pair]), phase);
+            tc_fence_after();
+            tock(0);
+            const uint32_t a_addr = ring_u32 + (uint32_t)pair * 2 * kChunkBytes;
+            if (zero_from < zero_to) {
+              // V rows past the sequence end may hold anything (0 * NaN = NaN): zero them before the tensor core reads
+              for (int hlf = 0; hlf < 2; ++hlf)
+                for (int u = zero_from * 8; u < zero_to * 8; ++u)
+                  *reinterpret_cast<uint4*>(ring_ptr + (size_t)(2 * pair + hlf) * kChunkBytes + (size_t)u * 16) = make_uint4(0, 0, 0, 0);
+              fence_async_smem();
+            }
+            const uint32_t a_lo = desc_lo(a_addr, kChunkBytes);
+            const uint32_t d_o = tm_o + j * NG;
+            tick();
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks)
+              if (ks < ksteps)
+                umma_f16(d_o, a_lo + ((ks * 2048) >> 4), kDescHiSw128,
+                         p_lo + (((ks >> 2) * NG * 128 + (ks & 3) * 32) >> 4), kDescHiSw128, idesc_o, (i | ks) != 0);
+            tock(2);
+            tick();
+            umma_commit(smem_u32(&misc->empty[pair]));
+            tock(3);
+            advance();
           }
-          const uint64_t a_desc = smem_desc_sw128(a_addr, kChunkBytes, 1024);
-          tick();
-          for (int ks = 0; ks < ksteps; ++ks)
-            umma_f16(tm_o + j * NG, a_desc + (uint64_t)((ks * 2048) >> 4),
-                     p_desc + (uint64_t)(((ks >> 2) * NG * 128 + (ks & 3) * 32) >> 4), idesc_o, (i | ks) != 0);
-          tock(2);
-          tick();
-          umma_commit(smem_u32(&misc->empty[pair]));
-          tock(3);
-          advance();
+          umma_commit(smem_u32(&misc->p_free));
+          stamp(0, x, 3);
+        };
+        issue_s(0);
+        for (int i = 0; i < T; ++i) {
+          if (i + 1 < T) issue_s(i + 1);
+          issue_pv(i);
         }
-        umma_commit(smem_u32(&misc->p_free));
-        stamp(0, i, 3);
-      };
-      issue_s(0);
-      for (int i = 0; i < T; ++i) {
-        if (i + 1 < T) issue_s(i + 1);
-        issue_pv(i);
-      }
-      umma_commit(smem_u32(&misc->o_full));
-      if (stamps != nullptr) {
-        for (int k = 0; k < 4; ++k) stamps[(0 * 64 + 63) * 4 + k] = acc[k];
-        stamps[(1 * 64 + 63) * 4 + 0] = T;
+        umma_commit(smem_u32(&misc->o_full));
+        gt += T;
+        if (nseg == 0 && stamps != nullptr) {
+          for (int k = 0; k < 4; ++k) stamps[(0 * 64 + 63) * 4 + k] = acc[k];
+          stamps[(1 * 64 + 63) * 4 + 0] = T;
+        }
       }
     }
     __syncwarp();
@@ -380,17 +580,26 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     const int row = quad * 32 + lane;            // token row within the tile / dv row within an O^T block
     const int st = tid;                          // 0..127
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    constexpr int HC = NG < 32 ? NG : 32;        // columns handled per pass (register budget)
+    long long done = 0;
+    int nseg = 0;
+    int gt = 0;   // tile counter across segments
+    for (MlaSeg g = first_seg(); g.valid; g = next_seg(g, done), ++nseg) {
+    const int t0 = g.tile0 * kTile, t1 = min(g.L, g.tile1 * kTile), T = g.tile1 - g.tile0;
+    const int h0 = g.group * NG;
+    const int nh = min(NG, p.H - h0);           // real heads of this group
     float lsum[NG];
 #pragma unroll
     for (int h = 0; h < NG; ++h) lsum[h] = 0.f;
+    if (st < 64) misc->mref[st] = -INFINITY;
+    softmax_bar_sync();
 
-    constexpr int HC = NG < 32 ? NG : 32;        // columns handled per pass (register budget)
-    for (int i = 0; i < T; ++i) {
-      const int b = i & 1;
-      mbar_wait(smem_u32(&misc->s_full[b]), (i >> 1) & 1);
+    for (int i = 0; i < T; ++i, ++gt) {
+      const int b = gt & 1;
+      mbar_wait(smem_u32(&misc->s_full[b]), (gt >> 1) & 1);
       tc_fence_after();
       const bool valid = t0 + i * kTile + row < t1;
-      if (tid == 0) stamp(1, i, 0);
+      if (tid == 0) stamp(1, gt, 0);
       // ---- pass 1: does any logit pass its reference by kTau?  (S^T is read again in pass 2: TMEM reads are cheap) ----
       bool over = false;
 #pragma unroll
@@ -398,7 +607,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
         uint32_t r[HC];
         tmem_ld<HC>(tm_s[b] + c0 + lane_base, r);
         tmem_ld_wait();
-        if (p.debug_logits != nullptr && i == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
+        if (p.debug_logits != nullptr && i == 0 && nseg == 0 && blockIdx.x == 0 && blockIdx.y == 0) {
 #pragma unroll
           for (int h = 0; h < HC; ++h) p.debug_logits[row * 64 + c0 + h] = __uint_as_float(r[h]);
         }
@@ -433,7 +642,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
 #pragma unroll
         for (int h = 0; h < NG; ++h) lsum[h] *= misc->fac[h];
         if (i > 0) {
-          mbar_wait(smem_u32(&misc->p_free), (i - 1) & 1);  // P.V of the previous tile has landed in O^T
+          mbar_wait(smem_u32(&misc->p_free), (gt - 1) & 1);  // P.V of the previous tile has landed in O^T
           tc_fence_after();
           for (int j = 0; j < 4; ++j) {
 #pragma unroll
@@ -450,7 +659,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           tc_fence_before();
         }
       }
-      if (tid == 0) stamp(1, i, 1);
+      if (tid == 0) stamp(1, gt, 1);
       // ---- pass 2: p = 2^(x - m_ref); 16-bit values into the P^T operand, fp32 into the running sums ----
       // P^T[h][token]: K-major SW128, chunk = row / 64, 16-byte unit (row % 64) / 8 XOR (h % 8)
       const uint32_t chunk = p_u32 + (row >> 6) * NG * 128;
@@ -471,8 +680,8 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           lsum[c0 + h] += pv;
           r[h] = p.f16 ? (uint32_t)__half_as_ushort(__float2half_rn(pv)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(pv));
         }
-        if (c0 == 0 && i > 0) mbar_wait(smem_u32(&misc->p_free), (i - 1) & 1);
-        if (c0 == 0 && tid == 0) stamp(1, i, 2);
+        if (c0 == 0 && gt > 0) mbar_wait(smem_u32(&misc->p_free), (gt - 1) & 1);
+        if (c0 == 0 && tid == 0) stamp(1, gt, 2);
 #pragma unroll
         for (int h = 0; h < HC; ++h) {
           const uint32_t addr = chunk + (c0 + h) * 128 + ((unit ^ (h & 7)) << 4) + within;
@@ -481,62 +690,146 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
       }
       fence_async_smem();
       mbar_arrive(smem_u32(&misc->p_full));
-      if (tid == 0) stamp(1, i, 3);
+      if (tid == 0) stamp(1, gt, 3);
     }
 
-    // ---- epilogue: reduce the per-thread row sums over the 128 token rows, normalise O^T, store ----
-    mbar_wait(smem_u32(&misc->o_full), 0);   // every MMA (hence every ring read) is complete: the ring is scratch now
+    // ---- epilogue of the segment: reduce the per-thread row sums over the 128 token rows, normalise O^T, store ----
+    if (tid == 0) stamp(2, nseg, 0);
+    mbar_wait(smem_u32(&misc->o_full), nseg & 1);   // every MMA of this segment is complete
     tc_fence_after();
-    float* scratch = reinterpret_cast<float*>(ring_ptr);  // [128][NG + 1]
+    if (tid == 0) stamp(2, nseg, 1);
+    {
+      float* wsum = reinterpret_cast<float*>(&misc->colmax[0][0]);   // [4 warps][64]: per-warp column sums
 #pragma unroll
-    for (int h = 0; h < NG; ++h) scratch[row * (NG + 1) + h] = lsum[h];
-    softmax_bar_sync();
-    const bool direct = nsplit == 1;
+      for (int h = 0; h < NG; ++h) {
+        float v = lsum[h];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) wsum[warp * 64 + h] = v;
+      }
+      softmax_bar_sync();
+      if (st < NG) misc->fac[st] = wsum[st] + wsum[64 + st] + wsum[128 + st] + wsum[192 + st];
+      softmax_bar_sync();
+    }
+    if (tid == 0) stamp(2, nseg, 2);
+    const bool direct = g.tile0 == 0 && g.tile1 == g.tiles_seq;
+    // where a partial goes: split mode [seq][head][split], flat mode [cta][slot][head of the group]
+    const long long part_row = p.flat ? ((long long)blockIdx.x * 2 + g.slot) * NG : 0;
     if (st < NG) {
-      float l = 0.f;
-      for (int t = 0; t < kTile; ++t) l += scratch[t * (NG + 1) + st];
-      misc->fac[st] = 1.f / l;
+      const float l = misc->fac[st];
       if (st < nh) {
         const float lse = (misc->mref[st] + log2f(l)) * kLn2;
         if (direct) {
-          if (p.lse != nullptr) p.lse[(long long)seq * p.lse_stride + h0 + st] = lse;
+          if (p.lse != nullptr) p.lse[(long long)g.seq * p.lse_stride + h0 + st] = lse;
+        } else if (p.flat) {
+          p.part_lse[part_row + st] = lse;
         } else {
-          p.part_lse[((long long)seq * p.H + h0 + st) * p.max_splits + split] = lse;
+          p.part_lse[((long long)g.seq * p.H + h0 + st) * p.max_splits + g.slot] = lse;
         }
       }
     }
     softmax_bar_sync();
-    for (int j = 0; j < 4; ++j) {
-      const int dv = j * 128 + row;
+    if (st < NG) misc->fac[st] = 1.f / misc->fac[st];
+    softmax_bar_sync();
+    // O^T -> global: one base pointer and one stride per mode, chosen once (the per-element form of this loop, with
+    // its 64-bit index arithmetic and mode branches, took 50-90 k cycles per segment)
+    {
+      auto store_all = [&](auto put) {
+        for (int j = 0; j < 4; ++j) {
+          const int dv = j * 128 + row;
 #pragma unroll
-      for (int c = 0; c < NG; c += 16) {
-        uint32_t o[16];
-        tmem_ld<16>(tm_o + j * NG + c + lane_base, o);
-        tmem_ld_wait();
+          for (int c = 0; c < NG; c += 16) {
+            uint32_t o[16];
+            tmem_ld<16>(tm_o + j * NG + c + lane_base, o);
+            tmem_ld_wait();
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
-          const int h = c + e;
-          if (h < nh) {
-            const float v = __uint_as_float(o[e]) * misc->fac[h];
-            if (direct) {
-              const long long off = (long long)seq * p.out_seq_stride + (long long)(h0 + h) * p.out_head_stride + dv;
-              if (p.f16) reinterpret_cast<__half*>(p.out)[off] = __float2half_rn(v);
-              else reinterpret_cast<__nv_bfloat16*>(p.out)[off] = __float2bfloat16_rn(v);
-            } else {
-              p.part_out[(((long long)seq * p.H + h0 + h) * p.max_splits + split) * 512 + dv] = v;
-            }
+            for (int e = 0; e < 16; ++e)
+              if (c + e < nh) put(c + e, dv, __uint_as_float(o[e]) * misc->fac[c + e]);
           }
         }
+      };
+      if (direct) {
+        const long long hs = p.out_head_stride;
+        if (p.f16) {
+          __half* ob = reinterpret_cast<__half*>(p.out) + (long long)g.seq * p.out_seq_stride + (long long)h0 * hs;
+          store_all([&](int h, int dv, float v) { ob[h * hs + dv] = __float2half_rn(v); });
+        } else {
+          __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)g.seq * p.out_seq_stride + (long long)h0 * hs;
+          store_all([&](int h, int dv, float v) { ob[h * hs + dv] = __float2bfloat16_rn(v); });
+        }
+      } else {
+        float* pb = p.flat ? p.part_out + part_row * 512
+                           : p.part_out + (((long long)g.seq * p.H + h0) * p.max_splits + g.slot) * 512;
+        const long long hs = p.flat ? 512 : (long long)p.max_splits * 512;
+        store_all([&](int h, int dv, float v) { pb[h * hs + dv] = v; });
       }
     }
     tc_fence_before();
+    if (tid == 0) stamp(2, nseg, 3);
+    mbar_arrive(smem_u32(&misc->o_free));   // O^T may be overwritten by the next segment
+    softmax_bar_sync();                      // fac / mref / the scratch are reused by the next segment
+    }
   }
 
   __syncthreads();
+  if (p.cta_times != nullptr && tid == 0) {
+    long long t1g;
+    uint32_t smid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1g));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    long long* rec = p.cta_times + ((long long)blockIdx.y * gridDim.x + blockIdx.x) * 3;
+    rec[0] = cta_t0, rec[1] = t1g, rec[2] = smid;
+  }
   if (warp == kMmaWarp) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kCols) : "memory");
   }
+}
+
+// flat mode: fold the partial slots of every item that more than one CTA worked on.  The decode kernel's CTA 0 left
+// the per-sequence unit prefix (and the total) in the workspace header; CTA c's range is [c W / P, (c + 1) W / P).
+__global__ void __launch_bounds__(128) mla_merge_flat_kernel(const MlaParams p, int P, int NG) {
+  const int seq = blockIdx.y, h = blockIdx.x;
+  const int L = p.seq_lens[seq];
+  if (L <= 0) return;
+  const int tiles = mla_tiles_of(L);
+  const int group = h / NG, hl = h % NG;
+  const long long W = p.flat_prefix[p.S];
+  if (p.flat_prefix[p.S + 1] != 0) return;   // item mode: every item was written directly
+  const long long a = p.flat_prefix[seq] + (long long)group * tiles, b = a + tiles;
+  auto cta_of = [&](long long u) { return (int)(((u + 1) * P + W - 1) / W - 1); };   // the c with c W / P <= u < (c + 1) W / P
+  const int c_lo = cta_of(a), c_hi = cta_of(b - 1);
+  if (c_lo == c_hi) return;   // one CTA had the whole item and wrote it directly
+  float m = -INFINITY;
+  for (int c = c_lo; c <= c_hi; ++c) {
+    if (W * c / P == W * (c + 1) / P) continue;  // a CTA without units (more CTAs than units)
+    const int slot = (W * c / P >= a) ? 0 : 1;   // the item continues from the CTA's range start (slot 0) or ends its range (slot 1)
+    m = fmaxf(m, p.part_lse[((long long)c * 2 + slot) * NG + hl]);
+  }
+  float denom = 0.f;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int c = c_lo; c <= c_hi; ++c) {
+    if (W * c / P == W * (c + 1) / P) continue;
+    const int slot = (W * c / P >= a) ? 0 : 1;
+    const long long rowi = ((long long)c * 2 + slot) * NG + hl;
+    const float w = __expf(p.part_lse[rowi] - m);
+    denom += w;
+    const float4 v = reinterpret_cast<const float4*>(p.part_out + rowi * 512)[threadIdx.x];
+    acc.x += w * v.x, acc.y += w * v.y, acc.z += w * v.z, acc.w += w * v.w;
+  }
+  const float inv = 1.f / denom;
+  acc.x *= inv, acc.y *= inv, acc.z *= inv, acc.w *= inv;
+  const long long off = (long long)seq * p.out_seq_stride + (long long)h * p.out_head_stride + threadIdx.x * 4;
+  if (p.f16) {
+    __half2* o = reinterpret_cast<__half2*>(reinterpret_cast<__half*>(p.out) + off);
+    o[0] = __floats2half2_rn(acc.x, acc.y);
+    o[1] = __floats2half2_rn(acc.z, acc.w);
+  } else {
+    __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off);
+    o[0] = __floats2bfloat162_rn(acc.x, acc.y);
+    o[1] = __floats2bfloat162_rn(acc.z, acc.w);
+  }
+  if (p.lse != nullptr && threadIdx.x == 0) p.lse[(long long)seq * p.lse_stride + h] = m + __logf(denom);
 }
 
 // =====================================================================================================================
@@ -610,10 +903,12 @@ __device__ __forceinline__ void st_cluster_u16(uint32_t cluster_addr, uint16_t v
 __device__ __forceinline__ void st_cluster_u32(uint32_t cluster_addr, uint32_t v) {
   asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(cluster_addr), "r"(v) : "memory");
 }
-__device__ __forceinline__ void umma_f16_2sm(uint32_t d_tmem, uint64_t a, uint64_t b, uint32_t idesc, uint32_t accumulate) {
+__device__ __forceinline__ void umma_f16_2sm(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                             uint32_t idesc, uint32_t accumulate) {
   asm volatile(
-      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(d_tmem),
-      "l"(a), "l"(b), "r"(idesc), "r"(accumulate)
+      "{\n.reg .pred p;\n.reg .b64 da, db;\nmov.b64 da, {%1, %2};\nmov.b64 db, {%3, %4};\nsetp.ne.b32 p, %6, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %5, p;\n}\n" ::"r"(d_tmem),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
 // arrives (once all MMAs issued so far are complete) on the barrier at this offset in BOTH CTAs of the pair
@@ -774,7 +1069,7 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
       auto advance = [&]() {
         if (++pair == npairs) { pair = 0; phase ^= 1; }
       };
-      const uint64_t q_desc = smem_desc_sw128(q_u32, 0, 1024);
+      const uint32_t q_lo = desc_lo(q_u32, 0);
       mbar_wait_cluster(smem_u32(&misc->q_full), 0);
       auto issue_s = [&](int u) {
         const int b = u & 1;
@@ -784,15 +1079,15 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
         for (int c2 = 0; c2 < 5; ++c2) {
           mbar_wait_cluster(smem_u32(&misc->full[pair]), phase);
           tc_fence_after();
-          const uint64_t a_desc = smem_desc_sw128(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, 0, 1024);
+          const uint32_t a_lo = desc_lo(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, 0);
+          const uint32_t b_lo = q_lo + (uint32_t)(c2 * 2 * 64 * 128 >> 4);
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
-            const int c = 2 * c2 + h;
-            if (c < kKChunks) {
+            if (2 * c2 + h < kKChunks) {
 #pragma unroll
               for (int k = 0; k < 4; ++k)
-                umma_f16_2sm(tm_s[b], a_desc + (uint64_t)((h * kChunkBytes + k * 32) >> 4),
-                             q_desc + (uint64_t)((c * 64 * 128 + k * 32) >> 4), idesc_s, (c | k) != 0);
+                umma_f16_2sm(tm_s[b], a_lo + ((h * kChunkBytes + k * 32) >> 4), kDescHiSw128,
+                             b_lo + ((h * 64 * 128 + k * 32) >> 4), kDescHiSw128, idesc_s, (c2 | h | k) != 0);
             }
           }
           umma_commit_2sm(smem_u32(&misc->empty[pair]));
@@ -808,7 +1103,7 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
         for (int t = 0; t < 2; ++t) {
           const int rows = max(0, min(kTile, t1 - (t0 + (2 * u + t) * kTile)));   // valid token rows of tile X_t
           const int ksteps = (rows + 15) >> 4;
-          const uint64_t p_desc = smem_desc_sw128(p_u32 + t * 16384, 0, 1024);
+          const uint32_t p_lo = desc_lo(p_u32 + t * 16384, 0);
           for (int j = 0; j < 2; ++j) {
             mbar_wait_cluster(smem_u32(&misc->full[pair]), phase);
             tc_fence_after();
@@ -823,10 +1118,13 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
               asm volatile("fence.acq_rel.cluster;" ::: "memory");
               asm volatile("fence.proxy.async;" ::: "memory");
             }
-            const uint64_t a_desc = smem_desc_sw128(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, kChunkBytes, 1024);
-            for (int ks = 0; ks < ksteps; ++ks)
-              umma_f16_2sm(tm_o + j * 128, a_desc + (uint64_t)((ks * 2048) >> 4),
-                           p_desc + (uint64_t)(((ks >> 2) * 64 * 128 + (ks & 3) * 32) >> 4), idesc_o, (u | t | ks) != 0);
+            const uint32_t a_lo = desc_lo(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, kChunkBytes);
+            const uint32_t d_o = tm_o + j * 128;
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks)
+              if (ks < ksteps)
+                umma_f16_2sm(d_o, a_lo + ((ks * 2048) >> 4), kDescHiSw128,
+                             p_lo + (((ks >> 2) * 64 * 128 + (ks & 3) * 32) >> 4), kDescHiSw128, idesc_o, (u | t | ks) != 0);
             umma_commit_2sm(smem_u32(&misc->empty[pair]));
             advance();
           }
@@ -1048,27 +1346,34 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
       }
     }
     asm volatile("bar.sync 1, 256;" ::: "memory");
-    for (int j = 0; j < 2; ++j) {
-      const int dv = 256 * j + 128 * (int)rank + row;
+    {
+      auto store_all = [&](auto put) {
+        for (int j = 0; j < 2; ++j) {
+          const int dv = 256 * j + 128 * (int)rank + row;
 #pragma unroll
-      for (int c = 0; c < 64; c += 16) {
-        uint32_t o[16];
-        tmem_ld<16>(tm_o + j * 128 + cbase + c + lane_base, o);
-        tmem_ld_wait();
+          for (int c = 0; c < 64; c += 16) {
+            uint32_t o[16];
+            tmem_ld<16>(tm_o + j * 128 + cbase + c + lane_base, o);
+            tmem_ld_wait();
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
-          const int h = cbase + c + e;
-          if (h < p.H) {
-            const float v = __uint_as_float(o[e]) * misc->fac[h];
-            if (direct) {
-              const long long off = (long long)seq * p.out_seq_stride + (long long)h * p.out_head_stride + dv;
-              if (p.f16) reinterpret_cast<__half*>(p.out)[off] = __float2half_rn(v);
-              else reinterpret_cast<__nv_bfloat16*>(p.out)[off] = __float2bfloat16_rn(v);
-            } else {
-              p.part_out[(((long long)seq * p.H + h) * p.max_splits + split) * 512 + dv] = v;
-            }
+            for (int e = 0; e < 16; ++e)
+              if (cbase + c + e < p.H) put(cbase + c + e, dv, __uint_as_float(o[e]) * misc->fac[cbase + c + e]);
           }
         }
+      };
+      if (direct) {
+        const long long hs = p.out_head_stride;
+        if (p.f16) {
+          __half* ob = reinterpret_cast<__half*>(p.out) + (long long)seq * p.out_seq_stride;
+          store_all([&](int h, int dv, float v) { ob[h * hs + dv] = __float2half_rn(v); });
+        } else {
+          __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)seq * p.out_seq_stride;
+          store_all([&](int h, int dv, float v) { ob[h * hs + dv] = __float2bfloat16_rn(v); });
+        }
+      } else {
+        float* pb = p.part_out + ((long long)seq * p.H * p.max_splits + split) * 512;
+        const long long hs = (long long)p.max_splits * 512;
+        store_all([&](int h, int dv, float v) { pb[h * hs + dv] = v; });
       }
     }
     tc_fence_before();
@@ -1154,6 +1459,17 @@ int encode_map3(TmaDesc* out, const void* ptr, bool f16, uint64_t d0, uint64_t d
 
 int mla_group_width(int H) { return H <= 16 ? 16 : (H <= 32 ? 32 : 64); }
 
+// flat (persistent, tile-balanced) schedule of the single-CTA kernel: whenever the caller leaves the split count to us
+bool mla_use_flat(int H, int requested_splits) {
+  static const int off = env_int("B200_MLA_FLAT_OFF");
+  return !off && requested_splits <= 0 && !(H > 64 && !env_int("B200_MLA_PAIR_OFF"));
+}
+uint64_t mla_flat_workspace_bytes(int S, int H) {
+  const int NG = mla_group_width(H);
+  const uint64_t header = ((uint64_t)(S + 2) * sizeof(long long) + 255) / 256 * 256;
+  return header + (uint64_t)device_sm_count() * 2 * NG * (512 + 1) * sizeof(float);
+}
+
 bool mla_use_pair(int H) {   // 65..128 heads: the two-CTA kernel (B200_MLA_PAIR_OFF=1 keeps two independent 64-head groups)
   static const int off = env_int("B200_MLA_PAIR_OFF");
   return H > 64 && !off;
@@ -1169,7 +1485,7 @@ int mla_choose_splits(int S, int H, long long max_seq_len, int requested) {
   if (requested > 1) return (int)min((long long)min(requested, kMaxSplits), max(1LL, tiles));
   const int NG = mla_group_width(H);
   const long long base = pair ? (long long)S : (long long)S * ((H + NG - 1) / NG);
-  int sms = device_sm_count() * ((NG <= 32 && env_int("B200_MLA_OCC2") != 0) ? 2 : 1);  // resident CTAs (or CTA pairs)
+  int sms = device_sm_count();  // resident CTAs (or CTA pairs)
   if (pair) sms /= 2;
   int best = 1;
   double best_cost = 1e30;
@@ -1210,7 +1526,7 @@ int launch_mla(const MlaParams& mp, const TmaDesc& kv, const TmaDesc& qn, const 
   int dev = 0;
   cudaGetDevice(&dev);
   if (configured_device != dev) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 704);
     if (e != cudaSuccess) {
       set_error("mla_decode: cudaFuncSetAttribute(smem) failed: %s", cudaGetErrorString(e));
       return B200_ERR_CUDA;
@@ -1229,6 +1545,7 @@ using namespace b200;
 extern "C" uint64_t b200_mla_decode_workspace_bytes(int32_t num_seqs, int32_t num_heads, int64_t max_seq_len,
                                                     int32_t num_kv_splits) {
   if (num_seqs <= 0 || num_heads <= 0 || max_seq_len <= 0) return 0;
+  if (mla_use_flat(num_heads, num_kv_splits)) return mla_flat_workspace_bytes(num_seqs, num_heads);
   const int splits = mla_choose_splits(num_seqs, num_heads, max_seq_len, num_kv_splits);
   if (splits <= 1) return 0;
   return (uint64_t)num_seqs * num_heads * splits * (512 + 1) * sizeof(float);
@@ -1256,13 +1573,17 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const bool f16 = p.dtype == B200_DTYPE_F16;
   const long long max_len = (long long)p.max_pages * p.page_size;
-  const int splits = mla_choose_splits(p.num_seqs, p.num_heads, max_len, p.num_kv_splits);
+  const bool flat = mla_use_flat(p.num_heads, p.num_kv_splits);
+  const int splits = flat ? 1 : mla_choose_splits(p.num_seqs, p.num_heads, max_len, p.num_kv_splits);
   const int NG = mla_group_width(p.num_heads);
 
   MlaParams mp;
   memset(&mp, 0, sizeof(mp));
   mp.out = p.out, mp.lse = p.lse, mp.seq_lens = p.seq_lens, mp.page_table = p.page_table;
   mp.debug_logits = p.debug_logits;
+  mp.stamp_cta = env_int("B200_MLA_STAMP_CTA");
+  if (p.debug_logits != nullptr && env_int("B200_MLA_CTA_TIMES"))   // tools/mla_debug.py --cta-times: buffer laid out after the stamps
+    mp.cta_times = reinterpret_cast<long long*>(p.debug_logits + 128 * 64 + 3 * 64 * 4 * 2);
   mp.out_seq_stride = p.out_seq_stride, mp.out_head_stride = p.out_head_stride;
   mp.page_table_stride = p.page_table_stride, mp.lse_stride = p.lse_stride;
   mp.scale_log2 = p.scale * kLog2e;
@@ -1276,15 +1597,24 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   const long long tiles = (max_len + unit - 1) / unit;
   mp.split_tokens = (int)((tiles + splits - 1) / splits) * unit;
   mp.f16 = f16 ? 1 : 0;
-  // shared memory: one CTA per SM for 64-head groups; two for the narrow groups (their MMA lanes then hide each
-  // other's barrier waits and commits), each with half of the SM's 228 KiB minus the per-block reservation
-  static const bool occ2 = env_int("B200_MLA_OCC2") != 0;
-  const size_t budget = (NG <= 32 && occ2) ? (233472 / 2 - 1024) : 232448;
+  // shared memory: one CTA per SM (two CTAs per SM for the narrow groups measured slower: less in flight per CTA)
+  const size_t budget = 232448 - 704;  // static shared memory: the flat schedule start record
   int nslots = (int)((budget - 1024 - (size_t)NG * 128 * (kKChunks + 2) - sizeof(MlaMisc)) / kChunkBytes);
   nslots = min(nslots & ~1, kMaxSlots);
   if (pair) nslots = (int)((232448 - 1024 - (size_t)64 * 128 * kKChunks - 3 * 16384 - sizeof(PairMisc)) / kChunkBytes) & ~1;
   mp.nslots = nslots;
-  if (splits > 1) {
+  if (flat) {
+    const uint64_t need = mla_flat_workspace_bytes(p.num_seqs, p.num_heads);
+    B200_REQUIRE(p.workspace != nullptr && p.workspace_bytes >= need, B200_ERR_WORKSPACE,
+                 "mla_decode: the flat schedule needs a workspace of %llu bytes (got %llu)", (unsigned long long)need,
+                 (unsigned long long)p.workspace_bytes);
+    B200_REQUIRE((uintptr_t)p.workspace % 16 == 0, B200_ERR_WORKSPACE, "mla_decode: workspace must be 16-byte aligned");
+    const uint64_t header = ((uint64_t)(p.num_seqs + 2) * sizeof(long long) + 255) / 256 * 256;
+    mp.flat = 1;
+    mp.flat_prefix = static_cast<long long*>(p.workspace);
+    mp.part_out = reinterpret_cast<float*>(static_cast<char*>(p.workspace) + header);
+    mp.part_lse = mp.part_out + (size_t)device_sm_count() * 2 * NG * 512;
+  } else if (splits > 1) {
     const uint64_t need = (uint64_t)p.num_seqs * p.num_heads * splits * (512 + 1) * sizeof(float);
     B200_REQUIRE(p.workspace != nullptr && p.workspace_bytes >= need, B200_ERR_WORKSPACE,
                  "mla_decode: %d token splits need a workspace of %llu bytes (got %llu)", splits, (unsigned long long)need,
@@ -1303,13 +1633,18 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   rc = encode_map3(&qp, p.q_pe, f16, 64, (uint64_t)p.num_heads, (uint64_t)p.num_seqs, p.q_pe_head_stride, p.q_pe_seq_stride,
                    (uint32_t)NG, "q_pe");
   if (rc != B200_OK) return rc;
-  const dim3 grid((unsigned)((pair ? 2 : mp.groups) * splits), (unsigned)p.num_seqs);
+  const dim3 grid = flat ? dim3((unsigned)device_sm_count(), 1)
+                         : dim3((unsigned)((pair ? 2 : mp.groups) * splits), (unsigned)p.num_seqs);
   if (pair) rc = launch_mla_pair(mp, kv, qn, qp, grid, s);
   else if (NG == 16) rc = launch_mla<16>(mp, kv, qn, qp, grid, s);
   else if (NG == 32) rc = launch_mla<32>(mp, kv, qn, qp, grid, s);
   else rc = launch_mla<64>(mp, kv, qn, qp, grid, s);
   if (rc != B200_OK) return rc;
-  if (splits > 1) {
+  if (flat) {
+    mla_merge_flat_kernel<<<dim3((unsigned)p.num_heads, (unsigned)p.num_seqs), 128, 0, s>>>(mp, (int)grid.x, NG);
+    count_launch();
+    rc = check_launch("mla_merge_flat");
+  } else if (splits > 1) {
     mla_merge_kernel<<<dim3((unsigned)p.num_heads, (unsigned)p.num_seqs), 128, 0, s>>>(mp);
     count_launch();
     rc = check_launch("mla_merge");

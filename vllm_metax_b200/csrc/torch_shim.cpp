@@ -812,8 +812,13 @@ void sm100_cutlass_mla_decode(at::Tensor& out, at::Tensor& lse, const at::Tensor
 int64_t sm100_cutlass_mla_get_workspace_size(int64_t max_seq_len, int64_t num_batches, int64_t sm_count,
                                              int64_t num_kv_splits) {
   (void)sm_count;
-  return static_cast<int64_t>(b200_mla_decode_workspace_bytes(static_cast<int32_t>(num_batches), 128, max_seq_len,
-                                                              num_kv_splits <= 0 ? 0 : static_cast<int32_t>(num_kv_splits)));
+  // the head count is not an argument of the stock op: size for whichever kernel the call will pick (<= 64 heads: flat
+  // schedule; 65..128: pair kernel)
+  const int32_t n = num_kv_splits <= 0 ? 0 : static_cast<int32_t>(num_kv_splits);
+  uint64_t need = 0;
+  for (int32_t heads : {16, 32, 64, 128})
+    need = std::max<uint64_t>(need, b200_mla_decode_workspace_bytes(static_cast<int32_t>(num_batches), heads, max_seq_len, n));
+  return static_cast<int64_t>(need);
 }
 
 void fill_gather_params(b200_gather_cache_params_t& p, const at::Tensor& src_cache, const at::Tensor& dst,
