@@ -169,11 +169,10 @@ def test_new_entry_points_validate_on_the_host(native):
     md = native.MlaDecodeParams()
     assert lib.b200_mla_decode(C.byref(md), None) == native.ERR_INVALID_ARGUMENT  # NULL tensors
     assert "null tensor" in lib.b200_last_error().decode()
-    # <= 64 heads with the split count left to the kernel: the flat schedule's two partial slots per SM (+ a header);
-    # 128 heads (pair kernel): splits (hence a workspace) only for one long sequence; an explicit count: [S][H][n][513]
+    # split count left to the kernel: the flat schedule's two partial slots per worker (+ a header) -- workers are the
+    # 148 CTAs with group-wide slots (<= 64 heads) or the 74 CTA pairs with 128-wide slots; an explicit count: [S][H][n][513]
     assert lib.b200_mla_decode_workspace_bytes(296, 64, 4096, 0) == 2560 + 148 * 2 * 64 * 513 * 4
-    assert lib.b200_mla_decode_workspace_bytes(296, 128, 4096, 0) == 0
-    assert lib.b200_mla_decode_workspace_bytes(1, 128, 131072, 0) > 0
+    assert lib.b200_mla_decode_workspace_bytes(296, 128, 4096, 0) == 2560 + 74 * 2 * 128 * 513 * 4
     assert lib.b200_mla_decode_workspace_bytes(1, 128, 131072, 1) == 0
     assert lib.b200_mla_decode_workspace_bytes(2, 16, 4096, 4) == 2 * 16 * 4 * 513 * 4
     assert lib.b200_copy_blocks(None, None, 0, None, 0, 0, None) == 0

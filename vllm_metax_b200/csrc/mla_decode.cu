@@ -169,6 +169,148 @@ struct MlaFlatStart {   // computed once per CTA (warp 0), shared through smem
 };
 
 __device__ __forceinline__ int mla_tiles_of(int L) { return L > 0 ? (L + kTile - 1) / kTile : 0; }
+__device__ __forceinline__ int mla_units_of(int L, int unit) { return L > 0 ? (L + unit - 1) / unit : 0; }
+
+// Flat-schedule prologue, run by every thread of the CTA: zero-fill of empty sequences, the item-mode / range-mode
+// decision and this worker's start position (worker = CTA, or CTA pair; `unit` = tokens per scheduling unit).
+__device__ void mla_flat_prologue(const MlaParams& p, MlaFlatStart& fs, int unit, int groups, int P, int worker,
+                                  int slack_pct, bool header_writer, int tid, int nthreads, int nzero, int zero_rank) {
+  const int warp = tid >> 5, lane = tid & 31;
+  // empty sequences never show up in the unit list: their zeros / -inf are written here
+  for (int s = worker; s < p.S; s += P) {
+    if (p.seq_lens[s] > 0) continue;
+    for (int i = tid + zero_rank * nthreads; i < p.H * 512; i += nzero * nthreads) {
+      const long long o = (long long)s * p.out_seq_stride + (long long)(i / 512) * p.out_head_stride + i % 512;
+      if (p.f16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(0.f);
+      else reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(0.f);
+    }
+    if (p.lse != nullptr && zero_rank == 0 && tid < p.H) p.lse[(long long)s * p.lse_stride + tid] = -INFINITY;
+  }
+  // Two ways to deal the work: whole items round-robin (no partial results, but only balanced when the items are
+  // alike) or equal unit ranges (always balanced; items cut across workers go through fp32 partials and the merge
+  // kernel).  Every worker evaluates both makespans from seq_lens and picks the same one.
+  for (int i = tid; i < 160; i += nthreads) fs.sums[i] = 0;
+  __syncthreads();
+  const int Pc = min(P, 160);
+  for (int i = tid; i < p.S * groups; i += nthreads) {
+    const int t = mla_units_of(p.seq_lens[i / groups], unit);
+    if (t > 0) atomicAdd(&fs.sums[i % Pc], t);
+  }
+  __syncthreads();
+  if (warp == 0) {
+    long long run = 0;
+    for (int s0 = 0; s0 < p.S; s0 += 32) {
+      const int s = s0 + lane;
+      const long long v = s < p.S ? (long long)mla_units_of(p.seq_lens[s], unit) * groups : 0;
+      long long inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const long long up = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += up;
+      }
+      if (header_writer && s < p.S) p.flat_prefix[s] = run + inc - v;
+      run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    const long long W = run;
+    int worst = 0;
+    for (int c = lane; c < Pc; c += 32) worst = max(worst, fs.sums[c]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) worst = max(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+    const long long quota = (W + P - 1) / P;
+    const int item_mode = P <= 160 && (long long)worst * 100 <= quota * (100 + slack_pct) + 200;
+    if (header_writer && lane == 0) {
+      p.flat_prefix[p.S] = W;
+      p.flat_prefix[p.S + 1] = item_mode;
+    }
+    if (lane == 0) fs.item_mode = item_mode;
+    if (item_mode) {
+      // first non-empty item of this worker: items w, w + P, ... in (sequence, group) order
+      int it = worker;
+      const int n_items = p.S * groups;
+      while (it < n_items && p.seq_lens[it / groups] <= 0) it += P;
+      if (lane == 0) {
+        fs.u0 = 0, fs.u1 = it < n_items ? 1 : 0;
+        fs.seq = it < n_items ? it / groups : -1, fs.group = it < n_items ? it % groups : 0, fs.tile = 0;
+      }
+    } else {
+      const long long u0 = W * worker / P, u1 = W * (worker + 1) / P;
+      int fseq = -1, fgroup = 0, ftile = 0;
+      long long acc = 0;
+      if (u0 < u1) {
+        for (int s0 = 0; s0 < p.S && fseq < 0; s0 += 32) {
+          const int s = s0 + lane;
+          const long long v = s < p.S ? (long long)mla_units_of(p.seq_lens[s], unit) * groups : 0;
+          long long inc = v;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) {
+            const long long up = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += up;
+          }
+          const bool here = v > 0 && acc + inc - v <= u0 && u0 < acc + inc;
+          const unsigned m = __ballot_sync(0xffffffffu, here);
+          if (m != 0) {
+            const int src = __ffs(m) - 1;
+            const long long before = __shfl_sync(0xffffffffu, acc + inc - v, src);
+            const long long span = __shfl_sync(0xffffffffu, v, src);
+            fseq = s0 + src;
+            const int ts = (int)(span / groups);
+            fgroup = (int)((u0 - before) / ts);
+            ftile = (int)((u0 - before) % ts);
+          }
+          acc += __shfl_sync(0xffffffffu, inc, 31);
+        }
+      }
+      if (lane == 0) {
+        fs.u0 = u0, fs.u1 = u1;
+        fs.seq = fseq, fs.group = fgroup, fs.tile = ftile;
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// the flat walk (tile0 / tile1 / tiles_seq in scheduling units of `unit` tokens)
+__device__ __forceinline__ MlaSeg mla_flat_first(const MlaParams& p, const MlaFlatStart& fs, int unit) {
+  MlaSeg g;
+  g.seq = fs.seq, g.group = fs.group;
+  g.L = p.seq_lens[g.seq];
+  g.tiles_seq = mla_units_of(g.L, unit);
+  if (fs.item_mode) {
+    g.tile0 = 0, g.tile1 = g.tiles_seq, g.slot = -1, g.valid = true;
+    return g;
+  }
+  g.tile0 = fs.tile;
+  g.tile1 = (int)min((long long)g.tiles_seq, g.tile0 + (fs.u1 - fs.u0));
+  g.slot = (g.tile0 == 0 && g.tile1 == g.tiles_seq) ? -1 : 0;
+  g.valid = true;
+  return g;
+}
+__device__ __forceinline__ MlaSeg mla_flat_next(const MlaParams& p, const MlaFlatStart& fs, int unit, int groups, int P,
+                                                MlaSeg g, long long& done) {
+  if (fs.item_mode) {
+    int it = g.seq * groups + g.group;
+    const int n_items = p.S * groups;
+    do { it += P; } while (it < n_items && p.seq_lens[it / groups] <= 0);
+    if (it >= n_items) { g.valid = false; return g; }
+    g.seq = it / groups, g.group = it % groups;
+    g.L = p.seq_lens[g.seq];
+    g.tiles_seq = mla_units_of(g.L, unit);
+    g.tile0 = 0, g.tile1 = g.tiles_seq, g.slot = -1;
+    return g;
+  }
+  done += g.tile1 - g.tile0;
+  const long long left = (fs.u1 - fs.u0) - done;
+  if (left <= 0 || g.tile1 < g.tiles_seq) { g.valid = false; return g; }
+  if (++g.group == groups) {
+    g.group = 0;
+    do { ++g.seq; g.L = p.seq_lens[g.seq]; } while (g.L <= 0);
+    g.tiles_seq = mla_units_of(g.L, unit);
+  }
+  g.tile0 = 0;
+  g.tile1 = (int)min((long long)g.tiles_seq, left);
+  g.slot = g.tile1 == g.tiles_seq ? -1 : 1;
+  return g;
+}
 
 template <int NG>
 __global__ void __launch_bounds__(kMlaThreads, 1)
@@ -194,161 +336,28 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     if (split * p.split_tokens >= L) return;
   }
   if (p.flat) {
-    // empty sequences never show up in the unit list: their zeros / -inf are written here
-    for (int s = blockIdx.x; s < p.S; s += gridDim.x) {
-      if (p.seq_lens[s] > 0) continue;
-      for (int i = tid; i < p.H * 512; i += kMlaThreads) {
-        const long long o = (long long)s * p.out_seq_stride + (long long)(i / 512) * p.out_head_stride + i % 512;
-        if (p.f16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(0.f);
-        else reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(0.f);
-      }
-      if (p.lse != nullptr && tid < p.H) p.lse[(long long)s * p.lse_stride + tid] = -INFINITY;
-    }
-    // Two ways to deal the work: whole items round-robin (no partial results, but only balanced when the items are
-    // alike) or equal unit ranges (always balanced; items cut across CTAs go through fp32 partials and the merge
-    // kernel, ~10 % extra).  Every CTA evaluates both makespans from seq_lens and picks the same one.
-    for (int i = tid; i < 160; i += kMlaThreads) fstart.sums[i] = 0;
-    __syncthreads();
-    {
-      const int P = min((int)gridDim.x, 160);
-      for (int i = tid; i < p.S * p.groups; i += kMlaThreads) {
-        const int t = mla_tiles_of(p.seq_lens[i / p.groups]);
-        if (t > 0) atomicAdd(&fstart.sums[i % P], t);
-      }
-    }
-    __syncthreads();
-    if (warp == 0) {
-      // W = groups * sum of tiles; this CTA's range; where it starts.  (CTA 0 also leaves the per-sequence prefix, W and
-      // the mode in the workspace header for the merge kernel.)
-      long long run = 0;
-      long long W = 0;
-      for (int s0 = 0; s0 < p.S; s0 += 32) {
-        const int s = s0 + lane;
-        long long v = s < p.S ? (long long)mla_tiles_of(p.seq_lens[s]) * p.groups : 0;
-        long long inc = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const long long up = __shfl_up_sync(0xffffffffu, inc, o);
-          if (lane >= o) inc += up;
-        }
-        if (blockIdx.x == 0 && s < p.S) p.flat_prefix[s] = run + inc - v;
-        run += __shfl_sync(0xffffffffu, inc, 31);
-      }
-      W = run;
-      int worst = 0;
-      for (int c = lane; c < min((int)gridDim.x, 160); c += 32) worst = max(worst, fstart.sums[c]);
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) worst = max(worst, __shfl_xor_sync(0xffffffffu, worst, o));
-      const long long quota = (W + gridDim.x - 1) / gridDim.x;
-      // partials cost in proportion to the group width: accept 3 % (16 heads) .. 15 % (64 heads) + 2 tiles of imbalance
-      const int slack = NG == 64 ? 15 : (NG == 32 ? 8 : 3);
-      const int item_mode = gridDim.x <= 160 && (long long)worst * 100 <= quota * (100 + slack) + 200;
-      if (blockIdx.x == 0 && lane == 0) {
-        p.flat_prefix[p.S] = W;
-        p.flat_prefix[p.S + 1] = item_mode;
-      }
-      if (lane == 0) fstart.item_mode = item_mode;
-      if (item_mode) {
-        // first non-empty item of this CTA: items c, c + P, ... in (sequence, group) order
-        int it = blockIdx.x;
-        const int n_items = p.S * p.groups;
-        while (it < n_items && p.seq_lens[it / p.groups] <= 0) it += gridDim.x;
-        if (lane == 0) {
-          fstart.u0 = 0, fstart.u1 = it < n_items ? 1 : 0;
-          fstart.seq = it < n_items ? it / p.groups : -1, fstart.group = it < n_items ? it % p.groups : 0, fstart.tile = 0;
-        }
-      } else {
-      const long long u0 = W * blockIdx.x / gridDim.x, u1 = W * (blockIdx.x + 1) / gridDim.x;
-      // locate u0: the sequence whose span contains it
-      int fseq = -1, fgroup = 0, ftile = 0;
-      long long acc = 0;
-      if (u0 < u1) {
-        for (int s0 = 0; s0 < p.S && fseq < 0; s0 += 32) {
-          const int s = s0 + lane;
-          const long long v = s < p.S ? (long long)mla_tiles_of(p.seq_lens[s]) * p.groups : 0;
-          long long inc = v;
-#pragma unroll
-          for (int o = 1; o < 32; o <<= 1) {
-            const long long up = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += up;
-          }
-          const bool here = v > 0 && acc + inc - v <= u0 && u0 < acc + inc;
-          const unsigned m = __ballot_sync(0xffffffffu, here);
-          if (m != 0) {
-            const int src = __ffs(m) - 1;
-            const long long before = __shfl_sync(0xffffffffu, acc + inc - v, src);
-            const long long span = __shfl_sync(0xffffffffu, v, src);
-            fseq = s0 + src;
-            const int ts = (int)(span / p.groups);
-            fgroup = (int)((u0 - before) / ts);
-            ftile = (int)((u0 - before) % ts);
-          }
-          acc += __shfl_sync(0xffffffffu, inc, 31);
-        }
-      }
-      if (lane == 0) {
-        fstart.u0 = u0, fstart.u1 = u1;
-        fstart.seq = fseq, fstart.group = fgroup, fstart.tile = ftile;
-      }
-      }
-    }
-    __syncthreads();
+    mla_flat_prologue(p, fstart, kTile, p.groups, (int)gridDim.x, (int)blockIdx.x, NG == 64 ? 15 : (NG == 32 ? 8 : 3),
+                      blockIdx.x == 0, tid, kMlaThreads, 1, 0);
     if (fstart.u0 >= fstart.u1) return;   // more CTAs than units
   }
   // the segment walk: every role runs the same deterministic sequence
   auto first_seg = [&]() {
+    if (p.flat) return mla_flat_first(p, fstart, kTile);
     MlaSeg g;
-    if (!p.flat) {
-      g.seq = blockIdx.y, g.group = blockIdx.x % p.groups;
-      g.L = p.seq_lens[g.seq];
-      g.tiles_seq = mla_tiles_of(g.L);
-      const int split = blockIdx.x / p.groups;
-      g.tile0 = split * (p.split_tokens / kTile);
-      g.tile1 = min(g.tiles_seq, g.tile0 + p.split_tokens / kTile);
-      g.slot = split;
-      g.valid = g.tile0 < g.tile1;
-      return g;
-    }
-    g.seq = fstart.seq, g.group = fstart.group;
+    g.seq = blockIdx.y, g.group = blockIdx.x % p.groups;
     g.L = p.seq_lens[g.seq];
     g.tiles_seq = mla_tiles_of(g.L);
-    if (fstart.item_mode) {
-      g.tile0 = 0, g.tile1 = g.tiles_seq, g.slot = -1, g.valid = true;
-      return g;
-    }
-    g.tile0 = fstart.tile;
-    g.tile1 = (int)min((long long)g.tiles_seq, g.tile0 + (fstart.u1 - fstart.u0));
-    g.slot = (g.tile0 == 0 && g.tile1 == g.tiles_seq) ? -1 : 0;
-    g.valid = true;
+    const int split = blockIdx.x / p.groups;
+    g.tile0 = split * (p.split_tokens / kTile);
+    g.tile1 = min(g.tiles_seq, g.tile0 + p.split_tokens / kTile);
+    g.slot = split;
+    g.valid = g.tile0 < g.tile1;
     return g;
   };
-  // `done` = units consumed so far by this CTA (flat mode)
+  // `done` = units consumed so far by this CTA (flat range mode)
   auto next_seg = [&](MlaSeg g, long long& done) {
     if (!p.flat) { g.valid = false; return g; }
-    if (fstart.item_mode) {
-      int it = g.seq * p.groups + g.group;
-      const int n_items = p.S * p.groups;
-      do { it += gridDim.x; } while (it < n_items && p.seq_lens[it / p.groups] <= 0);
-      if (it >= n_items) { g.valid = false; return g; }
-      g.seq = it / p.groups, g.group = it % p.groups;
-      g.L = p.seq_lens[g.seq];
-      g.tiles_seq = mla_tiles_of(g.L);
-      g.tile0 = 0, g.tile1 = g.tiles_seq, g.slot = -1;
-      return g;
-    }
-    done += g.tile1 - g.tile0;
-    const long long left = (fstart.u1 - fstart.u0) - done;
-    if (left <= 0) { g.valid = false; return g; }
-    if (g.tile1 < g.tiles_seq) { g.valid = false; return g; }   // cannot happen: a segment only stops early at the range end
-    if (++g.group == p.groups) {
-      g.group = 0;
-      do { ++g.seq; g.L = p.seq_lens[g.seq]; } while (g.L <= 0);
-      g.tiles_seq = mla_tiles_of(g.L);
-    }
-    g.tile0 = 0;
-    g.tile1 = (int)min((long long)g.tiles_seq, left);
-    g.slot = g.tile1 == g.tiles_seq ? -1 : 1;
-    return g;
+    return mla_flat_next(p, fstart, kTile, p.groups, (int)gridDim.x, g, done);
   };
 
   long long cta_t0 = 0;
@@ -788,11 +797,11 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
 
 // flat mode: fold the partial slots of every item that more than one CTA worked on.  The decode kernel's CTA 0 left
 // the per-sequence unit prefix (and the total) in the workspace header; CTA c's range is [c W / P, (c + 1) W / P).
-__global__ void __launch_bounds__(128) mla_merge_flat_kernel(const MlaParams p, int P, int NG) {
+__global__ void __launch_bounds__(128) mla_merge_flat_kernel(const MlaParams p, int P, int NG, int unit) {
   const int seq = blockIdx.y, h = blockIdx.x;
   const int L = p.seq_lens[seq];
   if (L <= 0) return;
-  const int tiles = mla_tiles_of(L);
+  const int tiles = mla_units_of(L, unit);
   const int group = h / NG, hl = h % NG;
   const long long W = p.flat_prefix[p.S];
   if (p.flat_prefix[p.S + 1] != 0) return;   // item mode: every item was written directly
@@ -847,7 +856,8 @@ __global__ void __launch_bounds__(128) mla_merge_flat_kernel(const MlaParams p, 
 // distributed shared memory and take the same decision.
 constexpr int kPairSoftmaxWarps = 8;   // thread = (token row, head half): warps w and w + 4 share a TMEM lane quadrant
 constexpr int kPairMmaWarp = 8;
-constexpr int kPairThreads = (kPairSoftmaxWarps + 1 + kProducers) * 32;
+constexpr int kPairProducers = 4;
+constexpr int kPairThreads = (kPairSoftmaxWarps + 1 + kPairProducers) * 32;
 constexpr int kPairSoftmaxThreads = kPairSoftmaxWarps * 32;
 
 struct PairPost {           // what one CTA tells the pair about a super-tile
@@ -857,13 +867,14 @@ struct PairPost {           // what one CTA tells the pair about a super-tile
 };
 struct PairMisc {
   uint64_t full[kMaxSlots / 2], empty[kMaxSlots / 2];
-  uint64_t s_full[2], s_free[2], p_full, p_free, o_full, q_full;
+  uint64_t s_full[2], s_free[2], p_full, p_free, o_full, q_full, q_free, o_free;
   uint64_t post_bar[2];     // both CTAs' posts of a super-tile have landed (parity by super-tile)
+  uint64_t l_bar[2];        // both CTAs' row sums of a segment have landed (parity by segment)
   uint32_t tmem_base;
   uint32_t pad[3];
   float mref[128];
   float fac[128];
-  float lpart[2][128];      // row sums of each CTA's tokens, exchanged at the end
+  float lpart[2][2][128];   // [segment parity][CTA]: row sums of each CTA's tokens, exchanged at the end of a segment
   int colmax_w[kPairSoftmaxWarps][64];
   PairPost post[2][2];      // [super-tile parity][source CTA]
 };
@@ -928,28 +939,47 @@ __device__ __forceinline__ void tma_load_3d_2sm(uint32_t dst, const void* tmap, 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
 mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, const __grid_constant__ TmaDesc tm_qn,
                        const __grid_constant__ TmaDesc tm_qp) {
-  const int seq = blockIdx.y;
-  const int split = blockIdx.x >> 1;
   const uint32_t rank = cluster_ctarank();       // 0 = leader (issues the MMAs), 1 = peer
-  const int L = p.seq_lens[seq];
-  const int t0 = split * p.split_tokens;
-  const int t1 = min(L, t0 + p.split_tokens);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int nsplit = L > 0 ? (L + p.split_tokens - 1) / p.split_tokens : 1;
-  if (L <= 0) {  // empty sequence (both CTAs take this branch): zeros and lse = -inf
-    if (split == 0) {
-      for (int i = tid + rank * kPairThreads; i < p.H * 512; i += 2 * kPairThreads) {
-        const long long o = (long long)seq * p.out_seq_stride + (long long)(i / 512) * p.out_head_stride + i % 512;
-        if (p.f16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(0.f);
-        else reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(0.f);
+  constexpr int kUnit = 2 * kTile;               // scheduling unit: one super-tile (a 128-token tile for each CTA)
+  __shared__ MlaFlatStart fstart;
+  const int npairs_grid = (int)gridDim.x >> 1, my_pair = (int)blockIdx.x >> 1;
+  if (!p.flat) {
+    const int seq = blockIdx.y, split = my_pair;
+    const int L = p.seq_lens[seq];
+    if (L <= 0) {  // empty sequence (both CTAs take this branch): zeros and lse = -inf
+      if (split == 0) {
+        for (int i = tid + rank * kPairThreads; i < p.H * 512; i += 2 * kPairThreads) {
+          const long long o = (long long)seq * p.out_seq_stride + (long long)(i / 512) * p.out_head_stride + i % 512;
+          if (p.f16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(0.f);
+          else reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(0.f);
+        }
+        if (p.lse != nullptr && rank == 0 && tid < p.H) p.lse[(long long)seq * p.lse_stride + tid] = -INFINITY;
       }
-      if (p.lse != nullptr && rank == 0 && tid < p.H) p.lse[(long long)seq * p.lse_stride + tid] = -INFINITY;
+      return;
     }
-    return;
+    if (split * p.split_tokens >= L) return;
+  } else {
+    // both CTAs of a pair compute the same walk (worker = pair)
+    mla_flat_prologue(p, fstart, kUnit, 1, npairs_grid, my_pair, 10, blockIdx.x == 0, tid, kPairThreads, 2, (int)rank);
+    if (fstart.u0 >= fstart.u1) return;   // more pairs than units (both CTAs of the pair return)
   }
-  if (t0 >= t1) return;
-  const int T = (t1 - t0 + kTile - 1) / kTile;   // token tiles of this split
-  const int U = (T + 1) >> 1;                    // super-tiles: CTA r owns tile 2u + r (which may not exist for r = 1)
+  auto first_seg = [&]() {
+    if (p.flat) return mla_flat_first(p, fstart, kUnit);
+    MlaSeg g;
+    g.seq = blockIdx.y, g.group = 0;
+    g.L = p.seq_lens[g.seq];
+    g.tiles_seq = mla_units_of(g.L, kUnit);
+    g.tile0 = my_pair * (p.split_tokens / kUnit);
+    g.tile1 = min(g.tiles_seq, g.tile0 + p.split_tokens / kUnit);
+    g.slot = my_pair;
+    g.valid = g.tile0 < g.tile1;
+    return g;
+  };
+  auto next_seg = [&](MlaSeg g, long long& done) {
+    if (!p.flat) { g.valid = false; return g; }
+    return mla_flat_next(p, fstart, kUnit, 1, npairs_grid, g, done);
+  };
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -971,14 +1001,16 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
       mbar_init(smem_u32(&misc->s_full[i]), 1);
       mbar_init(smem_u32(&misc->s_free[i]), 2 * kPairSoftmaxWarps);   // leader's copy: one arrival per softmax warp of the pair
       mbar_init(smem_u32(&misc->post_bar[i]), 2);                     // one post from each CTA
+      mbar_init(smem_u32(&misc->l_bar[i]), 2);                        // both CTAs' row sums of a segment have landed
     }
     mbar_init(smem_u32(&misc->p_full), 2 * kPairSoftmaxWarps);        // leader's copy
     mbar_init(smem_u32(&misc->p_free), 1);
     mbar_init(smem_u32(&misc->o_full), 1);
     mbar_init(smem_u32(&misc->q_full), 2);                            // leader's copy: both CTAs' query loads
+    mbar_init(smem_u32(&misc->q_free), 1);                            // multicast commit: the segment's last S^T has read Q
+    mbar_init(smem_u32(&misc->o_free), 2 * kPairSoftmaxWarps);        // leader's copy: the segment's O^T has been read out
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (tid < 128) misc->mref[tid] = -INFINITY;
   if (warp == kPairMmaWarp) {   // the same warp in both CTAs, the same destination address
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&misc->tmem_base)),
                  "r"(512u)
@@ -991,7 +1023,7 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
   const uint32_t tmem = misc->tmem_base;
   const uint32_t tm_s[2] = {tmem, tmem + 128};
   const uint32_t tm_o = tmem + 256;              // O^T blocks j = 0, 1: 128 columns each
-  long long* const stamps = (p.debug_logits != nullptr && blockIdx.x == 0 && blockIdx.y == 0)
+  long long* const stamps = (p.debug_logits != nullptr && (int)blockIdx.x == 2 * p.stamp_cta && blockIdx.y == 0)
                                 ? reinterpret_cast<long long*>(p.debug_logits + 128 * 64) : nullptr;
   auto stamp = [&](int role, int tile, int k) {
     if (stamps != nullptr && tile < 64) stamps[(role * 64 + tile) * 4 + k] = clock64();
@@ -999,63 +1031,70 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
   // leader-CTA addresses of the barriers that gather arrivals from both CTAs
   const uint32_t lead_q_full = mapa_u32(smem_u32(&misc->q_full), 0);
   const uint32_t lead_p_full = mapa_u32(smem_u32(&misc->p_full), 0);
+  const uint32_t lead_o_free = mapa_u32(smem_u32(&misc->o_free), 0);
 
   if (warp > kPairMmaWarp) {
-    // =================== TMA producers (both CTAs): half-pair f of the ring sequence by producer f % kProducers ===================
+    // =================== TMA producers (both CTAs): half-pair f of the ring sequence by producer f % kPairProducers ===================
     const int pw = warp - kPairMmaWarp - 1;
     if (lane == 0) {
-      if (pw == 0) {
-        // this CTA's 64 query heads; bytes are counted on the leader's barrier
-        mbar_expect_tx_cluster(lead_q_full, (uint32_t)(kKChunks * 64 * 128));
-        for (int c = 0; c < kVChunks; ++c) tma_load_3d_2sm(q_u32 + c * 64 * 128, &tm_qn, c * 64, 64 * (int)rank, seq, lead_q_full);
-        tma_load_3d_2sm(q_u32 + kVChunks * 64 * 128, &tm_qp, 0, 64 * (int)rank, seq, lead_q_full);
-      }
-      const int32_t* table = p.page_table + (long long)seq * p.page_table_stride;
       const int box_rows = p.box_rows;
       const uint32_t box_bytes = (uint32_t)box_rows * 128u;
       int pair = 0, turn = 0;
       uint32_t phase = 0;
-      // `nhalves` ring halves holding chunks chunk0, chunk0 + 1, ... (at most nchunks of them) of token tile `tile`
-      auto load_halves = [&](int tile, int chunk0, int nhalves, int nchunks) {
-        const int tok0 = t0 + tile * kTile;
-        const int valid = max(0, min(kTile, L - tok0));          // rows of this tile that hold cache entries
-        const int vbox = (valid + box_rows - 1) / box_rows;
-        int page[8], row[8];
-#pragma unroll
-        for (int b = 0; b < 8; ++b) {
-          if (b < vbox) {
-            const int tok = tok0 + b * box_rows;
-            page[b] = table[tok >> p.page_shift];
-            row[b] = tok & (p.page_size - 1);
-          }
+      long long done = 0;
+      int nseg = 0;
+      for (MlaSeg g = first_seg(); g.valid; g = next_seg(g, done), ++nseg) {
+        const int L = g.L, t0 = g.tile0 * kUnit, U = g.tile1 - g.tile0;
+        if (pw == 0) {
+          // this CTA's 64 query heads; bytes are counted on the leader's barrier
+          if (nseg > 0) mbar_wait(smem_u32(&misc->q_free), (nseg - 1) & 1);
+          mbar_expect_tx_cluster(lead_q_full, (uint32_t)(kKChunks * 64 * 128));
+          for (int c = 0; c < kVChunks; ++c) tma_load_3d_2sm(q_u32 + c * 64 * 128, &tm_qn, c * 64, 64 * (int)rank, g.seq, lead_q_full);
+          tma_load_3d_2sm(q_u32 + kVChunks * 64 * 128, &tm_qp, 0, 64 * (int)rank, g.seq, lead_q_full);
         }
-        for (int c = 0; c < nhalves; ++c) {
-          if (turn == pw) {
-            mbar_wait(smem_u32(&misc->empty[pair]), phase ^ 1);
-            const uint32_t full = mapa_u32(smem_u32(&misc->full[pair]), 0);
-            if (c < nchunks) {
-              mbar_expect_tx_cluster(full, box_bytes * (uint32_t)vbox);
-              const uint32_t dst = ring_u32 + (uint32_t)(2 * pair + (c & 1)) * kChunkBytes;
+        const int32_t* table = p.page_table + (long long)g.seq * p.page_table_stride;
+        // `nhalves` ring halves holding chunks chunk0, chunk0 + 1, ... (at most nchunks of them) of token tile `tile`
+        auto load_halves = [&](int tile, int chunk0, int nhalves, int nchunks) {
+          const int tok0 = t0 + tile * kTile;
+          const int valid = max(0, min(kTile, L - tok0));          // rows of this tile that hold cache entries
+          const int vbox = (valid + box_rows - 1) / box_rows;
+          int page[8], row[8];
 #pragma unroll
-              for (int b = 0; b < 8; ++b)
-                if (b < vbox) tma_load_3d_2sm(dst + b * box_bytes, &tm_kv, (chunk0 + c) * 64, row[b], page[b], full);
-            } else {
-              mbar_arrive_cluster(full);
+          for (int b = 0; b < 8; ++b) {
+            if (b < vbox) {
+              const int tok = tok0 + b * box_rows;
+              page[b] = table[tok >> p.page_shift];
+              row[b] = tok & (p.page_size - 1);
             }
           }
-          if (++turn == kProducers) turn = 0;
-          if (c & 1) {
-            if (++pair == npairs) { pair = 0; phase ^= 1; }
+          for (int c = 0; c < nhalves; ++c) {
+            if (turn == pw) {
+              mbar_wait(smem_u32(&misc->empty[pair]), phase ^ 1);
+              const uint32_t full = mapa_u32(smem_u32(&misc->full[pair]), 0);
+              if (c < nchunks) {
+                mbar_expect_tx_cluster(full, box_bytes * (uint32_t)vbox);
+                const uint32_t dst = ring_u32 + (uint32_t)(2 * pair + (c & 1)) * kChunkBytes;
+#pragma unroll
+                for (int b = 0; b < 8; ++b)
+                  if (b < vbox) tma_load_3d_2sm(dst + b * box_bytes, &tm_kv, (chunk0 + c) * 64, row[b], page[b], full);
+              } else {
+                mbar_arrive_cluster(full);
+              }
+            }
+            if (++turn == kPairProducers) turn = 0;
+            if (c & 1) {
+              if (++pair == npairs) { pair = 0; phase ^= 1; }
+            }
           }
+        };
+        // S^T of super-tile u: the 9 K chunks (+ an unused half) of this CTA's own tile 2u + rank
+        // O^T of super-tile u: for t = 0, 1 and j = 0, 1 the chunk pair (4j + 2 rank, +1) of tile 2u + t (this CTA's dv slice)
+        load_halves((int)rank, 0, 10, kKChunks);
+        for (int u = 0; u < U; ++u) {
+          if (u + 1 < U) load_halves(2 * (u + 1) + (int)rank, 0, 10, kKChunks);
+          for (int t = 0; t < 2; ++t)
+            for (int j = 0; j < 2; ++j) load_halves(2 * u + t, 4 * j + 2 * (int)rank, 2, 2);
         }
-      };
-      // S^T of super-tile u: the 9 K chunks (+ an unused half) of this CTA's own tile 2u + rank
-      // O^T of super-tile u: for t = 0, 1 and j = 0, 1 the chunk pair (4j + 2 rank, +1) of tile 2u + t (this CTA's dv slice)
-      load_halves((int)rank, 0, 10, kKChunks);
-      for (int u = 0; u < U; ++u) {
-        if (u + 1 < U) load_halves(2 * (u + 1) + (int)rank, 0, 10, kKChunks);
-        for (int t = 0; t < 2; ++t)
-          for (int j = 0; j < 2; ++j) load_halves(2 * u + t, 4 * j + 2 * (int)rank, 2, 2);
       }
     }
   } else if (warp == kPairMmaWarp) {
@@ -1070,74 +1109,85 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
         if (++pair == npairs) { pair = 0; phase ^= 1; }
       };
       const uint32_t q_lo = desc_lo(q_u32, 0);
-      mbar_wait_cluster(smem_u32(&misc->q_full), 0);
-      auto issue_s = [&](int u) {
-        const int b = u & 1;
-        if (u >= 2) mbar_wait_cluster(smem_u32(&misc->s_free[b]), ((u >> 1) & 1) ^ 1);
-        tc_fence_after();
-        stamp(0, u, 0);
-        for (int c2 = 0; c2 < 5; ++c2) {
-          mbar_wait_cluster(smem_u32(&misc->full[pair]), phase);
+      long long done = 0;
+      int nseg = 0;
+      int gu = 0;   // super-tile counter across segments
+      for (MlaSeg g = first_seg(); g.valid; g = next_seg(g, done), ++nseg) {
+        const int t0 = g.tile0 * kUnit, t1 = min(g.L, g.tile1 * kUnit), U = g.tile1 - g.tile0;
+        const int gu0 = gu;
+        mbar_wait_cluster(smem_u32(&misc->q_full), nseg & 1);
+        auto issue_s = [&](int u) {
+          const int x = gu0 + u, b = x & 1;
+          if (x >= 2) mbar_wait_cluster(smem_u32(&misc->s_free[b]), ((x >> 1) & 1) ^ 1);
           tc_fence_after();
-          const uint32_t a_lo = desc_lo(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, 0);
-          const uint32_t b_lo = q_lo + (uint32_t)(c2 * 2 * 64 * 128 >> 4);
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            if (2 * c2 + h < kKChunks) {
-#pragma unroll
-              for (int k = 0; k < 4; ++k)
-                umma_f16_2sm(tm_s[b], a_lo + ((h * kChunkBytes + k * 32) >> 4), kDescHiSw128,
-                             b_lo + ((h * 64 * 128 + k * 32) >> 4), kDescHiSw128, idesc_s, (c2 | h | k) != 0);
-            }
-          }
-          umma_commit_2sm(smem_u32(&misc->empty[pair]));
-          advance();
-        }
-        umma_commit_2sm(smem_u32(&misc->s_full[b]));
-        stamp(0, u, 1);
-      };
-      auto issue_pv = [&](int u) {
-        mbar_wait_cluster(smem_u32(&misc->p_full), u & 1);
-        tc_fence_after();
-        stamp(0, u, 2);
-        for (int t = 0; t < 2; ++t) {
-          const int rows = max(0, min(kTile, t1 - (t0 + (2 * u + t) * kTile)));   // valid token rows of tile X_t
-          const int ksteps = (rows + 15) >> 4;
-          const uint32_t p_lo = desc_lo(p_u32 + t * 16384, 0);
-          for (int j = 0; j < 2; ++j) {
+          stamp(0, x, 0);
+          for (int c2 = 0; c2 < 5; ++c2) {
             mbar_wait_cluster(smem_u32(&misc->full[pair]), phase);
             tc_fence_after();
-            if (rows < (ksteps << 4)) {
-              // V rows past the sequence end may hold anything (0 * NaN = NaN): zero them in BOTH CTAs' stages
-              for (uint32_t r2 = 0; r2 < 2; ++r2)
-                for (int hlf = 0; hlf < 2; ++hlf) {
-                  const uint32_t stage = mapa_u32(ring_u32 + (uint32_t)(2 * pair + hlf) * kChunkBytes, r2);
-                  for (int un = rows * 8; un < (ksteps << 4) * 8; ++un)
-                    asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(stage + un * 16), "r"(0u) : "memory");
-                }
-              asm volatile("fence.acq_rel.cluster;" ::: "memory");
-              asm volatile("fence.proxy.async;" ::: "memory");
-            }
-            const uint32_t a_lo = desc_lo(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, kChunkBytes);
-            const uint32_t d_o = tm_o + j * 128;
+            const uint32_t a_lo = desc_lo(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, 0);
+            const uint32_t b_lo = q_lo + (uint32_t)(c2 * 2 * 64 * 128 >> 4);
 #pragma unroll
-            for (int ks = 0; ks < 8; ++ks)
-              if (ks < ksteps)
-                umma_f16_2sm(d_o, a_lo + ((ks * 2048) >> 4), kDescHiSw128,
-                             p_lo + (((ks >> 2) * 64 * 128 + (ks & 3) * 32) >> 4), kDescHiSw128, idesc_o, (u | t | ks) != 0);
+            for (int h = 0; h < 2; ++h) {
+              if (2 * c2 + h < kKChunks) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                  umma_f16_2sm(tm_s[b], a_lo + ((h * kChunkBytes + k * 32) >> 4), kDescHiSw128,
+                               b_lo + ((h * 64 * 128 + k * 32) >> 4), kDescHiSw128, idesc_s, (c2 | h | k) != 0);
+              }
+            }
             umma_commit_2sm(smem_u32(&misc->empty[pair]));
             advance();
           }
+          umma_commit_2sm(smem_u32(&misc->s_full[b]));
+          if (u == U - 1) umma_commit_2sm(smem_u32(&misc->q_free));   // the query buffers may be reloaded once this is done
+          stamp(0, x, 1);
+        };
+        auto issue_pv = [&](int u) {
+          const int x = gu0 + u;
+          mbar_wait_cluster(smem_u32(&misc->p_full), x & 1);
+          if (u == 0 && nseg > 0) mbar_wait_cluster(smem_u32(&misc->o_free), (nseg - 1) & 1);  // previous O^T has been read out
+          tc_fence_after();
+          stamp(0, x, 2);
+          for (int t = 0; t < 2; ++t) {
+            const int rows = max(0, min(kTile, t1 - (t0 + (2 * u + t) * kTile)));   // valid token rows of tile X_t
+            const int ksteps = (rows + 15) >> 4;
+            const uint32_t p_lo = desc_lo(p_u32 + t * 16384, 0);
+            for (int j = 0; j < 2; ++j) {
+              mbar_wait_cluster(smem_u32(&misc->full[pair]), phase);
+              tc_fence_after();
+              if (rows < (ksteps << 4)) {
+                // V rows past the sequence end may hold anything (0 * NaN = NaN): zero them in BOTH CTAs' stages
+                for (uint32_t r2 = 0; r2 < 2; ++r2)
+                  for (int hlf = 0; hlf < 2; ++hlf) {
+                    const uint32_t stage = mapa_u32(ring_u32 + (uint32_t)(2 * pair + hlf) * kChunkBytes, r2);
+                    for (int un = rows * 8; un < (ksteps << 4) * 8; ++un)
+                      asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(stage + un * 16), "r"(0u) : "memory");
+                  }
+                asm volatile("fence.acq_rel.cluster;" ::: "memory");
+                asm volatile("fence.proxy.async;" ::: "memory");
+              }
+              const uint32_t a_lo = desc_lo(ring_u32 + (uint32_t)pair * 2 * kChunkBytes, kChunkBytes);
+              const uint32_t d_o = tm_o + j * 128;
+#pragma unroll
+              for (int ks = 0; ks < 8; ++ks)
+                if (ks < ksteps)
+                  umma_f16_2sm(d_o, a_lo + ((ks * 2048) >> 4), kDescHiSw128,
+                               p_lo + (((ks >> 2) * 64 * 128 + (ks & 3) * 32) >> 4), kDescHiSw128, idesc_o, (u | t | ks) != 0);
+              umma_commit_2sm(smem_u32(&misc->empty[pair]));
+              advance();
+            }
+          }
+          umma_commit_2sm(smem_u32(&misc->p_free));
+          stamp(0, x, 3);
+        };
+        issue_s(0);
+        for (int u = 0; u < U; ++u) {
+          if (u + 1 < U) issue_s(u + 1);
+          issue_pv(u);
         }
-        umma_commit_2sm(smem_u32(&misc->p_free));
-        stamp(0, u, 3);
-      };
-      issue_s(0);
-      for (int u = 0; u < U; ++u) {
-        if (u + 1 < U) issue_s(u + 1);
-        issue_pv(u);
+        umma_commit_2sm(smem_u32(&misc->o_full));
+        gu += U;
       }
-      umma_commit_2sm(smem_u32(&misc->o_full));
     }
     __syncwarp();
   } else {
@@ -1147,28 +1197,34 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     const int cbase = 64 * hh;                   // first S^T column (head) of this thread
     auto sm_bar = [&]() { asm volatile("bar.sync 1, 256;" ::: "memory"); };
+    // P^T[X_rank] lives in CTA hh (the CTA that supplies heads 64hh.. as its half of the B operand)
+    const uint32_t unit = (row & 63) >> 3, within = (row & 7) * 2;
+    const uint32_t peer = rank ^ 1;
+    // The CTAs agree on the references through "posts": after looking at its S^T tile, each CTA tells both CTAs whether a
+    // logit passed m_ref + kTau and, if so, its column maxima.  The post of super-tile u is consumed at the START of
+    // super-tile u + 1 (so the exchange is off the critical path); only the first super-tile of a segment, where no
+    // reference exists yet, waits for it.  A logit may therefore exceed its reference by more than kTau for one
+    // super-tile: harmless in bf16 / fp32 unless it jumps by more than ~2^100 within 256 tokens (the exponent is clamped).
+    const bool remote_half = (uint32_t)hh != rank;
+    long long done = 0;
+    int nseg = 0;
+    int gu = 0;   // super-tile counter across segments
+    for (MlaSeg g = first_seg(); g.valid; g = next_seg(g, done), ++nseg) {
+    const int t0 = g.tile0 * kUnit, t1 = min(g.L, g.tile1 * kUnit), U = g.tile1 - g.tile0;
     float lsum[64];
 #pragma unroll
     for (int h = 0; h < 64; ++h) lsum[h] = 0.f;
-    // P^T[X_rank] lives in CTA hh (the CTA that supplies heads 64hh.. as its half of the B operand)
-    const uint32_t p_dst = mapa_u32(p_u32 + rank * 16384 + (row >> 6) * 64 * 128, (uint32_t)hh);
-    const uint32_t unit = (row & 63) >> 3, within = (row & 7) * 2;
-    const uint32_t peer = rank ^ 1;
+    if (tid < 128) misc->mref[tid] = -INFINITY;
+    sm_bar();
 
-    // The CTAs agree on the references through "posts": after looking at its S^T tile, each CTA tells both CTAs whether a
-    // logit passed m_ref + kTau and, if so, its column maxima.  The post of super-tile u is consumed at the START of
-    // super-tile u + 1 (so the exchange is off the critical path); only the first super-tile, where no reference
-    // exists yet, waits for it.  A logit may therefore exceed its reference by more than kTau for one super-tile:
-    // harmless in bf16 / fp32 unless it jumps by more than ~2^100 within 256 tokens (the exponent is clamped).
-    const bool remote_half = (uint32_t)hh != rank;
-    for (int u = 0; u < U; ++u) {
-      const int b = u & 1;
-      // ---- references: posts of the previous super-tile (both CTAs take the same decision) ----
+    for (int u = 0; u < U; ++u, ++gu) {
+      const int b = gu & 1;
+      // ---- references: posts of the previous super-tile of this segment (both CTAs take the same decision) ----
       if (u > 0) {
-        const int pb = (u - 1) & 1;
-        mbar_wait_cluster(smem_u32(&misc->post_bar[pb]), ((u - 1) >> 1) & 1);
+        const int pb = (gu - 1) & 1;
+        mbar_wait_cluster(smem_u32(&misc->post_bar[pb]), ((gu - 1) >> 1) & 1);
         const int f0 = misc->post[pb][0].flag, f1 = misc->post[pb][1].flag;
-        if (u > 1 && (f0 | f1)) {   // (the posts of super-tile 0 were applied synchronously below)
+        if (u > 1 && (f0 | f1)) {   // (the posts of the segment's first super-tile were applied synchronously below)
           if (tid < 128) {
             float m_new = misc->mref[tid];
             const float m_old = m_new;
@@ -1180,7 +1236,7 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
           sm_bar();
 #pragma unroll
           for (int h = 0; h < 64; ++h) lsum[h] *= misc->fac[cbase + h];
-          mbar_wait(smem_u32(&misc->p_free), (u - 1) & 1);  // the previous super-tile's P.V has landed in O^T
+          mbar_wait(smem_u32(&misc->p_free), (gu - 1) & 1);  // the previous super-tile's P.V has landed in O^T
           tc_fence_after();
           for (int j = 0; j < 2; ++j) {
 #pragma unroll
@@ -1198,10 +1254,10 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
           sm_bar();   // fac / mref are rewritten by the next rare path only after everyone is done with them
         }
       }
-      mbar_wait(smem_u32(&misc->s_full[b]), (u >> 1) & 1);
+      mbar_wait(smem_u32(&misc->s_full[b]), (gu >> 1) & 1);
       tc_fence_after();
       const bool valid = t0 + (2 * u + (int)rank) * kTile + row < t1;
-      if (tid == 0) stamp(1, u, 0);
+      if (tid == 0) stamp(1, gu, 0);
       // ---- pass 1: does a logit of this tile pass its reference?  Post the answer (and the column maxima) ----
       bool over = false;
 #pragma unroll
@@ -1246,18 +1302,18 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
         mbar_arrive_cluster(mapa_u32(smem_u32(&misc->post_bar[b]), peer));
       }
       if (u == 0) {   // no reference yet: this one exchange is synchronous (O^T and the sums are still empty)
-        mbar_wait_cluster(smem_u32(&misc->post_bar[0]), 0);
-        const int f0 = misc->post[0][0].flag, f1 = misc->post[0][1].flag;
+        mbar_wait_cluster(smem_u32(&misc->post_bar[b]), (gu >> 1) & 1);
+        const int f0 = misc->post[b][0].flag, f1 = misc->post[b][1].flag;
         if (tid < 128) {
           float m_new = -INFINITY;
-          if (f0) m_new = fmaxf(m_new, sortable_f32(misc->post[0][0].colmax[tid]));
-          if (f1) m_new = fmaxf(m_new, sortable_f32(misc->post[0][1].colmax[tid]));
+          if (f0) m_new = fmaxf(m_new, sortable_f32(misc->post[b][0].colmax[tid]));
+          if (f1) m_new = fmaxf(m_new, sortable_f32(misc->post[b][1].colmax[tid]));
           if (m_new == -INFINITY) m_new = 0.f;
           misc->mref[tid] = m_new;
         }
         sm_bar();
       }
-      if (tid == 0) stamp(1, u, 1);
+      if (tid == 0) stamp(1, gu, 1);
       // ---- pass 2: probabilities of this thread's 64 heads ----
       const uint32_t wr_base = remote_half ? stage_u32 + (row >> 6) * 64 * 128 : p_u32 + rank * 16384 + (row >> 6) * 64 * 128;
 #pragma unroll
@@ -1279,8 +1335,8 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
         }
         // the local half goes straight into this CTA's P^T[X_rank] (once the previous P.V released it); the half bound
         // for the peer is staged locally first
-        if (c0 == 0 && u > 0 && !remote_half) mbar_wait(smem_u32(&misc->p_free), (u - 1) & 1);
-        if (c0 == 0 && tid == 0) stamp(1, u, 2);
+        if (c0 == 0 && gu > 0 && !remote_half) mbar_wait(smem_u32(&misc->p_free), (gu - 1) & 1);
+        if (c0 == 0 && tid == 0) stamp(1, gu, 2);
 #pragma unroll
         for (int h = 0; h < 32; ++h) {
           const uint32_t addr = wr_base + (c0 + h) * 128 + ((unit ^ (h & 7)) << 4) + within;
@@ -1290,7 +1346,7 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
       if (remote_half) {
         // this warp's 32 token rows are 4 sixteen-byte units per head: ship them to the peer's P^T[X_rank], 8 units per lane
         __syncwarp();
-        if (u > 0) mbar_wait(smem_u32(&misc->p_free), (u - 1) & 1);
+        if (gu > 0) mbar_wait(smem_u32(&misc->p_free), (gu - 1) & 1);
         const uint32_t src0 = stage_u32 + (quad >> 1) * 64 * 128;
         const uint32_t dst0 = mapa_u32(p_u32 + rank * 16384 + (quad >> 1) * 64 * 128, peer);
         const uint32_t ubase = (quad & 1) * 4;
@@ -1306,46 +1362,53 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
       asm volatile("fence.proxy.async;" ::: "memory");
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(lead_p_full);
-      if (tid == 0) stamp(1, u, 3);
+      if (tid == 0) stamp(1, gu, 3);
     }
 
-    // ---- row sums of this CTA's tokens, per head, posted to both CTAs ----
-    mbar_wait(smem_u32(&misc->o_full), 0);   // every MMA of the pair is complete: the ring is scratch now
+    // ---- epilogue of the segment: row sums of both CTAs' tokens, normalise this CTA's O^T rows, store ----
+    mbar_wait(smem_u32(&misc->o_full), nseg & 1);   // every MMA of the segment is complete
     tc_fence_after();
-    float* scratch = reinterpret_cast<float*>(ring_ptr);  // [128 rows][129]
+    {
+      float* wsum = reinterpret_cast<float*>(&misc->colmax_w[0][0]);   // [8 warps][64]: per-warp column sums
 #pragma unroll
-    for (int h = 0; h < 64; ++h) scratch[row * 129 + cbase + h] = lsum[h];
-    sm_bar();
-    if (tid < 128) {
-      float l = 0.f;
-      for (int t = 0; t < kTile; ++t) l += scratch[t * 129 + tid];
-      misc->lpart[rank][tid] = l;
-      st_cluster_u32(mapa_u32(smem_u32(&misc->lpart[rank][tid]), peer), __float_as_uint(l));
+      for (int h = 0; h < 64; ++h) {
+        float v = lsum[h];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) wsum[warp * 64 + h] = v;
+      }
+      sm_bar();
+      const int lb = nseg & 1;
+      if (tid < 128) {
+        const int w0 = (tid >> 6) * 4, c = tid & 63;
+        const float l = wsum[w0 * 64 + c] + wsum[(w0 + 1) * 64 + c] + wsum[(w0 + 2) * 64 + c] + wsum[(w0 + 3) * 64 + c];
+        misc->lpart[lb][rank][tid] = l;
+        st_cluster_u32(mapa_u32(smem_u32(&misc->lpart[lb][rank][tid]), peer), __float_as_uint(l));
+      }
+      sm_bar();
+      if (tid == 0) {
+        mbar_arrive_cluster(mapa_u32(smem_u32(&misc->l_bar[lb]), rank));
+        mbar_arrive_cluster(mapa_u32(smem_u32(&misc->l_bar[lb]), peer));
+      }
+      mbar_wait_cluster(smem_u32(&misc->l_bar[lb]), (nseg >> 1) & 1);
     }
-
-  }
-
-  // everyone: the row sums of both CTAs are in place (and no CTA touches the peer's shared memory after this point)
-  cluster_sync_all();
-  if (warp < kPairSoftmaxWarps) {
-    const int quad = warp & 3, hh = warp >> 2;
-    const int row = quad * 32 + lane;
-    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
-    const int cbase = 64 * hh;
-    const bool direct = nsplit == 1;
+    const bool direct = g.tile0 == 0 && g.tile1 == g.tiles_seq;
+    const long long part_row = p.flat ? ((long long)my_pair * 2 + g.slot) * 128 : 0;
     if (tid < 128) {
-      const float l = misc->lpart[0][tid] + misc->lpart[1][tid];
+      const float l = misc->lpart[nseg & 1][0][tid] + misc->lpart[nseg & 1][1][tid];
       misc->fac[tid] = 1.f / l;
       if (rank == 0 && tid < p.H) {
         const float lse = (misc->mref[tid] + log2f(l)) * kLn2;
         if (direct) {
-          if (p.lse != nullptr) p.lse[(long long)seq * p.lse_stride + tid] = lse;
+          if (p.lse != nullptr) p.lse[(long long)g.seq * p.lse_stride + tid] = lse;
+        } else if (p.flat) {
+          p.part_lse[part_row + tid] = lse;
         } else {
-          p.part_lse[((long long)seq * p.H + tid) * p.max_splits + split] = lse;
+          p.part_lse[((long long)g.seq * p.H + tid) * p.max_splits + g.slot] = lse;
         }
       }
     }
-    asm volatile("bar.sync 1, 256;" ::: "memory");
+    sm_bar();
     {
       auto store_all = [&](auto put) {
         for (int j = 0; j < 2; ++j) {
@@ -1364,20 +1427,26 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
       if (direct) {
         const long long hs = p.out_head_stride;
         if (p.f16) {
-          __half* ob = reinterpret_cast<__half*>(p.out) + (long long)seq * p.out_seq_stride;
+          __half* ob = reinterpret_cast<__half*>(p.out) + (long long)g.seq * p.out_seq_stride;
           store_all([&](int h, int dv, float v) { ob[h * hs + dv] = __float2half_rn(v); });
         } else {
-          __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)seq * p.out_seq_stride;
+          __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(p.out) + (long long)g.seq * p.out_seq_stride;
           store_all([&](int h, int dv, float v) { ob[h * hs + dv] = __float2bfloat16_rn(v); });
         }
       } else {
-        float* pb = p.part_out + ((long long)seq * p.H * p.max_splits + split) * 512;
-        const long long hs = (long long)p.max_splits * 512;
+        float* pb = p.flat ? p.part_out + part_row * 512 : p.part_out + ((long long)g.seq * p.H * p.max_splits + g.slot) * 512;
+        const long long hs = p.flat ? 512 : (long long)p.max_splits * 512;
         store_all([&](int h, int dv, float v) { pb[h * hs + dv] = v; });
       }
     }
     tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive_cluster(lead_o_free);   // O^T may be overwritten by the next segment
+    sm_bar();                                           // fac / mref / the scratch are reused by the next segment
+    }
   }
+
+  // no CTA leaves (or frees TMEM) while its peer may still touch its shared memory or issue pair MMAs
   cluster_sync_all();
   if (warp == kPairMmaWarp) {
     tc_fence_after();
@@ -1462,12 +1531,17 @@ int mla_group_width(int H) { return H <= 16 ? 16 : (H <= 32 ? 32 : 64); }
 // flat (persistent, tile-balanced) schedule of the single-CTA kernel: whenever the caller leaves the split count to us
 bool mla_use_flat(int H, int requested_splits) {
   static const int off = env_int("B200_MLA_FLAT_OFF");
-  return !off && requested_splits <= 0 && !(H > 64 && !env_int("B200_MLA_PAIR_OFF"));
+  (void)H;
+  return !off && requested_splits <= 0;
 }
+bool mla_use_pair(int H);
+// workers (CTAs, or CTA pairs) x 2 partial slots x slot width (the group's heads; all 128 for the pair kernel)
 uint64_t mla_flat_workspace_bytes(int S, int H) {
-  const int NG = mla_group_width(H);
+  const bool pair = mla_use_pair(H);
+  const int width = pair ? 128 : mla_group_width(H);
+  const int workers = pair ? device_sm_count() / 2 : device_sm_count();
   const uint64_t header = ((uint64_t)(S + 2) * sizeof(long long) + 255) / 256 * 256;
-  return header + (uint64_t)device_sm_count() * 2 * NG * (512 + 1) * sizeof(float);
+  return header + (uint64_t)workers * 2 * width * (512 + 1) * sizeof(float);
 }
 
 bool mla_use_pair(int H) {   // 65..128 heads: the two-CTA kernel (B200_MLA_PAIR_OFF=1 keeps two independent 64-head groups)
@@ -1506,7 +1580,7 @@ int launch_mla_pair(const MlaParams& mp, const TmaDesc& kv, const TmaDesc& qn, c
   int dev = 0;
   cudaGetDevice(&dev);
   if (configured_device != dev) {
-    cudaError_t e = cudaFuncSetAttribute(mla_decode_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+    cudaError_t e = cudaFuncSetAttribute(mla_decode_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - 704);
     if (e != cudaSuccess) {
       set_error("mla_decode: cudaFuncSetAttribute(smem, pair kernel) failed: %s", cudaGetErrorString(e));
       return B200_ERR_CUDA;
@@ -1601,7 +1675,7 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   const size_t budget = 232448 - 704;  // static shared memory: the flat schedule start record
   int nslots = (int)((budget - 1024 - (size_t)NG * 128 * (kKChunks + 2) - sizeof(MlaMisc)) / kChunkBytes);
   nslots = min(nslots & ~1, kMaxSlots);
-  if (pair) nslots = (int)((232448 - 1024 - (size_t)64 * 128 * kKChunks - 3 * 16384 - sizeof(PairMisc)) / kChunkBytes) & ~1;
+  if (pair) nslots = (int)((232448 - 704 - 1024 - (size_t)64 * 128 * kKChunks - 3 * 16384 - sizeof(PairMisc)) / kChunkBytes) & ~1;
   mp.nslots = nslots;
   if (flat) {
     const uint64_t need = mla_flat_workspace_bytes(p.num_seqs, p.num_heads);
@@ -1613,7 +1687,7 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
     mp.flat = 1;
     mp.flat_prefix = static_cast<long long*>(p.workspace);
     mp.part_out = reinterpret_cast<float*>(static_cast<char*>(p.workspace) + header);
-    mp.part_lse = mp.part_out + (size_t)device_sm_count() * 2 * NG * 512;
+    mp.part_lse = mp.part_out + (pair ? (size_t)(device_sm_count() / 2) * 2 * 128 : (size_t)device_sm_count() * 2 * NG) * 512;
   } else if (splits > 1) {
     const uint64_t need = (uint64_t)p.num_seqs * p.num_heads * splits * (512 + 1) * sizeof(float);
     B200_REQUIRE(p.workspace != nullptr && p.workspace_bytes >= need, B200_ERR_WORKSPACE,
@@ -1633,7 +1707,7 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   rc = encode_map3(&qp, p.q_pe, f16, 64, (uint64_t)p.num_heads, (uint64_t)p.num_seqs, p.q_pe_head_stride, p.q_pe_seq_stride,
                    (uint32_t)NG, "q_pe");
   if (rc != B200_OK) return rc;
-  const dim3 grid = flat ? dim3((unsigned)device_sm_count(), 1)
+  const dim3 grid = flat ? dim3((unsigned)(pair ? device_sm_count() / 2 * 2 : device_sm_count()), 1)
                          : dim3((unsigned)((pair ? 2 : mp.groups) * splits), (unsigned)p.num_seqs);
   if (pair) rc = launch_mla_pair(mp, kv, qn, qp, grid, s);
   else if (NG == 16) rc = launch_mla<16>(mp, kv, qn, qp, grid, s);
@@ -1641,7 +1715,8 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   else rc = launch_mla<64>(mp, kv, qn, qp, grid, s);
   if (rc != B200_OK) return rc;
   if (flat) {
-    mla_merge_flat_kernel<<<dim3((unsigned)p.num_heads, (unsigned)p.num_seqs), 128, 0, s>>>(mp, (int)grid.x, NG);
+    if (pair) mla_merge_flat_kernel<<<dim3((unsigned)p.num_heads, (unsigned)p.num_seqs), 128, 0, s>>>(mp, (int)grid.x / 2, 128, 2 * kTile);
+    else mla_merge_flat_kernel<<<dim3((unsigned)p.num_heads, (unsigned)p.num_seqs), 128, 0, s>>>(mp, (int)grid.x, NG, kTile);
     count_launch();
     rc = check_launch("mla_merge_flat");
   } else if (splits > 1) {
