@@ -340,6 +340,7 @@ def mla_config(ops, name, b, L, H, dev, steps, warmup, pk, n_parity):
          "attention_us": ms * 1e3, "gbs": byt / ms / 1e6, "frac_hbm": byt / ms / 1e6 / pk["hbm_gbs"],
          "tflops": flops / ms / 1e9, "frac_tensor": flops / ms / 1e9 / pk.get("bf16_tflops", 1674.0),
          "algorithmic_bytes": byt, "l2": "working set larger than L2"}
+    e["traffic"], e["traffic_source"] = measured_traffic(name)
     if n_parity > 0:
         picks = sorted(set(int(round(i * (b - 1) / max(n_parity - 1, 1))) for i in range(n_parity)))
         worst = 0.0

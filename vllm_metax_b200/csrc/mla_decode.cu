@@ -961,7 +961,7 @@ mla_decode_pair_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv,
     if (split * p.split_tokens >= L) return;
   } else {
     // both CTAs of a pair compute the same walk (worker = pair)
-    mla_flat_prologue(p, fstart, kUnit, 1, npairs_grid, my_pair, 10, blockIdx.x == 0, tid, kPairThreads, 2, (int)rank);
+    mla_flat_prologue(p, fstart, kUnit, 1, npairs_grid, my_pair, 20, blockIdx.x == 0, tid, kPairThreads, 2, (int)rank);
     if (fstart.u0 >= fstart.u1) return;   // more pairs than units (both CTAs of the pair return)
   }
   auto first_seg = [&]() {
