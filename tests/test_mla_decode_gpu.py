@@ -152,3 +152,36 @@ def test_triton_decode_attention_fwd_call_shape(ops, page, splits):
                          splits, d["scale"], page)
     check(o.cpu(), None, ref_out, None, torch.bfloat16)
     torch.testing.assert_close(lse.float().cpu(), ref_lse, atol=5e-2, rtol=1e-2)  # lse in the query dtype, as the caller allocates it
+
+
+def _ragged(bs, H, page, lens, seed):
+    d = orc.make_mla_inputs(bs, H, page, max(max(lens), 1), seed=seed, varlen=False)
+    d["seq_lens"] = torch.tensor(lens, dtype=torch.int32)
+    return d
+
+
+@pytest.mark.parametrize("H", [16, 64, 128])
+def test_flat_schedule_ragged_batch_with_empty_sequences(ops, H):
+    """more items than SMs, lengths from 0 to a few tiles: the persistent schedule walks several items per CTA (or CTA
+    pair), empty sequences get zeros / -inf, and whichever dealing mode the kernel picks the result is the oracle's"""
+    import random
+    rnd = random.Random(H)
+    lens = [rnd.choice([0, 1, 17, 128, 129, 300, 700, 1100]) for _ in range(200)]
+    lens[0], lens[7] = 0, 1100
+    d = _ragged(200, H, 64, lens, seed=H + 1)
+    ref_out, ref_lse = orc.mla_decode(d["query"], d["kv_cache"], d["scale"], d["block_tables"], d["seq_lens"])
+    out, lse = run(ops, d)
+    check(out, lse, ref_out, ref_lse, torch.bfloat16)
+    empty = [i for i, n in enumerate(lens) if n == 0]
+    assert (out[empty] == 0).all() and torch.isinf(lse[empty]).all()
+
+
+@pytest.mark.parametrize("H", [16, 128])
+def test_flat_schedule_one_long_sequence_among_short_ones(ops, H):
+    """one 20k-token sequence among 1-tile ones: range mode, the long item is cut across many CTAs (partial slots +
+    mla_merge_flat_kernel), the short ones are whole items inside a CTA's range"""
+    lens = [20000] + [100] * 30 + [0] + [257] * 8
+    d = _ragged(len(lens), H, 64, lens, seed=H + 9)
+    ref_out, ref_lse = orc.mla_decode(d["query"], d["kv_cache"], d["scale"], d["block_tables"], d["seq_lens"])
+    out, lse = run(ops, d)
+    check(out, lse, ref_out, ref_lse, torch.bfloat16)
