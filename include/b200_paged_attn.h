@@ -529,6 +529,7 @@ int b200_peer_free(void* ptr);
  *   q_nope [num_seqs, num_heads, 512], q_pe [num_seqs, num_heads, 64], out [num_seqs, num_heads, 512]: element type
  *     `dtype` (bf16 / f16), innermost contiguous, seq / head strides in elements (16-byte aligned rows)
  *   kv_cache [num_blocks, page_size, 576] same element type; block_stride / entry_stride in elements
+ *   kv_dtype FP8_E4M3: q_nope, q_pe and kv_cache hold e4m3 bytes instead (out stays `dtype`), as the reference op accepts
  *   seq_lens int32[num_seqs]; page_table int32[num_seqs, max_pages] (row stride page_table_stride)
  *   lse (optional) float32 [num_seqs, num_heads] (row stride lse_stride): natural-log sum of exp of the scaled logits
  *   num_heads <= 128 (the reference requires exactly 128 and pads; any count works here), page_size a power of two >= 16
@@ -559,9 +560,12 @@ typedef struct b200_mla_decode_params {
   int32_t num_heads;
   int32_t page_size;
   int32_t max_pages;
-  int32_t dtype; /* b200_dtype_t: BF16 or F16 */
+  int32_t dtype; /* b200_dtype_t of out: BF16 or F16 (and of q / cache when kv_dtype is auto) */
   int32_t num_kv_splits;
   float* debug_logits; /* NULL, or [128 x 64] fp32: raw S^T of the first tile of CTA 0 (tools/ only) */
+  int32_t kv_dtype;    /* b200_kv_dtype_t: AUTO = q / cache have the out dtype; FP8_E4M3 = q AND cache are e4m3 bytes
+                        * (the reference op's float8_e4m3fn form, descale 1; strides then count bytes) */
+  int32_t reserved;
 } b200_mla_decode_params_t;
 
 int b200_mla_decode(const b200_mla_decode_params_t* params, void* stream);

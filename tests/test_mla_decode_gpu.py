@@ -187,3 +187,28 @@ def test_flat_schedule_one_long_sequence_among_short_ones(ops, H):
     ref_out, ref_lse = orc.mla_decode(d["query"], d["kv_cache"], d["scale"], d["block_tables"], d["seq_lens"])
     out, lse = run(ops, d)
     check(out, lse, ref_out, ref_lse, torch.bfloat16)
+
+
+@pytest.mark.parametrize("H", [16, 64, 128])
+@pytest.mark.parametrize("L", [100, 1500, 5000])
+def test_fp8_e4m3_inputs(ops, H, L):
+    """the float8_e4m3fn form of the reference op (tests/kernels/attention/test_cutlass_mla_decode.py:53-58,91-101):
+    q and cache quantised to e4m3 (descale 1), bf16 output; the reference's bar for it is cos-diff < 1e-4 (out) and
+    < 1e-3 (lse) against the fp32 oracle on the dequantised values"""
+    d = orc.make_mla_inputs(3, H, 64, L, seed=H + L)
+    q8 = d["query"].to(torch.float8_e4m3fn)
+    c8 = d["kv_cache"].to(torch.float8_e4m3fn)
+    ref_out, ref_lse = orc.mla_decode(q8.float(), c8.float(), d["scale"], d["block_tables"], d["seq_lens"])
+    qd, cd = q8.to(DEV), c8.to(DEV)
+    out = torch.full((3, H, 512), float("nan"), dtype=torch.bfloat16, device=DEV)
+    lse = torch.full((3, H), float("nan"), dtype=torch.float32, device=DEV)
+    ws = torch.empty(ops.sm100_cutlass_mla_get_workspace_size(d["block_tables"].shape[1] * 64, 3, 148, -1), dtype=torch.uint8,
+                     device=DEV)
+    ops.sm100_cutlass_mla_decode(out, lse, qd[..., :512].contiguous(), qd[..., 512:].contiguous(), cd, d["seq_lens"].to(DEV),
+                                 d["block_tables"].to(DEV), ws, d["scale"], -1)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all()
+    assert cos_diff(out.float().cpu(), ref_out) < 1e-5        # two-term probabilities: far inside the reference's 1e-4
+    assert cos_diff(lse.cpu(), ref_lse) < 1e-3
+    torch.testing.assert_close(out.float().cpu(), ref_out, atol=2e-2, rtol=2e-2)
+    torch.testing.assert_close(lse.cpu(), ref_lse, atol=2e-3, rtol=1e-4)

@@ -241,6 +241,8 @@ class MlaDecodeParams(C.Structure):
         ("dtype", C.c_int32),
         ("num_kv_splits", C.c_int32),
         ("debug_logits", C.c_void_p),
+        ("kv_dtype", C.c_int32),
+        ("reserved", C.c_int32),
     ]
 
 

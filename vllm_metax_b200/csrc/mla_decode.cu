@@ -72,6 +72,19 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint32_t a_lo, uint32_
       "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// e4m3 x e4m3 -> f32 (kind::f8f6f4, K = 32 elements = the same 32 bytes per instruction as the 16-bit kinds)
+__device__ __forceinline__ void umma_f8(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                        uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n.reg .pred p;\n.reg .b64 da, db;\nmov.b64 da, {%1, %2};\nmov.b64 db, {%3, %4};\nsetp.ne.b32 p, %6, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], da, db, %5, p;\n}\n" ::"r"(d_tmem),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// kind::f8f6f4 instruction descriptor: f32 accumulate, e4m3 (format 0) operands, A major (0 K, 1 MN), B K-major
+__host__ __device__ constexpr uint32_t idesc_f8(int M, int N, int a_mn_major) {
+  return (1u << 4) | ((uint32_t)a_mn_major << 15) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
 // descriptor halves for the 128-byte swizzle: lo = (addr >> 4) | (LBO >> 4) << 16, hi = (SBO >> 4) | version 1 | layout 2
 __device__ __forceinline__ uint32_t desc_lo(uint32_t addr, uint32_t lbo_bytes) {
   return ((addr & 0x3FFFF) >> 4) | ((lbo_bytes >> 4) << 16);
@@ -144,8 +157,8 @@ struct MlaMisc {
   float fac[64];       // rescale factor of the last re-reference; 1 / row sum in the epilogue
   int colmax[4][64];   // per-warp column maxima (sortable-int encoding)
 };
-__host__ __device__ constexpr size_t mla_smem_bytes(int NG, int nslots) {
-  return 1024 + (size_t)NG * 128 * (kKChunks + 2) + (size_t)nslots * kChunkBytes + sizeof(MlaMisc);
+__host__ __device__ constexpr size_t mla_smem_bytes(int NG, int nslots, int kchunks = kKChunks) {
+  return 1024 + (size_t)NG * 128 * (kchunks + 2) + (size_t)nslots * kChunkBytes + sizeof(MlaMisc);
 }
 
 // A segment = consecutive tiles of one (sequence, head group).  Two ways to get them:
@@ -312,10 +325,19 @@ __device__ __forceinline__ MlaSeg mla_flat_next(const MlaParams& p, const MlaFla
   return g;
 }
 
-template <int NG>
+// FP8: q and cache are e4m3 bytes (the reference op's float8_e4m3fn form): rows of 576 bytes = four 128-byte chunks + a
+// fifth whose upper half lies outside the tensor and is zero-filled by TMA; K = 32 per instruction, so half as many S^T
+// products; the probabilities go to the tensor core as TWO e4m3 terms (hi = rn(p), lo = rn(p - hi): ~7 bits, where one
+// term would miss the reference's own fp8 tolerance on short contexts) with p scaled to at most 2^8.
+template <int NG, bool FP8>
 __global__ void __launch_bounds__(kMlaThreads, 1)
 mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, const __grid_constant__ TmaDesc tm_qn,
                   const __grid_constant__ TmaDesc tm_qp) {
+  constexpr int KC = FP8 ? 5 : kKChunks;           // K chunks per tile (16 KiB each)
+  constexpr int VC = FP8 ? 4 : kVChunks;           // V chunks per tile
+  constexpr int KH = FP8 ? 6 : 10;                 // ring halves of the K phase (an even count: chunks + unused)
+  constexpr float kTauX = FP8 ? 1.f : kTau;        // e4m3 probabilities must stay below 448: p <= 2^(7 + 1)
+  constexpr float kShift = FP8 ? 7.f : 0.f;        // p = 2^(x - m_ref + kShift)
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   __shared__ MlaFlatStart fstart;
   if (!p.flat) {
@@ -366,7 +388,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* const base_ptr = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t q_u32 = base;                                  // 9 chunks [NG rows x 128 B]
-  const uint32_t p_u32 = q_u32 + kKChunks * NG * 128;           // 2 chunks [NG rows x 128 B] (64 tokens each)
+  const uint32_t p_u32 = q_u32 + KC * NG * 128;                 // 2 chunks [NG rows x 128 B]: 64 tokens each (16-bit) / hi and lo terms (fp8)
   const uint32_t ring_u32 = p_u32 + 2 * NG * 128;
   uint8_t* const ring_ptr = base_ptr + (ring_u32 - base);
   MlaMisc* const misc = reinterpret_cast<MlaMisc*>(ring_ptr + (size_t)p.nslots * kChunkBytes);
@@ -430,10 +452,10 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
         if (pw == 0) {
           // query group: 8 latent chunks + the rope chunk, heads beyond H zero-filled by the tensor map bounds
           if (nseg > 0) mbar_wait(smem_u32(&misc->q_free), (nseg - 1) & 1);
-          mbar_expect_tx(smem_u32(&misc->q_full), (uint32_t)(kKChunks * NG * 128));
-          for (int c = 0; c < kVChunks; ++c)
-            tma_load_3d(q_u32 + c * NG * 128, &tm_qn, c * 64, g.group * NG, g.seq, smem_u32(&misc->q_full));
-          tma_load_3d(q_u32 + kVChunks * NG * 128, &tm_qp, 0, g.group * NG, g.seq, smem_u32(&misc->q_full));
+          mbar_expect_tx(smem_u32(&misc->q_full), (uint32_t)(KC * NG * 128));
+          for (int c = 0; c < VC; ++c)
+            tma_load_3d(q_u32 + c * NG * 128, &tm_qn, c * (FP8 ? 128 : 64), g.group * NG, g.seq, smem_u32(&misc->q_full));
+          tma_load_3d(q_u32 + VC * NG * 128, &tm_qp, 0, g.group * NG, g.seq, smem_u32(&misc->q_full));
         }
         const int32_t* table = p.page_table + (long long)g.seq * p.page_table_stride;
         // halves 0 .. nhalves-1 of the tile starting at token tok0: chunk index = half (the 10th K half is left unused)
@@ -458,7 +480,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
                 const uint32_t dst = ring_u32 + (uint32_t)(2 * pair + (c & 1)) * kChunkBytes;
 #pragma unroll
                 for (int b = 0; b < 8; ++b)
-                  if (b < vbox) tma_load_3d(dst + b * box_bytes, &tm_kv, c * 64, row[b], page[b], full);
+                  if (b < vbox) tma_load_3d(dst + b * box_bytes, &tm_kv, c * (FP8 ? 128 : 64), row[b], page[b], full);
               } else {
                 mbar_arrive(full);
               }
@@ -469,10 +491,10 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
             }
           }
         };
-        load_halves(t0, 10, kKChunks);
+        load_halves(t0, KH, KC);
         for (int i = 0; i < T; ++i) {
-          if (i + 1 < T) load_halves(t0 + (i + 1) * kTile, 10, kKChunks);
-          load_halves(t0 + i * kTile, 8, kVChunks);
+          if (i + 1 < T) load_halves(t0 + (i + 1) * kTile, KH, KC);
+          load_halves(t0 + i * kTile, VC, VC);
         }
       }
     }
@@ -480,8 +502,8 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     // =================== MMA issuer (one lane) ===================
     if (lane == 0) {
       const int fmt = p.f16 ? 0 : 1;
-      const uint32_t idesc_s = idesc_f16(128, NG, fmt, 0);
-      const uint32_t idesc_o = idesc_f16(128, NG, fmt, 1);
+      const uint32_t idesc_s = FP8 ? idesc_f8(128, NG, 0) : idesc_f16(128, NG, fmt, 0);
+      const uint32_t idesc_o = FP8 ? idesc_f8(128, NG, 1) : idesc_f16(128, NG, fmt, 1);
       int pair = 0;
       uint32_t phase = 0;
       auto advance = [&]() {
@@ -503,7 +525,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           if (x >= 2) mbar_wait(smem_u32(&misc->s_free[b]), ((x >> 1) & 1) ^ 1);
           tc_fence_after();
           stamp(0, x, 0);
-          for (int c2 = 0; c2 < 5; ++c2) {
+          for (int c2 = 0; c2 < KH / 2; ++c2) {
             tick();
             mbar_wait(smem_u32(&misc->full[pair]), phase);
             tc_fence_after();
@@ -513,11 +535,17 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
             tick();
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-              if (2 * c2 + h < kKChunks) {
+              if (2 * c2 + h < KC) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                  umma_f16(tm_s[b], a_lo + ((h * kChunkBytes + k * 32) >> 4), kDescHiSw128,
-                           b_lo + ((h * NG * 128 + k * 32) >> 4), kDescHiSw128, idesc_s, (c2 | h | k) != 0);
+                for (int k = 0; k < 4; ++k) {
+                  if (FP8 && 2 * c2 + h == 4 && k >= 2) continue;   // the rope chunk's upper 64 bytes are TMA zero fill
+                  if constexpr (FP8)
+                    umma_f8(tm_s[b], a_lo + ((h * kChunkBytes + k * 32) >> 4), kDescHiSw128,
+                            b_lo + ((h * NG * 128 + k * 32) >> 4), kDescHiSw128, idesc_s, (c2 | h | k) != 0);
+                  else
+                    umma_f16(tm_s[b], a_lo + ((h * kChunkBytes + k * 32) >> 4), kDescHiSw128,
+                             b_lo + ((h * NG * 128 + k * 32) >> 4), kDescHiSw128, idesc_s, (c2 | h | k) != 0);
+                }
               }
             }
             tock(1);
@@ -533,13 +561,14 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
         auto issue_pv = [&](int i) {
           const int x = gt0 + i;
           const int rows = min(kTile, t1 - (t0 + i * kTile));   // valid token rows of this tile
-          const int ksteps = (rows + 15) >> 4;
-          const int zero_from = rows, zero_to = ksteps << 4;     // rows of the last K step that are past the sequence
+          constexpr int KS = FP8 ? 32 : 16;                      // tokens per K step
+          const int ksteps = (rows + KS - 1) / KS;
+          const int zero_from = rows, zero_to = ksteps * KS;     // rows of the last K step that are past the sequence
           mbar_wait(smem_u32(&misc->p_full), x & 1);
           if (i == 0 && nseg > 0) mbar_wait(smem_u32(&misc->o_free), (nseg - 1) & 1);  // previous O^T has been read out
           tc_fence_after();
           stamp(0, x, 2);
-          for (int j = 0; j < 4; ++j) {
+          for (int j = 0; j < VC / 2; ++j) {
             tick();
             mbar_wait(smem_u32(&misc->full[pair]), phase);
             tc_fence_after();
@@ -552,14 +581,29 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
                   *reinterpret_cast<uint4*>(ring_ptr + (size_t)(2 * pair + hlf) * kChunkBytes + (size_t)u * 16) = make_uint4(0, 0, 0, 0);
               fence_async_smem();
             }
-            const uint32_t a_lo = desc_lo(a_addr, kChunkBytes);
-            const uint32_t d_o = tm_o + j * NG;
             tick();
+            if constexpr (FP8) {
+              // one chunk = one 128-row dv block (128 one-byte elements per swizzled row): blocks 2j and 2j + 1
 #pragma unroll
-            for (int ks = 0; ks < 8; ++ks)
-              if (ks < ksteps)
-                umma_f16(d_o, a_lo + ((ks * 2048) >> 4), kDescHiSw128,
-                         p_lo + (((ks >> 2) * NG * 128 + (ks & 3) * 32) >> 4), kDescHiSw128, idesc_o, (i | ks) != 0);
+              for (int hlf = 0; hlf < 2; ++hlf) {
+                const uint32_t a_lo = desc_lo(a_addr + hlf * kChunkBytes, 0);
+                const uint32_t d_o = tm_o + (2 * j + hlf) * NG;
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks)
+                  if (ks < ksteps) {
+                    umma_f8(d_o, a_lo + ((ks * 4096) >> 4), kDescHiSw128, p_lo + ((ks * 32) >> 4), kDescHiSw128, idesc_o, (i | ks) != 0);
+                    umma_f8(d_o, a_lo + ((ks * 4096) >> 4), kDescHiSw128, p_lo + ((NG * 128 + ks * 32) >> 4), kDescHiSw128, idesc_o, 1);
+                  }
+              }
+            } else {
+              const uint32_t a_lo = desc_lo(a_addr, kChunkBytes);
+              const uint32_t d_o = tm_o + j * NG;
+#pragma unroll
+              for (int ks = 0; ks < 8; ++ks)
+                if (ks < ksteps)
+                  umma_f16(d_o, a_lo + ((ks * 2048) >> 4), kDescHiSw128,
+                           p_lo + (((ks >> 2) * NG * 128 + (ks & 3) * 32) >> 4), kDescHiSw128, idesc_o, (i | ks) != 0);
+            }
             tock(2);
             tick();
             umma_commit(smem_u32(&misc->empty[pair]));
@@ -622,7 +666,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
         }
 #pragma unroll
         for (int h = 0; h < HC; ++h)
-          over |= valid && __uint_as_float(r[h]) * p.scale_log2 > misc->mref[c0 + h] + kTau;
+          over |= valid && __uint_as_float(r[h]) * p.scale_log2 > misc->mref[c0 + h] + kTauX;
       }
       if (softmax_bar_or(over)) {
         // ---- rare path: raise the references to this tile's column maxima, rescale O^T and the running sums ----
@@ -670,9 +714,11 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
       }
       if (tid == 0) stamp(1, gt, 1);
       // ---- pass 2: p = 2^(x - m_ref); 16-bit values into the P^T operand, fp32 into the running sums ----
-      // P^T[h][token]: K-major SW128, chunk = row / 64, 16-byte unit (row % 64) / 8 XOR (h % 8)
-      const uint32_t chunk = p_u32 + (row >> 6) * NG * 128;
-      const uint32_t unit = (row & 63) >> 3, within = (row & 7) * 2;
+      // P^T[h][token], K-major SW128.  16-bit: chunk = row / 64, 16-byte unit (row % 64) / 8 XOR (h % 8).
+      // fp8: one chunk per term (hi, lo), one byte per token: unit row / 16 XOR (h % 8).
+      const uint32_t chunk = FP8 ? p_u32 : p_u32 + (row >> 6) * NG * 128;
+      const uint32_t unit = FP8 ? (uint32_t)(row >> 4) : (uint32_t)((row & 63) >> 3);
+      const uint32_t within = FP8 ? (uint32_t)(row & 15) : (uint32_t)((row & 7) * 2);
 #pragma unroll
       for (int c0 = 0; c0 < NG; c0 += HC) {
         uint32_t r[HC];
@@ -685,16 +731,29 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
 #pragma unroll
         for (int h = 0; h < HC; ++h) {
           const float x = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
-          const float pv = fast_exp2(x - misc->mref[c0 + h]);
+          const float pv = fast_exp2(x - misc->mref[c0 + h] + kShift);
           lsum[c0 + h] += pv;
-          r[h] = p.f16 ? (uint32_t)__half_as_ushort(__float2half_rn(pv)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(pv));
+          if constexpr (FP8) {
+            // two e4m3 terms: hi = rn(p), lo = rn(p - hi); packed as (lo << 8) | hi
+            const __nv_fp8_storage_t hi = __nv_cvt_float_to_fp8(pv, __NV_SATFINITE, __NV_E4M3);
+            const float hif = __half2float(__half(__nv_cvt_fp8_to_halfraw(hi, __NV_E4M3)));
+            const __nv_fp8_storage_t lo = __nv_cvt_float_to_fp8(pv - hif, __NV_SATFINITE, __NV_E4M3);
+            r[h] = (uint32_t)hi | ((uint32_t)lo << 8);
+          } else {
+            r[h] = p.f16 ? (uint32_t)__half_as_ushort(__float2half_rn(pv)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(pv));
+          }
         }
         if (c0 == 0 && gt > 0) mbar_wait(smem_u32(&misc->p_free), (gt - 1) & 1);
         if (c0 == 0 && tid == 0) stamp(1, gt, 2);
 #pragma unroll
         for (int h = 0; h < HC; ++h) {
           const uint32_t addr = chunk + (c0 + h) * 128 + ((unit ^ (h & 7)) << 4) + within;
-          asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)r[h]) : "memory");
+          if constexpr (FP8) {
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(r[h] & 0xffu) : "memory");
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr + NG * 128), "r"(r[h] >> 8) : "memory");
+          } else {
+            asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)r[h]) : "memory");
+          }
         }
       }
       fence_async_smem();
@@ -727,7 +786,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     if (st < NG) {
       const float l = misc->fac[st];
       if (st < nh) {
-        const float lse = (misc->mref[st] + log2f(l)) * kLn2;
+        const float lse = (misc->mref[st] - kShift + log2f(l)) * kLn2;
         if (direct) {
           if (p.lse != nullptr) p.lse[(long long)g.seq * p.lse_stride + h0 + st] = lse;
         } else if (p.flat) {
@@ -1505,17 +1564,19 @@ EncodeTiledFn mla_encode_fn() {
 }
 
 // 3-D map (inner dim, rows, outer) with a [64 x box_rows x 1] box and the 128-byte swizzle; strides in elements
-int encode_map3(TmaDesc* out, const void* ptr, bool f16, uint64_t d0, uint64_t d1, uint64_t d2, int64_t s1, int64_t s2,
-                uint32_t box_rows, const char* what) {
+int encode_map3(TmaDesc* out, const void* ptr, int etype /* 0 bf16, 1 f16, 2 bytes (e4m3) */, uint64_t d0, uint64_t d1,
+                uint64_t d2, int64_t s1, int64_t s2, uint32_t box_rows, const char* what) {
   EncodeTiledFn enc = mla_encode_fn();
   B200_REQUIRE(enc != nullptr, B200_ERR_CUDA, "mla_decode: cuTensorMapEncodeTiled is not available from the driver");
+  const int eb = etype == 2 ? 1 : 2;
   const cuuint64_t dims[3] = {d0, d1, d2};
-  const cuuint64_t strides[2] = {(cuuint64_t)s1 * 2, (cuuint64_t)s2 * 2};
-  const cuuint32_t box[3] = {64, box_rows, 1};
+  const cuuint64_t strides[2] = {(cuuint64_t)s1 * eb, (cuuint64_t)s2 * eb};
+  const cuuint32_t box[3] = {(cuuint32_t)(128 / eb), box_rows, 1};   // 128-byte rows (a box may reach past dim 0: zero fill)
   const cuuint32_t estr[3] = {1, 1, 1};
   CUtensorMap m;
-  const CUresult r = enc(&m, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3,
-                         const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  const CUtensorMapDataType dt = etype == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                            : (etype == 1 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
+  const CUresult r = enc(&m, dt, 3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   B200_REQUIRE(r == CUDA_SUCCESS, B200_ERR_INVALID_ARGUMENT,
                "mla_decode: cuTensorMapEncodeTiled failed (%d) for %s (dims %llu/%llu/%llu, strides %lld/%lld elements)",
@@ -1535,6 +1596,7 @@ bool mla_use_flat(int H, int requested_splits) {
   return !off && requested_splits <= 0;
 }
 bool mla_use_pair(int H);
+thread_local bool g_mla_fp8 = false;   // the call being planned takes e4m3 inputs (no pair kernel for those)
 // workers (CTAs, or CTA pairs) x 2 partial slots x slot width (the group's heads; all 128 for the pair kernel)
 uint64_t mla_flat_workspace_bytes(int S, int H) {
   const bool pair = mla_use_pair(H);
@@ -1546,7 +1608,7 @@ uint64_t mla_flat_workspace_bytes(int S, int H) {
 
 bool mla_use_pair(int H) {   // 65..128 heads: the two-CTA kernel (B200_MLA_PAIR_OFF=1 keeps two independent 64-head groups)
   static const int off = env_int("B200_MLA_PAIR_OFF");
-  return H > 64 && !off;
+  return H > 64 && !off && !g_mla_fp8;
 }
 
 // number of token splits: minimise waves(items) / splits over the allowed range (every split >= kMinSplitTiles tiles)
@@ -1592,10 +1654,10 @@ int launch_mla_pair(const MlaParams& mp, const TmaDesc& kv, const TmaDesc& qn, c
   return check_launch("mla_decode (pair kernel)");
 }
 
-template <int NG>
+template <int NG, bool FP8>
 int launch_mla(const MlaParams& mp, const TmaDesc& kv, const TmaDesc& qn, const TmaDesc& qp, dim3 grid, cudaStream_t s) {
-  auto kern = mla_decode_kernel<NG>;
-  const size_t smem = mla_smem_bytes(NG, mp.nslots);
+  auto kern = mla_decode_kernel<NG, FP8>;
+  const size_t smem = mla_smem_bytes(NG, mp.nslots, FP8 ? 5 : kKChunks);
   static thread_local int configured_device = -1;
   int dev = 0;
   cudaGetDevice(&dev);
@@ -1633,14 +1695,19 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   B200_REQUIRE(p.num_seqs >= 0 && p.num_heads > 0 && p.max_pages > 0 && p.num_blocks > 0, B200_ERR_INVALID_ARGUMENT,
                "mla_decode: negative or zero size");
   B200_REQUIRE(p.dtype == B200_DTYPE_BF16 || p.dtype == B200_DTYPE_F16, B200_ERR_UNSUPPORTED,
-               "mla_decode: q / cache must be bf16 or f16 (dtype %d)", p.dtype);
+               "mla_decode: out must be bf16 or f16 (dtype %d)", p.dtype);
+  B200_REQUIRE(p.kv_dtype == B200_KV_AUTO || p.kv_dtype == B200_KV_FP8_E4M3, B200_ERR_UNSUPPORTED,
+               "mla_decode: q / cache are either of the out dtype (kv_dtype auto) or e4m3 bytes (fp8_e4m3), got %d", p.kv_dtype);
   B200_REQUIRE(p.num_heads <= 128, B200_ERR_UNSUPPORTED, "mla_decode: num_heads %d > 128", p.num_heads);
   B200_REQUIRE(p.page_size >= 16 && (p.page_size & (p.page_size - 1)) == 0, B200_ERR_UNSUPPORTED,
                "mla_decode: page_size %d must be a power of two >= 16", p.page_size);
-  B200_REQUIRE(p.entry_stride % 8 == 0 && p.block_stride % 8 == 0 && p.q_nope_head_stride % 8 == 0 &&
-                   p.q_nope_seq_stride % 8 == 0 && p.q_pe_head_stride % 8 == 0 && p.q_pe_seq_stride % 8 == 0 &&
+  const bool fp8 = p.kv_dtype == B200_KV_FP8_E4M3;
+  const int al = fp8 ? 16 : 8;   // elements per 16 bytes
+  B200_REQUIRE(p.entry_stride % al == 0 && p.block_stride % al == 0 && p.q_nope_head_stride % al == 0 &&
+                   p.q_nope_seq_stride % al == 0 && p.q_pe_head_stride % al == 0 && p.q_pe_seq_stride % al == 0 &&
                    p.out_head_stride % 4 == 0 && p.out_seq_stride % 4 == 0,
-               B200_ERR_UNSUPPORTED, "mla_decode: rows must be 16-byte aligned (strides multiple of 8 elements)");
+               B200_ERR_UNSUPPORTED, "mla_decode: rows must be 16-byte aligned");
+  g_mla_fp8 = fp8;
   B200_REQUIRE(((uintptr_t)p.kv_cache | (uintptr_t)p.q_nope | (uintptr_t)p.q_pe) % 16 == 0 && (uintptr_t)p.out % 8 == 0,
                B200_ERR_UNSUPPORTED, "mla_decode: base pointers must be 16-byte aligned");
   if (p.num_seqs == 0) return B200_OK;
@@ -1673,7 +1740,7 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
   mp.f16 = f16 ? 1 : 0;
   // shared memory: one CTA per SM (two CTAs per SM for the narrow groups measured slower: less in flight per CTA)
   const size_t budget = 232448 - 704;  // static shared memory: the flat schedule start record
-  int nslots = (int)((budget - 1024 - (size_t)NG * 128 * (kKChunks + 2) - sizeof(MlaMisc)) / kChunkBytes);
+  int nslots = (int)((budget - 1024 - (size_t)NG * 128 * ((fp8 ? 5 : kKChunks) + 2) - sizeof(MlaMisc)) / kChunkBytes);
   nslots = min(nslots & ~1, kMaxSlots);
   if (pair) nslots = (int)((232448 - 704 - 1024 - (size_t)64 * 128 * kKChunks - 3 * 16384 - sizeof(PairMisc)) / kChunkBytes) & ~1;
   mp.nslots = nslots;
@@ -1698,21 +1765,24 @@ extern "C" int b200_mla_decode(const b200_mla_decode_params_t* pp, void* stream)
     mp.part_lse = mp.part_out + (size_t)p.num_seqs * p.num_heads * splits * 512;
   }
   TmaDesc kv, qn, qp;
-  int rc = encode_map3(&kv, p.kv_cache, f16, 576, (uint64_t)p.page_size, (uint64_t)p.num_blocks, p.entry_stride, p.block_stride,
+  const int etype = fp8 ? 2 : (f16 ? 1 : 0);
+  int rc = encode_map3(&kv, p.kv_cache, etype, 576, (uint64_t)p.page_size, (uint64_t)p.num_blocks, p.entry_stride, p.block_stride,
                        (uint32_t)mp.box_rows, "kv_cache");
   if (rc != B200_OK) return rc;
-  rc = encode_map3(&qn, p.q_nope, f16, 512, (uint64_t)p.num_heads, (uint64_t)p.num_seqs, p.q_nope_head_stride,
+  rc = encode_map3(&qn, p.q_nope, etype, 512, (uint64_t)p.num_heads, (uint64_t)p.num_seqs, p.q_nope_head_stride,
                    p.q_nope_seq_stride, (uint32_t)NG, "q_nope");
   if (rc != B200_OK) return rc;
-  rc = encode_map3(&qp, p.q_pe, f16, 64, (uint64_t)p.num_heads, (uint64_t)p.num_seqs, p.q_pe_head_stride, p.q_pe_seq_stride,
+  rc = encode_map3(&qp, p.q_pe, etype, 64, (uint64_t)p.num_heads, (uint64_t)p.num_seqs, p.q_pe_head_stride, p.q_pe_seq_stride,
                    (uint32_t)NG, "q_pe");
   if (rc != B200_OK) return rc;
   const dim3 grid = flat ? dim3((unsigned)(pair ? device_sm_count() / 2 * 2 : device_sm_count()), 1)
                          : dim3((unsigned)((pair ? 2 : mp.groups) * splits), (unsigned)p.num_seqs);
   if (pair) rc = launch_mla_pair(mp, kv, qn, qp, grid, s);
-  else if (NG == 16) rc = launch_mla<16>(mp, kv, qn, qp, grid, s);
-  else if (NG == 32) rc = launch_mla<32>(mp, kv, qn, qp, grid, s);
-  else rc = launch_mla<64>(mp, kv, qn, qp, grid, s);
+  else if (fp8) rc = NG == 16 ? launch_mla<16, true>(mp, kv, qn, qp, grid, s)
+                              : (NG == 32 ? launch_mla<32, true>(mp, kv, qn, qp, grid, s) : launch_mla<64, true>(mp, kv, qn, qp, grid, s));
+  else if (NG == 16) rc = launch_mla<16, false>(mp, kv, qn, qp, grid, s);
+  else if (NG == 32) rc = launch_mla<32, false>(mp, kv, qn, qp, grid, s);
+  else rc = launch_mla<64, false>(mp, kv, qn, qp, grid, s);
   if (rc != B200_OK) return rc;
   if (flat) {
     if (pair) mla_merge_flat_kernel<<<dim3((unsigned)p.num_heads, (unsigned)p.num_seqs), 128, 0, s>>>(mp, (int)grid.x / 2, 128, 2 * kTile);

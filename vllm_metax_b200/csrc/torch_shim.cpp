@@ -736,11 +736,15 @@ void mla_decode_common(const at::Tensor& out, const at::Tensor* lse, const at::T
   TORCH_CHECK(page >= 16, "PAGE_SIZE must be at least 16");
   TORCH_CHECK(B == q_pe.size(0) && B == page_table.size(0) && B == out.size(0) && B == seq_lens.size(0),
               "Batch dims must be same for page_table, q_nope and q_pe, and out");
-  TORCH_CHECK(q_nope.scalar_type() == at::kHalf || q_nope.scalar_type() == at::kBFloat16,
-              "q_nope must be a half or bfloat16 tensor (float8_e4m3fn MLA is not implemented)");
-  TORCH_CHECK(cache.scalar_type() == q_nope.scalar_type() && q_pe.scalar_type() == q_nope.scalar_type() &&
-                  out.scalar_type() == q_nope.scalar_type(),
-              "kv_c_and_k_pe_cache, q_nope, q_pe and out must be the same type");
+  const bool fp8 = q_nope.scalar_type() == at::kFloat8_e4m3fn;
+  TORCH_CHECK(q_nope.scalar_type() == at::kHalf || q_nope.scalar_type() == at::kBFloat16 || fp8,
+              "q_nope must be a half, bfloat16, or float8_e4m3fn tensor");
+  TORCH_CHECK(cache.scalar_type() == q_nope.scalar_type() && q_pe.scalar_type() == q_nope.scalar_type(),
+              "kv_c_and_k_pe_cache, q_nope, and q_pe must be the same type");
+  // float8 inputs (descale 1, as in tests/kernels/attention/test_cutlass_mla_decode.py:91-101): out is bf16 / half
+  TORCH_CHECK(fp8 ? (out.scalar_type() == at::kHalf || out.scalar_type() == at::kBFloat16)
+                  : out.scalar_type() == q_nope.scalar_type(),
+              "out must have the query type (bfloat16 / half for float8 queries)");
   TORCH_CHECK(seq_lens.scalar_type() == at::kInt, "seq_lens must be a 32-bit integer tensor");
   TORCH_CHECK(page_table.scalar_type() == at::kInt, "page_table must be a 32-bit integer tensor");
   TORCH_CHECK(q_nope.stride(2) == 1 && q_pe.stride(2) == 1 && cache.stride(2) == 1 && out.stride(2) == 1 &&
@@ -767,7 +771,8 @@ void mla_decode_common(const at::Tensor& out, const at::Tensor* lse, const at::T
   p.num_heads = static_cast<int32_t>(H);
   p.page_size = static_cast<int32_t>(page);
   p.max_pages = static_cast<int32_t>(page_table.size(1));
-  p.dtype = to_dtype(q_nope.scalar_type());
+  p.dtype = to_dtype(out.scalar_type());
+  p.kv_dtype = fp8 ? B200_KV_FP8_E4M3 : B200_KV_AUTO;
   p.num_kv_splits = num_kv_splits <= 0 ? 0 : static_cast<int32_t>(num_kv_splits);
   if (lse != nullptr) {
     TORCH_CHECK(lse->scalar_type() == at::kFloat && lse->dim() == 2 && lse->size(0) == B && lse->size(1) >= H &&
