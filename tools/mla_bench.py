@@ -66,6 +66,7 @@ def main():
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--splits", type=int, default=-1)
     ap.add_argument("--only", type=int, default=-1)
+    ap.add_argument("--fp8", action="store_true", help="float8_e4m3fn query and cache (descale 1), bf16 output")
     ap.add_argument("--varlen", action="store_true", help="ragged sequence lengths (mean 0.6 ctx, sigma 0.3 ctx, capped at ctx)")
     ap.add_argument("--witness", help="(--impl upstream) run the stock kernel on small CPU-seeded inputs and save inputs + outputs")
     args = ap.parse_args()
@@ -123,7 +124,9 @@ def main():
         qn = torch.zeros(b, Hk, 512, dtype=q.dtype, device=dev)
         qp = torch.zeros(b, Hk, 64, dtype=q.dtype, device=dev)
         qn[:, :H], qp[:, :H] = q[..., :512], q[..., 512:]
-        out = torch.empty(b, Hk, 512, dtype=q.dtype, device=dev)
+        if args.fp8:
+            qn, qp, cache = qn.to(torch.float8_e4m3fn), qp.to(torch.float8_e4m3fn), cache.to(torch.float8_e4m3fn)
+        out = torch.empty(b, Hk, 512, dtype=torch.bfloat16, device=dev)
         lse = torch.empty(b, Hk, dtype=torch.float32, device=dev)
         ws = torch.empty(max(16, ws_size(L, b, 148, args.splits)), dtype=torch.uint8, device=dev)
         scale = 1.0 / math.sqrt(576)
@@ -137,12 +140,13 @@ def main():
             print(json.dumps({"impl": args.impl, "shape": [b, L, H], "error": "%s: %s" % (type(e).__name__, str(e)[:300])}), flush=True)
             continue
         tot = int(lens.sum().item())
-        kv_bytes = tot * 1152
-        byt = kv_bytes + b * H * (576 + 512) * 2
+        eb = 1 if args.fp8 else 2
+        kv_bytes = tot * 576 * eb
+        byt = kv_bytes + b * H * (576 * eb + 512 * 2)
         flops = 2.0 * tot * H * (576 + 512)
         print(json.dumps({"impl": args.impl, "shape": {"batch": b, "ctx": L, "heads": H, "page": PAGE}, "us": med * 1e3,
                           "us_min": mn * 1e3, "gbs": byt / med / 1e6, "tflops": flops / med / 1e9,
-                          "heads_computed": Hk, "varlen": VARLEN, "tokens": tot}), flush=True)
+                          "heads_computed": Hk, "varlen": VARLEN, "tokens": tot, "fp8": bool(args.fp8)}), flush=True)
         samples["out_b%d_L%d_H%d" % (b, L, H)] = out[:2, :H].float().cpu()
         samples["lse_b%d_L%d_H%d" % (b, L, H)] = lse[:2, :H].cpu()
         del q, cache, table, lens, qn, qp, out, lse, ws

@@ -23,6 +23,9 @@ def run(d, splits=1, debug=True):
     B, H, _ = q.shape
     qn, qp = q[..., :512].contiguous(), q[..., 512:].contiguous()
     cache, table, lens = d["kv_cache"].to(DEV), d["block_tables"].to(DEV), d["seq_lens"].to(DEV)
+    fp8 = bool(os.environ.get("B200_MLA_DEBUG_FP8"))
+    if fp8:
+        qn, qp, cache = qn.to(torch.float8_e4m3fn), qp.to(torch.float8_e4m3fn), cache.to(torch.float8_e4m3fn)
     out = torch.full((B, H, 512), float("nan"), dtype=q.dtype, device=DEV)
     lse = torch.full((B, H), float("nan"), dtype=torch.float32, device=DEV)
     dbg = torch.zeros(128 * 64 + 3 * 64 * 4 * 2 + 3 * 2 * 4096, dtype=torch.float32, device=DEV)
@@ -37,6 +40,7 @@ def run(d, splits=1, debug=True):
     p.scale, p.num_seqs, p.num_heads, p.page_size, p.max_pages = d["scale"], B, H, cache.shape[1], table.shape[1]
     p.dtype = _native.DTYPE_BF16 if q.dtype == torch.bfloat16 else _native.DTYPE_F16
     p.num_kv_splits = splits
+    p.kv_dtype = 1 if fp8 else 0
     need = lib.b200_mla_decode_workspace_bytes(B, H, table.shape[1] * cache.shape[1], splits)
     ws = torch.empty(max(need, 16), dtype=torch.uint8, device=DEV)
     p.workspace, p.workspace_bytes = ws.data_ptr(), need
@@ -91,7 +95,7 @@ def cta_times(B, H, L, page=64):
     os.environ["B200_MLA_CTA_TIMES"] = "1"
     d = orc.make_mla_inputs(B, H, page, L, seed=3, varlen=False)
     for _ in range(3):
-        run(d, 0)
+        run(d, int(os.environ.get("B200_MLA_DEBUG_SPLITS", "0")))
     t = CTA_TIMES[CTA_TIMES[:, 1] > 0]
     t0 = int(t[:, 0].min())
     dur = (t[:, 1] - t[:, 0]).float() / 1e3

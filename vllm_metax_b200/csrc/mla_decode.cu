@@ -85,6 +85,24 @@ __device__ __forceinline__ void umma_f8(uint32_t d_tmem, uint32_t a_lo, uint32_t
 __host__ __device__ constexpr uint32_t idesc_f8(int M, int N, int a_mn_major) {
   return (1u << 4) | ((uint32_t)a_mn_major << 15) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
+// two floats -> two e4m3 bytes (first argument in the low byte), round-to-nearest-even, saturating; and back (exact)
+__device__ __forceinline__ uint32_t cvt_e4m3x2(float lo, float hi) {
+  uint16_t d;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(d) : "f"(hi), "f"(lo));
+  return (uint32_t)d;
+}
+__device__ __forceinline__ float2 e4m3x2_to_f32x2(uint32_t v) {
+  uint32_t h2;
+  asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h2) : "h"((uint16_t)v));
+  return __half22float2(*reinterpret_cast<__half2*>(&h2));
+}
+// 4 x 4 byte transpose across the four lanes of a quad: lane j ends with byte j of every lane's word, in lane order
+__device__ __forceinline__ uint32_t quad_transpose_bytes(uint32_t w, int lane) {
+  uint32_t y = __shfl_xor_sync(0xffffffffu, w, 1);
+  w = (lane & 1) ? __byte_perm(w, y, 0x3715) : __byte_perm(w, y, 0x6240);
+  y = __shfl_xor_sync(0xffffffffu, w, 2);
+  return (lane & 2) ? __byte_perm(w, y, 0x3276) : __byte_perm(w, y, 0x5410);
+}
 // descriptor halves for the 128-byte swizzle: lo = (addr >> 4) | (LBO >> 4) << 16, hi = (SBO >> 4) | version 1 | layout 2
 __device__ __forceinline__ uint32_t desc_lo(uint32_t addr, uint32_t lbo_bytes) {
   return ((addr & 0x3FFFF) >> 4) | ((lbo_bytes >> 4) << 16);
@@ -336,8 +354,12 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   constexpr int KC = FP8 ? 5 : kKChunks;           // K chunks per tile (16 KiB each)
   constexpr int VC = FP8 ? 4 : kVChunks;           // V chunks per tile
   constexpr int KH = FP8 ? 6 : 10;                 // ring halves of the K phase (an even count: chunks + unused)
-  constexpr float kTauX = FP8 ? 1.f : kTau;        // e4m3 probabilities must stay below 448: p <= 2^(7 + 1)
-  constexpr float kShift = FP8 ? 7.f : 0.f;        // p = 2^(x - m_ref + kShift)
+  // e4m3 probabilities must stay below 448: p = 2^(x - m_ref + kShift) <= 2^(kShift + kTauX) = 2^8.  A re-reference
+  // puts m_ref kHead above the column maximum, so the next one needs a logit 5 log2 units above everything seen so
+  // far (with m_ref = the maximum itself and a small kTauX, 64 heads re-referenced every few tiles: ~10 k cycles each).
+  constexpr float kTauX = FP8 ? 3.f : kTau;
+  constexpr float kShift = FP8 ? 5.f : 0.f;
+  constexpr float kHead = FP8 ? 2.f : 0.f;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   __shared__ MlaFlatStart fstart;
   if (!p.flat) {
@@ -358,7 +380,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     if (split * p.split_tokens >= L) return;
   }
   if (p.flat) {
-    mla_flat_prologue(p, fstart, kTile, p.groups, (int)gridDim.x, (int)blockIdx.x, NG == 64 ? 15 : (NG == 32 ? 8 : 3),
+    mla_flat_prologue(p, fstart, kTile, p.groups, (int)gridDim.x, (int)blockIdx.x, 20,
                       blockIdx.x == 0, tid, kMlaThreads, 1, 0);
     if (fstart.u0 >= fstart.u1) return;   // more CTAs than units
   }
@@ -686,7 +708,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
         if (st < NG) {
           const int m = max(max(misc->colmax[0][st], misc->colmax[1][st]), max(misc->colmax[2][st], misc->colmax[3][st]));
           const float m_old = misc->mref[st];
-          float m_new = fmaxf(m_old, sortable_f32(m));
+          float m_new = fmaxf(m_old, sortable_f32(m) + kHead);
           if (m_new == -INFINITY) m_new = 0.f;
           misc->fac[st] = m_old == -INFINITY ? 0.f : exp2f(m_old - m_new);
           misc->mref[st] = m_new;
@@ -728,30 +750,48 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           tc_fence_before();
           mbar_arrive(smem_u32(&misc->s_free[b]));
         }
+        if constexpr (FP8) {
+          // two e4m3 terms per probability (hi = rn(p), lo = rn(p - hi)), converted two heads at a time; the bytes of
+          // four heads are transposed across the four lanes of a quad (= four consecutive tokens), so every lane
+          // stores one 32-bit word per term and head group instead of eight single bytes
 #pragma unroll
-        for (int h = 0; h < HC; ++h) {
-          const float x = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
-          const float pv = fast_exp2(x - misc->mref[c0 + h] + kShift);
-          lsum[c0 + h] += pv;
-          if constexpr (FP8) {
-            // two e4m3 terms: hi = rn(p), lo = rn(p - hi); packed as (lo << 8) | hi
-            const __nv_fp8_storage_t hi = __nv_cvt_float_to_fp8(pv, __NV_SATFINITE, __NV_E4M3);
-            const float hif = __half2float(__half(__nv_cvt_fp8_to_halfraw(hi, __NV_E4M3)));
-            const __nv_fp8_storage_t lo = __nv_cvt_float_to_fp8(pv - hif, __NV_SATFINITE, __NV_E4M3);
-            r[h] = (uint32_t)hi | ((uint32_t)lo << 8);
-          } else {
+          for (int h = 0; h < HC; h += 4) {
+            float pv[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float x = valid ? __uint_as_float(r[h + e]) * p.scale_log2 : -INFINITY;
+              pv[e] = fast_exp2(x - misc->mref[c0 + h + e] + kShift);
+              lsum[c0 + h + e] += pv[e];
+            }
+            const uint32_t hi01 = cvt_e4m3x2(pv[0], pv[1]), hi23 = cvt_e4m3x2(pv[2], pv[3]);
+            const float2 f01 = e4m3x2_to_f32x2(hi01), f23 = e4m3x2_to_f32x2(hi23);
+            const uint32_t lo01 = cvt_e4m3x2(pv[0] - f01.x, pv[1] - f01.y), lo23 = cvt_e4m3x2(pv[2] - f23.x, pv[3] - f23.y);
+            r[h] = hi01 | (hi23 << 16);        // bytes = heads h .. h+3 of this token, hi term
+            r[h + 1] = lo01 | (lo23 << 16);    // lo term
+          }
+          if (c0 == 0 && gt > 0) mbar_wait(smem_u32(&misc->p_free), (gt - 1) & 1);
+          if (c0 == 0 && tid == 0) stamp(1, gt, 2);
+#pragma unroll
+          for (int h = 0; h < HC; h += 4) {
+            const uint32_t thi = quad_transpose_bytes(r[h], lane), tlo = quad_transpose_bytes(r[h + 1], lane);
+            const int hd = c0 + h + (lane & 3);   // the head whose four tokens this lane now holds
+            const uint32_t addr = chunk + hd * 128 + ((unit ^ (hd & 7)) << 4) + (within & ~3u);
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(thi) : "memory");
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr + NG * 128), "r"(tlo) : "memory");
+          }
+        } else {
+#pragma unroll
+          for (int h = 0; h < HC; ++h) {
+            const float x = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
+            const float pv = fast_exp2(x - misc->mref[c0 + h] + kShift);
+            lsum[c0 + h] += pv;
             r[h] = p.f16 ? (uint32_t)__half_as_ushort(__float2half_rn(pv)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(pv));
           }
-        }
-        if (c0 == 0 && gt > 0) mbar_wait(smem_u32(&misc->p_free), (gt - 1) & 1);
-        if (c0 == 0 && tid == 0) stamp(1, gt, 2);
+          if (c0 == 0 && gt > 0) mbar_wait(smem_u32(&misc->p_free), (gt - 1) & 1);
+          if (c0 == 0 && tid == 0) stamp(1, gt, 2);
 #pragma unroll
-        for (int h = 0; h < HC; ++h) {
-          const uint32_t addr = chunk + (c0 + h) * 128 + ((unit ^ (h & 7)) << 4) + within;
-          if constexpr (FP8) {
-            asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(r[h] & 0xffu) : "memory");
-            asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr + NG * 128), "r"(r[h] >> 8) : "memory");
-          } else {
+          for (int h = 0; h < HC; ++h) {
+            const uint32_t addr = chunk + (c0 + h) * 128 + ((unit ^ (h & 7)) << 4) + within;
             asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((uint16_t)r[h]) : "memory");
           }
         }
