@@ -191,6 +191,25 @@ uint64_t b200_paged_attention_workspace_bytes(const b200_paged_attn_params_t* pa
 int b200_paged_attention_workspace_reset(void* workspace, uint64_t workspace_bytes, void* stream);
 
 /*
+ * b200_paged_attention_v1 without a caller workspace and without any device allocation: for code that cannot call
+ * cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).  NO COUNTERPART IN THE
+ * REFERENCE.
+ *   - Same arguments and results as b200_paged_attention_v1; params->workspace / workspace_bytes are ignored.
+ *   - The split-KV scratch is a static device array of B200_STATIC_SCRATCH_BYTES (32 MiB) inside the library; every
+ *     GPU that loads the library holds it until the process exits.
+ *   - Shapes for which b200_paged_attention_workspace_bytes() exceeds that size -> B200_ERR_WORKSPACE (every shape the
+ *     streaming kernels serve fits: their workspace is a constant ~26.6 MB; the generic kernel's split-KV partials get
+ *     the remaining ~6.9 MB).
+ *   - ALL calls on a device share the array: calls that may overlap on the GPU (different streams) race on it —
+ *     serialise them or use b200_paged_attention_v1 with one workspace per stream.  The array keeps the last call's
+ *     contents; each call re-zeroes the 1 MiB of arrival counters on `stream` before its kernel.
+ *   - Calls no cudaMalloc / cudaFree / allocating library routine.  The device of the call is the CURRENT device.
+ */
+#define B200_STATIC_SCRATCH_BYTES (32u << 20)
+int b200_paged_attention_v1_static(const b200_paged_attn_params_t* params, void* stream);
+uint64_t b200_paged_attention_static_scratch_bytes(void);
+
+/*
  * Arguments of reshape_and_cache / reshape_and_cache_flash.
  *   reference ops : csrc/torch_bindings.cpp:394-400, :403-411
  *   reference C++ : csrc/cache.h:21-40; csrc/cache_kernels.cu:407-433, :450-488

@@ -26,6 +26,8 @@ EXPORTED_SYMBOLS = (
     "b200_paged_attention_flash",
     "b200_paged_attention_workspace_bytes",
     "b200_paged_attention_workspace_reset",
+    "b200_paged_attention_v1_static",
+    "b200_paged_attention_static_scratch_bytes",
     "b200_reshape_and_cache",
     "b200_reshape_and_cache_flash",
     "b200_convert_fp8",
@@ -314,6 +316,10 @@ def load() -> C.CDLL:
     lib.b200_paged_attention_workspace_bytes.restype = C.c_uint64
     lib.b200_paged_attention_workspace_reset.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
     lib.b200_paged_attention_workspace_reset.restype = C.c_int
+    lib.b200_paged_attention_v1_static.argtypes = [C.POINTER(PagedAttnParams), C.c_void_p]
+    lib.b200_paged_attention_v1_static.restype = C.c_int
+    lib.b200_paged_attention_static_scratch_bytes.argtypes = []
+    lib.b200_paged_attention_static_scratch_bytes.restype = C.c_uint64
     lib.b200_reshape_and_cache.argtypes = [P(CacheWriteParams), C.c_void_p]
     lib.b200_reshape_and_cache.restype = C.c_int
     lib.b200_reshape_and_cache_flash.argtypes = [P(CacheWriteParams), C.c_void_p]
@@ -450,6 +456,15 @@ def workspace_bytes(p: PagedAttnParams) -> int:
 
 def paged_attention_v1(p: PagedAttnParams, stream: int) -> None:
     check(load().b200_paged_attention_v1(C.byref(p), C.c_void_p(stream)))
+
+
+def paged_attention_v1_static(p: PagedAttnParams, stream: int) -> None:
+    """v1 with the library's static device scratch (no allocation; calls on one device must not overlap)."""
+    check(load().b200_paged_attention_v1_static(C.byref(p), C.c_void_p(stream)))
+
+
+def static_scratch_bytes() -> int:
+    return int(load().b200_paged_attention_static_scratch_bytes())
 
 
 def paged_attention_v2(p: PagedAttnParams, stream: int) -> None:

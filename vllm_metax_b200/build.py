@@ -24,7 +24,7 @@ LIB_ABI = PKG / "libb200_paged_attn.so"
 LIB_SHIM = PKG / "_C.so"
 
 CU_SOURCES = ["api.cu", "cache_kernels.cu", "attention_generic.cu", "attention_stream.cu", "attention_umma_fp8.cu",
-              "merge_attn_states.cu", "cache_movers.cu", "dcp_exchange.cu", "mla_decode.cu"]
+              "merge_attn_states.cu", "cache_movers.cu", "dcp_exchange.cu", "mla_decode.cu", "static_scratch.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC",
