@@ -51,7 +51,8 @@ __device__ __forceinline__ unsigned long long gtime() {
   return t;
 }
 #define TL(slot) do { if ((threadIdx.x & 31) == 0) atomicMax(&g_timeline[blockIdx.x][slot], gtime()); } while (0)
-#define TL_FIRST(slot) do { if ((threadIdx.x & 31) == 0) atomicMin(&g_timeline[blockIdx.x][slot], gtime()); } while (0)
+// first tile of the warp only (a stamp per tile would slow the consumers down)
+#define TL_FIRST(slot) do { if ((threadIdx.x & 31) == 0 && !tl_seen) { tl_seen = true; atomicMin(&g_timeline[blockIdx.x][slot], gtime()); } } while (0)
 #else
 #define TL(slot) do { } while (0)
 #define TL_FIRST(slot) do { } while (0)
@@ -95,6 +96,9 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
     g_timeline[blockIdx.x][0] = gtime();
     g_timeline[blockIdx.x][2] = ~0ull;
     g_timeline[blockIdx.x][3] = 0; g_timeline[blockIdx.x][4] = 0;
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    g_timeline[blockIdx.x][5] = smid;  // tools/timeline_probe.py --per-sm
   }
 #endif
   if (tid == 0) {
@@ -146,6 +150,9 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
   }
 
   // ===================== consumer warps ============================================
+#ifdef B200_TIMELINE
+  bool tl_seen = false;
+#endif
   const int g = lane >> 2, c = lane & 3;
   // ldmatrix lane addressing (byte offsets inside a K / V chunk)
   const int mi = lane >> 3, r8 = lane & 7;
