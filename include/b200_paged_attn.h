@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define B200_PAGED_ATTN_ABI_VERSION 2
+#define B200_PAGED_ATTN_ABI_VERSION 3
 
 /* v2 partition size: template default of the reference launcher
  * (csrc/attention/paged_attention_v2.cu:45) and of its callers
@@ -481,8 +481,20 @@ int b200_rotary_embedding_and_cache_flash(const b200_rotary_params_t* params, vo
  *   out_lse [heads_local, num_seqs] float32 (nullable).
  * `epoch` starts at 1 and grows by one per step on every rank; the partial
  * buffers must alternate between two allocations by epoch parity (a peer may
- * be one step ahead).  A peer that does not arrive within 10 s traps the
- * kernel.  world <= B200_DCP_MAX_WORLD.
+ * be one step ahead).  A peer that does not arrive within
+ * B200_DCP_WAIT_SECONDS (default 120 s) traps the kernel.
+ * world <= B200_DCP_MAX_WORLD.
+ *
+ * Step number in device memory (ABI v3, CUDA-graph capture): with
+ * step_counter != NULL the launch takes its step from *step_counter — the word
+ * the b200_dcp_gather_query call of the same step has just advanced — and
+ * `epoch` is ignored, so nothing in the launch changes from step to step and
+ * the gather / attention / fold triple can be captured once and replayed.
+ * With a gather in every step ONE set of buffers is enough (no parity): a
+ * peer's gather of step k+1 returns only after every rank has published its
+ * gather flag k+1, which every rank does after its fold of step k has
+ * finished reading.  With step_counter == NULL (host-side epoch) the call
+ * refuses to be captured: a replay would wait for a step long passed.
  */
 #define B200_DCP_MAX_WORLD 16
 typedef struct b200_dcp_fold_params {
@@ -498,6 +510,8 @@ typedef struct b200_dcp_fold_params {
   int32_t head_size;
   int32_t dtype; /* b200_dtype_t of the partial and final outputs */
   uint32_t epoch;
+  /* ABI v3, nullable: the step counter of the paired b200_dcp_gather_query (local device memory), read only */
+  const uint32_t* step_counter;
 } b200_dcp_fold_params_t;
 int b200_dcp_exchange_fold(const b200_dcp_fold_params_t* params, void* stream);
 
@@ -513,6 +527,10 @@ int b200_dcp_exchange_fold(const b200_dcp_fold_params_t* params, void* stream);
  * gathered query.  peer_flags are arrays of `world` uint32 distinct from the
  * fold's; cta_counter is one zero-initialised uint32 of local device memory.
  * The gathered-query buffers alternate by epoch parity like the partials.
+ * ABI v3: with step_counter != NULL (one zero-initialised uint32 of local
+ * device memory) the step is *step_counter + 1, which the launch stores back
+ * before it completes; `epoch` is ignored and the call can be captured into a
+ * CUDA graph (see b200_dcp_exchange_fold).
  */
 typedef struct b200_dcp_gather_params {
   void* const* peer_q;         /* [world] host array of device pointers */
@@ -527,6 +545,7 @@ typedef struct b200_dcp_gather_params {
   int32_t head_size;
   int32_t dtype;
   uint32_t epoch;
+  uint32_t* step_counter; /* ABI v3, nullable */
 } b200_dcp_gather_params_t;
 int b200_dcp_gather_query(const b200_dcp_gather_params_t* params, void* stream);
 

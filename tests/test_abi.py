@@ -37,7 +37,7 @@ def test_every_declared_symbol_is_exported(native):
     lib = C.CDLL(os.fspath(native.LIB_PATH))
     for n in names:
         assert hasattr(lib, n), n
-    assert native.load().b200_abi_version() == 2
+    assert native.load().b200_abi_version() == 3
 
 
 def test_ctypes_structs_match_header_layout(native, tmp_path):

@@ -131,7 +131,7 @@ def _rank_main(rank: int, world: int, port: int, fused: bool, ret):
         max_local = int(local_lens.max())
         xch = DcpExchange(8, H, 128, torch.bfloat16) if fused else None
         errs = []
-        # several steps with different queries: the fused path alternates its two partial buffers and its flags grow
+        # several steps with different queries: the fused path reuses its one set of buffers and its flags grow
         for step in range(5 if fused else 1):
             q = d["query"] if step == 0 else torch.randn(d["query"].shape, generator=torch.Generator().manual_seed(step)).bfloat16()
             d_step = dict(d, query=q)
@@ -236,7 +236,7 @@ def test_dcp_nccl(world, fused):
 
 
 def test_dcp_exchange_world1():
-    """The fused exchange on one GPU (group of one): flags, double buffering and the fold with a single partial."""
+    """The fused exchange on one GPU (group of one): flags, buffer reuse and the fold with a single partial."""
     from vllm_metax_b200.attention.dcp import DcpExchange
 
     port = _free_port()
@@ -258,9 +258,10 @@ def test_dcp_exchange_world1():
         dist.destroy_process_group()
 
 
-def test_dcp_kernels_refuse_cuda_graph_capture():
-    """The step number is a host-side kernel argument: a replayed graph would wait for a step that has long passed
-    (ADVICE r1).  Both C entry points return B200_ERR_UNSUPPORTED under capture; DcpExchange raises."""
+def test_dcp_host_epoch_launches_refuse_cuda_graph_capture():
+    """A step number passed as a host-side kernel argument would be frozen by a graph: a replay would wait for a step
+    that has long passed.  Both C entry points return B200_ERR_UNSUPPORTED under capture in that mode; with
+    the step number in device memory (step_counter, what DcpExchange uses) they are capturable — next tests."""
     from vllm_metax_b200 import _native as native
 
     dev = torch.device("cuda", 0)
@@ -285,3 +286,170 @@ def test_dcp_kernels_refuse_cuda_graph_capture():
         finally:
             g.capture_end()
     torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_dcp_device_step_counter_with_emulated_peers(world):
+    """The device-side step number on ONE GPU: `world` emulated ranks (distinct local buffers, one stream each, all
+    resident at once: the launches are tiny) run gather -> fold for several steps with NO host-side epoch.  Every
+    rank's step word must advance by one per step, the flags must follow it, and the folded result must be the N-way
+    merge of the partials the ranks hold."""
+    from vllm_metax_b200 import _native as native
+
+    dev = torch.device("cuda", 0)
+    S, Hl, D = 3, 2, 128
+    H = Hl * world
+    g = torch.Generator(device=dev).manual_seed(5)
+    q_all_buf = [torch.zeros(S, H, D, dtype=torch.bfloat16, device=dev) for _ in range(world)]
+    part_out = [torch.randn(S, H, D, device=dev, generator=g).bfloat16() for _ in range(world)]
+    part_lse = [torch.randn(H, S, device=dev, generator=g) for _ in range(world)]
+    gflags = torch.zeros(world, 16, dtype=torch.int32, device=dev)
+    fflags = torch.zeros(world, 16, dtype=torch.int32, device=dev)
+    counters = torch.zeros(world, dtype=torch.int32, device=dev)
+    steps = torch.zeros(world, dtype=torch.int32, device=dev)
+    streams = [torch.cuda.Stream() for _ in range(world)]
+    torch.cuda.synchronize()
+    gp, fp, outs, lses = [], [], [], []
+    for r in range(world):
+        gp.append(native.dcp_gather_params([b.data_ptr() for b in q_all_buf], [gflags[t].data_ptr() for t in range(world)],
+                                           counters[r:].data_ptr(), r, S, Hl, D, torch.bfloat16, steps[r:].data_ptr()))
+        fp.append(native.dcp_fold_params([b.data_ptr() for b in part_out], [b.data_ptr() for b in part_lse],
+                                         [fflags[t].data_ptr() for t in range(world)], r, S, Hl, D, torch.bfloat16,
+                                         steps[r:].data_ptr()))
+        outs.append(torch.empty(S, Hl, D, dtype=torch.bfloat16, device=dev))
+        lses.append(torch.empty(Hl, S, dtype=torch.float32, device=dev))
+    # reference fold (fp32, merge_attn_states rule over all ranks at once)
+    lse_all = torch.stack(part_lse)                      # [world, H, S]
+    m = lse_all.max(dim=0).values
+    w = torch.exp(lse_all - m)                           # [world, H, S]
+    o_all = torch.stack([p.float() for p in part_out])   # [world, S, H, D]
+    want = (o_all * w.permute(0, 2, 1).unsqueeze(-1)).sum(0) / w.sum(0).t().unsqueeze(-1)
+    want_lse = m + torch.log(w.sum(0))
+    for step in range(1, 5):
+        qs = [torch.randn(S, Hl, D, device=dev, generator=g).bfloat16() for _ in range(world)]
+        torch.cuda.synchronize()
+        for r in range(world):   # every emulated rank enqueues its whole step; the kernels wait for each other on the GPU
+            with torch.cuda.stream(streams[r]):
+                native.dcp_gather_launch(gp[r], qs[r], 0, streams[r].cuda_stream)
+                native.dcp_fold_launch(fp[r], outs[r], lses[r], 0, streams[r].cuda_stream)
+        torch.cuda.synchronize()
+        assert (steps == step).all(), steps
+        assert (gflags[:, :world] == step).all() and (fflags[:, :world] == step).all()
+        assert (counters == 0).all()
+        for r in range(world):
+            for t in range(world):
+                assert torch.equal(q_all_buf[t][:, r * Hl:(r + 1) * Hl], qs[r])
+            torch.testing.assert_close(outs[r].float(), want[:, r * Hl:(r + 1) * Hl], atol=2e-2, rtol=2e-2)
+            torch.testing.assert_close(lses[r], want_lse[r * Hl:(r + 1) * Hl], atol=1e-5, rtol=1e-5)
+
+
+def test_dcp_exchange_graph_capture_world1():
+    """DcpExchange.forward_decode captured once and replayed on new queries (group of one, one GPU): the step word
+    advances on the device with every replay."""
+    from vllm_metax_b200 import _custom_ops as ops
+    from vllm_metax_b200.attention.dcp import DcpExchange
+
+    port = _free_port()
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % port, rank=0, world_size=1, device_id=dev)
+    try:
+        d = make_problem(S=5, H=8, Hkv=2, D=128, L=333)
+        xch = DcpExchange(8, 8, 128, torch.bfloat16)
+        kc, vc = d["key_cache"].to(dev), d["value_cache"].to(dev)
+        table, lens = d["block_tables"].to(dev), d["seq_lens"].to(dev)
+        q = d["query"].to(dev).clone()
+        L = int(d["seq_lens"].max())
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            ops.reserve_workspace(torch.empty(5, 8, 128, dtype=torch.bfloat16, device=dev), L)
+            xch.forward_decode(q, kc, vc, table, lens, L, d["scale"])   # warm-up: step 1
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            out, lse = xch.forward_decode(q, kc, vc, table, lens, L, d["scale"])
+        assert xch.step() == 1   # capture runs nothing
+        for k in range(3):
+            qk = torch.randn(d["query"].shape, generator=torch.Generator().manual_seed(40 + k)).bfloat16()
+            q.copy_(qk)
+            graph.replay()
+            torch.cuda.synchronize()
+            full, full_lse = _full(dict(d, query=qk))
+            assert (out.float().cpu() - full).abs().max().item() <= TOL
+            assert (lse.cpu() - full_lse).abs().max().item() <= TOL
+            assert xch.step() == 2 + k
+        xch.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def _graph_main(rank: int, world: int, port: int, ret):
+    """Every rank captures one fused step and replays it on new queries, interleaved with eager steps."""
+    from vllm_metax_b200 import _custom_ops as ops
+    from vllm_metax_b200.attention.dcp import DcpExchange
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        H = 4 * world
+        d = make_problem(S=6, H=H, Hkv=2, D=128, L=1000)
+        Hl = H // world
+        lk, lv, table, local_lens = shard_for_rank(d, world, rank)
+        lk, lv, table, lens_dev = lk.to(dev), lv.to(dev), table.to(dev), local_lens.to(dev)
+        max_local = int(local_lens.max())
+        xch = DcpExchange(8, H, 128, torch.bfloat16)
+        q_local = torch.zeros(6, Hl, 128, dtype=torch.bfloat16, device=dev)
+        side = torch.cuda.Stream()
+        with torch.cuda.stream(side):
+            ops.reserve_workspace(torch.empty(6, H, 128, dtype=torch.bfloat16, device=dev), max_local)
+            xch.forward_decode(q_local, lk, lv, table, lens_dev, max_local, d["scale"])
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            out, lse = xch.forward_decode(q_local, lk, lv, table, lens_dev, max_local, d["scale"])
+        errs = []
+        for step in range(6):
+            q = torch.randn(d["query"].shape, generator=torch.Generator().manual_seed(70 + step)).bfloat16()
+            q_local.copy_(q[:, rank * Hl:(rank + 1) * Hl])
+            if step % 3 == 2:   # an eager step between replays: both advance the same device-side step word
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    o, l = xch.forward_decode(q_local, lk, lv, table, lens_dev, max_local, d["scale"])
+            else:
+                torch.cuda._sleep(100000 * (rank + 1))   # skew the ranks
+                graph.replay()
+                o, l = out, lse
+            torch.cuda.synchronize()
+            full, full_lse = _full(dict(d, query=q))
+            errs.append(((o.float().cpu() - full[:, rank * Hl:(rank + 1) * Hl]).abs().max().item(),
+                         (l.cpu() - full_lse[rank * Hl:(rank + 1) * Hl]).abs().max().item()))
+        steps_done = xch.step()
+        xch.close()
+        ret[rank] = (max(e for e, _ in errs), max(l for _, l in errs), steps_done)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_dcp_exchange_graph_replay(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        ret = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_graph_main, args=(r, world, port, ret)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(300)
+            assert p.exitcode == 0
+        for r in range(world):
+            err, lerr, steps_done = ret[r]
+            assert err <= 2 * TOL and lerr <= TOL, (r, err, lerr)
+            assert steps_done == 7, steps_done   # warm-up + 6

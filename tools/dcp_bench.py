@@ -76,8 +76,25 @@ def main():
     xch = dcp.DcpExchange(S, H, D, torch.bfloat16)
     fused = timed(lambda: xch.forward_decode(q, kv[0], kv[1], table, lens, max_local, scale), a.iters)
     def fold_only():
-        xch._epoch += 1  # a fold of its own epoch over whatever the partial buffers hold
-        xch._fold(S, Hl, D, dev)
+        xch._fold(S, Hl, D, dev)  # a fold of the current step over whatever the partial buffers hold (flags already there)
+
+    # the same step captured once and replayed (the step number lives in device memory)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        xch.forward_decode(q, kv[0], kv[1], table, lens, max_local, scale)
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    dist.barrier()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=side):  # the stream whose attention workspace the warm-up call sized
+        g_out, g_lse = xch.forward_decode(q, kv[0], kv[1], table, lens, max_local, scale)
+    ref_out, ref_lse = xch.forward_decode(q, kv[0], kv[1], table, lens, max_local, scale)
+    graph.replay()
+    torch.cuda.synchronize()
+    graph_ok = bool(torch.equal(g_out, ref_out) and torch.equal(g_lse, ref_lse))
+    dist.barrier()
+    fused_graph = timed(graph.replay, a.iters)
 
     gather = timed(lambda: xch._gather(q), a.iters)
     fold = timed(fold_only, a.iters)
@@ -88,6 +105,7 @@ def main():
         print(json.dumps({
             "bench": "dcp_decode", "n_gpus": world, "seqs": S, "ctx": a.ctx, "heads": H, "kv_heads": Hkv,
             "step_us": round(step * 1e3, 1), "fused_step_us": round(fused * 1e3, 1),
+            "fused_graph_step_us": round(fused_graph * 1e3, 1), "graph_replay_bit_identical": graph_ok,
             "fused_step_gbs": round(kv_bytes / fused / 1e6), "attend_us": round(attend * 1e3, 1),
             "gather_launch_us": round(gather * 1e3, 1), "fold_launch_us": round(fold * 1e3, 1),
             "exchange_us": round((step - attend) * 1e3, 1),

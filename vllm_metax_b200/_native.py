@@ -262,6 +262,7 @@ class DcpFoldParams(C.Structure):
         ("head_size", C.c_int32),
         ("dtype", C.c_int32),
         ("epoch", C.c_uint32),
+        ("step_counter", C.c_void_p),
     ]
 
 
@@ -279,6 +280,7 @@ class DcpGatherParams(C.Structure):
         ("head_size", C.c_int32),
         ("dtype", C.c_int32),
         ("epoch", C.c_uint32),
+        ("step_counter", C.c_void_p),
     ]
 
 
@@ -565,8 +567,10 @@ def peer_free(ptr: int) -> None:
     check(load().b200_peer_free(C.c_void_p(ptr)))
 
 
-def dcp_fold_params(peer_out, peer_lse, peer_flags, rank, num_seqs, heads_local, head_size, dtype) -> DcpFoldParams:
-    """Everything of a fold launch that does not change from step to step (peer_*: `world` device addresses)."""
+def dcp_fold_params(peer_out, peer_lse, peer_flags, rank, num_seqs, heads_local, head_size, dtype,
+                    step_counter: int | None = None) -> DcpFoldParams:
+    """Everything of a fold launch that does not change from step to step (peer_*: `world` device addresses).
+    step_counter: device address of the step word the paired gather advances (then `epoch` is ignored)."""
     world = len(peer_out)
     arr = C.c_void_p * world
     p = DcpFoldParams()
@@ -574,6 +578,7 @@ def dcp_fold_params(peer_out, peer_lse, peer_flags, rank, num_seqs, heads_local,
     p.peer_out, p.peer_lse, p.peer_flags = p._keep
     p.rank, p.world, p.num_seqs, p.heads_local, p.head_size = rank, world, num_seqs, heads_local, head_size
     p.dtype = _torch_dtype_code(dtype)
+    p.step_counter = step_counter
     return p
 
 
@@ -592,7 +597,7 @@ def dcp_exchange_fold(peer_out, peer_lse, peer_flags, out, out_lse, rank, num_se
 
 
 def dcp_gather_params(peer_q, peer_flags, cta_counter: int, rank, num_seqs, heads_local, head_size,
-                      dtype) -> DcpGatherParams:
+                      dtype, step_counter: int | None = None) -> DcpGatherParams:
     world = len(peer_q)
     arr = C.c_void_p * world
     p = DcpGatherParams()
@@ -601,6 +606,7 @@ def dcp_gather_params(peer_q, peer_flags, cta_counter: int, rank, num_seqs, head
     p.cta_counter = cta_counter
     p.rank, p.world, p.num_seqs, p.heads_local, p.head_size = rank, world, num_seqs, heads_local, head_size
     p.dtype = _torch_dtype_code(dtype)
+    p.step_counter = step_counter
     return p
 
 

@@ -121,9 +121,16 @@ class DcpExchange:
     Steps 3 and 4 of `forward_decode_dcp` — pack, all-to-all, N-1 merge launches — become ONE launch: the attention
     kernel writes its partial (out, lse) for all heads straight into a buffer that the peers have mapped through CUDA
     IPC (NVLink / NVSwitch peer access), and the fold kernel signals the peers, waits for their flags and pulls the N
-    slices of this rank's heads, combining them in fp32 on the fly.  The partial buffers are double-buffered by step
-    parity (csrc/dcp_exchange.cu explains why two suffice).  One instance per (group, shape bound); every rank of the
-    group must call `forward_decode` the same number of times.  Same node only (CUDA IPC).
+    slices of this rank's heads, combining them in fp32 on the fly.
+
+    The step number lives in DEVICE memory (one word per rank, advanced by the gather launch, read by the fold launch),
+    so no launch argument changes from step to step and `forward_decode` can be captured into a CUDA graph and replayed
+    — every rank of the group must run (or replay) the same number of steps.  One set of buffers is enough: a rank's
+    gather of step k+1 returns only after every peer has published its gather flag k+1, which a peer does after its
+    fold of step k has finished reading this rank's partial, so the attention launch of step k+1 overwrites nothing
+    that is still being read; and a peer pushes its step-k+1 query into this rank's gathered query only after its own
+    fold of step k, which waited for this rank's fold flag k, i.e. for this rank's attention launch of step k.
+    One instance per (group, shape bound).  Same node only (CUDA IPC).
     """
 
     def __init__(self, max_seqs: int, num_heads_total: int, head_size: int, dtype: torch.dtype,
@@ -142,18 +149,17 @@ class DcpExchange:
         self._out_bytes = _align256(max_seqs * num_heads_total * head_size * self._esize)
         self._lse_bytes = _align256(num_heads_total * max_seqs * 4)
         self._q_bytes = self._out_bytes  # the gathered query has the shape of the partial output
-        self._half = self._out_bytes + self._lse_bytes + self._q_bytes
-        # two (partial out, partial lse, gathered query) buffers + 256 bytes of control words:
-        # fold flags [16] at +0, gather flags [16] at +64, the gather kernel's CTA counter at +128
-        total = 2 * self._half + 256
+        self._data = self._out_bytes + self._lse_bytes + self._q_bytes
+        # (partial out, partial lse, gathered query) + 256 bytes of control words:
+        # fold flags [16] at +0, gather flags [16] at +64, the gather kernel's CTA counter at +128, the step at +132
+        total = self._data + 256
         self._device = torch.device("cuda", torch.cuda.current_device())
         self._ptr, handle = native.peer_alloc(total)
         handles: list = [None] * self.world
         dist.all_gather_object(handles, handle, group=group)
         self._bases = [self._ptr if r == self.rank else native.peer_open(handles[r]) for r in range(self.world)]
         self._local = torch.as_tensor(_DeviceBytes(self._ptr, total), device=self._device)
-        self._epoch = 0
-        self._plans: dict[int, list[_Plan]] = {}
+        self._plans: dict[int, _Plan] = {}
         dist.barrier(group=group)  # every flag array is zeroed and mapped before the first signal
 
     def close(self) -> None:
@@ -169,10 +175,15 @@ class DcpExchange:
         self._local = None
         self._plans = {}
 
+    def step(self) -> int:
+        """Steps completed on this rank (reads the device word: synchronises the current stream)."""
+        torch.cuda.current_stream(self._device).synchronize()
+        return int(self._local[self._data + 132:self._data + 136].view(torch.int32).item()) & 0xFFFFFFFF
+
     def forward_decode(self, query: torch.Tensor, key_cache: torch.Tensor, value_cache: torch.Tensor,
                        block_table: torch.Tensor, local_seq_lens: torch.Tensor, max_local_seq_len: int,
                        scale: float) -> tuple[torch.Tensor, torch.Tensor]:
-        """Same contract as `forward_decode_dcp`: (out [S, H_local, D], lse [H_local, S])."""
+        """Same contract as `forward_decode_dcp`: (out [S, H_local, D], lse [H_local, S]).  CUDA-graph capturable."""
         from .. import _custom_ops as ops
 
         S, Hl, D = query.shape
@@ -183,55 +194,46 @@ class DcpExchange:
                                 self.dtype))
         q_all = self._gather(query)
         # 2. local attention, partial (out, lse) of all heads written into the peer-mapped buffer
-        plan = self._plan(S, Hl, D)[self._epoch & 1]
+        plan = self._plan(S, Hl, D)
         ops.paged_attention_flash(plan.out_all, q_all, key_cache, value_cache, scale, block_table, local_seq_lens,
                                   max_local_seq_len, None, plan.lse_all)
         return self._fold(S, Hl, D, query.device)
 
-    def _plan(self, S: int, Hl: int, D: int):
-        """Per batch size, for both parities: the views of the exchange buffer and the launch parameters that do not
-        change from step to step (built once; a decode step then only fills in pointers and the epoch)."""
-        plans = self._plans.get(S)
-        if plans is None:
-            native, H, ctl = self._native, Hl * self.world, 2 * self._half
-            plans = []
-            for par in (0, 1):
-                off = par * self._half
-                lse_off = off + self._out_bytes
-                q_off = lse_off + self._lse_bytes
-                plan = _Plan()
-                plan.q_all = self._local[q_off:q_off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
-                plan.out_all = self._local[off:off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
-                plan.lse_all = self._local[lse_off:lse_off + H * S * 4].view(torch.float32).view(H, S)
-                plan.gather = native.dcp_gather_params([b + q_off for b in self._bases],
-                                                       [b + ctl + 64 for b in self._bases], self._ptr + ctl + 128,
-                                                       self.rank, S, Hl, D, self.dtype)
-                plan.fold = native.dcp_fold_params([b + off for b in self._bases], [b + lse_off for b in self._bases],
-                                                   [b + ctl for b in self._bases], self.rank, S, Hl, D, self.dtype)
-                plans.append(plan)
-            self._plans[S] = plans
-        return plans
+    def _plan(self, S: int, Hl: int, D: int) -> _Plan:
+        """Per batch size: the views of the exchange buffer and the launch parameters (built once; a decode step then
+        only fills in the query / output pointers)."""
+        plan = self._plans.get(S)
+        if plan is None:
+            native, H, ctl = self._native, Hl * self.world, self._data
+            lse_off = self._out_bytes
+            q_off = lse_off + self._lse_bytes
+            plan = _Plan()
+            plan.q_all = self._local[q_off:q_off + S * H * D * self._esize].view(self.dtype).view(S, H, D)
+            plan.out_all = self._local[:S * H * D * self._esize].view(self.dtype).view(S, H, D)
+            plan.lse_all = self._local[lse_off:lse_off + H * S * 4].view(torch.float32).view(H, S)
+            step = self._ptr + ctl + 132
+            plan.gather = native.dcp_gather_params([b + q_off for b in self._bases], [b + ctl + 64 for b in self._bases],
+                                                   self._ptr + ctl + 128, self.rank, S, Hl, D, self.dtype, step)
+            plan.fold = native.dcp_fold_params(list(self._bases), [b + lse_off for b in self._bases],
+                                               [b + ctl for b in self._bases], self.rank, S, Hl, D, self.dtype, step)
+            self._plans[S] = plan
+        return plan
 
     def _gather(self, query: torch.Tensor) -> torch.Tensor:
-        """Step 1 (starts a new epoch): every rank pushes its heads into every rank's gathered query and waits for the
-        others' pushes.  Returns this rank's gathered query [S, H, D] (a view of the exchange buffer)."""
+        """Step 1 (starts a new step: the launch advances the device-side step word): every rank pushes its heads into
+        every rank's gathered query and waits for the others' pushes.  Returns this rank's gathered query [S, H, D]
+        (a view of the exchange buffer)."""
         S, Hl, D = query.shape
-        if torch.cuda.is_current_stream_capturing():
-            # the step number is a host-side kernel argument: a replayed graph would wait for a step that has long
-            # passed and read the peers' buffers unsynchronised (the C entry points refuse capture as well)
-            raise RuntimeError("DcpExchange.forward_decode cannot be captured into a CUDA graph")
-        self._epoch += 1
-        plan = self._plan(S, Hl, D)[self._epoch & 1]
+        plan = self._plan(S, Hl, D)
         if query.stride(1) != D or query.stride(2) != 1:
             query = query.contiguous()
-        self._native.dcp_gather_launch(plan.gather, query, self._epoch,
-                                       torch.cuda.current_stream(query.device).cuda_stream)
+        self._native.dcp_gather_launch(plan.gather, query, 0, torch.cuda.current_stream(query.device).cuda_stream)
         return plan.q_all
 
     def _fold(self, S: int, Hl: int, D: int, device) -> tuple[torch.Tensor, torch.Tensor]:
-        """Steps 3 + 4 of the current epoch: signal, wait, pull this rank's head slices from every peer and fold them."""
-        plan = self._plan(S, Hl, D)[self._epoch & 1]
+        """Steps 3 + 4 of the current step: signal, wait, pull this rank's head slices from every peer and fold them."""
+        plan = self._plan(S, Hl, D)
         out = torch.empty((S, Hl, D), dtype=self.dtype, device=device)
         lse = torch.empty((Hl, S), dtype=torch.float32, device=device)
-        self._native.dcp_fold_launch(plan.fold, out, lse, self._epoch, torch.cuda.current_stream(device).cuda_stream)
+        self._native.dcp_fold_launch(plan.fold, out, lse, 0, torch.cuda.current_stream(device).cuda_stream)
         return out, lse

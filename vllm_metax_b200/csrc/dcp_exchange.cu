@@ -38,6 +38,7 @@ struct DcpFoldArgs {
   float* out_lse;
   int32_t rank, world, num_seqs, heads_local, head_size;
   uint32_t epoch;
+  const uint32_t* step_counter;  // device-side step number (nullable): written by the gather of the same step
   uint64_t wait_limit_ns;
 };
 
@@ -80,19 +81,21 @@ __device__ __noinline__ void wait_timed_out(const char* what, int rank, int peer
 template <typename T>
 __global__ void __launch_bounds__(256) dcp_exchange_fold_kernel(const __grid_constant__ DcpFoldArgs a) {
   constexpr int kPack = 16 / sizeof(T);
+  // the step: a kernel argument, or the word the gather launch of this step advanced (nothing writes it during this launch)
+  const uint32_t epoch = a.step_counter != nullptr ? *a.step_counter : a.epoch;
   // 1. publish (one CTA; every CTA of this launch is past the producing attention launch)
   // (st.release.sys orders the partial — written by the previous launch on this stream — before the flag; a separate
   // membar.sys per thread on top of it cost ~10 us per launch in the first version)
-  if (blockIdx.x == 0 && threadIdx.x < a.world) st_release_sys(a.peer_flags[threadIdx.x] + a.rank, a.epoch);
+  if (blockIdx.x == 0 && threadIdx.x < a.world) st_release_sys(a.peer_flags[threadIdx.x] + a.rank, epoch);
   // 2. wait for every rank's partial
   if (threadIdx.x < a.world) {
     const uint32_t* f = a.peer_flags[a.rank] + threadIdx.x;
     const uint64_t t0 = globaltimer_ns();
     // flags only grow; the signed difference keeps the comparison right across a 2^32 wrap
     uint32_t seen;
-    while ((int32_t)((seen = ld_acquire_sys(f)) - a.epoch) < 0) {
+    while ((int32_t)((seen = ld_acquire_sys(f)) - epoch) < 0) {
       __nanosleep(64);
-      if (globaltimer_ns() - t0 > a.wait_limit_ns) wait_timed_out("exchange_fold", a.rank, (int)threadIdx.x, a.epoch, seen);
+      if (globaltimer_ns() - t0 > a.wait_limit_ns) wait_timed_out("exchange_fold", a.rank, (int)threadIdx.x, epoch, seen);
     }
   }
   __syncthreads();
@@ -160,6 +163,7 @@ struct DcpGatherArgs {
   int64_t q_stride;  // elements between sequences of `query`
   int32_t rank, world, num_seqs, heads_local, head_size;
   uint32_t epoch;
+  uint32_t* step_counter;  // device-side step number (nullable): this launch is step *step_counter + 1 and stores it back
   uint64_t wait_limit_ns;
 };
 
@@ -170,6 +174,9 @@ __global__ void __launch_bounds__(256) dcp_gather_query_kernel(const __grid_cons
   const uint64_t per_dest = (uint64_t)a.num_seqs * packs_per_seq;
   const uint64_t total = per_dest * a.world;
   const uint64_t row_all = (uint64_t)a.world * a.heads_local * a.head_size;
+  // Every CTA reads the counter before it is counted in below; the CTA that is counted in last advances it, so no CTA
+  // of this launch can see the new value and the fold launch that follows on the stream sees nothing else.
+  const uint32_t epoch = a.step_counter != nullptr ? *reinterpret_cast<volatile uint32_t*>(a.step_counter) + 1u : a.epoch;
   for (uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (uint64_t)gridDim.x * blockDim.x) {
     const uint32_t dest = idx / per_dest;
     const uint64_t rem = idx % per_dest;
@@ -193,17 +200,18 @@ __global__ void __launch_bounds__(256) dcp_gather_query_kernel(const __grid_cons
     if (last) {
       asm volatile("fence.acq_rel.sys;" ::: "memory");
       *a.cta_counter = 0;  // the next launch on this stream starts from zero
+      if (a.step_counter != nullptr) *a.step_counter = epoch;
     }
   }
   __syncthreads();
   if (!last || threadIdx.x >= a.world) return;
-  st_release_sys(a.peer_flags[threadIdx.x] + a.rank, a.epoch);
+  st_release_sys(a.peer_flags[threadIdx.x] + a.rank, epoch);
   const uint32_t* f = a.peer_flags[a.rank] + threadIdx.x;
   const uint64_t t0 = globaltimer_ns();
   uint32_t seen;
-  while ((int32_t)((seen = ld_acquire_sys(f)) - a.epoch) < 0) {
+  while ((int32_t)((seen = ld_acquire_sys(f)) - epoch) < 0) {
     __nanosleep(64);
-    if (globaltimer_ns() - t0 > a.wait_limit_ns) wait_timed_out("gather_query", a.rank, (int)threadIdx.x, a.epoch, seen);
+    if (globaltimer_ns() - t0 > a.wait_limit_ns) wait_timed_out("gather_query", a.rank, (int)threadIdx.x, epoch, seen);
   }
 }
 
@@ -215,9 +223,10 @@ uint64_t wait_limit_ns() {
   }();
   return ns;
 }
-// The step number (epoch) is a host-side kernel argument: a CUDA graph would freeze it, every `flag >= epoch` wait of a
-// replay would already be satisfied and the ranks would read each other's buffers unsynchronised.  Until the step
-// number lives in device memory the exchange kernels refuse to be captured.
+// A step number passed as a host-side kernel argument would be frozen by a CUDA graph: every `flag >= epoch` wait of a
+// replay would already be satisfied and the ranks would read each other's buffers unsynchronised.  Launches in that
+// mode refuse to be captured; with the step number in device memory (step_counter) nothing in the launch changes from
+// step to step and capture is fine.
 bool stream_is_capturing(cudaStream_t s) {
   cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
   if (cudaStreamIsCapturing(s, &st) != cudaSuccess) {
@@ -242,7 +251,8 @@ extern "C" int b200_dcp_exchange_fold(const b200_dcp_fold_params_t* p, void* str
                B200_ERR_UNSUPPORTED, "Unsupported data type of O: %d", p->dtype);
   const int pack = 16 / dtype_bytes(p->dtype);
   B200_REQUIRE(p->head_size % pack == 0, B200_ERR_UNSUPPORTED, "headsize must be multiple of pack_size:%d", pack);
-  B200_REQUIRE(p->epoch != 0, B200_ERR_INVALID_ARGUMENT, "dcp_exchange_fold: epoch 0 is the initial flag value");
+  B200_REQUIRE(p->epoch != 0 || p->step_counter != nullptr, B200_ERR_INVALID_ARGUMENT,
+               "dcp_exchange_fold: epoch 0 is the initial flag value");
   B200_REQUIRE(p->peer_out && p->peer_lse && p->peer_flags && p->out, B200_ERR_INVALID_ARGUMENT, "NULL pointer");
   DcpFoldArgs a{};
   for (int r = 0; r < p->world; ++r) {
@@ -258,10 +268,10 @@ extern "C" int b200_dcp_exchange_fold(const b200_dcp_fold_params_t* p, void* str
   a.out = p->out;
   a.out_lse = p->out_lse;
   a.rank = p->rank, a.world = p->world, a.num_seqs = p->num_seqs, a.heads_local = p->heads_local;
-  a.head_size = p->head_size, a.epoch = p->epoch;
+  a.head_size = p->head_size, a.epoch = p->epoch, a.step_counter = p->step_counter;
   a.wait_limit_ns = wait_limit_ns();
-  B200_REQUIRE(!stream_is_capturing(static_cast<cudaStream_t>(stream)), B200_ERR_UNSUPPORTED,
-               "dcp_exchange_fold cannot be captured into a CUDA graph: the step number is a host-side argument");
+  B200_REQUIRE(p->step_counter != nullptr || !stream_is_capturing(static_cast<cudaStream_t>(stream)), B200_ERR_UNSUPPORTED,
+               "dcp_exchange_fold cannot be captured into a CUDA graph with a host-side step number: pass step_counter");
   const uint64_t total = (uint64_t)p->num_seqs * p->heads_local * (p->head_size / pack);
   const int threads = 256;
   // at least one CTA even for an empty batch: the peers wait for this rank's flag
@@ -290,7 +300,8 @@ extern "C" int b200_dcp_gather_query(const b200_dcp_gather_params_t* p, void* st
                B200_ERR_UNSUPPORTED, "Unsupported data type of Q: %d", p->dtype);
   const int pack = 16 / dtype_bytes(p->dtype);
   B200_REQUIRE(p->head_size % pack == 0, B200_ERR_UNSUPPORTED, "headsize must be multiple of pack_size:%d", pack);
-  B200_REQUIRE(p->epoch != 0, B200_ERR_INVALID_ARGUMENT, "dcp_gather_query: epoch 0 is the initial flag value");
+  B200_REQUIRE(p->epoch != 0 || p->step_counter != nullptr, B200_ERR_INVALID_ARGUMENT,
+               "dcp_gather_query: epoch 0 is the initial flag value");
   B200_REQUIRE(p->peer_q && p->peer_flags && p->cta_counter && (p->query || p->num_seqs == 0), B200_ERR_INVALID_ARGUMENT,
                "NULL pointer");
   B200_REQUIRE(p->q_stride >= (int64_t)p->heads_local * p->head_size && p->q_stride % pack == 0 &&
@@ -306,10 +317,10 @@ extern "C" int b200_dcp_gather_query(const b200_dcp_gather_params_t* p, void* st
   }
   a.query = p->query, a.cta_counter = p->cta_counter, a.q_stride = p->q_stride;
   a.rank = p->rank, a.world = p->world, a.num_seqs = p->num_seqs, a.heads_local = p->heads_local;
-  a.head_size = p->head_size, a.epoch = p->epoch;
+  a.head_size = p->head_size, a.epoch = p->epoch, a.step_counter = p->step_counter;
   a.wait_limit_ns = wait_limit_ns();
-  B200_REQUIRE(!stream_is_capturing(static_cast<cudaStream_t>(stream)), B200_ERR_UNSUPPORTED,
-               "dcp_gather_query cannot be captured into a CUDA graph: the step number is a host-side argument");
+  B200_REQUIRE(p->step_counter != nullptr || !stream_is_capturing(static_cast<cudaStream_t>(stream)), B200_ERR_UNSUPPORTED,
+               "dcp_gather_query cannot be captured into a CUDA graph with a host-side step number: pass step_counter");
   const uint64_t total = (uint64_t)p->num_seqs * p->heads_local * (p->head_size / pack) * p->world;
   const int threads = 256;
   uint64_t blocks = (total + threads - 1) / threads;
