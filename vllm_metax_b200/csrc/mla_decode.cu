@@ -31,7 +31,14 @@ constexpr int kVChunks = 8;           // 512 / 64
 constexpr int kProducers = 4;         // issuing warps: one thread tops out near 47 GB/s, four reach ~120 GB/s per SM
 constexpr int kMmaWarp = 4;
 constexpr int kMlaThreads = (4 + 1 + kProducers) * 32;  // warps 0-3 softmax, 4 MMA issuer, 5-8 producers
-constexpr int kSoftmaxThreads = 128;
+// 64-head groups: four more softmax warps (12-15; warps 9-11 idle so that every role sits in whole warpgroups).  The
+// main warp and the helper warp of a TMEM lane quadrant (warp % 4) split the 64 S^T columns in two, thread = (token
+// row, head half): one softmax warp per scheduler alone left every dependent-instruction latency of a 64-column row
+// exposed (7.7 k cycles per tile against ~4 k of MMA issue).  512 threads launch with 128 registers each; the MMA /
+// producer warpgroups (warps 4-11) hand registers to the two softmax warpgroups with setmaxnreg (96 / 152).
+constexpr int kMlaThreadsWide = 16 * 32;
+constexpr int kHelperWarp0 = 12;
+__host__ __device__ constexpr int mla_threads(int NG) { return NG == 64 ? kMlaThreadsWide : kMlaThreads; }
 constexpr int kMaxSlots = 16;
 constexpr float kTau = 16.f;          // re-reference when a logit passes m_ref by 2^16
 constexpr int kMaxSplits = 256;
@@ -119,12 +126,14 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const void* tmap, int 
       ::"r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
       : "memory");
 }
-__device__ __forceinline__ void softmax_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void softmax_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(N) : "memory"); }
+template <int N>
 __device__ __forceinline__ bool softmax_bar_or(bool v) {
   uint32_t r;
-  asm volatile("{\n.reg .pred p, q;\nsetp.ne.b32 q, %1, 0;\nbar.red.or.pred p, 1, 128, q;\nselp.u32 %0, 1, 0, p;\n}\n"
+  asm volatile("{\n.reg .pred p, q;\nsetp.ne.b32 q, %1, 0;\nbar.red.or.pred p, 1, %2, q;\nselp.u32 %0, 1, 0, p;\n}\n"
                : "=r"(r)
-               : "r"((uint32_t)v)
+               : "r"((uint32_t)v), "n"(N)
                : "memory");
   return r != 0;
 }
@@ -348,7 +357,7 @@ __device__ __forceinline__ MlaSeg mla_flat_next(const MlaParams& p, const MlaFla
 // products; the probabilities go to the tensor core as TWO e4m3 terms (hi = rn(p), lo = rn(p - hi): ~7 bits, where one
 // term would miss the reference's own fp8 tolerance on short contexts) with p scaled to at most 2^8.
 template <int NG, bool FP8>
-__global__ void __launch_bounds__(kMlaThreads, 1)
+__global__ void __launch_bounds__(mla_threads(NG), 1)
 mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, const __grid_constant__ TmaDesc tm_qn,
                   const __grid_constant__ TmaDesc tm_qp) {
   constexpr int KC = FP8 ? 5 : kKChunks;           // K chunks per tile (16 KiB each)
@@ -360,6 +369,10 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   constexpr float kTauX = FP8 ? 3.f : kTau;
   constexpr float kShift = FP8 ? 5.f : 0.f;
   constexpr float kHead = FP8 ? 2.f : 0.f;
+  constexpr int NTHR = mla_threads(NG);              // threads of the CTA
+  constexpr bool SW2 = NG == 64;                     // two softmax threads per token row (helper warps 12-15)
+  constexpr int NS = SW2 ? 256 : 128;                // softmax threads
+  constexpr int CT = SW2 ? 32 : NG;                  // S^T columns (heads) per softmax thread
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   __shared__ MlaFlatStart fstart;
   if (!p.flat) {
@@ -368,7 +381,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     if (L <= 0) {  // empty sequence: zeros and lse = -inf, written by the split-0 CTAs
       if (split == 0) {
         const int h0 = group * NG, nh = min(NG, p.H - h0);
-        for (int i = tid; i < nh * 512; i += kMlaThreads) {
+        for (int i = tid; i < nh * 512; i += NTHR) {
           const long long o = (long long)seq * p.out_seq_stride + (long long)(h0 + i / 512) * p.out_head_stride + i % 512;
           if (p.f16) reinterpret_cast<__half*>(p.out)[o] = __float2half_rn(0.f);
           else reinterpret_cast<__nv_bfloat16*>(p.out)[o] = __float2bfloat16_rn(0.f);
@@ -381,7 +394,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   }
   if (p.flat) {
     mla_flat_prologue(p, fstart, kTile, p.groups, (int)gridDim.x, (int)blockIdx.x, 20,
-                      blockIdx.x == 0, tid, kMlaThreads, 1, 0);
+                      blockIdx.x == 0, tid, NTHR, 1, 0);
     if (fstart.u0 >= fstart.u1) return;   // more CTAs than units
   }
   // the segment walk: every role runs the same deterministic sequence
@@ -423,14 +436,14 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&misc->s_full[i]), 1);
-      mbar_init(smem_u32(&misc->s_free[i]), kSoftmaxThreads);
+      mbar_init(smem_u32(&misc->s_free[i]), NS);
     }
-    mbar_init(smem_u32(&misc->p_full), kSoftmaxThreads);
+    mbar_init(smem_u32(&misc->p_full), NS);
     mbar_init(smem_u32(&misc->p_free), 1);
     mbar_init(smem_u32(&misc->o_full), 1);
     mbar_init(smem_u32(&misc->q_full), 1);
     mbar_init(smem_u32(&misc->q_free), 1);               // the segment's last S^T product has read the query
-    mbar_init(smem_u32(&misc->o_free), kSoftmaxThreads); // the segment's O^T has been read out
+    mbar_init(smem_u32(&misc->o_free), NS); // the segment's O^T has been read out
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   constexpr uint32_t kCols = NG == 64 ? 512 : (NG == 32 ? 256 : 128);  // power of two >= 6 * NG
@@ -459,7 +472,10 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   // Tile-indexed barriers (S^T buffers, P^T) run on a tile counter that continues across segments; segment-indexed
   // ones (query, O^T) on the segment counter.
   const int npairs = nslots >> 1;
-  if (warp > kMmaWarp) {
+  // (setmaxnreg sits at the head of each role's own branch: ptxas sizes the register file of a region by the
+  // setmaxnreg that dominates it, and code after a join of a 96- and a 152-register path gets the smaller one)
+  if (warp > kMmaWarp && warp <= kMmaWarp + kProducers) {
+    if constexpr (SW2) asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
     // =================== TMA producers: half-pair f of the ring sequence is filled by producer f % kProducers ===================
     const int pw = warp - kMmaWarp - 1;
     if (lane == 0) {
@@ -520,7 +536,11 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
         }
       }
     }
+  } else if (SW2 && warp > kMmaWarp + kProducers && warp < kHelperWarp0) {
+    // idle warps of the MMA / producer warpgroups
+    if constexpr (SW2) asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
   } else if (warp == kMmaWarp) {
+    if constexpr (SW2) asm volatile("setmaxnreg.dec.sync.aligned.u32 96;\n");
     // =================== MMA issuer (one lane) ===================
     if (lane == 0) {
       const int fmt = p.f16 ? 0 : 1;
@@ -650,10 +670,15 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     }
     __syncwarp();
   } else {
-    // =================== softmax / epilogue warps (0..3): thread = one token row = one TMEM lane ===================
+    // =================== softmax / epilogue warps: thread = one token row = one TMEM lane ===================
+    // warps 0..3 and, for 64-head groups, the helper warps 12..15: the main warp of a quadrant takes columns 0..31,
+    // the helper columns 32..63
+    if constexpr (SW2) asm volatile("setmaxnreg.inc.sync.aligned.u32 152;\n");
+    const bool helper = SW2 && warp >= kHelperWarp0;
     const int quad = warp & 3;                   // TMEM lane quadrant this warp may access
     const int row = quad * 32 + lane;            // token row within the tile / dv row within an O^T block
-    const int st = tid;                          // 0..127
+    const int st = helper ? 128 + (warp - kHelperWarp0) * 32 + lane : tid;   // 0..NS-1; per-head work: st < NG
+    const int cbase = helper ? 32 : 0;           // first S^T / O^T column of this thread
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     constexpr int HC = NG < 32 ? NG : 32;        // columns handled per pass (register budget)
     long long done = 0;
@@ -663,11 +688,11 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     const int t0 = g.tile0 * kTile, t1 = min(g.L, g.tile1 * kTile), T = g.tile1 - g.tile0;
     const int h0 = g.group * NG;
     const int nh = min(NG, p.H - h0);           // real heads of this group
-    float lsum[NG];
+    float lsum[CT];
 #pragma unroll
-    for (int h = 0; h < NG; ++h) lsum[h] = 0.f;
+    for (int h = 0; h < CT; ++h) lsum[h] = 0.f;
     if (st < 64) misc->mref[st] = -INFINITY;
-    softmax_bar_sync();
+    softmax_bar_sync<NS>();
 
     for (int i = 0; i < T; ++i, ++gt) {
       const int b = gt & 1;
@@ -678,7 +703,8 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
       // ---- pass 1: does any logit pass its reference by kTau?  (S^T is read again in pass 2: TMEM reads are cheap) ----
       bool over = false;
 #pragma unroll
-      for (int c0 = 0; c0 < NG; c0 += HC) {
+      for (int cc = 0; cc < CT; cc += HC) {
+        const int c0 = cbase + cc;
         uint32_t r[HC];
         tmem_ld<HC>(tm_s[b] + c0 + lane_base, r);
         tmem_ld_wait();
@@ -690,10 +716,11 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
         for (int h = 0; h < HC; ++h)
           over |= valid && __uint_as_float(r[h]) * p.scale_log2 > misc->mref[c0 + h] + kTauX;
       }
-      if (softmax_bar_or(over)) {
+      if (softmax_bar_or<NS>(over)) {
         // ---- rare path: raise the references to this tile's column maxima, rescale O^T and the running sums ----
 #pragma unroll
-        for (int c0 = 0; c0 < NG; c0 += HC) {
+        for (int cc = 0; cc < CT; cc += HC) {
+          const int c0 = cbase + cc;
           uint32_t r[HC];
           tmem_ld<HC>(tm_s[b] + c0 + lane_base, r);
           tmem_ld_wait();
@@ -701,10 +728,10 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           for (int h = 0; h < HC; ++h) {
             const float x = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
             const int m = __reduce_max_sync(0xffffffffu, f32_sortable(x));
-            if (lane == 0) misc->colmax[warp][c0 + h] = m;
+            if (lane == 0) misc->colmax[quad][c0 + h] = m;
           }
         }
-        softmax_bar_sync();
+        softmax_bar_sync<NS>();
         if (st < NG) {
           const int m = max(max(misc->colmax[0][st], misc->colmax[1][st]), max(misc->colmax[2][st], misc->colmax[3][st]));
           const float m_old = misc->mref[st];
@@ -713,15 +740,16 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           misc->fac[st] = m_old == -INFINITY ? 0.f : exp2f(m_old - m_new);
           misc->mref[st] = m_new;
         }
-        softmax_bar_sync();
+        softmax_bar_sync<NS>();
 #pragma unroll
-        for (int h = 0; h < NG; ++h) lsum[h] *= misc->fac[h];
+        for (int h = 0; h < CT; ++h) lsum[h] *= misc->fac[cbase + h];
         if (i > 0) {
           mbar_wait(smem_u32(&misc->p_free), (gt - 1) & 1);  // P.V of the previous tile has landed in O^T
           tc_fence_after();
           for (int j = 0; j < 4; ++j) {
 #pragma unroll
-            for (int c = 0; c < NG; c += 16) {
+            for (int cl = 0; cl < CT; cl += 16) {
+              const int c = cbase + cl;
               uint32_t o[16];
               tmem_ld<16>(tm_o + j * NG + c + lane_base, o);
               tmem_ld_wait();
@@ -742,11 +770,12 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
       const uint32_t unit = FP8 ? (uint32_t)(row >> 4) : (uint32_t)((row & 63) >> 3);
       const uint32_t within = FP8 ? (uint32_t)(row & 15) : (uint32_t)((row & 7) * 2);
 #pragma unroll
-      for (int c0 = 0; c0 < NG; c0 += HC) {
+      for (int cc = 0; cc < CT; cc += HC) {
+        const int c0 = cbase + cc;
         uint32_t r[HC];
         tmem_ld<HC>(tm_s[b] + c0 + lane_base, r);
         tmem_ld_wait();
-        if (c0 + HC == NG) {   // last read of this S^T buffer
+        if (cc + HC == CT) {   // this thread's last read of this S^T buffer
           tc_fence_before();
           mbar_arrive(smem_u32(&misc->s_free[b]));
         }
@@ -761,7 +790,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
             for (int e = 0; e < 4; ++e) {
               const float x = valid ? __uint_as_float(r[h + e]) * p.scale_log2 : -INFINITY;
               pv[e] = fast_exp2(x - misc->mref[c0 + h + e] + kShift);
-              lsum[c0 + h + e] += pv[e];
+              lsum[cc + h + e] += pv[e];
             }
             const uint32_t hi01 = cvt_e4m3x2(pv[0], pv[1]), hi23 = cvt_e4m3x2(pv[2], pv[3]);
             const float2 f01 = e4m3x2_to_f32x2(hi01), f23 = e4m3x2_to_f32x2(hi23);
@@ -769,8 +798,8 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
             r[h] = hi01 | (hi23 << 16);        // bytes = heads h .. h+3 of this token, hi term
             r[h + 1] = lo01 | (lo23 << 16);    // lo term
           }
-          if (c0 == 0 && gt > 0) mbar_wait(smem_u32(&misc->p_free), (gt - 1) & 1);
-          if (c0 == 0 && tid == 0) stamp(1, gt, 2);
+          if (cc == 0 && gt > 0) mbar_wait(smem_u32(&misc->p_free), (gt - 1) & 1);
+          if (cc == 0 && tid == 0) stamp(1, gt, 2);
 #pragma unroll
           for (int h = 0; h < HC; h += 4) {
             const uint32_t thi = quad_transpose_bytes(r[h], lane), tlo = quad_transpose_bytes(r[h + 1], lane);
@@ -784,11 +813,11 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           for (int h = 0; h < HC; ++h) {
             const float x = valid ? __uint_as_float(r[h]) * p.scale_log2 : -INFINITY;
             const float pv = fast_exp2(x - misc->mref[c0 + h] + kShift);
-            lsum[c0 + h] += pv;
+            lsum[cc + h] += pv;
             r[h] = p.f16 ? (uint32_t)__half_as_ushort(__float2half_rn(pv)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(pv));
           }
-          if (c0 == 0 && gt > 0) mbar_wait(smem_u32(&misc->p_free), (gt - 1) & 1);
-          if (c0 == 0 && tid == 0) stamp(1, gt, 2);
+          if (cc == 0 && gt > 0) mbar_wait(smem_u32(&misc->p_free), (gt - 1) & 1);
+          if (cc == 0 && tid == 0) stamp(1, gt, 2);
 #pragma unroll
           for (int h = 0; h < HC; ++h) {
             const uint32_t addr = chunk + (c0 + h) * 128 + ((unit ^ (h & 7)) << 4) + within;
@@ -809,15 +838,15 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     {
       float* wsum = reinterpret_cast<float*>(&misc->colmax[0][0]);   // [4 warps][64]: per-warp column sums
 #pragma unroll
-      for (int h = 0; h < NG; ++h) {
+      for (int h = 0; h < CT; ++h) {
         float v = lsum[h];
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (lane == 0) wsum[warp * 64 + h] = v;
+        if (lane == 0) wsum[quad * 64 + cbase + h] = v;
       }
-      softmax_bar_sync();
+      softmax_bar_sync<NS>();
       if (st < NG) misc->fac[st] = wsum[st] + wsum[64 + st] + wsum[128 + st] + wsum[192 + st];
-      softmax_bar_sync();
+      softmax_bar_sync<NS>();
     }
     if (tid == 0) stamp(2, nseg, 2);
     const bool direct = g.tile0 == 0 && g.tile1 == g.tiles_seq;
@@ -836,9 +865,9 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
         }
       }
     }
-    softmax_bar_sync();
+    softmax_bar_sync<NS>();
     if (st < NG) misc->fac[st] = 1.f / misc->fac[st];
-    softmax_bar_sync();
+    softmax_bar_sync<NS>();
     // O^T -> global: one base pointer and one stride per mode, chosen once (the per-element form of this loop, with
     // its 64-bit index arithmetic and mode branches, took 50-90 k cycles per segment)
     {
@@ -846,7 +875,8 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
         for (int j = 0; j < 4; ++j) {
           const int dv = j * 128 + row;
 #pragma unroll
-          for (int c = 0; c < NG; c += 16) {
+          for (int cl = 0; cl < CT; cl += 16) {
+            const int c = cbase + cl;
             uint32_t o[16];
             tmem_ld<16>(tm_o + j * NG + c + lane_base, o);
             tmem_ld_wait();
@@ -875,7 +905,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     tc_fence_before();
     if (tid == 0) stamp(2, nseg, 3);
     mbar_arrive(smem_u32(&misc->o_free));   // O^T may be overwritten by the next segment
-    softmax_bar_sync();                      // fac / mref / the scratch are reused by the next segment
+    softmax_bar_sync<NS>();                  // fac / mref / the scratch are reused by the next segment
     }
   }
 
@@ -1709,7 +1739,7 @@ int launch_mla(const MlaParams& mp, const TmaDesc& kv, const TmaDesc& qn, const 
     }
     configured_device = dev;
   }
-  kern<<<grid, kMlaThreads, smem, s>>>(mp, kv, qn, qp);
+  kern<<<grid, mla_threads(NG), smem, s>>>(mp, kv, qn, qp);
   count_launch();
   return check_launch("mla_decode");
 }
