@@ -275,6 +275,7 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
   constexpr bool kPrefetchQ = !FLAT && NT == 1;
   Seg it, nx;
   int item = -1;
+  [[maybe_unused]] int seen_cnt = 0;  // flat schedule, thread 0: arrival counter of the segment's pair as the segment began
   bool has = next_item(nx);
   if (kPrefetchQ && has) q_issue(nx);
   while (has) {
@@ -282,6 +283,15 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
     ++item;
     const int ntiles = (it.t1 - it.t0 + kTileTokens - 1) / kTileTokens;
     if constexpr (!kPrefetchQ) q_issue(it);
+    if constexpr (FLAT) {
+      // A piece of a split pair: have ALL the other pieces been delivered already?  Then this CTA is the one that
+      // merges, and it can do so straight from its own result — no partial written, no fence, no counter round trip
+      // (the case of nearly every CTA's LAST segment: the rest of that pair was the next CTA's FIRST segment, long
+      // done).  The counter is read now — the load is in flight during the tile loop, its value is looked at when the
+      // segment ends — so the answer can only turn out pessimistic.
+      if (tid == 0 && !(it.starts && it.ends))
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen_cnt) : "l"(p.counters + it.s * p.Hkv + it.kvh) : "memory");
+    }
     q_finish(it);
     const bool use_alibi = p.alibi != nullptr;
 
@@ -599,6 +609,16 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
         }
       }
     }
+    if constexpr (FLAT) {
+      if (tid == 0 && !(it.starts && it.ends)) {
+        // c0 .. c1: the ranges (static shares and dynamic chunks, numbered in tile order) that hold a piece of this pair
+        const int c0 = range_of_tile(sched, it.pb);
+        const int c1 = range_of_tile(sched, it.pb + it.n - 1);
+        merge_flag[1] = seen_cnt == c1 - c0;
+        merge_flag[2] = c0;
+        merge_flag[3] = c1;
+      }
+    }
     consumer_bar_sync();
     const int d = tid & (kD - 1);
     if constexpr (!FLAT) {
@@ -643,6 +663,10 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
       // as the reference reduce, csrc/attention/attention_kernels.cuh:594-657) ----------------------------
       const bool whole = it.starts && it.ends;
       const int slot = (it.rid * 2 + (it.starts ? 1 : 0)) * p.G;
+      // split pair (the values were written by thread 0 when the segment began, barriers in between)
+      const bool fast = !whole && merge_flag[1] != 0;
+      const int c0 = merge_flag[2], c1 = merge_flag[3];
+      if (fast) __threadfence();  // acquire side: the other pieces' partials, published before the counter moved
       for (int h = tid >> 7; h < NH; h += (kConsumerWarps * kWarpSize) >> 7) {
         if (h >= p.G) break;
         float M = -INFINITY;
@@ -656,7 +680,24 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
           o = fmaf(merge_o[(w * NH + h) * kMergeStride + d], wgt, o);
         }
         o *= vsc;
-        if (whole) {
+        if (fast) {
+          // the merge of the `last` path below, with this CTA's piece taken from registers instead of its slot:
+          // same operands, same order (ranges c0 .. c1), hence the same bits
+          float Mg = M;
+          for (int c = c0; c <= c1; ++c)
+            if (c != it.rid) Mg = fmaxf(Mg, __ldcg(p.ws_m + (c * 2 + (c == c0 ? 1 : 0)) * p.G + h));
+          float lg = 0.f, og = 0.f;
+          for (int c = c0; c <= c1; ++c) {
+            const int sl = (c * 2 + (c == c0 ? 1 : 0)) * p.G + h;
+            const bool mine = c == it.rid;
+            const float wgt = exp2f((mine ? M : __ldcg(p.ws_m + sl)) - Mg);
+            lg = fmaf(mine ? lsum : __ldcg(p.ws_l + sl), wgt, lg);
+            og = fmaf(mine ? o : __ldcg(p.ws_o + (int64_t)sl * kD + d), wgt, og);
+          }
+          p.out[((int64_t)it.s * p.H + it.kvh * p.G + h) * kD + d] = __float2bfloat16_rn(og * __fdividef(1.f, lg + 1e-6f));
+          if (d == 0 && p.lse != nullptr)
+            p.lse[(int64_t)(it.kvh * p.G + h) * p.S + it.s] = fmaf(Mg, kLn2, logf(lg));
+        } else if (whole) {
           p.out[((int64_t)it.s * p.H + it.kvh * p.G + h) * kD + d] =
               __float2bfloat16_rn(o * __fdividef(1.f, lsum + 1e-6f));
           if (d == 0 && p.lse != nullptr)
@@ -669,12 +710,11 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
           }
         }
       }
-      if (!whole) {
+      if (fast) {
+        if (tid == 0) p.counters[it.s * p.Hkv + it.kvh] = 0;  // leave the counters zeroed for the next launch
+      } else if (!whole) {
         __threadfence();       // this thread's partials are visible device-wide
         consumer_bar_sync();   // ... and so are everyone's
-        // ranges (static shares and dynamic chunks, numbered in tile order) that hold a piece of this pair
-        const int c0 = range_of_tile(sched, it.pb);
-        const int c1 = range_of_tile(sched, it.pb + it.n - 1);
         if (tid == 0) {
           int* cnt = p.counters + it.s * p.Hkv + it.kvh;
           const int old = atomicAdd(cnt, 1);
