@@ -101,7 +101,7 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
     g_timeline[blockIdx.x][5] = smid;  // tools/timeline_probe.py --per-sm
   }
 #endif
-  if (tid == 0) {
+  if (tid == 32) {  // not warp 0: that one computes the schedule meanwhile
     for (int i = 0; i < nst; ++i) {
       mbar_init(full_u32 + 8u * i, 1);
       mbar_init(empty_u32 + 8u * i, 1);

@@ -245,12 +245,25 @@ __device__ __forceinline__ int range_of_tile(const Sched* sc, long long x) {
   return sc->neff * (1 + sc->nlev) - 1;  // not reached for x < T
 }
 __device__ void compute_sched(const StreamParams& p, Sched* sc, int lane) {
-  // tiles per kv head before every 32nd sequence, and the total
+  // tiles per kv head before every 32nd sequence, and the total.  Four blocks of 32 lengths are fetched before any is
+  // used: this is the first global access of a CTA that has just started (a miss all the way to HBM, ~1 us), and the
+  // kernel cannot issue a single KV byte before the schedule is known.
   long long running = 0;
-  for (int b = 0; b < p.S; b += 32) {
-    const long long n = b + lane < p.S ? tiles_of(__ldg(p.seq_lens + b + lane)) : 0;
-    if (lane == 0 && (b >> 5) <= kSeqBlocks) sc->blkpre[b >> 5] = running;
-    running += warp_sum_ll(n);
+  for (int b = 0; b < p.S; b += 128) {
+    int n4[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = b + 32 * k + lane;
+      n4[k] = i < p.S ? tiles_of(__ldg(p.seq_lens + i)) : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int bb = b + 32 * k;
+      if (bb < p.S) {
+        if (lane == 0 && (bb >> 5) <= kSeqBlocks) sc->blkpre[bb >> 5] = running;
+        running += __reduce_add_sync(0xffffffffu, n4[k]);  // 32 sequences of < 2^26 tiles each
+      }
+    }
   }
   if (lane == 0 && ((p.S + 31) >> 5) <= kSeqBlocks) sc->blkpre[(p.S + 31) >> 5] = running;
   const long long T = running * p.Hkv;
@@ -278,10 +291,10 @@ __device__ void compute_sched(const StreamParams& p, Sched* sc, int lane) {
   running = 0;  // tiles per kv head before sequence `b`
   for (int b = 0; b < p.S; b += 32) {
     const int n = b + lane < p.S ? tiles_of(__ldg(p.seq_lens + b + lane)) : 0;
-    long long incl = n;
+    int incl = n;
 #pragma unroll
     for (int m = 1; m < 32; m <<= 1) {
-      const long long o = __shfl_up_sync(0xffffffffu, incl, m);
+      const int o = __shfl_up_sync(0xffffffffu, incl, m);
       if (lane >= m) incl += o;
     }
     const long long lo = (running + incl - n) * p.Hkv, hi = (running + incl) * p.Hkv;
