@@ -45,6 +45,9 @@ struct DcpFoldArgs {
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -168,7 +171,7 @@ struct DcpGatherArgs {
 };
 
 template <typename T>
-__global__ void __launch_bounds__(256) dcp_gather_query_kernel(const __grid_constant__ DcpGatherArgs a) {
+__global__ void __launch_bounds__(1024) dcp_gather_query_kernel(const __grid_constant__ DcpGatherArgs a) {
   constexpr int kPack = 16 / sizeof(T);
   const uint32_t packs_per_seq = a.heads_local * a.head_size / kPack;  // the local heads of a sequence are contiguous
   const uint64_t per_dest = (uint64_t)a.num_seqs * packs_per_seq;
@@ -193,19 +196,31 @@ __global__ void __launch_bounds__(256) dcp_gather_query_kernel(const __grid_cons
   // below in the PTX memory model and not only in practice.
   __syncthreads();
   __shared__ bool last;
-  if (threadIdx.x == 0) {
+  if (gridDim.x == 1) {
+    // One CTA (decode-sized batches): no counter round trip.  The barrier orders every thread's peer stores before
+    // the fence of each signalling thread; the flag store after the fence can then be relaxed (fence + store is the
+    // release pattern), which saves the second MEMBAR.SYS a st.release would issue.
+    if (threadIdx.x == 0 && a.step_counter != nullptr) *a.step_counter = epoch;
+    if (threadIdx.x >= a.world) return;
     asm volatile("fence.acq_rel.sys;" ::: "memory");
-    const uint32_t prev = atomicAdd(a.cta_counter, 1u);
-    last = prev == gridDim.x - 1;
-    if (last) {
+    st_relaxed_sys(a.peer_flags[threadIdx.x] + a.rank, epoch);
+  } else {
+    if (threadIdx.x == 0) {
       asm volatile("fence.acq_rel.sys;" ::: "memory");
-      *a.cta_counter = 0;  // the next launch on this stream starts from zero
-      if (a.step_counter != nullptr) *a.step_counter = epoch;
+      const uint32_t prev = atomicAdd(a.cta_counter, 1u);
+      last = prev == gridDim.x - 1;
+      if (last) {
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+        *a.cta_counter = 0;  // the next launch on this stream starts from zero
+        if (a.step_counter != nullptr) *a.step_counter = epoch;
+      }
     }
+    __syncthreads();
+    if (!last || threadIdx.x >= a.world) return;
+    // ordered after the other CTAs' stores by the fence above (thread 0, then the barrier): the fence of this store's
+    // own release is what orders it for the threads other than thread 0
+    st_release_sys(a.peer_flags[threadIdx.x] + a.rank, epoch);
   }
-  __syncthreads();
-  if (!last || threadIdx.x >= a.world) return;
-  st_release_sys(a.peer_flags[threadIdx.x] + a.rank, epoch);
   const uint32_t* f = a.peer_flags[a.rank] + threadIdx.x;
   const uint64_t t0 = globaltimer_ns();
   uint32_t seen;
@@ -322,9 +337,12 @@ extern "C" int b200_dcp_gather_query(const b200_dcp_gather_params_t* p, void* st
   B200_REQUIRE(p->step_counter != nullptr || !stream_is_capturing(static_cast<cudaStream_t>(stream)), B200_ERR_UNSUPPORTED,
                "dcp_gather_query cannot be captured into a CUDA graph with a host-side step number: pass step_counter");
   const uint64_t total = (uint64_t)p->num_seqs * p->heads_local * (p->head_size / pack) * p->world;
-  const int threads = 256;
+  // up to 16 packs per thread in ONE CTA of 1024 threads (decode batches): the single-CTA path has no CTA counter
+  // round trip and one system fence fewer; beyond that, 64 CTAs of 256
+  int threads = 256;
   uint64_t blocks = (total + threads - 1) / threads;
   blocks = blocks < 1 ? 1 : (blocks > 64 ? 64 : blocks);
+  if (total <= 16 * 1024) threads = total <= 256 ? 256 : 1024, blocks = 1;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (p->dtype) {
     case B200_DTYPE_F32: dcp_gather_query_kernel<float><<<(unsigned)blocks, threads, 0, s>>>(a); break;
