@@ -189,7 +189,7 @@ def test_flat_schedule_one_long_sequence_among_short_ones(ops, H):
     check(out, lse, ref_out, ref_lse, torch.bfloat16)
 
 
-@pytest.mark.parametrize("H", [16, 64, 128])
+@pytest.mark.parametrize("H", [16, 32, 64, 128])
 @pytest.mark.parametrize("L", [100, 1500, 5000])
 def test_fp8_e4m3_inputs(ops, H, L):
     """the float8_e4m3fn form of the reference op (tests/kernels/attention/test_cutlass_mla_decode.py:53-58,91-101):

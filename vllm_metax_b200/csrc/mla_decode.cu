@@ -373,6 +373,12 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
   constexpr bool SW2 = NG == 64;                     // two softmax threads per token row (helper warps 12-15)
   constexpr int NS = SW2 ? 256 : 128;                // softmax threads
   constexpr int CT = SW2 ? 32 : NG;                  // S^T columns (heads) per softmax thread
+  // fp8, groups of <= 32 heads: the two e4m3 terms of P^T ([NG rows hi | NG rows lo], contiguous in shared memory) go to
+  // the tensor core as ONE B operand of 2 NG rows, so an O^T step is one instruction instead of two (an instruction
+  // with a shared-memory A operand costs the same for any N); the hi and lo products land in separate TMEM columns and
+  // are added in the epilogue.  64-head groups have no TMEM columns to spare for that (2 NG + 4 * 2 NG > 512).
+  constexpr bool MT = FP8 && NG <= 32;
+  constexpr int NO = MT ? 2 * NG : NG;               // TMEM columns of one 128-row O^T block
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   __shared__ MlaFlatStart fstart;
   if (!p.flat) {
@@ -446,7 +452,9 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     mbar_init(smem_u32(&misc->o_free), NS); // the segment's O^T has been read out
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  constexpr uint32_t kCols = NG == 64 ? 512 : (NG == 32 ? 256 : 128);  // power of two >= 6 * NG
+  constexpr uint32_t kColsNeed = 2 * NG + 4 * NO;
+  constexpr uint32_t kCols = kColsNeed <= 128 ? 128 : (kColsNeed <= 256 ? 256 : 512);  // power of two
+  static_assert(kColsNeed <= 512, "TMEM columns");
   if (warp == kMmaWarp) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&misc->tmem_base)),
                  "r"(kCols)
@@ -545,7 +553,7 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
     if (lane == 0) {
       const int fmt = p.f16 ? 0 : 1;
       const uint32_t idesc_s = FP8 ? idesc_f8(128, NG, 0) : idesc_f16(128, NG, fmt, 0);
-      const uint32_t idesc_o = FP8 ? idesc_f8(128, NG, 1) : idesc_f16(128, NG, fmt, 1);
+      const uint32_t idesc_o = FP8 ? idesc_f8(128, NO, 1) : idesc_f16(128, NG, fmt, 1);
       int pair = 0;
       uint32_t phase = 0;
       auto advance = [&]() {
@@ -629,17 +637,18 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
 #pragma unroll
               for (int hlf = 0; hlf < 2; ++hlf) {
                 const uint32_t a_lo = desc_lo(a_addr + hlf * kChunkBytes, 0);
-                const uint32_t d_o = tm_o + (2 * j + hlf) * NG;
+                const uint32_t d_o = tm_o + (2 * j + hlf) * NO;
 #pragma unroll
                 for (int ks = 0; ks < 4; ++ks)
                   if (ks < ksteps) {
                     umma_f8(d_o, a_lo + ((ks * 4096) >> 4), kDescHiSw128, p_lo + ((ks * 32) >> 4), kDescHiSw128, idesc_o, (i | ks) != 0);
-                    umma_f8(d_o, a_lo + ((ks * 4096) >> 4), kDescHiSw128, p_lo + ((NG * 128 + ks * 32) >> 4), kDescHiSw128, idesc_o, 1);
+                    if constexpr (!MT)   // the lo term as a second product into the same columns
+                      umma_f8(d_o, a_lo + ((ks * 4096) >> 4), kDescHiSw128, p_lo + ((NG * 128 + ks * 32) >> 4), kDescHiSw128, idesc_o, 1);
                   }
               }
             } else {
               const uint32_t a_lo = desc_lo(a_addr, kChunkBytes);
-              const uint32_t d_o = tm_o + j * NG;
+              const uint32_t d_o = tm_o + j * NO;
 #pragma unroll
               for (int ks = 0; ks < 8; ++ks)
                 if (ks < ksteps)
@@ -750,12 +759,15 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
 #pragma unroll
             for (int cl = 0; cl < CT; cl += 16) {
               const int c = cbase + cl;
-              uint32_t o[16];
-              tmem_ld<16>(tm_o + j * NG + c + lane_base, o);
-              tmem_ld_wait();
 #pragma unroll
-              for (int e = 0; e < 16; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * misc->fac[c + e]);
-              tmem_st16(tm_o + j * NG + c + lane_base, o);
+              for (int t = 0; t < (MT ? 2 : 1); ++t) {   // merged terms: the hi columns, then the lo columns
+                uint32_t o[16];
+                tmem_ld<16>(tm_o + j * NO + t * NG + c + lane_base, o);
+                tmem_ld_wait();
+#pragma unroll
+                for (int e = 0; e < 16; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) * misc->fac[c + e]);
+                tmem_st16(tm_o + j * NO + t * NG + c + lane_base, o);
+              }
             }
           }
           tmem_st_wait();
@@ -878,8 +890,16 @@ mla_decode_kernel(const MlaParams p, const __grid_constant__ TmaDesc tm_kv, cons
           for (int cl = 0; cl < CT; cl += 16) {
             const int c = cbase + cl;
             uint32_t o[16];
-            tmem_ld<16>(tm_o + j * NG + c + lane_base, o);
-            tmem_ld_wait();
+            tmem_ld<16>(tm_o + j * NO + c + lane_base, o);
+            if constexpr (MT) {   // O^T = hi products + lo products
+              uint32_t o2[16];
+              tmem_ld<16>(tm_o + j * NO + NG + c + lane_base, o2);
+              tmem_ld_wait();
+#pragma unroll
+              for (int e = 0; e < 16; ++e) o[e] = __float_as_uint(__uint_as_float(o[e]) + __uint_as_float(o2[e]));
+            } else {
+              tmem_ld_wait();
+            }
 #pragma unroll
             for (int e = 0; e < 16; ++e)
               if (c + e < nh) put(c + e, dv, __uint_as_float(o[e]) * misc->fac[c + e]);
