@@ -506,6 +506,12 @@ paged_attention_stream_kernel(const __grid_constant__ StreamParams p) {
       }
     }
     for (int ti = PW ? ntiles : (int)((warp - tile_base) & (kConsumerWarps - 1)); ti < ntiles; ti += kConsumerWarps) {
+      if constexpr (FLAT) {
+        // the arrival counter once more, one tile of this warp (~8 tiles of the CTA) before the segment ends: a piece
+        // whose partner was still running when the segment began (pairs longer than a CTA's share) may have it now
+        if (tid == 0 && ti + kConsumerWarps >= ntiles && !(it.starts && it.ends))
+          asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen_cnt) : "l"(p.counters + it.s * p.Hkv + it.kvh) : "memory");
+      }
       // this warp's tiles are gt = warp, warp + 8, ... over the whole stream, so stage / parity advance
       // incrementally (no division by the runtime ring depth)
       MBAR_WAIT(full_u32 + 8u * stage, parity, 2, item, (int)(tile_base + (uint32_t)ti));
